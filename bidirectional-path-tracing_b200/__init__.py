@@ -1,0 +1,335 @@
+"""bidirectional-path-tracing_b200 -- Python face of the B200-native BDPT hot path.
+
+This package is plumbing only: it loads the in-tree ``libtrb.so`` (host C++ + sm_100a CUDA kernels, built by
+``build.py``) and exposes the C ABI of ``include/trb.h`` through ctypes with numpy buffers.  The package
+name contains a hyphen, import it with ``importlib.import_module("bidirectional-path-tracing_b200")``.
+
+There is deliberately NO fallback: if the library is missing the import of :func:`lib` raises, and every
+compute call fails with ``TrbError`` when no CUDA device is usable.  Nothing under ``oracle/`` is imported
+from here (the oracle is test infrastructure).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "libtrb.so"
+
+TRB_OK = 0
+TRB_FLAG_NO_JITTER = 1
+
+
+class TrbError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"trb error {code}: {msg}")
+        self.code = code
+
+
+# ---- ctypes mirrors of include/trb.h -----------------------------------------------------------------
+class Material(C.Structure):
+    _fields_ = [("kd", C.c_float * 3), ("ks", C.c_float * 3), ("ke", C.c_float * 3), ("tf", C.c_float * 3),
+                ("ns", C.c_float), ("ni", C.c_float), ("illum", C.c_int32), ("_pad", C.c_int32)]
+
+
+class SceneDesc(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("n_positions", C.c_size_t),
+                ("normals", C.c_void_p), ("n_normals", C.c_size_t),
+                ("tri_v", C.c_void_p), ("tri_n", C.c_void_p), ("tri_mat", C.c_void_p), ("tri_shape", C.c_void_p),
+                ("n_tris", C.c_size_t),
+                ("materials", C.c_void_p), ("n_materials", C.c_size_t), ("n_shapes", C.c_size_t)]
+
+
+class RenderDesc(C.Structure):
+    _fields_ = [("eye", C.c_float * 3), ("at", C.c_float * 3), ("up", C.c_float * 3), ("fov_deg", C.c_float),
+                ("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("rr_depth", C.c_int32),
+                ("spp_begin", C.c_int32), ("spp_end", C.c_int32), ("seed", C.c_uint32), ("flags", C.c_uint32),
+                ("wave_samples", C.c_int64)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("ms_trace_closest", C.c_double), ("ms_trace_any", C.c_double),
+                ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
+                ("rays_any", C.c_uint64), ("launches", C.c_uint64), ("node_visits", C.c_uint64),
+                ("tri_tests", C.c_uint64)]
+
+    def as_dict(self) -> dict:
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+RAY_DTYPE = np.dtype([("o", "<f4", 3), ("d", "<f4", 3), ("min_t", "<f4"), ("max_t", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("hit", "<i4"), ("shape", "<i4"), ("prim", "<i4"),
+                      ("tri", "<i4"), ("_pad", "<i4")])
+BSDF_QUERY_DTYPE = np.dtype([("wo", "<f4", 3), ("wi", "<f4", 3), ("u", "<f4", 2), ("mat", "<i4"), ("_pad", "<i4")])
+BSDF_OUT_DTYPE = np.dtype([("eval", "<f4", 3), ("pdf", "<f4"), ("sample_val", "<f4", 3), ("sample_pdf", "<f4"),
+                           ("sample_wi", "<f4", 3), ("type", "<u4")])
+MATERIAL_DTYPE = np.dtype([("kd", "<f4", 3), ("ks", "<f4", 3), ("ke", "<f4", 3), ("tf", "<f4", 3), ("ns", "<f4"),
+                           ("ni", "<f4"), ("illum", "<i4"), ("_pad", "<i4")])
+assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 32 and MATERIAL_DTYPE.itemsize == C.sizeof(Material) == 64
+assert BSDF_QUERY_DTYPE.itemsize == 40 and BSDF_OUT_DTYPE.itemsize == 48
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """The loaded libtrb.so. Raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        path = Path(os.environ.get("TRB_LIB", LIB_PATH))
+        if not path.exists():
+            raise ImportError(f"{path} is missing: run `python bidirectional-path-tracing_b200/build.py` "
+                              "(or __graft_entry__.build()); the product has no CPU fallback")
+        L = C.CDLL(str(path))
+        L.trb_host_last_error.restype = C.c_char_p
+        for name in ("trb_last_error", "trb_build_info"):
+            if hasattr(L, name):
+                getattr(L, name).restype = C.c_char_p
+        if hasattr(L, "trb_last_error"):
+            L.trb_last_error.argtypes = [C.c_void_p]
+        if hasattr(L, "trb_scene_device_bytes"):
+            L.trb_scene_device_bytes.restype = C.c_size_t
+            L.trb_scene_device_bytes.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _ptr(a: np.ndarray) -> C.c_void_p:
+    return C.c_void_p(a.ctypes.data)
+
+
+def _chk_host(rc: int) -> int:
+    if rc < 0:
+        raise TrbError(rc, lib().trb_host_last_error().decode())
+    return rc
+
+
+def make_rays(o, d, min_t=1e-8, max_t=np.finfo(np.float32).max) -> np.ndarray:
+    o = np.asarray(o, np.float32).reshape(-1, 3)
+    d = np.asarray(d, np.float32).reshape(-1, 3)
+    r = np.zeros(len(o), RAY_DTYPE)
+    r["o"], r["d"] = o, d
+    r["min_t"], r["max_t"] = min_t, max_t
+    return r
+
+
+def render_desc(eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0), up=(0.0, 1.0, 0.0), fov=30.0, width=800, height=600, spp=1,
+                rr_depth=5, seed=260450963, spp_begin=0, spp_end=0, flags=0, wave_samples=0) -> RenderDesc:
+    d = RenderDesc()
+    d.eye[:], d.at[:], d.up[:] = eye, at, up
+    d.fov_deg = fov
+    d.width, d.height, d.spp, d.rr_depth = width, height, spp, rr_depth
+    d.spp_begin, d.spp_end, d.seed, d.flags, d.wave_samples = spp_begin, spp_end, seed, flags, wave_samples
+    return d
+
+
+# ---- host scene ------------------------------------------------------------------------------------------
+class HostScene:
+    """Flat scene arrays (what tinyobj::LoadObj + Scene::load hold). Built from an OBJ file by the library's
+    own loader, or from arrays / an .npz fixture."""
+
+    FIELDS = ("positions", "normals", "tri_v", "tri_n", "tri_mat", "tri_shape", "materials")
+
+    def __init__(self, positions, normals, tri_v, tri_n, tri_mat, tri_shape, materials, n_shapes=None, shape_names=None):
+        self.positions = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
+        self.normals = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
+        self.tri_v = np.ascontiguousarray(tri_v, np.int32).reshape(-1, 3)
+        self.tri_n = np.ascontiguousarray(tri_n, np.int32).reshape(-1, 3)
+        self.tri_mat = np.ascontiguousarray(tri_mat, np.int32).reshape(-1)
+        self.tri_shape = np.ascontiguousarray(tri_shape, np.int32).reshape(-1)
+        self.materials = np.ascontiguousarray(materials, MATERIAL_DTYPE).reshape(-1)
+        self.n_shapes = int(n_shapes if n_shapes is not None else (self.tri_shape.max() + 1 if len(self.tri_shape) else 0))
+        self.shape_names = list(shape_names) if shape_names is not None else [f"shape{i}" for i in range(self.n_shapes)]
+
+    @property
+    def n_tris(self) -> int:
+        return len(self.tri_mat)
+
+    def desc(self) -> SceneDesc:
+        d = SceneDesc()
+        d.positions, d.n_positions = self.positions.ctypes.data, len(self.positions)
+        d.normals, d.n_normals = self.normals.ctypes.data, len(self.normals)
+        d.tri_v, d.tri_n = self.tri_v.ctypes.data, self.tri_n.ctypes.data
+        d.tri_mat, d.tri_shape = self.tri_mat.ctypes.data, self.tri_shape.ctypes.data
+        d.n_tris = self.n_tris
+        d.materials, d.n_materials = self.materials.ctypes.data, len(self.materials)
+        d.n_shapes = self.n_shapes
+        return d
+
+    @classmethod
+    def load_obj(cls, path) -> "HostScene":
+        L = lib()
+        h = C.c_void_p()
+        _chk_host(L.trb_host_load_obj(str(path).encode(), C.byref(h)))
+        try:
+            d = SceneDesc()
+            _chk_host(L.trb_host_scene_desc(h, C.byref(d)))
+
+            def arr(p, n, dt):
+                if n == 0:
+                    return np.zeros(0, dt)
+                return np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_char)), shape=(n * np.dtype(dt).itemsize,)).view(dt).copy()
+
+            names = []
+            buf = C.create_string_buffer(256)
+            for i in range(d.n_shapes):
+                _chk_host(L.trb_host_shape_name(h, C.c_size_t(i), buf, C.c_size_t(256)))
+                names.append(buf.value.decode(errors="replace"))
+            return cls(arr(d.positions, d.n_positions * 3, np.float32), arr(d.normals, d.n_normals * 3, np.float32),
+                       arr(d.tri_v, d.n_tris * 3, np.int32), arr(d.tri_n, d.n_tris * 3, np.int32),
+                       arr(d.tri_mat, d.n_tris, np.int32), arr(d.tri_shape, d.n_tris, np.int32),
+                       arr(d.materials, d.n_materials, MATERIAL_DTYPE), n_shapes=d.n_shapes, shape_names=names)
+        finally:
+            L.trb_host_scene_free(h)
+
+    def save_npz(self, path) -> None:
+        np.savez_compressed(path, positions=self.positions, normals=self.normals, tri_v=self.tri_v, tri_n=self.tri_n,
+                            tri_mat=self.tri_mat, tri_shape=self.tri_shape, materials=self.materials.view(np.uint8),
+                            n_shapes=np.int64(self.n_shapes), shape_names=np.array(self.shape_names))
+
+    @classmethod
+    def load_npz(cls, path) -> "HostScene":
+        z = np.load(path, allow_pickle=False)
+        return cls(z["positions"], z["normals"], z["tri_v"], z["tri_n"], z["tri_mat"], z["tri_shape"],
+                   z["materials"].view(MATERIAL_DTYPE), n_shapes=int(z["n_shapes"]), shape_names=[str(s) for s in z["shape_names"]])
+
+    # host-side derived data (no GPU)
+    def bvh_order(self) -> np.ndarray:
+        out = np.zeros(self.n_tris, np.int32)
+        d = self.desc()
+        _chk_host(lib().trb_host_bvh_order(C.byref(d), _ptr(out), C.c_size_t(self.n_tris)))
+        return out
+
+    def emitters(self) -> dict:
+        d = self.desc()
+        cap = 64
+        shape = np.zeros(cap, np.int32)
+        area = np.zeros(cap, np.float32)
+        rad = np.zeros((cap, 3), np.float32)
+        cdf = np.zeros(self.n_tris + 2 * cap, np.float32)
+        n = _chk_host(lib().trb_host_emitters(C.byref(d), _ptr(shape), _ptr(area), _ptr(rad), C.c_size_t(cap), _ptr(cdf),
+                                              C.c_size_t(len(cdf))))
+        return {"n": n, "shape": shape[:n], "area": area[:n], "radiance": rad[:n], "cdf": cdf}
+
+
+def load_toml(path) -> tuple[RenderDesc, str, str, bool]:
+    """loadTOML (src/main.cpp:22-116): returns (render desc, resolved obj path, renderer.type, realtime)."""
+    d = RenderDesc()
+    obj = C.create_string_buffer(4096)
+    typ = C.create_string_buffer(64)
+    rt = C.c_int(0)
+    _chk_host(lib().trb_host_load_toml(str(path).encode(), C.byref(d), obj, C.c_size_t(4096), typ, C.c_size_t(64), C.byref(rt)))
+    return d, obj.value.decode(), typ.value.decode(), bool(rt.value)
+
+
+def camera_matrices(desc: RenderDesc) -> np.ndarray:
+    out = np.zeros((4, 4, 4), np.float32)
+    _chk_host(lib().trb_host_camera_matrices(C.byref(desc), _ptr(out)))
+    return out
+
+
+def save_exr(path, rgb: np.ndarray) -> None:
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    h, w, _ = rgb.shape
+    _chk_host(lib().trb_host_save_exr(str(path).encode(), _ptr(rgb), w, h))
+
+
+# ---- device context --------------------------------------------------------------------------------------
+class Context:
+    """One GPU + one uploaded scene (trb_context)."""
+
+    def __init__(self, device: int = 0):
+        self._L = lib()
+        if not hasattr(self._L, "trb_create"):
+            raise ImportError("libtrb.so was built without the CUDA half")
+        self._h = C.c_void_p()
+        rc = self._L.trb_create(int(device), C.byref(self._h))
+        if rc < 0:
+            raise TrbError(rc, self._L.trb_host_last_error().decode())
+        self.scene = None
+
+    def close(self) -> None:
+        if self._h:
+            self._L.trb_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc: int) -> int:
+        if rc < 0:
+            raise TrbError(rc, self._L.trb_last_error(self._h).decode())
+        return rc
+
+    def upload(self, scene: HostScene) -> None:
+        d = scene.desc()
+        self._chk(self._L.trb_scene_upload(self._h, C.byref(d)))
+        self.scene = scene
+
+    def scene_bytes(self) -> int:
+        return int(self._L.trb_scene_device_bytes(self._h))
+
+    def trace_closest(self, rays: np.ndarray) -> np.ndarray:
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        out = np.zeros(len(rays), HIT_DTYPE)
+        self._chk(self._L.trb_trace_closest(self._h, _ptr(rays), C.c_size_t(len(rays)), _ptr(out)))
+        return out
+
+    def trace_any(self, rays: np.ndarray) -> np.ndarray:
+        rays = np.ascontiguousarray(rays, RAY_DTYPE)
+        out = np.zeros(len(rays), np.uint8)
+        self._chk(self._L.trb_trace_any(self._h, _ptr(rays), C.c_size_t(len(rays)), _ptr(out)))
+        return out
+
+    def bsdf_batch(self, q: np.ndarray) -> np.ndarray:
+        q = np.ascontiguousarray(q, BSDF_QUERY_DTYPE)
+        out = np.zeros(len(q), BSDF_OUT_DTYPE)
+        self._chk(self._L.trb_bsdf_batch(self._h, _ptr(q), C.c_size_t(len(q)), _ptr(out)))
+        return out
+
+    def bdpt_paths(self, desc: RenderDesc, cam_rays: np.ndarray, rng: np.ndarray):
+        """BDPTIntegrator::render on given camera rays with injected random numbers (n x stride)."""
+        cam_rays = np.ascontiguousarray(cam_rays, RAY_DTYPE)
+        rng = np.ascontiguousarray(rng, np.float32)
+        n, stride = rng.shape
+        assert n == len(cam_rays)
+        k = max(desc.rr_depth - 1, 1)
+        li = np.zeros((n, 3), np.float32)
+        pix = np.full((n, k), -1, np.int32)
+        rgb = np.zeros((n, k, 3), np.float32)
+        draws = np.zeros(n, np.int32)
+        self._chk(self._L.trb_bdpt_paths(self._h, C.byref(desc), _ptr(cam_rays), _ptr(rng), C.c_size_t(n), C.c_size_t(stride),
+                                         _ptr(li), _ptr(pix), _ptr(rgb), _ptr(draws)))
+        return li, pix, rgb, draws
+
+    def render_bdpt(self, desc: RenderDesc, accumulate: bool = False, download: bool = True):
+        """Renderer::render (offline branch) with the BDPT integrator. Returns (H x W x 3 float32 | None, stats)."""
+        st = Stats()
+        img = np.zeros((desc.height, desc.width, 3), np.float32) if download else None
+        self._chk(self._L.trb_render_bdpt(self._h, C.byref(desc), int(accumulate), _ptr(img) if download else None, C.byref(st)))
+        return img, st.as_dict()
+
+    def render_bdpt_device(self, desc: RenderDesc, d_rgb_ptr: int, accumulate: bool = False) -> dict:
+        st = Stats()
+        self._chk(self._L.trb_render_bdpt_device(self._h, C.byref(desc), int(accumulate), C.c_void_p(d_rgb_ptr), C.byref(st)))
+        return st.as_dict()
+
+    def trace_closest_device(self, d_rays_ptr: int, n: int, d_out_ptr: int) -> float:
+        ms = C.c_float(0)
+        self._chk(self._L.trb_trace_closest_device(self._h, C.c_void_p(d_rays_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr), C.byref(ms)))
+        return ms.value
+
+    def trace_any_device(self, d_rays_ptr: int, n: int, d_out_ptr: int) -> float:
+        ms = C.c_float(0)
+        self._chk(self._L.trb_trace_any_device(self._h, C.c_void_p(d_rays_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr), C.byref(ms)))
+        return ms.value
+
+
+def build_info() -> str:
+    L = lib()
+    return L.trb_build_info().decode() if hasattr(L, "trb_build_info") else "host-only"

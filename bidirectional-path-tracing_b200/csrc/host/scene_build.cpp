@@ -1,0 +1,275 @@
+// scene_build.cpp -- the tail of Scene::load on the host (reference: src/core/renderer.cpp:259-339,
+// src/core/accel.h:115-123, externals/bvh.h:147-247) and the flattening into the device layout.
+//
+// Why the reference's BVH *topology* is kept (DESIGN.md "BVH"): the reference's traversal is exhaustive
+// along the infinite line and its answer is "the min-t triangle among those whose ancestors' boxes all
+// pass BBox::intersect; ties -> first in the build-reordered list" (bvh.h:259-352).  Bit-exact
+// hit ids need (a) that primitive order and (b) the same set of boxes, so the device tree has the same
+// partition; what changes is the node layout (children boxes in the parent, 64 B, float4 loads) and the
+// traversal (ordered, pruned, stack in registers/shared memory).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "tr_host.h"
+
+namespace trb {
+
+namespace {
+struct V3 { float x, y, z; };
+inline V3 vtx(const trb_scene_desc& s, int32_t i) { return {s.positions[3 * i], s.positions[3 * i + 1], s.positions[3 * i + 2]}; }
+inline V3 nrm(const trb_scene_desc& s, int32_t i) { return {s.normals[3 * i], s.normals[3 * i + 1], s.normals[3 * i + 2]}; }
+inline float lum(float r, float g, float b) { return (r * 0.212671f + g * 0.715160f) + b * 0.072169f; }  // math.h:56-58 (glm dot order)
+}  // namespace
+
+size_t FlatScene::bytes() const {
+    return nodes.size() * sizeof(DevNode) + tris.size() * sizeof(DevTri) + shade.size() * sizeof(DevShade) +
+           materials.size() * sizeof(DevMaterial) + emitters.size() * sizeof(DevEmitter) +
+           emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float);
+}
+
+// BSDF constructors: diffuse.h:20-32, phong.h:25-52, mixture.h:25-52, perfectmirror.h:18-26, glass.h:20-31;
+// class selection by illum: renderer.cpp:259-271.
+bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, std::string& err) {
+    out.resize(s.n_materials);
+    for (size_t i = 0; i < s.n_materials; ++i) {
+        const trb_material& m = s.materials[i];
+        DevMaterial d;
+        std::memset(&d, 0, sizeof(d));
+        for (int k = 0; k < 3; ++k) { d.kd[k] = m.kd[k]; d.ks[k] = m.ks[k]; d.ke[k] = m.ke[k]; d.tf[k] = m.tf[k]; }
+        d.ns = m.ns; d.ni = m.ni;
+        d.emissive = (m.ke[0] != 0.f || m.ke[1] != 0.f || m.ke[2] != 0.f) ? 1 : 0;
+        d.scale = 1.f; d.spec_weight = 0.f;
+        const uint32_t EDiffuseReflection = 0x2, EGlossyReflection = 0x8, EDeltaReflection = 0x20, EDeltaTransmission = 0x40;
+        switch (m.illum) {
+            case 7: d.cls = MAT_DIFFUSE; d.type = EDiffuseReflection; break;
+            case 3: d.cls = MAT_MIRROR; d.type = EDeltaReflection; break;
+            case 6: d.cls = MAT_GLASS; d.type = EDeltaReflection | EDeltaTransmission; break;
+            case 5:
+                err = "material " + std::to_string(i) + ": illum 5 has no BSDF in the reference (renderer.cpp:259-270)";
+                return false;
+            default: {
+                d.cls = (m.illum == 8) ? MAT_MIXTURE : MAT_PHONG;
+                d.type = EGlossyReflection | EDiffuseReflection;
+                // energy-conservation scale and lobe-selection weight (phong.h:41-47)
+                float mx = m.ks[0] + m.kd[0], my = m.ks[1] + m.kd[1], mz = m.ks[2] + m.kd[2];
+                float actual = std::max(std::max(mx, my), mz);
+                d.scale = actual > 1.0f ? 0.99f * (1.0f / actual) : 1.0f;
+                float dAvg = lum(m.kd[0] * d.scale, m.kd[1] * d.scale, m.kd[2] * d.scale);
+                float sAvg = lum(m.ks[0] * d.scale, m.ks[1] * d.scale, m.ks[2] * d.scale);
+                d.spec_weight = sAvg / (dAvg + sAvg);
+            }
+        }
+        out[i] = d;
+    }
+    return true;
+}
+
+// Emitters: one per shape whose FIRST face material is emissive (renderer.cpp:279-291); face-area CDF and
+// total area as Scene::getShapeArea / Distribution1D do (renderer.cpp:317-339, math.h:81-112).
+bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& mats, std::vector<DevEmitter>& em,
+                     std::vector<DevEmitterTri>& etris, std::vector<float>& cdf, std::vector<int32_t>& shape_to_emitter,
+                     std::string& err) {
+    em.clear(); etris.clear(); cdf.clear();
+    shape_to_emitter.assign(s.n_shapes, -1);
+    size_t t = 0;
+    for (size_t sh = 0; sh < s.n_shapes; ++sh) {
+        size_t first = t;
+        while (t < s.n_tris && size_t(s.tri_shape[t]) == sh) ++t;
+        size_t nf = t - first;
+        if (nf == 0) { err = "shape without faces"; return false; }
+        int32_t m0 = s.tri_mat[first];
+        if (m0 < 0 || size_t(m0) >= s.n_materials) { err = "face without a material (usemtl missing)"; return false; }
+        if (!mats[m0].emissive) continue;
+        DevEmitter e;
+        std::memset(&e, 0, sizeof(e));
+        e.shape = int32_t(sh);
+        e.first_face = int32_t(etris.size());
+        e.n_faces = int32_t(nf);
+        e.cdf_offset = int32_t(cdf.size());
+        for (int k = 0; k < 3; ++k) e.radiance[k] = mats[m0].ke[k];
+        size_t c0 = cdf.size();
+        cdf.push_back(0.f);
+        for (size_t f = first; f < t; ++f) {
+            V3 a = vtx(s, s.tri_v[3 * f]), b = vtx(s, s.tri_v[3 * f + 1]), c = vtx(s, s.tri_v[3 * f + 2]);
+            V3 e1{b.x - a.x, b.y - a.y, b.z - a.z}, e2{c.x - a.x, c.y - a.y, c.z - a.z};
+            V3 cr{e1.y * e2.z - e2.y * e1.z, e1.z * e2.x - e2.z * e1.x, e1.x * e2.y - e2.x * e1.y};  // glm::cross order
+            float area = 0.5f * std::sqrt(cr.x * cr.x + cr.y * cr.y + cr.z * cr.z);
+            cdf.push_back(cdf.back() + area);
+            DevEmitterTri et;
+            std::memset(&et, 0, sizeof(et));
+            V3 n0 = nrm(s, s.tri_n[3 * f]), n1 = nrm(s, s.tri_n[3 * f + 1]), n2 = nrm(s, s.tri_n[3 * f + 2]);
+            et.v0[0] = a.x; et.v0[1] = a.y; et.v0[2] = a.z; et.v1[0] = b.x; et.v1[1] = b.y; et.v1[2] = b.z;
+            et.v2[0] = c.x; et.v2[1] = c.y; et.v2[2] = c.z;
+            et.n0[0] = n0.x; et.n0[1] = n0.y; et.n0[2] = n0.z; et.n1[0] = n1.x; et.n1[1] = n1.y; et.n1[2] = n1.z;
+            et.n2[0] = n2.x; et.n2[1] = n2.y; et.n2[2] = n2.z;
+            etris.push_back(et);
+        }
+        e.area = cdf.back();
+        float sum = cdf.back();
+        for (size_t k = c0; k < cdf.size(); ++k) cdf[k] /= sum;  // Distribution1D::normalize divides every entry
+        shape_to_emitter[sh] = int32_t(em.size());
+        em.push_back(e);
+    }
+    // The reference looks the emitter up by shape whenever a face's material is emissive (bdpt.h:79-81,
+    // integrator.cpp:53-58) and walks off the end of the list when the shape is not an emitter.
+    for (size_t f = 0; f < s.n_tris; ++f) {
+        int32_t m = s.tri_mat[f];
+        if (m < 0 || size_t(m) >= s.n_materials) { err = "face without a material (usemtl missing)"; return false; }
+        if (mats[m].emissive && shape_to_emitter[s.tri_shape[f]] < 0) {
+            err = "emissive face in a shape whose first face is not emissive: undefined in the reference";
+            return false;
+        }
+    }
+    return true;
+}
+
+// ---- reference-order BVH build ---------------------------------------------------------------------
+bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
+    const size_t n = s.n_tris;
+    if (n == 0) { err = "empty scene"; return false; }
+    // per-triangle bounds and centroid, computed as AcceleratorBVH::BVHNode::{getBBox,getCentroid} do
+    // (accel.h:71-106): box by min/max over the vertices, centroid = ((v0 + v1) + v2) / 3.0f
+    std::vector<float> bmin(3 * n), bmax(3 * n), cen(3 * n);
+    for (size_t t = 0; t < n; ++t) {
+        V3 a = vtx(s, s.tri_v[3 * t]), b = vtx(s, s.tri_v[3 * t + 1]), c = vtx(s, s.tri_v[3 * t + 2]);
+        const float pa[3] = {a.x, a.y, a.z}, pb[3] = {b.x, b.y, b.z}, pc[3] = {c.x, c.y, c.z};
+        for (int k = 0; k < 3; ++k) {
+            bmin[3 * t + k] = std::min(std::min(pa[k], pb[k]), pc[k]);
+            bmax[3 * t + k] = std::max(std::max(pa[k], pb[k]), pc[k]);
+            cen[3 * t + k] = ((pa[k] + pb[k]) + pc[k]) / 3.0f;
+        }
+    }
+    out.order.resize(n);
+    for (size_t t = 0; t < n; ++t) out.order[t] = int32_t(t);  // objects are created shape-major, accel.h:116-120
+    out.nodes.clear();
+    out.nodes.reserve(2 * n / 3 + 16);
+
+    struct Todo { uint32_t start, end; int32_t parent; bool is_right; };
+    std::vector<Todo> stack;
+    stack.push_back({0u, uint32_t(n), -1, false});
+    std::vector<int32_t>& ord = out.order;
+    while (!stack.empty()) {
+        Todo td = stack.back();
+        stack.pop_back();
+        const uint32_t start = td.start, end = td.end, cnt = end - start;
+        RefTree::Node node;
+        node.start = start; node.count = cnt; node.left = -1; node.right = -1;
+        float cmin[3], cmax[3];
+        for (int k = 0; k < 3; ++k) {
+            node.bmin[k] = bmin[3 * ord[start] + k]; node.bmax[k] = bmax[3 * ord[start] + k];
+            cmin[k] = cmax[k] = cen[3 * ord[start] + k];
+        }
+        for (uint32_t p = start + 1; p < end; ++p) {
+            const int32_t t = ord[p];
+            for (int k = 0; k < 3; ++k) {
+                node.bmin[k] = std::min(node.bmin[k], bmin[3 * t + k]); node.bmax[k] = std::max(node.bmax[k], bmax[3 * t + k]);
+                cmin[k] = std::min(cmin[k], cen[3 * t + k]); cmax[k] = std::max(cmax[k], cen[3 * t + k]);
+            }
+        }
+        const int32_t me = int32_t(out.nodes.size());
+        out.nodes.push_back(node);
+        if (td.parent >= 0) {
+            if (td.is_right) out.nodes[td.parent].right = me; else out.nodes[td.parent].left = me;
+        }
+        if (cnt <= 4) continue;  // leafSize = 4 (bvh.h:122)
+        // split axis: BBox::maxDimension with its y/z comparison quirk (bvh.h:82-87)
+        const float ex = cmax[0] - cmin[0], ey = cmax[1] - cmin[1], ez = cmax[2] - cmin[2];
+        int dim = 0;
+        if (ey > ex) dim = 1;
+        if (ez > ey) dim = 2;
+        const float split = .5f * (cmin[dim] + cmax[dim]);
+        // in-place partition; the swap sequence defines the final primitive order (bvh.h:207-213)
+        uint32_t mid = start;
+        for (uint32_t i = start; i < end; ++i) {
+            if (cen[3 * ord[i] + dim] < split) { std::swap(ord[i], ord[mid]); ++mid; }
+        }
+        if (mid == start || mid == end) mid = start + (end - start) / 2;
+        // right is pushed first so that left is built next: pre-order, as the reference's flat array
+        stack.push_back({mid, end, me, true});
+        stack.push_back({start, mid, me, false});
+    }
+    return true;
+}
+
+bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
+    if (!s.positions || !s.normals || !s.tri_v || !s.tri_n || !s.tri_mat || !s.tri_shape || !s.materials) {
+        err = "null array in scene description"; return false;
+    }
+    for (size_t t = 0; t < s.n_tris; ++t) {
+        for (int k = 0; k < 3; ++k) {
+            if (s.tri_v[3 * t + k] < 0 || size_t(s.tri_v[3 * t + k]) >= s.n_positions) { err = "vertex index out of range"; return false; }
+            if (s.tri_n[3 * t + k] < 0 || size_t(s.tri_n[3 * t + k]) >= s.n_normals) { err = "normal index out of range (the reference needs vn on every face)"; return false; }
+        }
+        if (s.tri_shape[t] < 0 || size_t(s.tri_shape[t]) >= s.n_shapes || (t > 0 && s.tri_shape[t] < s.tri_shape[t - 1])) {
+            err = "tri_shape must be non-decreasing and < n_shapes"; return false;
+        }
+    }
+    if (!derive_materials(s, out.materials, err)) return false;
+    std::vector<int32_t> shape_to_emitter;
+    if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
+
+    RefTree tree;
+    if (!build_ref_tree(s, tree, err)) return false;
+    out.order = tree.order;
+    const size_t n = s.n_tris;
+
+    std::vector<int32_t> shape_first(s.n_shapes + 1, 0);
+    for (size_t t = 0; t < n; ++t) shape_first[s.tri_shape[t] + 1] = int32_t(t + 1);
+    for (size_t k = 1; k <= s.n_shapes; ++k) shape_first[k] = std::max(shape_first[k], shape_first[k - 1]);
+
+    out.tris.resize(n);
+    out.shade.resize(n);
+    for (size_t p = 0; p < n; ++p) {
+        const int32_t t = tree.order[p];
+        V3 a = vtx(s, s.tri_v[3 * t]), b = vtx(s, s.tri_v[3 * t + 1]), c = vtx(s, s.tri_v[3 * t + 2]);
+        V3 n0 = nrm(s, s.tri_n[3 * t]), n1 = nrm(s, s.tri_n[3 * t + 1]), n2 = nrm(s, s.tri_n[3 * t + 2]);
+        const int32_t mat = s.tri_mat[t];
+        DevTri& dt = out.tris[p];
+        dt.v0[0] = a.x; dt.v0[1] = a.y; dt.v0[2] = a.z;
+        dt.e1[0] = b.x - a.x; dt.e1[1] = b.y - a.y; dt.e1[2] = b.z - a.z;
+        dt.e2[0] = c.x - a.x; dt.e2[1] = c.y - a.y; dt.e2[2] = c.z - a.z;
+        dt.tri = t; dt.mat = mat;
+        dt.flags = out.materials[mat].cls | (out.materials[mat].emissive ? 8 : 0);
+        DevShade& ds = out.shade[p];
+        ds.v0[0] = a.x; ds.v0[1] = a.y; ds.v0[2] = a.z; ds.v1[0] = b.x; ds.v1[1] = b.y; ds.v1[2] = b.z;
+        ds.v2[0] = c.x; ds.v2[1] = c.y; ds.v2[2] = c.z;
+        ds.n0[0] = n0.x; ds.n0[1] = n0.y; ds.n0[2] = n0.z; ds.n1[0] = n1.x; ds.n1[1] = n1.y; ds.n1[2] = n1.z;
+        ds.n2[0] = n2.x; ds.n2[1] = n2.y; ds.n2[2] = n2.z;
+        ds.shape = s.tri_shape[t]; ds.prim = t - shape_first[s.tri_shape[t]]; ds.mat = mat;
+        ds.emitter = shape_to_emitter[s.tri_shape[t]]; ds.tri = t; ds.pad = 0;
+    }
+
+    // inner nodes only; leaves become negative child references
+    std::vector<int32_t> inner_index(tree.nodes.size(), -1);
+    int32_t n_inner = 0;
+    for (size_t i = 0; i < tree.nodes.size(); ++i) if (tree.nodes[i].left >= 0) inner_index[i] = n_inner++;
+    auto make_ref = [&](int32_t ni) -> int32_t {
+        const RefTree::Node& nd = tree.nodes[ni];
+        if (nd.left >= 0) return inner_index[ni];
+        return ~int32_t((nd.start << 3) | nd.count);
+    };
+    out.nodes.resize(size_t(n_inner));
+    for (size_t i = 0; i < tree.nodes.size(); ++i) {
+        const RefTree::Node& nd = tree.nodes[i];
+        if (nd.left < 0) continue;
+        DevNode& d = out.nodes[inner_index[i]];
+        const RefTree::Node& l = tree.nodes[nd.left];
+        const RefTree::Node& r = tree.nodes[nd.right];
+        for (int k = 0; k < 3; ++k) { d.c0min[k] = l.bmin[k]; d.c0max[k] = l.bmax[k]; d.c1min[k] = r.bmin[k]; d.c1max[k] = r.bmax[k]; }
+        d.ref0 = make_ref(nd.left); d.ref1 = make_ref(nd.right); d.pad0 = d.pad1 = 0;
+    }
+    out.root_ref = make_ref(0);
+    for (int k = 0; k < 3; ++k) { out.scene_min[k] = tree.nodes[0].bmin[k]; out.scene_max[k] = tree.nodes[0].bmax[k]; }
+    // depth (pre-order array: children always follow their parent)
+    std::vector<int32_t> depth(tree.nodes.size(), 0);
+    int32_t md = 0;
+    for (size_t i = 0; i < tree.nodes.size(); ++i) {
+        if (tree.nodes[i].left >= 0) { depth[tree.nodes[i].left] = depth[i] + 1; depth[tree.nodes[i].right] = depth[i] + 1; }
+        md = std::max(md, depth[i]);
+    }
+    out.max_depth = md;
+    return true;
+}
+
+}  // namespace trb

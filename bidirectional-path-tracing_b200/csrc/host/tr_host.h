@@ -1,0 +1,144 @@
+// tr_host.h -- host-side (CPU, no CUDA) half of the product: scene loading, the reference-order BVH
+// build, flattening into the device layout, camera matrices, TOML and EXR I/O.
+// This is the part of TinyRender's Scene::load / loadTOML / saveEXR that stays on the host
+// (reference: src/core/renderer.cpp:235-339, src/main.cpp:22-116, src/core/utils.h:95-156).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "../../../include/trb.h"
+
+namespace trb {
+
+// ---- what tinyobj::LoadObj(triangulate=true) yields, flattened shape-major -----------------------
+struct HostScene {
+    std::vector<float> positions, normals;
+    std::vector<int32_t> tri_v, tri_n, tri_mat, tri_shape;
+    std::vector<trb_material> materials;
+    std::vector<std::string> shape_names, material_names;
+    size_t n_shapes = 0;
+    trb_scene_desc desc() const;
+};
+
+bool load_obj(const std::string& obj_path, HostScene& out, std::string& err);
+
+// ---- device layouts (shared with the CUDA side; all 16-byte aligned, float4-vectorised) ----------
+// 64-byte 2-wide node: the two CHILD boxes live in the parent, so one 64 B fetch (two 32 B sectors,
+// 4x LDG.128) decides both children.  Same topology as the reference's flat tree
+// (externals/bvh.h:102-105, 48 B/node holding its OWN box) - see DESIGN.md for why topology is kept.
+struct alignas(16) DevNode {
+    float c0min[3], c0max[3];  // child 0 (reference: node ni+1)
+    float c1min[3], c1max[3];  // child 1 (reference: node ni+rightOffset)
+    int32_t ref0, ref1;        // >=0: inner node index; <0: leaf, ~ref = (first << 3) | count
+    int32_t pad0, pad1;
+};
+static_assert(sizeof(DevNode) == 64, "node must be 64 B");
+
+// 48-byte intersection record, stored in the reference's build-reordered primitive order so that the
+// array position IS the tie-break rank (first found wins, bvh.h:305).
+struct alignas(16) DevTri {
+    float v0[3];
+    int32_t tri;    // global shape-major triangle id
+    float e1[3];    // v1 - v0 (one fp32 subtraction, identical to core.h:386)
+    int32_t mat;    // material id (mesh.material_ids[primID])
+    float e2[3];    // v2 - v0
+    int32_t flags;  // bits 0-2: material class; bit 3: emissive material
+};
+static_assert(sizeof(DevTri) == 48, "triangle record must be 48 B");
+
+// 96-byte shading record (same order as DevTri): what AcceleratorBVH::intersect gathers after the
+// closest hit (accel.h:136-166).
+struct alignas(16) DevShade {
+    float v0[3]; int32_t shape;
+    float v1[3]; int32_t prim;
+    float v2[3]; int32_t mat;
+    float n0[3]; int32_t emitter;  // emitter index of the owning shape or -1
+    float n1[3]; int32_t tri;
+    float n2[3]; int32_t pad;
+};
+static_assert(sizeof(DevShade) == 96, "shading record must be 96 B");
+
+enum MatClass : int32_t { MAT_DIFFUSE = 0, MAT_PHONG = 1, MAT_MIXTURE = 2, MAT_MIRROR = 3, MAT_GLASS = 4, MAT_NCLASS = 5 };
+
+// BSDF parameters derived exactly as the reference's BSDF constructors do.
+struct alignas(16) DevMaterial {
+    float kd[3]; int32_t cls;
+    float ks[3]; uint32_t type;       // BSDF::combinedType
+    float ke[3]; float ns;            // emission; Phong exponent
+    float tf[3]; float ni;            // glass transmittance; IOR
+    float scale;                      // phong.h:41-43
+    float spec_weight;                // specularSamplingWeight, phong.h:45-47
+    int32_t emissive;                 // any(ke != 0)
+    int32_t pad;
+};
+static_assert(sizeof(DevMaterial) == 80, "material record must be 80 B");
+
+struct alignas(16) DevEmitter {
+    float radiance[3]; float area;
+    int32_t shape, first_face, n_faces, cdf_offset;  // first_face indexes emitter_tris; cdf has n_faces+1 entries
+};
+static_assert(sizeof(DevEmitter) == 32, "emitter record must be 32 B");
+
+// emitter faces in the shape's own face order (what sampleEmitterPosition indexes, integrator.cpp:73-100)
+struct alignas(16) DevEmitterTri {
+    float v0[3], v1[3], v2[3];
+    float n0[3], n1[3], n2[3];
+    float pad[2];
+};
+static_assert(sizeof(DevEmitterTri) == 80, "emitter triangle must be 80 B");
+
+struct FlatScene {
+    std::vector<DevNode> nodes;
+    std::vector<DevTri> tris;
+    std::vector<DevShade> shade;
+    std::vector<DevMaterial> materials;
+    std::vector<DevEmitter> emitters;
+    std::vector<DevEmitterTri> emitter_tris;
+    std::vector<float> emitter_cdf;
+    std::vector<int32_t> order;  // order[pos] = global tri id
+    int32_t root_ref = 0;        // root as a child reference (leaf when the scene has <= 4 triangles)
+    int32_t max_depth = 0;       // tree depth (traversal stack bound)
+    float scene_min[3], scene_max[3];
+    size_t bytes() const;
+};
+
+// Reference-order BVH build (externals/bvh.h:147-247).  order[pos] = global triangle id.
+struct RefTree {
+    struct Node { float bmin[3], bmax[3]; uint32_t start, count; int32_t left, right; };  // left<0: leaf
+    std::vector<Node> nodes;  // pre-order, node 0 = root
+    std::vector<int32_t> order;
+};
+bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err);
+
+bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, std::string& err);
+bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& mats, std::vector<DevEmitter>& em,
+                     std::vector<DevEmitterTri>& tris, std::vector<float>& cdf, std::vector<int32_t>& shape_to_emitter,
+                     std::string& err);
+bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err);
+
+// ---- camera (glm-order arithmetic; renderer.cpp:143-153, bdpt.h:49-55,485-496) --------------------
+struct CameraDev {
+    float eye[3]; float tan_half_fov;     // angle = tanf(deg2rad*fov*0.5f)
+    float forward[3]; float aspect;       // normalize(at - o); (float)W / H
+    float c2w[16];                        // cameraToWorld, column-major
+    float w2c[16];                        // worldToCamera
+    float clip[16];                       // cameraToClip = perspective(deg2rad*fov, aspect, 1, 1000)
+    float ndc2screen[16];                 // scale(W,H,1)*scale(.5,-.5,1)*translate(1,-1,0)
+    float inv_w, inv_h;                   // 1.f/W, 1.f/H
+    float vnear_dist;                     // (1/tanf(deg2rad*fov*.5f)) * H * .5f   (bdpt.h:52)
+    int32_t width, height;
+    int32_t pad[3];
+};
+void make_camera(const trb_render_desc& d, CameraDev& out);
+
+// ---- TOML / EXR ---------------------------------------------------------------------------------
+struct TomlConfig {
+    trb_render_desc desc;
+    std::string obj_path, type;
+    bool realtime = false;
+};
+bool load_toml(const std::string& path, TomlConfig& out, std::string& err);
+bool save_exr_bgr_half(const std::string& path, const float* rgb, int w, int h, std::string& err);
+
+}  // namespace trb

@@ -1,0 +1,200 @@
+/* trb.h -- C ABI of the B200-native BDPT hot path ("TinyRender on B200").
+ *
+ * This is the drop-in boundary underneath TinyRender's C++ host API (the headers under include/tinyrender).  The
+ * reference (JackMinn/Bidirectional-Path-Tracing) has no FFI layer: its operator API is in-process C++
+ * (Scene / Integrator / BSDF / Renderer).  Each entry point below cites the reference interface it
+ * replaces (file:line under the reference root).
+ *
+ * Conventions: extern "C"; plain pointers and sizes; every function returns 0 (TRB_OK) or a negative
+ * trb_status; the message is available from trb_last_error().  No exception crosses the boundary.  The
+ * caller owns every host buffer it passes; the context owns all device memory.  A context is bound to
+ * ONE device and is not thread-safe (one caller thread per context).  There is no CPU fallback: every
+ * compute entry point fails with TRB_ERR_NO_DEVICE when no sm_100 device is usable.
+ */
+#ifndef TRB_H
+#define TRB_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum trb_status {
+    TRB_OK = 0,
+    TRB_ERR_INVALID = -1,   /* bad argument / inconsistent description            */
+    TRB_ERR_NO_DEVICE = -2, /* no usable CUDA device (the product has no CPU path) */
+    TRB_ERR_CUDA = -3,      /* CUDA runtime error; see trb_last_error              */
+    TRB_ERR_NO_SCENE = -4,  /* compute call before trb_scene_upload                */
+    TRB_ERR_IO = -5,        /* file could not be read / written / parsed           */
+    TRB_ERR_UNSUPPORTED = -6 /* e.g. illum 5 (reference builds no BSDF, renderer.cpp:259-270) or map_Kd */
+} trb_status;
+
+typedef struct trb_context trb_context;       /* device side: one GPU, its scene, its wave buffers */
+typedef struct trb_host_scene trb_host_scene; /* host side: what Scene::load produces              */
+
+/* ---- plain-old-data mirrors of the reference's types ------------------------------------------- */
+
+/* Ray (src/core/core.h:117-122): origin, direction, [min_t, max_t]. 32 bytes. */
+typedef struct trb_ray {
+    float o[3];
+    float d[3];
+    float min_t, max_t;
+} trb_ray;
+
+/* Result of AcceleratorBVH::intersect (src/core/accel.h:125-172): hit flag, SurfaceInteraction::{t,u,v,
+ * shapeID,primID}.  `tri` is the shape-major global triangle number (sum of earlier shapes' face counts +
+ * primID).  On a miss shape = prim = tri = -1 and t follows the reference: FLT_MAX when nothing was hit,
+ * the (out-of-range) closest t when the closest hit failed the [min_t,max_t] test (accel.h:131-133,170). */
+typedef struct trb_hit {
+    float t, u, v;
+    int32_t hit;
+    int32_t shape, prim, tri;
+    int32_t _pad;
+} trb_hit;
+
+/* tinyobj::material_t fields the path reads (diffuse.h:20-32, phong.h:25-52, glass.h:20-31, renderer.cpp:229-231). */
+typedef struct trb_material {
+    float kd[3];  /* Kd  */
+    float ks[3];  /* Ks  */
+    float ke[3];  /* Ke  : emission                                    */
+    float tf[3];  /* Tf/Kt: glass transmittance                        */
+    float ns;     /* Ns  : Phong exponent                              */
+    float ni;     /* Ni  : index of refraction                         */
+    int32_t illum; /* 7 diffuse, 3 mirror, 6 glass, 8 mixture, 5 unsupported, else phong (renderer.cpp:259-271) */
+    int32_t _pad;
+} trb_material;
+
+/* What tinyobj::LoadObj(triangulate=true) + Scene::load hold (src/core/renderer.cpp:235-315), flattened.
+ * Triangles are listed shape-major in file order: tri_shape[] is non-decreasing. */
+typedef struct trb_scene_desc {
+    const float* positions;   /* attrib.vertices, 3 floats per vertex  */
+    size_t n_positions;       /* number of vertices                    */
+    const float* normals;     /* attrib.normals, 3 floats per normal   */
+    size_t n_normals;
+    const int32_t* tri_v;     /* 3 vertex indices per triangle         */
+    const int32_t* tri_n;     /* 3 normal indices per triangle         */
+    const int32_t* tri_mat;   /* mesh.material_ids                     */
+    const int32_t* tri_shape; /* owning shape                          */
+    size_t n_tris;
+    const trb_material* materials;
+    size_t n_materials;
+    size_t n_shapes;
+} trb_scene_desc;
+
+/* Config (src/core/core.h:195-248) restricted to what BDPT reads, plus the sample range that makes the
+ * call shardable by sample index.  Contributions are always normalised by the TOTAL spp, so partial
+ * frame buffers of disjoint [spp_begin, spp_end) ranges add up to the full render. */
+typedef struct trb_render_desc {
+    float eye[3], at[3], up[3];
+    float fov_deg;
+    int32_t width, height;
+    int32_t spp;       /* total samples per pixel (the normaliser, bdpt.h:332, renderer.cpp:201)       */
+    int32_t rr_depth;  /* renderer.rrDepth: subpaths have at most rr_depth-1 vertices (bdpt.h:68,188)  */
+    int32_t spp_begin; /* first sample index rendered by this call (0 for a whole render)              */
+    int32_t spp_end;   /* one past the last; 0 means spp                                                */
+    uint32_t seed;     /* key of the counter-based RNG; streams are keyed by (seed, pixel, sample, dim) */
+    uint32_t flags;    /* TRB_FLAG_*                                                                    */
+    int64_t wave_samples; /* samples per wavefront launch; 0 = library default                          */
+} trb_render_desc;
+
+#define TRB_FLAG_NONE 0u
+#define TRB_FLAG_NO_JITTER 1u /* force the spp==1 pixel-centre path of renderer.cpp:169-180 */
+
+typedef struct trb_stats {
+    double ms_total;          /* device time of the whole call, CUDA events            */
+    double ms_trace_closest;  /* summed over launches                                   */
+    double ms_trace_any;
+    double ms_logic;          /* generation / bounce / connection kernels               */
+    uint64_t samples;         /* Integrator::render calls                               */
+    uint64_t rays_closest;    /* BVH closest-hit queries traced                         */
+    uint64_t rays_any;        /* occlusion queries traced                               */
+    uint64_t launches;        /* kernels launched by this call                          */
+    uint64_t node_visits;     /* only when built with TRB_COUNTERS (else 0)             */
+    uint64_t tri_tests;
+} trb_stats;
+
+/* BSDF query in the local shading frame (SurfaceInteraction::{wo,wi}, core.h:173-180) */
+typedef struct trb_bsdf_query {
+    float wo[3];
+    float wi[3];
+    float u[2];     /* the v2f handed to BSDF::sample */
+    int32_t mat;
+    int32_t _pad;
+} trb_bsdf_query;
+
+typedef struct trb_bsdf_out {
+    float eval[3];       /* BSDF::eval  (f * cos)          */
+    float pdf;           /* BSDF::pdf                       */
+    float sample_val[3]; /* BSDF::sample return value       */
+    float sample_pdf;    /* *pdf written by BSDF::sample    */
+    float sample_wi[3];  /* i.wi written by BSDF::sample    */
+    uint32_t type;       /* BSDF::getType()                 */
+} trb_bsdf_out;
+
+/* ---- host side (replaces tinyobj::LoadObj + Scene::load, renderer.cpp:235-315; loadTOML, main.cpp:22-116) */
+int trb_host_load_obj(const char* obj_path, trb_host_scene** out);
+int trb_host_scene_desc(const trb_host_scene*, trb_scene_desc* out); /* pointers stay owned by the host scene */
+int trb_host_shape_name(const trb_host_scene*, size_t shape, char* buf, size_t buflen);
+void trb_host_scene_free(trb_host_scene*);
+/* Parses the reference's TOML scene file. obj_path_out receives input.objfile resolved against the
+ * toml's directory (renderer.cpp:236-241). type_out receives renderer.type. */
+int trb_host_load_toml(const char* toml_path, trb_render_desc* out, char* obj_path_out, size_t obj_len,
+                       char* type_out, size_t type_len, int* realtime_out);
+/* saveEXR (src/core/utils.h:95-156): channels B,G,R stored as half, row 0 = top. */
+int trb_host_save_exr(const char* path, const float* rgb, int width, int height);
+const char* trb_host_last_error(void);
+
+/* Host-side derived data, exposed so tests can pin them against the reference (no GPU needed):
+ * the build-reordered primitive order of BVH::build (externals/bvh.h:147-247): order[pos] = global tri id */
+int trb_host_bvh_order(const trb_scene_desc*, int32_t* order_out, size_t n);
+/* emitters as Scene::load builds them (renderer.cpp:279-305): returns count; per emitter shape id, area,
+ * radiance(3); cdf_out receives the concatenated normalised face-area CDFs (n_faces+1 each) if non-null */
+int trb_host_emitters(const trb_scene_desc*, int32_t* shape_out, float* area_out, float* radiance_out,
+                      size_t max_emitters, float* cdf_out, size_t cdf_capacity);
+/* camera matrices as glm builds them (renderer.cpp:143-153, bdpt.h:485-490): 4 column-major mat4:
+ * worldToCamera, cameraToWorld, cameraToClip, NDCToScreen */
+int trb_host_camera_matrices(const trb_render_desc*, float* out64);
+
+/* ---- device side ------------------------------------------------------------------------------- */
+int trb_create(int device, trb_context** out);
+void trb_destroy(trb_context*);
+const char* trb_last_error(const trb_context*);
+
+/* Scene::load's tail + AcceleratorBVH::build (renderer.cpp:259-312, accel.h:115-123): derives BSDF
+ * parameters, emitters and the BVH on the host and uploads the flattened scene. */
+int trb_scene_upload(trb_context*, const trb_scene_desc*);
+/* bytes of the flattened device scene (nodes + triangles + shading records + tables) */
+size_t trb_scene_device_bytes(const trb_context*);
+
+/* Renderer::render offline branch + BDPTIntegrator (renderer.cpp:130-214, bdpt.h:37-518).
+ * rgb_out: host, width*height*3 floats, row 0 = top (RenderBuffer, core.h:128-146); may be NULL.
+ * The device frame buffer is cleared first unless accumulate != 0. */
+int trb_render_bdpt(trb_context*, const trb_render_desc*, int accumulate, float* rgb_out, trb_stats* stats);
+/* Same, result left in a caller-provided DEVICE buffer (width*height*3 floats) - used for the multi-GPU
+ * NCCL reduce and the device-resident throughput measurement. */
+int trb_render_bdpt_device(trb_context*, const trb_render_desc*, int accumulate, float* d_rgb, trb_stats* stats);
+
+/* Parity entry points (north_star levels 1 and 2). Host buffers in, host buffers out. */
+int trb_trace_closest(trb_context*, const trb_ray* rays, size_t n, trb_hit* out);   /* accel.h:125-172 */
+int trb_trace_any(trb_context*, const trb_ray* rays, size_t n, uint8_t* out);       /* bvh.h:259-352, occlusion=true (bdpt.h:505) */
+int trb_bsdf_batch(trb_context*, const trb_bsdf_query* q, size_t n, trb_bsdf_out* out); /* BSDF::{eval,pdf,sample,getType} */
+/* BDPTIntegrator::render on n given camera rays with injected random numbers: rng is n x stride floats,
+ * consumed per path in the reference's order.  li_out: n x 3.  Light-tracing splats:
+ * splat_pix n x (rr_depth-1) pixel indices (-1 = none), splat_rgb n x (rr_depth-1) x 3, slot = light depth-1.
+ * draws_out (optional): random numbers consumed per path. */
+int trb_bdpt_paths(trb_context*, const trb_render_desc*, const trb_ray* cam_rays, const float* rng, size_t n,
+                   size_t stride, float* li_out, int32_t* splat_pix, float* splat_rgb, int32_t* draws_out);
+
+/* Device-resident variants used by the benchmark (pointers are DEVICE pointers). */
+int trb_trace_closest_device(trb_context*, const trb_ray* d_rays, size_t n, trb_hit* d_out, float* ms_out);
+int trb_trace_any_device(trb_context*, const trb_ray* d_rays, size_t n, uint8_t* d_out, float* ms_out);
+
+/* library build info: "sm_100a;fmad=off;..." */
+const char* trb_build_info(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TRB_H */
