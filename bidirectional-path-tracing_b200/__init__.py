@@ -247,7 +247,7 @@ class Context:
         self._h = C.c_void_p()
         rc = self._L.trb_create(int(device), C.byref(self._h))
         if rc < 0:
-            raise TrbError(rc, self._L.trb_host_last_error().decode())
+            raise TrbError(rc, self._L.trb_last_error(None).decode())
         self.scene = None
 
     def close(self) -> None:

@@ -1,0 +1,460 @@
+// bdpt_kernels.cuh -- the BDPT wavefront: one launch per stage over a wave of P samples.
+// Replaces BDPTIntegrator (src/integrators/bdpt.h:37-518) and the offline pixel loop of
+// Renderer::render (src/core/renderer.cpp:130-214).  Stage order per wave (host side: trb_abi.cu):
+//   gen_camera -> trace_closest -> light_init -> K x [trace_closest, light_bounce, trace_any+resolve]
+//   -> eye_init -> K x [(trace_closest), eye_bounce, trace_any+resolve]
+// Live samples are compacted into queues with warp-ballot pushes; every shadow ray carries its pending
+// contribution, so one resolve kernel serves light-tracing splats, NEE and vertex connections alike.
+#pragma once
+#include "bdpt_common.cuh"
+
+namespace trbk {
+
+#define TRB_BLOCK 128
+
+__device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref}; }
+
+// ---- generic traversal kernels (also behind trb_trace_closest / trb_trace_any) --------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_trace_closest(SceneDev sc, const RayT* __restrict__ rays, const int32_t* __restrict__ q,
+                                                              const uint32_t* __restrict__ n_ptr, uint32_t n_fixed, HitT* __restrict__ hits,
+                                                              unsigned long long* __restrict__ visit_counters) {
+    uint32_t n = n_ptr ? *n_ptr : n_fixed;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        int32_t i = q ? q[k] : int32_t(k);
+        RayT r = rays[i];
+        HitT h; bool occ;
+#ifdef TRB_COUNTERS
+        uint32_t nn = 0, nt = 0;
+        trace_ray<false>(bvh_of(sc), r, &h, &occ, &nn, &nt);
+        if (visit_counters) { atomicAdd(visit_counters, (unsigned long long)nn); atomicAdd(visit_counters + 1, (unsigned long long)nt); }
+#else
+        trace_ray<false>(bvh_of(sc), r, &h, &occ, nullptr, nullptr);
+#endif
+        hits[i] = h;
+    }
+}
+
+// occlusion query; either writes the flag (ABI) or resolves the pending contribution with atomics
+__global__ void __launch_bounds__(TRB_BLOCK) k_trace_any(SceneDev sc, const RayT* __restrict__ rays, const uint32_t* __restrict__ n_ptr,
+                                                          uint32_t n_fixed, uint32_t cap, uint8_t* __restrict__ occ_out,
+                                                          const Pending* __restrict__ pend, float* __restrict__ accum,
+                                                          unsigned long long* __restrict__ visit_counters) {
+    uint32_t n = n_ptr ? min(*n_ptr, cap) : n_fixed;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        RayT r = rays[k];
+        HitT h; bool occ;
+#ifdef TRB_COUNTERS
+        uint32_t nn = 0, nt = 0;
+        trace_ray<true>(bvh_of(sc), r, &h, &occ, &nn, &nt);
+        if (visit_counters) { atomicAdd(visit_counters, (unsigned long long)nn); atomicAdd(visit_counters + 1, (unsigned long long)nt); }
+#else
+        trace_ray<true>(bvh_of(sc), r, &h, &occ, nullptr, nullptr);
+#endif
+        if (occ_out) occ_out[k] = occ ? 1 : 0;
+        if (pend && !occ) {
+            Pending pd = pend[k];
+            float* a = accum + size_t(pd.target) * 3;
+            atomicAdd(a, pd.r); atomicAdd(a + 1, pd.g); atomicAdd(a + 2, pd.b);  // replaces g_FrameBufferLocks (bdpt.h:360-370)
+        }
+    }
+}
+
+// ---- camera rays (renderer.cpp:161-192) ------------------------------------------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_gen_camera(const __grid_constant__ WaveParams p) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= p.P) return;
+    uint32_t ctr = 0;
+    RayT r;
+    if (p.parity) {
+        r = p.inject_rays[i];
+    } else {
+        uint32_t pixel, sample;
+        slot_ids(p, i, &pixel, &sample);
+        Rng rng = make_rng(p, i, pixel, sample, 0);
+        int j = int(pixel % uint32_t(p.cam.width)), row = int(pixel / uint32_t(p.cam.width));
+        float y = (1.f - ((float)row + 0.5f) * p.cam.inv_h) * 2.f - 1.f;
+        float x = (((float)j + 0.5f) * p.cam.inv_w) * 2.f - 1.f;
+        float px, py;
+        if (p.spp == 1 || (p.flags & TRB_FLAG_NO_JITTER)) {
+            px = x * p.cam.tan_half_fov * p.cam.aspect; py = y * p.cam.tan_half_fov;
+        } else {
+            float rx = rng.next(), ry = rng.next();
+            rx -= 0.5f; ry -= 0.5f;
+            rx = rx * p.cam.inv_w; ry = ry * p.cam.inv_h;
+            px = (x + rx) * p.cam.tan_half_fov * p.cam.aspect; py = (y + ry) * p.cam.tan_half_fov;
+        }
+        float4 d4 = mat_mul(p.cam.c2w, make_float4(px, py, -1.f, 0.f));
+        V3 d = normalize(mk(d4.x, d4.y, d4.z));
+        r.ox = p.cam.eye[0]; r.oy = p.cam.eye[1]; r.oz = p.cam.eye[2];
+        r.dx = d.x; r.dy = d.y; r.dz = d.z; r.min_t = 1.f; r.max_t = 1000.f;
+        ctr = rng.ctr;
+    }
+    p.cam_ray[i] = r;
+    p.st_v[i] = make_float4(0.f, __uint_as_float(0u), __uint_as_float(ctr), 0.f);
+}
+
+// ---- connectToCamera (bdpt.h:295-371) + splatToImagePlane (bdpt.h:485-496) ---------------------------------
+__device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool active, int slot, int depth, const Surf& s, const Mat& m,
+                                                  V3 T, float vcm, float vc) {
+    bool want = false;
+    RayT sr; V3 radiance = mk(0.f); uint32_t target = 0;
+    if (active) {
+        V3 eye = mk(p.cam.eye[0], p.cam.eye[1], p.cam.eye[2]);
+        V3 fwd = mk(p.cam.forward[0], p.cam.forward[1], p.cam.forward[2]);
+        V3 e2l = s.p - eye;
+        float invD2 = 1.f / length2(e2l);
+        e2l = e2l * sqrtf(invD2);
+        float4 uv = mat_mul(p.cam.w2c, make_float4(s.p.x, s.p.y, s.p.z, 1.f));
+        uv = mat_mul(p.cam.clip, uv);
+        uv = make_float4(uv.x / uv.w, uv.y / uv.w, uv.z / uv.w, uv.w / uv.w);
+        uv = mat_mul(p.cam.ndc2screen, uv);
+        int xp = __float2int_rz(uv.x), yp = __float2int_rz(uv.y);
+        bool ok = !(xp < 0 || yp < 0 || xp >= p.cam.width || yp >= p.cam.height);
+        float cosCamera = dot(fwd, e2l);
+        ok = ok && !(cosCamera <= 0.f);
+        if (ok) {
+            V3 wi = to_local(s.f, -e2l);
+            V3 fcos = bsdf_eval(m, s.wo, wi);
+            if (!(is_zero(fcos) || wi.z <= 0.f)) {
+                sr = visibility_ray(eye, s.p);
+                float ipd = p.cam.vnear_dist / cosCamera;
+                float imgToSolid = ipd * ipd / cosCamera;
+                float solidToArea = wi.z * invD2;
+                float imgToSurf = imgToSolid * solidToArea;
+                float surfToImg = 1.f / imgToSurf;
+                int nlight = p.cam.width * p.cam.height;
+                radiance = T * (fcos * (1.f / wi.z)) * (1.f / surfToImg) * (1.f / nlight) * (1.f / p.spp);
+                float revPdfA = 1.f * imgToSurf;
+                float prevRev = bsdf_pdf(m, wi, s.wo) * 1.f;  // wi/wo swapped, rr = 1 (NO_RR)
+                float lightWeight = (revPdfA / nlight) * (vcm + prevRev * vc);
+                float mis = 1.f / (lightWeight + 1.f + 0.f);
+                radiance = radiance * mis;
+                int pixel = yp * p.cam.width + xp;
+                if (p.parity) {
+                    target = uint32_t(slot) * uint32_t(p.K + 1) + uint32_t(depth);
+                    p.splat_pix[size_t(slot) * p.K + (depth - 1)] = pixel;
+                } else {
+                    target = uint32_t(pixel);
+                }
+                want = true;
+            }
+        }
+    }
+    push_shadow(p, want, sr, radiance, target);
+}
+
+// ---- ContinuePathRandomWalk (bdpt.h:243-291); returns false when the walk stops ------------------------------
+__device__ __forceinline__ bool continue_walk(const Surf& s, const Mat& m, Rng& rng, V3* T, float* vc, float* vcm, RayT* next, V3* wi_out) {
+    float ux = rng.next(), uy = rng.next();
+    V3 wi; float pdf;
+    V3 fcos = bsdf_sample(m, s.wo, ux, uy, &wi, &pdf);
+    pdf *= 1.f;
+    *wi_out = wi;
+    float absCosOut = fabsf(wi.z);
+    if (is_zero(fcos)) return false;
+    *T = *T * (fcos * (1.f / pdf));
+    bool delta = is_delta(m);
+    float prevRev = delta ? pdf : bsdf_pdf(m, wi, s.wo) * 1.f;
+    if (delta) {
+        *vc = (absCosOut / pdf) * (prevRev * *vc);
+        *vcm = 0.f;
+    } else {
+        *vc = (absCosOut / pdf) * (*vcm + prevRev * *vc);
+        *vcm = 1.f / pdf;
+    }
+    V3 d = to_world(s.f, wi);
+    next->ox = s.p.x; next->oy = s.p.y; next->oz = s.p.z; next->dx = d.x; next->dy = d.y; next->dz = d.z;
+    next->min_t = 1e-8f; next->max_t = FLT_MAX;
+    return true;
+}
+
+// ---- light subpath start (bdpt.h:158-186) -------------------------------------------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant__ WaveParams p) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool in = i < p.P;
+    bool go = false;
+    if (in) {
+        RayT cr = p.cam_ray[i];
+        HitT h = p.hit[i];
+        p.hit0[i] = h;
+        p.nlv[i] = 0;
+        float4 sv = p.st_v[i];
+        uint32_t ctr = __float_as_uint(sv.z);
+        uint32_t flags = 0;
+        if (hit_valid(h, cr)) {  // bdpt.h:225: no subpaths at all when the primary ray misses
+            flags |= 2u;
+            uint32_t pixel, sample;
+            slot_ids(p, i, &pixel, &sample);
+            Rng rng = make_rng(p, i, pixel, sample, ctr);
+            EmitterSample es = sample_emitter(p.sc, rng);
+            float ux = rng.next(), uy = rng.next();
+            V3 ed = sq_to_uniform_hemisphere(ux, uy);
+            float emissionPdf = TRB_INV_TWOPI * es.area_pdf;
+            float areaPdf = es.area_pdf * es.sel_pdf;
+            emissionPdf *= es.sel_pdf;
+            Frame lf = make_frame(es.n);
+            V3 wd = to_world(lf, ed);
+            V3 T = ed.z * es.radiance * (1.f / emissionPdf);
+            float vc = ed.z * (1.f / emissionPdf);
+            float vcm = areaPdf / emissionPdf;
+            if (!(ed.z <= 0.f)) {
+                if (1 < p.rr_depth) {
+                    go = true;
+                    RayT lr; lr.ox = es.pos.x; lr.oy = es.pos.y; lr.oz = es.pos.z; lr.dx = wd.x; lr.dy = wd.y; lr.dz = wd.z;
+                    lr.min_t = 1e-8f; lr.max_t = FLT_MAX;
+                    p.ray[i] = lr;
+                    p.st_t[i] = make_float4(T.x, T.y, T.z, vcm);
+                    sv.x = vc;
+                } else {
+                    rng.next();  // the failing loop test still draws one number (Q3)
+                }
+            }
+            ctr = rng.ctr;
+        }
+        sv.y = __uint_as_float(flags); sv.z = __uint_as_float(ctr);
+        p.st_v[i] = sv;
+    }
+    uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
+    if (go) p.q_out[idx] = i;
+}
+
+// ---- one light bounce (body of the loop at bdpt.h:188-216) -------------------------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_light_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
+    uint32_t n = *n_in;
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    bool in = k < n;
+    int slot = in ? p.q_in[k] : 0;
+    bool alive = false, connect = false, go = false;
+    Surf s; Mat m; V3 T = mk(0.f); float vcm = 0.f, vc = 0.f;
+    float4 sv = make_float4(0.f, 0.f, 0.f, 0.f);
+    RayT r;
+    if (in) {
+        r = p.ray[slot];
+        HitT h = p.hit[slot];
+        sv = p.st_v[slot];
+        if (hit_valid(h, r)) {
+            alive = true;
+            s = make_surf(p.sc, h, r);
+            m = load_mat(p.sc.mats, s.mat);
+            float4 st = p.st_t[slot];
+            T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
+            const float distSquared = s.t * s.t;
+            const float absCosIn = fabsf(s.wo.z);
+            vcm *= (distSquared / absCosIn);
+            vc *= (1.f / absCosIn);
+            connect = !is_delta(m);
+        }
+    }
+    connect_to_camera(p, connect, slot, depth, s, m, T, vcm, vc);
+    if (alive) {
+        uint32_t pixel, sample;
+        slot_ids(p, slot, &pixel, &sample);
+        Rng rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
+        V3 Tn = T; float vcn = vc, vcmn = vcm; RayT nr; V3 wi;
+        if (continue_walk(s, m, rng, &Tn, &vcn, &vcmn, &nr, &wi)) {
+            if (connect) {  // non-delta vertices whose continuation succeeded are kept (bdpt.h:211-215, Q11)
+                int j = p.nlv[slot];
+                LightVertex lv;
+                lv.px = s.p.x; lv.py = s.p.y; lv.pz = s.p.z; lv.vcm = vcm;
+                lv.nx = s.n.x; lv.ny = s.n.y; lv.nz = s.n.z; lv.vc = vc;
+                lv.wox = s.wo.x; lv.woy = s.wo.y; lv.woz = s.wo.z; lv.mat = s.mat;
+                lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.pad = 0.f;
+                p.lv[size_t(j) * p.P + slot] = lv;
+                p.nlv[slot] = j + 1;
+            }
+            if (depth + 1 < p.rr_depth) {
+                go = true;
+                p.ray[slot] = nr;
+                p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
+                sv.x = vcn;
+            } else {
+                rng.next();  // depth cap: the loop test draws once more (Q3)
+            }
+        }
+        sv.z = __uint_as_float(rng.ctr);
+        p.st_v[slot] = sv;
+    }
+    uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
+    if (go) p.q_out[idx] = slot;
+}
+
+// ---- eye subpath start (bdpt.h:46-66) ------------------------------------------------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ WaveParams p) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    bool go = false;
+    if (i < p.P) {
+        float4 sv = p.st_v[i];
+        uint32_t flags = __float_as_uint(sv.y);
+        if (flags & 2u) {
+            RayT cr = p.cam_ray[i];
+            V3 fwd = mk(p.cam.forward[0], p.cam.forward[1], p.cam.forward[2]);
+            float cosCamera = dot(fwd, mk(cr.dx, cr.dy, cr.dz));
+            float ipd = p.cam.vnear_dist / cosCamera;
+            float imgToSolid = ipd * ipd / cosCamera;
+            float t1Pdf = 1.f * imgToSolid;
+            float vcm = float(p.cam.width * p.cam.height) * (1.f / t1Pdf);
+            if (1 < p.rr_depth) {
+                go = true;
+                p.ray[i] = cr;
+                p.hit[i] = p.hit0[i];
+                p.st_t[i] = make_float4(1.f, 1.f, 1.f, vcm);
+                sv.x = 0.f;
+                sv.y = __uint_as_float(flags | SLOT_PURE_SPECULAR);
+            } else {
+                sv.z = __uint_as_float(__float_as_uint(sv.z) + 1u);
+            }
+            p.st_v[i] = sv;
+        }
+    }
+    uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
+    if (go) p.q_out[idx] = i;
+}
+
+// ---- one eye bounce (body of the loop at bdpt.h:68-154) --------------------------------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_eye_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
+    uint32_t n = *n_in;
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    bool in = k < n;
+    int slot = in ? p.q_in[k] : 0;
+    bool alive = false, connect = false, go = false;
+    Surf s; Mat m; V3 T = mk(0.f); float vcm = 0.f, vc = 0.f;
+    float4 sv = make_float4(0.f, 0.f, 0.f, 0.f);
+    uint32_t pixel = 0, sample = 0, li_target = 0;
+    const float li_scale = p.parity ? 1.f : (1.f / p.spp);  // renderer.cpp:201: averageRadiance * (1.f / spp)
+    Rng rng; rng.inj = nullptr; rng.key = 0; rng.ctr = 0;
+    if (in) {
+        RayT r = p.ray[slot];
+        HitT h = p.hit[slot];
+        sv = p.st_v[slot];
+        slot_ids(p, slot, &pixel, &sample);
+        li_target = p.parity ? uint32_t(slot) * uint32_t(p.K + 1) : pixel;
+        rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
+        if (hit_valid(h, r)) {
+            alive = true;
+            s = make_surf(p.sc, h, r);
+            m = load_mat(p.sc.mats, s.mat);
+            float4 st = p.st_t[slot];
+            T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
+            const float distSquared = s.t * s.t;
+            const float absCosIn = fabsf(s.wo.z);
+            vcm *= (distSquared / absCosIn);
+            vc *= (1.f / absCosIn);
+            if (m.emissive) {  // bdpt.h:79-125: emitter hit ends the walk
+                bool pure = (__float_as_uint(sv.y) & SLOT_PURE_SPECULAR) != 0;
+                V3 c;
+                if (depth > 1) {
+                    const float4* ep = reinterpret_cast<const float4*>(p.sc.emitters + s.emitter);
+                    float4 e0 = __ldg(ep);
+                    float emitterPdf = 1.f / float(p.sc.n_emitters);
+                    c = mk(e0.x, e0.y, e0.z) * T;
+                    float posPdfA = 1.f / (e0.w * emitterPdf);
+                    float dirPdfW = TRB_INV_TWOPI;
+                    float cameraWeight = posPdfA * vcm + (posPdfA * dirPdfW) * vc;
+                    float mis = 1.f / (1.f + cameraWeight);
+                    if (!pure) c = c * mis;
+                } else {
+                    c = m.ke;
+                }
+                c = c * li_scale;
+                float* a = p.accum + size_t(li_target) * 3;
+                atomicAdd(a, c.x); atomicAdd(a + 1, c.y); atomicAdd(a + 2, c.z);
+                alive = false;
+            } else {
+                connect = !is_delta(m);
+            }
+        }
+    }
+    // ---- connectToLight (bdpt.h:374-430) ----
+    {
+        bool want = false; RayT sr; V3 Li = mk(0.f);
+        if (connect) {
+            EmitterSample es = sample_emitter(p.sc, rng);
+            V3 l2e = s.p - es.pos;
+            float d2 = length2(l2e);
+            l2e = l2e * (1.f / sqrtf(d2));
+            V3 wi = to_local(s.f, -l2e);
+            float cosAtLight = dot(es.n, l2e);
+            float cosAtEye = wi.z;
+            if (!(cosAtLight <= 0.f || cosAtEye <= 0.f)) {
+                float connA = es.sel_pdf * es.area_pdf;
+                float connW = connA * d2 / cosAtLight;
+                float dirPdfW = TRB_INV_TWOPI;
+                Li = bsdf_eval(m, s.wo, wi) * (1.f / connW) * T * es.radiance;
+                if (!is_zero(Li)) {
+                    sr = visibility_ray(s.p, es.pos);
+                    float lightRevW = bsdf_pdf(m, s.wo, wi) * 1.f;
+                    float lightWeight = lightRevW / connW;
+                    float eyePrevRevW = bsdf_pdf(m, wi, s.wo) * 1.f;
+                    float eyeCurRevA = cosAtEye * (1.f / d2) * dirPdfW;
+                    float eyeWeight = eyeCurRevA * (vcm + eyePrevRevW * vc);
+                    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
+                    Li = Li * mis;
+                    Li = Li * li_scale;
+                    want = true;
+                }
+            }
+        }
+        push_shadow(p, want, sr, Li, li_target);
+    }
+    // ---- connectVertices (bdpt.h:434-483) against every stored light vertex of this sample ----
+    {
+        int nl = connect ? p.nlv[slot] : 0;
+        int nmax = __reduce_max_sync(0xffffffffu, nl);
+        for (int j = 0; j < nmax; ++j) {
+            bool want = false; RayT sr; V3 Li = mk(0.f);
+            if (j < nl) {
+                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(j) * p.P + slot);
+                float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
+                V3 lpnt = mk(a.x, a.y, a.z);
+                V3 l2e = s.p - lpnt;
+                float invD2 = 1.f / length2(l2e);
+                l2e = l2e * sqrtf(invD2);
+                Frame lf = make_frame(mk(b.x, b.y, b.z));
+                V3 l_wo = mk(c.x, c.y, c.z);
+                V3 l_wi = to_local(lf, l2e);
+                V3 e_wi = to_local(s.f, -l2e);
+                float cosL = l_wi.z, cosE = e_wi.z;
+                if (!(cosL <= 0.f || cosE <= 0.f)) {
+                    Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
+                    Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, s.wo, e_wi);
+                    Li = Li * (mk(d.x, d.y, d.z) * T * invD2);
+                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * 1.f;
+                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * 1.f;
+                    float lightRevW = bsdf_pdf(m, s.wo, e_wi) * 1.f;
+                    float eyePrevRevW = bsdf_pdf(m, e_wi, s.wo) * 1.f;
+                    float lightRevA = lightRevW * (cosL) * invD2;
+                    float eyeRevA = eyeRevW * (cosE) * invD2;
+                    float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);
+                    float eyeWeight = eyeRevA * (vcm + eyePrevRevW * vc);
+                    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
+                    Li = Li * mis;
+                    Li = Li * li_scale;
+                    if (!is_zero(Li)) { sr = visibility_ray(s.p, lpnt); want = true; }
+                }
+            }
+            push_shadow(p, want, sr, Li, li_target);
+        }
+    }
+    if (in) {
+        if (alive) {
+            if (connect) sv.y = __uint_as_float(__float_as_uint(sv.y) & ~SLOT_PURE_SPECULAR);
+            V3 Tn = T; float vcn = vc, vcmn = vcm; RayT nr; V3 wi;
+            if (continue_walk(s, m, rng, &Tn, &vcn, &vcmn, &nr, &wi)) {
+                if (depth + 1 < p.rr_depth) {
+                    go = true;
+                    p.ray[slot] = nr;
+                    p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
+                    sv.x = vcn;
+                } else {
+                    rng.next();
+                }
+            }
+        }
+        sv.z = __uint_as_float(rng.ctr);
+        p.st_v[slot] = sv;
+    }
+    uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
+    if (go) p.q_out[idx] = slot;
+}
+
+}  // namespace trbk

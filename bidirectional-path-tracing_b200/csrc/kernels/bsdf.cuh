@@ -1,0 +1,192 @@
+// bsdf.cuh -- BSDF::{eval,pdf,sample} for the five material classes of the reference, in the local
+// shading frame, returning f*cos(theta_i) exactly as the reference does.
+//   DiffuseBSDF  src/bsdfs/diffuse.h:35-61      PhongBSDF   src/bsdfs/phong.h:61-105
+//   MixtureBSDF  src/bsdfs/mixture.h:60-151     MirrorBSDF  src/bsdfs/perfectmirror.h:33-59
+//   GlassBSDF    src/bsdfs/glass.h:40-108       Warp::*     src/core/math.h:118-268
+// Operation order follows the C++ expressions so that, with -fmad=false, only the transcendental
+// functions can differ from the x86-64 build; those go through fp64 (TRB_EXACT_TRANSCENDENTALS) so that the
+// fp32 result is the correctly rounded one glibc returns in all but ~1e-8 of the cases.
+#pragma once
+#include "../host/tr_host.h"
+#include "vec.cuh"
+
+#ifndef TRB_EXACT_TRANSCENDENTALS
+#define TRB_EXACT_TRANSCENDENTALS 1
+#endif
+
+namespace trbk {
+
+#if TRB_EXACT_TRANSCENDENTALS
+__device__ __forceinline__ float t_sinf(float x) { return (float)sin((double)x); }
+__device__ __forceinline__ float t_cosf(float x) { return (float)cos((double)x); }
+__device__ __forceinline__ float t_powf(float x, float y) { return (float)pow((double)x, (double)y); }
+#else
+__device__ __forceinline__ float t_sinf(float x) { return sinf(x); }
+__device__ __forceinline__ float t_cosf(float x) { return cosf(x); }
+__device__ __forceinline__ float t_powf(float x, float y) { return powf(x, y); }
+#endif
+
+struct Mat {
+    V3 kd, ks, ke, tf;
+    float ns, ni, scale, sw;
+    int cls;
+    uint32_t type;
+    bool emissive;
+};
+
+__device__ __forceinline__ Mat load_mat(const trb::DevMaterial* mats, int id) {
+    const float4* p = reinterpret_cast<const float4*>(mats + id);
+    float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3), e = __ldg(p + 4);
+    Mat m;
+    m.kd = mk(a.x, a.y, a.z); m.cls = __float_as_int(a.w);
+    m.ks = mk(b.x, b.y, b.z); m.type = __float_as_uint(b.w);
+    m.ke = mk(c.x, c.y, c.z); m.ns = c.w;
+    m.tf = mk(d.x, d.y, d.z); m.ni = d.w;
+    m.scale = e.x; m.sw = e.y; m.emissive = __float_as_int(e.z) != 0;
+    return m;
+}
+
+__device__ __forceinline__ bool is_delta(const Mat& m) { return (m.type & (0x1u | 0x20u | 0x40u)) != 0; }  // BSDF::EDelta
+
+__device__ __forceinline__ V3 reflect_z(V3 d) { return mk(-d.x, -d.y, d.z); }
+
+// ---- Warp (math.h) ---------------------------------------------------------------------------------
+__device__ __forceinline__ V3 sq_to_uniform_hemisphere(float ux, float uy) {  // math.h:136-144
+    float phi = ux * TRB_PI * 2.0f;
+    float cosTheta = uy;
+    float sinTheta = sqrtf(fmaxf(1.f - (cosTheta * cosTheta), 0.f));
+    return mk(sinTheta * t_cosf(phi), sinTheta * t_sinf(phi), cosTheta);
+}
+
+__device__ __forceinline__ V3 sq_to_cosine_hemisphere(float ux, float uy) {  // math.h:153-192
+    float rx = (2.f * ux) - 1.f, ry = (2.f * uy) - 1.f;
+    float dx = 0.f, dy = 0.f;
+    if (!(rx == 0 && ry == 0)) {
+        float phi, radius;
+        if ((rx * rx) > (ry * ry)) { radius = rx; phi = (TRB_PI * 0.25f) * (ry * (1.f / rx)); }
+        else { radius = ry; phi = (TRB_PI * 0.5f) - ((TRB_PI * 0.25f) * (rx * (1.f / ry))); }
+        dx = radius * t_cosf(phi); dy = radius * t_sinf(phi);
+    }
+    float z = 1.0f - (dx * dx + dy * dy);
+    z = fmaxf(z, 0.f);
+    z = sqrtf(z);
+    return mk(dx, dy, z);
+}
+
+__device__ __forceinline__ float cosine_hemisphere_pdf(V3 v) { return v.z >= 0.f ? v.z * TRB_INV_PI : 0.f; }  // math.h:194-208
+
+__device__ __forceinline__ V3 sq_to_phong_lobe(float ux, float uy, float exponent) {  // math.h:210-219
+    float cosTheta = t_powf(ux, 1.f / (exponent + 2));
+    float sinTheta = sqrtf(fmaxf(1.f - (cosTheta * cosTheta), 0.f));
+    float phi = uy * 2.f * TRB_PI;
+    return mk(sinTheta * t_cosf(phi), sinTheta * t_sinf(phi), cosTheta);
+}
+
+__device__ __forceinline__ float phong_lobe_pdf(V3 v, float exponent) {  // math.h:221-227
+    return v.z >= 0.f ? (exponent + 2) * TRB_INV_TWOPI * t_powf(v.z, exponent) : 0.f;
+}
+
+// ---- eval / pdf / sample ---------------------------------------------------------------------------
+__device__ __forceinline__ V3 glossy_eval(const Mat& m, V3 wo, V3 wi) {  // phong.h:61-74 == mixture.h:60-73
+    V3 val = mk(0.f);
+    if (wi.z >= 0.f && wo.z >= 0.f) {
+        val = val + m.kd * TRB_INV_PI;
+        float e = m.ns;
+        float cosTheta = fminf(fmaxf(dot(wi, reflect_z(wo)), 0.f), 1.f);
+        val = val + m.ks * (e + 2) * TRB_INV_TWOPI * t_powf(cosTheta, e);
+        val = val * m.scale;
+        val = val * wi.z;
+    }
+    return val;
+}
+
+__device__ __forceinline__ V3 bsdf_eval(const Mat& m, V3 wo, V3 wi) {
+    switch (m.cls) {
+        case trb::MAT_DIFFUSE:
+            if (wi.z >= 0.f && wo.z >= 0.f) return m.kd * TRB_INV_PI * wi.z;  // diffuse.h:35-43
+            return mk(0.f);
+        case trb::MAT_PHONG:
+        case trb::MAT_MIXTURE: return glossy_eval(m, wo, wi);
+        default: return mk(0.f);  // delta lobes: perfectmirror.h:33-38, glass.h:55-58
+    }
+}
+
+__device__ __forceinline__ float phong_pdf(const Mat& m, V3 wo, V3 wi) {  // phong.h:76-87
+    Frame rf = make_frame(reflect_z(wo));
+    V3 s = to_local(rf, wi);
+    return phong_lobe_pdf(s, m.ns);
+}
+
+__device__ __forceinline__ float bsdf_pdf(const Mat& m, V3 wo, V3 wi) {
+    switch (m.cls) {
+        case trb::MAT_DIFFUSE: return cosine_hemisphere_pdf(wi);  // diffuse.h:45-50
+        case trb::MAT_PHONG: return phong_pdf(m, wo, wi);
+        case trb::MAT_MIXTURE: {  // mixture.h:75-93
+            float pp = phong_pdf(m, wo, wi);
+            float pd = cosine_hemisphere_pdf(wi);
+            return (pp * m.sw) + (pd * (1.f - m.sw));
+        }
+        default: return 0.f;
+    }
+}
+
+__device__ __forceinline__ float fresnel_dielectric(float eta_i, float eta_t, float cos_i, float cos_t) {  // glass.h:40-53
+    float eta = eta_i / eta_t;
+    float sin2_t = eta * eta * (fmaxf(0.f, 1.f - cos_i * cos_i));
+    if (sin2_t >= 1.f) return 1.f;
+    float rPar = ((eta_t * cos_i) - (eta_i * cos_t)) / ((eta_t * cos_i) + (eta_i * cos_t));
+    float rPer = ((eta_i * cos_i) - (eta_t * cos_t)) / ((eta_i * cos_i) + (eta_t * cos_t));
+    return (rPar * rPar + rPer * rPer) * 0.5f;
+}
+
+// BSDF::sample: writes wi and pdf, returns f*cos
+__device__ __forceinline__ V3 bsdf_sample(const Mat& m, V3 wo, float ux, float uy, V3* wi, float* pdf) {
+    switch (m.cls) {
+        case trb::MAT_DIFFUSE: {  // diffuse.h:52-61
+            *wi = sq_to_cosine_hemisphere(ux, uy);
+            *pdf = cosine_hemisphere_pdf(*wi);
+            return bsdf_eval(m, wo, *wi);
+        }
+        case trb::MAT_PHONG: {  // phong.h:89-105
+            Frame rf = make_frame(reflect_z(wo));
+            V3 s = sq_to_phong_lobe(ux, uy, m.ns);
+            *pdf = phong_lobe_pdf(s, m.ns);
+            *wi = to_world(rf, s);
+            return glossy_eval(m, wo, *wi);
+        }
+        case trb::MAT_MIXTURE: {  // mixture.h:95-151
+            if (ux < m.sw) {
+                Frame rf = make_frame(reflect_z(wo));
+                V3 s = sq_to_phong_lobe(ux / m.sw, uy, m.ns);
+                *wi = to_world(rf, s);
+            } else {
+                *wi = sq_to_cosine_hemisphere((ux - m.sw) / (1.f - m.sw), uy);
+            }
+            V3 val = glossy_eval(m, wo, *wi);
+            *pdf = bsdf_pdf(m, wo, *wi);
+            return val;
+        }
+        case trb::MAT_MIRROR: {  // perfectmirror.h:48-59
+            *pdf = 1.f;
+            *wi = reflect_z(wo);
+            return mk(1.f);
+        }
+        default: {  // glass.h:60-108
+            *pdf = 1.f;
+            bool entering = wo.z > 0.f;
+            float eta_i = 1.f, eta_t = m.ni;
+            if (!entering) { float s = eta_i; eta_i = eta_t; eta_t = s; }
+            float eta = eta_i / eta_t;
+            float sin2_i = fmaxf(0.f, 1.f - wo.z * wo.z);
+            float sin2_t = eta * eta * sin2_i;
+            float cos_t = sqrtf(fmaxf(0.f, 1.f - sin2_t));
+            cos_t = entering ? -cos_t : cos_t;
+            float fr = fresnel_dielectric(eta_i, eta_t, fabsf(wo.z), fabsf(cos_t));
+            if (ux < fr) { *wi = reflect_z(wo); return mk(1.f); }
+            *wi = mk(eta * -wo.x, eta * -wo.y, cos_t);
+            return m.tf;
+        }
+    }
+}
+
+}  // namespace trbk

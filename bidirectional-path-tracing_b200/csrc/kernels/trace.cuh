@@ -1,0 +1,227 @@
+// trace.cuh -- BVH traversal with the reference's exact hit semantics.
+//
+// Replaces BVH::getIntersection + BBox::intersect (externals/bvh.h:259-352, 33-69),
+// AcceleratorBVH::BVHNode::getIntersection + rayTriangleIntersect (src/core/accel.h:27-52,
+// src/core/core.h:379-400) and the range test of AcceleratorBVH::intersect (accel.h:131-133).
+//
+// Reference semantics: BBox::intersect never reports distances, so the reference visits
+// EVERY node whose box the infinite line passes (decided by six IEEE divisions) and answers
+//   closest : argmin (t, position in the build-reordered primitive list) over triangles with
+//             (double)t > 1e-3 and t < ray.max_t, all of whose ancestors' boxes passed;
+//   any-hit : exists such a triangle with t <= max_t (bvh.h:299-307 + :351).
+// This traversal returns exactly that, but ordered and pruned:
+//   * box decision: (b - o) * (1/d) is within 2 ulp of the reference's (b - o) / d; when the slab
+//     overlap is decided by less than ~5 ulp the six divisions are redone exactly as bvh.h:33-69
+//     (rare slow path), so the SET of visited subtrees is the reference's;
+//   * pruning by entry distance uses a pad far above Moller-Trumbore's error for non-degenerate
+//     configurations; a ray that meets an ill-conditioned candidate (grazing / origin in the triangle's
+//     plane, where the reference's t is rounding noise) is re-traced exhaustively, i.e. with the
+//     reference's own visiting rule;
+//   * ties in t keep the lower list position (bvh.h:305 strict '<', first found wins).
+// The functions are __host__ __device__ so that tools/host_trace_check.cpp can run the identical code
+// against the compiled reference on the CPU box (development aid only; the product runs it on the GPU).
+#pragma once
+#include <cfloat>
+#include <cmath>
+#include <cstdint>
+
+#if defined(__CUDACC__)
+#define TRB_HD __host__ __device__ __forceinline__
+#define TRB_HD_NOINLINE __host__ __device__ __noinline__
+#else
+#define TRB_HD inline
+#define TRB_HD_NOINLINE inline
+#endif
+
+namespace trbk {
+
+struct F4 { float x, y, z, w; };
+
+struct RayT {
+    float ox, oy, oz, dx, dy, dz, min_t, max_t;
+};
+
+struct HitT {
+    float t, u, v;
+    int32_t pos;  // position in the reordered triangle list, -1 = none
+};
+
+struct BvhView {
+    const F4* nodes;  // 4 x F4 per node (DevNode)
+    const F4* tris;   // 3 x F4 per triangle (DevTri)
+    int32_t root_ref;
+};
+
+#ifndef TRB_STACK
+#define TRB_STACK 64
+#endif
+
+TRB_HD int32_t f2i(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_int(f);
+#else
+    int32_t i; memcpy(&i, &f, 4); return i;
+#endif
+}
+
+#if defined(__CUDA_ARCH__)
+#define TRB_LDG4(p) __ldg(reinterpret_cast<const float4*>(p))
+TRB_HD F4 ld4(const F4* p) { float4 v = TRB_LDG4(p); return F4{v.x, v.y, v.z, v.w}; }
+TRB_HD float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+#else
+TRB_HD F4 ld4(const F4* p) { return *p; }
+TRB_HD float fdiv(float a, float b) { return a / b; }
+#endif
+
+// BBox::intersect verbatim in behaviour (bvh.h:33-69), returning also the clipped interval for ordering.
+// NaN comparisons are false exactly as in the reference.
+TRB_HD_NOINLINE bool box_exact(const float* bmin, const float* bmax, const RayT& r, float* enter, float* exit_) {
+    float tmin = fdiv(bmin[0] - r.ox, r.dx), tmax = fdiv(bmax[0] - r.ox, r.dx);
+    if (tmin > tmax) { float s = tmin; tmin = tmax; tmax = s; }
+    float tymin = fdiv(bmin[1] - r.oy, r.dy), tymax = fdiv(bmax[1] - r.oy, r.dy);
+    if (tymin > tymax) { float s = tymin; tymin = tymax; tymax = s; }
+    if ((tmin > tymax) || (tymin > tmax)) return false;
+    if (tymin > tmin) tmin = tymin;
+    if (tymax < tmax) tmax = tymax;
+    float tzmin = fdiv(bmin[2] - r.oz, r.dz), tzmax = fdiv(bmax[2] - r.oz, r.dz);
+    if (tzmin > tzmax) { float s = tzmin; tzmin = tzmax; tzmax = s; }
+    if ((tmin > tzmax) || (tzmin > tmax)) return false;
+    if (tzmin > tmin) tmin = tzmin;
+    if (tzmax < tmax) tmax = tzmax;
+    *enter = (tmin == tmin) ? tmin : -INFINITY;   // NaN -> never prune
+    *exit_ = (tmax == tmax) ? tmax : INFINITY;
+    return true;
+}
+
+struct RayPre {
+    float ix, iy, iz;  // 1/d, IEEE
+    bool degenerate;   // a zero/non-finite direction component: every box goes through box_exact
+};
+
+TRB_HD RayPre ray_pre(const RayT& r) {
+    RayPre p;
+    p.ix = fdiv(1.f, r.dx); p.iy = fdiv(1.f, r.dy); p.iz = fdiv(1.f, r.dz);
+    float s = (p.ix - p.ix) + (p.iy - p.iy) + (p.iz - p.iz);  // NaN unless all finite
+    p.degenerate = !(s == 0.f);
+    return p;
+}
+
+// Decides one child box the way the reference does; enter/exit are the (approximate) line parameters.
+TRB_HD bool box_test(const float* bmin, const float* bmax, const RayT& r, const RayPre& p, float* enter, float* exit_) {
+    if (!p.degenerate) {
+        float ax = (bmin[0] - r.ox) * p.ix, bx = (bmax[0] - r.ox) * p.ix;
+        float ay = (bmin[1] - r.oy) * p.iy, by = (bmax[1] - r.oy) * p.iy;
+        float az = (bmin[2] - r.oz) * p.iz, bz = (bmax[2] - r.oz) * p.iz;
+        float en = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+        float ex = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        float gap = ex - en;
+        float tol = 6e-7f * fmaxf(fabsf(en), fabsf(ex)) + 1e-30f;
+        if (gap > tol) { *enter = en; *exit_ = ex; return true; }
+        if (gap < -tol) return false;
+    }
+    return box_exact(bmin, bmax, r, enter, exit_);
+}
+
+// rayTriangleIntersect (core.h:379-400) + the t > 1e-3 acceptance of accel.h:43, same operation order.
+// `ill` is set when the candidate is numerically ill-conditioned (see file header).
+TRB_HD bool tri_test(const F4& q0, const F4& q1, const F4& q2, const RayT& r, float* t, float* u, float* v, bool* ill) {
+    // pvec = cross(d, v0v2)
+    float px = r.dy * q2.z - q2.y * r.dz, py = r.dz * q2.x - q2.z * r.dx, pz = r.dx * q2.y - q2.x * r.dy;
+    float det = (q1.x * px + q1.y * py) + q1.z * pz;
+    if (fabsf(det) < 1e-8f) return false;
+    float invDet = fdiv(1.f, det);
+    float tx = r.ox - q0.x, ty = r.oy - q0.y, tz = r.oz - q0.z;
+    float uu = ((tx * px + ty * py) + tz * pz) * invDet;
+    if (uu < 0 || uu > 1) return false;
+    // qvec = cross(tvec, v0v1)
+    float qx = ty * q1.z - q1.y * tz, qy = tz * q1.x - q1.z * tx, qz = tx * q1.y - q1.x * ty;
+    float vv = ((r.dx * qx + r.dy * qy) + r.dz * qz) * invDet;
+    if (vv < 0 || uu + vv > 1) return false;
+    float tt = ((q2.x * qx + q2.y * qy) + q2.z * qz) * invDet;
+    // conditioning: |det| against |e1||e2||d| (grazing) and |n.tvec| against |tvec| (origin in the plane)
+    float e1 = (q1.x * q1.x + q1.y * q1.y) + q1.z * q1.z, e2 = (q2.x * q2.x + q2.y * q2.y) + q2.z * q2.z;
+    float dd = (r.dx * r.dx + r.dy * r.dy) + r.dz * r.dz;
+    if (det * det < 1e-6f * e1 * e2 * dd) *ill = true;
+    if (!(tt >= 0.001f)) return false;  // (double)t > 1e-3  <=>  t >= 0.001f for fp32 t
+    *t = tt; *u = uu; *v = vv;
+    return true;
+}
+
+// One traversal. ANY: occlusion query.  PRUNE=false visits what the reference visits (no distance test).
+// Returns true when an ill-conditioned candidate was met (caller re-runs with PRUNE=false).
+template <bool ANY, bool PRUNE>
+TRB_HD bool traverse(const BvhView& bvh, const RayT& r, const RayPre& pre, HitT* hit, bool* occluded,
+                     uint32_t* n_nodes, uint32_t* n_tris) {
+    int32_t stack[TRB_STACK];
+    int sp = 0;
+    int32_t cur = bvh.root_ref;
+    bool ill = false;
+    float best = r.max_t;  // bvh.h:263: intersection->t = ray.max_t
+    HitT h; h.t = r.max_t; h.u = 0.f; h.v = 0.f; h.pos = -1;
+    *occluded = false;
+    // bvh.h:287: the root is skipped when ray.min_t > ray.max_t
+    if (r.min_t > r.max_t) { *hit = h; return false; }
+    while (true) {
+        if (cur >= 0) {
+            const F4* n = bvh.nodes + 4 * size_t(cur);
+            F4 a = ld4(n), b = ld4(n + 1), c = ld4(n + 2), d = ld4(n + 3);
+            if (n_nodes) ++*n_nodes;
+            const float c0min[3] = {a.x, a.y, a.z}, c0max[3] = {a.w, b.x, b.y};
+            const float c1min[3] = {b.z, b.w, c.x}, c1max[3] = {c.y, c.z, c.w};
+            float e0, x0, e1, x1;
+            bool h0 = box_test(c0min, c0max, r, pre, &e0, &x0);
+            bool h1 = box_test(c1min, c1max, r, pre, &e1, &x1);
+            if (PRUNE) {
+                float lim = best + 1e-3f * (1.f + fabsf(best));
+                h0 = h0 && !(e0 > lim) && !(x0 < -1e-3f * (1.f + fabsf(x0)));
+                h1 = h1 && !(e1 > lim) && !(x1 < -1e-3f * (1.f + fabsf(x1)));
+            }
+            int32_t r0 = f2i(d.x), r1 = f2i(d.y);
+            if (h0 && h1) {
+                // reference order on equal footing: left first (bvh.h:317-336); nearer first when pruning
+                bool swap = PRUNE && (e1 < e0);
+                stack[sp++] = swap ? r0 : r1;
+                cur = swap ? r1 : r0;
+                continue;
+            }
+            if (h0) { cur = r0; continue; }
+            if (h1) { cur = r1; continue; }
+        } else {
+            uint32_t code = uint32_t(~cur);
+            uint32_t first = code >> 3, cnt = code & 7u;
+            for (uint32_t k = 0; k < cnt; ++k) {
+                const F4* tp = bvh.tris + 3 * size_t(first + k);
+                F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
+                if (n_tris) ++*n_tris;
+                float t, u, v;
+                if (tri_test(q0, q1, q2, r, &t, &u, &v, &ill)) {
+                    if (ANY) {
+                        // bvh.h:299-307: immediate return inside [min_t,max_t]; otherwise recorded when
+                        // t < max_t, which also makes the final `object != nullptr` true
+                        if ((t <= r.max_t && t >= r.min_t) || t < r.max_t) { *occluded = true; *hit = h; return false; }
+                    } else {
+                        int32_t pos = int32_t(first + k);
+                        // strict '<' in list order == (t, pos) lexicographic minimum for any visiting order
+                        if (t < h.t || (t == h.t && h.pos >= 0 && pos < h.pos)) { h.t = t; h.u = u; h.v = v; h.pos = pos; best = t; }
+                    }
+                }
+            }
+        }
+        if (sp == 0) break;
+        cur = stack[--sp];
+    }
+    *hit = h;
+    return ill;
+}
+
+// Full query with the exhaustive re-trace for ill-conditioned rays.
+template <bool ANY>
+TRB_HD void trace_ray(const BvhView& bvh, const RayT& r, HitT* hit, bool* occluded, uint32_t* n_nodes, uint32_t* n_tris) {
+    RayPre pre = ray_pre(r);
+    bool ill = traverse<ANY, true>(bvh, r, pre, hit, occluded, n_nodes, n_tris);
+    if (ill && !(ANY && *occluded)) {
+        traverse<ANY, false>(bvh, r, pre, hit, occluded, n_nodes, n_tris);
+    }
+}
+
+}  // namespace trbk

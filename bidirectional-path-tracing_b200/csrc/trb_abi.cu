@@ -1,0 +1,577 @@
+// trb_abi.cu -- device half of include/trb.h: context, scene upload, wave scheduling, parity entry points.
+// One context = one GPU.  All launches go to the context's stream; nothing here falls back to the CPU.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/trb.h"
+#include "host/tr_host.h"
+#include "kernels/bdpt_kernels.cuh"
+
+using namespace trbk;
+
+namespace {
+
+thread_local std::string g_create_err;
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        release();
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) n = count; else p = nullptr;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+    size_t bytes() const { return n * sizeof(T); }
+};
+
+enum LaunchKind { LK_CLOSEST = 0, LK_ANY = 1, LK_LOGIC = 2, LK_N = 3 };
+
+}  // namespace
+
+struct trb_context {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    cudaDeviceProp prop{};
+    // scene
+    bool has_scene = false;
+    trb::FlatScene flat;
+    DevBuf<trb::DevNode> d_nodes;
+    DevBuf<trb::DevTri> d_tris;
+    DevBuf<trb::DevShade> d_shade;
+    DevBuf<trb::DevMaterial> d_mats;
+    DevBuf<trb::DevEmitter> d_emitters;
+    DevBuf<trb::DevEmitterTri> d_etris;
+    DevBuf<float> d_cdf;
+    SceneDev sc{};
+    // wave buffers
+    DevBuf<RayT> cam_ray, ray, sray;
+    DevBuf<HitT> hit, hit0;
+    DevBuf<float4> st_t, st_v;
+    DevBuf<LightVertex> lv;
+    DevBuf<int32_t> nlv, q_a, q_b;
+    DevBuf<Pending> spend;
+    DevBuf<uint32_t> counters;           // per stage CTR_N counters
+    DevBuf<unsigned long long> d_stats;  // [0] closest rays, [1] any rays, [2] node visits, [3] tri tests
+    DevBuf<float> fb;                    // frame buffer W*H*3
+    // scratch for the parity entry points
+    DevBuf<RayT> io_rays;
+    DevBuf<HitT> io_hits;
+    DevBuf<uint8_t> io_occ;
+    // timing
+    std::vector<cudaEvent_t> events;
+    std::vector<int> event_kind;
+    size_t n_events = 0;
+    bool timing = false;
+    uint64_t launches = 0;
+
+    int fail(int code, const std::string& m) { err = m; return code; }
+    int cuda_fail(cudaError_t e, const char* what) {
+        err = std::string(what) + ": " + cudaGetErrorString(e);
+        return TRB_ERR_CUDA;
+    }
+    void mark(int kind) {
+        ++launches;
+        if (!timing) return;
+        if (n_events == events.size()) { cudaEvent_t ev; cudaEventCreate(&ev); events.push_back(ev); event_kind.push_back(0); }
+        event_kind[n_events] = kind;
+        cudaEventRecord(events[n_events++], stream);
+    }
+};
+
+#define TRB_CUDA(ctx, call)                                      \
+    do {                                                         \
+        cudaError_t e__ = (call);                                \
+        if (e__ != cudaSuccess) return (ctx)->cuda_fail(e__, #call); \
+    } while (0)
+
+namespace {
+
+inline int grid_for(size_t n, int sm_count) {
+    size_t blocks = (n + TRB_BLOCK - 1) / TRB_BLOCK;
+    size_t cap = size_t(sm_count) * 32;  // grid-stride kernels: a multiple of the SM count
+    return int(std::max<size_t>(1, std::min(blocks, cap)));
+}
+inline int grid_exact(size_t n) { return int(std::max<size_t>(1, (n + TRB_BLOCK - 1) / TRB_BLOCK)); }
+
+int ensure_wave(trb_context* c, size_t P, int K) {
+    size_t kk = size_t(std::max(K, 1));
+    size_t shadow_cap = P * (kk + 1);
+    TRB_CUDA(c, c->cam_ray.alloc(P)); TRB_CUDA(c, c->ray.alloc(P));
+    TRB_CUDA(c, c->hit.alloc(P)); TRB_CUDA(c, c->hit0.alloc(P));
+    TRB_CUDA(c, c->st_t.alloc(P)); TRB_CUDA(c, c->st_v.alloc(P));
+    TRB_CUDA(c, c->lv.alloc(P * kk)); TRB_CUDA(c, c->nlv.alloc(P));
+    TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P));
+    TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
+    TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
+    TRB_CUDA(c, c->d_stats.alloc(8));
+    return TRB_OK;
+}
+
+__global__ void k_fold_stats(const uint32_t* __restrict__ counters, int n_stage, int light_stages, int K, uint32_t P,
+                             unsigned long long* __restrict__ stats, uint32_t shadow_cap) {
+    // stage 0 = light_init (its QOUT feeds light depth 1), stages 1..K = light bounces, K+1 = eye_init, K+2.. = eye bounces
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    unsigned long long closest = P, any = 0;
+    for (int s = 0; s < n_stage; ++s) {
+        uint32_t qo = counters[s * CTR_N + CTR_QOUT], sh = min(counters[s * CTR_N + CTR_SHADOW], shadow_cap);
+        any += sh;
+        bool is_eye_init = (s == K + 1);
+        if (!is_eye_init) closest += qo;  // every queued slot is traced once more; eye depth 1 reuses the primary hit
+    }
+    stats[0] += closest; stats[1] += any;
+}
+
+}  // namespace
+
+extern "C" {
+
+int trb_create(int device, trb_context** out) {
+    if (!out) return TRB_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0 || device < 0 || device >= n) {
+        g_create_err = std::string("no usable CUDA device (the BDPT path has no CPU fallback): ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device index out of range");
+        // surface through the host error channel too
+        return TRB_ERR_NO_DEVICE;
+    }
+    auto* c = new trb_context();
+    c->device = device;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&c->prop, device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        g_create_err = "cudaSetDevice / stream creation failed";
+        delete c;
+        return TRB_ERR_NO_DEVICE;
+    }
+    if (c->prop.major < 10) {
+        g_create_err = "device is not sm_100 class (library is built for sm_100a only)";
+        cudaStreamDestroy(c->stream);
+        delete c;
+        return TRB_ERR_NO_DEVICE;
+    }
+    *out = c;
+    return TRB_OK;
+}
+
+void trb_destroy(trb_context* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
+    c->d_etris.release(); c->d_cdf.release();
+    c->cam_ray.release(); c->ray.release(); c->sray.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
+    c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->spend.release();
+    c->counters.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
+    for (auto ev : c->events) cudaEventDestroy(ev);
+    cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+const char* trb_last_error(const trb_context* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
+
+const char* trb_build_info(void) {
+#ifdef TRB_COUNTERS
+    return "trb sm_100a fmad=off exact_transcendentals=" "1" " counters=on";
+#else
+    return "trb sm_100a fmad=off exact_transcendentals=" "1" " counters=off";
+#endif
+}
+
+int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
+    if (!c || !s) return TRB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    std::string err;
+    trb::FlatScene& f = c->flat;
+    if (!trb::flatten_scene(*s, f, err)) return c->fail(err.find("illum 5") != std::string::npos ? TRB_ERR_UNSUPPORTED : TRB_ERR_INVALID, err);
+    if (f.emitters.empty()) return c->fail(TRB_ERR_INVALID, "scene has no emitter (the reference divides by emitters.size())");
+    if (f.max_depth + 2 > TRB_STACK) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
+    TRB_CUDA(c, c->d_nodes.alloc(f.nodes.size())); TRB_CUDA(c, c->d_tris.alloc(f.tris.size()));
+    TRB_CUDA(c, c->d_shade.alloc(f.shade.size())); TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
+    TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
+    TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size()));
+    auto up = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c->stream) : cudaSuccess; };
+    TRB_CUDA(c, up(c->d_nodes.p, f.nodes.data(), f.nodes.size() * sizeof(trb::DevNode)));
+    TRB_CUDA(c, up(c->d_tris.p, f.tris.data(), f.tris.size() * sizeof(trb::DevTri)));
+    TRB_CUDA(c, up(c->d_shade.p, f.shade.data(), f.shade.size() * sizeof(trb::DevShade)));
+    TRB_CUDA(c, up(c->d_mats.p, f.materials.data(), f.materials.size() * sizeof(trb::DevMaterial)));
+    TRB_CUDA(c, up(c->d_emitters.p, f.emitters.data(), f.emitters.size() * sizeof(trb::DevEmitter)));
+    TRB_CUDA(c, up(c->d_etris.p, f.emitter_tris.data(), f.emitter_tris.size() * sizeof(trb::DevEmitterTri)));
+    TRB_CUDA(c, up(c->d_cdf.p, f.emitter_cdf.data(), f.emitter_cdf.size() * sizeof(float)));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
+    c->sc.tris = reinterpret_cast<const F4*>(c->d_tris.p);
+    c->sc.shade = c->d_shade.p; c->sc.mats = c->d_mats.p; c->sc.emitters = c->d_emitters.p; c->sc.etris = c->d_etris.p;
+    c->sc.cdf = c->d_cdf.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
+    c->has_scene = true;
+    return TRB_OK;
+}
+
+size_t trb_scene_device_bytes(const trb_context* c) { return (c && c->has_scene) ? c->flat.bytes() : 0; }
+
+}  // extern "C"
+
+// ---- wave runner -------------------------------------------------------------------------------------------
+namespace {
+
+struct WaveRun {
+    const trb_render_desc* desc;
+    float* d_accum;            // frame buffer or parity accumulation buffer
+    int32_t* d_splat_pix;      // parity only
+    const RayT* d_inject_rays; // parity only
+    const float* d_inject_rng;
+    int inject_stride;
+    bool parity;
+};
+
+int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_t wave_base, int P, int spp_begin, int spp_count) {
+    const trb_render_desc& d = *w.desc;
+    const int K = std::max(d.rr_depth - 1, 0);
+    const int kk = std::max(K, 1);
+    const int sm = c->prop.multiProcessorCount;
+    WaveParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.sc = c->sc; p.cam = cam;
+    p.P = P; p.K = kk; p.rr_depth = d.rr_depth; p.spp = d.spp; p.spp_begin = spp_begin; p.spp_count = spp_count;
+    p.wave_base = wave_base; p.seed = d.seed; p.flags = d.flags;
+    p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
+    p.accum = w.d_accum; p.splat_pix = w.d_splat_pix;
+    p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.sray = c->sray.p; p.spend = c->spend.p;
+    p.shadow_cap = uint32_t(std::min<size_t>(c->sray.n, 0xffffffffu));
+    const int n_stage = 2 * kk + 4;
+    TRB_CUDA(c, cudaMemsetAsync(c->counters.p, 0, size_t(n_stage) * CTR_N * sizeof(uint32_t), c->stream));
+    unsigned long long* visit = nullptr;
+#ifdef TRB_COUNTERS
+    visit = c->d_stats.p + 2;
+#endif
+    int32_t* qa = c->q_a.p; int32_t* qb = c->q_b.p;
+    auto stage_ctr = [&](int s) { return c->counters.p + size_t(s) * CTR_N; };
+    const int gP = grid_exact(size_t(P));
+    const int gS = grid_for(size_t(P), sm);
+
+    k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, visit); c->mark(LK_CLOSEST);
+    // light subpath
+    int stage = 0;
+    p.counters = stage_ctr(stage); p.q_out = qa;
+    k_light_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    for (int depth = 1; depth <= K; ++depth) {
+        const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
+        p.q_in = (stage % 2 == 0) ? qa : qb;
+        p.q_out = (stage % 2 == 0) ? qb : qa;
+        ++stage;
+        p.counters = stage_ctr(stage);
+        k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST);
+        k_light_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
+        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit);
+        c->mark(LK_ANY);
+    }
+    // eye subpath
+    stage = kk + 1;
+    p.counters = stage_ctr(stage); p.q_out = qa;
+    k_eye_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    for (int depth = 1; depth <= K; ++depth) {
+        const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
+        const bool even = ((stage - (kk + 1)) % 2 == 0);
+        p.q_in = even ? qa : qb;
+        p.q_out = even ? qb : qa;
+        ++stage;
+        p.counters = stage_ctr(stage);
+        if (depth > 1) { k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST); }
+        k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
+        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit);
+        c->mark(LK_ANY);
+    }
+    k_fold_stats<<<1, 32, 0, c->stream>>>(c->counters.p, n_stage, kk, kk, uint32_t(P), c->d_stats.p, p.shadow_cap); c->mark(LK_LOGIC);
+    TRB_CUDA(c, cudaGetLastError());
+    return TRB_OK;
+}
+
+int check_desc(trb_context* c, const trb_render_desc* d) {
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    if (!d || d->width <= 0 || d->height <= 0 || d->spp <= 0 || d->rr_depth < 1) return c->fail(TRB_ERR_INVALID, "bad render description");
+    if (d->rr_depth > 64) return c->fail(TRB_ERR_INVALID, "rr_depth > 64 is not supported");
+    return TRB_OK;
+}
+
+void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
+    if (!st) return;
+    std::memset(st, 0, sizeof(*st));
+    unsigned long long h[8] = {0};
+    cudaMemcpyAsync(h, c->d_stats.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream);
+    cudaStreamSynchronize(c->stream);
+    st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3];
+    st->launches = c->launches;
+    double ms[LK_N] = {0, 0, 0};
+    for (size_t i = 1; i < c->n_events; ++i) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, c->events[i - 1], c->events[i]);
+        ms[c->event_kind[i]] += t;
+    }
+    if (c->n_events >= 2) { float t = 0.f; cudaEventElapsedTime(&t, c->events[0], c->events[c->n_events - 1]); st->ms_total = t; }
+    st->ms_trace_closest = ms[LK_CLOSEST]; st->ms_trace_any = ms[LK_ANY]; st->ms_logic = ms[LK_LOGIC];
+}
+
+int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float* d_rgb, trb_stats* stats) {
+    int rc = check_desc(c, d);
+    if (rc) return rc;
+    cudaSetDevice(c->device);
+    const int64_t npix = int64_t(d->width) * d->height;
+    const int spp_begin = d->spp_begin;
+    const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
+    if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
+    const int spp_count = spp_end - spp_begin;
+    const int K = std::max(d->rr_depth - 1, 1);
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 20);
+    const int64_t total = npix * spp_count;
+    P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
+    rc = ensure_wave(c, size_t(P), K);
+    if (rc) return rc;
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = stats != nullptr; c->n_events = 0; c->launches = 0;
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    c->mark(LK_LOGIC);
+    if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
+    WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
+    for (int64_t base = 0; base < total; base += P) {
+        int n = int(std::min<int64_t>(P, total - base));
+        rc = run_wave(c, w, cam, base, n, spp_begin, spp_count);
+        if (rc) return rc;
+    }
+    c->mark(LK_LOGIC);
+    if (stats) collect_stats(c, stats, uint64_t(total));
+    return TRB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int trb_render_bdpt_device(trb_context* c, const trb_render_desc* d, int accumulate, float* d_rgb, trb_stats* stats) {
+    if (!c || !d_rgb) return TRB_ERR_INVALID;
+    int rc = render_impl(c, d, accumulate, d_rgb, stats);
+    if (rc) return rc;
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_render_bdpt(trb_context* c, const trb_render_desc* d, int accumulate, float* rgb_out, trb_stats* stats) {
+    if (!c || !d) return TRB_ERR_INVALID;
+    if (d->width <= 0 || d->height <= 0) return c->fail(TRB_ERR_INVALID, "bad film size");
+    cudaSetDevice(c->device);
+    size_t nf = size_t(d->width) * d->height * 3;
+    bool fresh = c->fb.n < nf;
+    TRB_CUDA(c, c->fb.alloc(nf));
+    if (fresh && accumulate) TRB_CUDA(c, cudaMemsetAsync(c->fb.p, 0, nf * sizeof(float), c->stream));
+    int rc = render_impl(c, d, accumulate, c->fb.p, stats);
+    if (rc) return rc;
+    if (rgb_out) TRB_CUDA(c, cudaMemcpyAsync(rgb_out, c->fb.p, nf * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+}  // extern "C"
+
+// ---- parity entry points -------------------------------------------------------------------------------------
+namespace {
+
+// hit record -> trb_hit with the range semantics of AcceleratorBVH::intersect (accel.h:131-133,169-170)
+__global__ void k_export_hits(SceneDev sc, const RayT* __restrict__ rays, const HitT* __restrict__ hits, size_t n, trb_hit* __restrict__ out) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    HitT h = hits[i];
+    RayT r = rays[i];
+    trb_hit o;
+    o.t = h.pos >= 0 ? h.t : FLT_MAX; o.u = 0.f; o.v = 0.f; o.hit = 0; o.shape = -1; o.prim = -1; o.tri = -1; o._pad = 0;
+    if (hit_valid(h, r)) {
+        const trb::DevShade& s = sc.shade[h.pos];
+        o.hit = 1; o.u = h.u; o.v = h.v; o.shape = s.shape; o.prim = s.prim; o.tri = s.tri;
+    }
+    out[i] = o;
+}
+
+__global__ void k_bsdf_batch(SceneDev sc, const trb_bsdf_query* __restrict__ q, size_t n, int n_mats, trb_bsdf_out* __restrict__ out) {
+    size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    trb_bsdf_query x = q[i];
+    trb_bsdf_out o;
+    memset(&o, 0, sizeof(o));
+    if (x.mat >= 0 && x.mat < n_mats) {
+        Mat m = load_mat(sc.mats, x.mat);
+        V3 wo = mk(x.wo[0], x.wo[1], x.wo[2]), wi = mk(x.wi[0], x.wi[1], x.wi[2]);
+        V3 e = bsdf_eval(m, wo, wi);
+        o.eval[0] = e.x; o.eval[1] = e.y; o.eval[2] = e.z;
+        o.pdf = bsdf_pdf(m, wo, wi);
+        V3 swi; float spdf;
+        V3 sv = bsdf_sample(m, wo, x.u[0], x.u[1], &swi, &spdf);
+        o.sample_val[0] = sv.x; o.sample_val[1] = sv.y; o.sample_val[2] = sv.z; o.sample_pdf = spdf;
+        o.sample_wi[0] = swi.x; o.sample_wi[1] = swi.y; o.sample_wi[2] = swi.z; o.type = m.type;
+    }
+    out[i] = o;
+}
+
+__global__ void k_read_draws(const float4* __restrict__ st_v, int n, int32_t* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = int32_t(__float_as_uint(st_v[i].z));
+}
+
+int trace_device(trb_context* c, bool any, const RayT* d_rays, size_t n, HitT* d_hits, uint8_t* d_occ, float* ms_out) {
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    if (n > 0xffffffffull) return c->fail(TRB_ERR_INVALID, "too many rays for one call");
+    cudaSetDevice(c->device);
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (ms_out) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, c->stream); }
+    const int g = grid_for(n, c->prop.multiProcessorCount);
+    unsigned long long* visit = nullptr;
+#ifdef TRB_COUNTERS
+    TRB_CUDA(c, c->d_stats.alloc(8));
+    visit = c->d_stats.p + 2;
+#endif
+    if (n) {
+        if (any) k_trace_any<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, visit);
+        else k_trace_closest<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, nullptr, uint32_t(n), d_hits, visit);
+    }
+    ++c->launches;
+    if (ms_out) { cudaEventRecord(e1, c->stream); }
+    TRB_CUDA(c, cudaGetLastError());
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (ms_out) { cudaEventElapsedTime(ms_out, e0, e1); cudaEventDestroy(e0); cudaEventDestroy(e1); }
+    return TRB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int trb_trace_closest(trb_context* c, const trb_ray* rays, size_t n, trb_hit* out) {
+    if (!c || (n && (!rays || !out))) return TRB_ERR_INVALID;
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    cudaSetDevice(c->device);
+    static_assert(sizeof(trb_ray) == sizeof(RayT) && sizeof(trb_hit) == 32, "ABI layout");
+    TRB_CUDA(c, c->io_rays.alloc(n)); TRB_CUDA(c, c->io_hits.alloc(n));
+    DevBuf<trb_hit> d_out;
+    TRB_CUDA(c, d_out.alloc(n));
+    TRB_CUDA(c, cudaMemcpyAsync(c->io_rays.p, rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
+    int rc = trace_device(c, false, c->io_rays.p, n, c->io_hits.p, nullptr, nullptr);
+    if (rc == TRB_OK && n) {
+        k_export_hits<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->sc, c->io_rays.p, c->io_hits.p, n, d_out.p);
+        cudaError_t e = cudaMemcpyAsync(out, d_out.p, n * sizeof(trb_hit), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = c->cuda_fail(e, "trb_trace_closest download");
+    }
+    d_out.release();
+    return rc;
+}
+
+int trb_trace_any(trb_context* c, const trb_ray* rays, size_t n, uint8_t* out) {
+    if (!c || (n && (!rays || !out))) return TRB_ERR_INVALID;
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    cudaSetDevice(c->device);
+    TRB_CUDA(c, c->io_rays.alloc(n)); TRB_CUDA(c, c->io_occ.alloc(n));
+    TRB_CUDA(c, cudaMemcpyAsync(c->io_rays.p, rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
+    int rc = trace_device(c, true, c->io_rays.p, n, nullptr, c->io_occ.p, nullptr);
+    if (rc) return rc;
+    TRB_CUDA(c, cudaMemcpyAsync(out, c->io_occ.p, n, cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_trace_closest_device(trb_context* c, const trb_ray* d_rays, size_t n, trb_hit* d_out, float* ms_out) {
+    if (!c || !d_rays || !d_out) return TRB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    TRB_CUDA(c, c->io_hits.alloc(n));
+    int rc = trace_device(c, false, reinterpret_cast<const RayT*>(d_rays), n, c->io_hits.p, nullptr, ms_out);
+    if (rc) return rc;
+    if (n) k_export_hits<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->sc, reinterpret_cast<const RayT*>(d_rays), c->io_hits.p, n, d_out);
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_trace_any_device(trb_context* c, const trb_ray* d_rays, size_t n, uint8_t* d_out, float* ms_out) {
+    if (!c || !d_rays || !d_out) return TRB_ERR_INVALID;
+    return trace_device(c, true, reinterpret_cast<const RayT*>(d_rays), n, nullptr, d_out, ms_out);
+}
+
+int trb_bsdf_batch(trb_context* c, const trb_bsdf_query* q, size_t n, trb_bsdf_out* out) {
+    if (!c || (n && (!q || !out))) return TRB_ERR_INVALID;
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    cudaSetDevice(c->device);
+    DevBuf<trb_bsdf_query> dq; DevBuf<trb_bsdf_out> dout;
+    TRB_CUDA(c, dq.alloc(n)); TRB_CUDA(c, dout.alloc(n));
+    cudaError_t e = cudaMemcpyAsync(dq.p, q, n * sizeof(trb_bsdf_query), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess && n) {
+        k_bsdf_batch<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->sc, dq.p, n, int(c->flat.materials.size()), dout.p);
+        ++c->launches;
+        e = cudaMemcpyAsync(out, dout.p, n * sizeof(trb_bsdf_out), cudaMemcpyDeviceToHost, c->stream);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    dq.release(); dout.release();
+    if (e != cudaSuccess) return c->cuda_fail(e, "trb_bsdf_batch");
+    return TRB_OK;
+}
+
+int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_rays, const float* rng, size_t n, size_t stride,
+                   float* li_out, int32_t* splat_pix, float* splat_rgb, int32_t* draws_out) {
+    if (!c || !cam_rays || !rng || !li_out || !splat_pix || !splat_rgb) return TRB_ERR_INVALID;
+    int rc = check_desc(c, d);
+    if (rc) return rc;
+    if (n == 0) return TRB_OK;
+    if (n > (size_t(1) << 24)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: at most 2^24 paths per call");
+    cudaSetDevice(c->device);
+    const int K = std::max(d->rr_depth - 1, 1);
+    // worst case draws per path: 2 + 6 + 3K (light) + 7K (eye) + 2
+    if (stride < size_t(10 + 10 * K)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: rng stride must be >= 10 + 10*(rr_depth-1)");
+    rc = ensure_wave(c, n, K);
+    if (rc) return rc;
+    DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_pix, d_draws;
+    TRB_CUDA(c, d_rays.alloc(n)); TRB_CUDA(c, d_rng.alloc(n * stride)); TRB_CUDA(c, d_acc.alloc(n * size_t(K + 1) * 3));
+    TRB_CUDA(c, d_pix.alloc(n * size_t(K))); TRB_CUDA(c, d_draws.alloc(n));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rays.p, cam_rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(d_pix.p, 0xff, d_pix.bytes(), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = false; c->n_events = 0; c->launches = 0;
+    WaveRun w{d, d_acc.p, d_pix.p, d_rays.p, d_rng.p, int(stride), true};
+    rc = run_wave(c, w, cam, 0, int(n), 0, d->spp);
+    if (rc == TRB_OK) {
+        k_read_draws<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->st_v.p, int(n), d_draws.p);
+        std::vector<float> acc(n * size_t(K + 1) * 3);
+        std::vector<int32_t> pix(n * size_t(K)), draws(n);
+        cudaError_t e = cudaMemcpyAsync(acc.data(), d_acc.p, d_acc.bytes(), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(pix.data(), d_pix.p, d_pix.bytes(), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(draws.data(), d_draws.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = c->cuda_fail(e, "trb_bdpt_paths download");
+        else {
+            for (size_t i = 0; i < n; ++i) {
+                const float* a = acc.data() + i * size_t(K + 1) * 3;
+                li_out[3 * i] = a[0]; li_out[3 * i + 1] = a[1]; li_out[3 * i + 2] = a[2];
+                for (int k = 0; k < K; ++k) {
+                    const float* s = a + 3 * (k + 1);
+                    bool any = s[0] != 0.f || s[1] != 0.f || s[2] != 0.f;  // an occluded splat leaves no trace in the reference either
+                    splat_pix[i * K + k] = any ? pix[i * K + k] : -1;
+                    for (int ch = 0; ch < 3; ++ch) splat_rgb[(i * K + k) * 3 + ch] = s[ch];
+                }
+                if (draws_out) draws_out[i] = draws[i];
+            }
+        }
+    }
+    d_rays.release(); d_rng.release(); d_acc.release(); d_pix.release(); d_draws.release();
+    return rc;
+}
+
+}  // extern "C"
