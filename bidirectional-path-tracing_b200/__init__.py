@@ -54,7 +54,7 @@ class Stats(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_trace_closest", C.c_double), ("ms_trace_any", C.c_double),
                 ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
                 ("rays_any", C.c_uint64), ("launches", C.c_uint64), ("node_visits", C.c_uint64),
-                ("tri_tests", C.c_uint64)]
+                ("tri_tests", C.c_uint64), ("node_visits_any", C.c_uint64), ("tri_tests_any", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -270,6 +270,10 @@ class Context:
         d = scene.desc()
         self._chk(self._L.trb_scene_upload(self._h, C.byref(d)))
         self.scene = scene
+
+    def refresh_scene(self) -> None:
+        """host->device copy of the flattened scene from pinned memory (trb_scene_refresh)"""
+        self._chk(self._L.trb_scene_refresh(self._h))
 
     def scene_bytes(self) -> int:
         return int(self._L.trb_scene_device_bytes(self._h))

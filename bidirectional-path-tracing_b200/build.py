@@ -21,6 +21,7 @@ CSRC = PKG / "csrc"
 ROOT = PKG.parent
 OBJ = PKG / "build"
 LIB = PKG / "libtrb.so"
+LIB_COUNTERS = PKG / "libtrb_counters.so"  # same sources with -DTRB_COUNTERS (node / triangle visit counts)
 
 HOST_SRCS = ["host/obj_loader.cpp", "host/scene_build.cpp", "host/camera.cpp", "host/toml_exr.cpp", "host/host_abi.cpp"]
 CUDA_SRCS = ["trb_abi.cu"]
@@ -70,11 +71,13 @@ def _digest(paths: list[Path], extra: str) -> str:
 def build(force: bool = False, counters: bool = False, verbose: bool = False) -> Path:
     """Compile everything that is out of date; returns the path of libtrb.so."""
     OBJ.mkdir(exist_ok=True)
+    lib_out = LIB_COUNTERS if counters else LIB
+    sfx = "_cnt" if counters else ""
     deps = [p for p in CSRC.rglob("*") if p.suffix in (".cu", ".cuh", ".cpp", ".h")] + [ROOT / "include" / "trb.h"]
     tag = _digest(deps, "counters" if counters else "plain")
-    stamp = OBJ / "stamp.txt"
-    if not force and LIB.exists() and stamp.exists() and stamp.read_text() == tag:
-        return LIB
+    stamp = OBJ / f"stamp{sfx}.txt"
+    if not force and lib_out.exists() and stamp.exists() and stamp.read_text() == tag:
+        return lib_out
     objs = []
     for src in HOST_SRCS:
         o = OBJ / (Path(src).stem + ".o")
@@ -84,23 +87,23 @@ def build(force: bool = False, counters: bool = False, verbose: bool = False) ->
     for src in CUDA_SRCS:
         if not (CSRC / src).exists():
             continue
-        o = OBJ / (Path(src).stem + ".o")
+        o = OBJ / (Path(src).stem + sfx + ".o")
         flags = list(NVCC_FLAGS) + (["-DTRB_COUNTERS=1"] if counters else [])
-        _run([nvcc, *flags, "-I", str(ROOT / "include"), "-c", str(CSRC / src), "-o", str(o)], log=OBJ / (Path(src).stem + ".ptxas.log"))
+        _run([nvcc, *flags, "-I", str(ROOT / "include"), "-c", str(CSRC / src), "-o", str(o)], log=OBJ / (Path(src).stem + sfx + ".ptxas.log"))
         objs.append(str(o))
     have_cuda = any((CSRC / s).exists() for s in CUDA_SRCS)
-    link = ["g++", "-shared", *objs, "-o", str(LIB), *_stdcxx_link_args(), "-lm", "-lpthread"]
+    link = ["g++", "-shared", *objs, "-o", str(lib_out), *_stdcxx_link_args(), "-lm", "-lpthread"]
     if have_cuda:
         cuda_lib = Path(nvcc).resolve().parent.parent / "lib64"
         link += ["-L", str(cuda_lib), "-lcudart_static", "-ldl", "-lrt"]
     _run(link)
-    if (CSRC / CLI_SRC).exists():
+    if (CSRC / CLI_SRC).exists() and not counters:
         _run(["g++", *CXX_FLAGS, "-I", str(ROOT / "include"), str(CSRC / CLI_SRC), "-o", str(PKG / "tinyrender_b200"),
               "-L", str(PKG), "-l:libtrb.so", "-Wl,-rpath,$ORIGIN", *_stdcxx_link_args(), "-lm"])
     stamp.write_text(tag)
     if verbose:
-        print(f"built {LIB}")
-    return LIB
+        print(f"built {lib_out}")
+    return lib_out
 
 
 if __name__ == "__main__":

@@ -53,6 +53,8 @@ struct trb_context {
     DevBuf<trb::DevEmitterTri> d_etris;
     DevBuf<float> d_cdf;
     SceneDev sc{};
+    uint8_t* pinned = nullptr;  // flattened scene staged in pinned host memory (trb_scene_refresh)
+    size_t pinned_bytes = 0;
     // wave buffers
     DevBuf<RayT> cam_ray, ray, sray;
     DevBuf<HitT> hit, hit0;
@@ -172,6 +174,7 @@ void trb_destroy(trb_context* c) {
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->spend.release();
     c->counters.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
+    if (c->pinned) cudaFreeHost(c->pinned);
     for (auto ev : c->events) cudaEventDestroy(ev);
     cudaStreamDestroy(c->stream);
     delete c;
@@ -199,20 +202,41 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     TRB_CUDA(c, c->d_shade.alloc(f.shade.size())); TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
     TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
     TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size()));
-    auto up = [&](void* d, const void* h, size_t bytes) { return bytes ? cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c->stream) : cudaSuccess; };
-    TRB_CUDA(c, up(c->d_nodes.p, f.nodes.data(), f.nodes.size() * sizeof(trb::DevNode)));
-    TRB_CUDA(c, up(c->d_tris.p, f.tris.data(), f.tris.size() * sizeof(trb::DevTri)));
-    TRB_CUDA(c, up(c->d_shade.p, f.shade.data(), f.shade.size() * sizeof(trb::DevShade)));
-    TRB_CUDA(c, up(c->d_mats.p, f.materials.data(), f.materials.size() * sizeof(trb::DevMaterial)));
-    TRB_CUDA(c, up(c->d_emitters.p, f.emitters.data(), f.emitters.size() * sizeof(trb::DevEmitter)));
-    TRB_CUDA(c, up(c->d_etris.p, f.emitter_tris.data(), f.emitter_tris.size() * sizeof(trb::DevEmitterTri)));
-    TRB_CUDA(c, up(c->d_cdf.p, f.emitter_cdf.data(), f.emitter_cdf.size() * sizeof(float)));
-    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    // stage everything in one pinned blob so that (re-)uploads are plain async copies from pinned memory
+    const size_t sizes[7] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+                             f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
+                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float)};
+    const void* srcs[7] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data()};
+    size_t total = 0;
+    for (size_t b : sizes) total += (b + 255) & ~size_t(255);
+    if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
+    TRB_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&c->pinned), std::max<size_t>(total, 256)));
+    c->pinned_bytes = total;
+    size_t off = 0;
+    for (int k = 0; k < 7; ++k) { if (sizes[k]) std::memcpy(c->pinned + off, srcs[k], sizes[k]); off += (sizes[k] + 255) & ~size_t(255); }
     c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
     c->sc.tris = reinterpret_cast<const F4*>(c->d_tris.p);
     c->sc.shade = c->d_shade.p; c->sc.mats = c->d_mats.p; c->sc.emitters = c->d_emitters.p; c->sc.etris = c->d_etris.p;
     c->sc.cdf = c->d_cdf.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
     c->has_scene = true;
+    return trb_scene_refresh(c);
+}
+
+int trb_scene_refresh(trb_context* c) {
+    if (!c) return TRB_ERR_INVALID;
+    if (!c->has_scene || !c->pinned) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    cudaSetDevice(c->device);
+    void* dsts[7] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p};
+    const trb::FlatScene& f = c->flat;
+    const size_t sizes[7] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+                             f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
+                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float)};
+    size_t off = 0;
+    for (int k = 0; k < 7; ++k) {
+        if (sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], c->pinned + off, sizes[k], cudaMemcpyHostToDevice, c->stream));
+        off += (sizes[k] + 255) & ~size_t(255);
+    }
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
     return TRB_OK;
 }
 
@@ -273,7 +297,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.counters = stage_ctr(stage);
         k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST);
         k_light_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
-        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit);
+        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit ? visit + 2 : nullptr);
         c->mark(LK_ANY);
     }
     // eye subpath
@@ -289,7 +313,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.counters = stage_ctr(stage);
         if (depth > 1) { k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST); }
         k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
-        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit);
+        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit ? visit + 2 : nullptr);
         c->mark(LK_ANY);
     }
     k_fold_stats<<<1, 32, 0, c->stream>>>(c->counters.p, n_stage, kk, kk, uint32_t(P), c->d_stats.p, p.shadow_cap); c->mark(LK_LOGIC);
@@ -310,7 +334,7 @@ void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
     unsigned long long h[8] = {0};
     cudaMemcpyAsync(h, c->d_stats.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream);
     cudaStreamSynchronize(c->stream);
-    st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3];
+    st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5];
     st->launches = c->launches;
     double ms[LK_N] = {0, 0, 0};
     for (size_t i = 1; i < c->n_events; ++i) {
@@ -439,7 +463,7 @@ int trace_device(trb_context* c, bool any, const RayT* d_rays, size_t n, HitT* d
     visit = c->d_stats.p + 2;
 #endif
     if (n) {
-        if (any) k_trace_any<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, visit);
+        if (any) k_trace_any<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, visit ? visit + 2 : nullptr);
         else k_trace_closest<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, nullptr, uint32_t(n), d_hits, visit);
     }
     ++c->launches;

@@ -111,8 +111,10 @@ typedef struct trb_stats {
     uint64_t rays_closest;    /* BVH closest-hit queries traced                         */
     uint64_t rays_any;        /* occlusion queries traced                               */
     uint64_t launches;        /* kernels launched by this call                          */
-    uint64_t node_visits;     /* only when built with TRB_COUNTERS (else 0)             */
+    uint64_t node_visits;     /* closest-hit rays; only when built with TRB_COUNTERS (else 0) */
     uint64_t tri_tests;
+    uint64_t node_visits_any; /* occlusion rays; TRB_COUNTERS builds only                */
+    uint64_t tri_tests_any;
 } trb_stats;
 
 /* BSDF query in the local shading frame (SurfaceInteraction::{wo,wi}, core.h:173-180) */
@@ -165,6 +167,9 @@ const char* trb_last_error(const trb_context*);
 /* Scene::load's tail + AcceleratorBVH::build (renderer.cpp:259-312, accel.h:115-123): derives BSDF
  * parameters, emitters and the BVH on the host and uploads the flattened scene. */
 int trb_scene_upload(trb_context*, const trb_scene_desc*);
+/* Copies the already flattened scene (kept in pinned host memory by trb_scene_upload) to the device again:
+ * the per-frame host->device transfer of an end-to-end render without redoing the host-side BVH build. */
+int trb_scene_refresh(trb_context*);
 /* bytes of the flattened device scene (nodes + triangles + shading records + tables) */
 size_t trb_scene_device_bytes(const trb_context*);
 
