@@ -161,7 +161,10 @@ TRB_HD bool traverse(const BvhView& bvh, const RayT& r, const RayPre& pre, HitT*
     *occluded = false;
     // bvh.h:287: the root is skipped when ray.min_t > ray.max_t
     if (r.min_t > r.max_t) { *hit = h; return false; }
-    while (true) {
+    // One structured loop: every iteration is "inner node step" or "leaf step", both end by setting `cur`
+    // (-1 = done), and the branches re-join at the bottom of the iteration.  No `continue`/`break` out of
+    // divergent code: with independent thread scheduling those leave lanes permanently split.
+    while (cur != -1) {
         if (cur >= 0) {
             const F4* n = bvh.nodes + 4 * size_t(cur);
             F4 a = ld4(n), b = ld4(n + 1), c = ld4(n + 2), d = ld4(n + 3);
@@ -177,18 +180,18 @@ TRB_HD bool traverse(const BvhView& bvh, const RayT& r, const RayPre& pre, HitT*
                 h1 = h1 && !(e1 > lim) && !(x1 < -1e-3f * (1.f + fabsf(x1)));
             }
             int32_t r0 = f2i(d.x), r1 = f2i(d.y);
-            if (h0 && h1) {
-                // reference order on equal footing: left first (bvh.h:317-336); nearer first when pruning
-                bool swap = PRUNE && (e1 < e0);
-                stack[sp++] = swap ? r0 : r1;
-                cur = swap ? r1 : r0;
-                continue;
-            }
-            if (h0) { cur = r0; continue; }
-            if (h1) { cur = r1; continue; }
+            // reference order on equal footing: left first (bvh.h:317-336); nearer first when pruning
+            bool swap = PRUNE && h0 && h1 && (e1 < e0);
+            int32_t first = swap ? r1 : r0, second = swap ? r0 : r1;
+            bool hf = swap ? h1 : h0, hs = swap ? h0 : h1;
+            if (hf && hs) { stack[sp++] = second; cur = first; }
+            else if (hf) cur = first;
+            else if (hs) cur = second;
+            else cur = sp ? stack[--sp] : -1;
         } else {
             uint32_t code = uint32_t(~cur);
             uint32_t first = code >> 3, cnt = code & 7u;
+            bool done = false;
             for (uint32_t k = 0; k < cnt; ++k) {
                 const F4* tp = bvh.tris + 3 * size_t(first + k);
                 F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
@@ -198,7 +201,7 @@ TRB_HD bool traverse(const BvhView& bvh, const RayT& r, const RayPre& pre, HitT*
                     if (ANY) {
                         // bvh.h:299-307: immediate return inside [min_t,max_t]; otherwise recorded when
                         // t < max_t, which also makes the final `object != nullptr` true
-                        if ((t <= r.max_t && t >= r.min_t) || t < r.max_t) { *occluded = true; *hit = h; return false; }
+                        if ((t <= r.max_t && t >= r.min_t) || t < r.max_t) { *occluded = true; done = true; }
                     } else {
                         int32_t pos = int32_t(first + k);
                         // strict '<' in list order == (t, pos) lexicographic minimum for any visiting order
@@ -206,10 +209,10 @@ TRB_HD bool traverse(const BvhView& bvh, const RayT& r, const RayPre& pre, HitT*
                     }
                 }
             }
+            cur = (done || sp == 0) ? -1 : stack[--sp];
         }
-        if (sp == 0) break;
-        cur = stack[--sp];
     }
+    if (ANY && *occluded) ill = false;
     *hit = h;
     return ill;
 }

@@ -19,11 +19,11 @@ extern "C" int hc_trace(const trb_scene_desc* s, const float* rays8, long n, int
         trbk::RayT r; memcpy(&r, rays8 + 8 * i, 32);
         trbk::HitT h; bool oc = false; uint32_t a = 0, b = 0;
         trbk::RayPre pre = trbk::ray_pre(r);
-        if (force_exhaustive) {
+        if (force_exhaustive == 1) {
             if (any) trbk::traverse<true, false>(bv, r, pre, &h, &oc, &a, &b); else trbk::traverse<false, false>(bv, r, pre, &h, &oc, &a, &b);
         } else {
             bool ill = any ? trbk::traverse<true, true>(bv, r, pre, &h, &oc, &a, &b) : trbk::traverse<false, true>(bv, r, pre, &h, &oc, &a, &b);
-            if (ill && !(any && oc)) {
+            if (ill && !(any && oc) && force_exhaustive != 2) {
                 ++nill;
                 if (any) trbk::traverse<true, false>(bv, r, pre, &h, &oc, &a, &b); else trbk::traverse<false, false>(bv, r, pre, &h, &oc, &a, &b);
             }
