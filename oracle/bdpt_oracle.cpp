@@ -267,3 +267,726 @@ BSDF makeBSDF(const Material& m) {
 }
 
 }  // namespace
+
+namespace {
+
+/* ---- externals/bvh.h -------------------------------------------------------------------------------------- */
+struct BBox { /* bvh.h:28-91 */
+    v3 min, max, extent;
+    BBox() : min(V(0)), max(V(0)), extent(V(0)) {}
+    explicit BBox(v3 p) : min(p), max(p) { extent = max - min; }
+    void expandToInclude(v3 p) { min = vmin(min, p); max = vmax(max, p); extent = max - min; }
+    void expandToInclude(const BBox& b) { min = vmin(min, b.min); max = vmax(max, b.max); extent = max - min; }
+    uint32_t maxDimension() const { /* bvh.h:82-87, including the y/z comparison as written */
+        uint32_t result = 0;
+        if (extent.y > extent.x) result = 1;
+        if (extent.z > extent.y) result = 2;
+        return result;
+    }
+    bool intersect(const Ray& r) const { /* bvh.h:33-69; never reports distances */
+        float tmin = (min.x - r.o.x) / r.d.x, tmax = (max.x - r.o.x) / r.d.x;
+        if (tmin > tmax) std::swap(tmin, tmax);
+        float tymin = (min.y - r.o.y) / r.d.y, tymax = (max.y - r.o.y) / r.d.y;
+        if (tymin > tymax) std::swap(tymin, tymax);
+        if ((tmin > tymax) || (tymin > tmax)) return false;
+        if (tymin > tmin) tmin = tymin;
+        if (tymax < tmax) tmax = tymax;
+        float tzmin = (min.z - r.o.z) / r.d.z, tzmax = (max.z - r.o.z) / r.d.z;
+        if (tzmin > tzmax) std::swap(tzmin, tzmax);
+        if ((tmin > tzmax) || (tzmin > tmax)) return false;
+        return true;
+    }
+};
+
+struct FlatNode { BBox bbox; uint32_t start, nPrims, rightOffset; }; /* bvh.h:102-105 */
+
+struct IntersectionInfo { float t = 0, u = 0, v = 0; int object = -1; /* index into prims, -1 = nullptr */ };
+
+struct Emitter { /* core.h:324-332 */
+    size_t shapeID; float area; v3 radiance; std::vector<float> cdf;
+};
+
+struct Scene {
+    std::vector<v3> vertices, normals;
+    std::vector<int> tri_v, tri_n, tri_mat, tri_shape;  /* shape-major */
+    std::vector<int> shapeFirst;                        /* first global triangle of each shape */
+    std::vector<Material> materials;
+    std::vector<BSDF> bsdfs;
+    std::vector<Emitter> emitters;
+    std::vector<int> prims;        /* build_prims: global triangle ids, reordered by the build */
+    std::vector<FlatNode> flatTree;
+    /* camera / film (Config) */
+    v3 cam_o = V(0, 0.8f, 3.8f), cam_at = V(0, 0.8f, 0), cam_up = V(0, 1, 0);
+    float fov = 30.f;
+    int width = 800, height = 600, spp = 1, rrDepth = 5;
+
+    v3 vert(int t, int k) const { return vertices[tri_v[3 * t + k]]; }
+    v3 norm(int t, int k) const { return normals[tri_n[3 * t + k]]; }
+
+    /* accel.h:71-106 */
+    BBox triBBox(int t) const { BBox b(vert(t, 0)); b.expandToInclude(vert(t, 1)); b.expandToInclude(vert(t, 2)); return b; }
+    v3 triCentroid(int t) const { return (vert(t, 0) + vert(t, 1) + vert(t, 2)) / 3.0f; }
+
+    /* BVH::build, bvh.h:147-247 (explicit stack, right pushed before left, in-place partition) */
+    void buildBVH() {
+        const uint32_t Untouched = 0xffffffff, TouchedTwice = 0xfffffffd, leafSize = 4;
+        prims.resize(tri_mat.size());
+        for (size_t i = 0; i < prims.size(); i++) prims[i] = int(i); /* accel.h:115-120: shape-major creation order */
+        struct Entry { uint32_t parent, start, end; };
+        std::vector<Entry> todo(128);
+        uint32_t stackptr = 0, nNodes = 0;
+        todo[stackptr] = {0xfffffffc, 0, uint32_t(prims.size())};
+        stackptr++;
+        std::vector<FlatNode> buildnodes;
+        buildnodes.reserve(prims.size() * 2);
+        while (stackptr > 0) {
+            Entry bnode = todo[--stackptr];
+            uint32_t start = bnode.start, end = bnode.end, nPrims = end - start;
+            nNodes++;
+            FlatNode node;
+            node.start = start; node.nPrims = nPrims; node.rightOffset = Untouched;
+            BBox bb = triBBox(prims[start]);
+            BBox bc(triCentroid(prims[start]));
+            for (uint32_t p = start + 1; p < end; ++p) {
+                bb.expandToInclude(triBBox(prims[p]));
+                bc.expandToInclude(triCentroid(prims[p]));
+            }
+            node.bbox = bb;
+            if (nPrims <= leafSize) node.rightOffset = 0;
+            buildnodes.push_back(node);
+            if (bnode.parent != 0xfffffffc) {
+                buildnodes[bnode.parent].rightOffset--;
+                if (buildnodes[bnode.parent].rightOffset == TouchedTwice) buildnodes[bnode.parent].rightOffset = nNodes - 1 - bnode.parent;
+            }
+            if (node.rightOffset == 0) continue;
+            uint32_t split_dim = bc.maxDimension();
+            float split_coord = .5f * (at(bc.min, split_dim) + at(bc.max, split_dim));
+            uint32_t mid = start;
+            for (uint32_t i = start; i < end; ++i) {
+                if (at(triCentroid(prims[i]), split_dim) < split_coord) { std::swap(prims[i], prims[mid]); ++mid; }
+            }
+            if (mid == start || mid == end) mid = start + (end - start) / 2;
+            if (stackptr + 2 > todo.size()) todo.resize(todo.size() * 2);
+            todo[stackptr++] = {nNodes - 1, mid, end};
+            todo[stackptr++] = {nNodes - 1, start, mid};
+        }
+        flatTree = buildnodes;
+    }
+
+    /* rayTriangleIntersect, core.h:379-400 */
+    static bool rayTriangleIntersect(const Ray& r, v3 v0, v3 v1, v3 v2, float& t, float& u, float& v) {
+        v3 v0v1 = v1 - v0, v0v2 = v2 - v0;
+        v3 pvec = cross(r.d, v0v2);
+        float det = dot(v0v1, pvec);
+        if (std::fabs(det) < kEps) return false;
+        float invDet = 1 / det;
+        v3 tvec = r.o - v0;
+        u = dot(tvec, pvec) * invDet;
+        if (u < 0 || u > 1) return false;
+        v3 qvec = cross(tvec, v0v1);
+        v = dot(r.d, qvec) * invDet;
+        if (v < 0 || u + v > 1) return false;
+        t = dot(v0v2, qvec) * invDet;
+        return true;
+    }
+    /* AcceleratorBVH::BVHNode::getIntersection, accel.h:27-52 */
+    bool primIntersect(int prim, const Ray& ray, IntersectionInfo* I) const {
+        int tr = prims[prim];
+        float t, u, v;
+        if (rayTriangleIntersect(ray, vert(tr, 0), vert(tr, 1), vert(tr, 2), t, u, v)) {
+            if (t > 1e-3) { I->t = t; I->u = u; I->v = v; I->object = prim; return true; }
+        }
+        return false;
+    }
+    /* BVH::getIntersection, bvh.h:259-352: bbhits stay 0 because BBox::intersect never writes them */
+    bool getIntersection(const Ray& ray, IntersectionInfo* intersection, bool occlusion) const {
+        intersection->t = ray.max_t;
+        intersection->object = -1;
+        float bbhits[4] = {};
+        int32_t closer, other;
+        struct Trav { uint32_t i; float mint; };
+        Trav todo[64];
+        int32_t stackptr = 0;
+        todo[stackptr].i = 0;
+        todo[stackptr].mint = ray.min_t;
+        while (stackptr >= 0) {
+            int ni = todo[stackptr].i;
+            float near = todo[stackptr].mint;
+            stackptr--;
+            const FlatNode& node = flatTree[ni];
+            if (near > intersection->t) continue;
+            if (node.rightOffset == 0) {
+                for (uint32_t o = 0; o < node.nPrims; ++o) {
+                    IntersectionInfo current;
+                    bool hit = primIntersect(int(node.start + o), ray, &current);
+                    if (hit) {
+                        if (occlusion && current.t <= ray.max_t && current.t >= ray.min_t) return true;
+                        if (current.t < intersection->t) *intersection = current;
+                    }
+                }
+            } else {
+                bool hitc0 = flatTree[ni + 1].bbox.intersect(ray);
+                bool hitc1 = flatTree[ni + node.rightOffset].bbox.intersect(ray);
+                if (hitc0 && hitc1) {
+                    closer = ni + 1;
+                    other = ni + node.rightOffset;
+                    if (bbhits[2] < bbhits[0]) { std::swap(bbhits[0], bbhits[2]); std::swap(bbhits[1], bbhits[3]); std::swap(closer, other); }
+                    todo[++stackptr] = {uint32_t(other), bbhits[2]};
+                    todo[++stackptr] = {uint32_t(closer), bbhits[0]};
+                } else if (hitc0) {
+                    todo[++stackptr] = {uint32_t(ni + 1), bbhits[0]};
+                } else if (hitc1) {
+                    todo[++stackptr] = {uint32_t(ni + node.rightOffset), bbhits[2]};
+                }
+            }
+        }
+        return intersection->object != -1;
+    }
+    /* AcceleratorBVH::intersect, accel.h:125-172 */
+    bool intersect(const Ray& ray, SurfaceInteraction& info) const {
+        IntersectionInfo iInfo;
+        if (getIntersection(ray, &iInfo, false)) {
+            info.t = iInfo.t;
+            if (iInfo.t <= ray.max_t && iInfo.t >= ray.min_t) {
+                int tr = prims[iInfo.object];
+                v3 v0 = vert(tr, 0), v1 = vert(tr, 1), v2 = vert(tr, 2), n0 = norm(tr, 0), n1 = norm(tr, 1), n2 = norm(tr, 2);
+                info.shapeID = size_t(tri_shape[tr]);
+                info.primID = size_t(tr - shapeFirst[tri_shape[tr]]);
+                info.t = iInfo.t; info.u = iInfo.u; info.v = iInfo.v;
+                info.p = barycentric(v0, v1, v2, iInfo.u, iInfo.v);
+                info.frameNs = Frame(normalize(barycentric(n0, n1, n2, info.u, info.v)));
+                info.wo = info.frameNs.toLocal(-ray.d);
+                info.matID = tri_mat[tr];
+                return true;
+            }
+            return false;
+        }
+        info.t = std::numeric_limits<float>::max();
+        return false;
+    }
+
+    /* Scene::load tail: BSDFs (renderer.cpp:259-271), emitters (:279-305), getShapeArea (:317-339) */
+    void finish() {
+        bsdfs.clear();
+        for (auto& m : materials) bsdfs.push_back(makeBSDF(m));
+        size_t nShapes = tri_shape.empty() ? 0 : size_t(tri_shape.back()) + 1;
+        shapeFirst.assign(nShapes + 1, 0);
+        for (size_t t = 0; t < tri_shape.size(); t++) shapeFirst[tri_shape[t] + 1] = int(t + 1);
+        for (size_t s = 1; s <= nShapes; s++) shapeFirst[s] = std::max(shapeFirst[s], shapeFirst[s - 1]);
+        emitters.clear();
+        for (size_t s = 0; s < nShapes; s++) {
+            int first = shapeFirst[s], last = shapeFirst[s + 1];
+            if (first == last) continue;
+            const BSDF& b = bsdfs[tri_mat[first]];
+            if (!(length2(b.emission) > 0.f)) continue; /* BSDF::isEmissive, core.h:306-308 */
+            Emitter e;
+            e.shapeID = s; e.radiance = b.emission; e.cdf.push_back(0.f);
+            for (int t = first; t < last; t++) {
+                v3 e1 = vert(t, 1) - vert(t, 0), e2 = vert(t, 2) - vert(t, 0), e3 = cross(e1, e2);
+                e.cdf.push_back(e.cdf.back() + 0.5f * std::sqrt(e3.x * e3.x + e3.y * e3.y + e3.z * e3.z));
+            }
+            e.area = e.cdf.back();
+            float sum = e.cdf.back(); /* Distribution1D::normalize, math.h:94-101 */
+            for (float& c : e.cdf) c /= sum;
+            emitters.push_back(e);
+        }
+        buildBVH();
+    }
+};
+
+}  // namespace
+
+namespace {
+
+/* ---- camera matrices with glm's operation order (renderer.cpp:143-153, bdpt.h:485-490) --------------------- */
+struct M4 { float m[4][4]; };  /* m[col][row] */
+inline M4 ident() { M4 r; std::memset(&r, 0, sizeof(r)); for (int i = 0; i < 4; i++) r.m[i][i] = 1.f; return r; }
+inline void mulv(const M4& M, const float v[4], float o[4]) { /* (m0*x + m1*y) + (m2*z + m3*w) */
+    for (int r = 0; r < 4; r++) o[r] = (M.m[0][r] * v[0] + M.m[1][r] * v[1]) + (M.m[2][r] * v[2] + M.m[3][r] * v[3]);
+}
+inline M4 mulm(const M4& A, const M4& B) {
+    M4 R;
+    for (int j = 0; j < 4; j++) for (int r = 0; r < 4; r++)
+        R.m[j][r] = ((A.m[0][r] * B.m[j][0] + A.m[1][r] * B.m[j][1]) + A.m[2][r] * B.m[j][2]) + A.m[3][r] * B.m[j][3];
+    return R;
+}
+inline M4 lookAt(v3 eye, v3 center, v3 up) {
+    v3 f = normalize(center - eye), s = normalize(cross(f, up)), u = cross(s, f);
+    M4 R = ident();
+    R.m[0][0] = s.x; R.m[1][0] = s.y; R.m[2][0] = s.z;
+    R.m[0][1] = u.x; R.m[1][1] = u.y; R.m[2][1] = u.z;
+    R.m[0][2] = -f.x; R.m[1][2] = -f.y; R.m[2][2] = -f.z;
+    R.m[3][0] = -dot(s, eye); R.m[3][1] = -dot(u, eye); R.m[3][2] = dot(f, eye);
+    return R;
+}
+inline M4 perspective(float fovy, float aspect, float zn, float zf) {
+    float th = std::tan(fovy / 2.f);
+    M4 R; std::memset(&R, 0, sizeof(R));
+    R.m[0][0] = 1.f / (aspect * th); R.m[1][1] = 1.f / th; R.m[2][2] = -(zf + zn) / (zf - zn); R.m[2][3] = -1.f;
+    R.m[3][2] = -(2.f * zf * zn) / (zf - zn);
+    return R;
+}
+inline M4 scaleM(float x, float y, float z) { M4 R = ident(); R.m[0][0] *= x; R.m[1][1] *= y; R.m[2][2] *= z; return R; }
+inline M4 translateM(float x, float y, float z) {
+    M4 I = ident(), R = I;
+    for (int r = 0; r < 4; r++) R.m[3][r] = ((I.m[0][r] * x + I.m[1][r] * y) + I.m[2][r] * z) + I.m[3][r];
+    return R;
+}
+M4 inverse(const M4& M) { /* glm::inverse(mat4): cofactors, then one reciprocal determinant */
+    auto m = [&](int c, int r) { return M.m[c][r]; };
+    float c00 = m(2,2)*m(3,3) - m(3,2)*m(2,3), c02 = m(1,2)*m(3,3) - m(3,2)*m(1,3), c03 = m(1,2)*m(2,3) - m(2,2)*m(1,3);
+    float c04 = m(2,1)*m(3,3) - m(3,1)*m(2,3), c06 = m(1,1)*m(3,3) - m(3,1)*m(1,3), c07 = m(1,1)*m(2,3) - m(2,1)*m(1,3);
+    float c08 = m(2,1)*m(3,2) - m(3,1)*m(2,2), c10 = m(1,1)*m(3,2) - m(3,1)*m(1,2), c11 = m(1,1)*m(2,2) - m(2,1)*m(1,2);
+    float c12 = m(2,0)*m(3,3) - m(3,0)*m(2,3), c14 = m(1,0)*m(3,3) - m(3,0)*m(1,3), c15 = m(1,0)*m(2,3) - m(2,0)*m(1,3);
+    float c16 = m(2,0)*m(3,2) - m(3,0)*m(2,2), c18 = m(1,0)*m(3,2) - m(3,0)*m(1,2), c19 = m(1,0)*m(2,2) - m(2,0)*m(1,2);
+    float c20 = m(2,0)*m(3,1) - m(3,0)*m(2,1), c22 = m(1,0)*m(3,1) - m(3,0)*m(1,1), c23 = m(1,0)*m(2,1) - m(2,0)*m(1,1);
+    float F0[4] = {c00,c00,c02,c03}, F1[4] = {c04,c04,c06,c07}, F2[4] = {c08,c08,c10,c11}, F3[4] = {c12,c12,c14,c15}, F4[4] = {c16,c16,c18,c19}, F5[4] = {c20,c20,c22,c23};
+    float V0[4] = {m(1,0),m(0,0),m(0,0),m(0,0)}, V1[4] = {m(1,1),m(0,1),m(0,1),m(0,1)}, V2[4] = {m(1,2),m(0,2),m(0,2),m(0,2)}, V3[4] = {m(1,3),m(0,3),m(0,3),m(0,3)};
+    float SA[4] = {1,-1,1,-1}, SB[4] = {-1,1,-1,1};
+    M4 I;
+    for (int k = 0; k < 4; k++) {
+        I.m[0][k] = ((V1[k]*F0[k] - V2[k]*F1[k]) + V3[k]*F2[k]) * SA[k];
+        I.m[1][k] = ((V0[k]*F0[k] - V2[k]*F3[k]) + V3[k]*F4[k]) * SB[k];
+        I.m[2][k] = ((V0[k]*F1[k] - V1[k]*F3[k]) + V3[k]*F5[k]) * SA[k];
+        I.m[3][k] = ((V0[k]*F2[k] - V1[k]*F4[k]) + V2[k]*F5[k]) * SB[k];
+    }
+    float det = (m(0,0)*I.m[0][0] + m(0,1)*I.m[1][0]) + (m(0,2)*I.m[2][0] + m(0,3)*I.m[3][0]);
+    float inv = 1.f / det;
+    for (int c = 0; c < 4; c++) for (int r = 0; r < 4; r++) I.m[c][r] *= inv;
+    return I;
+}
+
+struct PathVertex { SurfaceInteraction hit; v3 throughput; float vcm, vc, rr; }; /* bdpt.h:24-35 */
+
+/* BDPTIntegrator (bdpt.h:37-518) with LIGHT_TRACING=0, PATH_TRACING=0, NO_RR=1 as the file is shipped */
+struct BDPT {
+    const Scene& scene;
+    std::vector<v3>* rgb;  /* RenderBuffer */
+    int m_rrDepth;
+    explicit BDPT(const Scene& s, std::vector<v3>* fb) : scene(s), rgb(fb), m_rrDepth(s.rrDepth) {}
+    float deg2radFov() const { return kPi / 180.f * scene.fov; }
+
+    /* integrator.cpp:35-100 */
+    const BSDF* getBSDF(const SurfaceInteraction& h) const { return &scene.bsdfs[scene.tri_mat[scene.shapeFirst[h.shapeID] + int(h.primID)]]; }
+    v3 getEmission(const SurfaceInteraction& h) const { return scene.materials[h.matID].ke; }
+    size_t selectEmitter(float sample, float& pdf) const {
+        size_t id = size_t(sample * scene.emitters.size());
+        id = std::min(id, scene.emitters.size() - 1);
+        pdf = 1.f / scene.emitters.size();
+        return id;
+    }
+    size_t getEmitterIDByShapeID(size_t shapeID) const {
+        for (size_t i = 0; i < scene.emitters.size(); i++) if (scene.emitters[i].shapeID == shapeID) return i;
+        return scene.emitters.size();
+    }
+    void sampleEmitterPosition(Sampler& sampler, const Emitter& em, v3& n, v3& pos, float& pdf) const {
+        float s = sampler.next();
+        auto it = std::upper_bound(em.cdf.begin(), em.cdf.end(), s); /* Distribution1D::sample, math.h:107-111 */
+        int primID = std::min(std::max(int(it - em.cdf.begin()) - 1, 0), int(em.cdf.size()) - 2);
+        float sx, sy; sampler.next2D(&sx, &sy);
+        float u = std::sqrt(1.f - sx); /* squareToUniformTriangle, math.h:229-234 */
+        float bu = 1 - u, bv = u * sy;
+        int t = scene.shapeFirst[em.shapeID] + primID;
+        pos = barycentric(scene.vert(t, 0), scene.vert(t, 1), scene.vert(t, 2), bu, bv);
+        n = normalize(barycentric(scene.norm(t, 0), scene.norm(t, 1), scene.norm(t, 2), bu, bv));
+        pdf = 1.f / em.area;
+    }
+
+    bool visibilityQuery(v3 start, v3 end) const { /* bdpt.h:498-506 */
+        v3 dir = end - start;
+        float dist = length(dir);
+        dir = dir / dist;
+        IntersectionInfo info;
+        Ray ray(start, dir, kEps, dist - 0.00001f);
+        return scene.getIntersection(ray, &info, true);
+    }
+    void splatToImagePlane(v3 position, int& xPixel, int& yPixel) const { /* bdpt.h:485-496 */
+        float aspectRatio = (float)scene.width / scene.height;
+        M4 worldToCamera = lookAt(scene.cam_o, scene.cam_at, scene.cam_up);
+        M4 cameraToClip = perspective(deg2radFov(), aspectRatio, 1.f, 1000.f);
+        M4 NDCToScreen = mulm(mulm(scaleM(float(scene.width), float(scene.height), 1.0f), scaleM(0.5f, -0.5f, 1.f)), translateM(1.f, -1.f, 0.f));
+        float uv[4] = {position.x, position.y, position.z, 1.f}, t[4];
+        mulv(worldToCamera, uv, t); mulv(cameraToClip, t, uv);
+        float w = uv[3];
+        for (int k = 0; k < 4; k++) uv[k] /= w;
+        mulv(NDCToScreen, uv, t);
+        xPixel = static_cast<int>(t[0]);
+        yPixel = static_cast<int>(t[1]);
+    }
+
+    bool ContinuePathRandomWalk(SurfaceInteraction& hit, Sampler& sampler, float rrProbability, PathVertex& pathVertex, v3& throughput,
+                                int& depth, float& vc, float& vcm, Ray& wi) const { /* bdpt.h:243-291 */
+        const BSDF* bsdf = getBSDF(hit);
+        bool isDeltaBsdf = (bsdf->combinedType & EDelta);
+        float bsdfPdf_w, sx, sy;
+        sampler.next2D(&sx, &sy);
+        v3 bsdfCosTheta = bsdf->sample(hit, sx, sy, &bsdfPdf_w);
+        bsdfPdf_w *= rrProbability;
+        pathVertex.hit.wi = hit.wi;
+        float absCosOut = std::fabs(hit.wi.z);
+        if (bsdfCosTheta == V(0.f)) return false;
+        throughput = throughput * (bsdfCosTheta * (1.f / bsdfPdf_w));
+        depth++;
+        SurfaceInteraction reverseHit(hit);
+        std::swap(reverseHit.wi, reverseHit.wo);
+        float previousVertexReversePdf_w = isDeltaBsdf ? bsdfPdf_w : bsdf->pdf(reverseHit) * rrProbability;
+        if (isDeltaBsdf) {
+            vc = (absCosOut / bsdfPdf_w) * (previousVertexReversePdf_w * vc);
+            vcm = 0.f;
+        } else {
+            vc = (absCosOut / bsdfPdf_w) * (vcm + previousVertexReversePdf_w * vc);
+            vcm = 1.f / bsdfPdf_w;
+        }
+        wi = Ray(hit.p, hit.frameNs.toWorld(hit.wi));
+        return true;
+    }
+
+    void connectToCamera(const PathVertex& lightVertex) const { /* bdpt.h:295-371 */
+        v3 cameraForward = normalize(scene.cam_at - scene.cam_o);
+        v3 eyeToLightVert = lightVertex.hit.p - scene.cam_o;
+        float invDistanceSquared = 1.f / length2(eyeToLightVert);
+        eyeToLightVert = eyeToLightVert * std::sqrt(invDistanceSquared);
+        int xPixel, yPixel;
+        splatToImagePlane(lightVertex.hit.p, xPixel, yPixel);
+        if (xPixel < 0 || yPixel < 0 || xPixel >= scene.width || yPixel >= scene.height) return;
+        float cosCamera = dot(cameraForward, eyeToLightVert);
+        if (cosCamera <= 0.f) return;
+        SurfaceInteraction ei(lightVertex.hit);
+        ei.wi = ei.frameNs.toLocal(-eyeToLightVert);
+        v3 bsdfCosTheta = getBSDF(ei)->eval(ei);
+        if (bsdfCosTheta == V(0.f) || ei.wi.z <= 0.f) return;
+        if (visibilityQuery(scene.cam_o, lightVertex.hit.p)) return;
+        float virtualNearPlaneDistance = (1.f / std::tan(deg2radFov() * 0.5f)) * scene.height * 0.5f;
+        float imagePointToCameraDist = virtualNearPlaneDistance / cosCamera;
+        float imageAreaToCameraSolidAngle = imagePointToCameraDist * imagePointToCameraDist / cosCamera;
+        float cameraSolidAngleToSurfaceArea = ei.wi.z * invDistanceSquared;
+        float imageAreaToSurfaceArea = imageAreaToCameraSolidAngle * cameraSolidAngleToSurfaceArea;
+        float surfaceAreaToImageArea = 1.f / imageAreaToSurfaceArea;
+        int nlightSubpath = scene.width * scene.height;
+        v3 radiance = lightVertex.throughput * (bsdfCosTheta * (1.f / ei.wi.z)) * (1.f / surfaceAreaToImageArea) * (1.f / nlightSubpath) * (1.f / scene.spp);
+        float reversePdf_a = 1.f * imageAreaToSurfaceArea;
+        SurfaceInteraction reverseHit(ei);
+        std::swap(reverseHit.wi, reverseHit.wo);
+        float previousVertexReversePdf_w = getBSDF(reverseHit)->pdf(reverseHit) * lightVertex.rr;
+        float lightWeight = (reversePdf_a / nlightSubpath) * (lightVertex.vcm + previousVertexReversePdf_w * lightVertex.vc);
+        float eyeWeight = 0.f;
+        float misWeight = 1.f / (lightWeight + 1.f + eyeWeight);
+        radiance = radiance * misWeight;
+        int pixel = yPixel * scene.width + xPixel;
+        (*rgb)[pixel] = (*rgb)[pixel] + radiance; /* under the per-pixel lock in the reference, bdpt.h:363-370 */
+    }
+
+    v3 connectToLight(const PathVertex& eyeVertex, Sampler& sampler) const { /* bdpt.h:374-430 */
+        float emitterPdf;
+        size_t emitterID = selectEmitter(sampler.next(), emitterPdf);
+        const Emitter& emitter = scene.emitters[emitterID];
+        v3 emitterNormal, emitterPosition;
+        float emitterPositionPdf;
+        sampleEmitterPosition(sampler, emitter, emitterNormal, emitterPosition, emitterPositionPdf);
+        v3 l2e = eyeVertex.hit.p - emitterPosition;
+        float d2 = length2(l2e);
+        l2e = l2e * (1.f / std::sqrt(d2));
+        SurfaceInteraction ei(eyeVertex.hit);
+        ei.wi = ei.frameNs.toLocal(-l2e);
+        float cosAtLight = dot(emitterNormal, l2e), cosAtEyeVertex = ei.wi.z;
+        if (cosAtLight <= 0.f || cosAtEyeVertex <= 0.f) return V(0.f);
+        float emitterConnectPdf_a = emitterPdf * emitterPositionPdf;
+        float emitterConnectPdf_w = emitterConnectPdf_a * d2 / cosAtLight;
+        float emitterDirectionPdf_w = kInvTwoPi;
+        v3 Li = getBSDF(ei)->eval(ei) * (1.f / emitterConnectPdf_w) * eyeVertex.throughput * emitter.radiance;
+        if (Li == V(0.f)) return V(0.f);
+        if (visibilityQuery(eyeVertex.hit.p, emitterPosition)) return V(0.f);
+        float lightPathReversePdf_w = getBSDF(ei)->pdf(ei) * eyeVertex.rr;
+        float lightWeight = lightPathReversePdf_w / emitterConnectPdf_w;
+        SurfaceInteraction ri(ei);
+        std::swap(ri.wi, ri.wo);
+        float eyePathPreviousVertexReversePdf_w = getBSDF(ri)->pdf(ri) * eyeVertex.rr;
+        float eyePathCurrentVertexReversePdf_a = cosAtEyeVertex * (1.f / d2) * emitterDirectionPdf_w;
+        float eyeWeight = eyePathCurrentVertexReversePdf_a * (eyeVertex.vcm + eyePathPreviousVertexReversePdf_w * eyeVertex.vc);
+        float misWeight = 1.f / (lightWeight + 1.f + eyeWeight);
+        return Li * misWeight;
+    }
+
+    v3 connectVertices(const PathVertex& lightVertex, const PathVertex& eyeVertex) const { /* bdpt.h:434-483 */
+        v3 l2e = eyeVertex.hit.p - lightVertex.hit.p;
+        float invDistanceSquared = 1.f / length2(l2e);
+        l2e = l2e * std::sqrt(invDistanceSquared);
+        SurfaceInteraction lh(lightVertex.hit);
+        lh.wi = lh.frameNs.toLocal(l2e);
+        SurfaceInteraction eh(eyeVertex.hit);
+        eh.wi = eh.frameNs.toLocal(-l2e);
+        float cosAtLightVertex = lh.wi.z, cosAtEyeVertex = eh.wi.z;
+        if (cosAtLightVertex <= 0.f || cosAtEyeVertex <= 0.f) return V(0.f);
+        if (visibilityQuery(eyeVertex.hit.p, lightVertex.hit.p)) return V(0.f);
+        v3 Li = getBSDF(lh)->eval(lh) * getBSDF(eh)->eval(eh);
+        Li = Li * (lightVertex.throughput * eyeVertex.throughput * invDistanceSquared);
+        float eyePathReversePdf_w = getBSDF(lh)->pdf(lh) * lightVertex.rr;
+        std::swap(lh.wi, lh.wo);
+        float lightPathPreviousVertexReversePdf_w = getBSDF(lh)->pdf(lh) * lightVertex.rr;
+        float lightPathReversePdf_w = getBSDF(eh)->pdf(eh) * eyeVertex.rr;
+        eh.wo = eh.wi;
+        eh.wi = eyeVertex.hit.wo;
+        float eyePathPreviousVertexReversePdf_w = getBSDF(eh)->pdf(eh) * eyeVertex.rr;
+        float lightPathReversePdf_a = lightPathReversePdf_w * (cosAtLightVertex) * invDistanceSquared;
+        float eyePathReversePdf_a = eyePathReversePdf_w * (cosAtEyeVertex) * invDistanceSquared;
+        float lightWeight = lightPathReversePdf_a * (lightVertex.vcm + lightPathPreviousVertexReversePdf_w * lightVertex.vc);
+        float eyeWeight = eyePathReversePdf_a * (eyeVertex.vcm + eyePathPreviousVertexReversePdf_w * eyeVertex.vc);
+        float misWeight = 1.f / (lightWeight + 1.f + eyeWeight);
+        return Li * misWeight;
+    }
+
+    void lightSubpathWalk(Sampler& sampler, std::vector<PathVertex>& lightSubpath) const { /* bdpt.h:158-217 */
+        float emitterPdf, emitterAreaPdf, emitterEmissionPdf;
+        v3 normalOut, positionOut;
+        size_t id = selectEmitter(sampler.next(), emitterPdf);
+        const Emitter& emitter = scene.emitters[id];
+        sampleEmitterPosition(sampler, emitter, normalOut, positionOut, emitterAreaPdf);
+        float sx, sy; sampler.next2D(&sx, &sy);
+        v3 emitterDirection = squareToUniformHemisphere(sx, sy);
+        emitterEmissionPdf = kInvTwoPi * emitterAreaPdf;
+        emitterAreaPdf *= emitterPdf;
+        emitterEmissionPdf *= emitterPdf;
+        Frame lightFrame(normalOut);
+        Ray wi(positionOut, lightFrame.toWorld(emitterDirection));
+        v3 throughput = emitterDirection.z * emitter.radiance * (1.f / emitterEmissionPdf);
+        float vc = emitterDirection.z * (1.f / emitterEmissionPdf);
+        float vcm = emitterAreaPdf / emitterEmissionPdf;
+        if (emitterDirection.z <= 0.f) return;
+        int depth = 1;
+        float rrProbability = 1.f;
+        while (depth < m_rrDepth || (sampler.next() < rrProbability && false /* !NO_RR */)) {
+            SurfaceInteraction hit;
+            if (!scene.intersect(wi, hit)) break;
+            const float distSquared = hit.t * hit.t, absCosIn = std::fabs(hit.wo.z);
+            vcm *= (distSquared / absCosIn);
+            vc *= (1.f / absCosIn);
+            rrProbability = 1.f; /* NO_RR */
+            unsigned hitBSDFType = getBSDF(hit)->combinedType;
+            PathVertex lightVertex{hit, throughput, vcm, vc, rrProbability};
+            if (!(hitBSDFType & EDelta)) connectToCamera(lightVertex);
+            if (!ContinuePathRandomWalk(hit, sampler, rrProbability, lightVertex, throughput, depth, vc, vcm, wi)) break;
+            if (!(hitBSDFType & EDelta)) lightSubpath.push_back(lightVertex);
+        }
+    }
+
+    void eyeSubpathWalk(const std::vector<PathVertex>& lightSubpath, const Ray& ray, Sampler& sampler, v3& Li) const { /* bdpt.h:46-155 */
+        bool isPathPureSpecular = true;
+        v3 cameraForward = normalize(scene.cam_at - scene.cam_o);
+        float cosCamera = dot(cameraForward, ray.d);
+        float virtualNearPlaneDistance = (1.f / std::tan(deg2radFov() * 0.5f)) * scene.height * 0.5f;
+        float imagePointToCameraDist = virtualNearPlaneDistance / cosCamera;
+        float imageAreaToCameraSolidAngle = imagePointToCameraDist * imagePointToCameraDist / cosCamera;
+        float t1Pdf = 1.f * imageAreaToCameraSolidAngle;
+        Ray wi(ray);
+        v3 throughput = V(1.f);
+        float vc = 0.f;
+        float vcm = scene.width * scene.height * (1.f / t1Pdf);
+        int depth = 1;
+        float rrProbability = 1.f;
+        while (depth < m_rrDepth || (sampler.next() < rrProbability && false /* !NO_RR */)) {
+            SurfaceInteraction hit;
+            if (!scene.intersect(wi, hit)) break;
+            const float distSquared = hit.t * hit.t, absCosIn = std::fabs(hit.wo.z);
+            vcm *= (distSquared / absCosIn);
+            vc *= (1.f / absCosIn);
+            if (getEmission(hit) != V(0.f)) {
+                const Emitter& emitter = scene.emitters[getEmitterIDByShapeID(hit.shapeID)];
+                float emitterPdf = 1.f / scene.emitters.size();
+                if (depth > 1) {
+                    v3 contribution = emitter.radiance * throughput;
+                    float emitterPositionPdf_a = 1.f / (emitter.area * emitterPdf);
+                    float emitterDirectionPdf_w = kInvTwoPi;
+                    float cameraWeight = emitterPositionPdf_a * vcm + (emitterPositionPdf_a * emitterDirectionPdf_w) * vc;
+                    float misWeight = 1.f / (1.f + cameraWeight);
+                    if (!isPathPureSpecular) contribution = contribution * misWeight;
+                    Li = Li + contribution;
+                } else if (depth == 1) {
+                    Li = Li + getEmission(hit);
+                }
+                break;
+            }
+            rrProbability = 1.f; /* NO_RR */
+            PathVertex eyeVertex{hit, throughput, vcm, vc, rrProbability};
+            unsigned hitBSDFType = getBSDF(hit)->combinedType;
+            if (!(hitBSDFType & EDelta)) {
+                isPathPureSpecular = false;
+                Li = Li + connectToLight(eyeVertex, sampler);
+                for (size_t i = 0; i < lightSubpath.size(); i++) Li = Li + connectVertices(lightSubpath[i], eyeVertex);
+            }
+            if (!ContinuePathRandomWalk(hit, sampler, rrProbability, eyeVertex, throughput, depth, vc, vcm, wi)) break;
+        }
+    }
+
+    v3 render(const Ray& ray, Sampler& sampler) const { /* bdpt.h:219-241 */
+        v3 Li = V(0.f);
+        SurfaceInteraction hit;
+        if (scene.intersect(ray, hit)) {
+            std::vector<PathVertex> lightSubpath;
+            lightSubpathWalk(sampler, lightSubpath);
+            eyeSubpathWalk(lightSubpath, ray, sampler, Li);
+        }
+        return Li;
+    }
+};
+
+}  // namespace
+
+/* ---- C interface (ctypes: oracle/oracle_port.py) ------------------------------------------------------------ */
+extern "C" {
+
+void* orc_create(const float* positions, size_t npos, const float* normals, size_t nnrm, const int* tri_v, const int* tri_n,
+                 const int* tri_mat, const int* tri_shape, size_t ntris, const float* mats16, size_t nmat) {
+    Scene* s = new Scene();
+    for (size_t i = 0; i < npos; i++) s->vertices.push_back(V(positions[3 * i], positions[3 * i + 1], positions[3 * i + 2]));
+    for (size_t i = 0; i < nnrm; i++) s->normals.push_back(V(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]));
+    s->tri_v.assign(tri_v, tri_v + 3 * ntris); s->tri_n.assign(tri_n, tri_n + 3 * ntris);
+    s->tri_mat.assign(tri_mat, tri_mat + ntris); s->tri_shape.assign(tri_shape, tri_shape + ntris);
+    for (size_t i = 0; i < nmat; i++) {
+        const float* m = mats16 + 16 * i;
+        s->materials.push_back(Material{V(m[0], m[1], m[2]), V(m[3], m[4], m[5]), V(m[6], m[7], m[8]), V(m[9], m[10], m[11]), m[12], m[13], int(m[14])});
+    }
+    s->finish();
+    return s;
+}
+void orc_destroy(void* h) { delete static_cast<Scene*>(h); }
+
+void orc_set_config(void* h, const float* eye, const float* at, const float* up, float fov, int width, int height, int spp, int rrDepth) {
+    Scene* s = static_cast<Scene*>(h);
+    s->cam_o = V(eye[0], eye[1], eye[2]); s->cam_at = V(at[0], at[1], at[2]); s->cam_up = V(up[0], up[1], up[2]);
+    s->fov = fov; s->width = width; s->height = height; s->spp = spp; s->rrDepth = rrDepth;
+}
+
+void orc_bvh_order(void* h, int* order) { Scene* s = static_cast<Scene*>(h); std::copy(s->prims.begin(), s->prims.end(), order); }
+int orc_bvh_node_count(void* h) { return int(static_cast<Scene*>(h)->flatTree.size()); }
+
+int orc_emitters(void* h, int* shape, float* area, float* radiance, float* cdf_concat, int max_e) {
+    Scene* s = static_cast<Scene*>(h);
+    size_t off = 0;
+    for (size_t i = 0; i < s->emitters.size() && int(i) < max_e; i++) {
+        shape[i] = int(s->emitters[i].shapeID); area[i] = s->emitters[i].area;
+        radiance[3 * i] = s->emitters[i].radiance.x; radiance[3 * i + 1] = s->emitters[i].radiance.y; radiance[3 * i + 2] = s->emitters[i].radiance.z;
+        for (float c : s->emitters[i].cdf) cdf_concat[off++] = c;
+    }
+    return int(s->emitters.size());
+}
+
+void orc_camera_matrices(void* h, float* out64) {
+    Scene* s = static_cast<Scene*>(h);
+    M4 w2c = lookAt(s->cam_o, s->cam_at, s->cam_up), c2w = inverse(w2c);
+    M4 clip = perspective(kPi / 180.f * s->fov, (float)s->width / s->height, 1.f, 1000.f);
+    M4 n2s = mulm(mulm(scaleM(float(s->width), float(s->height), 1.0f), scaleM(0.5f, -0.5f, 1.f)), translateM(1.f, -1.f, 0.f));
+    std::memcpy(out64, w2c.m, 64); std::memcpy(out64 + 16, c2w.m, 64); std::memcpy(out64 + 32, clip.m, 64); std::memcpy(out64 + 48, n2s.m, 64);
+}
+
+static Ray mkRay(const float* r) { return Ray(V(r[0], r[1], r[2]), V(r[3], r[4], r[5]), r[6], r[7]); }
+
+/* ids: n x 3 (hit, shapeID, primID); tuv: n x 3 */
+void orc_intersect(void* h, const float* rays8, int64_t n, int* ids, float* tuv) {
+    Scene* s = static_cast<Scene*>(h);
+    for (int64_t i = 0; i < n; i++) {
+        SurfaceInteraction si;
+        bool hit = s->intersect(mkRay(rays8 + 8 * i), si);
+        ids[3 * i] = hit; ids[3 * i + 1] = hit ? int(si.shapeID) : -1; ids[3 * i + 2] = hit ? int(si.primID) : -1;
+        tuv[3 * i] = si.t; tuv[3 * i + 1] = hit ? si.u : 0.f; tuv[3 * i + 2] = hit ? si.v : 0.f;
+    }
+}
+void orc_occluded(void* h, const float* rays8, int64_t n, uint8_t* out) {
+    Scene* s = static_cast<Scene*>(h);
+    for (int64_t i = 0; i < n; i++) { IntersectionInfo info; out[i] = s->getIntersection(mkRay(rays8 + 8 * i), &info, true) ? 1 : 0; }
+}
+/* q: n x 8 (wo, wi, u); out: n x 12 (eval3, pdf, sample3, sample_pdf, sample_wi3, type) */
+void orc_bsdf(void* h, int mat, const float* q, int64_t n, float* out) {
+    Scene* s = static_cast<Scene*>(h);
+    const BSDF& b = s->bsdfs[mat];
+    for (int64_t i = 0; i < n; i++) {
+        const float* x = q + 8 * i; float* o = out + 12 * i;
+        SurfaceInteraction si; si.wo = V(x[0], x[1], x[2]); si.wi = V(x[3], x[4], x[5]);
+        v3 e = b.eval(si); o[0] = e.x; o[1] = e.y; o[2] = e.z; o[3] = b.pdf(si);
+        SurfaceInteraction ss; ss.wo = si.wo;
+        float pdf = 0.f; v3 sv = b.sample(ss, x[6], x[7], &pdf);
+        o[4] = sv.x; o[5] = sv.y; o[6] = sv.z; o[7] = pdf; o[8] = ss.wi.x; o[9] = ss.wi.y; o[10] = ss.wi.z; o[11] = float(b.combinedType);
+    }
+}
+void orc_sampler_stream(int seed, int64_t n, float* out) { Sampler s(seed); for (int64_t i = 0; i < n; i++) out[i] = s.next(); }
+
+/* BDPTIntegrator::render per path. seeds != NULL: private Sampler(seed); else injected numbers (n x stride).
+ * Splats are returned by scanning the cleared frame buffer exactly like oracle/ref_harness.cpp does. */
+void orc_bdpt_paths(void* h, const float* rays8, const int* seeds, const float* injected, int64_t stride, int64_t n, int maxSplats,
+                    float* Li, int* splat_pix, float* splat_rgb, int* nDraws) {
+    Scene* s = static_cast<Scene*>(h);
+    std::vector<v3> fb(size_t(s->width) * s->height, V(0.f));
+    BDPT bdpt(*s, &fb);
+    for (int64_t i = 0; i < n; i++) {
+        std::fill(fb.begin(), fb.end(), V(0.f));
+        Sampler sm(seeds ? seeds[i] : 0);
+        if (!seeds) sm.injected = injected + i * stride;
+        v3 L = bdpt.render(mkRay(rays8 + 8 * i), sm);
+        Li[3 * i] = L.x; Li[3 * i + 1] = L.y; Li[3 * i + 2] = L.z;
+        int k = 0;
+        for (int m = 0; m < maxSplats; m++) splat_pix[i * maxSplats + m] = -1;
+        for (size_t p = 0; p < fb.size(); p++) {
+            if (fb[p].x != 0.f || fb[p].y != 0.f || fb[p].z != 0.f) {
+                if (k < maxSplats) {
+                    splat_pix[i * maxSplats + k] = int(p);
+                    splat_rgb[(i * maxSplats + k) * 3] = fb[p].x; splat_rgb[(i * maxSplats + k) * 3 + 1] = fb[p].y; splat_rgb[(i * maxSplats + k) * 3 + 2] = fb[p].z;
+                }
+                k++;
+            }
+        }
+        if (nDraws) nDraws[i] = int(sm.pos);
+    }
+}
+
+/* Renderer::render offline branch (renderer.cpp:130-214) over `threads` static pixel chunks (parallelfor.h:25-66).
+ * Unlike the reference, every chunk owns its Sampler (seed + chunk) and its splat buffer, so the run is race-free
+ * and deterministic; the buffers are summed at the end.  Returns seconds spent rendering. */
+double orc_render(void* h, float* rgb_out, int threads, int seed) {
+    Scene* s = static_cast<Scene*>(h);
+    const int W = s->width, H = s->height, np = W * H;
+    threads = std::max(1, threads);
+    M4 worldToCamera = lookAt(s->cam_o, s->cam_at, s->cam_up), cameraToWorld = inverse(worldToCamera);
+    const float invWidth = 1.f / W, invHeight = 1.f / H;
+    const float angle = std::tan(kPi / 180.f * s->fov * 0.5f), aspectRatio = (float)W / H;
+    std::vector<std::vector<v3>> fbs(threads, std::vector<v3>(size_t(np), V(0.f)));
+    auto t0 = std::chrono::high_resolution_clock::now();
+    auto work = [&](int tid) {
+        BDPT bdpt(*s, &fbs[tid]);
+        Sampler sampler(seed + tid);
+        int start = int(int64_t(np) * tid / threads), end = int(int64_t(np) * (tid + 1) / threads);
+        for (int pixel = start; pixel < end; ++pixel) {
+            int j = pixel % W, i = pixel / W;
+            float y = (1.f - ((float)i + 0.5f) * invHeight) * 2.f - 1.f;
+            float x = (((float)j + 0.5f) * invWidth) * 2.f - 1.f;
+            v3 averageRadiance = V(0.f);
+            for (int sidx = 0; sidx < s->spp; sidx++) {
+                float px, py;
+                if (s->spp == 1) { px = x * angle * aspectRatio; py = y * angle; }
+                else {
+                    float rx, ry; sampler.next2D(&rx, &ry);
+                    rx -= 0.5f; ry -= 0.5f; rx = rx * invWidth; ry = ry * invHeight;
+                    px = (x + rx) * angle * aspectRatio; py = (y + ry) * angle;
+                }
+                float ip[4] = {px, py, -1.f, 0.f}, d4[4];
+                mulv(cameraToWorld, ip, d4);
+                Ray ray(s->cam_o, normalize(V(d4[0], d4[1], d4[2])), 1.f, 1000.f);
+                averageRadiance = averageRadiance + bdpt.render(ray, sampler);
+            }
+            fbs[tid][pixel] = fbs[tid][pixel] + averageRadiance * (1.f / s->spp);
+        }
+    };
+    std::vector<std::thread> pool;
+    for (int t = 1; t < threads; t++) pool.emplace_back(work, t);
+    work(0);
+    for (auto& t : pool) t.join();
+    auto t1 = std::chrono::high_resolution_clock::now();
+    if (rgb_out) {
+        for (int p = 0; p < np; p++) {
+            v3 a = V(0.f);
+            for (int t = 0; t < threads; t++) a = a + fbs[t][p];
+            rgb_out[3 * p] = a.x; rgb_out[3 * p + 1] = a.y; rgb_out[3 * p + 2] = a.z;
+        }
+    }
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+}  // extern "C"
