@@ -54,7 +54,8 @@ class Stats(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_trace_closest", C.c_double), ("ms_trace_any", C.c_double),
                 ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
                 ("rays_any", C.c_uint64), ("launches", C.c_uint64), ("node_visits", C.c_uint64),
-                ("tri_tests", C.c_uint64), ("node_visits_any", C.c_uint64), ("tri_tests_any", C.c_uint64)]
+                ("tri_tests", C.c_uint64), ("node_visits_any", C.c_uint64), ("tri_tests_any", C.c_uint64),
+                ("retraces", C.c_uint64), ("retraces_any", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}

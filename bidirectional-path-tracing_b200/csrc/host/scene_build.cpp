@@ -258,6 +258,8 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         const RefTree::Node& r = tree.nodes[nd.right];
         for (int k = 0; k < 3; ++k) { d.c0min[k] = l.bmin[k]; d.c0max[k] = l.bmax[k]; d.c1min[k] = r.bmin[k]; d.c1max[k] = r.bmax[k]; }
         d.ref0 = make_ref(nd.left); d.ref1 = make_ref(nd.right); d.pad0 = d.pad1 = 0;
+        // the traversal kernel postpones sibling leaves as ONE contiguous triangle range (trace_warp.cuh)
+        if (l.left < 0 && r.left < 0 && r.start != l.start + l.count) { err = "sibling leaves are not adjacent in the primitive order"; return false; }
     }
     out.root_ref = make_ref(0);
     for (int k = 0; k < 3; ++k) { out.scene_min[k] = tree.nodes[0].bmin[k]; out.scene_max[k] = tree.nodes[0].bmax[k]; }

@@ -72,7 +72,7 @@ struct WaveParams {
     uint32_t shadow_cap;
 };
 
-enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_LIVE = 2, CTR_SPARE = 3, CTR_N = 8 };
+enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_LIVE = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 5, CTR_N = 8 };
 enum : uint32_t { SLOT_PURE_SPECULAR = 1u };
 
 // ---- random numbers ----------------------------------------------------------------------------------

@@ -14,50 +14,7 @@ namespace trbk {
 
 __device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref}; }
 
-// ---- generic traversal kernels (also behind trb_trace_closest / trb_trace_any) --------------------------
-__global__ void __launch_bounds__(TRB_BLOCK) k_trace_closest(SceneDev sc, const RayT* __restrict__ rays, const int32_t* __restrict__ q,
-                                                              const uint32_t* __restrict__ n_ptr, uint32_t n_fixed, HitT* __restrict__ hits,
-                                                              unsigned long long* __restrict__ visit_counters) {
-    uint32_t n = n_ptr ? *n_ptr : n_fixed;
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        int32_t i = q ? q[k] : int32_t(k);
-        RayT r = rays[i];
-        HitT h; bool occ;
-#ifdef TRB_COUNTERS
-        uint32_t nn = 0, nt = 0;
-        trace_ray<false>(bvh_of(sc), r, &h, &occ, &nn, &nt);
-        if (visit_counters) { atomicAdd(visit_counters, (unsigned long long)nn); atomicAdd(visit_counters + 1, (unsigned long long)nt); }
-#else
-        trace_ray<false>(bvh_of(sc), r, &h, &occ, nullptr, nullptr);
-#endif
-        hits[i] = h;
-    }
-}
-
-// occlusion query; either writes the flag (ABI) or resolves the pending contribution with atomics
-__global__ void __launch_bounds__(TRB_BLOCK) k_trace_any(SceneDev sc, const RayT* __restrict__ rays, const uint32_t* __restrict__ n_ptr,
-                                                          uint32_t n_fixed, uint32_t cap, uint8_t* __restrict__ occ_out,
-                                                          const Pending* __restrict__ pend, float* __restrict__ accum,
-                                                          unsigned long long* __restrict__ visit_counters) {
-    uint32_t n = n_ptr ? min(*n_ptr, cap) : n_fixed;
-    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
-        RayT r = rays[k];
-        HitT h; bool occ;
-#ifdef TRB_COUNTERS
-        uint32_t nn = 0, nt = 0;
-        trace_ray<true>(bvh_of(sc), r, &h, &occ, &nn, &nt);
-        if (visit_counters) { atomicAdd(visit_counters, (unsigned long long)nn); atomicAdd(visit_counters + 1, (unsigned long long)nt); }
-#else
-        trace_ray<true>(bvh_of(sc), r, &h, &occ, nullptr, nullptr);
-#endif
-        if (occ_out) occ_out[k] = occ ? 1 : 0;
-        if (pend && !occ) {
-            Pending pd = pend[k];
-            float* a = accum + size_t(pd.target) * 3;
-            atomicAdd(a, pd.r); atomicAdd(a + 1, pd.g); atomicAdd(a + 2, pd.b);  // replaces g_FrameBufferLocks (bdpt.h:360-370)
-        }
-    }
-}
+// (the traversal kernels live in trace_warp.cuh)
 
 // ---- camera rays (renderer.cpp:161-192) ------------------------------------------------------------------
 __global__ void __launch_bounds__(TRB_BLOCK) k_gen_camera(const __grid_constant__ WaveParams p) {

@@ -68,9 +68,11 @@ TRB_HD int32_t f2i(float f) {
 #define TRB_LDG4(p) __ldg(reinterpret_cast<const float4*>(p))
 TRB_HD F4 ld4(const F4* p) { float4 v = TRB_LDG4(p); return F4{v.x, v.y, v.z, v.w}; }
 TRB_HD float fdiv(float a, float b) { return __fdiv_rn(a, b); }
+TRB_HD float frcp(float a) { return __frcp_rn(a); }  // RN(1/a): the same value as fdiv(1.f, a), cheaper sequence
 #else
 TRB_HD F4 ld4(const F4* p) { return *p; }
 TRB_HD float fdiv(float a, float b) { return a / b; }
+TRB_HD float frcp(float a) { return 1.f / a; }
 #endif
 
 // BBox::intersect verbatim in behaviour (bvh.h:33-69), returning also the clipped interval for ordering.
@@ -100,45 +102,68 @@ struct RayPre {
 
 TRB_HD RayPre ray_pre(const RayT& r) {
     RayPre p;
-    p.ix = fdiv(1.f, r.dx); p.iy = fdiv(1.f, r.dy); p.iz = fdiv(1.f, r.dz);
+    p.ix = frcp(r.dx); p.iy = frcp(r.dy); p.iz = frcp(r.dz);
     float s = (p.ix - p.ix) + (p.iy - p.iy) + (p.iz - p.iz);  // NaN unless all finite
     p.degenerate = !(s == 0.f);
     return p;
 }
 
 // Decides one child box the way the reference does; enter/exit are the (approximate) line parameters.
+// The reference misses iff some CROSS-axis pair has tmin_i > tmax_j (bvh.h:33-69); the same-axis pair never
+// decides.  Three tiers: (1) the clipped interval [en, ex] is clearly non-empty / clearly empty; (2) it is
+// empty-or-touching only because one axis binds both ends (flat boxes: every axis-aligned wall of the Cornell
+// box) - then the six cross-axis gaps decide; (3) a cross-axis gap is within a few ulp: the reference's own six
+// IEEE divisions are redone (box_exact).
 TRB_HD bool box_test(const float* bmin, const float* bmax, const RayT& r, const RayPre& p, float* enter, float* exit_) {
     if (!p.degenerate) {
         float ax = (bmin[0] - r.ox) * p.ix, bx = (bmax[0] - r.ox) * p.ix;
         float ay = (bmin[1] - r.oy) * p.iy, by = (bmax[1] - r.oy) * p.iy;
         float az = (bmin[2] - r.oz) * p.iz, bz = (bmax[2] - r.oz) * p.iz;
-        float en = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-        float ex = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        float nx = fminf(ax, bx), ny = fminf(ay, by), nz = fminf(az, bz);
+        float xx = fmaxf(ax, bx), xy = fmaxf(ay, by), xz = fmaxf(az, bz);
+        float en = fmaxf(fmaxf(nx, ny), nz);
+        float ex = fminf(fminf(xx, xy), xz);
         float gap = ex - en;
         float tol = 6e-7f * fmaxf(fabsf(en), fabsf(ex)) + 1e-30f;
         if (gap > tol) { *enter = en; *exit_ = ex; return true; }
         if (gap < -tol) return false;
+        float g = fminf(fminf(fminf(xy - nx, xz - nx), fminf(xx - ny, xz - ny)), fminf(xx - nz, xy - nz));
+        tol = tol + tol;
+        if (g > tol) { *enter = en; *exit_ = ex; return true; }
+        if (g < -tol) return false;
     }
     return box_exact(bmin, bmax, r, enter, exit_);
 }
 
 // rayTriangleIntersect (core.h:379-400) + the t > 1e-3 acceptance of accel.h:43, same operation order.
 // `ill` is set when the candidate is numerically ill-conditioned (see file header).
+// The IEEE division 1/det is only paid by candidates that survive sign/magnitude pre-rejects which are strictly
+// weaker than the reference's own tests on u and v (a pre-reject fires only where uu < 0, uu > 1, vv < 0 or
+// uu + vv > 1 is certain for ANY rounding of the two multiplications), so accepted hits and their (t,u,v) are
+// bit-identical to computing invDet first.
 TRB_HD bool tri_test(const F4& q0, const F4& q1, const F4& q2, const RayT& r, float* t, float* u, float* v, bool* ill) {
     // pvec = cross(d, v0v2)
     float px = r.dy * q2.z - q2.y * r.dz, py = r.dz * q2.x - q2.z * r.dx, pz = r.dx * q2.y - q2.x * r.dy;
     float det = (q1.x * px + q1.y * py) + q1.z * pz;
-    if (fabsf(det) < 1e-8f) return false;
-    float invDet = fdiv(1.f, det);
+    float adet = fabsf(det);
+    if (adet < 1e-8f) return false;
     float tx = r.ox - q0.x, ty = r.oy - q0.y, tz = r.oz - q0.z;
-    float uu = ((tx * px + ty * py) + tz * pz) * invDet;
-    if (uu < 0 || uu > 1) return false;
+    float un = (tx * px + ty * py) + tz * pz;
+    const bool guard = adet <= 1e10f;           // keeps un * (1/det) away from underflow in the sign argument
+    float s_un = det < 0.f ? -un : un;          // un * sign(det), exact
+    if (guard && (s_un <= -1e-30f || s_un > adet * 1.000001f)) return false;  // uu < 0 or uu > 1 for certain
     // qvec = cross(tvec, v0v1)
     float qx = ty * q1.z - q1.y * tz, qy = tz * q1.x - q1.z * tx, qz = tx * q1.y - q1.x * ty;
-    float vv = ((r.dx * qx + r.dy * qy) + r.dz * qz) * invDet;
+    float vn = (r.dx * qx + r.dy * qy) + r.dz * qz;
+    float s_vn = det < 0.f ? -vn : vn;
+    if (guard && (s_vn <= -1e-30f || (s_un + s_vn) > adet * 1.000002f)) return false;  // vv < 0 or uu + vv > 1 for certain
+    float invDet = frcp(det);
+    float uu = un * invDet;
+    if (uu < 0 || uu > 1) return false;
+    float vv = vn * invDet;
     if (vv < 0 || uu + vv > 1) return false;
     float tt = ((q2.x * qx + q2.y * qy) + q2.z * qz) * invDet;
-    // conditioning: |det| against |e1||e2||d| (grazing) and |n.tvec| against |tvec| (origin in the plane)
+    // conditioning: |det| against |e1||e2||d| (grazing)
     float e1 = (q1.x * q1.x + q1.y * q1.y) + q1.z * q1.z, e2 = (q2.x * q2.x + q2.y * q2.y) + q2.z * q2.z;
     float dd = (r.dx * r.dx + r.dy * r.dy) + r.dz * r.dz;
     if (det * det < 1e-6f * e1 * e2 * dd) *ill = true;

@@ -11,6 +11,7 @@
 #include "../../include/trb.h"
 #include "host/tr_host.h"
 #include "kernels/bdpt_kernels.cuh"
+#include "kernels/trace_warp.cuh"
 
 using namespace trbk;
 
@@ -63,6 +64,7 @@ struct trb_context {
     DevBuf<int32_t> nlv, q_a, q_b;
     DevBuf<Pending> spend;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
+    DevBuf<uint32_t> fetch_ctr;          // queue cursor of the stand-alone trace entry points
     DevBuf<unsigned long long> d_stats;  // [0] closest rays, [1] any rays, [2] node visits, [3] tri tests
     DevBuf<float> fb;                    // frame buffer W*H*3
     // scratch for the parity entry points
@@ -104,6 +106,28 @@ inline int grid_for(size_t n, int sm_count) {
     return int(std::max<size_t>(1, std::min(blocks, cap)));
 }
 inline int grid_exact(size_t n) { return int(std::max<size_t>(1, (n + TRB_BLOCK - 1) / TRB_BLOCK)); }
+
+// persistent traversal grid: one wave of resident warps per SM (64 registers/thread -> 8 blocks of 128 per SM)
+inline int trace_grid(int sm_count) { return sm_count * 8; }
+
+// `fetch` is the launch's own queue cursor; the caller has zeroed it on the stream
+void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, HitT* hits,
+                    uint32_t* fetch, unsigned long long* visit) {
+    TraceArgs a{};
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = fetch;
+    a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
+    k_trace_warp<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+}
+
+void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t cap, uint8_t* occ_out,
+                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit) {
+    TraceArgs a{};
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.rays = rays; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
+    a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
+    k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+}
 
 int ensure_wave(trb_context* c, size_t P, int K) {
     size_t kk = size_t(std::max(K, 1));
@@ -173,7 +197,7 @@ void trb_destroy(trb_context* c) {
     c->d_etris.release(); c->d_cdf.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->spend.release();
-    c->counters.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
+    c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
     if (c->pinned) cudaFreeHost(c->pinned);
     for (auto ev : c->events) cudaEventDestroy(ev);
     cudaStreamDestroy(c->stream);
@@ -281,10 +305,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     int32_t* qa = c->q_a.p; int32_t* qb = c->q_b.p;
     auto stage_ctr = [&](int s) { return c->counters.p + size_t(s) * CTR_N; };
     const int gP = grid_exact(size_t(P));
-    const int gS = grid_for(size_t(P), sm);
 
     k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
-    k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, visit); c->mark(LK_CLOSEST);
+    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, stage_ctr(2 * kk + 2) + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
     // light subpath
     int stage = 0;
     p.counters = stage_ctr(stage); p.q_out = qa;
@@ -295,9 +318,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.q_out = (stage % 2 == 0) ? qb : qa;
         ++stage;
         p.counters = stage_ctr(stage);
-        k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST);
+        launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
         k_light_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
-        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit ? visit + 2 : nullptr);
+        launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY, visit ? visit + 2 : nullptr);
         c->mark(LK_ANY);
     }
     // eye subpath
@@ -311,9 +334,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.q_out = even ? qb : qa;
         ++stage;
         p.counters = stage_ctr(stage);
-        if (depth > 1) { k_trace_closest<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.ray, p.q_in, n_in, 0u, p.hit, visit); c->mark(LK_CLOSEST); }
+        if (depth > 1) { launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST); }
         k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
-        k_trace_any<<<gS, TRB_BLOCK, 0, c->stream>>>(p.sc, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, visit ? visit + 2 : nullptr);
+        launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY, visit ? visit + 2 : nullptr);
         c->mark(LK_ANY);
     }
     k_fold_stats<<<1, 32, 0, c->stream>>>(c->counters.p, n_stage, kk, kk, uint32_t(P), c->d_stats.p, p.shadow_cap); c->mark(LK_LOGIC);
@@ -334,7 +357,7 @@ void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
     unsigned long long h[8] = {0};
     cudaMemcpyAsync(h, c->d_stats.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream);
     cudaStreamSynchronize(c->stream);
-    st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5];
+    st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5]; st->retraces = h[6]; st->retraces_any = h[7];
     st->launches = c->launches;
     double ms[LK_N] = {0, 0, 0};
     for (size_t i = 1; i < c->n_events; ++i) {
@@ -456,15 +479,16 @@ int trace_device(trb_context* c, bool any, const RayT* d_rays, size_t n, HitT* d
     cudaSetDevice(c->device);
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (ms_out) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, c->stream); }
-    const int g = grid_for(n, c->prop.multiProcessorCount);
     unsigned long long* visit = nullptr;
 #ifdef TRB_COUNTERS
     TRB_CUDA(c, c->d_stats.alloc(8));
     visit = c->d_stats.p + 2;
 #endif
     if (n) {
-        if (any) k_trace_any<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, visit ? visit + 2 : nullptr);
-        else k_trace_closest<<<g, TRB_BLOCK, 0, c->stream>>>(c->sc, d_rays, nullptr, nullptr, uint32_t(n), d_hits, visit);
+        TRB_CUDA(c, c->fetch_ctr.alloc(1));
+        TRB_CUDA(c, cudaMemsetAsync(c->fetch_ctr.p, 0, sizeof(uint32_t), c->stream));
+        if (any) launch_any(c, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, c->fetch_ctr.p, visit ? visit + 2 : nullptr);
+        else launch_closest(c, d_rays, nullptr, nullptr, uint32_t(n), d_hits, c->fetch_ctr.p, visit);
     }
     ++c->launches;
     if (ms_out) { cudaEventRecord(e1, c->stream); }

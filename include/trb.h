@@ -115,6 +115,8 @@ typedef struct trb_stats {
     uint64_t tri_tests;
     uint64_t node_visits_any; /* occlusion rays; TRB_COUNTERS builds only                */
     uint64_t tri_tests_any;
+    uint64_t retraces;        /* closest-hit rays re-traced without distance pruning (ill-conditioned candidate met); TRB_COUNTERS only */
+    uint64_t retraces_any;    /* same for occlusion rays */
 } trb_stats;
 
 /* BSDF query in the local shading frame (SurfaceInteraction::{wo,wi}, core.h:173-180) */

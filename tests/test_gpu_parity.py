@@ -95,3 +95,52 @@ def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
     print(f"{scene_name}: paths ok {ok.sum()}/{n}, draws identical {draws_same.sum()}/{n}")
     assert frac >= 0.99, f"only {frac:.4f} of paths within {REL}"
     assert draws_same[ok].all()
+
+
+@pytest.fixture(scope="session")
+def ref_harness(trb):
+    """name -> the UNMODIFIED reference (oracle/_ref/libtr_ref.so, built by oracle/Makefile; it travels to the GPU box)
+    opened on an OBJ re-export of the committed scene fixture (nothing under /root/reference is read)."""
+    import tempfile
+    from pathlib import Path
+    refh = pytest.importorskip("refh")
+    if not refh.available():
+        pytest.skip("oracle/_ref/libtr_ref.so not built")
+    import scene_to_obj
+    cache = {}
+
+    def get(name):
+        if name not in cache:
+            scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{name}.npz")
+            obj = scene_to_obj.export_verified(scene, Path(tempfile.mkdtemp(prefix="trb_t_")) / "scene.obj")
+            cache[name] = (refh.RefHarness.open_scene(obj, width=64, height=64, spp=1, rr_depth=8), scene)
+        return cache[name]
+    yield get
+    for rh, _ in cache.values():
+        rh.close()
+
+
+def test_trace_million_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
+    """SURVEY 8(c) level 1 at size: >= 10^6 seeded rays per scene (camera, random surface rays, visibility segments,
+    axis-parallel rays) through the persistent-warp kernels vs AcceleratorBVH::intersect / BVH::getIntersection of the
+    reference itself: ids and (t,u,v) bit-exact, occlusion flags exact."""
+    import dev_rays
+    rh, scene = ref_harness(scene_name)
+    rng = np.random.default_rng(20261105)
+    n = 330_000
+    cam = dev_rays.camera_rays(trb.camera_matrices(trb.render_desc(width=640, height=480)), (0.0, 0.8, 3.8), 30.0, 640, 480)
+    rays = np.concatenate([cam, dev_rays.random_dir_rays(scene, n, rng), dev_rays.segment_rays(scene, n, rng)[0],
+                           dev_rays.axis_rays(scene, 40_000, rng)])
+    assert len(rays) >= 1_000_000
+    ids, tuv, _ = rh.intersect(rays)
+    occ_ref = rh.occluded(rays)
+    base = np.concatenate([[0], np.cumsum(np.bincount(scene.tri_shape, minlength=scene.n_shapes))])
+    tri_ref = np.where(ids[:, 0] == 1, base[np.clip(ids[:, 1], 0, None)] + ids[:, 2], -1).astype(np.int32)
+    ctx = gpu_ctx(scene_name)
+    h = ctx.trace_closest(_rays(trb, rays))
+    assert np.array_equal(h["hit"], ids[:, 0].astype(np.int32))
+    assert np.array_equal(h["tri"], tri_ref)
+    m = ids[:, 0] == 1
+    for k, f in enumerate(("t", "u", "v")):
+        assert np.array_equal(h[f][m].view(np.uint32), tuv[m, k].view(np.uint32)), f
+    assert np.array_equal(ctx.trace_any(_rays(trb, rays)), occ_ref)
