@@ -76,23 +76,28 @@ TRB_HD float frcp(float a) { return 1.f / a; }
 #endif
 
 // BBox::intersect verbatim in behaviour (bvh.h:33-69), returning also the clipped interval for ordering.
-// NaN comparisons are false exactly as in the reference.
-TRB_HD_NOINLINE bool box_exact(const float* bmin, const float* bmax, const RayT& r, float* enter, float* exit_) {
-    float tmin = fdiv(bmin[0] - r.ox, r.dx), tmax = fdiv(bmax[0] - r.ox, r.dx);
+// NaN comparisons are false exactly as in the reference.  Everything by value: pointer arguments to a
+// non-inlined function would force the caller's boxes into local memory.
+struct BoxR { float enter, exit_; bool hit; };
+TRB_HD_NOINLINE BoxR box_exact(float mnx, float mny, float mnz, float mxx, float mxy, float mxz,
+                               float ox, float oy, float oz, float dx, float dy, float dz) {
+    BoxR o; o.enter = 0.f; o.exit_ = 0.f; o.hit = false;
+    float tmin = fdiv(mnx - ox, dx), tmax = fdiv(mxx - ox, dx);
     if (tmin > tmax) { float s = tmin; tmin = tmax; tmax = s; }
-    float tymin = fdiv(bmin[1] - r.oy, r.dy), tymax = fdiv(bmax[1] - r.oy, r.dy);
+    float tymin = fdiv(mny - oy, dy), tymax = fdiv(mxy - oy, dy);
     if (tymin > tymax) { float s = tymin; tymin = tymax; tymax = s; }
-    if ((tmin > tymax) || (tymin > tmax)) return false;
+    if ((tmin > tymax) || (tymin > tmax)) return o;
     if (tymin > tmin) tmin = tymin;
     if (tymax < tmax) tmax = tymax;
-    float tzmin = fdiv(bmin[2] - r.oz, r.dz), tzmax = fdiv(bmax[2] - r.oz, r.dz);
+    float tzmin = fdiv(mnz - oz, dz), tzmax = fdiv(mxz - oz, dz);
     if (tzmin > tzmax) { float s = tzmin; tzmin = tzmax; tzmax = s; }
-    if ((tmin > tzmax) || (tzmin > tmax)) return false;
+    if ((tmin > tzmax) || (tzmin > tmax)) return o;
     if (tzmin > tmin) tmin = tzmin;
     if (tzmax < tmax) tmax = tzmax;
-    *enter = (tmin == tmin) ? tmin : -INFINITY;   // NaN -> never prune
-    *exit_ = (tmax == tmax) ? tmax : INFINITY;
-    return true;
+    o.enter = (tmin == tmin) ? tmin : -INFINITY;   // NaN -> never prune
+    o.exit_ = (tmax == tmax) ? tmax : INFINITY;
+    o.hit = true;
+    return o;
 }
 
 struct RayPre {
@@ -110,29 +115,45 @@ TRB_HD RayPre ray_pre(const RayT& r) {
 
 // Decides one child box the way the reference does; enter/exit are the (approximate) line parameters.
 // The reference misses iff some CROSS-axis pair has tmin_i > tmax_j (bvh.h:33-69); the same-axis pair never
-// decides.  Three tiers: (1) the clipped interval [en, ex] is clearly non-empty / clearly empty; (2) it is
-// empty-or-touching only because one axis binds both ends (flat boxes: every axis-aligned wall of the Cornell
-// box) - then the six cross-axis gaps decide; (3) a cross-axis gap is within a few ulp: the reference's own six
-// IEEE divisions are redone (box_exact).
-TRB_HD bool box_test(const float* bmin, const float* bmax, const RayT& r, const RayPre& p, float* enter, float* exit_) {
+// decides.  Three tiers: (1) box_fast: the clipped interval [en, ex] is clearly non-empty / clearly empty -
+// straight-line code, no branch, so that the two child tests of a node stay converged; (2) box_slow: the
+// interval is empty-or-touching only because one axis binds both ends (flat boxes: every axis-aligned wall of
+// the Cornell box) - then the six cross-axis gaps decide; (3) a cross-axis gap is within a few ulp, or the
+// direction has a zero / non-finite component: the reference's own six IEEE divisions are redone (box_exact).
+struct BoxF { float en, ex, nx, ny, nz, xx, xy, xz, tol; bool pass, undecided; };
+TRB_HD BoxF box_fast(float mnx, float mny, float mnz, float mxx, float mxy, float mxz, const RayT& r, const RayPre& p) {
+    BoxF f;
+    float ax = (mnx - r.ox) * p.ix, bx = (mxx - r.ox) * p.ix;
+    float ay = (mny - r.oy) * p.iy, by = (mxy - r.oy) * p.iy;
+    float az = (mnz - r.oz) * p.iz, bz = (mxz - r.oz) * p.iz;
+    f.nx = fminf(ax, bx); f.ny = fminf(ay, by); f.nz = fminf(az, bz);
+    f.xx = fmaxf(ax, bx); f.xy = fmaxf(ay, by); f.xz = fmaxf(az, bz);
+    f.en = fmaxf(fmaxf(f.nx, f.ny), f.nz);
+    f.ex = fminf(fminf(f.xx, f.xy), f.xz);
+    float gap = f.ex - f.en;
+    f.tol = 6e-7f * fmaxf(fabsf(f.en), fabsf(f.ex)) + 1e-30f;
+    f.pass = gap > f.tol;
+    f.undecided = p.degenerate || !(f.pass || gap < -f.tol);
+    return f;
+}
+// tiers 2 and 3 for an undecided box; updates en/ex when the exact test supplies them
+TRB_HD bool box_slow(float mnx, float mny, float mnz, float mxx, float mxy, float mxz, const RayT& r, const RayPre& p, BoxF& f) {
     if (!p.degenerate) {
-        float ax = (bmin[0] - r.ox) * p.ix, bx = (bmax[0] - r.ox) * p.ix;
-        float ay = (bmin[1] - r.oy) * p.iy, by = (bmax[1] - r.oy) * p.iy;
-        float az = (bmin[2] - r.oz) * p.iz, bz = (bmax[2] - r.oz) * p.iz;
-        float nx = fminf(ax, bx), ny = fminf(ay, by), nz = fminf(az, bz);
-        float xx = fmaxf(ax, bx), xy = fmaxf(ay, by), xz = fmaxf(az, bz);
-        float en = fmaxf(fmaxf(nx, ny), nz);
-        float ex = fminf(fminf(xx, xy), xz);
-        float gap = ex - en;
-        float tol = 6e-7f * fmaxf(fabsf(en), fabsf(ex)) + 1e-30f;
-        if (gap > tol) { *enter = en; *exit_ = ex; return true; }
-        if (gap < -tol) return false;
-        float g = fminf(fminf(fminf(xy - nx, xz - nx), fminf(xx - ny, xz - ny)), fminf(xx - nz, xy - nz));
-        tol = tol + tol;
-        if (g > tol) { *enter = en; *exit_ = ex; return true; }
+        float g = fminf(fminf(fminf(f.xy - f.nx, f.xz - f.nx), fminf(f.xx - f.ny, f.xz - f.ny)), fminf(f.xx - f.nz, f.xy - f.nz));
+        float tol = f.tol + f.tol;
+        if (g > tol) return true;
         if (g < -tol) return false;
     }
-    return box_exact(bmin, bmax, r, enter, exit_);
+    BoxR e = box_exact(mnx, mny, mnz, mxx, mxy, mxz, r.ox, r.oy, r.oz, r.dx, r.dy, r.dz);
+    f.en = e.enter; f.ex = e.exit_;
+    return e.hit;
+}
+TRB_HD bool box_test(const float* bmin, const float* bmax, const RayT& r, const RayPre& p, float* enter, float* exit_) {
+    BoxF f = box_fast(bmin[0], bmin[1], bmin[2], bmax[0], bmax[1], bmax[2], r, p);
+    bool hit = f.pass;
+    if (f.undecided) hit = box_slow(bmin[0], bmin[1], bmin[2], bmax[0], bmax[1], bmax[2], r, p, f);
+    *enter = f.en; *exit_ = f.ex;
+    return hit;
 }
 
 // rayTriangleIntersect (core.h:379-400) + the t > 1e-3 acceptance of accel.h:43, same operation order.

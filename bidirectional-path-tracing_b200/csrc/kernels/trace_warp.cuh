@@ -48,7 +48,7 @@ struct TraceArgs {
 };
 
 template <bool ANY>
-__global__ void __launch_bounds__(TRB_TRACE_BLOCK) k_trace_warp(const TraceArgs a) {
+__global__ void __launch_bounds__(TRB_TRACE_BLOCK, 8) k_trace_warp(const TraceArgs a) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -136,11 +136,15 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK) k_trace_warp(const TraceArgs 
 #ifdef TRB_COUNTERS
             ++c_nodes;
 #endif
-            const float c0min[3] = {na.x, na.y, na.z}, c0max[3] = {na.w, nb.x, nb.y};
-            const float c1min[3] = {nb.z, nb.w, nc.x}, c1max[3] = {nc.y, nc.z, nc.w};
-            float e0, x0, e1, x1;
-            bool h0 = box_test(c0min, c0max, r, pre, &e0, &x0);
-            bool h1 = box_test(c1min, c1max, r, pre, &e1, &x1);
+            // both child tests as straight-line code; the rare undecided box takes the slow tiers afterwards
+            BoxF f0 = box_fast(na.x, na.y, na.z, na.w, nb.x, nb.y, r, pre);
+            BoxF f1 = box_fast(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, r, pre);
+            bool h0 = f0.pass, h1 = f1.pass;
+            if (f0.undecided || f1.undecided) {
+                if (f0.undecided) h0 = box_slow(na.x, na.y, na.z, na.w, nb.x, nb.y, r, pre, f0);
+                if (f1.undecided) h1 = box_slow(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, r, pre, f1);
+            }
+            const float e0 = f0.en, x0 = f0.ex, e1 = f1.en, x1 = f1.ex;
             if (!exh) {
                 const float best = ANY ? r.max_t : h.t;
                 const float lim = best + 1e-3f * (1.f + fabsf(best));
