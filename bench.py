@@ -202,6 +202,7 @@ def run_ours(args):
     import torch
     import torch.distributed as dist
     trb = importlib.import_module(PKG)
+    par = importlib.import_module(PKG + ".parallel")
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     wl = WORKLOADS[args.workload]
@@ -213,8 +214,9 @@ def run_ours(args):
     ctx.upload(scene)
     W, H = wl["width"], wl["height"]
     total_spp = args.spp * world
-    desc = trb.render_desc(width=W, height=H, spp=total_spp, rr_depth=wl["rr_depth"], spp_begin=rank * args.spp,
-                           spp_end=(rank + 1) * args.spp, wave_samples=args.wave)
+    s_begin, s_end = par.sample_range(total_spp, rank, world)  # shard by sample index
+    desc = trb.render_desc(width=W, height=H, spp=total_spp, rr_depth=wl["rr_depth"], spp_begin=s_begin, spp_end=s_end,
+                           wave_samples=args.wave)
     if args._visits:
         _, st = ctx.render_bdpt(desc, download=False)
         print(json.dumps({k: int(st[k]) for k in ("rays_closest", "rays_any", "node_visits", "tri_tests", "node_visits_any", "tri_tests_any", "samples")}))
@@ -237,7 +239,7 @@ def run_ours(args):
         ms = st["ms_total"]
         if world > 1:
             ev0.record()
-            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
+            par.reduce_framebuffer(fb, dst=0)  # the one collective of the render
             ev1.record()
             torch.cuda.synchronize()
             ms += ev0.elapsed_time(ev1)

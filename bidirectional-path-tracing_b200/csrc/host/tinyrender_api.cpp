@@ -1,0 +1,322 @@
+// tinyrender_api.cpp -- TinyRender's C++ host API (include/tinyrender/tinyrender.h) on top of the C ABI.
+// Host logic only: every computation goes through trb_* (include/trb.h) to the GPU.
+#include "../../../include/tinyrender/tinyrender.h"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <thread>
+
+#include "tr_host.h"
+
+namespace TinyRender {
+
+namespace {
+trb_render_desc make_desc(const Config& c) {
+    trb_render_desc d;
+    std::memset(&d, 0, sizeof(d));
+    d.eye[0] = c.camera.o.x; d.eye[1] = c.camera.o.y; d.eye[2] = c.camera.o.z;
+    d.at[0] = c.camera.at.x; d.at[1] = c.camera.at.y; d.at[2] = c.camera.at.z;
+    d.up[0] = c.camera.up.x; d.up[1] = c.camera.up.y; d.up[2] = c.camera.up.z;
+    d.fov_deg = c.camera.fov;
+    d.width = c.width; d.height = c.height; d.spp = c.spp;
+    d.rr_depth = c.integratorSettings.bdpt.rrDepth;
+    d.seed = c.seed; d.wave_samples = c.waveSamples;
+    return d;
+}
+trb_ray to_ray(const Ray& r) {
+    trb_ray o;
+    o.o[0] = r.o.x; o.o[1] = r.o.y; o.o[2] = r.o.z; o.d[0] = r.d.x; o.d[1] = r.d.y; o.d[2] = r.d.z;
+    o.min_t = r.min_t; o.max_t = r.max_t;
+    return o;
+}
+}  // namespace
+
+// ---- loadTOML (main.cpp:22-116) ---------------------------------------------------------------------------
+bool loadTOML(Config& config, const std::string& inputFile) {
+    trb::TomlConfig t;
+    std::string err;
+    if (!trb::load_toml(inputFile, t, err)) throw std::runtime_error(err);
+    config.tomlFile = inputFile;
+    config.objFile = t.obj_path;
+    config.camera.o = v3f(t.desc.eye[0], t.desc.eye[1], t.desc.eye[2]);
+    config.camera.at = v3f(t.desc.at[0], t.desc.at[1], t.desc.at[2]);
+    config.camera.up = v3f(t.desc.up[0], t.desc.up[1], t.desc.up[2]);
+    config.camera.fov = t.desc.fov_deg;
+    config.width = t.desc.width; config.height = t.desc.height; config.spp = t.desc.spp;
+    config.seed = t.desc.seed; config.waveSamples = t.desc.wave_samples; config.gpus = t.gpus;
+    static const char* known[] = {"normal", "simple", "ao", "ro", "direct", "path", "bdpt"};
+    static const EIntegrator ids[] = {ENormalIntegrator, ESimpleIntegrator, EAOIntegrator, EROIntegrator, EDirectIntegrator,
+                                      EPathTracerIntegrator, EBDPTIntegrator};
+    bool found = false;
+    for (int k = 0; k < 7; ++k) if (t.type == known[k]) { config.integrator = ids[k]; found = true; }
+    if (!found && !t.realtime) throw std::runtime_error("Invalid integrator type");  // main.cpp:109
+    config.integratorSettings.bdpt.rrDepth = t.desc.rr_depth;
+    return t.realtime;
+}
+
+// ---- Scene (renderer.cpp:235-315) -------------------------------------------------------------------------
+Scene::Scene(const Config& c) : config(c) {}
+
+Scene::~Scene() {
+    for (trb_context* c : ctx) if (c) trb_destroy(c);
+    if (host) trb_host_scene_free(host);
+}
+
+const trb_scene_desc* Scene::desc() const { return host ? &sdesc : nullptr; }
+
+trb_context* Scene::context(int device) const {
+    if (device < 0) return nullptr;
+    if (size_t(device) >= ctx.size()) ctx.resize(size_t(device) + 1, nullptr);
+    if (!ctx[device]) {
+        trb_context* c = nullptr;
+        if (trb_create(device, &c) != TRB_OK) { err = trb_last_error(nullptr); return nullptr; }
+        if (host && trb_scene_upload(c, &sdesc) != TRB_OK) { err = trb_last_error(c); trb_destroy(c); return nullptr; }
+        ctx[device] = c;
+    }
+    return ctx[device];
+}
+
+bool Scene::load(bool isRealTime) {
+    if (isRealTime) { err = "the realtime (OpenGL) passes are not available: no graphics stack on this platform"; std::printf("%s\n", err.c_str()); return false; }
+    if (trb_host_load_obj(config.objFile.c_str(), &host) != TRB_OK) { err = trb_host_last_error(); std::printf("%s\n", err.c_str()); return false; }
+    trb_host_scene_desc(host, &sdesc);
+    nShapes = sdesc.n_shapes; nTriangles = sdesc.n_tris;
+    // BSDF class by illum (renderer.cpp:259-271)
+    bsdfs.clear();
+    for (size_t i = 0; i < sdesc.n_materials; ++i) {
+        const trb_material& m = sdesc.materials[i];
+        std::unique_ptr<BSDF> b;
+        switch (m.illum) {
+            case 7: b.reset(new DiffuseBSDF(*this, i)); b->combinedType = BSDF::EDiffuseReflection; break;
+            case 3: b.reset(new MirrorBSDF(*this, i)); b->combinedType = BSDF::EDeltaReflection; break;
+            case 6: b.reset(new GlassBSDF(*this, i)); b->combinedType = BSDF::EDeltaReflection | BSDF::EDeltaTransmission; break;
+            case 8: b.reset(new MixtureBSDF(*this, i)); b->combinedType = BSDF::EGlossyReflection | BSDF::EDiffuseReflection; break;
+            case 5: err = "illum 5: the reference builds no BSDF for it (renderer.cpp:259-270)"; std::printf("%s\n", err.c_str()); return false;
+            default: b.reset(new PhongBSDF(*this, i)); b->combinedType = BSDF::EGlossyReflection | BSDF::EDiffuseReflection; break;
+        }
+        b->emissive = m.ke[0] != 0.f || m.ke[1] != 0.f || m.ke[2] != 0.f;
+        bsdfs.push_back(std::move(b));
+    }
+    // emitters (renderer.cpp:279-305)
+    {
+        std::vector<int32_t> shape(64);
+        std::vector<float> area(64), rad(64 * 3), cdf(sdesc.n_tris + 128);
+        int n = trb_host_emitters(&sdesc, shape.data(), area.data(), rad.data(), 64, cdf.data(), cdf.size());
+        if (n < 0) { err = trb_host_last_error(); std::printf("%s\n", err.c_str()); return false; }
+        emitters.clear();
+        size_t off = 0;
+        std::vector<size_t> faces(sdesc.n_shapes, 0);
+        for (size_t t = 0; t < sdesc.n_tris; ++t) ++faces[sdesc.tri_shape[t]];
+        for (int e = 0; e < n; ++e) {
+            Emitter em;
+            em.shapeID = size_t(shape[e]); em.area = area[e]; em.radiance = v3f(rad[3 * e], rad[3 * e + 1], rad[3 * e + 2]);
+            size_t nf = faces[em.shapeID] + 1;
+            em.faceAreaCdf.assign(cdf.begin() + off, cdf.begin() + off + nf);
+            off += nf;
+            emitters.push_back(std::move(em));
+        }
+    }
+    for (int k = 0; k < 3; ++k) { aabb.min[k] = 3.4e38f; aabb.max[k] = -3.4e38f; }
+    for (size_t v = 0; v < sdesc.n_positions; ++v)
+        for (int k = 0; k < 3; ++k) { aabb.min[k] = std::fmin(aabb.min[k], sdesc.positions[3 * v + k]); aabb.max[k] = std::fmax(aabb.max[k], sdesc.positions[3 * v + k]); }
+    std::printf("Found %zu shapes, %zu triangles, %zu emitters\n", nShapes, nTriangles, emitters.size());
+    // AcceleratorBVH::build (accel.h:115-123) + device upload: fails loudly without a GPU
+    if (!context(0)) { std::printf("%s\n", err.c_str()); return false; }
+    bvh.reset(new AcceleratorBVH(*this));
+    return true;
+}
+
+// ---- AcceleratorBVH (accel.h:113-172) -----------------------------------------------------------------------
+bool AcceleratorBVH::build() { return scene.context(0) != nullptr; }
+
+bool AcceleratorBVH::intersectBatch(const trb_ray* rays, size_t n, trb_hit* out) const {
+    trb_context* c = scene.context(0);
+    return c && trb_trace_closest(c, rays, n, out) == TRB_OK;
+}
+bool AcceleratorBVH::occludedBatch(const trb_ray* rays, size_t n, uint8_t* out) const {
+    trb_context* c = scene.context(0);
+    return c && trb_trace_any(c, rays, n, out) == TRB_OK;
+}
+bool AcceleratorBVH::occluded(const Ray& ray) const {
+    trb_ray r = to_ray(ray);
+    uint8_t o = 0;
+    return occludedBatch(&r, 1, &o) && o != 0;
+}
+
+namespace {
+// host copies of the few fp32 expressions that fill SurfaceInteraction after a hit (accel.h:136-166, math.h:19-22,42-51)
+struct F3 { float x, y, z; };
+inline F3 bary3(const float* a, const float* b, const float* c, float u, float v) {
+    float w = 1 - u - v;
+    return {(a[0] * w + b[0] * u) + c[0] * v, (a[1] * w + b[1] * u) + c[1] * v, (a[2] * w + b[2] * u) + c[2] * v};
+}
+inline float dot3(F3 a, F3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
+inline F3 cross3(F3 x, F3 y) { return {x.y * y.z - y.y * x.z, x.z * y.x - y.z * x.x, x.x * y.y - y.x * x.y}; }
+}  // namespace
+
+bool AcceleratorBVH::intersect(const Ray& ray, SurfaceInteraction& info, bool) const {
+    trb_ray r = to_ray(ray);
+    trb_hit h;
+    if (!intersectBatch(&r, 1, &h)) return false;
+    info.t = h.t;
+    if (!h.hit) return false;
+    const trb_scene_desc& s = *scene.desc();
+    const int32_t* tv = s.tri_v + 3 * size_t(h.tri);
+    const int32_t* tn = s.tri_n + 3 * size_t(h.tri);
+    F3 p = bary3(s.positions + 3 * tv[0], s.positions + 3 * tv[1], s.positions + 3 * tv[2], h.u, h.v);
+    F3 n = bary3(s.normals + 3 * tn[0], s.normals + 3 * tn[1], s.normals + 3 * tn[2], h.u, h.v);
+    float inv = 1.f / std::sqrt(dot3(n, n));
+    n = {n.x * inv, n.y * inv, n.z * inv};
+    F3 t;  // coordinateSystem (math.h:42-51)
+    if (std::fabs(n.x) > std::fabs(n.y)) { float il = 1.f / std::sqrt(n.x * n.x + n.z * n.z); t = {n.z * il, 0.f, -n.x * il}; }
+    else { float il = 1.f / std::sqrt(n.y * n.y + n.z * n.z); t = {0.f, n.z * il, -n.y * il}; }
+    F3 sdir = cross3(t, n);
+    F3 md = {-ray.d.x, -ray.d.y, -ray.d.z};
+    info.p = v3f(p.x, p.y, p.z);
+    info.wo = v3f(dot3(md, sdir), dot3(md, t), dot3(md, n));
+    info.u = h.u; info.v = h.v;
+    info.shapeID = size_t(h.shape); info.primID = size_t(h.prim);
+    info.matID = s.tri_mat[h.tri];
+    return true;
+}
+
+// ---- BSDF (core.h:256-318) ------------------------------------------------------------------------------------
+bool BSDF::evalBatch(const trb_bsdf_query* q, size_t n, trb_bsdf_out* out) const {
+    trb_context* c = scene.context(0);
+    return c && trb_bsdf_batch(c, q, n, out) == TRB_OK;
+}
+namespace {
+trb_bsdf_out bsdf_one(const BSDF& b, const SurfaceInteraction& i, const v2f& u) {
+    trb_bsdf_query q;
+    std::memset(&q, 0, sizeof(q));
+    q.wo[0] = i.wo.x; q.wo[1] = i.wo.y; q.wo[2] = i.wo.z; q.wi[0] = i.wi.x; q.wi[1] = i.wi.y; q.wi[2] = i.wi.z;
+    q.u[0] = u.x; q.u[1] = u.y; q.mat = int32_t(b.matID);
+    trb_bsdf_out o;
+    std::memset(&o, 0, sizeof(o));
+    if (!b.evalBatch(&q, 1, &o)) throw std::runtime_error("BSDF: device evaluation failed (no CPU fallback)");
+    return o;
+}
+}  // namespace
+v3f BSDF::eval(const SurfaceInteraction& i) const { trb_bsdf_out o = bsdf_one(*this, i, v2f()); return v3f(o.eval[0], o.eval[1], o.eval[2]); }
+float BSDF::pdf(const SurfaceInteraction& i) const { return bsdf_one(*this, i, v2f()).pdf; }
+v3f BSDF::sample(SurfaceInteraction& i, const v2f& s, float* pdf) const {
+    trb_bsdf_out o = bsdf_one(*this, i, s);
+    i.wi = v3f(o.sample_wi[0], o.sample_wi[1], o.sample_wi[2]);
+    if (pdf) *pdf = o.sample_pdf;
+    return v3f(o.sample_val[0], o.sample_val[1], o.sample_val[2]);
+}
+
+// ---- Integrator (integrator.cpp:16-30) ----------------------------------------------------------------------
+bool Integrator::init() {
+    rgb.reset(new RenderBuffer(scene.config.width, scene.config.height));
+    rgb->clear();
+    return true;
+}
+
+bool Integrator::save() {
+    std::string out = scene.config.tomlFile;
+    size_t dot = out.find_last_of('.');
+    size_t slash = out.find_last_of('/');
+    if (dot != std::string::npos && (slash == std::string::npos || dot > slash)) out = out.substr(0, dot);
+    out += ".exr";
+    static_assert(sizeof(v3f) == 12, "RenderBuffer must be packed RGB floats");
+    if (trb_host_save_exr(out.c_str(), reinterpret_cast<const float*>(rgb->data.get()), rgb->width, rgb->height) != TRB_OK) {
+        std::printf("%s\n", trb_host_last_error());
+        return false;
+    }
+    std::printf("Saved EXR image to %s\n", out.c_str());
+    return true;
+}
+
+// ---- BDPTIntegrator (bdpt.h:37-518) ---------------------------------------------------------------------------
+BDPTIntegrator::BDPTIntegrator(const Scene& s) : Integrator(s) {
+    m_rrDepth = s.config.integratorSettings.bdpt.rrDepth;  // bdpt.h:38-43
+    m_rrProb = s.config.integratorSettings.bdpt.rrProb;
+}
+
+v3f BDPTIntegrator::render(const Ray& ray, Sampler& sampler) const {
+    trb_context* c = scene.context(0);
+    if (!c) throw std::runtime_error("BDPTIntegrator::render: no device context");
+    trb_render_desc d = make_desc(scene.config);
+    const int K = std::max(m_rrDepth - 1, 1);
+    const size_t stride = size_t(10 + 10 * K);
+    // the path consumes a prefix of the sampler's stream: feed a copy's numbers, then advance the real sampler
+    Sampler ahead = sampler;
+    std::vector<float> rng(stride);
+    for (float& f : rng) f = ahead.next();
+    trb_ray r = to_ray(ray);
+    float li[3] = {0, 0, 0};
+    std::vector<int32_t> pix(size_t(K), -1);
+    std::vector<float> srgb(size_t(K) * 3, 0.f);
+    int32_t draws = 0;
+    if (trb_bdpt_paths(c, &d, &r, rng.data(), 1, stride, li, pix.data(), srgb.data(), &draws) != TRB_OK)
+        throw std::runtime_error(std::string("BDPTIntegrator::render: ") + trb_last_error(c));
+    for (int k = 0; k < draws; ++k) sampler.next();
+    if (rgb) {  // light-tracing splats land in the frame buffer as a side effect (bdpt.h:360-370)
+        for (int k = 0; k < K; ++k)
+            if (pix[k] >= 0 && pix[k] < rgb->width * rgb->height) rgb->data[pix[k]] += v3f(srgb[3 * k], srgb[3 * k + 1], srgb[3 * k + 2]);
+    }
+    return v3f(li[0], li[1], li[2]);
+}
+
+bool BDPTIntegrator::renderFrame() {
+    const Config& cfg = scene.config;
+    const int G = std::max(1, std::min(cfg.gpus, cfg.spp));
+    trb_render_desc base = make_desc(cfg);
+    const size_t nf = size_t(cfg.width) * cfg.height * 3;
+    float* out = reinterpret_cast<float*>(rgb->data.get());
+    if (G == 1) {
+        trb_context* c = scene.context(0);
+        if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
+        if (trb_render_bdpt(c, &base, 0, out, &lastStats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
+        return true;
+    }
+    // sample-index sharding over G devices of this process: replicated scene, disjoint RNG streams, partial frame
+    // buffers are plain summands (contributions are normalised by the total spp).  One host thread per device.
+    std::vector<std::vector<float>> part;
+    part.assign(size_t(G), std::vector<float>(nf));
+    std::vector<int> rc;
+    rc.assign(size_t(G), 0);
+    std::vector<trb_context*> cs;
+    cs.assign(size_t(G), nullptr);
+    for (int g = 0; g < G; ++g) { cs[g] = scene.context(g); if (!cs[g]) { std::printf("%s\n", scene.error().c_str()); return false; } }
+    std::vector<std::thread> th;
+    for (int g = 0; g < G; ++g) {
+        th.emplace_back([&, g]() {
+            trb_render_desc d = base;
+            d.spp_begin = int32_t(int64_t(cfg.spp) * g / G);
+            d.spp_end = int32_t(int64_t(cfg.spp) * (g + 1) / G);
+            rc[g] = trb_render_bdpt(cs[g], &d, 0, part[g].data(), g == 0 ? &lastStats : nullptr);
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int g = 0; g < G; ++g) if (rc[g] != TRB_OK) { std::printf("%s\n", trb_last_error(cs[g])); return false; }
+    for (size_t i = 0; i < nf; ++i) { float s = 0.f; for (int g = 0; g < G; ++g) s += part[g][i]; out[i] = s; }
+    return true;
+}
+
+// ---- Renderer (renderer.cpp:53-227) ---------------------------------------------------------------------------
+Renderer::Renderer(const Config& config) : scene(config) {}
+
+bool Renderer::init(bool isRealTime, bool nogui_) {
+    realTime = isRealTime; nogui = nogui_;
+    if (!scene.load(isRealTime)) return false;
+    if (scene.config.integrator != EBDPTIntegrator) {
+        std::printf("Only the BDPT integrator is hosted on the B200 path (renderer.type = \"bdpt\")\n");
+        return false;
+    }
+    integrator.reset(new BDPTIntegrator(scene));
+    return integrator->init();
+}
+
+void Renderer::render() {
+    if (!integrator) return;
+    if (!integrator->renderFrame()) throw std::runtime_error("Renderer::render: device render failed");
+}
+
+void Renderer::cleanUp() {
+    if (integrator) integrator->cleanUp();
+}
+
+}  // namespace TinyRender

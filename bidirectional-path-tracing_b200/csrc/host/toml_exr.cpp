@@ -8,6 +8,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <fstream>
 #include <map>
@@ -181,7 +182,9 @@ bool load_toml(const std::string& path, TomlConfig& out, std::string& err) {
     out.desc.spp = get_int(ren, "spp", 1);            // main.cpp:112
     out.desc.spp_begin = 0; out.desc.spp_end = 0;
     out.desc.seed = uint32_t(get_int(ren, "seed", 260450963));  // renderer.cpp:155 (extension key)
-    out.desc.flags = 0; out.desc.wave_samples = 0;
+    out.desc.flags = 0;
+    out.desc.wave_samples = get_int(ren, "waveSamples", 0);  // extension keys: samples per wavefront, devices
+    out.gpus = std::max(1, get_int(ren, "gpus", 1));
     return true;
 }
 

@@ -137,6 +137,7 @@ struct TomlConfig {
     trb_render_desc desc;
     std::string obj_path, type;
     bool realtime = false;
+    int gpus = 1;
 };
 bool load_toml(const std::string& path, TomlConfig& out, std::string& err);
 bool save_exr_bgr_half(const std::string& path, const float* rgb, int w, int h, std::string& err);

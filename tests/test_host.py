@@ -3,6 +3,8 @@ replacements.  No GPU needed."""
 import ctypes
 import os
 import re
+import sys
+from pathlib import Path
 
 import numpy as np
 import pytest
@@ -138,3 +140,38 @@ def test_reference_loader_parity_if_available(trb):
         assert np.array_equal(getattr(hs, k), d[k]), k
     assert np.array_equal(hs.bvh_order(), rh.bvh_order())
     rh.close()
+
+
+def test_cpp_host_api_compiles_and_fails_loudly_without_gpu(trb, tmp_path):
+    """include/tinyrender/tinyrender.h is self-contained C++17, the CLI keeps the reference's syntax (main.cpp:160-171)
+    and - on a box without a CUDA device - stops at Renderer::init instead of falling back to any CPU path."""
+    import subprocess
+    import torch
+    root = Path(__file__).resolve().parent.parent
+    pkg = root / "bidirectional-path-tracing_b200"
+    src = tmp_path / "t.cpp"
+    src.write_text('#include "tinyrender/tinyrender.h"\n#include <cstdio>\nint main(int c, char** v) { TinyRender::Config cfg;\n'
+                   ' try { TinyRender::loadTOML(cfg, v[1]); } catch (const std::runtime_error& e) { std::printf("EXC %s\\n", e.what()); return 7; }\n'
+                   ' std::printf("%d %d %d %d %s\\n", cfg.width, cfg.height, cfg.spp, cfg.integratorSettings.bdpt.rrDepth, cfg.objFile.c_str()); return 0; }\n')
+    sys.path.insert(0, str(pkg))
+    import build as trb_build
+    exe = tmp_path / "t"
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Werror", "-I", str(root / "include"), str(src), "-o", str(exe), "-L", str(pkg), "-l:libtrb.so",
+                    f"-Wl,-rpath,{pkg}", *trb_build._stdcxx_link_args(), "-lm"], check=True)
+    toml = tmp_path / "s.toml"
+    body = ('[input]\nobjfile = "m/x.obj"\n[camera]\neye = [ 0.0, 0.8, 3.8 ]\nat = [ 0.0, 0.8, 0.0 ]\nup = [ 0.0, 1.0, 0.0 ]\nfov = 30.0\n'
+            '[film]\nwidth = 80\nheight = 60\n[renderer]\nrealtime = false\ntype = "%s"\nrrDepth = 7\nspp = 3\n')
+    toml.write_text(body % "bdpt")
+    r = subprocess.run([str(exe), str(toml)], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.split()[:4] == ["80", "60", "3", "7"] and r.stdout.strip().endswith("m/x.obj")
+    toml.write_text(body % "nonsense")
+    r = subprocess.run([str(exe), str(toml)], capture_output=True, text=True)
+    assert r.returncode == 7 and "Invalid integrator type" in r.stdout  # main.cpp:109
+    cli = pkg / "tinyrender_b200"
+    assert cli.exists()
+    r = subprocess.run([str(cli)], capture_output=True, text=True)
+    assert r.returncode != 0 and "Syntax" in r.stderr
+    if not torch.cuda.is_available():
+        toml.write_text(body % "bdpt")
+        r = subprocess.run([str(cli), str(toml), "nogui"], capture_output=True, text=True)
+        assert r.returncode != 0  # missing OBJ / no device: never a silent CPU render

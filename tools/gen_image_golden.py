@@ -1,0 +1,41 @@
+"""tools/gen_image_golden.py -- level-3 pins: the reference's own shipped converged renders
+(data/a5/**/tinyrender/*.exr, 800x600 half-float B,G,R), box-filtered 8x8 to 100x75 RGB float32 so that they can
+be committed as small fixtures (tests/golden/image_<name>.npz).  Only the goldens that the CURRENT reference code
+reproduces are used: cbox_bdpt_glass_{5,8}depth.exr <=> rrDepth 5/8 on cbox_mirror.obj and
+cbox_bdpt_final.exr <=> rrDepth 8 on bonus_bdpt/mesh/cbox.obj.  Needs /root/reference; run in the build container."""
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+import cv2  # noqa: E402
+
+ROOT = Path(__file__).resolve().parent.parent
+REF = Path(os.environ.get("TRB_REFERENCE", "/root/reference"))
+PINS = {
+    "caustic_rr5": ("data/a5/cbox/tinyrender/cbox_bdpt_glass_5depth.exr", "caustic", 5),
+    "caustic_rr8": ("data/a5/cbox/tinyrender/cbox_bdpt_glass_8depth.exr", "caustic", 8),
+    "hardlight_rr8": ("data/a5/bonus_bdpt/tinyrender/cbox_bdpt_final.exr", "hardlight", 8),
+}
+BOX = 8
+
+
+def box_filter(img, k=BOX):
+    h, w, c = img.shape
+    return img.reshape(h // k, k, w // k, k, c).astype(np.float64).mean((1, 3)).astype(np.float32)
+
+
+def main():
+    for name, (rel, scene, rr) in PINS.items():
+        bgr = cv2.imread(str(REF / rel), cv2.IMREAD_UNCHANGED)
+        assert bgr is not None and bgr.shape == (600, 800, 3), rel
+        rgb = bgr[:, :, ::-1].astype(np.float32)
+        np.savez_compressed(ROOT / "tests" / "golden" / f"image_{name}.npz", image=box_filter(rgb), scene=scene, rr_depth=rr,
+                            width=800, height=600, box=BOX, source=rel, mean=np.float64(rgb.mean()))
+        print(name, rel, "mean", rgb.mean())
+
+
+if __name__ == "__main__":
+    sys.exit(main())
