@@ -34,6 +34,17 @@ struct alignas(16) LightVertex {
     float tx, ty, tz, pad;
 };
 
+// Eye vertex handed from k_eye_bounce to k_connect_vertices (same 64 B shape as LightVertex; `target` is the
+// accumulation slot of the sample: its pixel, or its Li slot in parity mode)
+struct alignas(16) EyeVertex {
+    float px, py, pz, vcm;
+    float nx, ny, nz, vc;
+    float wox, woy, woz;
+    int32_t mat;
+    float tx, ty, tz;
+    uint32_t target;
+};
+
 struct WaveParams {
     SceneDev sc;
     trb::CameraDev cam;
@@ -66,13 +77,15 @@ struct WaveParams {
     int32_t* nlv;         // P
     int32_t* q_in;        // P   live slots entering this bounce
     int32_t* q_out;       // P   live slots leaving it
+    EyeVertex* ev;        // P   eye vertex of the current bounce (connecting slots only)
+    int32_t* q_conn;      // P   slots whose eye vertex connects this bounce (non-delta, not an emitter)
     uint32_t* counters;   // [0]=q_out count, [1]=shadow count, [2]=closest rays traced, [3]=any rays traced
     RayT* sray;           // shadow capacity
     Pending* spend;       // shadow capacity
     uint32_t shadow_cap;
 };
 
-enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_LIVE = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 5, CTR_N = 8 };
+enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_CONN = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 5, CTR_N = 8 };
 enum : uint32_t { SLOT_PURE_SPECULAR = 1u };
 
 // ---- random numbers ----------------------------------------------------------------------------------

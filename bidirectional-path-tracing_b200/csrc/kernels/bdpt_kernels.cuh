@@ -353,43 +353,18 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_bounce(const __grid_constant_
         }
         push_shadow(p, want, sr, Li, li_target);
     }
-    // ---- connectVertices (bdpt.h:434-483) against every stored light vertex of this sample ----
+    // ---- connectVertices (bdpt.h:434-483): handed to k_connect_vertices, one thread per (eye vertex, light vertex) ----
     {
-        int nl = connect ? p.nlv[slot] : 0;
-        int nmax = __reduce_max_sync(0xffffffffu, nl);
-        for (int j = 0; j < nmax; ++j) {
-            bool want = false; RayT sr; V3 Li = mk(0.f);
-            if (j < nl) {
-                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(j) * p.P + slot);
-                float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
-                V3 lpnt = mk(a.x, a.y, a.z);
-                V3 l2e = s.p - lpnt;
-                float invD2 = 1.f / length2(l2e);
-                l2e = l2e * sqrtf(invD2);
-                Frame lf = make_frame(mk(b.x, b.y, b.z));
-                V3 l_wo = mk(c.x, c.y, c.z);
-                V3 l_wi = to_local(lf, l2e);
-                V3 e_wi = to_local(s.f, -l2e);
-                float cosL = l_wi.z, cosE = e_wi.z;
-                if (!(cosL <= 0.f || cosE <= 0.f)) {
-                    Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
-                    Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, s.wo, e_wi);
-                    Li = Li * (mk(d.x, d.y, d.z) * T * invD2);
-                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * 1.f;
-                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * 1.f;
-                    float lightRevW = bsdf_pdf(m, s.wo, e_wi) * 1.f;
-                    float eyePrevRevW = bsdf_pdf(m, e_wi, s.wo) * 1.f;
-                    float lightRevA = lightRevW * (cosL) * invD2;
-                    float eyeRevA = eyeRevW * (cosE) * invD2;
-                    float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);
-                    float eyeWeight = eyeRevA * (vcm + eyePrevRevW * vc);
-                    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
-                    Li = Li * mis;
-                    Li = Li * li_scale;
-                    if (!is_zero(Li)) { sr = visibility_ray(s.p, lpnt); want = true; }
-                }
-            }
-            push_shadow(p, want, sr, Li, li_target);
+        const bool conn = connect && p.nlv[slot] > 0;
+        uint32_t ci = queue_push(p.counters + CTR_CONN, conn);
+        if (conn) {
+            p.q_conn[ci] = slot;
+            EyeVertex e;
+            e.px = s.p.x; e.py = s.p.y; e.pz = s.p.z; e.vcm = vcm;
+            e.nx = s.n.x; e.ny = s.n.y; e.nz = s.n.z; e.vc = vc;
+            e.wox = s.wo.x; e.woy = s.wo.y; e.woz = s.wo.z; e.mat = s.mat;
+            e.tx = T.x; e.ty = T.y; e.tz = T.z; e.target = li_target;
+            p.ev[slot] = e;
         }
     }
     if (in) {
@@ -412,6 +387,59 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_bounce(const __grid_constant_
     }
     uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
     if (go) p.q_out[idx] = slot;
+}
+
+// ---- connectVertices (bdpt.h:434-483): one thread per (connecting eye vertex k, light vertex j), j-major so that
+// the lanes of a warp share j and read consecutive queue entries.  Replaces the per-thread loop over the sample's
+// light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). -------------------------------
+__global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_conn_ptr) {
+    const uint32_t nc = *n_conn_ptr;
+    const unsigned long long total = (unsigned long long)nc * uint32_t(p.K);
+    const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballot of push_shadow
+    const float li_scale = p.parity ? 1.f : (1.f / p.spp);
+    for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total_w; t += (unsigned long long)gridDim.x * blockDim.x) {
+        bool want = false; RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
+        if (t < total) {
+            const uint32_t j = uint32_t(t / nc), k = uint32_t(t - (unsigned long long)j * nc);
+            const int slot = p.q_conn[k];
+            if (int(j) < p.nlv[slot]) {
+                const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
+                float4 ea = ep[0], eb = ep[1], ec = ep[2], ed = ep[3];
+                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(j) * p.P + slot);
+                float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
+                target = __float_as_uint(ed.w);
+                V3 epnt = mk(ea.x, ea.y, ea.z), lpnt = mk(a.x, a.y, a.z);
+                V3 l2e = epnt - lpnt;
+                float invD2 = 1.f / length2(l2e);
+                l2e = l2e * sqrtf(invD2);
+                Frame lf = make_frame(mk(b.x, b.y, b.z));
+                Frame ef = make_frame(mk(eb.x, eb.y, eb.z));
+                V3 l_wo = mk(c.x, c.y, c.z), e_wo = mk(ec.x, ec.y, ec.z);
+                V3 l_wi = to_local(lf, l2e);
+                V3 e_wi = to_local(ef, -l2e);
+                float cosL = l_wi.z, cosE = e_wi.z;
+                if (!(cosL <= 0.f || cosE <= 0.f)) {
+                    Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
+                    Mat m = load_mat(p.sc.mats, __float_as_int(ec.w));
+                    Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
+                    Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
+                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * 1.f;
+                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * 1.f;
+                    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * 1.f;
+                    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * 1.f;
+                    float lightRevA = lightRevW * (cosL) * invD2;
+                    float eyeRevA = eyeRevW * (cosE) * invD2;
+                    float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);
+                    float eyeWeight = eyeRevA * (ea.w + eyePrevRevW * eb.w);
+                    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
+                    Li = Li * mis;
+                    Li = Li * li_scale;
+                    if (!is_zero(Li)) { sr = visibility_ray(epnt, lpnt); want = true; }
+                }
+            }
+        }
+        push_shadow(p, want, sr, Li, target);
+    }
 }
 
 }  // namespace trbk

@@ -4,8 +4,12 @@
 //   MixtureBSDF  src/bsdfs/mixture.h:60-151     MirrorBSDF  src/bsdfs/perfectmirror.h:33-59
 //   GlassBSDF    src/bsdfs/glass.h:40-108       Warp::*     src/core/math.h:118-268
 // Operation order follows the C++ expressions so that, with -fmad=false, only the transcendental
-// functions can differ from the x86-64 build; those go through fp64 (TRB_EXACT_TRANSCENDENTALS) so that the
-// fp32 result is the correctly rounded one glibc returns in all but ~1e-8 of the cases.
+// functions can differ from the x86-64 build.  Where a transcendental decides a DIRECTION (sampling: sin/cos of the
+// azimuth, the pow of the Phong-lobe polar angle) it goes through fp64 (TRB_EXACT_TRANSCENDENTALS) so that the fp32
+// result is the correctly rounded one glibc returns in all but ~1e-8 of the cases - a path through the glass sphere
+// amplifies a 1-ulp direction error by orders of magnitude.  Where it only scales a VALUE (the Phong lobe in
+// eval / pdf: six pow per vertex connection) CUDA's fp32 powf (<= 4 ulp, 5e-7 relative, against the 1e-5 parity
+// tolerance) is used: the fp64 pow was 52 % of k_eye_bounce's instructions (profiles/r1e_ncu_lines_k_eye_bounce.txt).
 #pragma once
 #include "../host/tr_host.h"
 #include "vec.cuh"
@@ -20,7 +24,9 @@ namespace trbk {
 __device__ __forceinline__ float t_sinf(float x) { return (float)sin((double)x); }
 __device__ __forceinline__ float t_cosf(float x) { return (float)cos((double)x); }
 __device__ __forceinline__ float t_powf(float x, float y) { return (float)pow((double)x, (double)y); }
+__device__ __forceinline__ float v_powf(float x, float y) { return powf(x, y); }  // value-only uses
 #else
+__device__ __forceinline__ float v_powf(float x, float y) { return powf(x, y); }
 __device__ __forceinline__ float t_sinf(float x) { return sinf(x); }
 __device__ __forceinline__ float t_cosf(float x) { return cosf(x); }
 __device__ __forceinline__ float t_powf(float x, float y) { return powf(x, y); }
@@ -83,7 +89,7 @@ __device__ __forceinline__ V3 sq_to_phong_lobe(float ux, float uy, float exponen
 }
 
 __device__ __forceinline__ float phong_lobe_pdf(V3 v, float exponent) {  // math.h:221-227
-    return v.z >= 0.f ? (exponent + 2) * TRB_INV_TWOPI * t_powf(v.z, exponent) : 0.f;
+    return v.z >= 0.f ? (exponent + 2) * TRB_INV_TWOPI * v_powf(v.z, exponent) : 0.f;
 }
 
 // ---- eval / pdf / sample ---------------------------------------------------------------------------
@@ -93,7 +99,7 @@ __device__ __forceinline__ V3 glossy_eval(const Mat& m, V3 wo, V3 wi) {  // phon
         val = val + m.kd * TRB_INV_PI;
         float e = m.ns;
         float cosTheta = fminf(fmaxf(dot(wi, reflect_z(wo)), 0.f), 1.f);
-        val = val + m.ks * (e + 2) * TRB_INV_TWOPI * t_powf(cosTheta, e);
+        val = val + m.ks * (e + 2) * TRB_INV_TWOPI * v_powf(cosTheta, e);
         val = val * m.scale;
         val = val * wi.z;
     }

@@ -61,7 +61,8 @@ struct trb_context {
     DevBuf<HitT> hit, hit0;
     DevBuf<float4> st_t, st_v;
     DevBuf<LightVertex> lv;
-    DevBuf<int32_t> nlv, q_a, q_b;
+    DevBuf<int32_t> nlv, q_a, q_b, q_conn;
+    DevBuf<EyeVertex> ev;
     DevBuf<Pending> spend;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
     DevBuf<uint32_t> fetch_ctr;          // queue cursor of the stand-alone trace entry points
@@ -136,7 +137,7 @@ int ensure_wave(trb_context* c, size_t P, int K) {
     TRB_CUDA(c, c->hit.alloc(P)); TRB_CUDA(c, c->hit0.alloc(P));
     TRB_CUDA(c, c->st_t.alloc(P)); TRB_CUDA(c, c->st_v.alloc(P));
     TRB_CUDA(c, c->lv.alloc(P * kk)); TRB_CUDA(c, c->nlv.alloc(P));
-    TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P));
+    TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P)); TRB_CUDA(c, c->ev.alloc(P));
     TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
     TRB_CUDA(c, c->d_stats.alloc(8));
@@ -196,7 +197,7 @@ void trb_destroy(trb_context* c) {
     c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
     c->d_etris.release(); c->d_cdf.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
-    c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->spend.release();
+    c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->q_conn.release(); c->ev.release(); c->spend.release();
     c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
     if (c->pinned) cudaFreeHost(c->pinned);
     for (auto ev : c->events) cudaEventDestroy(ev);
@@ -294,7 +295,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
     p.accum = w.d_accum; p.splat_pix = w.d_splat_pix;
     p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
-    p.lv = c->lv.p; p.nlv = c->nlv.p; p.sray = c->sray.p; p.spend = c->spend.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p; p.q_conn = c->q_conn.p; p.sray = c->sray.p; p.spend = c->spend.p;
     p.shadow_cap = uint32_t(std::min<size_t>(c->sray.n, 0xffffffffu));
     const int n_stage = 2 * kk + 4;
     TRB_CUDA(c, cudaMemsetAsync(c->counters.p, 0, size_t(n_stage) * CTR_N * sizeof(uint32_t), c->stream));
@@ -335,7 +336,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         ++stage;
         p.counters = stage_ctr(stage);
         if (depth > 1) { launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST); }
-        k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
+        k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in);
+        k_connect_vertices<<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN); c->mark(LK_LOGIC);
+        ++c->launches;
         launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY, visit ? visit + 2 : nullptr);
         c->mark(LK_ANY);
     }
