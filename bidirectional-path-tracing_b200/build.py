@@ -69,13 +69,16 @@ def _digest(paths: list[Path], extra: str) -> str:
     return h.hexdigest()
 
 
-def build(force: bool = False, counters: bool = False, verbose: bool = False) -> Path:
-    """Compile everything that is out of date; returns the path of libtrb.so."""
+def build(force: bool = False, counters: bool = False, verbose: bool = False, variant: str = "", defines: tuple = ()) -> Path:
+    """Compile everything that is out of date; returns the path of libtrb.so.
+    variant/defines: tuning experiments - the same sources with extra -D flags into libtrb_<variant>.so (use with TRB_LIB=...)."""
     OBJ.mkdir(exist_ok=True)
     lib_out = LIB_COUNTERS if counters else LIB
     sfx = "_cnt" if counters else ""
+    if variant:
+        lib_out, sfx = PKG / f"libtrb_{variant}.so", "_" + variant
     deps = [p for p in CSRC.rglob("*") if p.suffix in (".cu", ".cuh", ".cpp", ".h")] + [ROOT / "include" / "trb.h"]
-    tag = _digest(deps, "counters" if counters else "plain")
+    tag = _digest(deps, ("counters" if counters else "plain") + variant + " ".join(defines))
     stamp = OBJ / f"stamp{sfx}.txt"
     if not force and lib_out.exists() and stamp.exists() and stamp.read_text() == tag:
         return lib_out
@@ -89,7 +92,7 @@ def build(force: bool = False, counters: bool = False, verbose: bool = False) ->
         if not (CSRC / src).exists():
             continue
         o = OBJ / (Path(src).stem + sfx + ".o")
-        flags = list(NVCC_FLAGS) + (["-DTRB_COUNTERS=1"] if counters else [])
+        flags = list(NVCC_FLAGS) + (["-DTRB_COUNTERS=1"] if counters else []) + list(defines)
         _run([nvcc, *flags, "-I", str(ROOT / "include"), "-c", str(CSRC / src), "-o", str(o)], log=OBJ / (Path(src).stem + sfx + ".ptxas.log"))
         objs.append(str(o))
     have_cuda = any((CSRC / s).exists() for s in CUDA_SRCS)
@@ -98,7 +101,7 @@ def build(force: bool = False, counters: bool = False, verbose: bool = False) ->
         cuda_lib = Path(nvcc).resolve().parent.parent / "lib64"
         link += ["-L", str(cuda_lib), "-lcudart_static", "-ldl", "-lrt"]
     _run(link)
-    if (CSRC / CLI_SRC).exists() and not counters:
+    if (CSRC / CLI_SRC).exists() and not counters and not variant:
         _run(["g++", *CXX_FLAGS, "-I", str(ROOT / "include"), str(CSRC / CLI_SRC), "-o", str(PKG / "tinyrender_b200"),
               "-L", str(PKG), "-l:libtrb.so", "-Wl,-rpath,$ORIGIN", *_stdcxx_link_args(), "-lm"])
     stamp.write_text(tag)
@@ -108,4 +111,8 @@ def build(force: bool = False, counters: bool = False, verbose: bool = False) ->
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose=True)
+    if "--variant" in sys.argv:  # python build.py --variant t4 -DTRB_FETCH_T=4 ...
+        i = sys.argv.index("--variant")
+        build(variant=sys.argv[i + 1], defines=tuple(a for a in sys.argv[i + 2:] if a.startswith("-D")), verbose=True)
+    else:
+        build(force="--force" in sys.argv, counters="--counters" in sys.argv, verbose=True)

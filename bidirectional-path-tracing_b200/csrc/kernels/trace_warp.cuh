@@ -29,7 +29,13 @@
 #define TRB_TRACE_BLOCK 128
 #endif
 
+#ifndef TRB_PREFETCH
+#define TRB_PREFETCH 0       // bit 0: postponed triangles, bit 1: pushed far child
+#endif
+
 namespace trbk {
+
+__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 struct TraceArgs {
     BvhView bvh;
@@ -160,12 +166,19 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, 8) k_trace_warp(const TraceAr
                 const uint32_t cnt = (l0 ? (k0 & 7u) : 0u) + (l1 ? (k1 & 7u) : 0u);
                 const uint32_t e = (first << 4) | cnt;
                 if (npend == 0) p0 = e; else p1 = e;
+#if TRB_PREFETCH & 1
+                prefetch_l1(a.bvh.tris + 3 * size_t(first));  // tested one or more iterations from now
+                if (cnt > 2) prefetch_l1(a.bvh.tris + 3 * size_t(first) + 8);
+#endif
                 ++npend;
             }
             const bool i0 = h0 && r0 >= 0, i1 = h1 && r1 >= 0;
             if (i0 && i1) {
                 const bool swap = !exh && (e1 < e0);  // nearer child first when pruning
                 stack[sp++] = swap ? r0 : r1;
+#if TRB_PREFETCH & 2
+                prefetch_l1(a.bvh.nodes + 4 * size_t(swap ? r0 : r1));  // the far child is popped later
+#endif
                 cur = swap ? r1 : r0;
             } else if (i0) cur = r0;
             else if (i1) cur = r1;
