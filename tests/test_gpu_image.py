@@ -20,9 +20,15 @@ def _box(img, k):
     return img.reshape(h // k, k, w // k, k, c).astype(np.float64).mean((1, 3))
 
 
-@pytest.mark.parametrize("pin", ["caustic_rr5", "caustic_rr8", "hardlight_rr8"])
+# tolerance per pin: box-filtered relMSE.  The shipped hard-light image (cbox_bdpt_final.exr) predates the final code:
+# the unmodified reference at HEAD differs from it by relMSE 5.9e-3 (tools/gen_image_golden.py), so that pin gets 1e-2
+# and the tight hard-light pin is a 96 spp render of the reference itself (image_hardlight_rr8_head.npz).
+PINS = {"caustic_rr5": 2e-3, "caustic_rr8": 2e-3, "hardlight_rr8_head": 2e-3, "hardlight_rr8": 1e-2}
+
+
+@pytest.mark.parametrize("pin", list(PINS))
 def test_image_matches_reference_golden(trb, gpu_ctx, pin):
-    """relMSE of a 128 spp render against the reference's shipped converged EXR (box-filtered 8x8 on both sides)."""
+    """relMSE of a 128 spp render against the reference's converged image (box-filtered 8x8 on both sides)."""
     g = np.load(GOLD / f"image_{pin}.npz")
     ctx = gpu_ctx(str(g["scene"]))
     desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=128, rr_depth=int(g["rr_depth"]))
@@ -31,7 +37,7 @@ def test_image_matches_reference_golden(trb, gpu_ctx, pin):
     rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
     mean_ratio = float(img.mean() / float(g["mean"]))
     print(f"{pin}: relMSE {rel_mse:.2e}, mean ratio {mean_ratio:.4f}, {st['samples'] / st['ms_total'] / 1e3:.1f} Msamples/s")
-    assert rel_mse <= 2e-3, rel_mse          # tolerance of this test: per-block relMSE <= 2e-3
+    assert rel_mse <= PINS[pin], rel_mse
     assert abs(mean_ratio - 1) <= 0.01, mean_ratio
 
 
