@@ -37,6 +37,9 @@ WORKLOADS = {
                     desc="caustic scene (glass sphere + area light, 32536 tris) 1024x1024 BDPT rrDepth 8"),
     "hardlight": dict(scene="scene_hardlight.npz", width=1024, height=1024, rr_depth=16,
                       desc="hard-light scene (occluded emitter, 36404 tris) 1024x1024 BDPT rrDepth 16"),
+    "tess": dict(scene=None, tris=10_000_000, width=1024, height=1024, rr_depth=8,
+                 desc="synthetic tessellated scene (tools/gen_tess_scene.py --tris 10000000 --seed 1: three displaced spheres, mirror/glass/"
+                      "phong + Mixture floor) 1024x1024 BDPT rrDepth 8"),
 }
 METRIC, UNIT = "bdpt_msamples_per_s", "Msamples/s"
 
@@ -95,6 +98,14 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def load_scene(trb, wl, cpu=False):
+    if wl["scene"] is not None:
+        return trb.HostScene.load_npz(GOLD / wl["scene"])
+    import gen_tess_scene
+    # the CPU reference needs one heap object per triangle and a text OBJ: it is timed on a 1 M-triangle instance
+    return gen_tess_scene.make_scene(1_000_000 if cpu else wl["tris"], seed=1)
+
+
 def measured_peak():
     f = ROOT / "MEASURED_PEAKS.json"
     if f.exists():
@@ -113,7 +124,7 @@ def cpu_reference_step_factory(workload: dict, budget_s: float = 8.0):
     import refh
     import scene_to_obj
     trb = importlib.import_module(PKG)
-    scene = trb.HostScene.load_npz(GOLD / workload["scene"])
+    scene = load_scene(trb, workload, cpu=True)
     tmp = Path(tempfile.mkdtemp(prefix="trb_ref_"))
     obj = scene_to_obj.export_verified(scene, tmp / "scene.obj")
     hw = os.cpu_count() or 8
@@ -209,7 +220,7 @@ def run_ours(args):
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    scene = trb.HostScene.load_npz(GOLD / wl["scene"])
+    scene = load_scene(trb, wl)
     ctx = trb.Context(local)
     ctx.upload(scene)
     W, H = wl["width"], wl["height"]

@@ -22,7 +22,7 @@ def trb():
     return importlib.import_module("bidirectional-path-tracing_b200")
 
 
-@pytest.fixture(scope="session", params=["caustic", "hardlight"])
+@pytest.fixture(scope="session", params=["caustic", "hardlight", "tess"])
 def scene_name(request):
     return request.param
 

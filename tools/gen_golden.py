@@ -28,13 +28,29 @@ SCENES = {
     "caustic": (REF / "data/a5/cbox/mesh/cbox_mirror.obj", 8),     # glass sphere, configs C1/C2/C4
     "hardlight": (REF / "data/a5/bonus_bdpt/mesh/cbox.obj", 8),    # occluded emitter, configs C1/C3
 }
+
+
+def _tess_obj():
+    """the synthetic scene of configs[4] at 20 k triangles (tools/gen_tess_scene.py): brings PhongBSDF (illum 2) and
+    MirrorBSDF (illum 3), which no shipped scene uses, under the reference's own pins"""
+    import tempfile
+    import gen_tess_scene
+    import scene_to_obj
+    return scene_to_obj.export_verified(gen_tess_scene.make_scene(20_000, seed=1), Path(tempfile.mkdtemp(prefix="trb_tess_")) / "tess.obj")
+
+
 PATH_W, PATH_H = 96, 72  # small film so the splat scan of the harness stays cheap
 N_TRACE, N_BSDF, N_PATHS, STRIDE = 8000, 1500, 3000, 128
 
 
 def main():
     GOLD.mkdir(parents=True, exist_ok=True)
-    for name, (obj, rr) in SCENES.items():
+    todo = dict(SCENES)
+    if "--only-tess" in sys.argv:
+        todo = {}
+    if "--tess" in sys.argv or "--only-tess" in sys.argv:
+        todo["tess"] = (_tess_obj(), 8)
+    for name, (obj, rr) in todo.items():
         hs = trb.HostScene.load_obj(obj)
         rh = refh.RefHarness.open_scene(obj, width=PATH_W, height=PATH_H, spp=4, rr_depth=rr)
         d = rh.scene_dump()

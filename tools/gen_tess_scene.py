@@ -1,0 +1,136 @@
+"""tools/gen_tess_scene.py -- BASELINE.json configs[4]: the synthetic tessellated-mesh scene (BVH-traversal stress).
+
+Seeded and reproducible; built directly as flat arrays (what tinyobj::LoadObj + Scene::load would hold) so that a
+10 M-triangle instance never has to go through a ~1 GB OBJ text file:
+
+    box   x in [-1,1], y in [0,1.6], z in [-1,1], open towards the camera (as the Cornell scenes), walls illum 7 (diffuse),
+          floor illum 8 (Mixture: Kd .5, Ks .3, Ns 30)
+    light one quad under the ceiling, Ke 35 (the only emitter)
+    three displaced UV-spheres, radius 0.3, n x n tessellation (2 n (n-1) triangles each), smooth vertex normals,
+          displacement = seeded value noise, amplitude 2 % of the radius:
+          left  illum 3 (mirror) | middle illum 6 (glass, Ni 1.5, Tf 1) | right illum 2 (-> PhongBSDF: Ns 50, Kd .3, Ks .6)
+
+    from gen_tess_scene import make_scene;  scene = make_scene(10_000_000, seed=1)     # -> trb.HostScene
+    python tools/gen_tess_scene.py --tris 200000 --seed 1 --out /tmp/tess.npz [--obj /tmp/tess.obj]
+"""
+from __future__ import annotations
+
+import argparse
+import importlib
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+CAMERA = dict(eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0), up=(0.0, 1.0, 0.0), fov=30.0)
+
+
+def _value_noise(p, rng, cells=12):
+    """trilinear value noise with a smoothstep fade on a seeded lattice; p: (N,3) in [-1,1] -> (N,) in [-1,1]"""
+    lat = rng.random((cells + 1, cells + 1, cells + 1)).astype(np.float64) * 2 - 1
+    q = (p * 0.5 + 0.5) * (cells - 1e-6)
+    i = np.floor(q).astype(np.int64)
+    f = q - i
+    f = f * f * (3 - 2 * f)
+    out = np.zeros(len(p))
+    for dx in (0, 1):
+        for dy in (0, 1):
+            for dz in (0, 1):
+                w = (f[:, 0] if dx else 1 - f[:, 0]) * (f[:, 1] if dy else 1 - f[:, 1]) * (f[:, 2] if dz else 1 - f[:, 2])
+                out += w * lat[i[:, 0] + dx, i[:, 1] + dy, i[:, 2] + dz]
+    return out
+
+
+def _sphere(n, center, radius, rng, amp=0.02):
+    """displaced UV sphere: poles are single vertices (fans), n-1 rings of n vertices between them"""
+    th = np.pi * np.arange(1, n) / n                       # ring polar angles
+    ph = 2 * np.pi * np.arange(n) / n
+    T, P = np.meshgrid(th, ph, indexing="ij")
+    unit = np.stack([np.sin(T) * np.cos(P), np.cos(T), np.sin(T) * np.sin(P)], -1).reshape(-1, 3)
+    unit = np.concatenate([[[0.0, 1.0, 0.0]], unit, [[0.0, -1.0, 0.0]]])
+    r = radius * (1 + amp * _value_noise(unit, rng))
+    pos = center + unit * r[:, None]
+    nr = n - 1                                             # rings
+    idx = lambda i, j: 1 + i * n + (j % n)                 # noqa: E731
+    jj = np.arange(n)
+    tris = [np.stack([np.zeros(n, np.int64), idx(0, jj + 1), idx(0, jj)], 1)]            # top fan
+    ii, jg = np.meshgrid(np.arange(nr - 1), jj, indexing="ij")
+    a, b, c, d = idx(ii, jg), idx(ii, jg + 1), idx(ii + 1, jg), idx(ii + 1, jg + 1)
+    tris.append(np.stack([a, b, d], -1).reshape(-1, 3))
+    tris.append(np.stack([a, d, c], -1).reshape(-1, 3))
+    last = 1 + nr * n
+    tris.append(np.stack([np.full(n, last, np.int64), idx(nr - 1, jj), idx(nr - 1, jj + 1)], 1))  # bottom fan
+    tris = np.concatenate(tris)
+    # smooth normals: area-weighted average of the face normals around each vertex
+    fn = np.cross(pos[tris[:, 1]] - pos[tris[:, 0]], pos[tris[:, 2]] - pos[tris[:, 0]])
+    nrm = np.zeros_like(pos)
+    for k in range(3):
+        np.add.at(nrm, tris[:, k], fn)
+    flip = np.sum(nrm * unit, 1) < 0                        # outward
+    nrm[flip] *= -1
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True)
+    return pos.astype(np.float32), nrm.astype(np.float32), tris.astype(np.int32)
+
+
+def _quad(p0, p1, p2, p3, normal):
+    return (np.array([p0, p1, p2, p3], np.float32), np.tile(np.array(normal, np.float32), (4, 1)), np.array([[0, 1, 2], [0, 2, 3]], np.int32))
+
+
+def make_scene(tris: int = 10_000_000, seed: int = 1):
+    trb = importlib.import_module("bidirectional-path-tracing_b200")
+    rng = np.random.default_rng(seed)
+    n = max(8, int(np.sqrt(max(tris - 12, 0) / 6.0)))
+    x0, x1, y0, y1, z0, z1 = -1.0, 1.0, 0.0, 1.6, -1.0, 1.0
+    parts = [  # (name, material, geometry)
+        ("light", 0, _quad((-0.25, 1.59, -0.25), (0.25, 1.59, -0.25), (0.25, 1.59, 0.25), (-0.25, 1.59, 0.25), (0, -1, 0))),
+        ("backWall", 1, _quad((x0, y0, z0), (x1, y0, z0), (x1, y1, z0), (x0, y1, z0), (0, 0, 1))),
+        ("ceiling", 1, _quad((x0, y1, z0), (x1, y1, z0), (x1, y1, z1), (x0, y1, z1), (0, -1, 0))),
+        ("leftWall", 2, _quad((x0, y0, z0), (x0, y1, z0), (x0, y1, z1), (x0, y0, z1), (1, 0, 0))),
+        ("rightWall", 3, _quad((x1, y0, z0), (x1, y0, z1), (x1, y1, z1), (x1, y1, z0), (-1, 0, 0))),
+        ("floor", 4, _quad((x0, y0, z0), (x0, y0, z1), (x1, y0, z1), (x1, y0, z0), (0, 1, 0))),
+        ("mirrorSphere", 5, _sphere(n, np.array([-0.55, 0.32, -0.3]), 0.3, rng)),
+        ("glassSphere", 6, _sphere(n, np.array([0.0, 0.32, 0.35]), 0.3, rng)),
+        ("phongSphere", 7, _sphere(n, np.array([0.55, 0.32, -0.3]), 0.3, rng)),
+    ]
+    mats = np.zeros(8, trb.MATERIAL_DTYPE)
+    mats["ni"], mats["tf"] = 1.0, 1.0
+
+    def setm(i, illum, kd=(0, 0, 0), ks=(0, 0, 0), ke=(0, 0, 0), ns=1.0, ni=1.0):
+        mats[i]["illum"], mats[i]["kd"], mats[i]["ks"], mats[i]["ke"], mats[i]["ns"], mats[i]["ni"] = illum, kd, ks, ke, ns, ni
+    setm(0, 7, kd=(0.78, 0.78, 0.78), ke=(35, 35, 35))
+    setm(1, 7, kd=(0.73, 0.73, 0.73))
+    setm(2, 7, kd=(0.63, 0.065, 0.05))
+    setm(3, 7, kd=(0.14, 0.45, 0.091))
+    setm(4, 8, kd=(0.5, 0.5, 0.5), ks=(0.3, 0.3, 0.3), ns=30.0)
+    setm(5, 3, ks=(1, 1, 1))
+    setm(6, 6, ks=(1, 1, 1), ni=1.5)
+    setm(7, 2, kd=(0.3, 0.3, 0.3), ks=(0.6, 0.6, 0.6), ns=50.0)
+    P, N, TV, TM, TS, names = [], [], [], [], [], []
+    base = 0
+    for s, (name, m, (pos, nrm, tri)) in enumerate(parts):
+        P.append(pos); N.append(nrm); TV.append(tri + base)
+        TM.append(np.full(len(tri), m, np.int32)); TS.append(np.full(len(tri), s, np.int32)); names.append(name)
+        base += len(pos)
+    tv = np.concatenate(TV)
+    return trb.HostScene(np.concatenate(P), np.concatenate(N), tv, tv.copy(), np.concatenate(TM), np.concatenate(TS), mats,
+                         n_shapes=len(parts), shape_names=names)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--tris", type=int, default=200_000)
+    ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--out", default="")
+    ap.add_argument("--obj", default="")
+    a = ap.parse_args()
+    sc = make_scene(a.tris, a.seed)
+    print(f"{sc.n_tris} triangles, {len(sc.positions)} vertices, {sc.n_shapes} shapes")
+    if a.out:
+        sc.save_npz(a.out)
+    if a.obj:
+        import scene_to_obj
+        scene_to_obj.write_obj(sc, a.obj)
