@@ -23,7 +23,7 @@ def _box(img, k):
 # tolerance per pin: box-filtered relMSE.  The shipped hard-light image (cbox_bdpt_final.exr) predates the final code:
 # the unmodified reference at HEAD differs from it by relMSE 5.9e-3 (tools/gen_image_golden.py), so that pin gets 1e-2
 # and the tight hard-light pin is a 96 spp render of the reference itself (image_hardlight_rr8_head.npz).
-PINS = {"caustic_rr5": 2e-3, "caustic_rr8": 2e-3, "hardlight_rr8_head": 2e-3, "hardlight_rr8": 1e-2}
+PINS = {"caustic_rr5": 2e-3, "caustic_rr8": 2e-3, "hardlight_rr8_head": 2e-3, "hardlight_rr16_head": 2e-3, "hardlight_rr8": 1e-2}
 
 
 @pytest.mark.parametrize("pin", list(PINS))
