@@ -1,0 +1,227 @@
+// trace_coop.cuh -- warp-cooperative traversal: node traversal per lane, triangle tests redistributed over the warp.
+//
+// trace_warp.cuh keeps a lane's postponed triangles private to the lane, so its triangle phase runs with ~15 of 32
+// lanes and its node phase with ~18 (lanes draining triangles, lanes whose pending list is full).  Here the two
+// kinds of work are decoupled through a per-warp queue in shared memory:
+//   * node phase: every lane with a current node tests its two child boxes; a reached leaf (or pair of sibling
+//     leaves = one contiguous range) is pushed triangle by triangle into the warp's queue as (owner lane, triangle);
+//   * triangle phase: runs whenever the queue holds >= 32 entries (or nothing else is left to do); lane i tests
+//     entry i for its OWNER's ray - the ray is read from the owner's registers with warp shuffles - and merges the
+//     result into the owner's record in shared memory: atomicMin on the packed (t bits << 32 | list position) for
+//     closest hits, which IS the reference's rule (min t, ties -> first in the build-reordered list, bvh.h:305), an
+//     OR of flags for occlusion / ill-conditioning.  (u, v) of the winner are recomputed once at completion by the
+//     same arithmetic, hence bit-identical.
+// Everything else (persistent warps with lane refill, straight-line slab tests, pruning, the exhaustive re-trace
+// of ill-conditioned rays, the result resolve) is as in trace_warp.cuh.
+#pragma once
+#include "trace_warp.cuh"
+
+#ifndef TRB_COOP_DRAIN
+#define TRB_COOP_DRAIN 32u    // run a triangle phase when this many tests are queued
+#endif
+#ifndef TRB_COOP_Q
+#define TRB_COOP_Q 512u       // queue entries per warp (power of two); a node phase adds at most 8 x 32
+#endif
+
+namespace trbk {
+
+struct CoopWarp {
+    unsigned long long best[32];   // closest: (float bits of t << 32) | list position; init (bits(max_t) << 32)
+    int32_t outst[32];             // triangles queued for this lane's ray and not yet tested
+    uint32_t flags[32];            // bit 0: ill-conditioned candidate met, bit 1: occluded
+    uint32_t tail;                 // queue write cursor (monotone; entries live at index & (Q-1))
+    uint32_t pad[3];
+    uint32_t queue[TRB_COOP_Q];    // (owner lane << 27) | triangle position
+};
+
+template <bool ANY>
+__global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_coop(const TraceArgs a) {
+    __shared__ CoopWarp sh_all[TRB_TRACE_BLOCK / 32];
+    CoopWarp& sh = sh_all[threadIdx.x >> 5];
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    uint32_t n = a.n_ptr ? *a.n_ptr : a.n_fixed;
+    if (ANY && a.n_ptr) n = min(n, a.cap);
+    bool more = true;       // warp-uniform: the ray queue may still hold rays
+    uint32_t head = 0;      // warp-uniform read cursor of the triangle queue
+
+    int32_t cur = -1;       // current inner node or -1
+    int sp = 0;
+    bool have = false, exh = false;
+    RayT r; RayPre pre;
+    int32_t slot = 0;
+    r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.min_t = r.max_t = 0.f;
+    pre.ix = pre.iy = pre.iz = 0.f; pre.degenerate = false;
+    int32_t stack[TRB_STACK];
+#ifdef TRB_COUNTERS
+    uint32_t c_nodes = 0, c_tris = 0, c_exh = 0;
+#endif
+    sh.outst[lane] = 0; sh.flags[lane] = 0; sh.best[lane] = 0ull;
+    if (lane == 0) sh.tail = 0;
+    __syncwarp();
+
+    auto push_range = [&](uint32_t first, uint32_t cnt) {   // this lane's ray must test triangles [first, first+cnt)
+        const uint32_t base = atomicAdd(&sh.tail, cnt);
+        const uint32_t e0 = (uint32_t(lane) << 27) | first;
+#pragma unroll
+        for (uint32_t k = 0; k < 8u; ++k)   // straight-line predicated stores (cnt <= 8): no divergent loop
+            if (k < cnt) sh.queue[(base + k) & (TRB_COOP_Q - 1u)] = e0 + k;
+        sh.outst[lane] += int32_t(cnt);   // only the owner adds; testers subtract atomically between __syncwarp()s
+    };
+    auto start_ray = [&]() {
+        sh.best[lane] = (unsigned long long)__float_as_uint(r.max_t) << 32;   // bvh.h:263: intersection->t = ray.max_t
+        sh.flags[lane] = 0; sp = 0; cur = -1;
+        if (!(r.min_t > r.max_t)) {                                            // bvh.h:287
+            if (a.bvh.root_ref >= 0) cur = a.bvh.root_ref;
+            else { const uint32_t code = uint32_t(~a.bvh.root_ref); push_range(code >> 3, code & 7u); }
+        }
+    };
+
+    while (true) {
+        const bool idle = cur < 0 && (!have || sh.outst[lane] == 0);
+        const unsigned idle_mask = __ballot_sync(FULL, idle);
+        if (idle_mask == FULL || (__popc(idle_mask) >= TRB_FETCH_T && more)) {
+            bool want = idle;
+            if (idle && have) {
+                const uint32_t fl = sh.flags[lane];
+                const bool occ = (fl & 2u) != 0;
+                if ((fl & 1u) && !exh && !(ANY && occ)) {
+                    exh = true;   // ill-conditioned candidate met: visit what the reference visits (no distance pruning)
+                    start_ray();
+                    want = false;
+#ifdef TRB_COUNTERS
+                    ++c_exh;
+#endif
+                } else {
+                    have = false;
+                    if (ANY) {
+                        if (a.occ_out) a.occ_out[slot] = occ ? 1 : 0;
+                        if (a.pend && !occ) {
+                            Pending pd = a.pend[slot];
+                            float* dst = a.accum + size_t(pd.target) * 3;
+                            atomicAdd(dst, pd.r); atomicAdd(dst + 1, pd.g); atomicAdd(dst + 2, pd.b);
+                        }
+                    } else {
+                        const unsigned long long b = sh.best[lane];
+                        HitT h; h.t = r.max_t; h.u = 0.f; h.v = 0.f; h.pos = -1;
+                        if (uint32_t(b >> 32) != __float_as_uint(r.max_t)) {
+                            // the winner's (t, u, v): the same arithmetic on the same inputs as when it won
+                            const uint32_t pos = uint32_t(b);
+                            const F4* tp = a.bvh.tris + 3 * size_t(pos);
+                            F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
+                            bool ill2 = false; float t, u, v;
+                            if (tri_test(q0, q1, q2, r, &t, &u, &v, &ill2)) { h.t = t; h.u = u; h.v = v; h.pos = int32_t(pos); }
+                        }
+                        a.hits[slot] = h;
+                    }
+                }
+            }
+            if (more) {
+                const unsigned wm = __ballot_sync(FULL, want);
+                const uint32_t cnt = uint32_t(__popc(wm));
+                uint32_t base = 0;
+                if (lane == 0 && cnt) base = atomicAdd(a.fetch, cnt);
+                base = __shfl_sync(FULL, base, 0);
+                const uint32_t idx = base + uint32_t(__popc(wm & lt));
+                if (want && idx < n) {
+                    slot = (!ANY && a.q) ? a.q[idx] : int32_t(idx);
+                    const float4* rp = reinterpret_cast<const float4*>(a.rays + slot);
+                    float4 r0 = rp[0], r1 = rp[1];
+                    r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.dx = r0.w; r.dy = r1.x; r.dz = r1.y; r.min_t = r1.z; r.max_t = r1.w;
+                    pre = ray_pre(r);
+                    have = true; exh = false;
+                    start_ray();
+                }
+                more = cnt == 0 || (base + cnt < n);
+            }
+            __syncwarp();
+            if (__ballot_sync(FULL, have) == 0) break;
+        }
+        // ---- node phase ----
+        if (cur >= 0) {
+            const F4* np = a.bvh.nodes + 4 * size_t(cur);
+            F4 na = ld4(np), nb = ld4(np + 1), nc = ld4(np + 2), nd = ld4(np + 3);
+#ifdef TRB_COUNTERS
+            ++c_nodes;
+#endif
+            BoxF f0 = box_fast(na.x, na.y, na.z, na.w, nb.x, nb.y, r, pre);
+            BoxF f1 = box_fast(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, r, pre);
+            bool h0 = f0.pass, h1 = f1.pass;
+            if (f0.undecided || f1.undecided) {
+                if (f0.undecided) h0 = box_slow(na.x, na.y, na.z, na.w, nb.x, nb.y, r, pre, f0);
+                if (f1.undecided) h1 = box_slow(nb.z, nb.w, nc.x, nc.y, nc.z, nc.w, r, pre, f1);
+            }
+            const float e0 = f0.en, x0 = f0.ex, e1 = f1.en, x1 = f1.ex;
+            const bool stop = ANY && (sh.flags[lane] & 2u) != 0;   // already occluded: nothing left to find
+            if (!exh) {
+                const float best = ANY ? r.max_t : __uint_as_float(uint32_t(sh.best[lane] >> 32));
+                const float lim = best + 1e-3f * (1.f + fabsf(best));
+                // a box wholly behind the origin: exit < -1e-3 (1 + |exit|)  <=>  exit < -1e-3 / (1 - 1e-3)
+                h0 = h0 && !(e0 > lim) && !(x0 < -0.0010011f);
+                h1 = h1 && !(e1 > lim) && !(x1 < -0.0010011f);
+            }
+            const int32_t r0 = f2i(nd.x), r1 = f2i(nd.y);
+            const bool l0 = h0 && r0 < 0, l1 = h1 && r1 < 0;
+            if ((l0 || l1) && !stop) {   // sibling leaves are adjacent in the primitive order: one contiguous range
+                const uint32_t k0 = uint32_t(~r0), k1 = uint32_t(~r1);
+                push_range(l0 ? (k0 >> 3) : (k1 >> 3), (l0 ? (k0 & 7u) : 0u) + (l1 ? (k1 & 7u) : 0u));
+            }
+            const bool i0 = h0 && r0 >= 0, i1 = h1 && r1 >= 0;
+            if (stop) { cur = -1; sp = 0; }
+            else if (i0 && i1) {
+                const bool swap = !exh && (e1 < e0);  // nearer child first when pruning
+                stack[sp++] = swap ? r0 : r1;
+                cur = swap ? r1 : r0;
+            } else if (i0) cur = r0;
+            else if (i1) cur = r1;
+            else cur = sp ? stack[--sp] : -1;
+        }
+        __syncwarp();
+        // ---- triangle phases: full warps of queued tests; drain when no lane is traversing or the queue is filling up ----
+        uint32_t count = sh.tail - head;
+        const bool trav = __ballot_sync(FULL, cur >= 0) != 0;
+        while (count >= TRB_COOP_DRAIN || (count > 0u && (!trav || count > TRB_COOP_Q - 256u))) {
+            const uint32_t nb_ = min(count, 32u);
+            const bool act = uint32_t(lane) < nb_;
+            const uint32_t e = act ? sh.queue[(head + uint32_t(lane)) & (TRB_COOP_Q - 1u)] : (uint32_t(lane) << 27);
+            const int owner = int(e >> 27);
+            const uint32_t pos = e & 0x07ffffffu;
+            RayT o;   // the owner's ray, from the owner's registers
+            o.ox = __shfl_sync(FULL, r.ox, owner); o.oy = __shfl_sync(FULL, r.oy, owner); o.oz = __shfl_sync(FULL, r.oz, owner);
+            o.dx = __shfl_sync(FULL, r.dx, owner); o.dy = __shfl_sync(FULL, r.dy, owner); o.dz = __shfl_sync(FULL, r.dz, owner);
+            o.max_t = __shfl_sync(FULL, r.max_t, owner); o.min_t = 0.f;
+            if (act) {
+                const F4* tp = a.bvh.tris + 3 * size_t(pos);
+                F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
+#ifdef TRB_COUNTERS
+                ++c_tris;
+#endif
+                float t, u, v;
+                bool ill = false;
+                const bool hit = tri_test(q0, q1, q2, o, &t, &u, &v, &ill);
+                if (hit) {
+                    if (ANY) {
+                        // bvh.h:299-307 + :351: occluded iff some accepted t <= max_t (min_t <= max_t holds for a traced ray)
+                        if (t <= o.max_t) { atomicOr(&sh.flags[owner], 2u); ill = false; }
+                    } else {
+                        // (t, list position) lexicographic minimum == strict '<' in list order for any visiting order
+                        atomicMin(&sh.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | pos);
+                    }
+                }
+                if (ill) atomicOr(&sh.flags[owner], 1u);
+                atomicSub(&sh.outst[owner], 1);
+            }
+            head += nb_; count -= nb_;
+            __syncwarp();
+        }
+    }
+#ifdef TRB_COUNTERS
+    if (a.visit) {
+        atomicAdd(a.visit, (unsigned long long)c_nodes); atomicAdd(a.visit + 1, (unsigned long long)c_tris);
+        if (a.visit_exh) atomicAdd(a.visit_exh, (unsigned long long)c_exh);
+    }
+#endif
+}
+
+}  // namespace trbk

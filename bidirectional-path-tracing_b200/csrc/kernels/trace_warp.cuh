@@ -28,14 +28,15 @@
 #ifndef TRB_TRACE_BLOCK
 #define TRB_TRACE_BLOCK 128
 #endif
+#ifndef TRB_TRACE_MINBLOCKS
+#define TRB_TRACE_MINBLOCKS 8  // resident blocks per SM the register budget is capped for (8 x 128 threads x 64 registers)
+#endif
 
-#ifndef TRB_PREFETCH
-#define TRB_PREFETCH 0       // bit 0: postponed triangles, bit 1: pushed far child
+#ifndef TRB_HOIST
+#define TRB_HOIST 1          // issue the triangle fetch of this iteration BEFORE the node phase (two fetches in flight per lane)
 #endif
 
 namespace trbk {
-
-__device__ __forceinline__ void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
 
 struct TraceArgs {
     BvhView bvh;
@@ -54,7 +55,7 @@ struct TraceArgs {
 };
 
 template <bool ANY>
-__global__ void __launch_bounds__(TRB_TRACE_BLOCK, 8) k_trace_warp(const TraceArgs a) {
+__global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_warp(const TraceArgs a) {
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -135,6 +136,16 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, 8) k_trace_warp(const TraceAr
             if (__ballot_sync(FULL, have) == 0) break;
             continue;
         }
+#if TRB_HOIST
+        // the triangle tested in this iteration is known now: fetch it first so that its latency overlaps the node phase
+        const bool do_tri = npend > 0;
+        const uint32_t tfirst = p0 >> 4, tcnt = p0 & 15u;
+        F4 q0, q1, q2;
+        if (do_tri) {
+            const F4* tp = a.bvh.tris + 3 * size_t(tfirst);
+            q0 = ld4(tp); q1 = ld4(tp + 1); q2 = ld4(tp + 2);
+        }
+#endif
         // ---- node phase: two child boxes of the current inner node ----
         if (cur >= 0 && npend < 2) {
             const F4* np = a.bvh.nodes + 4 * size_t(cur);
@@ -166,29 +177,27 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, 8) k_trace_warp(const TraceAr
                 const uint32_t cnt = (l0 ? (k0 & 7u) : 0u) + (l1 ? (k1 & 7u) : 0u);
                 const uint32_t e = (first << 4) | cnt;
                 if (npend == 0) p0 = e; else p1 = e;
-#if TRB_PREFETCH & 1
-                prefetch_l1(a.bvh.tris + 3 * size_t(first));  // tested one or more iterations from now
-                if (cnt > 2) prefetch_l1(a.bvh.tris + 3 * size_t(first) + 8);
-#endif
                 ++npend;
             }
             const bool i0 = h0 && r0 >= 0, i1 = h1 && r1 >= 0;
             if (i0 && i1) {
                 const bool swap = !exh && (e1 < e0);  // nearer child first when pruning
                 stack[sp++] = swap ? r0 : r1;
-#if TRB_PREFETCH & 2
-                prefetch_l1(a.bvh.nodes + 4 * size_t(swap ? r0 : r1));  // the far child is popped later
-#endif
                 cur = swap ? r1 : r0;
             } else if (i0) cur = r0;
             else if (i1) cur = r1;
             else cur = sp ? stack[--sp] : -1;
         }
         // ---- triangle phase: one postponed triangle ----
+#if TRB_HOIST
+        if (do_tri) {
+            const uint32_t first = tfirst, cnt = tcnt;
+#else
         if (npend > 0) {
             const uint32_t first = p0 >> 4, cnt = p0 & 15u;
             const F4* tp = a.bvh.tris + 3 * size_t(first);
             F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
+#endif
 #ifdef TRB_COUNTERS
             ++c_tris;
 #endif

@@ -12,6 +12,11 @@
 #include "host/tr_host.h"
 #include "kernels/bdpt_kernels.cuh"
 #include "kernels/trace_warp.cuh"
+#include "kernels/trace_coop.cuh"
+
+#ifndef TRB_COOP
+#define TRB_COOP 1  // 1: warp-cooperative triangle queue (trace_coop.cuh); 0: per-lane postponed leaves (trace_warp.cuh)
+#endif
 
 using namespace trbk;
 
@@ -109,7 +114,7 @@ inline int grid_for(size_t n, int sm_count) {
 inline int grid_exact(size_t n) { return int(std::max<size_t>(1, (n + TRB_BLOCK - 1) / TRB_BLOCK)); }
 
 // persistent traversal grid: one wave of resident warps per SM (64 registers/thread -> 8 blocks of 128 per SM)
-inline int trace_grid(int sm_count) { return sm_count * 8; }
+inline int trace_grid(int sm_count) { return sm_count * TRB_TRACE_MINBLOCKS; }
 
 // `fetch` is the launch's own queue cursor; the caller has zeroed it on the stream
 void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, HitT* hits,
@@ -118,7 +123,11 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
+#if TRB_COOP
+    k_trace_coop<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+#else
     k_trace_warp<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+#endif
 }
 
 void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t cap, uint8_t* occ_out,
@@ -127,7 +136,11 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.rays = rays; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
+#if TRB_COOP
+    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+#else
     k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+#endif
 }
 
 int ensure_wave(trb_context* c, size_t P, int K) {
@@ -382,7 +395,7 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
     const int spp_count = spp_end - spp_begin;
     const int K = std::max(d->rr_depth - 1, 1);
-    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 20);
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 22);
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     rc = ensure_wave(c, size_t(P), K);
