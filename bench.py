@@ -311,29 +311,35 @@ def run_ours(args):
         # ---- roofline of the dominant kernel ----
         peak, how = measured_peak()
         vis = visits_subprocess(args) if world == 1 else None
-        dom = "k_trace_any" if agg["ms_trace_any"] >= agg["ms_trace_closest"] else "k_trace_closest"
+        any_dom = agg["ms_trace_any"] >= agg["ms_trace_closest"]
+        dom = "k_trace_coop<1>" if any_dom else "k_trace_coop<0>"   # <1>: occlusion + resolve, <0>: closest hit
+        K = wl["rr_depth"] - 1
+        waves = -(-(W * H * args.spp) // (args.wave if args.wave > 0 else 1 << 22))
+        dom_launches = (2 * K if any_dom else 2 * K) * waves * args.steps  # per wave: K light + K eye (any) / 1 + K + (K-1) (closest)
+        scene_note = ("acceleration structure ~0.8 GB: HBM/L2-resident, the HBM-bound case" if args.workload == "tess" else
+                      "this scene's BVH (~2.5 MB nodes+triangles) is L1/L2-resident, so the figure measures issue/L1/L2-side efficiency "
+                      "against the HBM peak (ncu: DRAM traffic is a few % of the algorithmic bytes)")
+        roof = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None, "peak_source": how}
         if vis:
-            if dom == "k_trace_any":
-                per_ray = 32 + 16 + 64 * vis["node_visits_any"] / max(vis["rays_any"], 1) + 48 * vis["tri_tests_any"] / max(vis["rays_any"], 1)
-                nrays, ms = agg["rays_any"], agg["ms_trace_any"]
-            else:
-                per_ray = 32 + 16 + 64 * vis["node_visits"] / max(vis["rays_closest"], 1) + 48 * vis["tri_tests"] / max(vis["rays_closest"], 1)
-                nrays, ms = agg["rays_closest"], agg["ms_trace_closest"]
+            tag = "_any" if any_dom else ""
+            nrays_v = max(vis["rays_any" if any_dom else "rays_closest"], 1)
+            per_ray = 32 + 16 + 64 * vis["node_visits" + tag] / nrays_v + 48 * vis["tri_tests" + tag] / nrays_v
+            nrays, ms = (agg["rays_any"], agg["ms_trace_any"]) if any_dom else (agg["rays_closest"], agg["ms_trace_closest"])
             achieved = per_ray * nrays / (ms * 1e-3) / 1e9
-            traffic = None
-            tf = ROOT / "profiles" / "dram_traffic.json"
-            if tf.exists():
-                try:
-                    traffic = json.loads(tf.read_text()).get(dom)
-                except Exception:
-                    traffic = None
-            out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                               "traffic": traffic, "peak_source": how, "bytes_per_ray": per_ray,
-                               "note": "algorithmic bytes = rays x (32 B ray + 16 B result/pending + 64 B x nodes visited + 48 B x triangles tested); "
-                                       "this scene's BVH (~4 MB) is L2-resident, so the figure measures L2/issue-side efficiency against the HBM peak"}
-        else:
-            out["roofline"] = {"bound": "hbm", "kernel": dom, "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,
-                               "peak_source": how}
+            roof.update(achieved=achieved, frac=achieved / peak, bytes_per_ray=per_ray, rays_per_launch=nrays / dom_launches,
+                        bytes_per_launch=per_ray * nrays / dom_launches, ms_per_launch=ms / dom_launches,
+                        nodes_per_ray=vis["node_visits" + tag] / nrays_v, tris_per_ray=vis["tri_tests" + tag] / nrays_v)
+        tf = ROOT / "profiles" / "dram_traffic.json"
+        if tf.exists():
+            try:
+                t = json.loads(tf.read_text())[args.workload]
+                roof["traffic"] = t["kernels"][dom]["dram_bytes_per_launch"]
+                roof["traffic_source"] = f"profiles/dram_traffic.json ({t['source']}: ncu dram__bytes_read+write per launch, {t['spp']} spp)"
+            except Exception:
+                pass
+        roof["note"] = ("algorithmic bytes = rays x (32 B ray + 16 B result/pending + 64 B x nodes visited + 48 B x triangles tested), "
+                        "visit counts from the -DTRB_COUNTERS twin library on the same workload; " + scene_note)
+        out["roofline"] = roof
         # ---- the reference's CPU renderer on this box's host cores (a reported baseline, not the target) ----
         if world == 1 and not args.no_cpu_baseline:
             try:
