@@ -389,8 +389,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_bounce(const __grid_constant_
     if (go) p.q_out[idx] = slot;
 }
 
-// ---- connectVertices (bdpt.h:434-483): one thread per (connecting eye vertex k, light vertex j), j-major so that
-// the lanes of a warp share j and read consecutive queue entries.  Replaces the per-thread loop over the sample's
+// ---- connectVertices (bdpt.h:434-483): one thread per (connecting eye vertex k, light vertex j), j fastest.  Replaces the per-thread loop over the sample's
 // light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). -------------------------------
 __global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_conn_ptr) {
     const uint32_t nc = *n_conn_ptr;
@@ -400,7 +399,10 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_con
     for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total_w; t += (unsigned long long)gridDim.x * blockDim.x) {
         bool want = false; RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
         if (t < total) {
-            const uint32_t j = uint32_t(t / nc), k = uint32_t(t - (unsigned long long)j * nc);
+            // j fastest: the K lanes of one eye vertex read the same EyeVertex / nlv / q_conn words (one broadcast
+            // transaction instead of K re-reads from HBM: the j-major order re-read every eye vertex K times and
+            // measured 2.1 GB of DRAM traffic per launch, profiles/dram_traffic.json r1i)
+            const uint32_t k = uint32_t(t / uint32_t(p.K)), j = uint32_t(t - (unsigned long long)k * uint32_t(p.K));
             const int slot = p.q_conn[k];
             if (int(j) < p.nlv[slot]) {
                 const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);

@@ -46,6 +46,7 @@ enum LaunchKind { LK_CLOSEST = 0, LK_ANY = 1, LK_LOGIC = 2, LK_N = 3 };
 struct trb_context {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;  // shadow-ray traversal of stage d overlaps the closest-hit traversal of stage d+1
     std::string err;
     cudaDeviceProp prop{};
     // scene
@@ -62,13 +63,13 @@ struct trb_context {
     uint8_t* pinned = nullptr;  // flattened scene staged in pinned host memory (trb_scene_refresh)
     size_t pinned_bytes = 0;
     // wave buffers
-    DevBuf<RayT> cam_ray, ray, sray;
+    DevBuf<RayT> cam_ray, ray, sray, sray2;   // two shadow queues: one is traced while the next is being filled
     DevBuf<HitT> hit, hit0;
     DevBuf<float4> st_t, st_v;
     DevBuf<LightVertex> lv;
     DevBuf<int32_t> nlv, q_a, q_b, q_conn;
     DevBuf<EyeVertex> ev;
-    DevBuf<Pending> spend;
+    DevBuf<Pending> spend, spend2;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
     DevBuf<uint32_t> fetch_ctr;          // queue cursor of the stand-alone trace entry points
     DevBuf<unsigned long long> d_stats;  // [0] closest rays, [1] any rays, [2] node visits, [3] tri tests
@@ -78,9 +79,10 @@ struct trb_context {
     DevBuf<HitT> io_hits;
     DevBuf<uint8_t> io_occ;
     // timing
-    std::vector<cudaEvent_t> events;
-    std::vector<int> event_kind;
-    size_t n_events = 0;
+    std::vector<cudaEvent_t> events, events2;   // per stream
+    std::vector<int> event_kind, event_kind2;
+    size_t n_events = 0, n_events2 = 0;
+    std::vector<cudaEvent_t> dep_a, dep_b;       // untimed dependency events between the two streams
     bool timing = false;
     uint64_t launches = 0;
 
@@ -89,12 +91,15 @@ struct trb_context {
         err = std::string(what) + ": " + cudaGetErrorString(e);
         return TRB_ERR_CUDA;
     }
-    void mark(int kind) {
-        ++launches;
+    void mark(int kind, bool second = false) {  // kind < 0: a begin marker on the second stream, not a launch
+        if (kind >= 0) ++launches;
         if (!timing) return;
-        if (n_events == events.size()) { cudaEvent_t ev; cudaEventCreate(&ev); events.push_back(ev); event_kind.push_back(0); }
-        event_kind[n_events] = kind;
-        cudaEventRecord(events[n_events++], stream);
+        std::vector<cudaEvent_t>& evs = second ? events2 : events;
+        std::vector<int>& kinds = second ? event_kind2 : event_kind;
+        size_t& n = second ? n_events2 : n_events;
+        if (n == evs.size()) { cudaEvent_t ev; cudaEventCreate(&ev); evs.push_back(ev); kinds.push_back(0); }
+        kinds[n] = kind;
+        cudaEventRecord(evs[n++], second ? stream2 : stream);
     }
 };
 
@@ -131,15 +136,16 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
 }
 
 void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t cap, uint8_t* occ_out,
-                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit) {
+                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit, cudaStream_t stream = nullptr) {
+    if (!stream) stream = c->stream;
     TraceArgs a{};
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.rays = rays; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
 #if TRB_COOP
-    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
 #else
-    k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
 #endif
 }
 
@@ -152,6 +158,7 @@ int ensure_wave(trb_context* c, size_t P, int K) {
     TRB_CUDA(c, c->lv.alloc(P * kk)); TRB_CUDA(c, c->nlv.alloc(P));
     TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P)); TRB_CUDA(c, c->ev.alloc(P));
     TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
+    TRB_CUDA(c, c->sray2.alloc(shadow_cap)); TRB_CUDA(c, c->spend2.alloc(shadow_cap));
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
     TRB_CUDA(c, c->d_stats.alloc(8));
     return TRB_OK;
@@ -188,7 +195,8 @@ int trb_create(int device, trb_context** out) {
     auto* c = new trb_context();
     c->device = device;
     if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&c->prop, device) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking) != cudaSuccess) {
         g_create_err = "cudaSetDevice / stream creation failed";
         delete c;
         return TRB_ERR_NO_DEVICE;
@@ -209,11 +217,16 @@ void trb_destroy(trb_context* c) {
     cudaStreamSynchronize(c->stream);
     c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
     c->d_etris.release(); c->d_cdf.release();
-    c->cam_ray.release(); c->ray.release(); c->sray.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
+    c->cam_ray.release(); c->ray.release(); c->sray.release(); c->sray2.release(); c->spend2.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->q_conn.release(); c->ev.release(); c->spend.release();
     c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
     if (c->pinned) cudaFreeHost(c->pinned);
     for (auto ev : c->events) cudaEventDestroy(ev);
+    for (auto ev : c->events2) cudaEventDestroy(ev);
+    for (auto ev : c->dep_a) cudaEventDestroy(ev);
+    for (auto ev : c->dep_b) cudaEventDestroy(ev);
+    cudaStreamSynchronize(c->stream2);
+    cudaStreamDestroy(c->stream2);
     cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -320,6 +333,32 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     auto stage_ctr = [&](int s) { return c->counters.p + size_t(s) * CTR_N; };
     const int gP = grid_exact(size_t(P));
 
+    // Shadow rays of stage d are traced on the second stream while the first goes on with the closest-hit traversal
+    // and the bounce of stage d+1 (the tail of one persistent kernel is filled by the other).  Two shadow queues
+    // alternate; a bounce may refill a queue only after the traversal that read it has finished.
+    const size_t n_dep = size_t(n_stage) + 2;
+    while (c->dep_a.size() < n_dep) { cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming); c->dep_a.push_back(e); }
+    while (c->dep_b.size() < n_dep) { cudaEvent_t e; cudaEventCreateWithFlags(&e, cudaEventDisableTiming); c->dep_b.push_back(e); }
+    int n_any = 0;                       // shadow launches issued so far in this wave
+    int last_any_of_buf[2] = {-1, -1};   // index (into dep_b) of the last traversal that read each queue
+    auto shadow_buffers = [&]() {        // before a bounce kernel: pick the queue and wait until it is free again
+        const int b = n_any & 1;
+        p.sray = b ? c->sray2.p : c->sray.p; p.spend = b ? c->spend2.p : c->spend.p;
+        if (last_any_of_buf[b] >= 0) cudaStreamWaitEvent(c->stream, c->dep_b[last_any_of_buf[b]], 0);
+    };
+    auto trace_shadow = [&]() {          // after the bounce kernel(s) of a stage
+        const int b = n_any & 1;
+        cudaEventRecord(c->dep_a[n_any], c->stream);
+        cudaStreamWaitEvent(c->stream2, c->dep_a[n_any], 0);
+        c->mark(-1, true);
+        launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
+                   visit ? visit + 2 : nullptr, c->stream2);
+        c->mark(LK_ANY, true);
+        cudaEventRecord(c->dep_b[n_any], c->stream2);
+        last_any_of_buf[b] = n_any;
+        ++n_any;
+    };
+
     k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
     launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, stage_ctr(2 * kk + 2) + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
     // light subpath
@@ -333,9 +372,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         ++stage;
         p.counters = stage_ctr(stage);
         launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
+        shadow_buffers();
         k_light_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
-        launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY, visit ? visit + 2 : nullptr);
-        c->mark(LK_ANY);
+        trace_shadow();
     }
     // eye subpath
     stage = kk + 1;
@@ -349,12 +388,14 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         ++stage;
         p.counters = stage_ctr(stage);
         if (depth > 1) { launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST); }
+        shadow_buffers();
         k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in);
         k_connect_vertices<<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN); c->mark(LK_LOGIC);
         ++c->launches;
-        launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY, visit ? visit + 2 : nullptr);
-        c->mark(LK_ANY);
+        trace_shadow();
     }
+    for (int b = 0; b < 2; ++b)  // join: the wave is complete on the first stream
+        if (last_any_of_buf[b] >= 0) cudaStreamWaitEvent(c->stream, c->dep_b[last_any_of_buf[b]], 0);
     k_fold_stats<<<1, 32, 0, c->stream>>>(c->counters.p, n_stage, kk, kk, uint32_t(P), c->d_stats.p, p.shadow_cap); c->mark(LK_LOGIC);
     TRB_CUDA(c, cudaGetLastError());
     return TRB_OK;
@@ -376,10 +417,17 @@ void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
     st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5]; st->retraces = h[6]; st->retraces_any = h[7];
     st->launches = c->launches;
     double ms[LK_N] = {0, 0, 0};
+    // kernel time summed per kind on each stream; the two streams overlap, so the kinds can add up to more than ms_total
     for (size_t i = 1; i < c->n_events; ++i) {
         float t = 0.f;
         cudaEventElapsedTime(&t, c->events[i - 1], c->events[i]);
         ms[c->event_kind[i]] += t;
+    }
+    for (size_t i = 1; i < c->n_events2; ++i) {
+        if (c->event_kind2[i] < 0) continue;  // a begin marker
+        float t = 0.f;
+        cudaEventElapsedTime(&t, c->events2[i - 1], c->events2[i]);
+        ms[c->event_kind2[i]] += t;
     }
     if (c->n_events >= 2) { float t = 0.f; cudaEventElapsedTime(&t, c->events[0], c->events[c->n_events - 1]); st->ms_total = t; }
     st->ms_trace_closest = ms[LK_CLOSEST]; st->ms_trace_any = ms[LK_ANY]; st->ms_logic = ms[LK_LOGIC];
@@ -402,7 +450,7 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     if (rc) return rc;
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
-    c->timing = stats != nullptr; c->n_events = 0; c->launches = 0;
+    c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
     TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
     c->mark(LK_LOGIC);
     if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
@@ -608,7 +656,7 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
     TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
-    c->timing = false; c->n_events = 0; c->launches = 0;
+    c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
     WaveRun w{d, d_acc.p, d_pix.p, d_rays.p, d_rng.p, int(stride), true};
     rc = run_wave(c, w, cam, 0, int(n), 0, d->spp);
     if (rc == TRB_OK) {
