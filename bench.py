@@ -307,11 +307,21 @@ def run_ours(args):
                        "steps": e2e_steps, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (host frame buffer out)"},
                "mrays_per_s": {"closest": agg["rays_closest"] / (tot_ms * 1e-3) / 1e6, "any": agg["rays_any"] / (tot_ms * 1e-3) / 1e6,
                                "rays_per_sample": (agg["rays_closest"] + agg["rays_any"]) / max(agg["samples"], 1)},
-               "stage_ms_per_step": {k: agg[k] / args.steps for k in ("ms_trace_closest", "ms_trace_any", "ms_logic")}}
-        # ---- roofline of the dominant kernel ----
+               "stage_ms_per_step": {k: agg[k] / args.steps for k in ("ms_trace_closest", "ms_trace_any", "ms_logic")},
+               "stage_ms_note": "kernel time summed per kind; shadow traversal runs on a second stream, so the kinds overlap and add up to more than ms_per_step"}
+        # ---- roofline of the dominant kernel: per-kernel time from an extra pass with the two streams serialised
+        # (TRB_FLAG_NO_OVERLAP), so that the kernel's duration is its own and not a share of an overlapped interval ----
+        desc_serial = trb.render_desc(width=W, height=H, spp=total_spp, rr_depth=wl["rr_depth"], spp_begin=s_begin, spp_end=s_end,
+                                      wave_samples=args.wave, flags=trb.TRB_FLAG_NO_OVERLAP)
+        ser = {}
+        for _ in range(2):
+            flush.zero_(); torch.cuda.synchronize()
+            ser = ctx.render_bdpt_device(desc_serial, fb.data_ptr())
+        out["stage_ms_serial"] = {k: ser[k] for k in ("ms_total", "ms_trace_closest", "ms_trace_any", "ms_logic")}
+        agg_s = {k: ser[k] * args.steps for k in ser}  # same units as agg (sums over args.steps steps)
         peak, how = measured_peak()
         vis = visits_subprocess(args) if world == 1 else None
-        any_dom = agg["ms_trace_any"] >= agg["ms_trace_closest"]
+        any_dom = agg_s["ms_trace_any"] >= agg_s["ms_trace_closest"]
         dom = "k_trace_coop<1>" if any_dom else "k_trace_coop<0>"   # <1>: occlusion + resolve, <0>: closest hit
         K = wl["rr_depth"] - 1
         waves = -(-(W * H * args.spp) // (args.wave if args.wave > 0 else 1 << 22))
@@ -324,7 +334,7 @@ def run_ours(args):
             tag = "_any" if any_dom else ""
             nrays_v = max(vis["rays_any" if any_dom else "rays_closest"], 1)
             per_ray = 32 + 16 + 64 * vis["node_visits" + tag] / nrays_v + 48 * vis["tri_tests" + tag] / nrays_v
-            nrays, ms = (agg["rays_any"], agg["ms_trace_any"]) if any_dom else (agg["rays_closest"], agg["ms_trace_closest"])
+            nrays, ms = (agg_s["rays_any"], agg_s["ms_trace_any"]) if any_dom else (agg_s["rays_closest"], agg_s["ms_trace_closest"])
             achieved = per_ray * nrays / (ms * 1e-3) / 1e9
             roof.update(achieved=achieved, frac=achieved / peak, bytes_per_ray=per_ray, rays_per_launch=nrays / dom_launches,
                         bytes_per_launch=per_ray * nrays / dom_launches, ms_per_launch=ms / dom_launches,

@@ -21,6 +21,7 @@ LIB_PATH = PKG_DIR / "libtrb.so"
 
 TRB_OK = 0
 TRB_FLAG_NO_JITTER = 1
+TRB_FLAG_NO_OVERLAP = 2
 
 
 class TrbError(RuntimeError):

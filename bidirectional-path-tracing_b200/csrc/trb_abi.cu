@@ -346,8 +346,16 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.sray = b ? c->sray2.p : c->sray.p; p.spend = b ? c->spend2.p : c->spend.p;
         if (last_any_of_buf[b] >= 0) cudaStreamWaitEvent(c->stream, c->dep_b[last_any_of_buf[b]], 0);
     };
+    const bool overlap = (d.flags & TRB_FLAG_NO_OVERLAP) == 0;
     auto trace_shadow = [&]() {          // after the bounce kernel(s) of a stage
         const int b = n_any & 1;
+        if (!overlap) {
+            launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
+                       visit ? visit + 2 : nullptr, c->stream);
+            c->mark(LK_ANY);
+            ++n_any;
+            return;
+        }
         cudaEventRecord(c->dep_a[n_any], c->stream);
         cudaStreamWaitEvent(c->stream2, c->dep_a[n_any], 0);
         c->mark(-1, true);

@@ -101,6 +101,7 @@ typedef struct trb_render_desc {
 
 #define TRB_FLAG_NONE 0u
 #define TRB_FLAG_NO_JITTER 1u /* force the spp==1 pixel-centre path of renderer.cpp:169-180 */
+#define TRB_FLAG_NO_OVERLAP 2u /* one stream: every kernel runs alone (per-kernel timing for the roofline line); same results */
 
 typedef struct trb_stats {
     double ms_total;          /* device time of the whole call, CUDA events            */
