@@ -24,12 +24,14 @@ namespace trbk {
 __device__ __forceinline__ float t_sinf(float x) { return (float)sin((double)x); }
 __device__ __forceinline__ float t_cosf(float x) { return (float)cos((double)x); }
 __device__ __forceinline__ float t_powf(float x, float y) { return (float)pow((double)x, (double)y); }
+__device__ __forceinline__ void t_sincosf(float x, float* s, float* c) { double ds, dc; sincos((double)x, &ds, &dc); *s = (float)ds; *c = (float)dc; }
 __device__ __forceinline__ float v_powf(float x, float y) { return powf(x, y); }  // value-only uses
 #else
 __device__ __forceinline__ float v_powf(float x, float y) { return powf(x, y); }
 __device__ __forceinline__ float t_sinf(float x) { return sinf(x); }
 __device__ __forceinline__ float t_cosf(float x) { return cosf(x); }
 __device__ __forceinline__ float t_powf(float x, float y) { return powf(x, y); }
+__device__ __forceinline__ void t_sincosf(float x, float* s, float* c) { sincosf(x, s, c); }
 #endif
 
 struct Mat {
@@ -61,7 +63,8 @@ __device__ __forceinline__ V3 sq_to_uniform_hemisphere(float ux, float uy) {  //
     float phi = ux * TRB_PI * 2.0f;
     float cosTheta = uy;
     float sinTheta = sqrtf(fmaxf(1.f - (cosTheta * cosTheta), 0.f));
-    return mk(sinTheta * t_cosf(phi), sinTheta * t_sinf(phi), cosTheta);
+    float sn, cs; t_sincosf(phi, &sn, &cs);  // one shared range reduction
+    return mk(sinTheta * cs, sinTheta * sn, cosTheta);
 }
 
 __device__ __forceinline__ V3 sq_to_cosine_hemisphere(float ux, float uy) {  // math.h:153-192
@@ -71,7 +74,8 @@ __device__ __forceinline__ V3 sq_to_cosine_hemisphere(float ux, float uy) {  // 
         float phi, radius;
         if ((rx * rx) > (ry * ry)) { radius = rx; phi = (TRB_PI * 0.25f) * (ry * (1.f / rx)); }
         else { radius = ry; phi = (TRB_PI * 0.5f) - ((TRB_PI * 0.25f) * (rx * (1.f / ry))); }
-        dx = radius * t_cosf(phi); dy = radius * t_sinf(phi);
+        float sn, cs; t_sincosf(phi, &sn, &cs);
+        dx = radius * cs; dy = radius * sn;
     }
     float z = 1.0f - (dx * dx + dy * dy);
     z = fmaxf(z, 0.f);
@@ -85,7 +89,8 @@ __device__ __forceinline__ V3 sq_to_phong_lobe(float ux, float uy, float exponen
     float cosTheta = t_powf(ux, 1.f / (exponent + 2));
     float sinTheta = sqrtf(fmaxf(1.f - (cosTheta * cosTheta), 0.f));
     float phi = uy * 2.f * TRB_PI;
-    return mk(sinTheta * t_cosf(phi), sinTheta * t_sinf(phi), cosTheta);
+    float sn, cs; t_sincosf(phi, &sn, &cs);
+    return mk(sinTheta * cs, sinTheta * sn, cosTheta);
 }
 
 __device__ __forceinline__ float phong_lobe_pdf(V3 v, float exponent) {  // math.h:221-227

@@ -332,6 +332,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     int32_t* qa = c->q_a.p; int32_t* qb = c->q_b.p;
     auto stage_ctr = [&](int s) { return c->counters.p + size_t(s) * CTR_N; };
     const int gP = grid_exact(size_t(P));
+    const int gB = int((size_t(P) + TRB_SORT_BLOCK - 1) / TRB_SORT_BLOCK);
 
     // Shadow rays of stage d are traced on the second stream while the first goes on with the closest-hit traversal
     // and the bounce of stage d+1 (the tail of one persistent kernel is filled by the other).  Two shadow queues
@@ -381,7 +382,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.counters = stage_ctr(stage);
         launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
         shadow_buffers();
-        k_light_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
+        k_light_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
         trace_shadow();
     }
     // eye subpath
@@ -397,7 +398,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.counters = stage_ctr(stage);
         if (depth > 1) { launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST); }
         shadow_buffers();
-        k_eye_bounce<<<gP, TRB_BLOCK, 0, c->stream>>>(p, depth, n_in);
+        k_eye_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in);
         k_connect_vertices<<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN); c->mark(LK_LOGIC);
         ++c->launches;
         trace_shadow();
