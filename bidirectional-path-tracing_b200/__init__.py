@@ -22,6 +22,8 @@ LIB_PATH = PKG_DIR / "libtrb.so"
 TRB_OK = 0
 TRB_FLAG_NO_JITTER = 1
 TRB_FLAG_NO_OVERLAP = 2
+TRB_FLAG_RUSSIAN_ROULETTE = 4  # the reference's NO_RR 0 behaviour (bdpt.h:18,68,129); default off = shipped behaviour
+TRB_RR_DEFAULT_MAX_DEPTH = 32
 
 
 class TrbError(RuntimeError):
@@ -48,7 +50,7 @@ class RenderDesc(C.Structure):
     _fields_ = [("eye", C.c_float * 3), ("at", C.c_float * 3), ("up", C.c_float * 3), ("fov_deg", C.c_float),
                 ("width", C.c_int32), ("height", C.c_int32), ("spp", C.c_int32), ("rr_depth", C.c_int32),
                 ("spp_begin", C.c_int32), ("spp_end", C.c_int32), ("seed", C.c_uint32), ("flags", C.c_uint32),
-                ("wave_samples", C.c_int64)]
+                ("wave_samples", C.c_int64), ("max_depth", C.c_int32), ("reserved", C.c_int32)]
 
 
 class Stats(C.Structure):
@@ -118,13 +120,22 @@ def make_rays(o, d, min_t=1e-8, max_t=np.finfo(np.float32).max) -> np.ndarray:
 
 
 def render_desc(eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0), up=(0.0, 1.0, 0.0), fov=30.0, width=800, height=600, spp=1,
-                rr_depth=5, seed=260450963, spp_begin=0, spp_end=0, flags=0, wave_samples=0) -> RenderDesc:
+                rr_depth=5, seed=260450963, spp_begin=0, spp_end=0, flags=0, wave_samples=0, max_depth=0) -> RenderDesc:
     d = RenderDesc()
     d.eye[:], d.at[:], d.up[:] = eye, at, up
     d.fov_deg = fov
     d.width, d.height, d.spp, d.rr_depth = width, height, spp, rr_depth
     d.spp_begin, d.spp_end, d.seed, d.flags, d.wave_samples = spp_begin, spp_end, seed, flags, wave_samples
+    d.max_depth = max_depth
     return d
+
+
+def max_vertices(desc: RenderDesc) -> int:
+    """vertices per subpath: rr_depth-1, or max_depth-1 under TRB_FLAG_RUSSIAN_ROULETTE (trb_abi.cu: max_vertices_of)"""
+    if desc.flags & TRB_FLAG_RUSSIAN_ROULETTE:
+        md = desc.max_depth if desc.max_depth > 0 else max(TRB_RR_DEFAULT_MAX_DEPTH, desc.rr_depth)
+        return max(md - 1, 0)
+    return max(desc.rr_depth - 1, 0)
 
 
 # ---- host scene ------------------------------------------------------------------------------------------
@@ -304,7 +315,7 @@ class Context:
         rng = np.ascontiguousarray(rng, np.float32)
         n, stride = rng.shape
         assert n == len(cam_rays)
-        k = max(desc.rr_depth - 1, 1)
+        k = max(max_vertices(desc), 1)
         li = np.zeros((n, 3), np.float32)
         pix = np.full((n, k), -1, np.int32)
         rgb = np.zeros((n, k, 3), np.float32)

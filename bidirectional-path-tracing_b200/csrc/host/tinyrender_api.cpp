@@ -22,6 +22,8 @@ trb_render_desc make_desc(const Config& c) {
     d.width = c.width; d.height = c.height; d.spp = c.spp;
     d.rr_depth = c.integratorSettings.bdpt.rrDepth;
     d.seed = c.seed; d.wave_samples = c.waveSamples;
+    if (c.russianRoulette) d.flags |= TRB_FLAG_RUSSIAN_ROULETTE;
+    d.max_depth = c.maxDepth;
     return d;
 }
 trb_ray to_ray(const Ray& r) {
@@ -45,6 +47,7 @@ bool loadTOML(Config& config, const std::string& inputFile) {
     config.camera.fov = t.desc.fov_deg;
     config.width = t.desc.width; config.height = t.desc.height; config.spp = t.desc.spp;
     config.seed = t.desc.seed; config.waveSamples = t.desc.wave_samples; config.gpus = t.gpus;
+    config.russianRoulette = (t.desc.flags & TRB_FLAG_RUSSIAN_ROULETTE) != 0; config.maxDepth = t.desc.max_depth;
     static const char* known[] = {"normal", "simple", "ao", "ro", "direct", "path", "bdpt"};
     static const EIntegrator ids[] = {ENormalIntegrator, ESimpleIntegrator, EAOIntegrator, EROIntegrator, EDirectIntegrator,
                                       EPathTracerIntegrator, EBDPTIntegrator};

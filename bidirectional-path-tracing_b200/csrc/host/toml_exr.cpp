@@ -183,6 +183,10 @@ bool load_toml(const std::string& path, TomlConfig& out, std::string& err) {
     out.desc.spp_begin = 0; out.desc.spp_end = 0;
     out.desc.seed = uint32_t(get_int(ren, "seed", 260450963));  // renderer.cpp:155 (extension key)
     out.desc.flags = 0;
+    // extension keys: the reference's compiled-out Russian roulette (bdpt.h:18 NO_RR) and the device's depth cap
+    if (get_bool(ren, "russianRoulette", false)) out.desc.flags |= TRB_FLAG_RUSSIAN_ROULETTE;
+    out.desc.max_depth = get_int(ren, "maxDepth", 0);
+    out.desc.reserved = 0;
     out.desc.wave_samples = get_int(ren, "waveSamples", 0);  // extension keys: samples per wavefront, devices
     out.gpus = std::max(1, get_int(ren, "gpus", 1));
     return true;

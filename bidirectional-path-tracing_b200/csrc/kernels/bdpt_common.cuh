@@ -31,7 +31,7 @@ struct alignas(16) LightVertex {
     float nx, ny, nz, vc;
     float wox, woy, woz;
     int32_t mat;
-    float tx, ty, tz, pad;
+    float tx, ty, tz, rr;   // rr = PathVertex::rr (bdpt.h:31-32): 1, or 0.5 under Russian roulette
 };
 
 // Eye vertex handed from k_eye_bounce to k_connect_vertices (same 64 B shape as LightVertex; `target` is the
@@ -40,18 +40,21 @@ struct alignas(16) EyeVertex {
     float px, py, pz, vcm;
     float nx, ny, nz, vc;
     float wox, woy, woz;
-    int32_t mat;
+    int32_t mat;             // | EV_RR_HALF when the vertex's continuation probability is 0.5
     float tx, ty, tz;
     uint32_t target;
 };
+enum : int32_t { EV_RR_HALF = 1 << 30 };
 
 struct WaveParams {
     SceneDev sc;
     trb::CameraDev cam;
     // wave geometry
     int32_t P;            // sample slots in this wave
-    int32_t K;            // rr_depth - 1: max vertices per subpath
+    int32_t K;            // max vertices per subpath: rr_depth - 1, or max_depth - 1 under Russian roulette
     int32_t rr_depth;
+    int32_t rr_on;        // TRB_FLAG_RUSSIAN_ROULETTE: the reference's loop test with NO_RR 0 (bdpt.h:68,129,188,201)
+    int32_t max_depth;    // hard cap on `depth` (== rr_depth when rr_on is 0)
     int32_t spp;          // total spp (normaliser)
     int32_t spp_begin;    // first sample index of this call
     int32_t spp_count;    // samples per pixel rendered by this call

@@ -50,9 +50,23 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_gen_camera(const __grid_constant_
     p.st_v[i] = make_float4(0.f, __uint_as_float(0u), __uint_as_float(ctr), 0.f);
 }
 
+// ---- Russian roulette (bdpt.h:68,129,188,201 with NO_RR 0; the shipped build has NO_RR 1 => rr == 1) --------
+// Continuation probability stored with the vertex reached at `depth`, from the throughput ON ARRIVAL.
+__device__ __forceinline__ float rr_prob(const WaveParams& p, int depth, V3 T) {
+    if (!p.rr_on) return 1.f;
+    return (depth + 1) < p.rr_depth ? 1.f : (luminance(T) < 0.01f ? 0.5f : 1.f);
+}
+// The loop test `depth < rrDepth || (sampler.next() < rr && !NO_RR)` evaluated for the NEXT iteration: past rrDepth it
+// always draws one number (Q3), and continues only under Russian roulette (and below the device's hard cap).
+__device__ __forceinline__ bool rr_continue(const WaveParams& p, int depth_next, float rr, Rng& rng) {
+    if (depth_next < p.rr_depth) return true;
+    float u = rng.next();
+    return p.rr_on && u < rr && depth_next < p.max_depth;
+}
+
 // ---- connectToCamera (bdpt.h:295-371) + splatToImagePlane (bdpt.h:485-496) ---------------------------------
 __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool active, int slot, int depth, const Surf& s, const Mat& m,
-                                                  V3 T, float vcm, float vc) {
+                                                  V3 T, float vcm, float vc, float rr) {
     bool want = false;
     RayT sr; V3 radiance = mk(0.f); uint32_t target = 0;
     if (active) {
@@ -82,7 +96,7 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
                 int nlight = p.cam.width * p.cam.height;
                 radiance = T * (fcos * (1.f / wi.z)) * (1.f / surfToImg) * (1.f / nlight) * (1.f / p.spp);
                 float revPdfA = 1.f * imgToSurf;
-                float prevRev = bsdf_pdf(m, wi, s.wo) * 1.f;  // wi/wo swapped, rr = 1 (NO_RR)
+                float prevRev = bsdf_pdf(m, wi, s.wo) * rr;  // wi/wo swapped (bdpt.h:342)
                 float lightWeight = (revPdfA / nlight) * (vcm + prevRev * vc);
                 float mis = 1.f / (lightWeight + 1.f + 0.f);
                 radiance = radiance * mis;
@@ -101,17 +115,17 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
 }
 
 // ---- ContinuePathRandomWalk (bdpt.h:243-291); returns false when the walk stops ------------------------------
-__device__ __forceinline__ bool continue_walk(const Surf& s, const Mat& m, Rng& rng, V3* T, float* vc, float* vcm, RayT* next, V3* wi_out) {
+__device__ __forceinline__ bool continue_walk(const Surf& s, const Mat& m, Rng& rng, float rr, V3* T, float* vc, float* vcm, RayT* next, V3* wi_out) {
     float ux = rng.next(), uy = rng.next();
     V3 wi; float pdf;
     V3 fcos = bsdf_sample(m, s.wo, ux, uy, &wi, &pdf);
-    pdf *= 1.f;
+    pdf *= rr;
     *wi_out = wi;
     float absCosOut = fabsf(wi.z);
     if (is_zero(fcos)) return false;
     *T = *T * (fcos * (1.f / pdf));
     bool delta = is_delta(m);
-    float prevRev = delta ? pdf : bsdf_pdf(m, wi, s.wo) * 1.f;
+    float prevRev = delta ? pdf : bsdf_pdf(m, wi, s.wo) * rr;
     if (delta) {
         *vc = (absCosOut / pdf) * (prevRev * *vc);
         *vcm = 0.f;
@@ -155,15 +169,13 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
             float vc = ed.z * (1.f / emissionPdf);
             float vcm = areaPdf / emissionPdf;
             if (!(ed.z <= 0.f)) {
-                if (1 < p.rr_depth) {
+                if (rr_continue(p, 1, 1.f, rng)) {  // the loop test of bdpt.h:188 at depth 1 (draws when rrDepth <= 1, Q3)
                     go = true;
                     RayT lr; lr.ox = es.pos.x; lr.oy = es.pos.y; lr.oz = es.pos.z; lr.dx = wd.x; lr.dy = wd.y; lr.dz = wd.z;
                     lr.min_t = 1e-8f; lr.max_t = FLT_MAX;
                     p.ray[i] = lr;
                     p.st_t[i] = make_float4(T.x, T.y, T.z, vcm);
                     sv.x = vc;
-                } else {
-                    rng.next();  // the failing loop test still draws one number (Q3)
                 }
             }
             ctr = rng.ctr;
@@ -241,30 +253,29 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_light_bounce(const __grid_co
             connect = !is_delta(m);
         }
     }
-    connect_to_camera(p, connect, slot, depth, s, m, T, vcm, vc);
+    const float rr = rr_prob(p, depth, T);
+    connect_to_camera(p, connect, slot, depth, s, m, T, vcm, vc, rr);
     if (alive) {
         uint32_t pixel, sample;
         slot_ids(p, slot, &pixel, &sample);
         Rng rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
         V3 Tn = T; float vcn = vc, vcmn = vcm; RayT nr; V3 wi;
-        if (continue_walk(s, m, rng, &Tn, &vcn, &vcmn, &nr, &wi)) {
+        if (continue_walk(s, m, rng, rr, &Tn, &vcn, &vcmn, &nr, &wi)) {
             if (connect) {  // non-delta vertices whose continuation succeeded are kept (bdpt.h:211-215, Q11)
                 int j = p.nlv[slot];
                 LightVertex lv;
                 lv.px = s.p.x; lv.py = s.p.y; lv.pz = s.p.z; lv.vcm = vcm;
                 lv.nx = s.n.x; lv.ny = s.n.y; lv.nz = s.n.z; lv.vc = vc;
                 lv.wox = s.wo.x; lv.woy = s.wo.y; lv.woz = s.wo.z; lv.mat = s.mat;
-                lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.pad = 0.f;
+                lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.rr = rr;
                 p.lv[size_t(j) * p.P + slot] = lv;
                 p.nlv[slot] = j + 1;
             }
-            if (depth + 1 < p.rr_depth) {
+            if (rr_continue(p, depth + 1, rr, rng)) {
                 go = true;
                 p.ray[slot] = nr;
                 p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
                 sv.x = vcn;
-            } else {
-                rng.next();  // depth cap: the loop test draws once more (Q3)
             }
         }
         sv.z = __uint_as_float(rng.ctr);
@@ -289,15 +300,18 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ 
             float imgToSolid = ipd * ipd / cosCamera;
             float t1Pdf = 1.f * imgToSolid;
             float vcm = float(p.cam.width * p.cam.height) * (1.f / t1Pdf);
-            if (1 < p.rr_depth) {
+            bool cont = 1 < p.rr_depth;
+            if (!cont) {  // the loop test of bdpt.h:68 draws (Q3); with rr == 1 the draw always passes
+                sv.z = __uint_as_float(__float_as_uint(sv.z) + 1u);
+                cont = p.rr_on && 1 < p.max_depth;
+            }
+            if (cont) {
                 go = true;
                 p.ray[i] = cr;
                 p.hit[i] = p.hit0[i];
                 p.st_t[i] = make_float4(1.f, 1.f, 1.f, vcm);
                 sv.x = 0.f;
                 sv.y = __uint_as_float(flags | SLOT_PURE_SPECULAR);
-            } else {
-                sv.z = __uint_as_float(__float_as_uint(sv.z) + 1u);
             }
             p.st_v[i] = sv;
         }
@@ -361,6 +375,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
             }
         }
     }
+    const float rr = rr_prob(p, depth, T);
     // ---- connectToLight (bdpt.h:374-430) ----
     {
         bool want = false; RayT sr; V3 Li = mk(0.f);
@@ -379,9 +394,9 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
                 Li = bsdf_eval(m, s.wo, wi) * (1.f / connW) * T * es.radiance;
                 if (!is_zero(Li)) {
                     sr = visibility_ray(s.p, es.pos);
-                    float lightRevW = bsdf_pdf(m, s.wo, wi) * 1.f;
+                    float lightRevW = bsdf_pdf(m, s.wo, wi) * rr;
                     float lightWeight = lightRevW / connW;
-                    float eyePrevRevW = bsdf_pdf(m, wi, s.wo) * 1.f;
+                    float eyePrevRevW = bsdf_pdf(m, wi, s.wo) * rr;
                     float eyeCurRevA = cosAtEye * (1.f / d2) * dirPdfW;
                     float eyeWeight = eyeCurRevA * (vcm + eyePrevRevW * vc);
                     float mis = 1.f / (lightWeight + 1.f + eyeWeight);
@@ -402,7 +417,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
             EyeVertex e;
             e.px = s.p.x; e.py = s.p.y; e.pz = s.p.z; e.vcm = vcm;
             e.nx = s.n.x; e.ny = s.n.y; e.nz = s.n.z; e.vc = vc;
-            e.wox = s.wo.x; e.woy = s.wo.y; e.woz = s.wo.z; e.mat = s.mat;
+            e.wox = s.wo.x; e.woy = s.wo.y; e.woz = s.wo.z; e.mat = s.mat | (rr < 1.f ? EV_RR_HALF : 0);
             e.tx = T.x; e.ty = T.y; e.tz = T.z; e.target = li_target;
             p.ev[slot] = e;
         }
@@ -411,14 +426,12 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
         if (alive) {
             if (connect) sv.y = __uint_as_float(__float_as_uint(sv.y) & ~SLOT_PURE_SPECULAR);
             V3 Tn = T; float vcn = vc, vcmn = vcm; RayT nr; V3 wi;
-            if (continue_walk(s, m, rng, &Tn, &vcn, &vcmn, &nr, &wi)) {
-                if (depth + 1 < p.rr_depth) {
+            if (continue_walk(s, m, rng, rr, &Tn, &vcn, &vcmn, &nr, &wi)) {
+                if (rr_continue(p, depth + 1, rr, rng)) {
                     go = true;
                     p.ray[slot] = nr;
                     p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
                     sv.x = vcn;
-                } else {
-                    rng.next();
                 }
             }
         }
@@ -462,13 +475,15 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_con
                 float cosL = l_wi.z, cosE = e_wi.z;
                 if (!(cosL <= 0.f || cosE <= 0.f)) {
                     Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
-                    Mat m = load_mat(p.sc.mats, __float_as_int(ec.w));
+                    const int emat = __float_as_int(ec.w);
+                    const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
+                    Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
                     Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
                     Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
-                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * 1.f;
-                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * 1.f;
-                    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * 1.f;
-                    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * 1.f;
+                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * lrr;
+                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * lrr;
+                    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * err;
+                    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * err;
                     float lightRevA = lightRevW * (cosL) * invD2;
                     float eyeRevA = eyeRevW * (cosE) * invD2;
                     float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);

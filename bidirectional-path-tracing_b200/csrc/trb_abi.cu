@@ -149,6 +149,14 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
 #endif
 }
 
+// depth cap and vertices per subpath of a render description (bdpt.h:68,188: `depth < rrDepth`, depth starts at 1)
+inline bool rr_enabled(const trb_render_desc& d) { return (d.flags & TRB_FLAG_RUSSIAN_ROULETTE) != 0; }
+inline int max_depth_of(const trb_render_desc& d) {
+    if (!rr_enabled(d)) return d.rr_depth;
+    return d.max_depth > 0 ? d.max_depth : std::max(TRB_RR_DEFAULT_MAX_DEPTH, d.rr_depth);
+}
+inline int max_vertices_of(const trb_render_desc& d) { return std::max(max_depth_of(d) - 1, 0); }
+
 int ensure_wave(trb_context* c, size_t P, int K) {
     size_t kk = size_t(std::max(K, 1));
     size_t shadow_cap = P * (kk + 1);
@@ -310,13 +318,13 @@ struct WaveRun {
 
 int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_t wave_base, int P, int spp_begin, int spp_count) {
     const trb_render_desc& d = *w.desc;
-    const int K = std::max(d.rr_depth - 1, 0);
+    const int K = max_vertices_of(d);
     const int kk = std::max(K, 1);
     const int sm = c->prop.multiProcessorCount;
     WaveParams p;
     std::memset(&p, 0, sizeof(p));
     p.sc = c->sc; p.cam = cam;
-    p.P = P; p.K = kk; p.rr_depth = d.rr_depth; p.spp = d.spp; p.spp_begin = spp_begin; p.spp_count = spp_count;
+    p.P = P; p.K = kk; p.rr_depth = d.rr_depth; p.rr_on = rr_enabled(d) ? 1 : 0; p.max_depth = max_depth_of(d); p.spp = d.spp; p.spp_begin = spp_begin; p.spp_count = spp_count;
     p.wave_base = wave_base; p.seed = d.seed; p.flags = d.flags;
     p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
     p.accum = w.d_accum; p.splat_pix = w.d_splat_pix;
@@ -414,6 +422,8 @@ int check_desc(trb_context* c, const trb_render_desc* d) {
     if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     if (!d || d->width <= 0 || d->height <= 0 || d->spp <= 0 || d->rr_depth < 1) return c->fail(TRB_ERR_INVALID, "bad render description");
     if (d->rr_depth > 64) return c->fail(TRB_ERR_INVALID, "rr_depth > 64 is not supported");
+    if (rr_enabled(*d) && (max_depth_of(*d) < d->rr_depth || max_depth_of(*d) > 64))
+        return c->fail(TRB_ERR_INVALID, "Russian roulette: max_depth must lie in [rr_depth, 64]");
     return TRB_OK;
 }
 
@@ -451,8 +461,8 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
     if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
     const int spp_count = spp_end - spp_begin;
-    const int K = std::max(d->rr_depth - 1, 1);
-    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 22);
+    const int K = std::max(max_vertices_of(*d), 1);
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << (rr_enabled(*d) ? 21 : 22));
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     rc = ensure_wave(c, size_t(P), K);
@@ -650,9 +660,9 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
     if (n == 0) return TRB_OK;
     if (n > (size_t(1) << 24)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: at most 2^24 paths per call");
     cudaSetDevice(c->device);
-    const int K = std::max(d->rr_depth - 1, 1);
+    const int K = std::max(max_vertices_of(*d), 1);  // rr_depth-1, or max_depth-1 under Russian roulette
     // worst case draws per path: 2 + 6 + 3K (light) + 7K (eye) + 2
-    if (stride < size_t(10 + 10 * K)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: rng stride must be >= 10 + 10*(rr_depth-1)");
+    if (stride < size_t(10 + 10 * K)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: rng stride must be >= 10 + 10*K, K = max vertices per subpath");
     rc = ensure_wave(c, n, K);
     if (rc) return rc;
     DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_pix, d_draws;

@@ -61,6 +61,8 @@ struct Config {  // core.h:195-248 (the fields the offline BDPT path reads) + op
     int gpus = 1;                 // devices used by Renderer::render, sharded by sample index
     uint32_t seed = 260450963u;   // renderer.cpp:155
     int64_t waveSamples = 0;      // samples per wavefront, 0 = library default
+    bool russianRoulette = false; // bdpt.h:18 ships NO_RR 1; true runs the reference's own NO_RR 0 code (TRB_FLAG_RUSSIAN_ROULETTE)
+    int maxDepth = 0;             // depth cap under russianRoulette, 0 = TRB_RR_DEFAULT_MAX_DEPTH
 };
 
 // main.cpp:22-116. Returns renderer.realtime. Throws std::runtime_error("Invalid integrator type") for an unknown

@@ -97,11 +97,20 @@ typedef struct trb_render_desc {
     uint32_t seed;     /* key of the counter-based RNG; streams are keyed by (seed, pixel, sample, dim) */
     uint32_t flags;    /* TRB_FLAG_*                                                                    */
     int64_t wave_samples; /* samples per wavefront launch; 0 = library default                          */
+    int32_t max_depth; /* TRB_FLAG_RUSSIAN_ROULETTE only: hard cap on the walk depth (the reference has none,
+                          bdpt.h:66-67); 0 = TRB_RR_DEFAULT_MAX_DEPTH; rr_depth <= max_depth <= 64            */
+    int32_t reserved;
 } trb_render_desc;
 
 #define TRB_FLAG_NONE 0u
 #define TRB_FLAG_NO_JITTER 1u /* force the spp==1 pixel-centre path of renderer.cpp:169-180 */
 #define TRB_FLAG_NO_OVERLAP 2u /* one stream: every kernel runs alone (per-kernel timing for the roofline line); same results */
+/* Russian roulette as the reference writes it but compiles out (`#define NO_RR 1`, bdpt.h:18): past rr_depth a walk
+ * continues with probability rr = (luminance(throughput) < 0.01 ? 0.5 : 1) (bdpt.h:68,129,188,201), pdfs and reverse
+ * pdfs are scaled by the vertex's rr (bdpt.h:250,272,342,410,417,461-472).  Off (the default) is the shipped
+ * behaviour: rr_depth is a hard cap.  renderer.rrProb is read but never used by the reference (bdpt.h:40). */
+#define TRB_FLAG_RUSSIAN_ROULETTE 4u
+#define TRB_RR_DEFAULT_MAX_DEPTH 32
 
 typedef struct trb_stats {
     double ms_total;          /* device time of the whole call, CUDA events            */
@@ -190,7 +199,8 @@ int trb_trace_any(trb_context*, const trb_ray* rays, size_t n, uint8_t* out);   
 int trb_bsdf_batch(trb_context*, const trb_bsdf_query* q, size_t n, trb_bsdf_out* out); /* BSDF::{eval,pdf,sample,getType} */
 /* BDPTIntegrator::render on n given camera rays with injected random numbers: rng is n x stride floats,
  * consumed per path in the reference's order.  li_out: n x 3.  Light-tracing splats:
- * splat_pix n x (rr_depth-1) pixel indices (-1 = none), splat_rgb n x (rr_depth-1) x 3, slot = light depth-1.
+ * splat_pix n x K pixel indices (-1 = none), splat_rgb n x K x 3, slot = light depth-1, with K = max(rr_depth-1, 1)
+ * (max(max_depth-1, 1) under TRB_FLAG_RUSSIAN_ROULETTE); stride >= 10 + 10 K.
  * draws_out (optional): random numbers consumed per path. */
 int trb_bdpt_paths(trb_context*, const trb_render_desc*, const trb_ray* cam_rays, const float* rng, size_t n,
                    size_t stride, float* li_out, int32_t* splat_pix, float* splat_rgb, int32_t* draws_out);

@@ -319,6 +319,8 @@ struct Scene {
     v3 cam_o = V(0, 0.8f, 3.8f), cam_at = V(0, 0.8f, 0), cam_up = V(0, 1, 0);
     float fov = 30.f;
     int width = 800, height = 600, spp = 1, rrDepth = 5;
+    bool rrOn = false;   /* false = NO_RR 1, the shipped build */
+    int rrMaxDepth = 0;  /* 0 = no cap (the reference) */
 
     v3 vert(int t, int k) const { return vertices[tri_v[3 * t + k]]; }
     v3 norm(int t, int k) const { return normals[tri_n[3 * t + k]]; }
@@ -558,12 +560,17 @@ M4 inverse(const M4& M) { /* glm::inverse(mat4): cofactors, then one reciprocal 
 
 struct PathVertex { SurfaceInteraction hit; v3 throughput; float vcm, vc, rr; }; /* bdpt.h:24-35 */
 
-/* BDPTIntegrator (bdpt.h:37-518) with LIGHT_TRACING=0, PATH_TRACING=0, NO_RR=1 as the file is shipped */
+/* BDPTIntegrator (bdpt.h:37-518) with LIGHT_TRACING=0, PATH_TRACING=0, NO_RR=1 as the file is shipped (NO_RR=0 selectable, see m_noRR) */
 struct BDPT {
     const Scene& scene;
     std::vector<v3>* rgb;  /* RenderBuffer */
     int m_rrDepth;
-    explicit BDPT(const Scene& s, std::vector<v3>* fb) : scene(s), rgb(fb), m_rrDepth(s.rrDepth) {}
+    /* NO_RR is a #define (bdpt.h:18, shipped as 1); here a run-time switch so that the reference's Russian-roulette code
+     * (NO_RR 0) can be checked too.  m_maxDepth > 0 adds the device's hard depth cap, which the reference lacks (bdpt.h:66-67). */
+    bool m_noRR;
+    int m_maxDepth;
+    bool belowCap(int depth) const { return m_maxDepth <= 0 || depth < m_maxDepth; }
+    explicit BDPT(const Scene& s, std::vector<v3>* fb) : scene(s), rgb(fb), m_rrDepth(s.rrDepth), m_noRR(!s.rrOn), m_maxDepth(s.rrMaxDepth) {}
     float deg2radFov() const { return kPi / 180.f * scene.fov; }
 
     /* integrator.cpp:35-100 */
@@ -754,13 +761,14 @@ struct BDPT {
         if (emitterDirection.z <= 0.f) return;
         int depth = 1;
         float rrProbability = 1.f;
-        while (depth < m_rrDepth || (sampler.next() < rrProbability && false /* !NO_RR */)) {
+        while (depth < m_rrDepth || (sampler.next() < rrProbability && !m_noRR && belowCap(depth))) {
             SurfaceInteraction hit;
             if (!scene.intersect(wi, hit)) break;
             const float distSquared = hit.t * hit.t, absCosIn = std::fabs(hit.wo.z);
             vcm *= (distSquared / absCosIn);
             vc *= (1.f / absCosIn);
-            rrProbability = 1.f; /* NO_RR */
+            rrProbability = (depth + 1) < m_rrDepth ? 1.f : (getLuminance(throughput) < 0.01f ? 0.5f : 1.f); /* bdpt.h:129,201 */
+            if (m_noRR) rrProbability = 1.f;                                                                  /* bdpt.h:130-132,202-204 */
             unsigned hitBSDFType = getBSDF(hit)->combinedType;
             PathVertex lightVertex{hit, throughput, vcm, vc, rrProbability};
             if (!(hitBSDFType & EDelta)) connectToCamera(lightVertex);
@@ -783,7 +791,7 @@ struct BDPT {
         float vcm = scene.width * scene.height * (1.f / t1Pdf);
         int depth = 1;
         float rrProbability = 1.f;
-        while (depth < m_rrDepth || (sampler.next() < rrProbability && false /* !NO_RR */)) {
+        while (depth < m_rrDepth || (sampler.next() < rrProbability && !m_noRR && belowCap(depth))) {
             SurfaceInteraction hit;
             if (!scene.intersect(wi, hit)) break;
             const float distSquared = hit.t * hit.t, absCosIn = std::fabs(hit.wo.z);
@@ -805,7 +813,8 @@ struct BDPT {
                 }
                 break;
             }
-            rrProbability = 1.f; /* NO_RR */
+            rrProbability = (depth + 1) < m_rrDepth ? 1.f : (getLuminance(throughput) < 0.01f ? 0.5f : 1.f); /* bdpt.h:129,201 */
+            if (m_noRR) rrProbability = 1.f;                                                                  /* bdpt.h:130-132,202-204 */
             PathVertex eyeVertex{hit, throughput, vcm, vc, rrProbability};
             unsigned hitBSDFType = getBSDF(hit)->combinedType;
             if (!(hitBSDFType & EDelta)) {
@@ -854,6 +863,11 @@ void orc_set_config(void* h, const float* eye, const float* at, const float* up,
     Scene* s = static_cast<Scene*>(h);
     s->cam_o = V(eye[0], eye[1], eye[2]); s->cam_at = V(at[0], at[1], at[2]); s->cam_up = V(up[0], up[1], up[2]);
     s->fov = fov; s->width = width; s->height = height; s->spp = spp; s->rrDepth = rrDepth;
+}
+
+void orc_set_rr(void* h, int rr_on, int max_depth) {
+    Scene* s = static_cast<Scene*>(h);
+    s->rrOn = rr_on != 0; s->rrMaxDepth = max_depth;
 }
 
 void orc_bvh_order(void* h, int* order) { Scene* s = static_cast<Scene*>(h); std::copy(s->prims.begin(), s->prims.end(), order); }

@@ -59,6 +59,10 @@ class Oracle:
         self.L.orc_set_config(self.h, _p(eye), _p(at), _p(up), C.c_float(desc.fov_deg), int(desc.width), int(desc.height), int(desc.spp), int(desc.rr_depth))
         self.width, self.height = int(desc.width), int(desc.height)
 
+    def set_rr(self, on: bool, max_depth: int = 0):
+        """the reference's Russian-roulette code (NO_RR 0); max_depth > 0 adds the device's hard cap, 0 = none as in the reference"""
+        self.L.orc_set_rr(self.h, int(bool(on)), int(max_depth))
+
     def bvh_order(self):
         o = np.zeros(self.n_tris, np.int32)
         self.L.orc_bvh_order(self.h, _p(o))

@@ -16,10 +16,12 @@ import numpy as np
 HERE = Path(__file__).resolve().parent
 REF_LIB = HERE / "_ref" / "libtr_ref.so"
 REF_BIN = HERE / "_ref" / "tinyrender_ref"
+# the same sources with the reference's own Russian-roulette code compiled in (`make -C oracle ref_rr`: NO_RR 0, bdpt.h:18)
+REF_RR_LIB = HERE / "_ref" / "libtr_ref_rr.so"
 
 
-def available() -> bool:
-    return REF_LIB.exists()
+def available(rr: bool = False) -> bool:
+    return (REF_RR_LIB if rr else REF_LIB).exists()
 
 
 def write_toml(path, objfile, width=800, height=600, spp=1, rr_depth=5, eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0),
@@ -33,21 +35,21 @@ def write_toml(path, objfile, width=800, height=600, spp=1, rr_depth=5, eye=(0.0
     return str(path)
 
 
-_lib = None
+_libs = {}
 
 
-def _L():
-    global _lib
-    if _lib is None:
-        if not REF_LIB.exists():
-            raise FileNotFoundError(f"{REF_LIB} missing: run `make -C oracle ref` where /root/reference exists")
-        L = C.CDLL(str(REF_LIB))
+def _L(rr: bool = False):
+    if rr not in _libs:
+        path = REF_RR_LIB if rr else REF_LIB
+        if not path.exists():
+            raise FileNotFoundError(f"{path} missing: run `make -C oracle {'ref_rr' if rr else 'ref'}` where /root/reference exists")
+        L = C.CDLL(str(path))
         L.refh_open.restype = C.c_void_p
         L.refh_open.argtypes = [C.c_char_p]
         L.refh_render.restype = C.c_double
         L.refh_bvh_nodes.restype = C.c_int
-        _lib = L
-    return _lib
+        _libs[rr] = L
+    return _libs[rr]
 
 
 def _p(a):
@@ -57,8 +59,8 @@ def _p(a):
 class RefHarness:
     """The reference renderer opened on a TOML scene file (stdout chatter of the reference is kept)."""
 
-    def __init__(self, toml_path):
-        self.L = _L()
+    def __init__(self, toml_path, rr: bool = False):
+        self.L = _L(rr)
         self.h = C.c_void_p(self.L.refh_open(str(toml_path).encode()))
         if not self.h:
             raise RuntimeError(f"reference failed to open {toml_path}")
@@ -68,9 +70,9 @@ class RefHarness:
          self.height, self.spp, self.rr_depth) = [int(x) for x in c]
 
     @classmethod
-    def open_scene(cls, objfile, **kw):
+    def open_scene(cls, objfile, rr: bool = False, **kw):
         d = tempfile.mkdtemp(prefix="refh_")
-        return cls(write_toml(os.path.join(d, "scene.toml"), objfile, **kw))
+        return cls(write_toml(os.path.join(d, "scene.toml"), objfile, **kw), rr=rr)
 
     def close(self):
         if self.h:

@@ -41,6 +41,33 @@ def test_image_matches_reference_golden(trb, gpu_ctx, pin):
     assert abs(mean_ratio - 1) <= 0.01, mean_ratio
 
 
+def test_russian_roulette_image(trb, gpu_ctx):
+    """TRB_FLAG_RUSSIAN_ROULETTE at image level: (1) against a render by the reference built with its own Russian-
+    roulette code (NO_RR 0; tools/gen_image_golden.py --rr) when that pin is present; (2) unbiasedness against the
+    hard-capped estimator run to the same depth: roulette only re-weights the tail, so the two converge to the same
+    image (cap 32 on both sides)."""
+    ctx = gpu_ctx("caustic")
+    kw = dict(width=800, height=600, spp=128, rr_depth=5)
+    rr, st = ctx.render_bdpt(trb.render_desc(flags=trb.TRB_FLAG_RUSSIAN_ROULETTE, **kw))
+    pin = GOLD / "image_caustic_rr5_roulette.npz"
+    if pin.exists():
+        g = np.load(pin)
+        a, b = _box(rr, int(g["box"])), g["image"].astype(np.float64)
+        rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+        ratio = float(rr.mean() / float(g["mean"]))
+        print(f"roulette vs NO_RR-0 reference: relMSE {rel_mse:.2e}, mean ratio {ratio:.4f}")
+        assert rel_mse <= 3e-3 and abs(ratio - 1) <= 0.01
+    deep, st2 = ctx.render_bdpt(trb.render_desc(width=800, height=600, spp=128, rr_depth=trb.TRB_RR_DEFAULT_MAX_DEPTH))
+    a, b = _box(rr, 8), _box(deep, 8)
+    rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+    print(f"roulette vs hard cap {trb.TRB_RR_DEFAULT_MAX_DEPTH}: relMSE {rel_mse:.2e}, mean ratio {rr.mean() / deep.mean():.4f}; rays/sample "
+          f"{(st['rays_closest'] + st['rays_any']) / st['samples']:.1f} vs {(st2['rays_closest'] + st2['rays_any']) / st2['samples']:.1f}")
+    assert rel_mse <= 3e-3 and abs(rr.mean() / deep.mean() - 1) <= 0.01
+    # and it is not the capped render at rr_depth 5 (which loses the deeper bounces)
+    shallow, _ = ctx.render_bdpt(trb.render_desc(**kw))
+    assert rr.mean() > shallow.mean() * 1.01
+
+
 def test_sample_range_additivity(trb, gpu_ctx, scene_name):
     """disjoint sample ranges are plain summands (what sharding by sample index relies on)"""
     ctx = gpu_ctx(scene_name)

@@ -4,6 +4,8 @@ UNMODIFIED reference (tools/gen_golden.py).  Levels 1 and 2 of BASELINE.json's n
            occlusion booleans exact;
   level 2: BSDF eval/pdf/sample and whole-path Li / splats under injected random numbers within 1e-5 relative.
 """
+from pathlib import Path
+
 import numpy as np
 import pytest
 
@@ -67,6 +69,24 @@ def test_bsdf_matches_reference(trb, gpu_ctx, gold, scene_name):
     assert bad_rows.mean() <= 1e-3, f"{bad_rows.sum()} of {len(bad_rows)} BSDF rows off by more than {REL}: max {err.max()}"
 
 
+def _paths_agree(g_li, g_pix, g_rgb, li, pix, rgb):
+    """per-path agreement of (Li, splat pixel -> rgb map) within REL; the reference lists splats by pixel (its frame
+    buffer is the only record), and several light vertices of one path may land in the same pixel (their sum is held)"""
+    n = len(li)
+    scale = np.maximum(np.abs(g_li).max(1, keepdims=True), 1e-6)
+    li_ok = (np.abs(li - g_li) <= REL * np.maximum(scale, np.abs(li))).all(1)
+    ok = np.zeros(n, bool)
+    for i in range(n):
+        b = {int(p): g_rgb[i, k] for k, p in enumerate(g_pix[i]) if p >= 0}
+        a2 = {}
+        for k, p in enumerate(pix[i]):
+            if p >= 0:
+                a2[int(p)] = a2.get(int(p), 0) + rgb[i, k].astype(np.float64)
+        same = a2.keys() == b.keys() and all(np.all(np.abs(a2[p] - b[p]) <= REL * np.maximum(np.abs(b[p]).max(), 1e-12) * 4) for p in b)
+        ok[i] = same and li_ok[i]
+    return ok
+
+
 def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
     g = gold("paths", scene_name)
     desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
@@ -75,26 +95,49 @@ def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
     # a path agrees when its Li, every splat pixel and every splat value agree; paths are chaotic (one flipped
     # discrete decision changes everything after it), so the bar is: >= 99% of paths within REL, and the number
     # of random draws consumed (i.e. the sequence of decisions) identical for those.
-    scale = np.maximum(np.abs(g["li"]).max(1, keepdims=True), 1e-6)
-    li_ok = (np.abs(li - g["li"]) <= REL * np.maximum(scale, np.abs(li))).all(1)
-    rscale = np.maximum(np.abs(g["splat_rgb"]).max(2, keepdims=True), 1e-12)
-    # the reference lists splats by pixel (its frame buffer is the only record): compare as per-path pixel->rgb maps
-    ok = np.zeros(n, bool)
-    for i in range(n):
-        a = {int(p): rgb[i, k] for k, p in enumerate(pix[i]) if p >= 0}
-        b = {int(p): g["splat_rgb"][i, k] for k, p in enumerate(g["splat_pix"][i]) if p >= 0}
-        # several light vertices of one path may land in the same pixel: the reference's buffer holds their sum
-        a2 = {}
-        for k, p in enumerate(pix[i]):
-            if p >= 0:
-                a2[int(p)] = a2.get(int(p), 0) + rgb[i, k].astype(np.float64)
-        same = a2.keys() == b.keys() and all(np.all(np.abs(a2[p] - b[p]) <= REL * np.maximum(np.abs(b[p]).max(), 1e-12) * 4) for p in b)
-        ok[i] = same and li_ok[i]
+    ok = _paths_agree(g["li"], g["splat_pix"], g["splat_rgb"], li, pix, rgb)
     frac = ok.mean()
     draws_same = (draws == g["draws"])
     print(f"{scene_name}: paths ok {ok.sum()}/{n}, draws identical {draws_same.sum()}/{n}")
     assert frac >= 0.99, f"only {frac:.4f} of paths within {REL}"
     assert draws_same[ok].all()
+
+
+def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, scene_name):
+    """TRB_FLAG_RUSSIAN_ROULETTE against the reference built with its own Russian-roulette code enabled (NO_RR 0,
+    tools/gen_golden_rr.py).  The reference's walks are unbounded; the device caps them at max_depth, so the walks
+    the cap cuts short are compared with the restatement run with the same cap (pinned bit-exact to the reference
+    without a cap in tests/test_oracle.py)."""
+    oracle_port = pytest.importorskip("oracle_port")
+    g = gold("paths", scene_name + "_rr")
+    cap = trb.TRB_RR_DEFAULT_MAX_DEPTH
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]),
+                           flags=trb.TRB_FLAG_RUSSIAN_ROULETTE)
+    k = trb.max_vertices(desc)
+    assert k == cap - 1
+    stride = 10 + 10 * k
+    streams = np.stack([oracle_port.sampler_stream(int(s), stride) for s in g["seeds"]])
+    li, pix, rgb, draws = gpu_ctx(scene_name).bdpt_paths(desc, _rays(trb, g["rays"]), streams)
+    n = len(li)
+    assert pix.shape[1] == k
+    # (1) against the reference itself, on the walks the cap leaves alone
+    scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{scene_name}.npz")
+    orc = oracle_port.Oracle(scene)
+    orc.set_config(desc)
+    orc.set_rr(True, cap)
+    c_li, c_pix, c_rgb, c_draws = orc.bdpt_paths(g["rays"], k, injected=streams)
+    orc.close()
+    untouched = (c_draws == g["draws"]) & np.all(c_li == g["li"], 1)
+    assert untouched.mean() >= 0.98
+    kk = g["splat_pix"].shape[1]
+    ok_ref = _paths_agree(g["li"], g["splat_pix"], g["splat_rgb"], li, pix, rgb) & (draws == g["draws"])
+    # (2) against the capped restatement, every walk
+    ok_cap = _paths_agree(c_li, c_pix, c_rgb, li, pix, rgb) & (draws == c_draws)
+    print(f"{scene_name} RR: vs reference {ok_ref[untouched].sum()}/{untouched.sum()} untouched walks, vs capped restatement {ok_cap.sum()}/{n}; "
+          f"mean draws {draws.mean():.1f}, splat columns used {int((pix >= 0).sum(1).max())} (reference {kk})")
+    assert ok_ref[untouched].mean() >= 0.99
+    assert ok_cap.mean() >= 0.99
+    assert draws.mean() > 45  # the walks do run past rr_depth
 
 
 @pytest.fixture(scope="session")

@@ -56,6 +56,25 @@ def test_bsdf_bit_exact(orc, gold, scene_name):
         assert np.array_equal(out.view(np.uint32), g["out"][sel].view(np.uint32)), f"material {m}"
 
 
+def test_bdpt_paths_russian_roulette_bit_exact(trb, orc, gold, scene_name):
+    """the restatement's NO_RR 0 branch against the reference built with its own Russian-roulette code enabled
+    (oracle/Makefile ref_rr; vectors by tools/gen_golden_rr.py)"""
+    g = gold("paths", scene_name + "_rr")
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
+    orc.set_config(desc)
+    orc.set_rr(True, 0)
+    try:
+        k = g["splat_pix"].shape[1]
+        li, pix, rgb, nd = orc.bdpt_paths(g["rays"], k, seeds=g["seeds"])
+    finally:
+        orc.set_rr(False)
+    assert np.array_equal(nd, g["draws"])
+    assert nd.mean() > 45  # walks really run past rr_depth 4 (the capped build draws < 30 per path there)
+    assert np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+    assert np.array_equal(pix, g["splat_pix"])
+    assert np.array_equal(rgb.view(np.uint32), g["splat_rgb"].view(np.uint32))
+
+
 def test_bdpt_paths_bit_exact(trb, orc, gold, scene_name):
     g = gold("paths", scene_name)
     desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))

@@ -47,7 +47,23 @@ def head_render(name="hardlight_rr8_head", scene="hardlight", obj="data/a5/bonus
     print(name, "mean", rgb.mean())
 
 
+def rr_render(name="caustic_rr5_roulette", scene="caustic", obj="data/a5/cbox/mesh/cbox_mirror.obj", rr=5, spp=64):
+    """Level-3 pin for TRB_FLAG_RUSSIAN_ROULETTE: a render by the reference with its own Russian-roulette code enabled
+    (oracle/_ref/libtr_ref_rr.so = the same sources with NO_RR 0, `make -C oracle ref_rr`), through Renderer::render."""
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import refh
+    rh = refh.RefHarness.open_scene(str(REF / obj), rr=True, width=800, height=600, spp=spp, rr_depth=rr)
+    rgb, sec = rh.render()
+    rh.close()
+    np.savez_compressed(ROOT / "tests" / "golden" / f"image_{name}.npz", image=box_filter(rgb), scene=scene, rr_depth=rr, width=800,
+                        height=600, box=BOX, source=f"oracle/_ref/libtr_ref_rr.so (NO_RR 0) {obj} rrDepth {rr} spp {spp}",
+                        mean=np.float64(rgb.mean()))
+    print(name, "mean", rgb.mean(), "render s", sec)
+
+
 def main():
+    if "--rr" in sys.argv:
+        return rr_render()
     if "--head" in sys.argv:
         i = sys.argv.index("--head")
         return head_render(exr=sys.argv[i + 1] if len(sys.argv) > i + 1 else None)
