@@ -139,22 +139,45 @@ def cpu_reference_step_factory(workload: dict, budget_s: float = 8.0):
             w, h = w // 2, h // 2
         rh = refh.RefHarness.open_scene(obj, width=w, height=h, spp=1, rr_depth=workload["rr_depth"])
 
-        def run():
-            _, s = rh.render()
-            return w * h, s
-        info = dict(kind="reference", cores=threads, sample=f"{w}x{h} film, 1 spp, rrDepth {workload['rr_depth']}, whole frame through "
+        def run(want_image=False):
+            img, s = rh.render()
+            return (w * h, s, img) if want_image else (w * h, s)
+        info = dict(film=(w, h), kind="reference", cores=threads, sample=f"{w}x{h} film, 1 spp, rrDepth {workload['rr_depth']}, whole frame through "
                     f"Renderer::render of the unmodified reference (oracle/_ref), {threads} threads")
         return run, info
     import oracle_port
     w, h = 256, 256
     orc = oracle_port.Oracle(scene)
 
-    def run():
+    def run(want_image=False):
         t0 = time.perf_counter()
-        orc.render(trb.render_desc(width=w, height=h, spp=1, rr_depth=workload["rr_depth"]), threads=hw)
-        return w * h, time.perf_counter() - t0
-    info = dict(kind="port", cores=hw, sample=f"{w}x{h} film, 1 spp, rrDepth {workload['rr_depth']}, oracle/bdpt_oracle.cpp, {hw} threads")
+        img, _ = orc.render(trb.render_desc(width=w, height=h, spp=1, rr_depth=workload["rr_depth"]), threads=hw)
+        s = time.perf_counter() - t0
+        return (w * h, s, img) if want_image else (w * h, s)
+    info = dict(film=(w, h), kind="port", cores=hw, sample=f"{w}x{h} film, 1 spp, rrDepth {workload['rr_depth']}, oracle/bdpt_oracle.cpp, {hw} threads")
     return run, info
+
+
+def rel_mse(img, ref):
+    """per-pixel relative MSE, mean over pixels and channels of (I - R)^2 / (R^2 + 1e-2)"""
+    a, b = np.asarray(img, np.float64), np.asarray(ref, np.float64)
+    return float(np.mean((a - b) ** 2 / (b * b + 1e-2)))
+
+
+def equal_time_relmse(trb, ctx, wl, w, h, cpu_img, cpu_s, gpu_rate):
+    """BASELINE.json's "relMSE at equal time" (SURVEY 8(d)): the reference's CPU frame took cpu_s seconds; render on
+    the GPU for about as long (spp chosen from the measured device rate), and compare both against a converged GPU image
+    (independent seed, >= 8x the equal-time spp) that passes level-3 parity (tests/test_gpu_image.py)."""
+    spp_gpu = int(max(1, min(round(cpu_s * gpu_rate / (w * h)), 4096)))
+    spp_ref = int(min(max(8 * spp_gpu, 1024), 16384))
+    t0 = time.perf_counter()
+    img, _ = ctx.render_bdpt(trb.render_desc(width=w, height=h, spp=spp_gpu, rr_depth=wl["rr_depth"]))
+    gpu_s = time.perf_counter() - t0
+    ref, _ = ctx.render_bdpt(trb.render_desc(width=w, height=h, spp=spp_ref, rr_depth=wl["rr_depth"], seed=977))
+    return {"film": f"{w}x{h}", "cpu_seconds": cpu_s, "cpu_spp": 1, "relmse_cpu": rel_mse(cpu_img, ref), "gpu_seconds": gpu_s,
+            "gpu_spp": spp_gpu, "relmse_gpu": rel_mse(img, ref), "reference_image": f"this library, {spp_ref} spp, seed 977",
+            "definition": "mean over pixels and channels of (I - R)^2 / (R^2 + 1e-2); the converged image's own noise "
+                          "(1/8 of the GPU image's variance or less) is included in both figures"}
 
 
 def run_reference_arm(args):
@@ -163,6 +186,7 @@ def run_reference_arm(args):
         return
     wl = WORKLOADS[args.workload]
     run, info = cpu_reference_step_factory(wl)
+    info.pop("film", None)
     for _ in range(args.warmup):
         run()
     tot_s, tot_n = 0.0, 0
@@ -355,8 +379,11 @@ def run_ours(args):
             try:
                 with quiet_stdout():
                     run, info = cpu_reference_step_factory(wl)
-                    n, s = run()
+                    n, s, cpu_img = run(want_image=True)
+                fw, fh = info.pop("film")
                 out["cpu_baseline"] = dict(info, value=n / s / 1e6, unit=UNIT)
+                if wl["scene"] is not None:  # (the tess workload times the CPU on a smaller instance of the scene: no common image)
+                    out["equal_time"] = equal_time_relmse(trb, ctx, wl, fw, fh, cpu_img, s, value * 1e6)
             except Exception as e:  # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "unavailable", "sample": str(e)}
         print(json.dumps(out))
