@@ -37,6 +37,9 @@ WORKLOADS = {
                     desc="caustic scene (glass sphere + area light, 32536 tris) 1024x1024 BDPT rrDepth 8"),
     "hardlight": dict(scene="scene_hardlight.npz", width=1024, height=1024, rr_depth=16,
                       desc="hard-light scene (occluded emitter, 36404 tris) 1024x1024 BDPT rrDepth 16"),
+    "cbox4k": dict(scene="scene_caustic.npz", width=3840, height=2160, rr_depth=8,
+                   desc="configs[3]: Cornell box (cbox_mirror.obj) 3840x2160 BDPT rrDepth 8, partitioned by sample index, one reduce of the "
+                        "99.5 MB frame buffer (4096 spp in total = --spp 512 on 8 GPUs)"),
     "tess": dict(scene=None, tris=10_000_000, width=1024, height=1024, rr_depth=8,
                  desc="synthetic tessellated scene (tools/gen_tess_scene.py --tris 10000000 --seed 1: three displaced spheres, mirror/glass/"
                       "phong + Mixture floor) 1024x1024 BDPT rrDepth 8"),

@@ -1,5 +1,5 @@
 """tools/ncu_lines.py -- per-source-line hot spots from an .ncu-rep (needs -lineinfo and --import-source on):
-    python tools/ncu_lines.py <report.ncu-rep> [launch-index] [top-N]
+    python tools/ncu_lines.py <report.ncu-rep> [launch-index] [top-N] [inst]      (inst: sort by instruction share)
 prints share of warp instructions, average active threads and stall samples per CUDA source line."""
 import csv, subprocess, sys, io
 rep = sys.argv[1]; top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
@@ -18,5 +18,6 @@ for r in rows:
         except ValueError: pass
 tot = sum(d[0] for d in data); ts = sum(d[2] for d in data)
 print(f"total warp inst {tot}, thread inst/warp inst {sum(d[1] for d in data)/max(tot,1):.2f}, samples {ts}")
-for d in sorted(data, key=lambda x: -x[2])[:top]:
+by = 0 if (len(sys.argv) > 4 and sys.argv[4] == "inst") else 2
+for d in sorted(data, key=lambda x: -x[by])[:top]:
     print(f"inst {d[0]/tot:6.3f} thr {d[1]/max(d[0],1):5.1f} samp {d[2]/max(ts,1):6.3f} {d[3]}:{d[4]:<4d} {d[5]}")
