@@ -80,6 +80,23 @@ def test_sample_range_additivity(trb, gpu_ctx, scene_name):
     assert full.mean() > 0.01
 
 
+def test_4k_film_sharded_by_sample_index(trb, gpu_ctx):
+    """configs[3] at its film size (3840x2160, 99.5 MB frame buffer): two sample shards accumulated == one render, and the
+    downsampled image agrees with an 800x600 render of the same camera (same estimator, same aspect handling)"""
+    ctx = gpu_ctx("caustic")
+    kw = dict(width=3840, height=2160, spp=2, rr_depth=8)
+    full, st = ctx.render_bdpt(trb.render_desc(**kw))
+    assert st["samples"] == 3840 * 2160 * 2
+    ctx.render_bdpt(trb.render_desc(spp_begin=0, spp_end=1, **kw), download=False)
+    parts, _ = ctx.render_bdpt(trb.render_desc(spp_begin=1, spp_end=2, **kw), accumulate=True)
+    assert np.allclose(full, parts, rtol=2e-5, atol=2e-6), float(np.abs(full - parts).max())
+    small, _ = ctx.render_bdpt(trb.render_desc(width=1920, height=1080, spp=8, rr_depth=8))
+    a, b = _box(full, 48), _box(small, 24)   # both 80 x 45
+    rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+    print(f"4K vs 1080p: relMSE {rel_mse:.2e}, mean ratio {full.mean() / small.mean():.4f}")
+    assert rel_mse <= 3e-3 and abs(full.mean() / small.mean() - 1) <= 0.01
+
+
 def test_wave_size_independence(trb, gpu_ctx, scene_name):
     ctx = gpu_ctx(scene_name)
     kw = dict(width=200, height=150, spp=4, rr_depth=8)
