@@ -53,6 +53,19 @@ class RenderDesc(C.Structure):
                 ("wave_samples", C.c_int64), ("max_depth", C.c_int32), ("reserved", C.c_int32)]
 
 
+class PathDesc(C.Structure):
+    """trb_path_desc: PathTracerIntegrator settings (main.cpp:94-102 defaults)"""
+    _fields_ = [("is_explicit", C.c_int32), ("max_depth", C.c_int32), ("rr_prob", C.c_float), ("emitter_samples", C.c_int32),
+                ("bsdf_samples", C.c_int32)]
+
+
+def path_desc(is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, bsdf_samples=0) -> PathDesc:
+    return PathDesc(int(bool(is_explicit)), int(max_depth), float(rr_prob), int(emitter_samples), int(bsdf_samples))
+
+
+TRB_PT_DEFAULT_DEPTH_CAP = 64
+
+
 class Stats(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_trace_closest", C.c_double), ("ms_trace_any", C.c_double),
                 ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
@@ -323,6 +336,25 @@ class Context:
         self._chk(self._L.trb_bdpt_paths(self._h, C.byref(desc), _ptr(cam_rays), _ptr(rng), C.c_size_t(n), C.c_size_t(stride),
                                          _ptr(li), _ptr(pix), _ptr(rgb), _ptr(draws)))
         return li, pix, rgb, draws
+
+    def render_path(self, desc: RenderDesc, pd: PathDesc, accumulate: bool = False, download: bool = True):
+        """Renderer::render with the PathTracerIntegrator (path.h). Returns (H x W x 3 float32 | None, stats)."""
+        st = Stats()
+        img = np.zeros((desc.height, desc.width, 3), np.float32) if download else None
+        self._chk(self._L.trb_render_path(self._h, C.byref(desc), C.byref(pd), int(accumulate), _ptr(img) if download else None, C.byref(st)))
+        return img, st.as_dict()
+
+    def path_paths(self, desc: RenderDesc, pd: PathDesc, cam_rays: np.ndarray, rng: np.ndarray):
+        """PathTracerIntegrator::render on given camera rays with injected random numbers (n x stride)."""
+        cam_rays = np.ascontiguousarray(cam_rays, RAY_DTYPE)
+        rng = np.ascontiguousarray(rng, np.float32)
+        n, stride = rng.shape
+        assert n == len(cam_rays)
+        li = np.zeros((n, 3), np.float32)
+        draws = np.zeros(n, np.int32)
+        self._chk(self._L.trb_path_paths(self._h, C.byref(desc), C.byref(pd), _ptr(cam_rays), _ptr(rng), C.c_size_t(n), C.c_size_t(stride),
+                                         _ptr(li), _ptr(draws)))
+        return li, draws
 
     def render_bdpt(self, desc: RenderDesc, accumulate: bool = False, download: bool = True):
         """Renderer::render (offline branch) with the BDPT integrator. Returns (H x W x 3 float32 | None, stats)."""

@@ -102,9 +102,10 @@ struct Rng {
     const float* inj;  // parity mode pointer to this path's row, or nullptr
     uint32_t key;      // hash of (seed, pixel, sample)
     uint32_t ctr;
+    uint32_t lim;      // parity mode: floats in the row; past its end every draw reads 0.99 (ends any roulette)
     __device__ __forceinline__ float next() {
         uint32_t c = ctr++;
-        if (inj) return inj[c];
+        if (inj) return c < lim ? inj[c] : 0.99f;
         uint32_t h = mix32(key ^ mix32(c * 0x9e3779b9u + 0x85ebca6bu));
         return float(h >> 8) * (1.0f / 16777216.0f);
     }
@@ -114,6 +115,7 @@ __device__ __forceinline__ Rng make_rng(const WaveParams& p, int slot, uint32_t 
     r.inj = p.inject_rng ? p.inject_rng + size_t(slot) * p.inject_stride : nullptr;
     r.key = mix32(p.seed ^ mix32(pixel * 0x9e3779b9u + 0x7f4a7c15u) ^ mix32(sample * 0x85ebca6bu + 0xc2b2ae35u));
     r.ctr = ctr;
+    r.lim = uint32_t(p.inject_stride);
     return r;
 }
 
@@ -167,6 +169,7 @@ __device__ __forceinline__ Surf make_surf(const SceneDev& sc, const HitT& h, con
 struct EmitterSample {
     V3 pos, n, radiance;
     float sel_pdf, area_pdf;
+    int id;   // emitter index (Integrator::selectEmitter)
 };
 
 __device__ __forceinline__ EmitterSample sample_emitter(const SceneDev& sc, Rng& rng) {
@@ -176,6 +179,7 @@ __device__ __forceinline__ EmitterSample sample_emitter(const SceneDev& sc, Rng&
     uint32_t id = uint32_t(s0 * float(ne));
     id = min(id, ne - 1u);
     es.sel_pdf = 1.f / float(ne);
+    es.id = int(id);
     const float4* ep = reinterpret_cast<const float4*>(sc.emitters + id);
     float4 e0 = __ldg(ep), e1 = __ldg(ep + 1);
     es.radiance = mk(e0.x, e0.y, e0.z);

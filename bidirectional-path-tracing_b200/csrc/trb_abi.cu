@@ -11,6 +11,7 @@
 #include "../../include/trb.h"
 #include "host/tr_host.h"
 #include "kernels/bdpt_kernels.cuh"
+#include "kernels/pt_kernels.cuh"
 #include "kernels/trace_warp.cuh"
 #include "kernels/trace_coop.cuh"
 
@@ -68,6 +69,7 @@ struct trb_context {
     DevBuf<float4> st_t, st_v;
     DevBuf<LightVertex> lv;
     DevBuf<int32_t> nlv, q_a, q_b, q_conn;
+    DevBuf<uint32_t> pt_ctr;             // path tracer: one counter per queue / traversal launch
     DevBuf<EyeVertex> ev;
     DevBuf<Pending> spend, spend2;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
@@ -157,9 +159,9 @@ inline int max_depth_of(const trb_render_desc& d) {
 }
 inline int max_vertices_of(const trb_render_desc& d) { return std::max(max_depth_of(d) - 1, 0); }
 
-int ensure_wave(trb_context* c, size_t P, int K) {
+int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     size_t kk = size_t(std::max(K, 1));
-    size_t shadow_cap = P * (kk + 1);
+    size_t shadow_cap = shadow ? P * (kk + 1) : 1;  // (the path tracer traces closest hits only)
     TRB_CUDA(c, c->cam_ray.alloc(P)); TRB_CUDA(c, c->ray.alloc(P));
     TRB_CUDA(c, c->hit.alloc(P)); TRB_CUDA(c, c->hit0.alloc(P));
     TRB_CUDA(c, c->st_t.alloc(P)); TRB_CUDA(c, c->st_v.alloc(P));
@@ -484,6 +486,211 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     return TRB_OK;
 }
 
+
+// ---- PathTracerIntegrator on the same wave buffers (kernels/pt_kernels.cuh; path.h:15-262) ------------------------------
+__global__ void k_read_draws(const float4* __restrict__ st_v, int n, int32_t* __restrict__ out);  // defined with the parity entry points
+
+// rays traced by a path-tracer wave = P primary rays + the sizes of all traced queues
+__global__ void k_pt_fold_stats(const uint32_t* __restrict__ ctr, uint32_t n_ray, uint32_t P, unsigned long long* __restrict__ stats) {
+    __shared__ unsigned long long part[256];
+    unsigned long long s = 0;
+    for (uint32_t i = threadIdx.x; i < n_ray; i += blockDim.x) s += ctr[i];
+    part[threadIdx.x] = s;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long t = P;
+        for (int i = 0; i < 256; ++i) t += part[i];
+        stats[0] += t;
+    }
+}
+
+int check_path_desc(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, PtParams* out) {
+    int rc = check_desc(c, d);
+    if (rc) return rc;
+    if (!pd) return c->fail(TRB_ERR_INVALID, "no path description");
+    if (pd->emitter_samples < 0 || pd->emitter_samples > 16 || pd->bsdf_samples < 0 || pd->bsdf_samples > 16)
+        return c->fail(TRB_ERR_INVALID, "emitter_samples / bsdf_samples must lie in [0, 16]");
+    if (pd->max_depth < -1 || pd->max_depth > 256) return c->fail(TRB_ERR_INVALID, "path max_depth must lie in [-1, 256]");
+    const int cap = d->max_depth > 0 ? d->max_depth : TRB_PT_DEFAULT_DEPTH_CAP;
+    if (cap > 256) return c->fail(TRB_ERR_INVALID, "depth cap (trb_render_desc.max_depth) must be <= 256");
+    out->is_explicit = pd->is_explicit ? 1 : 0; out->max_depth = pd->max_depth; out->rr_depth = d->rr_depth; out->rr_prob = pd->rr_prob;
+    out->emitter_samples = pd->emitter_samples; out->bsdf_samples = pd->bsdf_samples;
+    // stack levels: a bounded recursion (maxDepth >= 0) enters maxDepth calls and makes one more that only draws its roulette
+    // number (path.h:70-74), the roulette-driven one gets the cap
+    out->cap = pd->max_depth >= 0 ? pd->max_depth + 1 : cap;
+    return TRB_OK;
+}
+
+int run_pt_wave(trb_context* c, const WaveRun& w, const PtParams& pt, const trb::CameraDev& cam, int64_t wave_base, int P, int spp_begin, int spp_count) {
+    const trb_render_desc& d = *w.desc;
+    WaveParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.sc = c->sc; p.cam = cam;
+    p.P = P; p.K = pt.cap; p.rr_depth = d.rr_depth; p.max_depth = pt.cap; p.spp = d.spp; p.spp_begin = spp_begin; p.spp_count = spp_count;
+    p.wave_base = wave_base; p.seed = d.seed; p.flags = d.flags;
+    p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
+    p.accum = w.d_accum;
+    p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p;
+    const int D = pt.cap, M = pt.emitter_samples, NB = pt.bsdf_samples;
+    // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then the other queues, then one fetch cursor per traversal launch
+    const size_t n_ray = size_t(D) * size_t(1 + M + NB) + size_t(pt.max_depth >= 0 ? pt.max_depth : 0) + 8;
+    const size_t n_other = size_t(D) + 8, n_fetch = n_ray + 8;
+    TRB_CUDA(c, c->pt_ctr.alloc(n_ray + n_other + n_fetch));
+    TRB_CUDA(c, cudaMemsetAsync(c->pt_ctr.p, 0, (n_ray + n_other + n_fetch) * sizeof(uint32_t), c->stream));
+    size_t i_ray = 0, i_other = n_ray, i_fetch = n_ray + n_other;
+    auto ray_ctr = [&]() { return c->pt_ctr.p + i_ray++; };
+    auto other_ctr = [&]() { return c->pt_ctr.p + i_other++; };
+    auto fetch_ctr = [&]() { return c->pt_ctr.p + i_fetch++; };
+    unsigned long long* visit = nullptr;
+#ifdef TRB_COUNTERS
+    visit = c->d_stats.p + 2;
+#endif
+    const int gP = grid_exact(size_t(P));
+    k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
+    int32_t* q_cur = c->q_a.p; int32_t* q_next = c->q_b.p;
+    uint32_t* n_cur = other_ctr();
+    k_pt_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p, q_cur, n_cur); c->mark(LK_LOGIC);
+    if (!pt.is_explicit) {
+        for (int depth = 0; depth <= std::max(pt.max_depth, 0); ++depth) {
+            uint32_t* n_out = ray_ctr();
+            k_pt_implicit<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, q_cur, n_cur, q_next, n_out); c->mark(LK_LOGIC);
+            launch_closest(c, p.ray, q_next, n_out, 0u, p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
+            std::swap(q_cur, q_next); n_cur = n_out;
+        }
+    } else {
+        // forward: descend, one stack level per depth
+        for (int depth = 0; depth < D; ++depth) {
+            uint32_t* n_try = ray_ctr();
+            uint32_t* n_next = other_ctr();
+            k_pt_begin<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, q_cur, n_cur, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+            launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
+            k_pt_check<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, c->q_conn.p, n_try, q_next, n_next, c->d_stats.p); c->mark(LK_LOGIC);
+            std::swap(q_cur, q_next); n_cur = n_next;
+        }
+        // backward: direct illumination and the combination, deepest level first
+        for (int depth = D - 1; depth >= 0; --depth) {
+            for (int e = 0; e < M; ++e) {
+                uint32_t* n_try = ray_ctr();
+                k_pt_emitter_gen<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, e, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+                launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
+                k_pt_emitter_resolve<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+            }
+            for (int b = 0; b < NB; ++b) {
+                uint32_t* n_try = ray_ctr();
+                k_pt_bsdf_gen<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+                launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
+                k_pt_bsdf_resolve<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+            }
+            k_pt_combine<<<gP, TRB_BLOCK, 0, c->stream>>>(p, pt, depth); c->mark(LK_LOGIC);
+        }
+    }
+    k_pt_fold_stats<<<1, 256, 0, c->stream>>>(c->pt_ctr.p, uint32_t(i_ray), uint32_t(P), c->d_stats.p); c->mark(LK_LOGIC);
+    TRB_CUDA(c, cudaGetLastError());
+    return TRB_OK;
+}
+
+int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, int accumulate, float* d_rgb, trb_stats* stats) {
+    PtParams pt;
+    int rc = check_path_desc(c, d, pd, &pt);
+    if (rc) return rc;
+    cudaSetDevice(c->device);
+    const int64_t npix = int64_t(d->width) * d->height;
+    const int spp_begin = d->spp_begin;
+    const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
+    if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
+    const int spp_count = spp_end - spp_begin;
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 21);
+    const int64_t total = npix * spp_count;
+    P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
+    rc = ensure_wave(c, size_t(P), pt.is_explicit ? pt.cap : 1, /*shadow=*/false);
+    if (rc) return rc;
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    c->mark(LK_LOGIC);
+    if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
+    WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
+    for (int64_t base = 0; base < total; base += P) {
+        int n = int(std::min<int64_t>(P, total - base));
+        rc = run_pt_wave(c, w, pt, cam, base, n, spp_begin, spp_count);
+        if (rc) return rc;
+    }
+    c->mark(LK_LOGIC);
+    if (stats) collect_stats(c, stats, uint64_t(total));
+    return TRB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int trb_render_path_device(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, int accumulate, float* d_rgb, trb_stats* stats) {
+    if (!c || !d_rgb) return TRB_ERR_INVALID;
+    int rc = render_path_impl(c, d, pd, accumulate, d_rgb, stats);
+    if (rc) return rc;
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_render_path(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, int accumulate, float* rgb_out, trb_stats* stats) {
+    if (!c || !d) return TRB_ERR_INVALID;
+    if (d->width <= 0 || d->height <= 0) return c->fail(TRB_ERR_INVALID, "bad film size");
+    cudaSetDevice(c->device);
+    size_t nf = size_t(d->width) * d->height * 3;
+    bool fresh = c->fb.n < nf;
+    TRB_CUDA(c, c->fb.alloc(nf));
+    if (fresh && accumulate) TRB_CUDA(c, cudaMemsetAsync(c->fb.p, 0, nf * sizeof(float), c->stream));
+    int rc = render_path_impl(c, d, pd, accumulate, c->fb.p, stats);
+    if (rc) return rc;
+    if (rgb_out) TRB_CUDA(c, cudaMemcpyAsync(rgb_out, c->fb.p, nf * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+/* PathTracerIntegrator::render on n given camera rays with injected random numbers (n x stride, consumed in the reference's
+ * depth-first order).  li_out: n x 3; draws_out (optional): numbers consumed per path. */
+int trb_path_paths(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, const trb_ray* cam_rays, const float* rng, size_t n,
+                   size_t stride, float* li_out, int32_t* draws_out) {
+    if (!c || !cam_rays || !rng || !li_out) return TRB_ERR_INVALID;
+    PtParams pt;
+    int rc = check_path_desc(c, d, pd, &pt);
+    if (rc) return rc;
+    if (n == 0) return TRB_OK;
+    if (n > (size_t(1) << 24)) return c->fail(TRB_ERR_INVALID, "trb_path_paths: at most 2^24 paths per call");
+    cudaSetDevice(c->device);
+    if (stride < 8) return c->fail(TRB_ERR_INVALID, "trb_path_paths: rng stride must be >= 8");
+    rc = ensure_wave(c, n, pt.is_explicit ? pt.cap : 1, /*shadow=*/false);
+    if (rc) return rc;
+    DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_draws;
+    TRB_CUDA(c, d_rays.alloc(n)); TRB_CUDA(c, d_rng.alloc(n * stride)); TRB_CUDA(c, d_acc.alloc(n * 3)); TRB_CUDA(c, d_draws.alloc(n));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rays.p, cam_rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
+    WaveRun w{d, d_acc.p, nullptr, d_rays.p, d_rng.p, int(stride), true};
+    rc = run_pt_wave(c, w, pt, cam, 0, int(n), 0, d->spp);
+    if (rc == TRB_OK) {
+        k_read_draws<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->st_v.p, int(n), d_draws.p);
+        std::vector<int32_t> draws(n);
+        cudaError_t e = cudaMemcpyAsync(li_out, d_acc.p, d_acc.bytes(), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(draws.data(), d_draws.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = c->cuda_fail(e, "trb_path_paths download");
+        else if (draws_out) std::copy(draws.begin(), draws.end(), draws_out);
+    }
+    d_rays.release(); d_rng.release(); d_acc.release(); d_draws.release();
+    return rc;
+}
+
+}  // extern "C"
+
+namespace {
 }  // namespace
 
 extern "C" {

@@ -112,6 +112,18 @@ typedef struct trb_render_desc {
 #define TRB_FLAG_RUSSIAN_ROULETTE 4u
 #define TRB_RR_DEFAULT_MAX_DEPTH 32
 
+/* PathTracerIntegrator settings (Config::integratorSettings.pt, core.h:229-236; TOML defaults main.cpp:94-102).
+ * rrDepth comes from trb_render_desc.rr_depth.  The reference recurses without bound when max_depth == -1; the device
+ * keeps at most trb_render_desc.max_depth vertices per path (0 = TRB_PT_DEFAULT_DEPTH_CAP, <= 256). */
+typedef struct trb_path_desc {
+    int32_t is_explicit;     /* renderer.isExplicit (default true): recursiveExplicit, else recursiveImplicit      */
+    int32_t max_depth;       /* renderer.maxDepth (default -1 = Russian roulette past rrDepth with rr_prob)         */
+    float rr_prob;           /* renderer.rrProb (default 0.95)                                                      */
+    int32_t emitter_samples; /* renderer.emitterSamples (default 1), 0..16                                          */
+    int32_t bsdf_samples;    /* renderer.bsdfSamples (default 0), 0..16                                             */
+} trb_path_desc;
+#define TRB_PT_DEFAULT_DEPTH_CAP 64
+
 typedef struct trb_stats {
     double ms_total;          /* device time of the whole call, CUDA events            */
     double ms_trace_closest;  /* summed over launches                                   */
@@ -192,6 +204,16 @@ int trb_render_bdpt(trb_context*, const trb_render_desc*, int accumulate, float*
 /* Same, result left in a caller-provided DEVICE buffer (width*height*3 floats) - used for the multi-GPU
  * NCCL reduce and the device-resident throughput measurement. */
 int trb_render_bdpt_device(trb_context*, const trb_render_desc*, int accumulate, float* d_rgb, trb_stats* stats);
+
+/* The reference's unidirectional path tracer (src/integrators/path.h:15-262, `type = "path"`) on the same wavefront:
+ * the independent estimator the reference checks BDPT against (cbox_bdpt_path.toml).  Same conventions as trb_render_bdpt. */
+int trb_render_path(trb_context*, const trb_render_desc*, const trb_path_desc*, int accumulate, float* rgb_out, trb_stats* out);
+int trb_render_path_device(trb_context*, const trb_render_desc*, const trb_path_desc*, int accumulate, float* d_rgb, trb_stats* out);
+/* PathTracerIntegrator::render on n given camera rays with injected random numbers (n x stride floats, consumed in the
+ * reference's depth-first order); li_out n x 3; draws_out optional.  A path that needs more than `stride` numbers reads
+ * 0.99 past the end of its row (which ends every roulette); draws_out then exceeds stride. */
+int trb_path_paths(trb_context*, const trb_render_desc*, const trb_path_desc*, const trb_ray* cam_rays, const float* rng, size_t n,
+                   size_t stride, float* li_out, int32_t* draws_out);
 
 /* Parity entry points (north_star levels 1 and 2). Host buffers in, host buffers out. */
 int trb_trace_closest(trb_context*, const trb_ray* rays, size_t n, trb_hit* out);   /* accel.h:125-172 */

@@ -85,6 +85,7 @@ struct SurfaceInteraction {
     float t = 0, u = 0, v = 0;
     size_t shapeID = 0, primID = 0;
     Frame frameNs;
+    v3 ng = V(0);  /* frameNg.n (accel.h:161); only path.h's bsdf-sampling estimator reads it */
     int matID = 0;
 };
 
@@ -319,6 +320,9 @@ struct Scene {
     v3 cam_o = V(0, 0.8f, 3.8f), cam_at = V(0, 0.8f, 0), cam_up = V(0, 1, 0);
     float fov = 30.f;
     int width = 800, height = 600, spp = 1, rrDepth = 5;
+    /* PathTracerIntegrator settings (main.cpp:94-102 defaults) */
+    bool ptExplicit = true; int ptMaxDepth = -1; float ptRRProb = 0.95f; int ptEmitterSamples = 1, ptBsdfSamples = 0;
+    int ptDepthCap = 0;  /* > 0: the device's hard cap on the recursion depth (the reference has none); 0 = none */
     bool rrOn = false;   /* false = NO_RR 1, the shipped build */
     int rrMaxDepth = 0;  /* 0 = no cap (the reference) */
 
@@ -456,6 +460,7 @@ struct Scene {
                 info.primID = size_t(tr - shapeFirst[tri_shape[tr]]);
                 info.t = iInfo.t; info.u = iInfo.u; info.v = iInfo.v;
                 info.p = barycentric(v0, v1, v2, iInfo.u, iInfo.v);
+                info.ng = normalize(cross(v1 - v0, v2 - v0));
                 info.frameNs = Frame(normalize(barycentric(n0, n1, n2, info.u, info.v)));
                 info.wo = info.frameNs.toLocal(-ray.d);
                 info.matID = tri_mat[tr];
@@ -838,6 +843,140 @@ struct BDPT {
     }
 };
 
+
+/* PathTracerIntegrator (src/integrators/path.h:15-262): the unidirectional estimator the author cross-checks BDPT with
+ * (data/a5/bonus_bdpt/tinyrender/cbox_bdpt_path.toml).  Integrator services are BDPT's (same base class). */
+struct PathTracer {
+    const Scene& scene;
+    BDPT svc;
+    bool m_isExplicit; int m_maxDepth, m_rrDepth; float m_rrProb; size_t m_emitterSamples, m_bsdfSamples; int m_cap;
+    explicit PathTracer(const Scene& s) : scene(s), svc(s, nullptr), m_isExplicit(s.ptExplicit), m_maxDepth(s.ptMaxDepth), m_rrDepth(s.rrDepth),
+        m_rrProb(s.ptRRProb), m_emitterSamples(size_t(s.ptEmitterSamples)), m_bsdfSamples(size_t(s.ptBsdfSamples)), m_cap(s.ptDepthCap) {}
+    static float balanceHeuristic(float nf, float fPdf, float ng, float gPdf) { float f = nf * fPdf, g = ng * gPdf; return f / (f + g); } /* :30-33 */
+    static Ray mkRay(v3 o, v3 d) { return Ray(o, d, kEps, std::numeric_limits<float>::infinity()); }
+
+    v3 recursiveImplicit(Sampler& sampler, SurfaceInteraction& hit, int depth) const { /* path.h:35-66 */
+        if (depth < m_maxDepth) {
+            float sx, sy; sampler.next2D(&sx, &sy);
+            float pdf;
+            v3 brdfCosTheta = svc.getBSDF(hit)->sample(hit, sx, sy, &pdf);
+            SurfaceInteraction vis;
+            v3 wiW = hit.frameNs.toWorld(hit.wi);
+            bool intersects = scene.intersect(mkRay(hit.p, wiW), vis);
+            if (intersects) {
+                if (svc.getEmission(vis) == V(0.f)) {
+                    v3 Li = recursiveImplicit(sampler, vis, depth + 1);
+                    return Li * brdfCosTheta * float(1.0 / pdf);
+                } else {
+                    v3 Li = svc.getEmission(vis);
+                    Li = dot(vis.frameNs.n, -wiW) > 0.f ? Li : V(0.f);
+                    return Li * brdfCosTheta * float(1.0 / pdf);
+                }
+            }
+            return V(0.f);
+        }
+        return V(0.f);
+    }
+
+    v3 recursiveExplicit(Sampler& sampler, SurfaceInteraction& hit, int depth) const { /* path.h:68-206 */
+        v3 Lr = V(0.f);
+        float rrSample = sampler.next();
+        v3 indirectEstimator = V(0.f), directEstimator = V(0.f);
+        if (depth < m_maxDepth || (m_maxDepth == -1 && (depth < m_rrDepth || rrSample < m_rrProb))) {
+            {
+                unsigned int nSamples = 0;
+                float indRRProb = 0.95f, cumRRProb = 1.f;
+                SurfaceInteraction vis;
+                bool intersects = false;
+                float pdf;
+                v3 brdfCosTheta;
+                do {
+                    vis = SurfaceInteraction();
+                    float sx, sy; sampler.next2D(&sx, &sy);
+                    brdfCosTheta = svc.getBSDF(hit)->sample(hit, sx, sy, &pdf);
+                    v3 wiW = hit.frameNs.toWorld(hit.wi);
+                    intersects = scene.intersect(mkRay(hit.p, wiW), vis);
+                    nSamples++;
+                } while (svc.getEmission(vis) != V(0.f) && sampler.next() < indRRProb);
+                cumRRProb = nSamples > 1 ? indRRProb : 1.f;
+                if (intersects && brdfCosTheta != V(0.f)) {
+                    if (svc.getEmission(vis) == V(0.f) && brdfCosTheta != V(0.f) && (m_cap <= 0 || depth + 1 < m_cap)) {
+                        v3 Li = recursiveExplicit(sampler, vis, depth + 1);
+                        indirectEstimator = Li * brdfCosTheta * (1.f / pdf) * (1.f / nSamples) * (1.f / cumRRProb);
+                    }
+                }
+            }
+            {
+                v3 emitterEstimator = V(0.f), bsdfEstimator = V(0.f);
+                for (unsigned int i = 0; i < m_emitterSamples; ++i) {
+                    float emitterPdf, emitterAreaPdf;
+                    v3 normalOut, positionOut;
+                    size_t id = svc.selectEmitter(sampler.next(), emitterPdf);
+                    const Emitter& emitter = scene.emitters[id];
+                    svc.sampleEmitterPosition(sampler, emitter, normalOut, positionOut, emitterAreaPdf);
+                    v3 wiW = normalize(positionOut - hit.p);
+                    v3 wiLocal = hit.frameNs.toLocal(wiW);
+                    float lightDistanceSquared = length2(positionOut - hit.p); /* glm::distance2(a, b) = length2(b - a) */
+                    float cosOutgoing = dot(-wiW, normalOut);
+                    if (cosOutgoing > 0.f && wiLocal.z > 0.f) {
+                        SurfaceInteraction vis;
+                        bool intersects = scene.intersect(mkRay(hit.p, wiW), vis);
+                        if (intersects) {
+                            if (vis.shapeID == emitter.shapeID) {
+                                v3 Li = svc.getEmission(vis);
+                                hit.wi = wiLocal;
+                                float areaToSolidAngle = cosOutgoing * (1.f / lightDistanceSquared);
+                                float bsdfPdf = svc.getBSDF(hit)->pdf(hit);
+                                float weight = balanceHeuristic(float(m_emitterSamples), emitterAreaPdf * emitterPdf * (1.f / areaToSolidAngle), float(m_bsdfSamples), bsdfPdf);
+                                emitterEstimator = emitterEstimator + weight * Li * svc.getBSDF(hit)->eval(hit) * (1.f / emitterAreaPdf) * (1.f / emitterPdf) * areaToSolidAngle;
+                            }
+                        }
+                    }
+                }
+                emitterEstimator = m_emitterSamples == 0 ? V(0.f) : (emitterEstimator / float(m_emitterSamples));
+                for (unsigned int i = 0; i < m_bsdfSamples; ++i) {
+                    float sx, sy; sampler.next2D(&sx, &sy);
+                    float bsdfPdf;
+                    v3 brdfCosTheta = svc.getBSDF(hit)->sample(hit, sx, sy, &bsdfPdf);
+                    if (brdfCosTheta != V(0.f)) {
+                        SurfaceInteraction vis;
+                        v3 wiW = hit.frameNs.toWorld(hit.wi);
+                        bool intersects = scene.intersect(mkRay(hit.p, wiW), vis);
+                        if (intersects) {
+                            v3 Li = svc.getEmission(vis);
+                            if (Li == V(0.f)) continue;
+                            const Emitter& emitter = scene.emitters[svc.getEmitterIDByShapeID(vis.shapeID)];
+                            float emitterPdf = 1.f / scene.emitters.size();
+                            float emitterAreaPdf = 1.f / emitter.area;
+                            float lightDistanceSquared = length2(hit.p - vis.p);
+                            float cosOutgoing = dot(-wiW, vis.ng);
+                            if (cosOutgoing > 0.f) {
+                                float areaToSolidAngle = cosOutgoing * (1.f / lightDistanceSquared);
+                                float weight = balanceHeuristic(float(m_bsdfSamples), bsdfPdf, float(m_emitterSamples), emitterPdf * emitterAreaPdf * (1.f / areaToSolidAngle));
+                                bsdfEstimator = bsdfEstimator + weight * Li * brdfCosTheta * (1.f / bsdfPdf);
+                            }
+                        }
+                    }
+                }
+                bsdfEstimator = m_bsdfSamples == 0 ? V(0.f) : (bsdfEstimator / float(m_bsdfSamples));
+                directEstimator = emitterEstimator + bsdfEstimator;
+            }
+            Lr = directEstimator + indirectEstimator;
+            if (m_maxDepth == -1 && !(depth < m_rrDepth) && (rrSample < m_rrProb)) Lr = Lr * (1.f / m_rrProb);
+        }
+        return Lr;
+    }
+
+    v3 render(const Ray& ray, Sampler& sampler) const { /* path.h:208-251 */
+        SurfaceInteraction hit;
+        if (scene.intersect(ray, hit)) {
+            if (svc.getEmission(hit) != V(0.f)) return svc.getEmission(hit);
+            return m_isExplicit ? recursiveExplicit(sampler, hit, 0) : recursiveImplicit(sampler, hit, 0);
+        }
+        return V(0.f);
+    }
+};
+
 }  // namespace
 
 /* ---- C interface (ctypes: oracle/oracle_port.py) ------------------------------------------------------------ */
@@ -868,6 +1007,26 @@ void orc_set_config(void* h, const float* eye, const float* at, const float* up,
 void orc_set_rr(void* h, int rr_on, int max_depth) {
     Scene* s = static_cast<Scene*>(h);
     s->rrOn = rr_on != 0; s->rrMaxDepth = max_depth;
+}
+
+void orc_set_path(void* h, int is_explicit, int max_depth, float rr_prob, int emitter_samples, int bsdf_samples, int depth_cap) {
+    Scene* s = static_cast<Scene*>(h);
+    s->ptExplicit = is_explicit != 0; s->ptMaxDepth = max_depth; s->ptRRProb = rr_prob; s->ptEmitterSamples = emitter_samples;
+    s->ptBsdfSamples = bsdf_samples; s->ptDepthCap = depth_cap;
+}
+
+/* PathTracerIntegrator::render on given camera rays; random numbers from Sampler(seed) or injected rows */
+void orc_path_paths(void* h, const float* rays8, const int* seeds, const float* injected, int64_t stride, int64_t n, float* Li, int* nDraws) {
+    Scene* s = static_cast<Scene*>(h);
+    PathTracer pt(*s);
+    for (int64_t i = 0; i < n; i++) {
+        Sampler sm(seeds ? seeds[i] : 0);
+        if (!seeds) sm.injected = injected + i * stride;
+        const float* r = rays8 + 8 * i;
+        v3 L = pt.render(Ray(V(r[0], r[1], r[2]), V(r[3], r[4], r[5]), r[6], r[7]), sm);
+        Li[3 * i] = L.x; Li[3 * i + 1] = L.y; Li[3 * i + 2] = L.z;
+        if (nDraws) nDraws[i] = int(sm.pos);
+    }
 }
 
 void orc_bvh_order(void* h, int* order) { Scene* s = static_cast<Scene*>(h); std::copy(s->prims.begin(), s->prims.end(), order); }

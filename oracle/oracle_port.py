@@ -63,6 +63,22 @@ class Oracle:
         """the reference's Russian-roulette code (NO_RR 0); max_depth > 0 adds the device's hard cap, 0 = none as in the reference"""
         self.L.orc_set_rr(self.h, int(bool(on)), int(max_depth))
 
+    def set_path(self, is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, bsdf_samples=0, depth_cap=0):
+        """PathTracerIntegrator settings (main.cpp:94-102); depth_cap > 0 = the device's cap on the recursion, 0 = none (reference)"""
+        self.L.orc_set_path(self.h, int(bool(is_explicit)), int(max_depth), C.c_float(rr_prob), int(emitter_samples), int(bsdf_samples), int(depth_cap))
+
+    def path_paths(self, rays8, seeds=None, injected=None):
+        rays8 = np.ascontiguousarray(rays8, np.float32).reshape(-1, 8)
+        n = len(rays8)
+        li, nd = np.zeros((n, 3), np.float32), np.zeros(n, np.int32)
+        if seeds is not None:
+            seeds = np.ascontiguousarray(seeds, np.int32)
+            self.L.orc_path_paths(self.h, _p(rays8), _p(seeds), None, C.c_int64(0), C.c_int64(n), _p(li), _p(nd))
+        else:
+            injected = np.ascontiguousarray(injected, np.float32)
+            self.L.orc_path_paths(self.h, _p(rays8), None, _p(injected), C.c_int64(injected.shape[1]), C.c_int64(n), _p(li), _p(nd))
+        return li, nd
+
     def bvh_order(self):
         o = np.zeros(self.n_tris, np.int32)
         self.L.orc_bvh_order(self.h, _p(o))

@@ -301,6 +301,25 @@ void refh_camera_matrices(void* hp, float* out64) {
     std::memcpy(out64 + 48, glm::value_ptr(NDCToScreen), 64);
 }
 
+/* Whole samples through ANY offline integrator of the reference (Integrator::render is the virtual the pixel loop calls,
+ * renderer.cpp:194): used for PathTracerIntegrator (src/integrators/path.h:15-262), which returns everything in Li. */
+void refh_integrator_paths(void* hp, const float* rays, const int* seeds, int64_t n, float* Li, int* nDraws) {
+    auto* h = static_cast<Handle*>(hp);
+    const Integrator* in = h->renderer->integrator.get();
+    for (int64_t i = 0; i < n; i++) {
+        Ray r = mkRay(rays + 8 * i);
+        Sampler s(seeds[i]);
+        v3f L = in->render(r, s);
+        Li[3 * i] = L.x; Li[3 * i + 1] = L.y; Li[3 * i + 2] = L.z;
+        if (nDraws) {
+            Sampler replay(seeds[i]);
+            int c = 0;
+            while (!(replay.g == s.g) && c < 1000000) { replay.next(); c++; }
+            nDraws[i] = c;
+        }
+    }
+}
+
 /* Whole-frame render through Renderer::render (the reference's own threaded pixel loop).
  * Returns the seconds spent inside render(); rgb_out = W*H*3 floats. */
 double refh_render(void* hp, float* rgb_out) {

@@ -25,12 +25,13 @@ def available(rr: bool = False) -> bool:
 
 
 def write_toml(path, objfile, width=800, height=600, spp=1, rr_depth=5, eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0),
-               up=(0.0, 1.0, 0.0), fov=30.0, type_="bdpt") -> str:
+               up=(0.0, 1.0, 0.0), fov=30.0, type_="bdpt", rr_prob=0.95, extra="") -> str:
+    """extra: further `[renderer]` lines, e.g. 'isExplicit = true\nmaxDepth = -1\n' for type_="path" (main.cpp:94-102)"""
     def v(x):
         return "[ " + ", ".join(repr(float(c)) for c in x) + " ]"
     txt = (f'[input]\nobjfile = "{objfile}"\n\n[camera]\neye = {v(eye)}\nat = {v(at)}\nup = {v(up)}\nfov = {float(fov)!r}\n\n'
            f'[film]\nwidth = {int(width)}\nheight = {int(height)}\n\n[renderer]\nrealtime = false\ntype = "{type_}"\n'
-           f'rrDepth = {int(rr_depth)}\nrrProb = 0.95\nspp = {int(spp)}\n')
+           f'rrDepth = {int(rr_depth)}\nrrProb = {float(rr_prob)!r}\nspp = {int(spp)}\n{extra}')
     Path(path).write_text(txt)
     return str(path)
 
@@ -156,6 +157,16 @@ class RefHarness:
         nd = np.zeros(n, np.int32)
         self.L.refh_bdpt_paths(self.h, _p(rays8), _p(seeds), C.c_int64(n), int(max_splats), _p(li), _p(pix), _p(rgb), _p(nd))
         return li, pix, rgb, nd
+
+    def integrator_paths(self, rays8: np.ndarray, seeds: np.ndarray):
+        """Integrator::render of whatever integrator the TOML named (used for type = "path")"""
+        rays8 = np.ascontiguousarray(rays8, np.float32).reshape(-1, 8)
+        seeds = np.ascontiguousarray(seeds, np.int32)
+        n = len(rays8)
+        li = np.zeros((n, 3), np.float32)
+        nd = np.zeros(n, np.int32)
+        self.L.refh_integrator_paths(self.h, _p(rays8), _p(seeds), C.c_int64(n), _p(li), _p(nd))
+        return li, nd
 
     def render(self):
         img = np.zeros((self.height, self.width, 3), np.float32)

@@ -140,6 +140,40 @@ def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, scene_name):
     assert draws.mean() > 45  # the walks do run past rr_depth
 
 
+@pytest.mark.parametrize("config", ["rr", "mis", "implicit"])
+def test_path_tracer_paths_match_reference(trb, gpu_ctx, gold, scene_name, config):
+    """the path tracer on the wavefront (trb_path_paths) against whole samples of the unmodified reference's
+    PathTracerIntegrator::render under identical injected random numbers: Li within 1e-5 relative and the same number of draws
+    (= the same sequence of decisions, re-sampling loops included) for >= 99 % of the paths.  Walks longer than the device's
+    64-vertex cap (rr config only) are compared with the restatement run with the same cap."""
+    oracle_port = pytest.importorskip("oracle_port")
+    g = gold("ptpaths", f"{scene_name}_{config}")
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
+    pd = trb.path_desc(is_explicit=bool(g["is_explicit"]), max_depth=int(g["max_depth"]), rr_prob=float(g["rr_prob"]),
+                       emitter_samples=int(g["emitter_samples"]), bsdf_samples=int(g["bsdf_samples"]))
+    stride = int(g["draws"].max()) + 16
+    streams = np.stack([oracle_port.sampler_stream(int(s), stride) for s in g["seeds"]])
+    li, draws = gpu_ctx(scene_name).path_paths(desc, pd, _rays(trb, g["rays"]), streams)
+    ref_li, ref_draws = g["li"], g["draws"]
+    if int(g["max_depth"]) < 0:
+        scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{scene_name}.npz")
+        orc = oracle_port.Oracle(scene)
+        orc.set_config(desc)
+        orc.set_path(is_explicit=True, max_depth=-1, rr_prob=float(g["rr_prob"]), emitter_samples=int(g["emitter_samples"]),
+                     bsdf_samples=int(g["bsdf_samples"]), depth_cap=trb.TRB_PT_DEFAULT_DEPTH_CAP)
+        c_li, c_draws = orc.path_paths(g["rays"], injected=streams)
+        orc.close()
+        untouched = (c_draws == ref_draws) & np.all(c_li == ref_li, 1)
+        assert untouched.mean() >= 0.98
+        ref_li, ref_draws = c_li, c_draws
+    scale = np.maximum(np.abs(ref_li).max(1, keepdims=True), 1e-6)
+    ok = (np.abs(li - ref_li) <= REL * np.maximum(scale, np.abs(li))).all(1) & (draws == ref_draws)
+    print(f"{scene_name}/{config}: {ok.sum()}/{len(ok)} paths agree; mean draws {draws.mean():.1f} (reference {g['draws'].mean():.1f}); "
+          f"mean Li {li.mean():.4f} (reference {g['li'].mean():.4f})")
+    assert ok.mean() >= 0.99
+    assert (li > 0).any()
+
+
 @pytest.fixture(scope="session")
 def ref_harness(trb):
     """name -> the UNMODIFIED reference (oracle/_ref/libtr_ref.so, built by oracle/Makefile; it travels to the GPU box)

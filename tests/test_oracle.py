@@ -56,6 +56,28 @@ def test_bsdf_bit_exact(orc, gold, scene_name):
         assert np.array_equal(out.view(np.uint32), g["out"][sel].view(np.uint32)), f"material {m}"
 
 
+PT_CONFIGS = ["rr", "rr95", "mis", "implicit"]
+
+
+def _pt_settings(g):
+    return dict(is_explicit=bool(g["is_explicit"]), max_depth=int(g["max_depth"]), rr_prob=float(g["rr_prob"]),
+                emitter_samples=int(g["emitter_samples"]), bsdf_samples=int(g["bsdf_samples"]))
+
+
+@pytest.mark.parametrize("config", PT_CONFIGS)
+def test_path_tracer_bit_exact(trb, orc, gold, scene_name, config):
+    """the restatement of PathTracerIntegrator (path.h) against whole samples of the unmodified reference
+    (tools/gen_golden_path.py): Li and the number of draws, bit for bit"""
+    g = gold("ptpaths", f"{scene_name}_{config}")
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
+    orc.set_config(desc)
+    orc.set_path(depth_cap=0, **_pt_settings(g))
+    li, nd = orc.path_paths(g["rays"], seeds=g["seeds"])
+    assert np.array_equal(nd, g["draws"])
+    assert np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+    assert (li > 0).any()
+
+
 def test_bdpt_paths_russian_roulette_bit_exact(trb, orc, gold, scene_name):
     """the restatement's NO_RR 0 branch against the reference built with its own Russian-roulette code enabled
     (oracle/Makefile ref_rr; vectors by tools/gen_golden_rr.py)"""
