@@ -250,6 +250,13 @@ def load_toml(path) -> tuple[RenderDesc, str, str, bool]:
     return d, obj.value.decode(), typ.value.decode(), bool(rt.value)
 
 
+def load_toml_path(path) -> PathDesc:
+    """the `type = "path"` keys of a scene TOML (src/main.cpp:94-102)"""
+    pd = PathDesc()
+    _chk_host(lib().trb_host_load_toml_path(str(path).encode(), C.byref(pd)))
+    return pd
+
+
 def camera_matrices(desc: RenderDesc) -> np.ndarray:
     out = np.zeros((4, 4, 4), np.float32)
     _chk_host(lib().trb_host_camera_matrices(C.byref(desc), _ptr(out)))

@@ -58,6 +58,15 @@ int trb_host_load_toml(const char* toml_path, trb_render_desc* out, char* obj_pa
     return TRB_OK;
 }
 
+int trb_host_load_toml_path(const char* toml_path, trb_path_desc* out) {
+    if (!toml_path || !out) return fail(TRB_ERR_INVALID, "trb_host_load_toml_path: null argument");
+    trb::TomlConfig cfg;
+    std::string err;
+    if (!trb::load_toml(toml_path, cfg, err)) return fail(TRB_ERR_IO, err);
+    *out = cfg.path;
+    return TRB_OK;
+}
+
 int trb_host_save_exr(const char* path, const float* rgb, int width, int height) {
     if (!path) return fail(TRB_ERR_INVALID, "trb_host_save_exr: null path");
     std::string err;

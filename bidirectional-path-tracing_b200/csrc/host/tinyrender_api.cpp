@@ -5,6 +5,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <iostream>
 #include <thread>
 
 #include "tr_host.h"
@@ -55,6 +56,9 @@ bool loadTOML(Config& config, const std::string& inputFile) {
     for (int k = 0; k < 7; ++k) if (t.type == known[k]) { config.integrator = ids[k]; found = true; }
     if (!found && !t.realtime) throw std::runtime_error("Invalid integrator type");  // main.cpp:109
     config.integratorSettings.bdpt.rrDepth = t.desc.rr_depth;
+    auto& pt = config.integratorSettings.pt;
+    pt.isExplicit = t.path.is_explicit != 0; pt.maxDepth = t.path.max_depth; pt.rrDepth = t.desc.rr_depth; pt.rrProb = t.path.rr_prob;
+    pt.emitterSamples = size_t(std::max(t.path.emitter_samples, 0)); pt.bsdfSamples = size_t(std::max(t.path.bsdf_samples, 0));
     return t.realtime;
 }
 
@@ -263,20 +267,20 @@ v3f BDPTIntegrator::render(const Ray& ray, Sampler& sampler) const {
     return v3f(li[0], li[1], li[2]);
 }
 
-bool BDPTIntegrator::renderFrame() {
+// Whole frame on G devices of this process: sample-index sharding (replicated scene, disjoint RNG streams; contributions are
+// normalised by the total spp, so partial frame buffers are plain summands), one host thread per device, host-side sum.
+template <class RenderCall>
+static bool render_frame_sharded(const Scene& scene, const trb_render_desc& base, RenderBuffer& rgb, trb_stats* stats, RenderCall call) {
     const Config& cfg = scene.config;
     const int G = std::max(1, std::min(cfg.gpus, cfg.spp));
-    trb_render_desc base = make_desc(cfg);
     const size_t nf = size_t(cfg.width) * cfg.height * 3;
-    float* out = reinterpret_cast<float*>(rgb->data.get());
+    float* out = reinterpret_cast<float*>(rgb.data.get());
     if (G == 1) {
         trb_context* c = scene.context(0);
         if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
-        if (trb_render_bdpt(c, &base, 0, out, &lastStats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
+        if (call(c, base, out, stats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
         return true;
     }
-    // sample-index sharding over G devices of this process: replicated scene, disjoint RNG streams, partial frame
-    // buffers are plain summands (contributions are normalised by the total spp).  One host thread per device.
     std::vector<std::vector<float>> part;
     part.assign(size_t(G), std::vector<float>(nf));
     std::vector<int> rc;
@@ -290,7 +294,7 @@ bool BDPTIntegrator::renderFrame() {
             trb_render_desc d = base;
             d.spp_begin = int32_t(int64_t(cfg.spp) * g / G);
             d.spp_end = int32_t(int64_t(cfg.spp) * (g + 1) / G);
-            rc[g] = trb_render_bdpt(cs[g], &d, 0, part[g].data(), g == 0 ? &lastStats : nullptr);
+            rc[g] = call(cs[g], d, part[g].data(), g == 0 ? stats : nullptr);
         });
     }
     for (auto& t : th) t.join();
@@ -299,17 +303,69 @@ bool BDPTIntegrator::renderFrame() {
     return true;
 }
 
+bool BDPTIntegrator::renderFrame() {
+    return render_frame_sharded(scene, make_desc(scene.config), *rgb, &lastStats,
+                                [](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_bdpt(c, &d, 0, out, st); });
+}
+
+// ---- PathTracerIntegrator (path.h:15-262) ---------------------------------------------------------------------
+PathTracerIntegrator::PathTracerIntegrator(const Scene& s) : Integrator(s) {
+    const auto& pt = s.config.integratorSettings.pt;  // path.h:16-22
+    m_isExplicit = pt.isExplicit; m_maxDepth = pt.maxDepth; m_rrDepth = pt.rrDepth; m_rrProb = pt.rrProb;
+    m_emitterSamples = pt.emitterSamples; m_bsdfSamples = pt.bsdfSamples;
+    std::cout << "Samples per pixel are: " << s.config.spp << std::endl;  // path.h:24-27
+    std::cout << "DI emitter samples are: " << m_emitterSamples << std::endl;
+    std::cout << "DI bsdf samples are: " << m_bsdfSamples << std::endl;
+    std::cout << "Max depth is: " << m_maxDepth << std::endl;
+}
+
+trb_path_desc PathTracerIntegrator::pathDesc() const {
+    trb_path_desc p;
+    p.is_explicit = m_isExplicit ? 1 : 0; p.max_depth = m_maxDepth; p.rr_prob = m_rrProb;
+    p.emitter_samples = int32_t(m_emitterSamples); p.bsdf_samples = int32_t(m_bsdfSamples);
+    return p;
+}
+
+v3f PathTracerIntegrator::render(const Ray& ray, Sampler& sampler) const {
+    trb_context* c = scene.context(0);
+    if (!c) throw std::runtime_error("PathTracerIntegrator::render: no device context");
+    trb_render_desc d = make_desc(scene.config);
+    d.rr_depth = m_rrDepth;
+    const trb_path_desc pd = pathDesc();
+    // the walk consumes a prefix of the sampler's stream: feed a copy's numbers, then advance the real sampler
+    const size_t stride = 4096;
+    Sampler ahead = sampler;
+    std::vector<float> rng(stride);
+    for (float& f : rng) f = ahead.next();
+    trb_ray r = to_ray(ray);
+    float li[3] = {0, 0, 0};
+    int32_t draws = 0;
+    if (trb_path_paths(c, &d, &pd, &r, rng.data(), 1, stride, li, &draws) != TRB_OK)
+        throw std::runtime_error(std::string("PathTracerIntegrator::render: ") + trb_last_error(c));
+    for (int k = 0; k < draws; ++k) sampler.next();
+    return v3f(li[0], li[1], li[2]);
+}
+
+bool PathTracerIntegrator::renderFrame() {
+    trb_render_desc base = make_desc(scene.config);
+    base.rr_depth = m_rrDepth;
+    const trb_path_desc pd = pathDesc();
+    return render_frame_sharded(scene, base, *rgb, &lastStats,
+                                [pd](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_path(c, &d, &pd, 0, out, st); });
+}
+
 // ---- Renderer (renderer.cpp:53-227) ---------------------------------------------------------------------------
 Renderer::Renderer(const Config& config) : scene(config) {}
 
 bool Renderer::init(bool isRealTime, bool nogui_) {
     realTime = isRealTime; nogui = nogui_;
     if (!scene.load(isRealTime)) return false;
-    if (scene.config.integrator != EBDPTIntegrator) {
-        std::printf("Only the BDPT integrator is hosted on the B200 path (renderer.type = \"bdpt\")\n");
+    if (scene.config.integrator == EBDPTIntegrator) integrator.reset(new BDPTIntegrator(scene));
+    else if (scene.config.integrator == EPathTracerIntegrator) integrator.reset(new PathTracerIntegrator(scene));
+    else {
+        std::printf("Only the BDPT and path integrators are hosted on the B200 path (renderer.type = \"bdpt\" | \"path\")\n");
         return false;
     }
-    integrator.reset(new BDPTIntegrator(scene));
     return integrator->init();
 }
 

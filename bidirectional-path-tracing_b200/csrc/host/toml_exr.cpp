@@ -189,6 +189,12 @@ bool load_toml(const std::string& path, TomlConfig& out, std::string& err) {
     out.desc.reserved = 0;
     out.desc.wave_samples = get_int(ren, "waveSamples", 0);  // extension keys: samples per wavefront, devices
     out.gpus = std::max(1, get_int(ren, "gpus", 1));
+    // PathTracerIntegrator (main.cpp:94-102); rrDepth is shared with the BDPT branch (:98,105)
+    out.path.is_explicit = get_bool(ren, "isExplicit", true) ? 1 : 0;
+    out.path.max_depth = get_int(ren, "maxDepth", -1);
+    out.path.rr_prob = float(get_double(ren, "rrProb", 0.95));
+    out.path.emitter_samples = get_int(ren, "emitterSamples", 1);
+    out.path.bsdf_samples = get_int(ren, "bsdfSamples", 0);
     return true;
 }
 

@@ -135,6 +135,7 @@ void make_camera(const trb_render_desc& d, CameraDev& out);
 // ---- TOML / EXR ---------------------------------------------------------------------------------
 struct TomlConfig {
     trb_render_desc desc;
+    trb_path_desc path;  // [renderer] keys of type = "path" (main.cpp:94-102)
     std::string obj_path, type;
     bool realtime = false;
     int gpus = 1;

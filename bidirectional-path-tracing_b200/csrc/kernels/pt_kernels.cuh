@@ -192,14 +192,16 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_check(const __grid_constant__ 
             PtVertex v = pt_load_vertex(p, depth, slot, nullptr, nullptr, &pdf0, &ns);
             Mat m = load_mat(p.sc.mats, v.mat);
             const BvhView bvh = bvh_of(p.sc);
-            uint32_t tries = 0;
+            uint32_t tries = 0, traced = 0;
             while (!is_zero(ke) && rng.next() < 0.95f && tries < TRB_PT_MAX_RETRIES) {
                 float ux = rng.next(), uy = rng.next();
                 V3 wi; float pdf;
                 V3 fcos = bsdf_sample(m, v.wo, ux, uy, &wi, &pdf);
-                r = pt_ray(v.p, to_world(v.f, wi));
-                bool occ;
-                trace_ray<false>(bvh, r, &h, &occ, nullptr, nullptr);
+                const RayT r2 = pt_ray(v.p, to_world(v.f, wi));
+                // a mirror re-samples the very same direction (glass: one of two): the same ray has the same hit
+                const bool same = r2.dx == r.dx && r2.dy == r.dy && r2.dz == r.dz;
+                r = r2;
+                if (!same) { bool occ; trace_ray<false>(bvh, r, &h, &occ, nullptr, nullptr); ++traced; }
                 ++ns; ++tries;
                 vp->vcm = pdf; vp->tx = fcos.x; vp->ty = fcos.y; vp->tz = fcos.z;
                 valid = hit_valid(h, r);
@@ -209,7 +211,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_check(const __grid_constant__ 
             if (tries) {
                 vp->vc = __uint_as_float(ns);
                 p.ray[slot] = r; p.hit[slot] = h;
-                if (extra_rays) atomicAdd(extra_rays, (unsigned long long)tries);
+                if (extra_rays && traced) atomicAdd(extra_rays, (unsigned long long)traced);
             }
             sv.z = __uint_as_float(rng.ctr);
             p.st_v[slot] = sv;

@@ -56,6 +56,10 @@ struct Config {  // core.h:195-248 (the fields the offline BDPT path reads) + op
     int width = 0, height = 0, spp = 1;
     struct IntegratorConfig {
         struct bdpt_s { int rrDepth = 5; float rrProb = 0.f; } bdpt;  // main.cpp:103-107 (rrProb is read and never used)
+        struct pt_s {  // main.cpp:94-102, core.h:229-236
+            bool isExplicit = true; int maxDepth = -1; int rrDepth = 5; float rrProb = 0.95f;
+            size_t emitterSamples = 1, bsdfSamples = 0;
+        } pt;
     } integratorSettings;
     // additive [renderer] keys (defaults reproduce the reference run)
     int gpus = 1;                 // devices used by Renderer::render, sharded by sample index
@@ -187,6 +191,16 @@ struct BDPTIntegrator : Integrator {  // bdpt.h:37-518
     // light-tracing splats are added into rgb->data as the reference does (bdpt.h:360-370). Returns Li.
     v3f render(const Ray& ray, Sampler& sampler) const override;
     bool renderFrame() override;
+};
+
+struct PathTracerIntegrator : Integrator {  // path.h:15-262, the estimator the reference cross-checks BDPT with
+    bool m_isExplicit; int m_maxDepth, m_rrDepth; float m_rrProb; size_t m_emitterSamples, m_bsdfSamples;
+    mutable trb_stats lastStats{};
+    explicit PathTracerIntegrator(const Scene& s);
+    // One sample on the device with the sampler's own number stream, consumed in the reference's (depth-first) order.
+    v3f render(const Ray& ray, Sampler& sampler) const override;
+    bool renderFrame() override;
+    trb_path_desc pathDesc() const;
 };
 
 struct Renderer {  // renderer.h:20-33

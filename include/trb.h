@@ -168,6 +168,8 @@ void trb_host_scene_free(trb_host_scene*);
  * toml's directory (renderer.cpp:236-241). type_out receives renderer.type. */
 int trb_host_load_toml(const char* toml_path, trb_render_desc* out, char* obj_path_out, size_t obj_len,
                        char* type_out, size_t type_len, int* realtime_out);
+/* the `type = "path"` keys of the same file (main.cpp:94-102: isExplicit, maxDepth, rrProb, emitterSamples, bsdfSamples) */
+int trb_host_load_toml_path(const char* toml_path, struct trb_path_desc* out);
 /* saveEXR (src/core/utils.h:95-156): channels B,G,R stored as half, row 0 = top. */
 int trb_host_save_exr(const char* path, const float* rgb, int width, int height);
 const char* trb_host_last_error(void);

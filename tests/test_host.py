@@ -47,6 +47,15 @@ def test_load_toml_keys_defaults_and_errors(trb, tmp_path):
     d, obj, typ, rt = trb.load_toml(p)
     assert (d.width, d.height, d.spp, d.rr_depth) == (768, 576, 1, 5) and obj == "/abs/a.obj"
     assert list(d.eye) == [1.0, 1.0, 0.0] and list(d.up) == [0.0, 1.0, 0.0] and d.fov_deg == 30.0
+    # type = "path" (main.cpp:94-102): defaults, then the shipped cbox_bdpt_path.toml settings and the extra keys
+    pd = trb.load_toml_path(p)
+    assert (pd.is_explicit, pd.max_depth, pd.emitter_samples, pd.bsdf_samples) == (1, -1, 1, 0) and abs(pd.rr_prob - 0.95) < 1e-7
+    p.write_text('[input]\nobjfile = "a.obj"\n[camera]\n[film]\n[renderer]\nrealtime = false\nisExplicit = false\ntype = "path"\nmaxDepth = 4\n'
+                 'rrDepth = 7\nrrProb = 0.8\nemitterSamples = 2\nbsdfSamples = 3\nspp = 512\n')
+    d, obj, typ, rt = trb.load_toml(p)
+    pd = trb.load_toml_path(p)
+    assert (typ, d.rr_depth, d.spp) == ("path", 7, 512)
+    assert (pd.is_explicit, pd.max_depth, pd.emitter_samples, pd.bsdf_samples) == (0, 4, 2, 3) and abs(pd.rr_prob - 0.8) < 1e-7
     p.write_text('[input]\nobjfile = "a.obj"\n[camera]\n[film]\n')
     with pytest.raises(trb.TrbError):
         trb.load_toml(p)

@@ -18,6 +18,8 @@ PINS = {
     "caustic_rr5": ("data/a5/cbox/tinyrender/cbox_bdpt_glass_5depth.exr", "caustic", 5),
     "caustic_rr8": ("data/a5/cbox/tinyrender/cbox_bdpt_glass_8depth.exr", "caustic", 8),
     "hardlight_rr8": ("data/a5/bonus_bdpt/tinyrender/cbox_bdpt_final.exr", "hardlight", 8),
+    # the author's independent estimator: PathTracerIntegrator, cbox_bdpt_path.toml (explicit, maxDepth -1, rrDepth 5, rrProb 0.95, 512 spp)
+    "hardlight_path": ("data/a5/bonus_bdpt/tinyrender/cbox_bdpt_path.exr", "hardlight", 5),
 }
 BOX = 8
 
