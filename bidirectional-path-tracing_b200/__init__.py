@@ -24,6 +24,7 @@ TRB_FLAG_NO_JITTER = 1
 TRB_FLAG_NO_OVERLAP = 2
 TRB_FLAG_RUSSIAN_ROULETTE = 4  # the reference's NO_RR 0 behaviour (bdpt.h:18,68,129); default off = shipped behaviour
 TRB_RR_DEFAULT_MAX_DEPTH = 32
+TRB_FLAG_SORT_RAYS = 8      # experiment: sort every ray queue by (origin cell, direction) before traversal (off by default)
 
 
 class TrbError(RuntimeError):

@@ -125,7 +125,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                 base = __shfl_sync(FULL, base, 0);
                 const uint32_t idx = base + uint32_t(__popc(wm & lt));
                 if (want && idx < n) {
-                    slot = (!ANY && a.q) ? a.q[idx] : int32_t(idx);
+                    slot = a.q ? a.q[idx] : int32_t(idx);
                     const float4* rp = reinterpret_cast<const float4*>(a.rays + slot);
                     float4 r0 = rp[0], r1 = rp[1];
                     r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.dx = r0.w; r.dy = r1.x; r.dz = r1.y; r.min_t = r1.z; r.max_t = r1.w;

@@ -14,6 +14,7 @@
 #include "kernels/pt_kernels.cuh"
 #include "kernels/trace_warp.cuh"
 #include "kernels/trace_coop.cuh"
+#include "kernels/trace_sort.cuh"
 
 #ifndef TRB_COOP
 #define TRB_COOP 1  // 1: warp-cooperative triangle queue (trace_coop.cuh); 0: per-lane postponed leaves (trace_warp.cuh)
@@ -70,6 +71,8 @@ struct trb_context {
     DevBuf<LightVertex> lv;
     DevBuf<int32_t> nlv, q_a, q_b, q_conn;
     DevBuf<uint32_t> pt_ctr;             // path tracer: one counter per queue / traversal launch
+    DevBuf<uint32_t> sort_keys[2], sort_hist[2];   // ray-queue sort (trace_sort.cuh): [0] main stream (closest), [1] shadow stream
+    DevBuf<int32_t> sort_q[2];
     DevBuf<EyeVertex> ev;
     DevBuf<Pending> spend, spend2;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
@@ -138,17 +141,47 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
 }
 
 void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t cap, uint8_t* occ_out,
-                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit, cudaStream_t stream = nullptr) {
+                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit, cudaStream_t stream = nullptr,
+                const int32_t* q = nullptr) {
     if (!stream) stream = c->stream;
     TraceArgs a{};
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
-    a.rays = rays; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
+    a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
 #if TRB_COOP
     k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
 #else
     k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
 #endif
+}
+
+// Re-order a ray queue for coherence before it is traversed (kernels/trace_sort.cuh). `which`: 0 = main stream, 1 = shadow stream.
+// Returns the queue to hand to the traversal launch.
+inline bool sort_enabled(const trb_context* c, const trb_render_desc& d) {
+    (void)c;
+    return (d.flags & TRB_FLAG_SORT_RAYS) != 0;  // off by default: measured, the sort costs more than the traversal gains (profiles/r1f_tuning_variants.md)
+}
+const int32_t* sort_queue(trb_context* c, int which, cudaStream_t st, const RayT* rays, const int32_t* q, const uint32_t* n_ptr,
+                          uint32_t n_fixed, uint32_t cap) {
+    SortArgs a{};
+    a.rays = rays; a.q_in = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap;
+    const trb::FlatScene& f = c->flat;
+    a.mnx = f.scene_min[0]; a.mny = f.scene_min[1]; a.mnz = f.scene_min[2];
+    a.sx = 16.f / std::max(f.scene_max[0] - f.scene_min[0], 1e-20f);
+    a.sy = 16.f / std::max(f.scene_max[1] - f.scene_min[1], 1e-20f);
+    a.sz = 16.f / std::max(f.scene_max[2] - f.scene_min[2], 1e-20f);
+    a.keys = c->sort_keys[which].p; a.hist = c->sort_hist[which].p; a.q_out = c->sort_q[which].p;
+    cudaMemsetAsync(a.hist, 0, size_t(TRB_SORT_BINS) * sizeof(uint32_t), st);
+    const int g = c->prop.multiProcessorCount * 8;
+    k_sort_count<<<g, 256, 0, st>>>(a);
+    k_sort_scan<<<1, 1024, 0, st>>>(a.hist);
+    k_sort_scatter<<<g, 256, 0, st>>>(a);
+    return a.q_out;
+}
+int ensure_sort(trb_context* c, size_t n_main, size_t n_shadow) {
+    TRB_CUDA(c, c->sort_keys[0].alloc(n_main)); TRB_CUDA(c, c->sort_q[0].alloc(n_main)); TRB_CUDA(c, c->sort_hist[0].alloc(TRB_SORT_BINS));
+    TRB_CUDA(c, c->sort_keys[1].alloc(n_shadow)); TRB_CUDA(c, c->sort_q[1].alloc(n_shadow)); TRB_CUDA(c, c->sort_hist[1].alloc(TRB_SORT_BINS));
+    return TRB_OK;
 }
 
 // depth cap and vertices per subpath of a render description (bdpt.h:68,188: `depth < rrDepth`, depth starts at 1)
@@ -358,11 +391,18 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         if (last_any_of_buf[b] >= 0) cudaStreamWaitEvent(c->stream, c->dep_b[last_any_of_buf[b]], 0);
     };
     const bool overlap = (d.flags & TRB_FLAG_NO_OVERLAP) == 0;
+    const bool sort = sort_enabled(c, d);
+    auto closest = [&](const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t* fetch) {
+        if (sort) { q = sort_queue(c, 0, c->stream, rays, q, n_ptr, n_fixed, 0xffffffffu); c->mark(LK_LOGIC); }
+        launch_closest(c, rays, q, n_ptr, n_fixed, p.hit, fetch, visit); c->mark(LK_CLOSEST);
+    };
     auto trace_shadow = [&]() {          // after the bounce kernel(s) of a stage
         const int b = n_any & 1;
         if (!overlap) {
+            const int32_t* sq = sort ? sort_queue(c, 1, c->stream, p.sray, nullptr, p.counters + CTR_SHADOW, 0u, p.shadow_cap) : nullptr;
+            if (sort) c->mark(LK_LOGIC);
             launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
-                       visit ? visit + 2 : nullptr, c->stream);
+                       visit ? visit + 2 : nullptr, c->stream, sq);
             c->mark(LK_ANY);
             ++n_any;
             return;
@@ -370,8 +410,10 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         cudaEventRecord(c->dep_a[n_any], c->stream);
         cudaStreamWaitEvent(c->stream2, c->dep_a[n_any], 0);
         c->mark(-1, true);
+        const int32_t* sq = sort ? sort_queue(c, 1, c->stream2, p.sray, nullptr, p.counters + CTR_SHADOW, 0u, p.shadow_cap) : nullptr;
+        if (sort) c->mark(LK_LOGIC, true);
         launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
-                   visit ? visit + 2 : nullptr, c->stream2);
+                   visit ? visit + 2 : nullptr, c->stream2, sq);
         c->mark(LK_ANY, true);
         cudaEventRecord(c->dep_b[n_any], c->stream2);
         last_any_of_buf[b] = n_any;
@@ -379,7 +421,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     };
 
     k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
-    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, stage_ctr(2 * kk + 2) + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
+    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, stage_ctr(2 * kk + 2) + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);  // (camera rays are coherent as generated)
     // light subpath
     int stage = 0;
     p.counters = stage_ctr(stage); p.q_out = qa;
@@ -390,7 +432,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.q_out = (stage % 2 == 0) ? qb : qa;
         ++stage;
         p.counters = stage_ctr(stage);
-        launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);
+        closest(p.ray, p.q_in, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
         shadow_buffers();
         k_light_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
         trace_shadow();
@@ -406,7 +448,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         p.q_out = even ? qb : qa;
         ++stage;
         p.counters = stage_ctr(stage);
-        if (depth > 1) { launch_closest(c, p.ray, p.q_in, n_in, 0u, p.hit, p.counters + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST); }
+        if (depth > 1) closest(p.ray, p.q_in, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
         shadow_buffers();
         k_eye_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in);
         k_connect_vertices<<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN); c->mark(LK_LOGIC);
@@ -469,6 +511,7 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     rc = ensure_wave(c, size_t(P), K);
     if (rc) return rc;
+    if (sort_enabled(c, *d)) { rc = ensure_sort(c, size_t(P), c->sray.n); if (rc) return rc; }
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -872,6 +915,7 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
     if (stride < size_t(10 + 10 * K)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: rng stride must be >= 10 + 10*K, K = max vertices per subpath");
     rc = ensure_wave(c, n, K);
     if (rc) return rc;
+    if (sort_enabled(c, *d)) { rc = ensure_sort(c, n, c->sray.n); if (rc) return rc; }
     DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_pix, d_draws;
     TRB_CUDA(c, d_rays.alloc(n)); TRB_CUDA(c, d_rng.alloc(n * stride)); TRB_CUDA(c, d_acc.alloc(n * size_t(K + 1) * 3));
     TRB_CUDA(c, d_pix.alloc(n * size_t(K))); TRB_CUDA(c, d_draws.alloc(n));

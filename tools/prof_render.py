@@ -18,6 +18,7 @@ if wl == "tess":  # python tools/prof_render.py tess <spp> <wave> <tris>
     ctx.upload(gen_tess_scene.make_scene(int(sys.argv[4]) if len(sys.argv) > 4 else 10_000_000, seed=1))
 else:
     ctx.upload(trb.HostScene.load_npz(ROOT / "tests" / "golden" / f"scene_{wl}.npz"))
-desc = trb.render_desc(width=1024, height=1024, spp=spp, rr_depth=rr, wave_samples=wave)
+import os
+desc = trb.render_desc(width=1024, height=1024, spp=spp, rr_depth=rr, wave_samples=wave, flags=int(os.environ.get("TRB_FLAGS", "0")))
 img, st = ctx.render_bdpt(desc)
 print({k: (round(v, 3) if isinstance(v, float) else v) for k, v in st.items()}, "mean", float(img.mean()))
