@@ -67,6 +67,11 @@ def path_desc(is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, b
 TRB_PT_DEFAULT_DEPTH_CAP = 64
 
 
+class CheckpointInfo(C.Structure):
+    """trb_checkpoint_info"""
+    _fields_ = [("desc", RenderDesc), ("path", PathDesc), ("integrator", C.c_int32), ("spp_done", C.c_int32), ("scene_hash", C.c_uint64)]
+
+
 class Stats(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_trace_closest", C.c_double), ("ms_trace_any", C.c_double),
                 ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
@@ -258,6 +263,33 @@ def load_toml_path(path) -> PathDesc:
     return pd
 
 
+def save_checkpoint(path, info: CheckpointInfo, rgb: np.ndarray) -> None:
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    assert rgb.size == info.desc.width * info.desc.height * 3
+    _chk_host(lib().trb_host_save_checkpoint(str(path).encode(), C.byref(info), _ptr(rgb)))
+
+
+def load_checkpoint(path, header_only: bool = False):
+    """-> (CheckpointInfo, H x W x 3 float32 | None); raises TrbError for a missing, truncated or corrupted file"""
+    info = CheckpointInfo()
+    _chk_host(lib().trb_host_load_checkpoint(str(path).encode(), C.byref(info), None, C.c_size_t(0)))
+    if header_only:
+        return info, None
+    rgb = np.zeros((info.desc.height, info.desc.width, 3), np.float32)
+    _chk_host(lib().trb_host_load_checkpoint(str(path).encode(), C.byref(info), _ptr(rgb), C.c_size_t(rgb.size)))
+    return info, rgb
+
+
+def checkpoint_matches(a: CheckpointInfo, b: CheckpointInfo) -> bool:
+    return bool(lib().trb_host_checkpoint_matches(C.byref(a), C.byref(b)))
+
+
+def save_png(path, rgb: np.ndarray, exposure: float = 1.0) -> None:
+    rgb = np.ascontiguousarray(rgb, np.float32)
+    h, w = rgb.shape[:2]
+    _chk_host(lib().trb_host_save_png(str(path).encode(), _ptr(rgb), int(w), int(h), C.c_float(exposure)))
+
+
 def camera_matrices(desc: RenderDesc) -> np.ndarray:
     out = np.zeros((4, 4, 4), np.float32)
     _chk_host(lib().trb_host_camera_matrices(C.byref(desc), _ptr(out)))
@@ -344,6 +376,11 @@ class Context:
         self._chk(self._L.trb_bdpt_paths(self._h, C.byref(desc), _ptr(cam_rays), _ptr(rng), C.c_size_t(n), C.c_size_t(stride),
                                          _ptr(li), _ptr(pix), _ptr(rgb), _ptr(draws)))
         return li, pix, rgb, draws
+
+    def framebuffer_upload(self, rgb: np.ndarray) -> None:
+        """restore the context's frame buffer (what accumulate=True adds to), e.g. from a checkpoint"""
+        rgb = np.ascontiguousarray(rgb, np.float32)
+        self._chk(self._L.trb_framebuffer_upload(self._h, _ptr(rgb), int(rgb.shape[1]), int(rgb.shape[0])))
 
     def render_path(self, desc: RenderDesc, pd: PathDesc, accumulate: bool = False, download: bool = True):
         """Renderer::render with the PathTracerIntegrator (path.h). Returns (H x W x 3 float32 | None, stats)."""

@@ -23,7 +23,7 @@ OBJ = PKG / "build"
 LIB = PKG / "libtrb.so"
 LIB_COUNTERS = PKG / "libtrb_counters.so"  # same sources with -DTRB_COUNTERS (node / triangle visit counts)
 
-HOST_SRCS = ["host/obj_loader.cpp", "host/scene_build.cpp", "host/camera.cpp", "host/toml_exr.cpp", "host/host_abi.cpp",
+HOST_SRCS = ["host/obj_loader.cpp", "host/scene_build.cpp", "host/camera.cpp", "host/toml_exr.cpp", "host/checkpoint_png.cpp", "host/host_abi.cpp",
              "host/tinyrender_api.cpp"]
 CUDA_SRCS = ["trb_abi.cu"]
 CLI_SRC = "host/tinyrender_main.cpp"

@@ -67,6 +67,31 @@ int trb_host_load_toml_path(const char* toml_path, trb_path_desc* out) {
     return TRB_OK;
 }
 
+int trb_host_save_checkpoint(const char* path, const trb_checkpoint_info* info, const float* rgb) {
+    if (!path || !info) return fail(TRB_ERR_INVALID, "trb_host_save_checkpoint: null argument");
+    std::string err;
+    if (!trb::save_checkpoint(path, *info, rgb, err)) return fail(TRB_ERR_IO, err);
+    return TRB_OK;
+}
+
+int trb_host_load_checkpoint(const char* path, trb_checkpoint_info* info_out, float* rgb_out, size_t capacity_floats) {
+    if (!path || !info_out) return fail(TRB_ERR_INVALID, "trb_host_load_checkpoint: null argument");
+    std::string err;
+    if (!trb::load_checkpoint(path, *info_out, rgb_out, capacity_floats, err)) return fail(TRB_ERR_IO, err);
+    return TRB_OK;
+}
+
+int trb_host_checkpoint_matches(const trb_checkpoint_info* a, const trb_checkpoint_info* b) {
+    return (a && b && trb::checkpoint_matches(*a, *b)) ? 1 : 0;
+}
+
+int trb_host_save_png(const char* path, const float* rgb, int width, int height, float exposure) {
+    if (!path) return fail(TRB_ERR_INVALID, "trb_host_save_png: null path");
+    std::string err;
+    if (!trb::save_png_srgb(path, rgb, width, height, exposure, err)) return fail(TRB_ERR_IO, err);
+    return TRB_OK;
+}
+
 int trb_host_save_exr(const char* path, const float* rgb, int width, int height) {
     if (!path) return fail(TRB_ERR_INVALID, "trb_host_save_exr: null path");
     std::string err;

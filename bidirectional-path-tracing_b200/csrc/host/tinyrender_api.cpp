@@ -49,6 +49,7 @@ bool loadTOML(Config& config, const std::string& inputFile) {
     config.width = t.desc.width; config.height = t.desc.height; config.spp = t.desc.spp;
     config.seed = t.desc.seed; config.waveSamples = t.desc.wave_samples; config.gpus = t.gpus;
     config.russianRoulette = (t.desc.flags & TRB_FLAG_RUSSIAN_ROULETTE) != 0; config.maxDepth = t.desc.max_depth;
+    config.checkpointFile = t.checkpoint; config.previewPng = t.preview; config.checkpointEvery = t.checkpoint_every;
     static const char* known[] = {"normal", "simple", "ao", "ro", "direct", "path", "bdpt"};
     static const EIntegrator ids[] = {ENormalIntegrator, ESimpleIntegrator, EAOIntegrator, EROIntegrator, EDirectIntegrator,
                                       EPathTracerIntegrator, EBDPTIntegrator};
@@ -308,6 +309,21 @@ bool BDPTIntegrator::renderFrame() {
                                 [](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_bdpt(c, &d, 0, out, st); });
 }
 
+bool BDPTIntegrator::renderRange(int sppBegin, int sppEnd, bool accumulate) {
+    trb_context* c = scene.context(0);
+    if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
+    trb_render_desc d = make_desc(scene.config);
+    d.spp_begin = sppBegin; d.spp_end = sppEnd;
+    if (trb_render_bdpt(c, &d, accumulate ? 1 : 0, reinterpret_cast<float*>(rgb->data.get()), &lastStats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
+    return true;
+}
+
+void BDPTIntegrator::describe(trb_checkpoint_info& info) const {
+    std::memset(&info, 0, sizeof(info));
+    info.desc = make_desc(scene.config);
+    info.integrator = 0;
+}
+
 // ---- PathTracerIntegrator (path.h:15-262) ---------------------------------------------------------------------
 PathTracerIntegrator::PathTracerIntegrator(const Scene& s) : Integrator(s) {
     const auto& pt = s.config.integratorSettings.pt;  // path.h:16-22
@@ -354,6 +370,24 @@ bool PathTracerIntegrator::renderFrame() {
                                 [pd](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_path(c, &d, &pd, 0, out, st); });
 }
 
+bool PathTracerIntegrator::renderRange(int sppBegin, int sppEnd, bool accumulate) {
+    trb_context* c = scene.context(0);
+    if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
+    trb_render_desc d = make_desc(scene.config);
+    d.rr_depth = m_rrDepth; d.spp_begin = sppBegin; d.spp_end = sppEnd;
+    const trb_path_desc pd = pathDesc();
+    if (trb_render_path(c, &d, &pd, accumulate ? 1 : 0, reinterpret_cast<float*>(rgb->data.get()), &lastStats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
+    return true;
+}
+
+void PathTracerIntegrator::describe(trb_checkpoint_info& info) const {
+    std::memset(&info, 0, sizeof(info));
+    info.desc = make_desc(scene.config);
+    info.desc.rr_depth = m_rrDepth;
+    info.path = pathDesc();
+    info.integrator = 1;
+}
+
 // ---- Renderer (renderer.cpp:53-227) ---------------------------------------------------------------------------
 Renderer::Renderer(const Config& config) : scene(config) {}
 
@@ -371,7 +405,42 @@ bool Renderer::init(bool isRealTime, bool nogui_) {
 
 void Renderer::render() {
     if (!integrator) return;
-    if (!integrator->renderFrame()) throw std::runtime_error("Renderer::render: device render failed");
+    const Config& cfg = scene.config;
+    if (cfg.checkpointEvery <= 0 || cfg.checkpointFile.empty()) {
+        if (!integrator->renderFrame()) throw std::runtime_error("Renderer::render: device render failed");
+        return;
+    }
+    // the frame in slices of checkpointEvery samples per pixel; after each slice the running sum is saved, and a
+    // run that finds a checkpoint of this very render (same camera, film, spp, depth, seed, integrator, scene) continues from it.
+    trb_checkpoint_info me;
+    integrator->describe(me);
+    const trb_scene_desc* sd = scene.desc();
+    me.scene_hash = sd ? (uint64_t(sd->n_tris) * 1000003ull) ^ (uint64_t(sd->n_positions) << 20) ^ uint64_t(sd->n_materials) : 0;
+    float* out = reinterpret_cast<float*>(integrator->rgb->data.get());
+    const size_t nf = size_t(cfg.width) * cfg.height * 3;
+    int done = 0;
+    trb_checkpoint_info old;
+    if (trb_host_load_checkpoint(cfg.checkpointFile.c_str(), &old, nullptr, 0) == TRB_OK && trb_host_checkpoint_matches(&old, &me) &&
+        old.spp_done > 0 && old.spp_done <= cfg.spp && trb_host_load_checkpoint(cfg.checkpointFile.c_str(), &old, out, nf) == TRB_OK) {
+        trb_context* c = scene.context(0);
+        if (!c || trb_framebuffer_upload(c, out, cfg.width, cfg.height) != TRB_OK) throw std::runtime_error("Renderer::render: cannot restore the checkpoint");
+        done = old.spp_done;
+        std::printf("Resuming from %s: %d of %d samples per pixel done\n", cfg.checkpointFile.c_str(), done, cfg.spp);
+    }
+    int written = 0;
+    while (done < cfg.spp) {
+        if (cfg.stopAfterCheckpoints > 0 && written >= cfg.stopAfterCheckpoints) { std::printf("Stopped after %d checkpoint(s)\n", written); return; }
+        const int end = std::min(done + cfg.checkpointEvery, cfg.spp);
+        if (!integrator->renderRange(done, end, done > 0)) throw std::runtime_error("Renderer::render: device render failed");
+        done = end;
+        me.spp_done = done;
+        if (trb_host_save_checkpoint(cfg.checkpointFile.c_str(), &me, out) != TRB_OK) std::printf("%s\n", trb_host_last_error());
+        else { ++written; std::printf("Checkpoint: %d of %d samples per pixel\n", done, cfg.spp); }
+        if (!cfg.previewPng.empty()) {
+            // the buffer is normalised by the TOTAL spp: scale the preview up to what is there so far
+            if (trb_host_save_png(cfg.previewPng.c_str(), out, cfg.width, cfg.height, float(cfg.spp) / float(done)) != TRB_OK) std::printf("%s\n", trb_host_last_error());
+        }
+    }
 }
 
 void Renderer::cleanUp() {

@@ -17,6 +17,7 @@ static void run(const std::string& file, bool nogui) {
         std::fprintf(stderr, "Error while parsing scene file: %s\n", e.what());
         std::exit(EXIT_FAILURE);
     }
+    if (const char* stop = std::getenv("TRB_STOP_AFTER_CHECKPOINTS")) config.stopAfterCheckpoints = std::atoi(stop);
     TinyRender::Renderer renderer(config);
     if (!renderer.init(isRealTime, nogui)) {
         std::fprintf(stderr, "Renderer initialisation failed\n");

@@ -195,6 +195,14 @@ bool load_toml(const std::string& path, TomlConfig& out, std::string& err) {
     out.path.rr_prob = float(get_double(ren, "rrProb", 0.95));
     out.path.emitter_samples = get_int(ren, "emitterSamples", 1);
     out.path.bsdf_samples = get_int(ren, "bsdfSamples", 0);
+    // restartable renders: file names relative to the toml's directory, like objfile
+    auto resolve = [&](std::string f) {
+        if (!f.empty() && f[0] != '/') { size_t slash = path.find_last_of('/'); f = (slash == std::string::npos ? std::string() : path.substr(0, slash + 1)) + f; }
+        return f;
+    };
+    out.checkpoint = resolve(get_str(ren, "checkpoint", ""));
+    out.preview = resolve(get_str(ren, "preview", ""));
+    out.checkpoint_every = get_int(ren, "checkpointEvery", 0);
     return true;
 }
 

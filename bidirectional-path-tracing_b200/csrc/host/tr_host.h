@@ -139,8 +139,15 @@ struct TomlConfig {
     std::string obj_path, type;
     bool realtime = false;
     int gpus = 1;
+    // restartable renders (extension keys): renderer.checkpoint = "file", renderer.checkpointEvery = spp, renderer.preview = "file.png"
+    std::string checkpoint, preview;
+    int checkpoint_every = 0;
 };
 bool load_toml(const std::string& path, TomlConfig& out, std::string& err);
+bool save_checkpoint(const std::string& path, const trb_checkpoint_info& info, const float* rgb, std::string& err);
+bool load_checkpoint(const std::string& path, trb_checkpoint_info& info, float* rgb, size_t capacity, std::string& err);
+bool checkpoint_matches(const trb_checkpoint_info& a, const trb_checkpoint_info& b);
+bool save_png_srgb(const std::string& path, const float* rgb, int w, int h, float exposure, std::string& err);
 bool save_exr_bgr_half(const std::string& path, const float* rgb, int w, int h, std::string& err);
 
 }  // namespace trb

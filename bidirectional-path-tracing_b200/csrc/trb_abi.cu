@@ -670,6 +670,16 @@ int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_de
 
 extern "C" {
 
+int trb_framebuffer_upload(trb_context* c, const float* rgb, int width, int height) {
+    if (!c || !rgb || width <= 0 || height <= 0) return TRB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    const size_t nf = size_t(width) * height * 3;
+    TRB_CUDA(c, c->fb.alloc(nf));
+    TRB_CUDA(c, cudaMemcpyAsync(c->fb.p, rgb, nf * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
 int trb_render_path_device(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, int accumulate, float* d_rgb, trb_stats* stats) {
     if (!c || !d_rgb) return TRB_ERR_INVALID;
     int rc = render_path_impl(c, d, pd, accumulate, d_rgb, stats);

@@ -20,6 +20,7 @@
 #pragma once
 #include <cstddef>
 #include <cstdint>
+#include <cstring>
 #include <memory>
 #include <random>
 #include <stdexcept>
@@ -67,6 +68,11 @@ struct Config {  // core.h:195-248 (the fields the offline BDPT path reads) + op
     int64_t waveSamples = 0;      // samples per wavefront, 0 = library default
     bool russianRoulette = false; // bdpt.h:18 ships NO_RR 1; true runs the reference's own NO_RR 0 code (TRB_FLAG_RUSSIAN_ROULETTE)
     int maxDepth = 0;             // depth cap under russianRoulette, 0 = TRB_RR_DEFAULT_MAX_DEPTH
+    // restartable renders: every checkpointEvery samples per pixel the running frame buffer goes to checkpointFile (and, tone-
+    // mapped, to previewPng); a run that finds a checkpoint of the same render continues from it
+    std::string checkpointFile, previewPng;
+    int checkpointEvery = 0;
+    int stopAfterCheckpoints = 0; // > 0: leave Renderer::render() after that many checkpoints, as an interrupted run would (tests; CLI: $TRB_STOP_AFTER_CHECKPOINTS)
 };
 
 // main.cpp:22-116. Returns renderer.realtime. Throws std::runtime_error("Invalid integrator type") for an unknown
@@ -178,6 +184,9 @@ struct Integrator {  // integrator.h:23-70
     virtual bool init();                                        // integrator.cpp:16-20: allocate + clear rgb
     virtual v3f render(const Ray&, Sampler&) const = 0;         // one sample
     virtual bool renderFrame() { return false; }                // ADDED: the offline pixel loop as one device call
+    // ADDED: samples [sppBegin, sppEnd) of every pixel on device 0, onto the context's frame buffer when `accumulate`; rgb = the sum so far
+    virtual bool renderRange(int /*sppBegin*/, int /*sppEnd*/, bool /*accumulate*/) { return false; }
+    virtual void describe(trb_checkpoint_info& info) const { std::memset(&info, 0, sizeof(info)); }
     virtual void cleanUp() { save(); }                          // integrator.cpp:22-24
     bool save();                                                // writes <toml stem>.exr (integrator.cpp:26-30, utils.h:95-156)
 };
@@ -191,6 +200,8 @@ struct BDPTIntegrator : Integrator {  // bdpt.h:37-518
     // light-tracing splats are added into rgb->data as the reference does (bdpt.h:360-370). Returns Li.
     v3f render(const Ray& ray, Sampler& sampler) const override;
     bool renderFrame() override;
+    bool renderRange(int sppBegin, int sppEnd, bool accumulate) override;
+    void describe(trb_checkpoint_info& info) const override;
 };
 
 struct PathTracerIntegrator : Integrator {  // path.h:15-262, the estimator the reference cross-checks BDPT with
@@ -200,6 +211,8 @@ struct PathTracerIntegrator : Integrator {  // path.h:15-262, the estimator the 
     // One sample on the device with the sampler's own number stream, consumed in the reference's (depth-first) order.
     v3f render(const Ray& ray, Sampler& sampler) const override;
     bool renderFrame() override;
+    bool renderRange(int sppBegin, int sppEnd, bool accumulate) override;
+    void describe(trb_checkpoint_info& info) const override;
     trb_path_desc pathDesc() const;
 };
 
@@ -209,7 +222,8 @@ struct Renderer {  // renderer.h:20-33
     bool realTime = false, nogui = true;
     explicit Renderer(const Config& config);
     bool init(bool isRealTime, bool nogui);  // renderer.cpp:55-110 (offline branch; isRealTime => false: no graphics stack)
-    void render();                           // renderer.cpp:112-215 (offline branch) => integrator->renderFrame()
+    void render();                           // renderer.cpp:112-215 (offline branch) => integrator->renderFrame(), or the
+                                             // checkpointed loop over integrator->renderRange() (Config::checkpointEvery)
     void cleanUp();                          // renderer.cpp:221-227
 };
 

@@ -173,6 +173,22 @@ int trb_host_load_toml(const char* toml_path, trb_render_desc* out, char* obj_pa
                        char* type_out, size_t type_len, int* realtime_out);
 /* the `type = "path"` keys of the same file (main.cpp:94-102: isExplicit, maxDepth, rrProb, emitterSamples, bsdfSamples) */
 int trb_host_load_toml_path(const char* toml_path, struct trb_path_desc* out);
+/* restartable renders.  A checkpoint holds the running-sum frame buffer, the number of samples per pixel in it
+ * and the description of the render; trb_host_checkpoint_matches says whether a description continues it.  Resume = restore the
+ * buffer (trb_framebuffer_upload), then render [spp_done, spp) with accumulate = 1.  The save is write-then-rename. */
+typedef struct trb_checkpoint_info {
+    trb_render_desc desc;
+    trb_path_desc path;     /* integrator == 1 only */
+    int32_t integrator;     /* 0 = bdpt, 1 = path */
+    int32_t spp_done;
+    uint64_t scene_hash;    /* caller's fingerprint of the scene (0 = unchecked) */
+} trb_checkpoint_info;
+int trb_host_save_checkpoint(const char* path, const trb_checkpoint_info* info, const float* rgb);
+/* rgb_out may be null to read the header only */
+int trb_host_load_checkpoint(const char* path, trb_checkpoint_info* info_out, float* rgb_out, size_t capacity_floats);
+int trb_host_checkpoint_matches(const trb_checkpoint_info* a, const trb_checkpoint_info* b);
+/* quick-look image: 8-bit sRGB PNG of exposure * rgb (row 0 = top) */
+int trb_host_save_png(const char* path, const float* rgb, int width, int height, float exposure);
 /* saveEXR (src/core/utils.h:95-156): channels B,G,R stored as half, row 0 = top. */
 int trb_host_save_exr(const char* path, const float* rgb, int width, int height);
 const char* trb_host_last_error(void);
@@ -209,6 +225,9 @@ int trb_render_bdpt(trb_context*, const trb_render_desc*, int accumulate, float*
 /* Same, result left in a caller-provided DEVICE buffer (width*height*3 floats) - used for the multi-GPU
  * NCCL reduce and the device-resident throughput measurement. */
 int trb_render_bdpt_device(trb_context*, const trb_render_desc*, int accumulate, float* d_rgb, trb_stats* stats);
+
+/* Restore the context's frame buffer (the one trb_render_*(accumulate = 1, host buffer out) adds to), e.g. from a checkpoint. */
+int trb_framebuffer_upload(trb_context*, const float* rgb, int width, int height);
 
 /* The reference's unidirectional path tracer (src/integrators/path.h:15-262, `type = "path"`) on the same wavefront:
  * the independent estimator the reference checks BDPT against (cbox_bdpt_path.toml).  Same conventions as trb_render_bdpt. */

@@ -157,6 +157,32 @@ def test_cli_renders_exr(trb, gpu_ctx, tmp_path):
     assert bad.returncode != 0 and "Syntax" in bad.stderr
 
 
+def test_cli_checkpoint_resume(trb, gpu_ctx, tmp_path):
+    """a run interrupted after its first checkpoint and started again resumes from the file and ends with the
+    image of an uninterrupted run; the preview PNG is there."""
+    cv2 = pytest.importorskip("cv2")
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    extra = 'checkpoint = "run.ckpt"\ncheckpointEvery = 3\npreview = "run.png"\n'
+    _, toml = _export(trb, "caustic", tmp_path, extra=extra, width=160, height=120, rr_depth=8, spp=8)
+    exe = [str(PKG / "tinyrender_b200"), str(toml), "nogui"]
+    r1 = subprocess.run(exe, capture_output=True, text=True, timeout=300, env=dict(os.environ, TRB_STOP_AFTER_CHECKPOINTS="1"))
+    assert r1.returncode == 0 and "Checkpoint: 3 of 8" in r1.stdout and "Stopped after 1" in r1.stdout, r1.stdout + r1.stderr
+    info, part = trb.load_checkpoint(tmp_path / "run.ckpt")
+    assert info.spp_done == 3 and info.desc.spp == 8 and part.mean() > 0
+    r2 = subprocess.run(exe, capture_output=True, text=True, timeout=300)
+    assert r2.returncode == 0 and "Resuming from" in r2.stdout and "3 of 8" in r2.stdout and "Checkpoint: 8 of 8" in r2.stdout, r2.stdout + r2.stderr
+    assert "Checkpoint: 3 of 8" not in r2.stdout   # the first slice was not rendered again
+    bgr = cv2.imread(str(tmp_path / "scene.exr"), cv2.IMREAD_UNCHANGED)
+    img, _ = gpu_ctx("caustic").render_bdpt(trb.render_desc(width=160, height=120, spp=8, rr_depth=8))
+    assert bgr is not None and np.allclose(bgr[:, :, ::-1], img, rtol=2e-3, atol=1e-4)
+    png = cv2.imread(str(tmp_path / "run.png"), cv2.IMREAD_UNCHANGED)
+    assert png is not None and png.shape == (120, 160, 3) and png.mean() > 10
+    # a different render (other seed) does not pick the checkpoint up
+    toml.write_text(toml.read_text() + "seed = 99\n")
+    r3 = subprocess.run(exe, capture_output=True, text=True, timeout=300)
+    assert r3.returncode == 0 and "Resuming from" not in r3.stdout
+
+
 def test_cli_and_cpp_api_path_tracer(trb, gpu_ctx, gold, tmp_path):
     """`type = "path"` through the same host surface: the CLI writes the frame trb_render_path gives, and
     PathTracerIntegrator::render(ray, sampler) with Sampler(seed) per path returns the unmodified reference's Li

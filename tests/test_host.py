@@ -136,6 +136,46 @@ def test_exr_writer(trb, tmp_path):
     assert np.allclose(back[..., ::-1], img, rtol=1e-3, atol=1e-4)  # half precision, channels B,G,R, row 0 = top
 
 
+def test_checkpoint_round_trip_and_png(trb, tmp_path):
+    """the checkpoint file (running-sum frame buffer + samples done + render description) round-trips, a damaged
+    file is refused, `matches` tells the same render from another one, and the quick-look PNG decodes to the sRGB curve"""
+    rng = np.random.default_rng(5)
+    info = trb.CheckpointInfo()
+    info.desc = trb.render_desc(width=40, height=30, spp=64, rr_depth=8)
+    info.integrator, info.spp_done, info.scene_hash = 0, 24, 1234567
+    rgb = rng.random((30, 40, 3)).astype(np.float32)
+    f = tmp_path / "a.ckpt"
+    trb.save_checkpoint(f, info, rgb)
+    got, img = trb.load_checkpoint(f)
+    assert (got.spp_done, got.desc.spp, got.desc.width, got.scene_hash) == (24, 64, 40, 1234567) and np.array_equal(img, rgb)
+    assert trb.checkpoint_matches(info, got)
+    other = trb.CheckpointInfo.from_buffer_copy(bytes(info))
+    other.desc.seed = 7
+    assert not trb.checkpoint_matches(info, other)
+    other = trb.CheckpointInfo.from_buffer_copy(bytes(info))
+    other.desc.spp_begin, other.desc.spp_end, other.desc.wave_samples, other.spp_done = 24, 64, 4096, 0   # what a resumed run passes
+    assert trb.checkpoint_matches(info, other)
+    raw = bytearray(f.read_bytes())
+    raw[len(raw) // 2] ^= 0x40
+    (tmp_path / "bad.ckpt").write_bytes(bytes(raw))
+    with pytest.raises(trb.TrbError):
+        trb.load_checkpoint(tmp_path / "bad.ckpt")
+    (tmp_path / "short.ckpt").write_bytes(bytes(raw[: len(raw) // 3]))
+    with pytest.raises(trb.TrbError):
+        trb.load_checkpoint(tmp_path / "short.ckpt")
+    with pytest.raises(trb.TrbError):
+        trb.load_checkpoint(tmp_path / "missing.ckpt")
+    cv2 = pytest.importorskip("cv2")
+    ramp = np.linspace(0, 1.2, 40, dtype=np.float32)[None, :, None].repeat(30, 0).repeat(3, 2)
+    ramp[:, :, 1] *= 0.5
+    trb.save_png(tmp_path / "a.png", ramp, exposure=1.0)
+    bgr = cv2.imread(str(tmp_path / "a.png"), cv2.IMREAD_UNCHANGED)
+    assert bgr is not None and bgr.shape == (30, 40, 3) and bgr.dtype == np.uint8
+    v = np.clip(ramp, 0, 1)
+    want = np.where(v <= 0.0031308, 12.92 * v, 1.055 * np.power(v, 1 / 2.4) - 0.055)
+    assert np.abs(bgr[:, :, ::-1].astype(np.float64) - want * 255).max() <= 1.0
+
+
 def test_reference_loader_parity_if_available(trb):
     """Where the reference itself is present (this container), the loader is compared array by array."""
     import refh
