@@ -81,7 +81,7 @@ struct WaveParams {
     int32_t* q_in;        // P   live slots entering this bounce
     int32_t* q_out;       // P   live slots leaving it
     EyeVertex* ev;        // P   eye vertex of the current bounce (connecting slots only)
-    int32_t* q_conn;      // P   slots whose eye vertex connects this bounce (non-delta, not an emitter)
+    int32_t* q_conn;      // P*K (slot << 6 | light vertex) pairs to connect this bounce, dense (path tracer: a P-slot queue)
     uint32_t* counters;   // [0]=q_out count, [1]=shadow count, [2]=closest rays traced, [3]=any rays traced
     RayT* sray;           // shadow capacity
     Pending* spend;       // shadow capacity

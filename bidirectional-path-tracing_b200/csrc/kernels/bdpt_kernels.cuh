@@ -408,12 +408,23 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
         }
         push_shadow(p, want, sr, Li, li_target);
     }
-    // ---- connectVertices (bdpt.h:434-483): handed to k_connect_vertices, one thread per (eye vertex, light vertex) ----
+    // ---- connectVertices (bdpt.h:434-483): handed to k_connect_vertices as a DENSE list of (slot, light vertex) pairs ----
+    // A slot has 0..K stored light vertices (3-4 on average): one thread per (slot, j < K) left most lanes of the pair kernel
+    // without work.  Each connecting lane reserves nlv entries (warp scan + one atomic per warp) and writes them in order.
     {
-        const bool conn = connect && p.nlv[slot] > 0;
-        uint32_t ci = queue_push(p.counters + CTR_CONN, conn);
-        if (conn) {
-            p.q_conn[ci] = slot;
+        const int nl = connect ? p.nlv[slot] : 0;
+        int inc = nl;
+        const int lane = threadIdx.x & 31;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += t; }
+        const int total = __shfl_sync(0xffffffffu, inc, 31);
+        if (total) {
+            uint32_t base = 0;
+            if (lane == 31) base = atomicAdd(p.counters + CTR_CONN, uint32_t(total));
+            base = __shfl_sync(0xffffffffu, base, 31) + uint32_t(inc - nl);
+            for (int j = 0; j < nl; ++j) p.q_conn[base + uint32_t(j)] = (slot << 6) | j;
+        }
+        if (nl > 0) {
             EyeVertex e;
             e.px = s.p.x; e.py = s.p.y; e.pz = s.p.z; e.vcm = vcm;
             e.nx = s.n.x; e.ny = s.n.y; e.nz = s.n.z; e.vc = vc;
@@ -442,22 +453,21 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
     if (go) p.q_out[idx] = slot;
 }
 
-// ---- connectVertices (bdpt.h:434-483): one thread per (connecting eye vertex k, light vertex j), j fastest.  Replaces the per-thread loop over the sample's
-// light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). -------------------------------
-__global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_conn_ptr) {
-    const uint32_t nc = *n_conn_ptr;
-    const unsigned long long total = (unsigned long long)nc * uint32_t(p.K);
+// ---- connectVertices (bdpt.h:434-483): one thread per (eye vertex, stored light vertex) pair of the dense list k_eye_bounce wrote.
+// Replaces the per-thread loop over the sample's light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). ----
+__global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_pairs_ptr) {
+    const unsigned long long total = *n_pairs_ptr;
     const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballot of push_shadow
     const float li_scale = p.parity ? 1.f : (1.f / p.spp);
     for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total_w; t += (unsigned long long)gridDim.x * blockDim.x) {
         bool want = false; RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
         if (t < total) {
-            // j fastest: the K lanes of one eye vertex read the same EyeVertex / nlv / q_conn words (one broadcast
-            // transaction instead of K re-reads from HBM: the j-major order re-read every eye vertex K times and
-            // measured 2.1 GB of DRAM traffic per launch, profiles/dram_traffic.json r1i)
-            const uint32_t k = uint32_t(t / uint32_t(p.K)), j = uint32_t(t - (unsigned long long)k * uint32_t(p.K));
-            const int slot = p.q_conn[k];
-            if (int(j) < p.nlv[slot]) {
+            // the pairs of one eye vertex are neighbours: its lanes read the same EyeVertex words (one broadcast transaction)
+            const int pair = p.q_conn[t];
+            const int slot = pair >> 6;
+            const uint32_t j = uint32_t(pair & 63);
+            {
+
                 const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
                 float4 ea = ep[0], eb = ep[1], ec = ep[2], ed = ep[3];
                 const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(j) * p.P + slot);

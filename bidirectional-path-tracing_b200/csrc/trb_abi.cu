@@ -199,7 +199,7 @@ int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     TRB_CUDA(c, c->hit.alloc(P)); TRB_CUDA(c, c->hit0.alloc(P));
     TRB_CUDA(c, c->st_t.alloc(P)); TRB_CUDA(c, c->st_v.alloc(P));
     TRB_CUDA(c, c->lv.alloc(P * kk)); TRB_CUDA(c, c->nlv.alloc(P));
-    TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P)); TRB_CUDA(c, c->ev.alloc(P));
+    TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P * kk)); TRB_CUDA(c, c->ev.alloc(P));  // q_conn: (slot, light vertex) pairs
     TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
     TRB_CUDA(c, c->sray2.alloc(shadow_cap)); TRB_CUDA(c, c->spend2.alloc(shadow_cap));
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
@@ -509,6 +509,7 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << (rr_enabled(*d) ? 21 : 22));
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
+    if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");  // (slot << 6 | vertex) pair words
     rc = ensure_wave(c, size_t(P), K);
     if (rc) return rc;
     if (sort_enabled(c, *d)) { rc = ensure_sort(c, size_t(P), c->sray.n); if (rc) return rc; }
