@@ -8,8 +8,13 @@
 // partition; what changes is the node layout (children boxes in the parent, 64 B, float4 loads) and the
 // traversal (ordered, pruned, stack in registers/shared memory).
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
+#include <utility>
+#include <vector>
 
 #include "tr_host.h"
 
@@ -125,33 +130,49 @@ bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& ma
 }
 
 // ---- reference-order BVH build ---------------------------------------------------------------------
+// Host threads for the build: the arithmetic and the resulting order are those of the sequential algorithm (every thread
+// works on a disjoint primitive range); only the wall time changes (10 M triangles: 1.9 s -> see DESIGN section 12).
+static unsigned build_threads() {
+    if (const char* e = std::getenv("TRB_BUILD_THREADS")) { int v = std::atoi(e); if (v >= 1) return unsigned(std::min(v, 64)); }
+    return std::max(1u, std::min(std::thread::hardware_concurrency(), 16u));
+}
+template <class F>
+static void parallel_for(size_t n, size_t grain, F fn) {  // fn(begin, end)
+    const unsigned T = build_threads();
+    if (T <= 1 || n < 2 * grain) { fn(size_t(0), n); return; }
+    const size_t chunks = std::min<size_t>(T, (n + grain - 1) / grain);
+    std::vector<std::thread> th;
+    for (size_t c = 1; c < chunks; ++c) th.emplace_back([=]() { fn(n * c / chunks, n * (c + 1) / chunks); });
+    fn(size_t(0), n / chunks);
+    for (auto& t : th) t.join();
+}
+
 bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
     const size_t n = s.n_tris;
     if (n == 0) { err = "empty scene"; return false; }
     // per-triangle bounds and centroid, computed as AcceleratorBVH::BVHNode::{getBBox,getCentroid} do
     // (accel.h:71-106): box by min/max over the vertices, centroid = ((v0 + v1) + v2) / 3.0f
     std::vector<float> bmin(3 * n), bmax(3 * n), cen(3 * n);
-    for (size_t t = 0; t < n; ++t) {
-        V3 a = vtx(s, s.tri_v[3 * t]), b = vtx(s, s.tri_v[3 * t + 1]), c = vtx(s, s.tri_v[3 * t + 2]);
-        const float pa[3] = {a.x, a.y, a.z}, pb[3] = {b.x, b.y, b.z}, pc[3] = {c.x, c.y, c.z};
-        for (int k = 0; k < 3; ++k) {
-            bmin[3 * t + k] = std::min(std::min(pa[k], pb[k]), pc[k]);
-            bmax[3 * t + k] = std::max(std::max(pa[k], pb[k]), pc[k]);
-            cen[3 * t + k] = ((pa[k] + pb[k]) + pc[k]) / 3.0f;
+    parallel_for(n, 1 << 16, [&](size_t t0, size_t t1) {
+        for (size_t t = t0; t < t1; ++t) {
+            V3 a = vtx(s, s.tri_v[3 * t]), b = vtx(s, s.tri_v[3 * t + 1]), c = vtx(s, s.tri_v[3 * t + 2]);
+            const float pa[3] = {a.x, a.y, a.z}, pb[3] = {b.x, b.y, b.z}, pc[3] = {c.x, c.y, c.z};
+            for (int k = 0; k < 3; ++k) {
+                bmin[3 * t + k] = std::min(std::min(pa[k], pb[k]), pc[k]);
+                bmax[3 * t + k] = std::max(std::max(pa[k], pb[k]), pc[k]);
+                cen[3 * t + k] = ((pa[k] + pb[k]) + pc[k]) / 3.0f;
+            }
         }
-    }
+    });
     out.order.resize(n);
     for (size_t t = 0; t < n; ++t) out.order[t] = int32_t(t);  // objects are created shape-major, accel.h:116-120
-    out.nodes.clear();
-    out.nodes.reserve(2 * n / 3 + 16);
+    std::vector<int32_t>& ord = out.order;
 
     struct Todo { uint32_t start, end; int32_t parent; bool is_right; };
-    std::vector<Todo> stack;
-    stack.push_back({0u, uint32_t(n), -1, false});
-    std::vector<int32_t>& ord = out.order;
-    while (!stack.empty()) {
-        Todo td = stack.back();
-        stack.pop_back();
+    // One step of the reference's loop (bvh.h:159-246): bound the range, emit the node, split it.  `nodes` is the array the
+    // node goes into (the whole tree, or a subtree built on its own); children are pushed right first so that the left one
+    // is built next: pre-order, as the reference's flat array.
+    auto step = [&](const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack) {
         const uint32_t start = td.start, end = td.end, cnt = end - start;
         RefTree::Node node;
         node.start = start; node.count = cnt; node.left = -1; node.right = -1;
@@ -167,12 +188,12 @@ bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
                 cmin[k] = std::min(cmin[k], cen[3 * t + k]); cmax[k] = std::max(cmax[k], cen[3 * t + k]);
             }
         }
-        const int32_t me = int32_t(out.nodes.size());
-        out.nodes.push_back(node);
+        const int32_t me = int32_t(nodes.size());
+        nodes.push_back(node);
         if (td.parent >= 0) {
-            if (td.is_right) out.nodes[td.parent].right = me; else out.nodes[td.parent].left = me;
+            if (td.is_right) nodes[td.parent].right = me; else nodes[td.parent].left = me;
         }
-        if (cnt <= 4) continue;  // leafSize = 4 (bvh.h:122)
+        if (cnt <= 4) return;  // leafSize = 4 (bvh.h:122)
         // split axis: BBox::maxDimension with its y/z comparison quirk (bvh.h:82-87)
         const float ex = cmax[0] - cmin[0], ey = cmax[1] - cmin[1], ez = cmax[2] - cmin[2];
         int dim = 0;
@@ -185,9 +206,79 @@ bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
             if (cen[3 * ord[i] + dim] < split) { std::swap(ord[i], ord[mid]); ++mid; }
         }
         if (mid == start || mid == end) mid = start + (end - start) / 2;
-        // right is pushed first so that left is built next: pre-order, as the reference's flat array
         stack.push_back({mid, end, me, true});
         stack.push_back({start, mid, me, false});
+    };
+
+    const unsigned T = build_threads();
+    const uint32_t defer_below = (T > 1 && n >= (size_t(1) << 17)) ? uint32_t(n / (size_t(T) * 8)) : 0u;  // 0: plain sequential build
+    // top of the tree, sequentially and in pre-order; a range smaller than `defer_below` is set aside as a subtree task and
+    // leaves a placeholder in the pre-order sequence
+    struct Item { int32_t top_index; int32_t task; };  // one of the two is >= 0
+    struct Task { Todo td; std::vector<RefTree::Node> nodes; };
+    std::vector<RefTree::Node> top;
+    std::vector<Item> seq;
+    std::vector<Task> tasks;
+    std::vector<std::pair<int32_t, bool>> task_parent;  // (top parent, is_right) per task
+    {
+        std::vector<Todo> stack;
+        stack.push_back({0u, uint32_t(n), -1, false});
+        while (!stack.empty()) {
+            Todo td = stack.back();
+            stack.pop_back();
+            if (defer_below && td.end - td.start < defer_below && td.parent >= 0) {
+                seq.push_back({-1, int32_t(tasks.size())});
+                task_parent.push_back({td.parent, td.is_right});
+                Task t; t.td = {td.start, td.end, -1, false};
+                tasks.push_back(std::move(t));
+                continue;
+            }
+            seq.push_back({int32_t(top.size()), -1});
+            step(td, top, stack);
+        }
+    }
+    // the set-aside subtrees, in parallel (disjoint primitive ranges), each into its own node array with local indices
+    if (!tasks.empty()) {
+        std::atomic<size_t> next{0};
+        auto worker = [&]() {
+            std::vector<Todo> stack;
+            for (size_t i = next.fetch_add(1); i < tasks.size(); i = next.fetch_add(1)) {
+                Task& t = tasks[i];
+                t.nodes.reserve(2 * size_t(t.td.end - t.td.start) / 3 + 4);
+                stack.clear();
+                stack.push_back(t.td);
+                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(td, t.nodes, stack); }
+            }
+        };
+        std::vector<std::thread> th;
+        for (unsigned k = 1; k < T; ++k) th.emplace_back(worker);
+        worker();
+        for (auto& t : th) t.join();
+    }
+    // stitch: final index = position in the pre-order sequence, a subtree counting for all of its nodes
+    std::vector<int32_t> top_final(top.size(), 0), task_base(tasks.size(), 0);
+    size_t total = 0;
+    for (const Item& it : seq) {
+        if (it.top_index >= 0) { top_final[it.top_index] = int32_t(total); total += 1; }
+        else { task_base[it.task] = int32_t(total); total += tasks[it.task].nodes.size(); }
+    }
+    out.nodes.assign(total, RefTree::Node{});
+    for (size_t i = 0; i < top.size(); ++i) {
+        RefTree::Node nd = top[i];
+        if (nd.left >= 0) nd.left = top_final[nd.left];
+        if (nd.right >= 0) nd.right = top_final[nd.right];
+        out.nodes[top_final[i]] = nd;
+    }
+    for (size_t k = 0; k < tasks.size(); ++k) {
+        const int32_t base = task_base[k];
+        const std::vector<RefTree::Node>& sub = tasks[k].nodes;
+        for (size_t i = 0; i < sub.size(); ++i) {
+            RefTree::Node nd = sub[i];
+            if (nd.left >= 0) { nd.left += base; nd.right += base; }
+            out.nodes[size_t(base) + i] = nd;
+        }
+        RefTree::Node& par = out.nodes[top_final[task_parent[k].first]];
+        if (task_parent[k].second) par.right = base; else par.left = base;
     }
     return true;
 }
@@ -196,15 +287,19 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     if (!s.positions || !s.normals || !s.tri_v || !s.tri_n || !s.tri_mat || !s.tri_shape || !s.materials) {
         err = "null array in scene description"; return false;
     }
-    for (size_t t = 0; t < s.n_tris; ++t) {
-        for (int k = 0; k < 3; ++k) {
-            if (s.tri_v[3 * t + k] < 0 || size_t(s.tri_v[3 * t + k]) >= s.n_positions) { err = "vertex index out of range"; return false; }
-            if (s.tri_n[3 * t + k] < 0 || size_t(s.tri_n[3 * t + k]) >= s.n_normals) { err = "normal index out of range (the reference needs vn on every face)"; return false; }
+    std::atomic<int> bad{0};  // 1 vertex index, 2 normal index, 3 shape order
+    parallel_for(s.n_tris, 1 << 16, [&](size_t t0, size_t t1) {
+        for (size_t t = t0; t < t1; ++t) {
+            for (int k = 0; k < 3; ++k) {
+                if (s.tri_v[3 * t + k] < 0 || size_t(s.tri_v[3 * t + k]) >= s.n_positions) bad.store(1);
+                else if (s.tri_n[3 * t + k] < 0 || size_t(s.tri_n[3 * t + k]) >= s.n_normals) { int z = 0; bad.compare_exchange_strong(z, 2); }
+            }
+            if (s.tri_shape[t] < 0 || size_t(s.tri_shape[t]) >= s.n_shapes || (t > 0 && s.tri_shape[t] < s.tri_shape[t - 1])) { int z = 0; bad.compare_exchange_strong(z, 3); }
         }
-        if (s.tri_shape[t] < 0 || size_t(s.tri_shape[t]) >= s.n_shapes || (t > 0 && s.tri_shape[t] < s.tri_shape[t - 1])) {
-            err = "tri_shape must be non-decreasing and < n_shapes"; return false;
-        }
-    }
+    });
+    if (bad.load() == 1) { err = "vertex index out of range"; return false; }
+    if (bad.load() == 2) { err = "normal index out of range (the reference needs vn on every face)"; return false; }
+    if (bad.load() == 3) { err = "tri_shape must be non-decreasing and < n_shapes"; return false; }
     if (!derive_materials(s, out.materials, err)) return false;
     std::vector<int32_t> shape_to_emitter;
     if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
@@ -220,7 +315,8 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
 
     out.tris.resize(n);
     out.shade.resize(n);
-    for (size_t p = 0; p < n; ++p) {
+    parallel_for(n, 1 << 16, [&](size_t p0, size_t p1) {
+    for (size_t p = p0; p < p1; ++p) {
         const int32_t t = tree.order[p];
         V3 a = vtx(s, s.tri_v[3 * t]), b = vtx(s, s.tri_v[3 * t + 1]), c = vtx(s, s.tri_v[3 * t + 2]);
         V3 n0 = nrm(s, s.tri_n[3 * t]), n1 = nrm(s, s.tri_n[3 * t + 1]), n2 = nrm(s, s.tri_n[3 * t + 2]);
@@ -239,6 +335,7 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         ds.shape = s.tri_shape[t]; ds.prim = t - shape_first[s.tri_shape[t]]; ds.mat = mat;
         ds.emitter = shape_to_emitter[s.tri_shape[t]]; ds.tri = t; ds.pad = 0;
     }
+    });
 
     // inner nodes only; leaves become negative child references
     std::vector<int32_t> inner_index(tree.nodes.size(), -1);
@@ -250,17 +347,21 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         return ~int32_t((nd.start << 3) | nd.count);
     };
     out.nodes.resize(size_t(n_inner));
-    for (size_t i = 0; i < tree.nodes.size(); ++i) {
-        const RefTree::Node& nd = tree.nodes[i];
-        if (nd.left < 0) continue;
-        DevNode& d = out.nodes[inner_index[i]];
-        const RefTree::Node& l = tree.nodes[nd.left];
-        const RefTree::Node& r = tree.nodes[nd.right];
-        for (int k = 0; k < 3; ++k) { d.c0min[k] = l.bmin[k]; d.c0max[k] = l.bmax[k]; d.c1min[k] = r.bmin[k]; d.c1max[k] = r.bmax[k]; }
-        d.ref0 = make_ref(nd.left); d.ref1 = make_ref(nd.right); d.pad0 = d.pad1 = 0;
-        // the traversal kernel postpones sibling leaves as ONE contiguous triangle range (trace_warp.cuh)
-        if (l.left < 0 && r.left < 0 && r.start != l.start + l.count) { err = "sibling leaves are not adjacent in the primitive order"; return false; }
-    }
+    std::atomic<bool> apart{false};
+    parallel_for(tree.nodes.size(), 1 << 15, [&](size_t i0, size_t i1) {
+        for (size_t i = i0; i < i1; ++i) {
+            const RefTree::Node& nd = tree.nodes[i];
+            if (nd.left < 0) continue;
+            DevNode& d = out.nodes[inner_index[i]];
+            const RefTree::Node& l = tree.nodes[nd.left];
+            const RefTree::Node& r = tree.nodes[nd.right];
+            for (int k = 0; k < 3; ++k) { d.c0min[k] = l.bmin[k]; d.c0max[k] = l.bmax[k]; d.c1min[k] = r.bmin[k]; d.c1max[k] = r.bmax[k]; }
+            d.ref0 = make_ref(nd.left); d.ref1 = make_ref(nd.right); d.pad0 = d.pad1 = 0;
+            // the traversal kernel postpones sibling leaves as ONE contiguous triangle range (trace_coop.cuh)
+            if (l.left < 0 && r.left < 0 && r.start != l.start + l.count) apart.store(true);
+        }
+    });
+    if (apart.load()) { err = "sibling leaves are not adjacent in the primitive order"; return false; }
     out.root_ref = make_ref(0);
     for (int k = 0; k < 3; ++k) { out.scene_min[k] = tree.nodes[0].bmin[k]; out.scene_max[k] = tree.nodes[0].bmax[k]; }
     // depth (pre-order array: children always follow their parent)

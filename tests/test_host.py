@@ -136,6 +136,18 @@ def test_exr_writer(trb, tmp_path):
     assert np.allclose(back[..., ::-1], img, rtol=1e-3, atol=1e-4)  # half precision, channels B,G,R, row 0 = top
 
 
+def test_parallel_bvh_build_is_the_sequential_build(trb, monkeypatch):
+    """the multi-threaded host build (subtrees on their own threads, stitched in pre-order) yields the primitive order of the
+    single-threaded, reference-order build (bvh.h:147-247) on a scene large enough to be split up"""
+    import gen_tess_scene
+    scene = gen_tess_scene.make_scene(300_000, seed=3)
+    monkeypatch.setenv("TRB_BUILD_THREADS", "1")
+    seq = scene.bvh_order()
+    monkeypatch.setenv("TRB_BUILD_THREADS", "5")
+    par = scene.bvh_order()
+    assert np.array_equal(seq, par) and sorted(seq.tolist()) == list(range(scene.n_tris))
+
+
 def test_checkpoint_round_trip_and_png(trb, tmp_path):
     """the checkpoint file (running-sum frame buffer + samples done + render description) round-trips, a damaged
     file is refused, `matches` tells the same render from another one, and the quick-look PNG decodes to the sRGB curve"""
