@@ -37,6 +37,10 @@ WORKLOADS = {
                     desc="caustic scene (glass sphere + area light, 32536 tris) 1024x1024 BDPT rrDepth 8"),
     "hardlight": dict(scene="scene_hardlight.npz", width=1024, height=1024, rr_depth=16,
                       desc="hard-light scene (occluded emitter, 36404 tris) 1024x1024 BDPT rrDepth 16"),
+    "c1_glass": dict(scene="scene_caustic.npz", width=800, height=600, rr_depth=8,
+                     desc="configs[0] as shipped: data/a5/cbox/tinyrender/cbox_bdpt_glass.toml (cbox_mirror.obj, 800x600, rrDepth 8; 256 spp = --spp 256)"),
+    "c1_bonus": dict(scene="scene_hardlight.npz", width=800, height=600, rr_depth=2,
+                     desc="configs[0] as shipped: data/a5/bonus_bdpt/tinyrender/cbox_bdpt.toml (bonus_bdpt/mesh/cbox.obj, 800x600, rrDepth 2; 512 spp = --spp 512)"),
     "cbox4k": dict(scene="scene_caustic.npz", width=3840, height=2160, rr_depth=8,
                    desc="configs[3]: Cornell box (cbox_mirror.obj) 3840x2160 BDPT rrDepth 8, partitioned by sample index, one reduce of the "
                         "99.5 MB frame buffer (4096 spp in total = --spp 512 on 8 GPUs)"),
