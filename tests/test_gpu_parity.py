@@ -223,6 +223,54 @@ def test_trace_million_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
     assert np.array_equal(ctx.trace_any(_rays(trb, rays)), occ_ref)
 
 
+def test_degenerate_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
+    """The inputs the reference never guards against, against the reference itself: zero direction components (0/0 and
+    x/0 in BBox::intersect, bvh.h:33-69), an all-zero direction, unnormalised and tiny directions, origins ON scene vertices
+    and box faces, origins far outside, max_t below the 1e-3 acceptance threshold, negative and infinite ranges, NaN.  Ids, t
+    and the occlusion flags must be the reference's, whatever it makes of them."""
+    rh, scene = ref_harness(scene_name)
+    rng = np.random.default_rng(77)
+    n = 6000
+    pos = scene.positions
+    v = pos[rng.integers(0, len(pos), n)]
+    tri = rng.integers(0, scene.n_tris, n)
+    cen = pos[scene.tri_v[tri]].mean(1)
+    d = rng.normal(size=(n, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    R = []
+
+    def add(o, dd, mn=1e-8, mx=np.finfo(np.float32).max):
+        r = np.zeros((len(o), 8), np.float32)
+        r[:, 0:3], r[:, 3:6], r[:, 6], r[:, 7] = o, dd, mn, mx
+        R.append(r)
+    for ax in range(3):                      # one and two zero components, from vertices and from centroids
+        z = d.copy(); z[:, ax] = 0; add(v, z); add(cen, z)
+        z = np.zeros_like(d); z[:, ax] = np.sign(d[:, ax]) + (d[:, ax] == 0); add(v, z); add(cen + 1e-3, z)
+    add(cen, np.zeros_like(d))               # no direction at all
+    add(cen, d * 1e-20); add(cen, d * 1e6)   # tiny / huge unnormalised directions
+    add(v, d); add(v, -d)                    # origin exactly on a vertex
+    add(cen - d * 1e4, d)                    # from far outside
+    add(cen - d * 5e-4, d, mx=1e-3); add(cen - d * 5e-4, d, mx=9e-4)   # ranges around the absolute 1e-3 threshold (accel.h:43)
+    add(cen - d, d, mn=-5.0, mx=0.5); add(cen - d, d, mn=0.0, mx=np.inf); add(cen - d, d, mn=2.0, mx=1.0)
+    nan = d.copy(); nan[::3, 0] = np.nan; add(cen, nan)
+    o_nan = cen.copy(); o_nan[::5, 1] = np.nan; add(o_nan, d)
+    rays = np.concatenate(R)
+    ids, tuv, _ = rh.intersect(rays)
+    occ_ref = rh.occluded(rays)
+    base = np.concatenate([[0], np.cumsum(np.bincount(scene.tri_shape, minlength=scene.n_shapes))])
+    tri_ref = np.where(ids[:, 0] == 1, base[np.clip(ids[:, 1], 0, None)] + ids[:, 2], -1).astype(np.int32)
+    ctx = gpu_ctx(scene_name)
+    h = ctx.trace_closest(_rays(trb, rays))
+    bad = np.flatnonzero((h["hit"] != ids[:, 0]) | (h["tri"] != tri_ref))
+    assert len(bad) == 0, (len(bad), len(rays), (bad[:10] // n).tolist(), rays[bad[:3]].tolist())
+    m = ids[:, 0] == 1
+    assert np.array_equal(h["t"][m].view(np.uint32), tuv[m, 0].view(np.uint32))
+    occ = ctx.trace_any(_rays(trb, rays))
+    bad = np.flatnonzero(occ != occ_ref)
+    assert len(bad) == 0, (len(bad), (bad[:10] // n).tolist(), rays[bad[:3]].tolist())
+    print(f"{scene_name}: {len(rays)} degenerate rays, {int(m.sum())} hits, {int(occ_ref.sum())} occluded - identical")
+
+
 def test_tessellated_scene_at_size_vs_oracle(trb):
     """configs[4] at 2 M triangles (HBM-resident acceleration structure, mirror / glass / Phong / Mixture materials):
     hits bit-exact and whole BDPT samples within 1e-5 against the oracle restatement (oracle/bdpt_oracle.cpp, itself
