@@ -424,6 +424,24 @@ class Context:
         return ms.value
 
 
+def render_bdpt_multi(contexts, desc: RenderDesc):
+    """trb_render_bdpt_multi: one frame on the contexts' devices (one context per device, same scene), sample-index sharding and ONE
+    ncclReduce inside the library.  Returns (H x W x 3 float32, stats of device 0)."""
+    arr = (C.c_void_p * len(contexts))(*[c._h.value for c in contexts])
+    st = Stats()
+    img = np.zeros((desc.height, desc.width, 3), np.float32)
+    contexts[0]._chk(lib().trb_render_bdpt_multi(arr, len(contexts), C.byref(desc), _ptr(img), C.byref(st)))
+    return img, st.as_dict()
+
+
+def render_path_multi(contexts, desc: RenderDesc, pd: PathDesc):
+    arr = (C.c_void_p * len(contexts))(*[c._h.value for c in contexts])
+    st = Stats()
+    img = np.zeros((desc.height, desc.width, 3), np.float32)
+    contexts[0]._chk(lib().trb_render_path_multi(arr, len(contexts), C.byref(desc), C.byref(pd), _ptr(img), C.byref(st)))
+    return img, st.as_dict()
+
+
 def build_info() -> str:
     L = lib()
     return L.trb_build_info().decode() if hasattr(L, "trb_build_info") else "host-only"

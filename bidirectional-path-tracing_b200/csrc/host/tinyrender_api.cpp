@@ -270,8 +270,8 @@ v3f BDPTIntegrator::render(const Ray& ray, Sampler& sampler) const {
 
 // Whole frame on G devices of this process: sample-index sharding (replicated scene, disjoint RNG streams; contributions are
 // normalised by the total spp, so partial frame buffers are plain summands), one host thread per device, host-side sum.
-template <class RenderCall>
-static bool render_frame_sharded(const Scene& scene, const trb_render_desc& base, RenderBuffer& rgb, trb_stats* stats, RenderCall call) {
+template <class RenderCall, class MultiCall>
+static bool render_frame_sharded(const Scene& scene, const trb_render_desc& base, RenderBuffer& rgb, trb_stats* stats, RenderCall call, MultiCall multi) {
     const Config& cfg = scene.config;
     const int G = std::max(1, std::min(cfg.gpus, cfg.spp));
     const size_t nf = size_t(cfg.width) * cfg.height * 3;
@@ -281,6 +281,15 @@ static bool render_frame_sharded(const Scene& scene, const trb_render_desc& base
         if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
         if (call(c, base, out, stats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
         return true;
+    }
+    {   // the library's own multi-GPU call: one NCCL reduce of the partial frame buffers over NVLink
+        std::vector<trb_context*> cs;
+        cs.assign(size_t(G), nullptr);
+        for (int g = 0; g < G; ++g) { cs[g] = scene.context(g); if (!cs[g]) { std::printf("%s\n", scene.error().c_str()); return false; } }
+        const int rc = multi(cs.data(), G, base, out, stats);
+        if (rc == TRB_OK) return true;
+        if (rc != TRB_ERR_UNSUPPORTED) { std::printf("%s\n", trb_last_error(cs[0])); return false; }
+        std::printf("NCCL is not available (%s): summing the partial frame buffers on the host\n", trb_last_error(cs[0]));
     }
     std::vector<std::vector<float>> part;
     part.assign(size_t(G), std::vector<float>(nf));
@@ -306,7 +315,8 @@ static bool render_frame_sharded(const Scene& scene, const trb_render_desc& base
 
 bool BDPTIntegrator::renderFrame() {
     return render_frame_sharded(scene, make_desc(scene.config), *rgb, &lastStats,
-                                [](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_bdpt(c, &d, 0, out, st); });
+                                [](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_bdpt(c, &d, 0, out, st); },
+                                [](trb_context* const* cs, int n, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_bdpt_multi(cs, n, &d, out, st); });
 }
 
 bool BDPTIntegrator::renderRange(int sppBegin, int sppEnd, bool accumulate) {
@@ -367,7 +377,8 @@ bool PathTracerIntegrator::renderFrame() {
     base.rr_depth = m_rrDepth;
     const trb_path_desc pd = pathDesc();
     return render_frame_sharded(scene, base, *rgb, &lastStats,
-                                [pd](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_path(c, &d, &pd, 0, out, st); });
+                                [pd](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_path(c, &d, &pd, 0, out, st); },
+                                [pd](trb_context* const* cs, int n, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_path_multi(cs, n, &d, &pd, out, st); });
 }
 
 bool PathTracerIntegrator::renderRange(int sppBegin, int sppEnd, bool accumulate) {

@@ -787,6 +787,110 @@ int trb_render_bdpt(trb_context* c, const trb_render_desc* d, int accumulate, fl
 
 }  // extern "C"
 
+// ---- one frame on several GPUs of this process: sample-index sharding + ONE ncclReduce over NVLink ------------------
+// (bench.py does the same across processes with torch.distributed).  NCCL is loaded at run time by its SONAME
+// - the library has no link-time dependency on it, and a process that already holds torch's copy gets that one.
+#include <dlfcn.h>
+#include <mutex>
+namespace {
+struct Nccl {
+    void* lib = nullptr;
+    int (*CommInitAll)(void** comms, int n, const int* devs) = nullptr;
+    int (*CommDestroy)(void* comm) = nullptr;
+    int (*Reduce)(const void* send, void* recv, size_t count, int dtype, int op, int root, void* comm, cudaStream_t st) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    std::string err;
+    bool load() {
+        if (lib) return true;
+        const char* names[] = {std::getenv("TRB_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) { if (nm && *nm && (lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL))) break; }
+        if (!lib) { err = std::string("cannot load libnccl.so.2: ") + (dlerror() ? dlerror() : "?"); return false; }
+        CommInitAll = reinterpret_cast<decltype(CommInitAll)>(dlsym(lib, "ncclCommInitAll"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
+        Reduce = reinterpret_cast<decltype(Reduce)>(dlsym(lib, "ncclReduce"));
+        GroupStart = reinterpret_cast<decltype(GroupStart)>(dlsym(lib, "ncclGroupStart"));
+        GroupEnd = reinterpret_cast<decltype(GroupEnd)>(dlsym(lib, "ncclGroupEnd"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
+        if (!CommInitAll || !CommDestroy || !Reduce || !GroupStart || !GroupEnd) { err = "libnccl.so.2 lacks a required symbol"; lib = nullptr; return false; }
+        return true;
+    }
+    std::vector<int> devs;      // communicators are kept for the device list they were made for
+    std::vector<void*> comms;
+    bool comms_for(const std::vector<int>& want) {
+        if (want == devs && !comms.empty()) return true;
+        for (void* cm : comms) CommDestroy(cm);
+        comms.assign(want.size(), nullptr); devs = want;
+        int rc = CommInitAll(comms.data(), int(want.size()), want.data());
+        if (rc != 0) { err = std::string("ncclCommInitAll: ") + (GetErrorString ? GetErrorString(rc) : "error"); comms.clear(); devs.clear(); return false; }
+        return true;
+    }
+};
+Nccl g_nccl;
+std::mutex g_nccl_mutex;
+}  // namespace
+
+namespace {
+// fn(context, description of its sample range, device frame buffer, stats or null) -> status
+template <class RenderOne>
+int render_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, float* rgb_out, trb_stats* stats, RenderOne fn) {
+    trb_context* c0 = ctxs[0];
+    if (d->width <= 0 || d->height <= 0 || d->spp < n) return c0->fail(TRB_ERR_INVALID, "trb_render_bdpt_multi: needs spp >= number of devices");
+    std::lock_guard<std::mutex> lock(g_nccl_mutex);
+    if (!g_nccl.load()) return c0->fail(TRB_ERR_UNSUPPORTED, g_nccl.err);
+    std::vector<int> devs;
+    for (int g = 0; g < n; ++g) { if (!ctxs[g]) return TRB_ERR_INVALID; devs.push_back(ctxs[g]->device); }
+    for (int g = 0; g < n; ++g) for (int h = g + 1; h < n; ++h) if (devs[g] == devs[h]) return c0->fail(TRB_ERR_INVALID, "trb_render_bdpt_multi: one context per device");
+    if (!g_nccl.comms_for(devs)) return c0->fail(TRB_ERR_CUDA, g_nccl.err);
+    const size_t nf = size_t(d->width) * d->height * 3;
+    const int s0 = d->spp_begin, s1 = d->spp_end > 0 ? d->spp_end : d->spp;
+    std::vector<int> rc(size_t(n), TRB_OK);
+    std::vector<std::thread> th;
+    for (int g = 0; g < n; ++g) {
+        th.emplace_back([&, g]() {   // one host thread per device: each context has its own streams
+            trb_context* c = ctxs[g];
+            cudaSetDevice(c->device);
+            if (c->fb.alloc(nf) != cudaSuccess) { rc[g] = c->fail(TRB_ERR_CUDA, "frame buffer allocation"); return; }
+            trb_render_desc part = *d;
+            part.spp_begin = s0 + int(int64_t(s1 - s0) * g / n);
+            part.spp_end = s0 + int(int64_t(s1 - s0) * (g + 1) / n);
+            rc[g] = fn(c, &part, c->fb.p, g == 0 ? stats : nullptr);
+        });
+    }
+    for (auto& t : th) t.join();
+    for (int g = 0; g < n; ++g) if (rc[g] != TRB_OK) return rc[g];
+    // contributions are normalised by the total spp: the partial frame buffers are plain summands -> one reduce onto device 0
+    int nrc = g_nccl.GroupStart();
+    for (int g = 0; g < n && nrc == 0; ++g) {
+        cudaSetDevice(ctxs[g]->device);
+        nrc = g_nccl.Reduce(ctxs[g]->fb.p, ctxs[g]->fb.p, nf, /*ncclFloat*/ 7, /*ncclSum*/ 0, 0, g_nccl.comms[g], ctxs[g]->stream);
+    }
+    const int erc = g_nccl.GroupEnd();
+    if (nrc == 0) nrc = erc;
+    if (nrc != 0) return c0->fail(TRB_ERR_CUDA, std::string("ncclReduce: ") + (g_nccl.GetErrorString ? g_nccl.GetErrorString(nrc) : "error"));
+    for (int g = 0; g < n; ++g) { cudaSetDevice(ctxs[g]->device); TRB_CUDA(ctxs[g], cudaStreamSynchronize(ctxs[g]->stream)); }
+    cudaSetDevice(c0->device);
+    if (rgb_out) TRB_CUDA(c0, cudaMemcpyAsync(rgb_out, c0->fb.p, nf * sizeof(float), cudaMemcpyDeviceToHost, c0->stream));
+    TRB_CUDA(c0, cudaStreamSynchronize(c0->stream));
+    return TRB_OK;
+}
+}  // namespace
+
+extern "C" int trb_render_bdpt_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, float* rgb_out, trb_stats* stats) {
+    if (!ctxs || n < 1 || !d || !ctxs[0]) return TRB_ERR_INVALID;
+    if (n == 1) return trb_render_bdpt(ctxs[0], d, 0, rgb_out, stats);
+    return render_multi(ctxs, n, d, rgb_out, stats,
+                        [](trb_context* c, const trb_render_desc* part, float* fb, trb_stats* st) { return render_impl(c, part, 0, fb, st); });
+}
+
+extern "C" int trb_render_path_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, const trb_path_desc* pd, float* rgb_out, trb_stats* stats) {
+    if (!ctxs || n < 1 || !d || !pd || !ctxs[0]) return TRB_ERR_INVALID;
+    if (n == 1) return trb_render_path(ctxs[0], d, pd, 0, rgb_out, stats);
+    return render_multi(ctxs, n, d, rgb_out, stats,
+                        [pd](trb_context* c, const trb_render_desc* part, float* fb, trb_stats* st) { return render_path_impl(c, part, pd, 0, fb, st); });
+}
+
 // ---- parity entry points -------------------------------------------------------------------------------------
 namespace {
 

@@ -226,6 +226,14 @@ int trb_render_bdpt(trb_context*, const trb_render_desc*, int accumulate, float*
  * NCCL reduce and the device-resident throughput measurement. */
 int trb_render_bdpt_device(trb_context*, const trb_render_desc*, int accumulate, float* d_rgb, trb_stats* stats);
 
+/* One frame on n GPUs from ONE process: context g (one per device) renders the sample indices
+ * [g*spp/n, (g+1)*spp/n) of every pixel, then ONE ncclReduce(sum) over NVLink brings the partial frame buffers together on
+ * ctxs[0]'s device; rgb_out (host) receives the sum.  Every context must hold the same scene.  libnccl.so.2 is loaded at run
+ * time ($TRB_NCCL_LIB overrides the name); TRB_ERR_UNSUPPORTED when it is absent.  Replaces the T-thread pixel loop +
+ * g_FrameBufferLocks of renderer.cpp:130-214 / main.cpp:137-143 at node scale. */
+int trb_render_bdpt_multi(trb_context* const* ctxs, int n, const trb_render_desc*, float* rgb_out, trb_stats* stats);
+int trb_render_path_multi(trb_context* const* ctxs, int n, const trb_render_desc*, const trb_path_desc*, float* rgb_out, trb_stats* stats);
+
 /* Restore the context's frame buffer (the one trb_render_*(accumulate = 1, host buffer out) adds to), e.g. from a checkpoint. */
 int trb_framebuffer_upload(trb_context*, const float* rgb, int width, int height);
 

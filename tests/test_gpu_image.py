@@ -121,6 +121,38 @@ def test_4k_film_sharded_by_sample_index(trb, gpu_ctx):
     assert rel_mse <= 3e-3 and abs(full.mean() / small.mean() - 1) <= 0.01
 
 
+def test_in_library_multi_gpu_render(trb, gpu_ctx):
+    """trb_render_bdpt_multi / trb_render_path_multi (needs >= 2 GPUs): sample-index shards on two devices + one ncclReduce inside the
+    library == the single-device render of the same sample indices (same RNG streams; float atomics may reorder)"""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    scene = trb.HostScene.load_npz(GOLD / "scene_caustic.npz")
+    ctxs = [gpu_ctx("caustic"), trb.Context(1)]
+    ctxs[1].upload(scene)
+    desc = trb.render_desc(width=320, height=240, spp=8, rr_depth=8)
+    one, _ = ctxs[0].render_bdpt(desc)
+    two, st = trb.render_bdpt_multi(ctxs, desc)
+    assert np.allclose(one, two, rtol=2e-5, atol=2e-6), float(np.abs(one - two).max())
+    assert st["samples"] == 320 * 240 * 4          # device 0 rendered its half
+    pd = trb.path_desc()
+    one, _ = ctxs[0].render_path(trb.render_desc(width=320, height=240, spp=8, rr_depth=5), pd)
+    two, _ = trb.render_path_multi(ctxs, trb.render_desc(width=320, height=240, spp=8, rr_depth=5), pd)
+    assert np.allclose(one, two, rtol=2e-5, atol=2e-6), float(np.abs(one - two).max())
+    ctxs[1].close()
+    # and through the host surface: `gpus = 2` in the TOML
+    cv2 = pytest.importorskip("cv2")
+    import tempfile
+    tmp = Path(tempfile.mkdtemp(prefix="trb_multi_"))
+    _, toml = _export(trb, "caustic", tmp, extra="gpus = 2\n", width=160, height=120, rr_depth=8, spp=4)
+    r = subprocess.run([str(PKG / "tinyrender_b200"), str(toml), "nogui"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "NCCL is not available" not in r.stdout, r.stdout + r.stderr
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    bgr = cv2.imread(str(tmp / "scene.exr"), cv2.IMREAD_UNCHANGED)
+    img, _ = ctxs[0].render_bdpt(trb.render_desc(width=160, height=120, spp=4, rr_depth=8))
+    assert bgr is not None and np.allclose(bgr[:, :, ::-1], img, rtol=2e-3, atol=1e-4)
+
+
 def test_wave_size_independence(trb, gpu_ctx, scene_name):
     ctx = gpu_ctx(scene_name)
     kw = dict(width=200, height=150, spp=4, rr_depth=8)
