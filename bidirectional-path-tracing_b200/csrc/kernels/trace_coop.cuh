@@ -65,8 +65,13 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         const uint32_t base = atomicAdd(&sh.tail, cnt);
         const uint32_t e0 = (uint32_t(lane) << 27) | first;
 #pragma unroll
-        for (uint32_t k = 0; k < 8u; ++k)   // straight-line predicated stores (cnt <= 8): no divergent loop
+        for (uint32_t k = 0; k < 4u; ++k)   // straight-line predicated stores: a leaf holds <= 4 triangles ...
             if (k < cnt) sh.queue[(base + k) & (TRB_COOP_Q - 1u)] = e0 + k;
+        if (cnt > 4u) {                     // ... only two sibling leaves hit together give more (cnt <= 8)
+#pragma unroll
+            for (uint32_t k = 4; k < 8u; ++k)
+                if (k < cnt) sh.queue[(base + k) & (TRB_COOP_Q - 1u)] = e0 + k;
+        }
         sh.outst[lane] += int32_t(cnt);   // only the owner adds; testers subtract atomically between __syncwarp()s
     };
     auto start_ray = [&]() {
