@@ -325,7 +325,12 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         dt.v0[0] = a.x; dt.v0[1] = a.y; dt.v0[2] = a.z;
         dt.e1[0] = b.x - a.x; dt.e1[1] = b.y - a.y; dt.e1[2] = b.z - a.z;
         dt.e2[0] = c.x - a.x; dt.e2[1] = c.y - a.y; dt.e2[2] = c.z - a.z;
-        dt.tri = t; dt.mat = mat;
+        dt.tri = t;
+        {   // same operation order as the device evaluated it: ((1e-6f * e1.e1) * e2.e2), each dot as (x*x + y*y) + z*z
+            const float e1 = (dt.e1[0] * dt.e1[0] + dt.e1[1] * dt.e1[1]) + dt.e1[2] * dt.e1[2];
+            const float e2 = (dt.e2[0] * dt.e2[0] + dt.e2[1] * dt.e2[1]) + dt.e2[2] * dt.e2[2];
+            dt.illk = 1e-6f * e1 * e2;
+        }
         dt.flags = out.materials[mat].cls | (out.materials[mat].emissive ? 8 : 0);
         DevShade& ds = out.shade[p];
         ds.v0[0] = a.x; ds.v0[1] = a.y; ds.v0[2] = a.z; ds.v1[0] = b.x; ds.v1[1] = b.y; ds.v1[2] = b.z;

@@ -41,7 +41,7 @@ struct alignas(16) DevTri {
     float v0[3];
     int32_t tri;    // global shape-major triangle id
     float e1[3];    // v1 - v0 (one fp32 subtraction, identical to core.h:386)
-    int32_t mat;    // material id (mesh.material_ids[primID])
+    float illk;     // 1e-6f * |e1|^2 * |e2|^2: the conditioning bound of tri_test (trace.cuh), so that it is not recomputed per test
     float e2[3];    // v2 - v0
     int32_t flags;  // bits 0-2: material class; bit 3: emissive material
 };

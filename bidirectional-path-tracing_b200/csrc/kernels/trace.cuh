@@ -184,10 +184,9 @@ TRB_HD bool tri_test(const F4& q0, const F4& q1, const F4& q2, const RayT& r, fl
     float vv = vn * invDet;
     if (vv < 0 || uu + vv > 1) return false;
     float tt = ((q2.x * qx + q2.y * qy) + q2.z * qz) * invDet;
-    // conditioning: |det| against |e1||e2||d| (grazing)
-    float e1 = (q1.x * q1.x + q1.y * q1.y) + q1.z * q1.z, e2 = (q2.x * q2.x + q2.y * q2.y) + q2.z * q2.z;
+    // conditioning: |det| against |e1||e2||d| (grazing); q1.w = 1e-6f * |e1|^2 * |e2|^2 from the host build
     float dd = (r.dx * r.dx + r.dy * r.dy) + r.dz * r.dz;
-    if (det * det < 1e-6f * e1 * e2 * dd) *ill = true;
+    if (det * det < q1.w * dd) *ill = true;
     if (!(tt >= 0.001f)) return false;  // (double)t > 1e-3  <=>  t >= 0.001f for fp32 t
     *t = tt; *u = uu; *v = vv;
     return true;
