@@ -187,6 +187,21 @@ def equal_time_relmse(trb, ctx, wl, w, h, cpu_img, cpu_s, gpu_rate):
                           "(1/8 of the GPU image's variance or less) is included in both figures"}
 
 
+def cpu_port_all_cores(trb, wl, w, h):
+    """BASELINE.md section 3, optional second row: the race-free CPU ceiling.  The reference shares one mt19937 between its
+    worker threads (renderer.cpp:155) and leaves four cores idle (parallelfor.h:30-32); the restatement (oracle/bdpt_oracle.cpp,
+    pinned bit-exact to the reference per path) gives every thread its own Sampler and uses every core."""
+    import oracle_port
+    hw = os.cpu_count() or 8
+    orc = oracle_port.Oracle(load_scene(trb, wl, cpu=True))
+    t0 = time.perf_counter()
+    orc.render(trb.render_desc(width=w, height=h, spp=1, rr_depth=wl["rr_depth"]), threads=hw)
+    sec = time.perf_counter() - t0
+    orc.close()
+    return {"value": w * h / sec / 1e6, "unit": UNIT, "cores": hw, "kind": "port",
+            "sample": f"{w}x{h} film, 1 spp, rrDepth {wl['rr_depth']}, oracle/bdpt_oracle.cpp with one Sampler per thread, {hw} threads"}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -391,6 +406,7 @@ def run_ours(args):
                 out["cpu_baseline"] = dict(info, value=n / s / 1e6, unit=UNIT)
                 if wl["scene"] is not None:  # (the tess workload times the CPU on a smaller instance of the scene: no common image)
                     out["equal_time"] = equal_time_relmse(trb, ctx, wl, fw, fh, cpu_img, s, value * 1e6)
+                    out["cpu_ceiling"] = cpu_port_all_cores(trb, wl, fw, fh)
             except Exception as e:  # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "unavailable", "sample": str(e)}
         print(json.dumps(out))
