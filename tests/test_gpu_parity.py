@@ -145,6 +145,52 @@ def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
     assert draws_same[ok].all()
 
 
+@pytest.mark.parametrize("rr_depth", [1, 2, 3])
+def test_bdpt_paths_at_the_smallest_depths(trb, gpu_ctx, gold, scene_name, rr_depth):
+    """rrDepth 1 (no vertex at all: only the loop tests' draws, Q3), 2 (the shipped cbox_bdpt.toml: one vertex per subpath) and 3,
+    against the restatement (pinned bit-exact to the reference) on the golden rays and random streams: Li, splats, draws"""
+    oracle_port = pytest.importorskip("oracle_port")
+    g = gold("paths", scene_name)
+    n = 1500
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=rr_depth)
+    scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{scene_name}.npz")
+    orc = oracle_port.Oracle(scene)
+    orc.set_config(desc)
+    k = max(rr_depth - 1, 1)
+    c_li, c_pix, c_rgb, c_draws = orc.bdpt_paths(g["rays"][:n], k, injected=g["rng"][:n])
+    orc.close()
+    li, pix, rgb, draws = gpu_ctx(scene_name).bdpt_paths(desc, _rays(trb, g["rays"][:n]), g["rng"][:n])
+    ok = _paths_agree(c_li, c_pix, c_rgb, li, pix, rgb) & (draws == c_draws)
+    print(f"{scene_name} rrDepth {rr_depth}: {ok.sum()}/{n} agree, mean draws {draws.mean():.2f}")
+    assert ok.mean() >= 0.99
+    if rr_depth == 1:
+        assert not li.any() and (pix < 0).all()      # nothing is ever connected
+
+
+def test_edge_configurations_render(trb, gpu_ctx):
+    """sizes and settings at their limits: 1x1 and odd films, one-sample waves, spp 1 (pixel centres, no jitter draws), the deepest
+    supported walk, roulette with max_depth == rr_depth, path tracer with no direct or no indirect samples"""
+    ctx = gpu_ctx("caustic")
+    for kw in (dict(width=1, height=1, spp=3, rr_depth=8), dict(width=7, height=5, spp=2, rr_depth=8, wave_samples=1),
+               dict(width=33, height=17, spp=1, rr_depth=8), dict(width=16, height=16, spp=2, rr_depth=64),
+               dict(width=16, height=16, spp=2, rr_depth=1), dict(width=16, height=16, spp=2, rr_depth=6, max_depth=6, flags=trb.TRB_FLAG_RUSSIAN_ROULETTE)):
+        img, st = ctx.render_bdpt(trb.render_desc(**kw))
+        assert np.isfinite(img).all() and st["samples"] == kw["width"] * kw["height"] * kw["spp"], kw
+        if kw["rr_depth"] == 1:
+            assert not img.any()
+    d = trb.render_desc(width=24, height=16, spp=2, rr_depth=5)
+    for pd in (trb.path_desc(True, 0), trb.path_desc(True, 2, 0.95, 0, 0), trb.path_desc(True, 2, 0.95, 0, 3), trb.path_desc(False, 0),
+               trb.path_desc(True, -1, 0.0), trb.path_desc(True, -1, 1.0)):
+        img, st = ctx.render_path(d, pd)
+        assert np.isfinite(img).all(), (pd.is_explicit, pd.max_depth, pd.emitter_samples, pd.bsdf_samples)
+    with pytest.raises(trb.TrbError):
+        ctx.render_bdpt(trb.render_desc(width=16, height=16, spp=2, rr_depth=65))
+    with pytest.raises(trb.TrbError):
+        ctx.render_bdpt(trb.render_desc(width=16, height=16, spp=2, rr_depth=8, max_depth=4, flags=trb.TRB_FLAG_RUSSIAN_ROULETTE))
+    with pytest.raises(trb.TrbError):
+        ctx.render_path(d, trb.path_desc(True, 2, 0.95, 17, 0))
+
+
 def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, scene_name):
     """TRB_FLAG_RUSSIAN_ROULETTE against the reference built with its own Russian-roulette code enabled (NO_RR 0,
     tools/gen_golden_rr.py).  The reference's walks are unbounded; the device caps them at max_depth, so the walks
