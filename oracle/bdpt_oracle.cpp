@@ -323,6 +323,9 @@ struct Scene {
     /* PathTracerIntegrator settings (main.cpp:94-102 defaults) */
     bool ptExplicit = true; int ptMaxDepth = -1; float ptRRProb = 0.95f; int ptEmitterSamples = 1, ptBsdfSamples = 0;
     int ptDepthCap = 0;  /* > 0: the device's hard cap on the recursion depth (the reference has none); 0 = none */
+    /* DirectIntegrator settings (main.cpp:88-93): 0 mis, 1 area, 2 solidAngle, 3 cosineHemisphere, 4 bsdf */
+    int diStrategy = 0, diEmitterSamples = 1, diBsdfSamples = 1;
+    std::vector<v3> shapesCenter; std::vector<float> shapesMaxX;  /* renderer.cpp:294-304, :349-358 */
     bool rrOn = false;   /* false = NO_RR 1, the shipped build */
     int rrMaxDepth = 0;  /* 0 = no cap (the reference) */
 
@@ -497,8 +500,18 @@ struct Scene {
             for (float& c : e.cdf) c /= sum;
             emitters.push_back(e);
         }
+        /* Scene::load's tail (renderer.cpp:294-304): centre = running sum over mesh.indices / their number; the AABB's max.x */
+        shapesCenter.assign(nShapes, V(0.f)); shapesMaxX.assign(nShapes, -std::numeric_limits<float>::infinity());
+        for (size_t sh = 0; sh < nShapes; sh++) {
+            v3 c = V(0.f);
+            for (int t = shapeFirst[sh]; t < shapeFirst[sh + 1]; t++)
+                for (int k = 0; k < 3; k++) { v3 p = vert(t, k); c = c + p; shapesMaxX[sh] = std::max(shapesMaxX[sh], p.x); }
+            shapesCenter[sh] = c / float(3 * (shapeFirst[sh + 1] - shapeFirst[sh]));
+        }
         buildBVH();
     }
+    v3 getShapeCenter(size_t shapeID) const { return shapesCenter[shapeID]; }
+    float getShapeRadius(size_t shapeID) const { return shapesMaxX[shapeID] - shapesCenter[shapeID].x; } /* renderer.cpp:349-353 */
 };
 
 }  // namespace
@@ -977,6 +990,202 @@ struct PathTracer {
     }
 };
 
+
+/* DirectIntegrator (src/integrators/direct.h:16-467, `type = "direct"`): one-bounce direct illumination with five sampling
+ * strategies, written for sphere emitters (centre = shape centre, radius = AABB max.x - centre.x, renderer.cpp:349-358).
+ * SURVEY 8(f) N4.  M_PI is platform.h:51's FLOAT constant, so `4 * M_PI * r * r` is fp32. */
+inline v3 squareToUniformSphere(float sx, float sy) { /* math.h:119-127 */
+    float phi = sx * kPi * 2.0f;
+    float cosTheta = 1.f - (2.f * sy);
+    float sinTheta = sqrtf(float(std::fmax(1.f - cosTheta * cosTheta, 0)));
+    return V(sinTheta * cosf(phi), sinTheta * sinf(phi), cosTheta);
+}
+inline bool quadratic(double a, double b, double c, double& t0, double& t1) { /* direct.h:16-35 */
+    double discriminant = b * b - 4 * a * c;
+    if (discriminant > 0) {
+        double sqrtDiscriminant = std::sqrt(discriminant), inv2a = 1 / (2 * a);
+        t0 = (-b + sqrtDiscriminant) * inv2a; t1 = (-b - sqrtDiscriminant) * inv2a;
+        return true;
+    } else if (discriminant == 0) {
+        t0 = (-b + std::sqrt(discriminant)) / (2 * a); t1 = t0;
+        return true;
+    }
+    return false;
+}
+inline bool raySphereIntersect(const Ray& ray_, v3 sphereCenter, float sphereRadius, float& outT) { /* direct.h:37-69 */
+    v3 newOrigin = ray_.o - sphereCenter;
+    double c = dot(newOrigin, newOrigin) - (sphereRadius * sphereRadius);
+    double b = dot(newOrigin, ray_.d) * 2.0;
+    double a = dot(ray_.d, ray_.d);
+    double r1, r2;
+    r1 = ray_.min_t;
+    bool intersects = quadratic(a, b, c, r1, r2);
+    if (!intersects) return false; /* (r2 is read uninitialised in the reference on this branch; the result is false either way) */
+    const double inf = std::numeric_limits<double>::infinity();
+    r1 = r1 < 0 ? inf : r1; r2 = r2 < 0 ? inf : r2;
+    r1 = (r1 > ray_.min_t && r1 < ray_.max_t) ? r1 : inf;
+    r2 = (r2 > ray_.min_t && r2 < ray_.max_t) ? r2 : inf;
+    double closestT = std::fmin(r1, r2);
+    if (closestT > ray_.min_t && closestT < ray_.max_t) { outT = float(closestT); return true; }
+    return false;
+}
+
+struct Direct {
+    const Scene& scene;
+    BDPT svc;
+    size_t m_emitterSamples, m_bsdfSamples; int m_strategy;
+    explicit Direct(const Scene& s) : scene(s), svc(s, nullptr), m_emitterSamples(size_t(s.diEmitterSamples)), m_bsdfSamples(size_t(s.diBsdfSamples)),
+        m_strategy(s.diStrategy) {}
+    static float balanceHeuristic(float nf, float fPdf, float ng, float gPdf) { float f = nf * fPdf, g = ng * gPdf; return f / (f + g); } /* :81-84 */
+    static const float inf() { return std::numeric_limits<float>::infinity(); }
+
+    void sampleSphereByArea(float sx, float sy, v3 pShading, v3 emitterCenter, float emitterRadius, v3& pos, v3& ne, v3& wiW, float& pdf) const { /* :96-109 */
+        ne = squareToUniformSphere(sx, sy);
+        pos = ne * emitterRadius + emitterCenter;
+        wiW = normalize(pos - pShading);
+        pdf = 1.f / (4 * kPi * emitterRadius * emitterRadius);
+    }
+    static float coneCosThetaMax(v3 pShading, v3 emitterCenter, float emitterRadius) { /* :123-124, :427-428 */
+        float sinThetaMaxSquared = emitterRadius * emitterRadius / length2(emitterCenter - pShading);
+        return sqrtf(std::fmax(0.f, 1.f - sinThetaMaxSquared));
+    }
+    void sampleSphereBySolidAngle(float sx, float sy, v3 pShading, v3 emitterCenter, float emitterRadius, v3& wiW, float& pdf) const { /* :111-141 */
+        v3 centerDir = normalize(emitterCenter - pShading);
+        Frame fr(centerDir);
+        float cosThetaMax = coneCosThetaMax(pShading, emitterCenter, emitterRadius);
+        float cosTheta = (1.f - sx) + (sx * cosThetaMax);
+        float phi = sy * kPi * 2.0f;
+        float sinTheta = sqrtf(float(std::fmax(1.f - (cosTheta * cosTheta), 0)));
+        v3 sampleDir = V(sinTheta * cosf(phi), sinTheta * sinf(phi), cosTheta);
+        wiW = fr.toWorld(sampleDir);
+        pdf = kInvTwoPi * (1.f / (1.f - cosThetaMax));
+    }
+
+    v3 renderArea(SurfaceInteraction& hit, Sampler& sampler) const { /* :143-197 */
+        v3 Lr = V(0.f);
+        for (unsigned int i = 0; i < m_emitterSamples; ++i) {
+            float emitterPdf;
+            size_t id = svc.selectEmitter(sampler.next(), emitterPdf);
+            const Emitter& emitter = scene.emitters[id];
+            v3 emitterCenter = scene.getShapeCenter(emitter.shapeID);
+            float emitterRadius = scene.getShapeRadius(emitter.shapeID);
+            float sx, sy; sampler.next2D(&sx, &sy);
+            v3 outPos, outNe, outwiW; float outPdf;
+            sampleSphereByArea(sx, sy, hit.p, emitterCenter, emitterRadius, outPos, outNe, outwiW, outPdf);
+            float lightDistanceSquared = length2(hit.p - outPos);
+            float cosOutgoing = dot(-outwiW, outNe);
+            v3 wiLocal = hit.frameNs.toLocal(outwiW);
+            if (cosOutgoing <= 0.f || wiLocal.z <= 0.f) continue;
+            Ray r(hit.p, outwiW, kEps, std::sqrt(lightDistanceSquared) - kEps);
+            SurfaceInteraction vis;
+            if (!scene.intersect(r, vis)) {
+                hit.wi = wiLocal;
+                float areaToSolidAngle = cosOutgoing * (1.f / lightDistanceSquared);
+                Lr = Lr + emitter.radiance * svc.getBSDF(hit)->eval(hit) * (1.f / outPdf) * (1.f / emitterPdf) * areaToSolidAngle;
+            }
+        }
+        return Lr / float(m_emitterSamples);
+    }
+    v3 renderCosineHemisphere(SurfaceInteraction& hit, Sampler& sampler) const { /* :200-234 */
+        v3 Lr = V(0.f);
+        for (unsigned int i = 0; i < m_emitterSamples; ++i) {
+            float sx, sy; sampler.next2D(&sx, &sy);
+            v3 localRayDir = squareToCosineHemisphere(sx, sy);
+            v3 worldRayDir = normalize(hit.frameNs.toWorld(localRayDir));
+            SurfaceInteraction vis;
+            if (scene.intersect(Ray(hit.p, worldRayDir, kEps, inf()), vis)) {
+                v3 emittedRadiance = svc.getEmission(vis);
+                hit.wi = localRayDir;
+                Lr = Lr + emittedRadiance * svc.getBSDF(hit)->eval(hit) * (1.0f / squareToCosineHemispherePdf(localRayDir));
+            }
+        }
+        return Lr / float(m_emitterSamples);
+    }
+    v3 renderBSDF(SurfaceInteraction& hit, Sampler& sampler) const { /* :236-268 */
+        v3 Lr = V(0.f);
+        for (unsigned int i = 0; i < m_bsdfSamples; ++i) {
+            float sx, sy; sampler.next2D(&sx, &sy);
+            float pdf;
+            v3 brdfCosTheta = svc.getBSDF(hit)->sample(hit, sx, sy, &pdf);
+            SurfaceInteraction vis;
+            if (scene.intersect(Ray(hit.p, hit.frameNs.toWorld(hit.wi), kEps, inf()), vis)) {
+                v3 emittedRadiance = svc.getEmission(vis);
+                Lr = Lr + emittedRadiance * brdfCosTheta * float(1.0 / pdf);
+            }
+        }
+        return Lr / float(m_bsdfSamples);
+    }
+    /* the emitter loop shared by renderSolidAngle (:284-331, weighted = false, ray up to the centre distance + Epsilon) and
+     * renderMIS (:357-403, weighted = true, unbounded ray) */
+    v3 solidAngleLoop(SurfaceInteraction& hit, Sampler& sampler, bool weighted) const {
+        v3 Lr = V(0.f);
+        for (unsigned int i = 0; i < m_emitterSamples; ++i) {
+            float emitterPdf;
+            size_t id = svc.selectEmitter(sampler.next(), emitterPdf);
+            const Emitter& emitter = scene.emitters[id];
+            v3 emitterCenter = scene.getShapeCenter(emitter.shapeID);
+            float emitterRadius = scene.getShapeRadius(emitter.shapeID);
+            float sx, sy; sampler.next2D(&sx, &sy);
+            v3 outwiW; float outPdf;
+            sampleSphereBySolidAngle(sx, sy, hit.p, emitterCenter, emitterRadius, outwiW, outPdf);
+            v3 wiLocal = hit.frameNs.toLocal(outwiW);
+            if (wiLocal.z <= 0.f) continue;
+            Ray r(hit.p, outwiW, kEps, weighted ? inf() : length(emitterCenter - hit.p) + kEps);
+            SurfaceInteraction vis;
+            bool contributes;
+            if (scene.intersect(r, vis)) contributes = emitter.shapeID == vis.shapeID;
+            else { float outT; contributes = raySphereIntersect(r, emitterCenter, emitterRadius, outT); }
+            if (contributes) {
+                hit.wi = wiLocal;
+                if (weighted) {
+                    float bsdfPdf = svc.getBSDF(hit)->pdf(hit);
+                    float weight = balanceHeuristic(float(m_emitterSamples), outPdf * emitterPdf, float(m_bsdfSamples), bsdfPdf);
+                    Lr = Lr + emitter.radiance * svc.getBSDF(hit)->eval(hit) * weight * (1.f / outPdf) * (1.f / emitterPdf);
+                } else {
+                    Lr = Lr + emitter.radiance * svc.getBSDF(hit)->eval(hit) * (1.f / outPdf) * (1.f / emitterPdf);
+                }
+            }
+        }
+        return Lr;
+    }
+    v3 renderSolidAngle(SurfaceInteraction& hit, Sampler& sampler) const { return solidAngleLoop(hit, sampler, false) / float(m_emitterSamples); }
+    v3 renderMIS(SurfaceInteraction& hit, Sampler& sampler) const { /* :340-447 */
+        v3 emitterEstimator = solidAngleLoop(hit, sampler, true), bsdfEstimator = V(0.f);
+        emitterEstimator = m_emitterSamples == 0 ? V(0.f) : (emitterEstimator / float(m_emitterSamples));
+        for (unsigned int i = 0; i < m_bsdfSamples; ++i) {
+            float sx, sy; sampler.next2D(&sx, &sy);
+            float outPdf;
+            v3 brdfCosTheta = svc.getBSDF(hit)->sample(hit, sx, sy, &outPdf);
+            SurfaceInteraction vis;
+            if (scene.intersect(Ray(hit.p, hit.frameNs.toWorld(hit.wi), kEps, inf()), vis)) {
+                v3 emittedRadiance = svc.getEmission(vis);
+                if (emittedRadiance == V(0.f)) continue;
+                const Emitter& emitter = scene.emitters[svc.getEmitterIDByShapeID(vis.shapeID)];
+                float cosThetaMax = coneCosThetaMax(hit.p, scene.getShapeCenter(emitter.shapeID), scene.getShapeRadius(emitter.shapeID));
+                float emitterSolidAnglePdf = kInvTwoPi * (1.f / (1.f - cosThetaMax));
+                emitterSolidAnglePdf *= 1.f / scene.emitters.size(); /* getEmitterPdf */
+                float weight = balanceHeuristic(float(m_bsdfSamples), outPdf, float(m_emitterSamples), emitterSolidAnglePdf);
+                bsdfEstimator = bsdfEstimator + emittedRadiance * brdfCosTheta * weight * (1.f / outPdf);
+            }
+        }
+        bsdfEstimator = m_bsdfSamples == 0 ? V(0.f) : (bsdfEstimator / float(m_bsdfSamples));
+        return V(0.f) + (emitterEstimator + bsdfEstimator);
+    }
+    v3 render(const Ray& ray, Sampler& sampler) const { /* :449-462; every strategy starts the same way (:147-154) */
+        SurfaceInteraction hit;
+        if (!scene.intersect(ray, hit)) return V(0.f);
+        v3 emittedRadiance = svc.getEmission(hit);
+        if (emittedRadiance != V(0.f)) return emittedRadiance;
+        switch (m_strategy) {
+            case 0: return renderMIS(hit, sampler);
+            case 1: return renderArea(hit, sampler);
+            case 2: return renderSolidAngle(hit, sampler);
+            case 3: return renderCosineHemisphere(hit, sampler);
+            default: return renderBSDF(hit, sampler);
+        }
+    }
+};
+
 }  // namespace
 
 /* ---- C interface (ctypes: oracle/oracle_port.py) ------------------------------------------------------------ */
@@ -1026,6 +1235,34 @@ void orc_path_paths(void* h, const float* rays8, const int* seeds, const float* 
         v3 L = pt.render(Ray(V(r[0], r[1], r[2]), V(r[3], r[4], r[5]), r[6], r[7]), sm);
         Li[3 * i] = L.x; Li[3 * i + 1] = L.y; Li[3 * i + 2] = L.z;
         if (nDraws) nDraws[i] = int(sm.pos);
+    }
+}
+
+void orc_set_direct(void* h, int strategy, int emitter_samples, int bsdf_samples) {
+    Scene* s = static_cast<Scene*>(h);
+    s->diStrategy = strategy; s->diEmitterSamples = emitter_samples; s->diBsdfSamples = bsdf_samples;
+}
+
+/* DirectIntegrator::render on given camera rays; random numbers from Sampler(seed) or injected rows */
+void orc_direct_paths(void* h, const float* rays8, const int* seeds, const float* injected, int64_t stride, int64_t n, float* Li, int* nDraws) {
+    Scene* s = static_cast<Scene*>(h);
+    Direct di(*s);
+    for (int64_t i = 0; i < n; i++) {
+        Sampler sm(seeds ? seeds[i] : 0);
+        if (!seeds) sm.injected = injected + i * stride;
+        const float* r = rays8 + 8 * i;
+        v3 L = di.render(Ray(V(r[0], r[1], r[2]), V(r[3], r[4], r[5]), r[6], r[7]), sm);
+        Li[3 * i] = L.x; Li[3 * i + 1] = L.y; Li[3 * i + 2] = L.z;
+        if (nDraws) nDraws[i] = int(sm.pos);
+    }
+}
+
+/* per shape: centre xyz + radius (Scene::getShapeCenter / getShapeRadius) */
+void orc_shape_spheres(void* h, float* out4) {
+    Scene* s = static_cast<Scene*>(h);
+    for (size_t i = 0; i < s->shapesCenter.size(); i++) {
+        out4[4 * i] = s->shapesCenter[i].x; out4[4 * i + 1] = s->shapesCenter[i].y; out4[4 * i + 2] = s->shapesCenter[i].z;
+        out4[4 * i + 3] = s->getShapeRadius(i);
     }
 }
 

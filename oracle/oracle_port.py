@@ -79,6 +79,29 @@ class Oracle:
             self.L.orc_path_paths(self.h, _p(rays8), None, _p(injected), C.c_int64(injected.shape[1]), C.c_int64(n), _p(li), _p(nd))
         return li, nd
 
+    STRATEGIES = {"mis": 0, "area": 1, "solidAngle": 2, "cosineHemisphere": 3, "bsdf": 4}
+
+    def set_direct(self, strategy="mis", emitter_samples=1, bsdf_samples=1):
+        """DirectIntegrator settings (main.cpp:88-93)"""
+        self.L.orc_set_direct(self.h, int(self.STRATEGIES.get(strategy, strategy)), int(emitter_samples), int(bsdf_samples))
+
+    def direct_paths(self, rays8, seeds=None, injected=None):
+        rays8 = np.ascontiguousarray(rays8, np.float32).reshape(-1, 8)
+        n = len(rays8)
+        li, nd = np.zeros((n, 3), np.float32), np.zeros(n, np.int32)
+        if seeds is not None:
+            seeds = np.ascontiguousarray(seeds, np.int32)
+            self.L.orc_direct_paths(self.h, _p(rays8), _p(seeds), None, C.c_int64(0), C.c_int64(n), _p(li), _p(nd))
+        else:
+            injected = np.ascontiguousarray(injected, np.float32)
+            self.L.orc_direct_paths(self.h, _p(rays8), None, _p(injected), C.c_int64(injected.shape[1]), C.c_int64(n), _p(li), _p(nd))
+        return li, nd
+
+    def shape_spheres(self, n_shapes):
+        out = np.zeros((n_shapes, 4), np.float32)
+        self.L.orc_shape_spheres(self.h, _p(out))
+        return out
+
     def bvh_order(self):
         o = np.zeros(self.n_tris, np.int32)
         self.L.orc_bvh_order(self.h, _p(o))

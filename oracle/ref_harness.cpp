@@ -320,6 +320,16 @@ void refh_integrator_paths(void* hp, const float* rays, const int* seeds, int64_
     }
 }
 
+/* Scene::getShapeCenter / getShapeRadius (renderer.cpp:349-358) per shape: centre xyz + radius - DirectIntegrator's sphere emitters */
+void refh_shape_spheres(void* hp, float* out4) {
+    auto* h = static_cast<Handle*>(hp);
+    const Scene& sc = h->renderer->scene;
+    for (size_t i = 0; i < sc.worldData.shapes.size(); i++) {
+        v3f c = sc.getShapeCenter(i);
+        out4[4 * i] = c.x; out4[4 * i + 1] = c.y; out4[4 * i + 2] = c.z; out4[4 * i + 3] = sc.getShapeRadius(i);
+    }
+}
+
 /* Whole-frame render through Renderer::render (the reference's own threaded pixel loop).
  * Returns the seconds spent inside render(); rgb_out = W*H*3 floats. */
 double refh_render(void* hp, float* rgb_out) {

@@ -168,6 +168,12 @@ class RefHarness:
         self.L.refh_integrator_paths(self.h, _p(rays8), _p(seeds), C.c_int64(n), _p(li), _p(nd))
         return li, nd
 
+    def shape_spheres(self, n_shapes: int) -> np.ndarray:
+        """Scene::getShapeCenter / getShapeRadius per shape: (n_shapes, 4) = centre xyz, radius"""
+        out = np.zeros((n_shapes, 4), np.float32)
+        self.L.refh_shape_spheres(self.h, _p(out))
+        return out
+
     def render(self):
         img = np.zeros((self.height, self.width, 3), np.float32)
         sec = self.L.refh_render(self.h, _p(img))

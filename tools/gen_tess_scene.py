@@ -120,6 +120,50 @@ def make_scene(tris: int = 10_000_000, seed: int = 1):
                          n_shapes=len(parts), shape_names=names)
 
 
+def make_sphere_light_scene(n: int = 20, seed: int = 3):
+    """what DirectIntegrator (src/integrators/direct.h) is written for - SPHERE emitters, which no shipped scene
+    has.  The same open box with two emissive UV spheres (exact, no displacement; different radii and radiances, so that
+    selectEmitter and the per-emitter cone matter), a Phong sphere, a diffuse sphere and a glass sphere on a Mixture floor."""
+    trb = importlib.import_module("bidirectional-path-tracing_b200")
+    rng = np.random.default_rng(seed)
+    x0, x1, y0, y1, z0, z1 = -1.0, 1.0, 0.0, 1.6, -1.0, 1.0
+    parts = [
+        ("lightA", 0, _sphere(n, np.array([-0.45, 1.25, -0.2]), 0.14, rng, amp=0.0)),
+        ("lightB", 8, _sphere(n, np.array([0.5, 1.05, 0.25]), 0.09, rng, amp=0.0)),
+        ("backWall", 1, _quad((x0, y0, z0), (x1, y0, z0), (x1, y1, z0), (x0, y1, z0), (0, 0, 1))),
+        ("ceiling", 1, _quad((x0, y1, z0), (x1, y1, z0), (x1, y1, z1), (x0, y1, z1), (0, -1, 0))),
+        ("leftWall", 2, _quad((x0, y0, z0), (x0, y1, z0), (x0, y1, z1), (x0, y0, z1), (1, 0, 0))),
+        ("rightWall", 3, _quad((x1, y0, z0), (x1, y0, z1), (x1, y1, z1), (x1, y1, z0), (-1, 0, 0))),
+        ("floor", 4, _quad((x0, y0, z0), (x0, y0, z1), (x1, y0, z1), (x1, y0, z0), (0, 1, 0))),
+        ("phongSphere", 7, _sphere(n, np.array([-0.5, 0.3, -0.1]), 0.3, rng, amp=0.0)),
+        ("diffuseSphere", 1, _sphere(n, np.array([0.45, 0.25, -0.35]), 0.25, rng, amp=0.0)),
+        ("glassSphere", 6, _sphere(n, np.array([0.1, 0.2, 0.45]), 0.2, rng, amp=0.0)),
+    ]
+    mats = np.zeros(9, trb.MATERIAL_DTYPE)
+    mats["ni"], mats["tf"] = 1.0, 1.0
+
+    def setm(i, illum, kd=(0, 0, 0), ks=(0, 0, 0), ke=(0, 0, 0), ns=1.0, ni=1.0):
+        mats[i]["illum"], mats[i]["kd"], mats[i]["ks"], mats[i]["ke"], mats[i]["ns"], mats[i]["ni"] = illum, kd, ks, ke, ns, ni
+    setm(0, 7, kd=(0.78, 0.78, 0.78), ke=(30, 28, 24))
+    setm(1, 7, kd=(0.73, 0.73, 0.73))
+    setm(2, 7, kd=(0.63, 0.065, 0.05))
+    setm(3, 7, kd=(0.14, 0.45, 0.091))
+    setm(4, 8, kd=(0.5, 0.5, 0.5), ks=(0.3, 0.3, 0.3), ns=30.0)
+    setm(5, 3, ks=(1, 1, 1))
+    setm(6, 6, ks=(1, 1, 1), ni=1.5)
+    setm(7, 2, kd=(0.3, 0.3, 0.3), ks=(0.6, 0.6, 0.6), ns=50.0)
+    setm(8, 7, kd=(0.78, 0.78, 0.78), ke=(12, 20, 40))
+    P, N, TV, TM, TS, names = [], [], [], [], [], []
+    base = 0
+    for s, (name, m, (pos, nrm, tri)) in enumerate(parts):
+        P.append(pos); N.append(nrm); TV.append(tri + base)
+        TM.append(np.full(len(tri), m, np.int32)); TS.append(np.full(len(tri), s, np.int32)); names.append(name)
+        base += len(pos)
+    tv = np.concatenate(TV)
+    return trb.HostScene(np.concatenate(P), np.concatenate(N), tv, tv.copy(), np.concatenate(TM), np.concatenate(TS), mats,
+                         n_shapes=len(parts), shape_names=names)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--tris", type=int, default=200_000)
