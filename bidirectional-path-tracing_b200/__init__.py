@@ -67,6 +67,18 @@ def path_desc(is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, b
 TRB_PT_DEFAULT_DEPTH_CAP = 64
 
 
+class DirectDesc(C.Structure):
+    """trb_direct_desc: DirectIntegrator settings (main.cpp:88-93)"""
+    _fields_ = [("strategy", C.c_int32), ("emitter_samples", C.c_int32), ("bsdf_samples", C.c_int32), ("reserved", C.c_int32)]
+
+
+DI_STRATEGIES = {"mis": 0, "area": 1, "solidAngle": 2, "cosineHemisphere": 3, "bsdf": 4}  # TRB_DI_*; any other name -> -1
+
+
+def direct_desc(strategy="mis", emitter_samples=1, bsdf_samples=1) -> DirectDesc:
+    return DirectDesc(int(DI_STRATEGIES.get(strategy, -1) if isinstance(strategy, str) else strategy), int(emitter_samples), int(bsdf_samples), 0)
+
+
 class CheckpointInfo(C.Structure):
     """trb_checkpoint_info"""
     _fields_ = [("desc", RenderDesc), ("path", PathDesc), ("integrator", C.c_int32), ("spp_done", C.c_int32), ("scene_hash", C.c_uint64)]
@@ -234,6 +246,13 @@ class HostScene:
         _chk_host(lib().trb_host_bvh_order(C.byref(d), _ptr(out), C.c_size_t(self.n_tris)))
         return out
 
+    def shape_spheres(self) -> np.ndarray:
+        """Scene::getShapeCenter / getShapeRadius per shape (renderer.cpp:294-304, 349-358): (n_shapes, 4) = centre xyz, radius"""
+        out = np.zeros((self.n_shapes, 4), np.float32)
+        d = self.desc()
+        _chk_host(lib().trb_host_shape_spheres(C.byref(d), _ptr(out), C.c_size_t(self.n_shapes)))
+        return out
+
     def emitters(self) -> dict:
         d = self.desc()
         cap = 64
@@ -261,6 +280,13 @@ def load_toml_path(path) -> PathDesc:
     pd = PathDesc()
     _chk_host(lib().trb_host_load_toml_path(str(path).encode(), C.byref(pd)))
     return pd
+
+
+def load_toml_direct(path) -> DirectDesc:
+    """the `type = "direct"` keys of a scene TOML (src/main.cpp:88-93); an unknown samplingStrategy comes back as -1"""
+    dd = DirectDesc()
+    _chk_host(lib().trb_host_load_toml_direct(str(path).encode(), C.byref(dd)))
+    return dd
 
 
 def save_checkpoint(path, info: CheckpointInfo, rgb: np.ndarray) -> None:
@@ -401,6 +427,25 @@ class Context:
                                          _ptr(li), _ptr(draws)))
         return li, draws
 
+    def render_direct(self, desc: RenderDesc, dd: DirectDesc, accumulate: bool = False, download: bool = True):
+        """Renderer::render with the DirectIntegrator (direct.h). Returns (H x W x 3 float32 | None, stats)."""
+        st = Stats()
+        img = np.zeros((desc.height, desc.width, 3), np.float32) if download else None
+        self._chk(self._L.trb_render_direct(self._h, C.byref(desc), C.byref(dd), int(accumulate), _ptr(img) if download else None, C.byref(st)))
+        return img, st.as_dict()
+
+    def direct_paths(self, desc: RenderDesc, dd: DirectDesc, cam_rays: np.ndarray, rng: np.ndarray):
+        """DirectIntegrator::render on given camera rays with injected random numbers (n x stride)."""
+        cam_rays = np.ascontiguousarray(cam_rays, RAY_DTYPE)
+        rng = np.ascontiguousarray(rng, np.float32)
+        n, stride = rng.shape
+        assert n == len(cam_rays)
+        li = np.zeros((n, 3), np.float32)
+        draws = np.zeros(n, np.int32)
+        self._chk(self._L.trb_direct_paths(self._h, C.byref(desc), C.byref(dd), _ptr(cam_rays), _ptr(rng), C.c_size_t(n), C.c_size_t(stride),
+                                           _ptr(li), _ptr(draws)))
+        return li, draws
+
     def render_bdpt(self, desc: RenderDesc, accumulate: bool = False, download: bool = True):
         """Renderer::render (offline branch) with the BDPT integrator. Returns (H x W x 3 float32 | None, stats)."""
         st = Stats()
@@ -439,6 +484,14 @@ def render_path_multi(contexts, desc: RenderDesc, pd: PathDesc):
     st = Stats()
     img = np.zeros((desc.height, desc.width, 3), np.float32)
     contexts[0]._chk(lib().trb_render_path_multi(arr, len(contexts), C.byref(desc), C.byref(pd), _ptr(img), C.byref(st)))
+    return img, st.as_dict()
+
+
+def render_direct_multi(contexts, desc: RenderDesc, dd: DirectDesc):
+    arr = (C.c_void_p * len(contexts))(*[c._h.value for c in contexts])
+    st = Stats()
+    img = np.zeros((desc.height, desc.width, 3), np.float32)
+    contexts[0]._chk(lib().trb_render_direct_multi(arr, len(contexts), C.byref(desc), C.byref(dd), _ptr(img), C.byref(st)))
     return img, st.as_dict()
 
 

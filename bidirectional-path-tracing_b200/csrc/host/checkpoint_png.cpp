@@ -121,7 +121,7 @@ bool checkpoint_matches(const trb_checkpoint_info& a, const trb_checkpoint_info&
     bool same = std::memcmp(x.eye, y.eye, sizeof(x.eye)) == 0 && std::memcmp(x.at, y.at, sizeof(x.at)) == 0 && std::memcmp(x.up, y.up, sizeof(x.up)) == 0 &&
                 x.fov_deg == y.fov_deg && x.width == y.width && x.height == y.height && x.spp == y.spp && x.rr_depth == y.rr_depth && x.seed == y.seed &&
                 (x.flags & image_flags) == (y.flags & image_flags) && x.max_depth == y.max_depth && a.integrator == b.integrator && a.scene_hash == b.scene_hash;
-    if (same && a.integrator == 1) same = std::memcmp(&a.path, &b.path, sizeof(a.path)) == 0;
+    if (same && (a.integrator == 1 || a.integrator == 2)) same = std::memcmp(&a.path, &b.path, sizeof(a.path)) == 0;
     return same;
 }
 }  // namespace trb

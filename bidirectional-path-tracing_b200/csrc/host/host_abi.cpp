@@ -67,6 +67,15 @@ int trb_host_load_toml_path(const char* toml_path, trb_path_desc* out) {
     return TRB_OK;
 }
 
+int trb_host_load_toml_direct(const char* toml_path, trb_direct_desc* out) {
+    if (!toml_path || !out) return fail(TRB_ERR_INVALID, "trb_host_load_toml_direct: null argument");
+    trb::TomlConfig cfg;
+    std::string err;
+    if (!trb::load_toml(toml_path, cfg, err)) return fail(TRB_ERR_IO, err);
+    *out = cfg.direct;
+    return TRB_OK;
+}
+
 int trb_host_save_checkpoint(const char* path, const trb_checkpoint_info* info, const float* rgb) {
     if (!path || !info) return fail(TRB_ERR_INVALID, "trb_host_save_checkpoint: null argument");
     std::string err;
@@ -126,6 +135,18 @@ int trb_host_emitters(const trb_scene_desc* s, int32_t* shape_out, float* area_o
     }
     if (cdf_out) std::memcpy(cdf_out, cdf.data(), std::min(cdf.size(), cdf_capacity) * sizeof(float));
     return int(em.size());
+}
+
+int trb_host_shape_spheres(const trb_scene_desc* s, float* out4, size_t n_shapes) {
+    if (!s || !out4) return fail(TRB_ERR_INVALID, "trb_host_shape_spheres: null argument");
+    if (n_shapes < s->n_shapes) return fail(TRB_ERR_INVALID, "trb_host_shape_spheres: buffer too small");
+    for (size_t t = 0; t < s->n_tris; ++t)
+        for (int k = 0; k < 3; ++k)
+            if (s->tri_v[3 * t + k] < 0 || size_t(s->tri_v[3 * t + k]) >= s->n_positions) return fail(TRB_ERR_INVALID, "vertex index out of range");
+    std::vector<float> sph;
+    trb::shape_spheres(*s, sph);
+    std::memcpy(out4, sph.data(), sph.size() * sizeof(float));
+    return TRB_OK;
 }
 
 int trb_host_camera_matrices(const trb_render_desc* d, float* out64) {

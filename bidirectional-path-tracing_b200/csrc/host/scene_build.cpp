@@ -30,7 +30,7 @@ inline float lum(float r, float g, float b) { return (r * 0.212671f + g * 0.7151
 size_t FlatScene::bytes() const {
     return nodes.size() * sizeof(DevNode) + tris.size() * sizeof(DevTri) + shade.size() * sizeof(DevShade) +
            materials.size() * sizeof(DevMaterial) + emitters.size() * sizeof(DevEmitter) +
-           emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float);
+           emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float);
 }
 
 // BSDF constructors: diffuse.h:20-32, phong.h:25-52, mixture.h:25-52, perfectmirror.h:18-26, glass.h:20-31;
@@ -127,6 +127,24 @@ bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& ma
         }
     }
     return true;
+}
+
+void shape_spheres(const trb_scene_desc& s, std::vector<float>& out4) {
+    out4.assign(4 * s.n_shapes, 0.f);
+    size_t t = 0;
+    for (size_t sh = 0; sh < s.n_shapes; ++sh) {
+        float cx = 0.f, cy = 0.f, cz = 0.f, mx = -std::numeric_limits<float>::infinity();
+        size_t first = t;
+        for (; t < s.n_tris && size_t(s.tri_shape[t]) == sh; ++t)
+            for (int k = 0; k < 3; ++k) {
+                V3 p = vtx(s, s.tri_v[3 * t + k]);
+                cx += p.x; cy += p.y; cz += p.z;
+                mx = std::max(mx, p.x);
+            }
+        const float n = float(3 * (t - first));
+        cx /= n; cy /= n; cz /= n;
+        out4[4 * sh] = cx; out4[4 * sh + 1] = cy; out4[4 * sh + 2] = cz; out4[4 * sh + 3] = mx - cx;
+    }
 }
 
 // ---- reference-order BVH build ---------------------------------------------------------------------
@@ -303,6 +321,12 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     if (!derive_materials(s, out.materials, err)) return false;
     std::vector<int32_t> shape_to_emitter;
     if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
+    {
+        std::vector<float> sph;
+        shape_spheres(s, sph);
+        out.emitter_sphere.clear();
+        for (const DevEmitter& e : out.emitters) out.emitter_sphere.insert(out.emitter_sphere.end(), sph.begin() + 4 * e.shape, sph.begin() + 4 * e.shape + 4);
+    }
 
     RefTree tree;
     if (!build_ref_tree(s, tree, err)) return false;

@@ -195,6 +195,16 @@ bool load_toml(const std::string& path, TomlConfig& out, std::string& err) {
     out.path.rr_prob = float(get_double(ren, "rrProb", 0.95));
     out.path.emitter_samples = get_int(ren, "emitterSamples", 1);
     out.path.bsdf_samples = get_int(ren, "bsdfSamples", 0);
+    // DirectIntegrator (main.cpp:88-93); its bsdfSamples default is 1 where the path tracer's is 0, and its samplingStrategy default,
+    // "emitter", is a name DirectIntegrator::render does not know (direct.h:449-461)
+    out.direct.emitter_samples = get_int(ren, "emitterSamples", 1);
+    out.direct.bsdf_samples = get_int(ren, "bsdfSamples", 1);
+    out.direct.reserved = 0;
+    {
+        const std::string st = get_str(ren, "samplingStrategy", "emitter");
+        out.direct.strategy = st == "mis" ? TRB_DI_MIS : st == "area" ? TRB_DI_AREA : st == "solidAngle" ? TRB_DI_SOLID_ANGLE
+                            : st == "cosineHemisphere" ? TRB_DI_COSINE_HEMISPHERE : st == "bsdf" ? TRB_DI_BSDF : TRB_DI_INVALID;
+    }
     // restartable renders: file names relative to the toml's directory, like objfile
     auto resolve = [&](std::string f) {
         if (!f.empty() && f[0] != '/') { size_t slash = path.find_last_of('/'); f = (slash == std::string::npos ? std::string() : path.substr(0, slash + 1)) + f; }

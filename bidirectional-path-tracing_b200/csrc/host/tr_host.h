@@ -96,6 +96,7 @@ struct FlatScene {
     std::vector<DevEmitter> emitters;
     std::vector<DevEmitterTri> emitter_tris;
     std::vector<float> emitter_cdf;
+    std::vector<float> emitter_sphere;  // per emitter: Scene::getShapeCenter xyz, getShapeRadius (renderer.cpp:349-358) - DirectIntegrator's sphere lights
     std::vector<int32_t> order;  // order[pos] = global tri id
     int32_t root_ref = 0;        // root as a child reference (leaf when the scene has <= 4 triangles)
     int32_t max_depth = 0;       // tree depth (traversal stack bound)
@@ -115,6 +116,9 @@ bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, st
 bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& mats, std::vector<DevEmitter>& em,
                      std::vector<DevEmitterTri>& tris, std::vector<float>& cdf, std::vector<int32_t>& shape_to_emitter,
                      std::string& err);
+// Scene::load's tail (renderer.cpp:294-304): per shape the mean of the vertices its indices name (running fp32 sum in index
+// order) and radius = AABB max.x - centre.x; out4 = n_shapes x (cx, cy, cz, r)
+void shape_spheres(const trb_scene_desc& s, std::vector<float>& out4);
 bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err);
 
 // ---- camera (glm-order arithmetic; renderer.cpp:143-153, bdpt.h:49-55,485-496) --------------------
@@ -136,6 +140,7 @@ void make_camera(const trb_render_desc& d, CameraDev& out);
 struct TomlConfig {
     trb_render_desc desc;
     trb_path_desc path;  // [renderer] keys of type = "path" (main.cpp:94-102)
+    trb_direct_desc direct;  // [renderer] keys of type = "direct" (main.cpp:88-93)
     std::string obj_path, type;
     bool realtime = false;
     int gpus = 1;

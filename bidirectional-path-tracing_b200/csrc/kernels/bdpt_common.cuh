@@ -15,6 +15,7 @@ struct SceneDev {
     const trb::DevEmitter* emitters;
     const trb::DevEmitterTri* etris;
     const float* cdf;
+    const float4* esphere;  // per emitter: shape centre xyz, radius (renderer.cpp:349-358; DirectIntegrator only)
     int32_t root_ref;
     int32_t n_emitters;
 };

@@ -13,6 +13,7 @@
 #include "host/tr_host.h"
 #include "kernels/bdpt_kernels.cuh"
 #include "kernels/pt_kernels.cuh"
+#include "kernels/di_kernels.cuh"
 #include "kernels/trace_warp.cuh"
 #include "kernels/trace_coop.cuh"
 #include "kernels/trace_sort.cuh"
@@ -62,6 +63,7 @@ struct trb_context {
     DevBuf<trb::DevEmitter> d_emitters;
     DevBuf<trb::DevEmitterTri> d_etris;
     DevBuf<float> d_cdf;
+    DevBuf<float4> d_esphere;
     SceneDev sc{};
     uint8_t* pinned = nullptr;  // flattened scene staged in pinned host memory (trb_scene_refresh)
     size_t pinned_bytes = 0;
@@ -260,7 +262,7 @@ void trb_destroy(trb_context* c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
-    c->d_etris.release(); c->d_cdf.release();
+    c->d_etris.release(); c->d_cdf.release(); c->d_esphere.release(); c->pt_ctr.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->sray2.release(); c->spend2.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->q_conn.release(); c->ev.release(); c->spend.release();
     c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
@@ -296,12 +298,14 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     TRB_CUDA(c, c->d_nodes.alloc(f.nodes.size())); TRB_CUDA(c, c->d_tris.alloc(f.tris.size()));
     TRB_CUDA(c, c->d_shade.alloc(f.shade.size())); TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
     TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
-    TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size()));
+    TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size())); TRB_CUDA(c, c->d_esphere.alloc(f.emitter_sphere.size() / 4));
     // stage everything in one pinned blob so that (re-)uploads are plain async copies from pinned memory
-    const size_t sizes[7] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+    const size_t sizes[8] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
                              f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
-                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float)};
-    const void* srcs[7] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data()};
+                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
+                             f.emitter_sphere.size() * sizeof(float)};
+    const void* srcs[8] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data(),
+                           f.emitter_sphere.data()};
     size_t total = 0;
     for (size_t b : sizes) total += (b + 255) & ~size_t(255);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
@@ -310,7 +314,7 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     size_t off = 0;
     {   // the staging copy (1.8 GB for 10 M triangles) on a few host threads
         std::vector<std::thread> th;
-        for (int k = 0; k < 7; ++k) {
+        for (int k = 0; k < 8; ++k) {
             const size_t piece = size_t(64) << 20;
             for (size_t o = 0; o < sizes[k]; o += piece) {
                 uint8_t* dst = c->pinned + off + o; const char* src = static_cast<const char*>(srcs[k]) + o; const size_t len = std::min(piece, sizes[k] - o);
@@ -324,7 +328,7 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
     c->sc.tris = reinterpret_cast<const F4*>(c->d_tris.p);
     c->sc.shade = c->d_shade.p; c->sc.mats = c->d_mats.p; c->sc.emitters = c->d_emitters.p; c->sc.etris = c->d_etris.p;
-    c->sc.cdf = c->d_cdf.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
+    c->sc.cdf = c->d_cdf.p; c->sc.esphere = c->d_esphere.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
     c->has_scene = true;
     return trb_scene_refresh(c);
 }
@@ -333,13 +337,14 @@ int trb_scene_refresh(trb_context* c) {
     if (!c) return TRB_ERR_INVALID;
     if (!c->has_scene || !c->pinned) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     cudaSetDevice(c->device);
-    void* dsts[7] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p};
+    void* dsts[8] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p};
     const trb::FlatScene& f = c->flat;
-    const size_t sizes[7] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+    const size_t sizes[8] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
                              f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
-                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float)};
+                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
+                             f.emitter_sphere.size() * sizeof(float)};
     size_t off = 0;
-    for (int k = 0; k < 7; ++k) {
+    for (int k = 0; k < 8; ++k) {
         if (sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], c->pinned + off, sizes[k], cudaMemcpyHostToDevice, c->stream));
         off += (sizes[k] + 255) & ~size_t(255);
     }
@@ -680,6 +685,93 @@ int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_de
     return TRB_OK;
 }
 
+// ---- DirectIntegrator on the same wave buffers (kernels/di_kernels.cuh; direct.h:74-467) ----------------------------------
+int check_direct_desc(trb_context* c, const trb_render_desc* d, const trb_direct_desc* dd, DiParams* out) {
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    if (!d || d->width <= 0 || d->height <= 0 || d->spp <= 0) return c->fail(TRB_ERR_INVALID, "bad render description");
+    if (!dd) return c->fail(TRB_ERR_INVALID, "no direct-integrator description");
+    if (dd->strategy < TRB_DI_MIS || dd->strategy > TRB_DI_BSDF) return c->fail(TRB_ERR_INVALID, "Error: wrong strategy");  // direct.h:460
+    if (dd->emitter_samples < 0 || dd->emitter_samples > 64 || dd->bsdf_samples < 0 || dd->bsdf_samples > 64)
+        return c->fail(TRB_ERR_INVALID, "emitter_samples / bsdf_samples must lie in [0, 64]");
+    const bool emitter_loop = dd->strategy == TRB_DI_AREA || dd->strategy == TRB_DI_SOLID_ANGLE || dd->strategy == TRB_DI_COSINE_HEMISPHERE;
+    if ((emitter_loop && dd->emitter_samples == 0) || (dd->strategy == TRB_DI_BSDF && dd->bsdf_samples == 0))
+        return c->fail(TRB_ERR_INVALID, "this strategy divides by its sample count (direct.h:192,229,263,332): it must be >= 1");
+    out->strategy = dd->strategy; out->emitter_samples = dd->emitter_samples; out->bsdf_samples = dd->bsdf_samples;
+    return TRB_OK;
+}
+
+int run_di_wave(trb_context* c, const WaveRun& w, const DiParams& dp, const trb::CameraDev& cam, int64_t wave_base, int P, int spp_begin, int spp_count) {
+    const trb_render_desc& d = *w.desc;
+    WaveParams p;
+    std::memset(&p, 0, sizeof(p));
+    p.sc = c->sc; p.cam = cam;
+    p.P = P; p.K = 1; p.rr_depth = d.rr_depth; p.max_depth = 1; p.spp = d.spp; p.spp_begin = spp_begin; p.spp_count = spp_count;
+    p.wave_base = wave_base; p.seed = d.seed; p.flags = d.flags;
+    p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
+    p.accum = w.d_accum;
+    p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p;
+    const int M = dp.strategy == DI_BSDF ? 0 : dp.emitter_samples;
+    const int NB = (dp.strategy == DI_MIS || dp.strategy == DI_BSDF) ? dp.bsdf_samples : 0;
+    // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then one fetch cursor per traversal launch
+    const size_t n_ray = size_t(M + NB) + 8, n_fetch = n_ray + 8;
+    TRB_CUDA(c, c->pt_ctr.alloc(n_ray + n_fetch));
+    TRB_CUDA(c, cudaMemsetAsync(c->pt_ctr.p, 0, (n_ray + n_fetch) * sizeof(uint32_t), c->stream));
+    size_t i_ray = 0, i_fetch = n_ray;
+    unsigned long long* visit = nullptr;
+#ifdef TRB_COUNTERS
+    visit = c->d_stats.p + 2;
+#endif
+    const int gP = grid_exact(size_t(P));
+    k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, c->pt_ctr.p + i_fetch++, visit); c->mark(LK_CLOSEST);
+    k_di_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
+    for (int phase = 0; phase < 2; ++phase)
+        for (int i = 0; i < (phase == 0 ? M : NB); ++i) {
+            uint32_t* n_try = c->pt_ctr.p + i_ray++;
+            k_di_gen<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp, phase, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+            launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, c->pt_ctr.p + i_fetch++, visit); c->mark(LK_CLOSEST);
+            k_di_resolve<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp, phase, c->q_conn.p, n_try); c->mark(LK_LOGIC);
+        }
+    k_di_combine<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp); c->mark(LK_LOGIC);
+    k_pt_fold_stats<<<1, 256, 0, c->stream>>>(c->pt_ctr.p, uint32_t(i_ray), uint32_t(P), c->d_stats.p); c->mark(LK_LOGIC);
+    TRB_CUDA(c, cudaGetLastError());
+    return TRB_OK;
+}
+
+int render_direct_impl(trb_context* c, const trb_render_desc* d, const trb_direct_desc* dd, int accumulate, float* d_rgb, trb_stats* stats) {
+    DiParams dp;
+    int rc = check_direct_desc(c, d, dd, &dp);
+    if (rc) return rc;
+    cudaSetDevice(c->device);
+    const int64_t npix = int64_t(d->width) * d->height;
+    const int spp_begin = d->spp_begin;
+    const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
+    if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
+    const int spp_count = spp_end - spp_begin;
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 22);
+    const int64_t total = npix * spp_count;
+    P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
+    if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");
+    rc = ensure_wave(c, size_t(P), 1, /*shadow=*/false);
+    if (rc) return rc;
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    c->mark(LK_LOGIC);
+    if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
+    WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
+    for (int64_t base = 0; base < total; base += P) {
+        int n = int(std::min<int64_t>(P, total - base));
+        rc = run_di_wave(c, w, dp, cam, base, n, spp_begin, spp_count);
+        if (rc) return rc;
+    }
+    c->mark(LK_LOGIC);
+    if (stats) collect_stats(c, stats, uint64_t(total));
+    return TRB_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -692,6 +784,67 @@ int trb_framebuffer_upload(trb_context* c, const float* rgb, int width, int heig
     TRB_CUDA(c, cudaMemcpyAsync(c->fb.p, rgb, nf * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaStreamSynchronize(c->stream));
     return TRB_OK;
+}
+
+int trb_render_direct_device(trb_context* c, const trb_render_desc* d, const trb_direct_desc* dd, int accumulate, float* d_rgb, trb_stats* stats) {
+    if (!c || !d_rgb) return TRB_ERR_INVALID;
+    int rc = render_direct_impl(c, d, dd, accumulate, d_rgb, stats);
+    if (rc) return rc;
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_render_direct(trb_context* c, const trb_render_desc* d, const trb_direct_desc* dd, int accumulate, float* rgb_out, trb_stats* stats) {
+    if (!c || !d) return TRB_ERR_INVALID;
+    if (d->width <= 0 || d->height <= 0) return c->fail(TRB_ERR_INVALID, "bad film size");
+    cudaSetDevice(c->device);
+    size_t nf = size_t(d->width) * d->height * 3;
+    bool fresh = c->fb.n < nf;
+    TRB_CUDA(c, c->fb.alloc(nf));
+    if (fresh && accumulate) TRB_CUDA(c, cudaMemsetAsync(c->fb.p, 0, nf * sizeof(float), c->stream));
+    int rc = render_direct_impl(c, d, dd, accumulate, c->fb.p, stats);
+    if (rc) return rc;
+    if (rgb_out) TRB_CUDA(c, cudaMemcpyAsync(rgb_out, c->fb.p, nf * sizeof(float), cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+/* DirectIntegrator::render on n given camera rays with injected random numbers (n x stride, consumed in the reference's order).
+ * li_out: n x 3; draws_out (optional): numbers consumed per sample. */
+int trb_direct_paths(trb_context* c, const trb_render_desc* d, const trb_direct_desc* dd, const trb_ray* cam_rays, const float* rng, size_t n,
+                     size_t stride, float* li_out, int32_t* draws_out) {
+    if (!c || !cam_rays || !rng || !li_out) return TRB_ERR_INVALID;
+    DiParams dp;
+    int rc = check_direct_desc(c, d, dd, &dp);
+    if (rc) return rc;
+    if (n == 0) return TRB_OK;
+    if (n > (size_t(1) << 24)) return c->fail(TRB_ERR_INVALID, "trb_direct_paths: at most 2^24 samples per call");
+    if (stride < 1) return c->fail(TRB_ERR_INVALID, "trb_direct_paths: rng stride must be >= 1");
+    cudaSetDevice(c->device);
+    rc = ensure_wave(c, n, 1, /*shadow=*/false);
+    if (rc) return rc;
+    DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_draws;
+    TRB_CUDA(c, d_rays.alloc(n)); TRB_CUDA(c, d_rng.alloc(n * stride)); TRB_CUDA(c, d_acc.alloc(n * 3)); TRB_CUDA(c, d_draws.alloc(n));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rays.p, cam_rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    trb::CameraDev cam;
+    trb::make_camera(*d, cam);
+    c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
+    WaveRun w{d, d_acc.p, nullptr, d_rays.p, d_rng.p, int(stride), true};
+    rc = run_di_wave(c, w, dp, cam, 0, int(n), 0, d->spp);
+    if (rc == TRB_OK) {
+        k_read_draws<<<grid_exact(n), TRB_BLOCK, 0, c->stream>>>(c->st_v.p, int(n), d_draws.p);
+        std::vector<int32_t> draws(n);
+        cudaError_t e = cudaMemcpyAsync(li_out, d_acc.p, d_acc.bytes(), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(draws.data(), d_draws.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) rc = c->cuda_fail(e, "trb_direct_paths download");
+        else if (draws_out) std::copy(draws.begin(), draws.end(), draws_out);
+    }
+    d_rays.release(); d_rng.release(); d_acc.release(); d_draws.release();
+    return rc;
 }
 
 int trb_render_path_device(trb_context* c, const trb_render_desc* d, const trb_path_desc* pd, int accumulate, float* d_rgb, trb_stats* stats) {
@@ -889,6 +1042,13 @@ extern "C" int trb_render_path_multi(trb_context* const* ctxs, int n, const trb_
     if (n == 1) return trb_render_path(ctxs[0], d, pd, 0, rgb_out, stats);
     return render_multi(ctxs, n, d, rgb_out, stats,
                         [pd](trb_context* c, const trb_render_desc* part, float* fb, trb_stats* st) { return render_path_impl(c, part, pd, 0, fb, st); });
+}
+
+extern "C" int trb_render_direct_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, const trb_direct_desc* dd, float* rgb_out, trb_stats* stats) {
+    if (!ctxs || n < 1 || !d || !dd || !ctxs[0]) return TRB_ERR_INVALID;
+    if (n == 1) return trb_render_direct(ctxs[0], d, dd, 0, rgb_out, stats);
+    return render_multi(ctxs, n, d, rgb_out, stats,
+                        [dd](trb_context* c, const trb_render_desc* part, float* fb, trb_stats* st) { return render_direct_impl(c, part, dd, 0, fb, st); });
 }
 
 // ---- parity entry points -------------------------------------------------------------------------------------

@@ -127,6 +127,21 @@ typedef struct trb_path_desc {
 } trb_path_desc;
 #define TRB_PT_DEFAULT_DEPTH_CAP 64
 
+/* DirectIntegrator settings (Config::integratorSettings.di, core.h; TOML keys main.cpp:88-93).  The reference exits with
+ * "Error: wrong strategy" for any other name (direct.h:460-461) - its own TOML default, "emitter", included. */
+typedef struct trb_direct_desc {
+    int32_t strategy;        /* renderer.samplingStrategy: TRB_DI_*                                                   */
+    int32_t emitter_samples; /* renderer.emitterSamples (default 1), 0..64; >= 1 unless strategy is mis or bsdf        */
+    int32_t bsdf_samples;    /* renderer.bsdfSamples (default 1), 0..64; >= 1 for strategy bsdf                        */
+    int32_t reserved;
+} trb_direct_desc;
+#define TRB_DI_MIS 0               /* "mis"              direct.h:340-447 */
+#define TRB_DI_AREA 1              /* "area"             direct.h:143-197 */
+#define TRB_DI_SOLID_ANGLE 2       /* "solidAngle"       direct.h:271-338 */
+#define TRB_DI_COSINE_HEMISPHERE 3 /* "cosineHemisphere" direct.h:200-234 */
+#define TRB_DI_BSDF 4              /* "bsdf"             direct.h:236-268 */
+#define TRB_DI_INVALID (-1)        /* any other name                      */
+
 typedef struct trb_stats {
     double ms_total;          /* device time of the whole call, CUDA events            */
     double ms_trace_closest;  /* summed over launches                                   */
@@ -173,13 +188,17 @@ int trb_host_load_toml(const char* toml_path, trb_render_desc* out, char* obj_pa
                        char* type_out, size_t type_len, int* realtime_out);
 /* the `type = "path"` keys of the same file (main.cpp:94-102: isExplicit, maxDepth, rrProb, emitterSamples, bsdfSamples) */
 int trb_host_load_toml_path(const char* toml_path, struct trb_path_desc* out);
+/* the `type = "direct"` keys of the same file (main.cpp:88-93: emitterSamples, bsdfSamples, samplingStrategy); an unknown
+ * strategy name is reported as TRB_DI_INVALID, which every render entry point refuses */
+int trb_host_load_toml_direct(const char* toml_path, struct trb_direct_desc* out);
 /* restartable renders.  A checkpoint holds the running-sum frame buffer, the number of samples per pixel in it
  * and the description of the render; trb_host_checkpoint_matches says whether a description continues it.  Resume = restore the
  * buffer (trb_framebuffer_upload), then render [spp_done, spp) with accumulate = 1.  The save is write-then-rename. */
 typedef struct trb_checkpoint_info {
     trb_render_desc desc;
-    trb_path_desc path;     /* integrator == 1 only */
-    int32_t integrator;     /* 0 = bdpt, 1 = path */
+    trb_path_desc path;     /* integrator == 1; integrator == 2 keeps its trb_direct_desc here: is_explicit = strategy,
+                               emitter_samples, bsdf_samples as named, the rest 0 */
+    int32_t integrator;     /* 0 = bdpt, 1 = path, 2 = direct */
     int32_t spp_done;
     uint64_t scene_hash;    /* caller's fingerprint of the scene (0 = unchecked) */
 } trb_checkpoint_info;
@@ -200,6 +219,9 @@ int trb_host_bvh_order(const trb_scene_desc*, int32_t* order_out, size_t n);
  * radiance(3); cdf_out receives the concatenated normalised face-area CDFs (n_faces+1 each) if non-null */
 int trb_host_emitters(const trb_scene_desc*, int32_t* shape_out, float* area_out, float* radiance_out,
                       size_t max_emitters, float* cdf_out, size_t cdf_capacity);
+/* Scene::getShapeCenter / getShapeRadius (renderer.cpp:294-304, 349-358) per shape: out4 = n_shapes x (cx, cy, cz, radius);
+ * DirectIntegrator treats every emitter as the sphere so described */
+int trb_host_shape_spheres(const trb_scene_desc*, float* out4, size_t n_shapes);
 /* camera matrices as glm builds them (renderer.cpp:143-153, bdpt.h:485-490): 4 column-major mat4:
  * worldToCamera, cameraToWorld, cameraToClip, NDCToScreen */
 int trb_host_camera_matrices(const trb_render_desc*, float* out64);
@@ -246,6 +268,17 @@ int trb_render_path_device(trb_context*, const trb_render_desc*, const trb_path_
  * 0.99 past the end of its row (which ends every roulette); draws_out then exceeds stride. */
 int trb_path_paths(trb_context*, const trb_render_desc*, const trb_path_desc*, const trb_ray* cam_rays, const float* rng, size_t n,
                    size_t stride, float* li_out, int32_t* draws_out);
+
+/* The reference's DirectIntegrator (src/integrators/direct.h:74-467, `type = "direct"`): one-bounce direct
+ * illumination, five sampling strategies, every emitter treated as the sphere (shape centre, AABB max.x - centre.x).  Same
+ * conventions as trb_render_bdpt; rr_depth is not read. */
+int trb_render_direct(trb_context*, const trb_render_desc*, const trb_direct_desc*, int accumulate, float* rgb_out, trb_stats* out);
+int trb_render_direct_device(trb_context*, const trb_render_desc*, const trb_direct_desc*, int accumulate, float* d_rgb, trb_stats* out);
+int trb_render_direct_multi(trb_context* const* ctxs, int n, const trb_render_desc*, const trb_direct_desc*, float* rgb_out, trb_stats* stats);
+/* DirectIntegrator::render on n given camera rays with injected random numbers (n x stride floats, consumed in the
+ * reference's order: the emitter loop's (1 +) 2 numbers per sample, then the BSDF loop's 2); li_out n x 3; draws_out optional. */
+int trb_direct_paths(trb_context*, const trb_render_desc*, const trb_direct_desc*, const trb_ray* cam_rays, const float* rng, size_t n,
+                     size_t stride, float* li_out, int32_t* draws_out);
 
 /* Parity entry points (north_star levels 1 and 2). Host buffers in, host buffers out. */
 int trb_trace_closest(trb_context*, const trb_ray* rays, size_t n, trb_hit* out);   /* accel.h:125-172 */
