@@ -60,6 +60,10 @@ bool loadTOML(Config& config, const std::string& inputFile) {
     auto& pt = config.integratorSettings.pt;
     pt.isExplicit = t.path.is_explicit != 0; pt.maxDepth = t.path.max_depth; pt.rrDepth = t.desc.rr_depth; pt.rrProb = t.path.rr_prob;
     pt.emitterSamples = size_t(std::max(t.path.emitter_samples, 0)); pt.bsdfSamples = size_t(std::max(t.path.bsdf_samples, 0));
+    auto& di = config.integratorSettings.di;  // main.cpp:88-93
+    di.emitterSamples = size_t(std::max(t.direct.emitter_samples, 0)); di.bsdfSamples = size_t(std::max(t.direct.bsdf_samples, 0));
+    static const char* strategies[] = {"mis", "area", "solidAngle", "cosineHemisphere", "bsdf"};
+    di.samplingStrategy = (t.direct.strategy >= 0 && t.direct.strategy <= 4) ? strategies[t.direct.strategy] : "emitter";
     return t.realtime;
 }
 
@@ -399,6 +403,68 @@ void PathTracerIntegrator::describe(trb_checkpoint_info& info) const {
     info.integrator = 1;
 }
 
+// ---- DirectIntegrator (direct.h:74-467) -------------------------------------------------------------------------
+DirectIntegrator::DirectIntegrator(const Scene& s) : Integrator(s) {
+    const auto& di = s.config.integratorSettings.di;  // direct.h:75-79
+    m_emitterSamples = di.emitterSamples; m_bsdfSamples = di.bsdfSamples; m_samplingStrategy = di.samplingStrategy;
+}
+
+trb_direct_desc DirectIntegrator::directDesc() const {
+    trb_direct_desc d;
+    d.strategy = m_samplingStrategy == "mis" ? TRB_DI_MIS : m_samplingStrategy == "area" ? TRB_DI_AREA
+               : m_samplingStrategy == "solidAngle" ? TRB_DI_SOLID_ANGLE : m_samplingStrategy == "cosineHemisphere" ? TRB_DI_COSINE_HEMISPHERE
+               : m_samplingStrategy == "bsdf" ? TRB_DI_BSDF : TRB_DI_INVALID;
+    d.emitter_samples = int32_t(m_emitterSamples); d.bsdf_samples = int32_t(m_bsdfSamples); d.reserved = 0;
+    return d;
+}
+
+v3f DirectIntegrator::render(const Ray& ray, Sampler& sampler) const {
+    trb_context* c = scene.context(0);
+    if (!c) throw std::runtime_error("DirectIntegrator::render: no device context");
+    const trb_render_desc d = make_desc(scene.config);
+    const trb_direct_desc dd = directDesc();
+    if (dd.strategy == TRB_DI_INVALID) throw std::runtime_error("Error: wrong strategy");  // direct.h:460
+    // the sample consumes a prefix of the sampler's stream: feed a copy's numbers, then advance the real sampler
+    const size_t stride = 3 * m_emitterSamples + 2 * m_bsdfSamples + 4;
+    Sampler ahead = sampler;
+    std::vector<float> rng(stride);
+    for (float& f : rng) f = ahead.next();
+    trb_ray r = to_ray(ray);
+    float li[3] = {0, 0, 0};
+    int32_t draws = 0;
+    if (trb_direct_paths(c, &d, &dd, &r, rng.data(), 1, stride, li, &draws) != TRB_OK)
+        throw std::runtime_error(std::string("DirectIntegrator::render: ") + trb_last_error(c));
+    for (int k = 0; k < draws; ++k) sampler.next();
+    return v3f(li[0], li[1], li[2]);
+}
+
+bool DirectIntegrator::renderFrame() {
+    const trb_direct_desc dd = directDesc();
+    if (dd.strategy == TRB_DI_INVALID) { std::cout << "Error: wrong strategy" << std::endl; return false; }  // direct.h:460 (the reference then exits)
+    return render_frame_sharded(scene, make_desc(scene.config), *rgb, &lastStats,
+                                [dd](trb_context* c, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_direct(c, &d, &dd, 0, out, st); },
+                                [dd](trb_context* const* cs, int n, const trb_render_desc& d, float* out, trb_stats* st) { return trb_render_direct_multi(cs, n, &d, &dd, out, st); });
+}
+
+bool DirectIntegrator::renderRange(int sppBegin, int sppEnd, bool accumulate) {
+    trb_context* c = scene.context(0);
+    if (!c) { std::printf("%s\n", scene.error().c_str()); return false; }
+    trb_render_desc d = make_desc(scene.config);
+    d.spp_begin = sppBegin; d.spp_end = sppEnd;
+    const trb_direct_desc dd = directDesc();
+    if (dd.strategy == TRB_DI_INVALID) { std::cout << "Error: wrong strategy" << std::endl; return false; }
+    if (trb_render_direct(c, &d, &dd, accumulate ? 1 : 0, reinterpret_cast<float*>(rgb->data.get()), &lastStats) != TRB_OK) { std::printf("%s\n", trb_last_error(c)); return false; }
+    return true;
+}
+
+void DirectIntegrator::describe(trb_checkpoint_info& info) const {
+    std::memset(&info, 0, sizeof(info));
+    info.desc = make_desc(scene.config);
+    const trb_direct_desc dd = directDesc();
+    info.path.is_explicit = dd.strategy; info.path.emitter_samples = dd.emitter_samples; info.path.bsdf_samples = dd.bsdf_samples;  // trb.h: integrator 2
+    info.integrator = 2;
+}
+
 // ---- Renderer (renderer.cpp:53-227) ---------------------------------------------------------------------------
 Renderer::Renderer(const Config& config) : scene(config) {}
 
@@ -407,8 +473,9 @@ bool Renderer::init(bool isRealTime, bool nogui_) {
     if (!scene.load(isRealTime)) return false;
     if (scene.config.integrator == EBDPTIntegrator) integrator.reset(new BDPTIntegrator(scene));
     else if (scene.config.integrator == EPathTracerIntegrator) integrator.reset(new PathTracerIntegrator(scene));
+    else if (scene.config.integrator == EDirectIntegrator) integrator.reset(new DirectIntegrator(scene));
     else {
-        std::printf("Only the BDPT and path integrators are hosted on the B200 path (renderer.type = \"bdpt\" | \"path\")\n");
+        std::printf("Only the BDPT, path and direct integrators are hosted on the B200 path (renderer.type = \"bdpt\" | \"path\" | \"direct\")\n");
         return false;
     }
     return integrator->init();

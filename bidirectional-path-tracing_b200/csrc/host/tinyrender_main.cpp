@@ -27,12 +27,14 @@ static void run(const std::string& file, bool nogui) {
     renderer.render();
     double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     std::printf("Render took: %f seconds.\n", sec);
-    auto* b = dynamic_cast<TinyRender::BDPTIntegrator*>(renderer.integrator.get());
-    if (b && b->lastStats.samples)
-        std::printf("device: %.3f ms, %.2f Msamples/s, %.1f rays/sample, %llu launches\n", b->lastStats.ms_total,
-                    double(b->lastStats.samples) / (b->lastStats.ms_total * 1e3),
-                    double(b->lastStats.rays_closest + b->lastStats.rays_any) / double(b->lastStats.samples),
-                    (unsigned long long)b->lastStats.launches);
+    const trb_stats* st = nullptr;
+    if (auto* b = dynamic_cast<TinyRender::BDPTIntegrator*>(renderer.integrator.get())) st = &b->lastStats;
+    else if (auto* pt = dynamic_cast<TinyRender::PathTracerIntegrator*>(renderer.integrator.get())) st = &pt->lastStats;
+    else if (auto* di = dynamic_cast<TinyRender::DirectIntegrator*>(renderer.integrator.get())) st = &di->lastStats;
+    if (st && st->samples)
+        std::printf("device: %.3f ms, %.2f Msamples/s, %.1f rays/sample, %llu launches\n", st->ms_total,
+                    double(st->samples) / (st->ms_total * 1e3), double(st->rays_closest + st->rays_any) / double(st->samples),
+                    (unsigned long long)st->launches);
     renderer.cleanUp();
 }
 

@@ -12,6 +12,8 @@
 //   AcceleratorBVH               src/core/accel.h:113-172
 //   Scene                        src/core/core.h:352-374, src/core/renderer.cpp:235-315
 //   Integrator, BDPTIntegrator   src/core/integrator.h:23-70, src/integrators/bdpt.h:37-518
+//   PathTracerIntegrator         src/integrators/path.h:15-262
+//   DirectIntegrator             src/integrators/direct.h:74-467
 //   Renderer                     src/core/renderer.h:20-33, src/core/renderer.cpp:53-227
 // Two additive changes: Integrator gains `virtual bool renderFrame()` (the whole offline pixel loop of
 // Renderer::render as ONE call; BDPTIntegrator implements it with trb_render_bdpt) and the single-item virtuals
@@ -61,6 +63,9 @@ struct Config {  // core.h:195-248 (the fields the offline BDPT path reads) + op
             bool isExplicit = true; int maxDepth = -1; int rrDepth = 5; float rrProb = 0.95f;
             size_t emitterSamples = 1, bsdfSamples = 0;
         } pt;
+        struct di_s {  // main.cpp:88-93: the reference's own default strategy name, "emitter", is one DirectIntegrator::render rejects
+            size_t emitterSamples = 1, bsdfSamples = 1; std::string samplingStrategy = "emitter";
+        } di;
     } integratorSettings;
     // additive [renderer] keys (defaults reproduce the reference run)
     int gpus = 1;                 // devices used by Renderer::render, sharded by sample index
@@ -214,6 +219,20 @@ struct PathTracerIntegrator : Integrator {  // path.h:15-262, the estimator the 
     bool renderRange(int sppBegin, int sppEnd, bool accumulate) override;
     void describe(trb_checkpoint_info& info) const override;
     trb_path_desc pathDesc() const;
+};
+
+struct DirectIntegrator : Integrator {  // direct.h:74-467: one-bounce direct illumination, five sampling strategies
+    size_t m_emitterSamples, m_bsdfSamples;
+    std::string m_samplingStrategy;  // "mis" | "area" | "solidAngle" | "cosineHemisphere" | "bsdf"
+    mutable trb_stats lastStats{};
+    explicit DirectIntegrator(const Scene& s);
+    // One sample on the device with the sampler's own number stream, consumed in the reference's order.  An unknown strategy
+    // throws std::runtime_error("Error: wrong strategy") where the reference prints that and exits (direct.h:460-461).
+    v3f render(const Ray& ray, Sampler& sampler) const override;
+    bool renderFrame() override;
+    bool renderRange(int sppBegin, int sppEnd, bool accumulate) override;
+    void describe(trb_checkpoint_info& info) const override;
+    trb_direct_desc directDesc() const;
 };
 
 struct Renderer {  // renderer.h:20-33

@@ -117,3 +117,59 @@ def test_direct_strategies_agree_on_sphere_lights(trb, gpu_ctx):
     print(means)
     for s in ("solidAngle", "bsdf", "cosineHemisphere", "area"):
         assert abs(means[s] / means["mis"] - 1) < 0.03, means
+
+
+def test_cli_and_cpp_api_direct(trb, gpu_ctx, gold, tmp_path):
+    """`type = "direct"` through the reference's host surface: the CLI writes the frame trb_render_direct gives, a checkpointed run
+    resumes, an unknown strategy fails as the reference does, and DirectIntegrator::render(ray, sampler) with Sampler(seed) per
+    sample returns the unmodified reference's Li (tests/golden/dipaths_spherelight_mis.npz)."""
+    import os
+    import subprocess
+    import sys
+    cv2 = pytest.importorskip("cv2")
+    root = Path(__file__).resolve().parent.parent
+    pkg = root / "bidirectional-path-tracing_b200"
+    sys.path.insert(0, str(pkg)); sys.path.insert(0, str(root / "tools"))
+    import build as trb_build
+    import scene_to_obj
+    g = gold("dipaths", "spherelight_mis")
+    w, h, spp = int(g["width"]), int(g["height"]), int(g["spp"])
+    scene_to_obj.export_verified(trb.HostScene.load_npz(GOLD / "scene_spherelight.npz"), tmp_path / "scene.obj")
+    toml = tmp_path / "scene.toml"
+
+    def write(strategy, extra=""):
+        toml.write_text('[input]\nobjfile = "scene.obj"\n\n[camera]\neye = [ 0.0, 0.8, 3.8 ]\nat = [ 0.0, 0.8, 0.0 ]\nup = [ 0.0, 1.0, 0.0 ]\nfov = 30.0\n\n'
+                        f'[film]\nwidth = {w}\nheight = {h}\n\n[renderer]\nrealtime = false\ntype = "direct"\nspp = {spp}\n'
+                        f'emitterSamples = 2\nbsdfSamples = 2\nsamplingStrategy = "{strategy}"\n{extra}')
+    write("mis", 'checkpoint = "run.ckpt"\ncheckpointEvery = 3\n')
+    exe = [str(pkg / "tinyrender_b200"), str(toml), "nogui"]
+    r1 = subprocess.run(exe, capture_output=True, text=True, timeout=300, env=dict(os.environ, TRB_STOP_AFTER_CHECKPOINTS="1"))
+    assert r1.returncode == 0 and "Checkpoint: 3 of 4" in r1.stdout, r1.stdout + r1.stderr
+    info, _ = trb.load_checkpoint(tmp_path / "run.ckpt")
+    assert info.integrator == 2 and info.spp_done == 3 and (info.path.is_explicit, info.path.emitter_samples, info.path.bsdf_samples) == (0, 2, 2)
+    r2 = subprocess.run(exe, capture_output=True, text=True, timeout=300)
+    assert r2.returncode == 0 and "Resuming from" in r2.stdout and "Saved EXR" in r2.stdout, r2.stdout + r2.stderr
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    bgr = cv2.imread(str(tmp_path / "scene.exr"), cv2.IMREAD_UNCHANGED)
+    img, _ = gpu_ctx("spherelight").render_direct(trb.render_desc(width=w, height=h, spp=spp), trb.direct_desc("mis", 2, 2))
+    assert bgr is not None and np.allclose(bgr[:, :, ::-1], img, rtol=2e-3, atol=1e-4)
+    # per-sample virtual with the reference's Sampler
+    api = tmp_path / "api_check"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", str(root / "include"), str(root / "tests/cpp/api_check.cpp"), "-o", str(api),
+                    "-L", str(pkg), "-l:libtrb.so", f"-Wl,-rpath,{pkg}", *trb_build._stdcxx_link_args(), "-lm"], check=True)
+    write("mis")
+    n = 300
+    rec = np.zeros(n, np.dtype([("ray", "<f4", 8), ("seed", "<i4")]))
+    rec["ray"], rec["seed"] = g["rays"][:n], g["seeds"][:n]
+    (tmp_path / "in.bin").write_bytes(np.int32(n).tobytes() + rec.tobytes())
+    r = subprocess.run([str(api), str(toml), str(tmp_path / "in.bin"), str(tmp_path / "out.bin")], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = np.fromfile(tmp_path / "out.bin", np.float32).reshape(n, 6)
+    ref = g["li"][:n]
+    scale = np.maximum(np.abs(ref).max(1, keepdims=True), 1e-6)
+    ok = (np.abs(out[:, :3] - ref) <= 1e-5 * np.maximum(scale, np.abs(out[:, :3]))).all(1)
+    assert ok.mean() >= 0.99, ok.mean()
+    # the reference's own default strategy name is one its integrator rejects ("Error: wrong strategy", direct.h:460)
+    write("emitter")
+    bad = subprocess.run(exe, capture_output=True, text=True, timeout=300)
+    assert "wrong strategy" in bad.stdout + bad.stderr

@@ -56,6 +56,16 @@ def test_load_toml_keys_defaults_and_errors(trb, tmp_path):
     pd = trb.load_toml_path(p)
     assert (typ, d.rr_depth, d.spp) == ("path", 7, 512)
     assert (pd.is_explicit, pd.max_depth, pd.emitter_samples, pd.bsdf_samples) == (0, 4, 2, 3) and abs(pd.rr_prob - 0.8) < 1e-7
+    # type = "direct" (main.cpp:88-93): bsdfSamples defaults to 1 here (0 for "path"); the default strategy name, "emitter", is
+    # one DirectIntegrator::render rejects (direct.h:449-461)
+    dd = trb.load_toml_direct(p)
+    assert (dd.strategy, dd.emitter_samples, dd.bsdf_samples) == (-1, 2, 3)
+    p.write_text('[input]\nobjfile = "a.obj"\n[camera]\n[film]\n[renderer]\ntype = "direct"\nsamplingStrategy = "solidAngle"\nspp = 4\n')
+    dd = trb.load_toml_direct(p)
+    assert (trb.load_toml(p)[2], dd.strategy, dd.emitter_samples, dd.bsdf_samples) == ("direct", trb.DI_STRATEGIES["solidAngle"], 1, 1)
+    for name, code in trb.DI_STRATEGIES.items():
+        p.write_text(f'[input]\nobjfile = "a.obj"\n[camera]\n[film]\n[renderer]\ntype = "direct"\nsamplingStrategy = "{name}"\n')
+        assert trb.load_toml_direct(p).strategy == code == trb.direct_desc(name).strategy
     p.write_text('[input]\nobjfile = "a.obj"\n[camera]\n[film]\n')
     with pytest.raises(trb.TrbError):
         trb.load_toml(p)
@@ -236,3 +246,29 @@ def test_cpp_host_api_compiles_and_fails_loudly_without_gpu(trb, tmp_path):
         toml.write_text(body % "bdpt")
         r = subprocess.run([str(cli), str(toml), "nogui"], capture_output=True, text=True)
         assert r.returncode != 0  # missing OBJ / no device: never a silent CPU render
+
+
+@pytest.mark.parametrize("name", ["spherelight", "caustic", "tess"])
+def test_shape_spheres_match_reference(trb, name):
+    """Scene::getShapeCenter / getShapeRadius (renderer.cpp:294-304, 349-358) as the host builder derives them for the device
+    (DirectIntegrator's sphere emitters) against the reference's own values (tools/gen_golden_direct.py), bit for bit"""
+    from conftest import GOLD
+    g = np.load(GOLD / f"dipaths_{name}_mis.npz")
+    hs = trb.HostScene.load_npz(GOLD / f"scene_{name}.npz")
+    assert np.array_equal(hs.shape_spheres().view(np.uint32), g["spheres"].view(np.uint32))
+
+
+def test_spherelight_scene_is_reproducible_and_pinned(trb):
+    """the sphere-light scene is generated (tools/gen_tess_scene.make_sphere_light_scene); the committed fixture is that output, and
+    the host builder's BVH order and emitters on it are the reference's"""
+    from conftest import GOLD
+    import gen_tess_scene
+    sc = gen_tess_scene.make_sphere_light_scene()
+    hs = trb.HostScene.load_npz(GOLD / "scene_spherelight.npz")
+    for k in ("positions", "normals", "tri_v", "tri_n", "tri_mat", "tri_shape"):
+        assert np.array_equal(getattr(sc, k), getattr(hs, k)), k
+    g = np.load(GOLD / "host_spherelight.npz")
+    assert np.array_equal(hs.bvh_order(), g["order"])
+    em = hs.emitters()
+    assert em["n"] == 2 and np.array_equal(em["shape"], g["em_shape"]) and np.array_equal(em["area"].view(np.uint32), g["em_area"].view(np.uint32))
+    assert np.array_equal(em["cdf"][: len(g["em_cdf"])].view(np.uint32), g["em_cdf"].view(np.uint32))
