@@ -367,9 +367,23 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     });
 
     // inner nodes only; leaves become negative child references
+    // Numbering: the first TRB_TOP_NODES_MAX inner nodes in breadth-first order come first (the traversal kernel stages a prefix
+    // of them - the top levels of the tree - in shared memory), the rest follow in the reference's pre-order (left child adjacent).
+    // Only the child references depend on the numbering; the set of boxes a ray tests and the hits do not.
     std::vector<int32_t> inner_index(tree.nodes.size(), -1);
     int32_t n_inner = 0;
-    for (size_t i = 0; i < tree.nodes.size(); ++i) if (tree.nodes[i].left >= 0) inner_index[i] = n_inner++;
+    if (!tree.nodes.empty() && tree.nodes[0].left >= 0) {
+        std::vector<int32_t> bfs;
+        bfs.push_back(0);
+        for (size_t k = 0; k < bfs.size() && bfs.size() < size_t(TRB_TOP_NODES_MAX); ++k) {
+            const RefTree::Node& nd = tree.nodes[bfs[k]];
+            for (int32_t ch : {nd.left, nd.right})
+                if (tree.nodes[ch].left >= 0 && bfs.size() < size_t(TRB_TOP_NODES_MAX)) bfs.push_back(ch);
+        }
+        for (int32_t ni : bfs) inner_index[ni] = n_inner++;
+    }
+    out.top_nodes = n_inner;
+    for (size_t i = 0; i < tree.nodes.size(); ++i) if (tree.nodes[i].left >= 0 && inner_index[i] < 0) inner_index[i] = n_inner++;
     auto make_ref = [&](int32_t ni) -> int32_t {
         const RefTree::Node& nd = tree.nodes[ni];
         if (nd.left >= 0) return inner_index[ni];

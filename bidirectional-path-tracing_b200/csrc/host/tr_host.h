@@ -88,6 +88,7 @@ struct alignas(16) DevEmitterTri {
 };
 static_assert(sizeof(DevEmitterTri) == 80, "emitter triangle must be 80 B");
 
+#define TRB_TOP_NODES_MAX 1024
 struct FlatScene {
     std::vector<DevNode> nodes;
     std::vector<DevTri> tris;
@@ -98,6 +99,7 @@ struct FlatScene {
     std::vector<float> emitter_cdf;
     std::vector<float> emitter_sphere;  // per emitter: Scene::getShapeCenter xyz, getShapeRadius (renderer.cpp:349-358) - DirectIntegrator's sphere lights
     std::vector<int32_t> order;  // order[pos] = global tri id
+    int32_t top_nodes = 0;       // nodes [0, top_nodes) are the top of the tree in breadth-first order (<= TRB_TOP_NODES_MAX)
     int32_t root_ref = 0;        // root as a child reference (leaf when the scene has <= 4 triangles)
     int32_t max_depth = 0;       // tree depth (traversal stack bound)
     float scene_min[3], scene_max[3];

@@ -12,7 +12,7 @@ namespace trbk {
 
 #define TRB_BLOCK 128
 
-__device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref}; }
+__device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref, 0}; }
 
 // (the traversal kernels live in trace_warp.cuh)
 

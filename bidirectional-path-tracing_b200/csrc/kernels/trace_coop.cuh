@@ -23,6 +23,10 @@
 #define TRB_COOP_Q 512u       // queue entries per warp (power of two); a node phase adds at most 8 x 32
 #endif
 
+#ifndef TRB_TOP
+#define TRB_TOP 0             // inner nodes (64 B each) of the top of the tree staged in shared memory per block; 0 = none
+#endif
+
 namespace trbk {
 
 struct CoopWarp {
@@ -38,6 +42,14 @@ template <bool ANY>
 __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_coop(const TraceArgs a) {
     __shared__ CoopWarp sh_all[TRB_TRACE_BLOCK / 32];
     CoopWarp& sh = sh_all[threadIdx.x >> 5];
+#if TRB_TOP > 0
+    // The top levels of the tree (host numbering: breadth-first prefix) in shared memory: a warp whose lanes sit in unrelated
+    // nodes pays one L1 wavefront per lane and load for global memory, four per load for conflict-free 16 B shared reads.
+    extern __shared__ float4 top[];   // TRB_TOP x 64 B, dynamic (may exceed the 48 KB static limit)
+    const int32_t n_top = min(a.bvh.n_top, int32_t(TRB_TOP));
+    for (int i = threadIdx.x; i < n_top * 4; i += TRB_TRACE_BLOCK) { const F4 v = ld4(a.bvh.nodes + i); top[i] = make_float4(v.x, v.y, v.z, v.w); }
+    __syncthreads();
+#endif
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
@@ -145,8 +157,18 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         }
         // ---- node phase ----
         if (cur >= 0) {
-            const F4* np = a.bvh.nodes + 4 * size_t(cur);
-            F4 na = ld4(np), nb = ld4(np + 1), nc = ld4(np + 2), nd = ld4(np + 3);
+            F4 na, nb, nc, nd;
+#if TRB_TOP > 0
+            if (cur < n_top) {
+                const float4* tp4 = top + 4 * cur;
+                const float4 t0 = tp4[0], t1 = tp4[1], t2 = tp4[2], t3 = tp4[3];
+                na = F4{t0.x, t0.y, t0.z, t0.w}; nb = F4{t1.x, t1.y, t1.z, t1.w}; nc = F4{t2.x, t2.y, t2.z, t2.w}; nd = F4{t3.x, t3.y, t3.z, t3.w};
+            } else
+#endif
+            {
+                const F4* np = a.bvh.nodes + 4 * size_t(cur);
+                na = ld4(np); nb = ld4(np + 1); nc = ld4(np + 2); nd = ld4(np + 3);
+            }
 #ifdef TRB_COUNTERS
             ++c_nodes;
 #endif

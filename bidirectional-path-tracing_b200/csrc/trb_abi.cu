@@ -133,11 +133,13 @@ inline int trace_grid(int sm_count) { return sm_count * TRB_TRACE_MINBLOCKS; }
 void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, HitT* hits,
                     uint32_t* fetch, unsigned long long* visit) {
     TraceArgs a{};
-    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref, c->flat.top_nodes};
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
 #if TRB_COOP
-    k_trace_coop<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    static const bool attr = (cudaFuncSetAttribute(k_trace_coop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64), true);
+    (void)attr;
+    k_trace_coop<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, c->stream>>>(a);
 #else
     k_trace_warp<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
 #endif
@@ -148,11 +150,13 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
                 const int32_t* q = nullptr) {
     if (!stream) stream = c->stream;
     TraceArgs a{};
-    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref, c->flat.top_nodes};
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
 #if TRB_COOP
-    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
+    static const bool attr = (cudaFuncSetAttribute(k_trace_coop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64), true);
+    (void)attr;
+    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, stream>>>(a);
 #else
     k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
 #endif
