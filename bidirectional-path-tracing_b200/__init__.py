@@ -36,7 +36,7 @@ class TrbError(RuntimeError):
 # ---- ctypes mirrors of include/trb.h -----------------------------------------------------------------
 class Material(C.Structure):
     _fields_ = [("kd", C.c_float * 3), ("ks", C.c_float * 3), ("ke", C.c_float * 3), ("tf", C.c_float * 3),
-                ("ns", C.c_float), ("ni", C.c_float), ("illum", C.c_int32), ("_pad", C.c_int32)]
+                ("ns", C.c_float), ("ni", C.c_float), ("illum", C.c_int32), ("tex", C.c_int32)]
 
 
 class SceneDesc(C.Structure):
@@ -44,7 +44,14 @@ class SceneDesc(C.Structure):
                 ("normals", C.c_void_p), ("n_normals", C.c_size_t),
                 ("tri_v", C.c_void_p), ("tri_n", C.c_void_p), ("tri_mat", C.c_void_p), ("tri_shape", C.c_void_p),
                 ("n_tris", C.c_size_t),
-                ("materials", C.c_void_p), ("n_materials", C.c_size_t), ("n_shapes", C.c_size_t)]
+                ("materials", C.c_void_p), ("n_materials", C.c_size_t), ("n_shapes", C.c_size_t),
+                ("texcoords", C.c_void_p), ("n_texcoords", C.c_size_t), ("tri_t", C.c_void_p),
+                ("textures", C.c_void_p), ("n_textures", C.c_size_t)]
+
+
+class Texture(C.Structure):
+    """trb_texture: width*height RGB floats as BitmapTexture3f holds them (gamma-expanded, row 0 = last row of the PPM)"""
+    _fields_ = [("rgb", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32)]
 
 
 class RenderDesc(C.Structure):
@@ -102,7 +109,7 @@ BSDF_QUERY_DTYPE = np.dtype([("wo", "<f4", 3), ("wi", "<f4", 3), ("u", "<f4", 2)
 BSDF_OUT_DTYPE = np.dtype([("eval", "<f4", 3), ("pdf", "<f4"), ("sample_val", "<f4", 3), ("sample_pdf", "<f4"),
                            ("sample_wi", "<f4", 3), ("type", "<u4")])
 MATERIAL_DTYPE = np.dtype([("kd", "<f4", 3), ("ks", "<f4", 3), ("ke", "<f4", 3), ("tf", "<f4", 3), ("ns", "<f4"),
-                           ("ni", "<f4"), ("illum", "<i4"), ("_pad", "<i4")])
+                           ("ni", "<f4"), ("illum", "<i4"), ("tex", "<i4")])
 assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 32 and MATERIAL_DTYPE.itemsize == C.sizeof(Material) == 64
 assert BSDF_QUERY_DTYPE.itemsize == 40 and BSDF_OUT_DTYPE.itemsize == 48
 
@@ -176,7 +183,8 @@ class HostScene:
 
     FIELDS = ("positions", "normals", "tri_v", "tri_n", "tri_mat", "tri_shape", "materials")
 
-    def __init__(self, positions, normals, tri_v, tri_n, tri_mat, tri_shape, materials, n_shapes=None, shape_names=None):
+    def __init__(self, positions, normals, tri_v, tri_n, tri_mat, tri_shape, materials, n_shapes=None, shape_names=None,
+                 texcoords=None, tri_t=None, textures=None):
         self.positions = np.ascontiguousarray(positions, np.float32).reshape(-1, 3)
         self.normals = np.ascontiguousarray(normals, np.float32).reshape(-1, 3)
         self.tri_v = np.ascontiguousarray(tri_v, np.int32).reshape(-1, 3)
@@ -186,6 +194,10 @@ class HostScene:
         self.materials = np.ascontiguousarray(materials, MATERIAL_DTYPE).reshape(-1)
         self.n_shapes = int(n_shapes if n_shapes is not None else (self.tri_shape.max() + 1 if len(self.tri_shape) else 0))
         self.shape_names = list(shape_names) if shape_names is not None else [f"shape{i}" for i in range(self.n_shapes)]
+        # bitmap textures (materials["tex"]): vt array, per-corner vt indices (-1 = none), H x W x 3 float32 images (row 0 = bottom)
+        self.texcoords = np.ascontiguousarray(texcoords if texcoords is not None else np.zeros((0, 2)), np.float32).reshape(-1, 2)
+        self.tri_t = np.ascontiguousarray(tri_t if tri_t is not None else np.full((len(self.tri_mat), 3), -1), np.int32).reshape(-1, 3)
+        self.textures = [np.ascontiguousarray(t, np.float32) for t in (textures or [])]
 
     @property
     def n_tris(self) -> int:
@@ -200,6 +212,9 @@ class HostScene:
         d.n_tris = self.n_tris
         d.materials, d.n_materials = self.materials.ctypes.data, len(self.materials)
         d.n_shapes = self.n_shapes
+        self._tex_views = (Texture * max(len(self.textures), 1))(*[Texture(t.ctypes.data, t.shape[1], t.shape[0]) for t in self.textures])
+        d.texcoords, d.n_texcoords, d.tri_t = self.texcoords.ctypes.data, len(self.texcoords), self.tri_t.ctypes.data
+        d.textures, d.n_textures = C.cast(self._tex_views, C.c_void_p).value, len(self.textures)
         return d
 
     @classmethod
@@ -221,23 +236,31 @@ class HostScene:
             for i in range(d.n_shapes):
                 _chk_host(L.trb_host_shape_name(h, C.c_size_t(i), buf, C.c_size_t(256)))
                 names.append(buf.value.decode(errors="replace"))
+            tv = C.cast(d.textures, C.POINTER(Texture))
+            textures = [arr(tv[i].rgb, tv[i].width * tv[i].height * 3, np.float32).reshape(tv[i].height, tv[i].width, 3) for i in range(d.n_textures)]
             return cls(arr(d.positions, d.n_positions * 3, np.float32), arr(d.normals, d.n_normals * 3, np.float32),
                        arr(d.tri_v, d.n_tris * 3, np.int32), arr(d.tri_n, d.n_tris * 3, np.int32),
                        arr(d.tri_mat, d.n_tris, np.int32), arr(d.tri_shape, d.n_tris, np.int32),
-                       arr(d.materials, d.n_materials, MATERIAL_DTYPE), n_shapes=d.n_shapes, shape_names=names)
+                       arr(d.materials, d.n_materials, MATERIAL_DTYPE), n_shapes=d.n_shapes, shape_names=names,
+                       texcoords=arr(d.texcoords, d.n_texcoords * 2, np.float32),
+                       tri_t=arr(d.tri_t, d.n_tris * 3, np.int32) if d.tri_t else None, textures=textures)
         finally:
             L.trb_host_scene_free(h)
 
     def save_npz(self, path) -> None:
         np.savez_compressed(path, positions=self.positions, normals=self.normals, tri_v=self.tri_v, tri_n=self.tri_n,
                             tri_mat=self.tri_mat, tri_shape=self.tri_shape, materials=self.materials.view(np.uint8),
-                            n_shapes=np.int64(self.n_shapes), shape_names=np.array(self.shape_names))
+                            n_shapes=np.int64(self.n_shapes), shape_names=np.array(self.shape_names),
+                            **({"texcoords": self.texcoords, "tri_t": self.tri_t, **{f"texture{i}": t for i, t in enumerate(self.textures)}}
+                               if self.textures else {}))
 
     @classmethod
     def load_npz(cls, path) -> "HostScene":
         z = np.load(path, allow_pickle=False)
         return cls(z["positions"], z["normals"], z["tri_v"], z["tri_n"], z["tri_mat"], z["tri_shape"],
-                   z["materials"].view(MATERIAL_DTYPE), n_shapes=int(z["n_shapes"]), shape_names=[str(s) for s in z["shape_names"]])
+                   z["materials"].view(MATERIAL_DTYPE), n_shapes=int(z["n_shapes"]), shape_names=[str(s) for s in z["shape_names"]],
+                   texcoords=z["texcoords"] if "texcoords" in z else None, tri_t=z["tri_t"] if "tri_t" in z else None,
+                   textures=[z[f"texture{i}"] for i in range(sum(k.startswith("texture") for k in z.files))])
 
     # host-side derived data (no GPU)
     def bvh_order(self) -> np.ndarray:

@@ -209,8 +209,31 @@ void default_material(trb_material& m) {
     m.illum = 0;
 }
 
+// tinyobj's texture-name parse (tiny_obj_loader.h ParseTextureNameAndOption): options start with '-', the last plain token is the name
+std::string texture_name(const char* t) {
+    std::istringstream ss{std::string(t)};
+    std::string w, name;
+    while (ss >> w) {
+        if (w[0] == '-') {  // every option of the MTL spec takes one value except -o/-s/-t (up to three) and -mm (two)
+            int take = (w == "-o" || w == "-s" || w == "-t") ? 3 : (w == "-mm" ? 2 : 1);
+            for (int k = 0; k < take; ++k) {
+                std::streampos pos = ss.tellg();
+                std::string v;
+                if (!(ss >> v)) break;
+                char* end = nullptr;
+                std::strtod(v.c_str(), &end);
+                const bool numeric = end && *end == '\0';
+                if (take > 1 && k > 0 && !numeric) { ss.clear(); ss.seekg(pos); break; }  // optional trailing values
+            }
+            continue;
+        }
+        name = w;
+    }
+    return name;
+}
+
 bool load_mtl(const std::string& path, std::vector<trb_material>& mats, std::vector<std::string>& names,
-              std::map<std::string, int>& index, std::string& err) {
+              std::map<std::string, int>& index, std::vector<std::string>& tex_files, std::string& err) {
     std::ifstream in(path);
     if (!in) { err += "cannot open material file " + path + "\n"; return false; }
     trb_material cur; default_material(cur);
@@ -241,9 +264,18 @@ bool load_mtl(const std::string& path, std::vector<trb_material>& mats, std::vec
         if (key3("Ni")) { c.p = t + 2; cur.ni = c.real(); continue; }
         if (key3("Ns")) { c.p = t + 2; cur.ns = c.real(); continue; }
         if (!std::strncmp(t, "illum", 5) && is_space(t[5])) { c.p = t + 6; cur.illum = c.integer(); continue; }
-        if (!std::strncmp(t, "map_Kd", 6) || !std::strncmp(t, "map_Ks", 6)) {
-            err += "bitmap textures (map_Kd/map_Ks) are not supported on the device path (SURVEY 8(f) N4)\n";
-            return false;
+        if ((!std::strncmp(t, "map_Kd", 6) || !std::strncmp(t, "map_Ks", 6)) && is_space(t[6])) {  // diffuse_texname / specular_texname
+            const std::string fn = texture_name(t + 7);
+            if (!fn.empty()) {
+                size_t id = 0;
+                while (id < tex_files.size() && tex_files[id] != fn) ++id;
+                if (id == tex_files.size()) tex_files.push_back(fn);
+                if (id >= 0x7fff) { err += "too many textures\n"; return false; }
+                const int32_t code = int32_t(id) + 1;
+                if (t[5] == 'd') cur.tex = (cur.tex & ~0xffff) | code;
+                else cur.tex = (cur.tex & 0xffff) | (code << 16);
+            }
+            continue;
         }
         // Ka, d, Tr, Pr, ... : parsed by the reference but never read on the BDPT path
     }
@@ -261,7 +293,40 @@ trb_scene_desc HostScene::desc() const {
     d.n_tris = tri_mat.size();
     d.materials = materials.data(); d.n_materials = materials.size();
     d.n_shapes = n_shapes;
+    texture_views.clear();
+    for (const Texture& t : textures) texture_views.push_back(trb_texture{t.rgb.data(), t.w, t.h});
+    d.texcoords = texcoords.data(); d.n_texcoords = texcoords.size() / 2;
+    d.tri_t = tri_t.empty() ? nullptr : tri_t.data();
+    d.textures = texture_views.data(); d.n_textures = texture_views.size();
     return d;
+}
+
+void load_ppm_texture(const std::string& path, HostScene::Texture& out) {
+    out.file = path;
+    auto pink = [&]() { out.w = 1; out.h = 1; out.rgb = {1.f, 0.f, 1.f}; };  // Tex::pink
+    // Tex::load always reads `<stem>.ppm` (core.h:490-496)
+    std::string ppm = path;
+    {
+        const size_t slash = ppm.find_last_of("/\\"), dot = ppm.find_last_of('.');
+        if (dot != std::string::npos && (slash == std::string::npos || dot > slash + 1)) ppm.resize(dot);
+        ppm += ".ppm";
+    }
+    FILE* f = std::fopen(ppm.c_str(), "rb");
+    if (!f) { pink(); return; }
+    int w = 0, h = 0, e = 0;
+    if (std::fscanf(f, "%*s %d %d %d%*c", &w, &h, &e) < 3 || w <= 0 || h <= 0 || e <= 0) { std::fclose(f); pink(); return; }
+    const size_t sz = size_t(w) * h * 3;
+    std::vector<uint8_t> ct(sz, 0);
+    if (std::fread(ct.data(), 1, sz, f) == 0) { std::fclose(f); pink(); return; }
+    std::fclose(f);
+    float lut[256];
+    for (int b = 0; b < 256; ++b) lut[b] = std::pow(float(b) / float(e), 2.2f);  // Tex::pf, float overload
+    out.w = w; out.h = h;
+    out.rgb.resize(sz);
+    for (size_t i = 0; i < sz; ++i) {  // Tex::fl: the vertically flipped image
+        const size_t j = i / 3, x = j % size_t(w), y = j / size_t(w);
+        out.rgb[i] = lut[ct[3 * ((size_t(h) - y - 1) * size_t(w) + x) + i % 3]];
+    }
 }
 
 bool load_obj(const std::string& obj_path, HostScene& out, std::string& err) {
@@ -273,7 +338,8 @@ bool load_obj(const std::string& obj_path, HostScene& out, std::string& err) {
         base = slash == std::string::npos ? std::string() : obj_path.substr(0, slash + 1);
     }
     out = HostScene();
-    std::vector<float> vt;
+    std::vector<float>& vt = out.texcoords;
+    std::vector<std::string> tex_files;
     std::map<std::string, int> mat_index;
     std::vector<ShapeAcc> shapes;
     ShapeAcc shape;
@@ -341,7 +407,7 @@ bool load_obj(const std::string& obj_path, HostScene& out, std::string& err) {
             while (!found && std::getline(ss, fn, ' ')) {
                 if (fn.empty()) continue;
                 std::string e2;
-                if (load_mtl(base + fn, out.materials, out.material_names, mat_index, e2)) found = true;
+                if (load_mtl(base + fn, out.materials, out.material_names, mat_index, tex_files, e2)) found = true;
                 else if (e2.find("not supported") != std::string::npos) { err = e2; return false; }
             }
             if (!found) err += "WARN: failed to load material file(s)\n";
@@ -378,12 +444,19 @@ bool load_obj(const std::string& obj_path, HostScene& out, std::string& err) {
             for (int k = 0; k < 3; ++k) {
                 out.tri_v.push_back(s.corners[3 * f + k].v);
                 out.tri_n.push_back(s.corners[3 * f + k].vn);
+                out.tri_t.push_back(s.corners[3 * f + k].vt);
             }
             out.tri_mat.push_back(s.mats[f]);
             out.tri_shape.push_back(int32_t(j));
         }
     }
     out.n_shapes = shapes.size();
+    // BitmapTexture3f (core.h:528-543): a relative texture name is resolved against the OBJ file's directory
+    for (const std::string& fn : tex_files) {
+        HostScene::Texture t;
+        load_ppm_texture((!fn.empty() && fn[0] == '/') ? fn : base + fn, t);
+        out.textures.push_back(std::move(t));
+    }
     if (out.tri_mat.empty()) { err = "no faces in " + obj_path; return false; }
     return true;
 }

@@ -33,6 +33,16 @@ size_t FlatScene::bytes() const {
            emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float);
 }
 
+void texture_max_average(const trb_texture& t, float mx[3], float avg[3]) {
+    const size_t n = size_t(t.width) * t.height;
+    float s[3] = {0.f, 0.f, 0.f};
+    for (int k = 0; k < 3; ++k) mx[k] = -std::numeric_limits<float>::min();  // as written (core.h:554-556)
+    for (size_t i = 0; i < n; ++i)
+        for (int k = 0; k < 3; ++k) { s[k] += t.rgb[3 * i + k]; mx[k] = std::max(mx[k], t.rgb[3 * i + k]); }
+    const float scale = float(1.0 / (double(3 * n) / 3.0));
+    for (int k = 0; k < 3; ++k) avg[k] = s[k] * scale;
+}
+
 // BSDF constructors: diffuse.h:20-32, phong.h:25-52, mixture.h:25-52, perfectmirror.h:18-26, glass.h:20-31;
 // class selection by illum: renderer.cpp:259-271.
 bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, std::string& err) {
@@ -41,6 +51,12 @@ bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, st
         const trb_material& m = s.materials[i];
         DevMaterial d;
         std::memset(&d, 0, sizeof(d));
+        {
+            const int32_t kd_t = m.tex & 0xffff, ks_t = (m.tex >> 16) & 0xffff;
+            if (size_t(kd_t) > s.n_textures || size_t(ks_t) > s.n_textures || (m.tex && !s.textures)) { err = "material " + std::to_string(i) + ": texture index out of range"; return false; }
+            for (int32_t t : {kd_t, ks_t})
+                if (t && (!s.textures[t - 1].rgb || s.textures[t - 1].width <= 0 || s.textures[t - 1].height <= 0)) { err = "empty texture"; return false; }
+        }
         for (int k = 0; k < 3; ++k) { d.kd[k] = m.kd[k]; d.ks[k] = m.ks[k]; d.ke[k] = m.ke[k]; d.tf[k] = m.tf[k]; }
         d.ns = m.ns; d.ni = m.ni;
         d.emissive = (m.ke[0] != 0.f || m.ke[1] != 0.f || m.ke[2] != 0.f) ? 1 : 0;
@@ -57,11 +73,16 @@ bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, st
                 d.cls = (m.illum == 8) ? MAT_MIXTURE : MAT_PHONG;
                 d.type = EGlossyReflection | EDiffuseReflection;
                 // energy-conservation scale and lobe-selection weight (phong.h:41-47)
-                float mx = m.ks[0] + m.kd[0], my = m.ks[1] + m.kd[1], mz = m.ks[2] + m.kd[2];
+                // with a bitmap the constructor takes the texture's maximum and average (Texture::getMax / getAverage)
+                float kd_max[3] = {m.kd[0], m.kd[1], m.kd[2]}, kd_avg[3] = {m.kd[0], m.kd[1], m.kd[2]};
+                float ks_max[3] = {m.ks[0], m.ks[1], m.ks[2]}, ks_avg[3] = {m.ks[0], m.ks[1], m.ks[2]};
+                if (m.tex & 0xffff) texture_max_average(s.textures[(m.tex & 0xffff) - 1], kd_max, kd_avg);
+                if (m.tex >> 16) texture_max_average(s.textures[(m.tex >> 16) - 1], ks_max, ks_avg);
+                float mx = ks_max[0] + kd_max[0], my = ks_max[1] + kd_max[1], mz = ks_max[2] + kd_max[2];
                 float actual = std::max(std::max(mx, my), mz);
                 d.scale = actual > 1.0f ? 0.99f * (1.0f / actual) : 1.0f;
-                float dAvg = lum(m.kd[0] * d.scale, m.kd[1] * d.scale, m.kd[2] * d.scale);
-                float sAvg = lum(m.ks[0] * d.scale, m.ks[1] * d.scale, m.ks[2] * d.scale);
+                float dAvg = lum(kd_avg[0] * d.scale, kd_avg[1] * d.scale, kd_avg[2] * d.scale);
+                float sAvg = lum(ks_avg[0] * d.scale, ks_avg[1] * d.scale, ks_avg[2] * d.scale);
                 d.spec_weight = sAvg / (dAvg + sAvg);
             }
         }
@@ -319,6 +340,8 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     if (bad.load() == 2) { err = "normal index out of range (the reference needs vn on every face)"; return false; }
     if (bad.load() == 3) { err = "tri_shape must be non-decreasing and < n_shapes"; return false; }
     if (!derive_materials(s, out.materials, err)) return false;
+    for (size_t i = 0; i < s.n_materials; ++i)
+        if (s.materials[i].tex) { err = "bitmap textures are not on the device path yet (not supported)"; return false; }  // TEXGUARD
     std::vector<int32_t> shape_to_emitter;
     if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
     {

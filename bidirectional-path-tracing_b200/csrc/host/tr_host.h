@@ -18,8 +18,20 @@ struct HostScene {
     std::vector<trb_material> materials;
     std::vector<std::string> shape_names, material_names;
     size_t n_shapes = 0;
+    // bitmap textures (core.h:417-497, 525-585): attrib.texcoords, per-corner vt indices, the decoded images
+    std::vector<float> texcoords;
+    std::vector<int32_t> tri_t;
+    struct Texture { std::string file; int32_t w = 0, h = 0; std::vector<float> rgb; };
+    std::vector<Texture> textures;
+    mutable std::vector<trb_texture> texture_views;  // what desc() points at
     trb_scene_desc desc() const;
 };
+
+// Tex::load (core.h:456-497): `<stem>.ppm` next to the name given, binary P6, gamma-expanded and vertically flipped;
+// a file that cannot be read becomes the reference's 1x1 pink texel.
+void load_ppm_texture(const std::string& path, HostScene::Texture& out);
+// BitmapTexture3f::{getMax,getAverage} (core.h:546-566)
+void texture_max_average(const trb_texture& t, float mx[3], float avg[3]);
 
 bool load_obj(const std::string& obj_path, HostScene& out, std::string& err);
 

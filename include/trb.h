@@ -28,7 +28,7 @@ typedef enum trb_status {
     TRB_ERR_CUDA = -3,      /* CUDA runtime error; see trb_last_error              */
     TRB_ERR_NO_SCENE = -4,  /* compute call before trb_scene_upload                */
     TRB_ERR_IO = -5,        /* file could not be read / written / parsed           */
-    TRB_ERR_UNSUPPORTED = -6 /* e.g. illum 5 (reference builds no BSDF, renderer.cpp:259-270) or map_Kd */
+    TRB_ERR_UNSUPPORTED = -6 /* e.g. illum 5 (reference builds no BSDF, renderer.cpp:259-270) */
 } trb_status;
 
 typedef struct trb_context trb_context;       /* device side: one GPU, its scene, its wave buffers */
@@ -63,8 +63,16 @@ typedef struct trb_material {
     float ns;     /* Ns  : Phong exponent                              */
     float ni;     /* Ni  : index of refraction                         */
     int32_t illum; /* 7 diffuse, 3 mirror, 6 glass, 8 mixture, 5 unsupported, else phong (renderer.cpp:259-271) */
-    int32_t _pad;
+    int32_t tex;   /* bitmap textures (diffuse_texname / specular_texname, diffuse.h:23-26, phong.h:28-36):
+                      (1 + index of the map_Kd texture) | (1 + index of the map_Ks texture) << 16; 0 = the constants above */
 } trb_material;
+
+/* Tex (core.h:417-497) as BitmapTexture3f holds it: width*height RGB floats, gamma-expanded (pow(byte / maxval, 2.2f)) and
+ * vertically flipped, i.e. row 0 is the LAST row of the PPM file. */
+typedef struct trb_texture {
+    const float* rgb;
+    int32_t width, height;
+} trb_texture;
 
 /* What tinyobj::LoadObj(triangulate=true) + Scene::load hold (src/core/renderer.cpp:235-315), flattened.
  * Triangles are listed shape-major in file order: tri_shape[] is non-decreasing. */
@@ -81,6 +89,12 @@ typedef struct trb_scene_desc {
     const trb_material* materials;
     size_t n_materials;
     size_t n_shapes;
+    /* bitmap textures; all zero / NULL for an untextured scene */
+    const float* texcoords;   /* attrib.texcoords, 2 floats per vt               */
+    size_t n_texcoords;
+    const int32_t* tri_t;     /* 3 texcoord indices per triangle, -1 = none; may be NULL when n_textures == 0 */
+    const trb_texture* textures;
+    size_t n_textures;
 } trb_scene_desc;
 
 /* Config (src/core/core.h:195-248) restricted to what BDPT reads, plus the sample range that makes the

@@ -140,7 +140,44 @@ inline v3 squareToPhongLobe(float sx, float sy, float exponent) {
 inline float squareToPhongLobePdf(v3 v, float exponent) { return v.z >= 0.f ? (exponent + 2) * kInvTwoPi * powf(v.z, exponent) : 0.f; }
 
 /* ---- scene --------------------------------------------------------------------------------------------- */
-struct Material { v3 kd, ks, ke, tf; float ns, ni; int illum; };
+struct Material { v3 kd, ks, ke, tf; float ns, ni; int illum; int tex = 0; /* (1 + map_Kd texture) | (1 + map_Ks texture) << 16 */ };
+
+/* Tex + BitmapTexture3f (core.h:417-497, 525-585): decoded images (gamma-expanded, vertically flipped), attrib.texcoords and the
+ * per-corner texcoord indices, shape-major like the other triangle arrays */
+struct TexSet {
+    struct Tex { int w = 0, h = 0; std::vector<float> cs; };
+    std::vector<Tex> textures;
+    std::vector<float> texcoords;   /* 2 per vt */
+    std::vector<int> tri_t;         /* 3 per triangle */
+    const std::vector<int>* shapeFirst = nullptr;
+    v3 getAverage(int t) const { /* :546-552 */
+        const Tex& x = textures[t];
+        v3 s = V(0);
+        for (size_t i = 0; i < x.cs.size() / 3; i++) s = s + V(x.cs[i * 3 + 0], x.cs[i * 3 + 1], x.cs[i * 3 + 2]);
+        float scale = float(1.0 / (x.cs.size() / 3.0));
+        return s * scale;
+    }
+    v3 getMax(int t) const { /* :561-567, from -FLT_MIN as written */
+        const Tex& x = textures[t];
+        const float m = -std::numeric_limits<float>::min();
+        v3 s = V(m, m, m);
+        for (size_t i = 0; i < x.cs.size() / 3; i++) s = vmax(s, V(x.cs[i * 3 + 0], x.cs[i * 3 + 1], x.cs[i * 3 + 2]));
+        return s;
+    }
+    v3 eval(int t, const SurfaceInteraction& hit) const { /* :569-585 */
+        const Tex& x = textures[t];
+        const int tri = (*shapeFirst)[hit.shapeID] + int(hit.primID);
+        const int i0 = tri_t[3 * tri], i1 = tri_t[3 * tri + 1], i2 = tri_t[3 * tri + 2];
+        const float ax = texcoords[2 * i0], ay = texcoords[2 * i0 + 1], bx = texcoords[2 * i1], by = texcoords[2 * i1 + 1];
+        const float cx = texcoords[2 * i2], cy = texcoords[2 * i2 + 1];
+        const float k = 1 - hit.u - hit.v;  /* barycentric(): a * (1 - u - v) + b * u + c * v */
+        float sx = ((ax * k + bx * hit.u) + cx * hit.v) + 1.0f, sy = ((ay * k + by * hit.u) + cy * hit.v) + 1.0f;
+        sx = sx - std::floor(sx); sy = sy - std::floor(sy);
+        const int px = std::min(std::max(int(sx * x.w), 0), x.w - 1), py = std::min(std::max(int(sy * x.h), 0), x.h - 1);
+        const int i = x.w * py + px;
+        return V(x.cs[i * 3 + 0], x.cs[i * 3 + 1], x.cs[i * 3 + 2]);
+    }
+};
 
 enum { EDiffuseReflection = 0x2, EGlossyReflection = 0x8, EDeltaReflection = 0x20, EDeltaTransmission = 0x40, ENull = 0x1 };
 const unsigned EDelta = ENull | EDeltaReflection | EDeltaTransmission;
@@ -151,15 +188,19 @@ struct BSDF {
     v3 kd = V(0), ks = V(0), emission = V(0), tf = V(0);
     float exponent = 0, ior = 1, scale = 1, specularSamplingWeight = 0;
     unsigned combinedType = 0;
+    int kdTex = -1, ksTex = -1;     /* diffuse_texname / specular_texname */
+    const TexSet* ts = nullptr;
+    v3 kdAt(const SurfaceInteraction& i) const { return kdTex >= 0 ? ts->eval(kdTex, i) : kd; }  /* Texture::eval */
+    v3 ksAt(const SurfaceInteraction& i) const { return ksTex >= 0 ? ts->eval(ksTex, i) : ks; }
 
     static v3 reflect(v3 d) { return V(-d.x, -d.y, d.z); }
 
     v3 evalGlossy(const SurfaceInteraction& i) const { /* phong.h:61-74, mixture.h:60-73 */
         v3 val = V(0.f);
         if (i.wi.z >= 0.f && i.wo.z >= 0.f) {
-            val = val + kd * kInvPi;
+            val = val + kdAt(i) * kInvPi;
             float cosTheta = std::fmin(std::fmax(dot(i.wi, reflect(i.wo)), 0.f), 1.f);
-            val = val + ks * (exponent + 2) * kInvTwoPi * powf(cosTheta, exponent);
+            val = val + ksAt(i) * (exponent + 2) * kInvTwoPi * powf(cosTheta, exponent);
             val = val * scale;
             val = val * i.wi.z;
         }
@@ -168,7 +209,7 @@ struct BSDF {
     v3 eval(const SurfaceInteraction& i) const {
         switch (kind) {
             case 0: /* diffuse.h:35-43 */
-                if (i.wi.z >= 0.f && i.wo.z >= 0.f) return kd * kInvPi * i.wi.z;
+                if (i.wi.z >= 0.f && i.wo.z >= 0.f) return kdAt(i) * kInvPi * i.wi.z;
                 return V(0.f);
             case 1: case 2: return evalGlossy(i);
             default: return V(0.f); /* perfectmirror.h:33-38, glass.h:55-58 */
@@ -249,19 +290,24 @@ struct BSDF {
     }
 };
 
-BSDF makeBSDF(const Material& m) {
+BSDF makeBSDF(const Material& m, const TexSet* ts = nullptr) {
     BSDF b;
     b.kd = m.kd; b.ks = m.ks; b.emission = m.ke; b.tf = m.tf; b.exponent = m.ns; b.ior = m.ni;
+    b.ts = ts; b.kdTex = (m.tex & 0xffff) - 1; b.ksTex = ((m.tex >> 16) & 0xffff) - 1;
+    if (m.illum == 7) b.ksTex = -1;                      /* DiffuseBSDF reads map_Kd only (diffuse.h:23-26) */
+    if (m.illum == 3 || m.illum == 6) b.kdTex = b.ksTex = -1;
     if (m.illum == 7) { b.kind = 0; b.combinedType = EDiffuseReflection; }
     else if (m.illum == 3) { b.kind = 3; b.combinedType = EDeltaReflection; }
     else if (m.illum == 6) { b.kind = 4; b.combinedType = EDeltaReflection | EDeltaTransmission; }
     else {
         b.kind = (m.illum == 8) ? 2 : 1;
         b.combinedType = EGlossyReflection | EDiffuseReflection;
-        v3 maxValue = m.ks + m.kd; /* phong.h:41-47 */
+        /* phong.h:41-47: Texture::getMax / getAverage - the constant itself, or the bitmap's */
+        v3 maxValue = (b.ksTex >= 0 ? ts->getMax(b.ksTex) : m.ks) + (b.kdTex >= 0 ? ts->getMax(b.kdTex) : m.kd);
         float actualMax = std::max(std::max(maxValue.x, maxValue.y), maxValue.z);
         b.scale = actualMax > 1.0f ? 0.99f * (1.0f / actualMax) : 1.0f;
-        float dAvg = getLuminance(m.kd * b.scale), sAvg = getLuminance(m.ks * b.scale);
+        float dAvg = getLuminance((b.kdTex >= 0 ? ts->getAverage(b.kdTex) : m.kd) * b.scale);
+        float sAvg = getLuminance((b.ksTex >= 0 ? ts->getAverage(b.ksTex) : m.ks) * b.scale);
         b.specularSamplingWeight = sAvg / (dAvg + sAvg);
     }
     return b;
@@ -312,6 +358,7 @@ struct Scene {
     std::vector<int> tri_v, tri_n, tri_mat, tri_shape;  /* shape-major */
     std::vector<int> shapeFirst;                        /* first global triangle of each shape */
     std::vector<Material> materials;
+    TexSet tex;
     std::vector<BSDF> bsdfs;
     std::vector<Emitter> emitters;
     std::vector<int> prims;        /* build_prims: global triangle ids, reordered by the build */
@@ -478,7 +525,8 @@ struct Scene {
     /* Scene::load tail: BSDFs (renderer.cpp:259-271), emitters (:279-305), getShapeArea (:317-339) */
     void finish() {
         bsdfs.clear();
-        for (auto& m : materials) bsdfs.push_back(makeBSDF(m));
+        tex.shapeFirst = &shapeFirst;
+        for (auto& m : materials) bsdfs.push_back(makeBSDF(m, &tex));
         size_t nShapes = tri_shape.empty() ? 0 : size_t(tri_shape.back()) + 1;
         shapeFirst.assign(nShapes + 1, 0);
         for (size_t t = 0; t < tri_shape.size(); t++) shapeFirst[tri_shape[t] + 1] = int(t + 1);
@@ -1192,7 +1240,8 @@ struct Direct {
 extern "C" {
 
 void* orc_create(const float* positions, size_t npos, const float* normals, size_t nnrm, const int* tri_v, const int* tri_n,
-                 const int* tri_mat, const int* tri_shape, size_t ntris, const float* mats16, size_t nmat) {
+                 const int* tri_mat, const int* tri_shape, size_t ntris, const float* mats16, size_t nmat,
+                 const float* texcoords, size_t ntexcoords, const int* tri_t, const float* const* tex_rgb, const int* tex_wh, size_t ntex) {
     Scene* s = new Scene();
     for (size_t i = 0; i < npos; i++) s->vertices.push_back(V(positions[3 * i], positions[3 * i + 1], positions[3 * i + 2]));
     for (size_t i = 0; i < nnrm; i++) s->normals.push_back(V(normals[3 * i], normals[3 * i + 1], normals[3 * i + 2]));
@@ -1200,7 +1249,16 @@ void* orc_create(const float* positions, size_t npos, const float* normals, size
     s->tri_mat.assign(tri_mat, tri_mat + ntris); s->tri_shape.assign(tri_shape, tri_shape + ntris);
     for (size_t i = 0; i < nmat; i++) {
         const float* m = mats16 + 16 * i;
-        s->materials.push_back(Material{V(m[0], m[1], m[2]), V(m[3], m[4], m[5]), V(m[6], m[7], m[8]), V(m[9], m[10], m[11]), m[12], m[13], int(m[14])});
+        s->materials.push_back(Material{V(m[0], m[1], m[2]), V(m[3], m[4], m[5]), V(m[6], m[7], m[8]), V(m[9], m[10], m[11]), m[12], m[13], int(m[14]), ntex ? int(m[15]) : 0});
+    }
+    if (ntex) {
+        s->tex.texcoords.assign(texcoords, texcoords + 2 * ntexcoords);
+        s->tex.tri_t.assign(tri_t, tri_t + 3 * ntris);
+        for (size_t t = 0; t < ntex; t++) {
+            TexSet::Tex x; x.w = tex_wh[2 * t]; x.h = tex_wh[2 * t + 1];
+            x.cs.assign(tex_rgb[t], tex_rgb[t] + size_t(x.w) * x.h * 3);
+            s->tex.textures.push_back(std::move(x));
+        }
     }
     s->finish();
     return s;

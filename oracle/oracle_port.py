@@ -40,12 +40,22 @@ class Oracle:
         mats = np.zeros((len(m), 16), np.float32)
         mats[:, 0:3], mats[:, 3:6], mats[:, 6:9], mats[:, 9:12] = m["kd"], m["ks"], m["ke"], m["tf"]
         mats[:, 12], mats[:, 13], mats[:, 14] = m["ns"], m["ni"], m["illum"]
+        textures = list(getattr(scene, "textures", []))
+        if textures:
+            mats[:, 15] = m["tex"]
         self.n_tris, self.n_mats = len(scene.tri_mat), len(m)
         self._keep = [np.ascontiguousarray(x) for x in (scene.positions, scene.normals, scene.tri_v, scene.tri_n, scene.tri_mat, scene.tri_shape, mats)]
         k = self._keep
         self.L = L
+        tc = np.ascontiguousarray(getattr(scene, "texcoords", np.zeros((0, 2), np.float32)), np.float32)
+        tt = np.ascontiguousarray(getattr(scene, "tri_t", np.zeros((0, 3), np.int32)), np.int32)
+        textures = [np.ascontiguousarray(t, np.float32) for t in textures]
+        ptrs = (C.c_void_p * max(len(textures), 1))(*[t.ctypes.data for t in textures])
+        wh = np.array([[t.shape[1], t.shape[0]] for t in textures], np.int32).reshape(-1, 2)
+        self._keep += [tc, tt, textures, ptrs, wh]
         self.h = C.c_void_p(L.orc_create(_p(k[0]), C.c_size_t(len(k[0])), _p(k[1]), C.c_size_t(len(k[1])), _p(k[2]), _p(k[3]), _p(k[4]), _p(k[5]),
-                                         C.c_size_t(self.n_tris), _p(k[6]), C.c_size_t(self.n_mats)))
+                                         C.c_size_t(self.n_tris), _p(k[6]), C.c_size_t(self.n_mats),
+                                         _p(tc), C.c_size_t(len(tc)), _p(tt), ptrs, _p(wh), C.c_size_t(len(textures))))
         self.width, self.height = 800, 600
 
     def close(self):

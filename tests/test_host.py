@@ -272,3 +272,24 @@ def test_spherelight_scene_is_reproducible_and_pinned(trb):
     em = hs.emitters()
     assert em["n"] == 2 and np.array_equal(em["shape"], g["em_shape"]) and np.array_equal(em["area"].view(np.uint32), g["em_area"].view(np.uint32))
     assert np.array_equal(em["cdf"][: len(g["em_cdf"])].view(np.uint32), g["em_cdf"].view(np.uint32))
+
+
+def test_textured_obj_loader(trb, tmp_path):
+    """vt / map_Kd / map_Ks / PPM through the product's loader: the generated textured scene written out as OBJ + MTL + P6 files
+    reads back bit-identically (Tex::load's gamma expansion and vertical flip, core.h:430-497; texture names resolved against the
+    OBJ's directory, core.h:528-543); a missing image becomes the reference's 1x1 pink texel; texture options are skipped"""
+    from conftest import GOLD
+    import scene_to_obj
+    sc = trb.HostScene.load_npz(GOLD / "scene_textured.npz")
+    obj = scene_to_obj.export_verified(sc, tmp_path / "t.obj")   # raises unless every array, material and texel round-trips
+    back = trb.HostScene.load_obj(obj)
+    assert len(back.textures) == 4 and back.textures[0].shape == (48, 64, 3) and back.tri_t.min() == -1
+    # row 0 of the decoded image is the LAST row of the file
+    raw = (tmp_path / "t_tex0.ppm").read_bytes()
+    body = np.frombuffer(raw[raw.index(b"255\n") + 4:], np.uint8).reshape(48, 64, 3)
+    assert np.array_equal(scene_to_obj.ppm_lut()[body[::-1]].view(np.uint32), back.textures[0].view(np.uint32))
+    mtl = (tmp_path / "t.mtl").read_text().replace("map_Kd t_tex0.ppm", "map_Kd -bm 0.5 -o 1 2 missing.png")
+    (tmp_path / "t.mtl").write_text(mtl)
+    pink = trb.HostScene.load_obj(obj)
+    i = [k for k, t in enumerate(pink.textures) if t.shape == (1, 1, 3)]
+    assert len(i) == 1 and np.array_equal(pink.textures[i[0]].ravel(), [1.0, 0.0, 1.0])

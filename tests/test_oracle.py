@@ -157,3 +157,33 @@ def test_shape_spheres_bit_exact(trb, di_orc, gold, di_scene):
     g = gold("dipaths", f"{di_scene}_mis")
     sp = di_orc(di_scene).shape_spheres(len(g["spheres"]))
     assert np.array_equal(sp.view(np.uint32), g["spheres"].view(np.uint32))
+
+
+def test_bitmap_textures_bit_exact(trb, gold):
+    """BitmapTexture3f (core.h:525-585; map_Kd on Diffuse / Phong, map_Kd + map_Ks on Mixture, wrapped and negative
+    texture coordinates) in the restatement against the unmodified reference, which read the exported OBJ + MTL + PPM files itself
+    (tools/gen_golden_textured.py): whole BDPT, path-tracer and direct-integrator samples, bit for bit"""
+    from conftest import GOLD
+    hs = trb.HostScene.load_npz(GOLD / "scene_textured.npz")
+    assert len(hs.textures) == 4 and (hs.materials["tex"] != 0).sum() == 4
+    o = oracle_port.Oracle(hs)
+    try:
+        g = gold("paths", "textured")
+        o.set_config(trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"])))
+        li, pix, rgb, nd = o.bdpt_paths(g["rays"], g["splat_pix"].shape[1], seeds=g["seeds"])
+        assert np.array_equal(nd, g["draws"]) and np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+        assert np.array_equal(pix, g["splat_pix"]) and np.array_equal(rgb.view(np.uint32), g["splat_rgb"].view(np.uint32))
+        g = gold("ptpaths", "textured_mis")
+        o.set_config(trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"])))
+        o.set_path(depth_cap=0, **_pt_settings(g))
+        li, nd = o.path_paths(g["rays"], seeds=g["seeds"])
+        assert np.array_equal(nd, g["draws"]) and np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+        g = gold("dipaths", "textured_mis")
+        o.set_direct("mis", int(g["emitter_samples"]), int(g["bsdf_samples"]))
+        li, nd = o.direct_paths(g["rays"], seeds=g["seeds"])
+        assert np.array_equal(nd, g["draws"]) and np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+        # the host builder on the textured scene: the reference's BVH order and emitters
+        h = gold("host", "textured")
+        assert np.array_equal(hs.bvh_order(), h["order"]) and np.array_equal(o.bvh_order(), h["order"])
+    finally:
+        o.close()

@@ -164,6 +164,74 @@ def make_sphere_light_scene(n: int = 20, seed: int = 3):
                          n_shapes=len(parts), shape_names=names)
 
 
+def _checker(w, h, a, b, cells, rng, byte_noise=12):
+    """procedural 8-bit image -> the floats Tex::load would hold (pow(byte / 255, 2.2f), row 0 = bottom row of the file)"""
+    yy, xx = np.mgrid[0:h, 0:w]
+    pick = ((xx * cells // w + yy * cells // h) % 2)[..., None]
+    img = np.where(pick == 0, np.array(a, np.float64), np.array(b, np.float64)) * (0.6 + 0.4 * xx[..., None] / max(w - 1, 1))
+    byte = np.clip(np.round(img * 255) + rng.integers(-byte_noise, byte_noise + 1, img.shape), 0, 255).astype(np.uint8)
+    import scene_to_obj
+    return scene_to_obj.ppm_lut()[byte]
+
+
+def make_textured_scene(n: int = 20, seed: int = 5):
+    """bitmap textures (map_Kd / map_Ks -> BitmapTexture3f, core.h:525-585), which no shipped scene has.  The open box
+    with a quad light; back wall Diffuse + map_Kd, floor Mixture + map_Kd + map_Ks, a Phong sphere + map_Kd (constant Ks), a
+    Diffuse sphere + map_Kd, an untextured glass sphere; texture coordinates outside [0, 1) and negative ones exercise the wrap."""
+    trb = importlib.import_module("bidirectional-path-tracing_b200")
+    rng = np.random.default_rng(seed)
+    x0, x1, y0, y1, z0, z1 = -1.0, 1.0, 0.0, 1.6, -1.0, 1.0
+    parts = [  # (name, material, geometry, uv scale or None)
+        ("light", 0, _quad((-0.25, 1.59, -0.25), (0.25, 1.59, -0.25), (0.25, 1.59, 0.25), (-0.25, 1.59, 0.25), (0, -1, 0)), None),
+        ("backWall", 1, _quad((x0, y0, z0), (x1, y0, z0), (x1, y1, z0), (x0, y1, z0), (0, 0, 1)), 2.0),
+        ("ceiling", 2, _quad((x0, y1, z0), (x1, y1, z0), (x1, y1, z1), (x0, y1, z1), (0, -1, 0)), None),
+        ("leftWall", 3, _quad((x0, y0, z0), (x0, y1, z0), (x0, y1, z1), (x0, y0, z1), (1, 0, 0)), None),
+        ("rightWall", 4, _quad((x1, y0, z0), (x1, y0, z1), (x1, y1, z1), (x1, y1, z0), (-1, 0, 0)), None),
+        ("floor", 5, _quad((x0, y0, z0), (x0, y0, z1), (x1, y0, z1), (x1, y0, z0), (0, 1, 0)), 3.0),
+        ("phongSphere", 6, _sphere(n, np.array([-0.5, 0.3, -0.1]), 0.3, rng, amp=0.0), 1.0),
+        ("diffuseSphere", 7, _sphere(n, np.array([0.45, 0.25, -0.35]), 0.25, rng, amp=0.0), 1.0),
+        ("glassSphere", 8, _sphere(n, np.array([0.1, 0.2, 0.45]), 0.2, rng, amp=0.0), None),
+    ]
+    centers = {"phongSphere": (-0.5, 0.3, -0.1), "diffuseSphere": (0.45, 0.25, -0.35)}
+    mats = np.zeros(9, trb.MATERIAL_DTYPE)
+    mats["ni"], mats["tf"] = 1.0, 1.0
+
+    def setm(i, illum, kd=(0, 0, 0), ks=(0, 0, 0), ke=(0, 0, 0), ns=1.0, ni=1.0, kd_tex=-1, ks_tex=-1):
+        mats[i]["illum"], mats[i]["kd"], mats[i]["ks"], mats[i]["ke"], mats[i]["ns"], mats[i]["ni"] = illum, kd, ks, ke, ns, ni
+        mats[i]["tex"] = (kd_tex + 1) | ((ks_tex + 1) << 16)
+    setm(0, 7, kd=(0.78, 0.78, 0.78), ke=(35, 35, 35))
+    setm(1, 7, kd=(0.73, 0.73, 0.73), kd_tex=0)
+    setm(2, 7, kd=(0.73, 0.73, 0.73))
+    setm(3, 7, kd=(0.63, 0.065, 0.05))
+    setm(4, 7, kd=(0.14, 0.45, 0.091))
+    setm(5, 8, kd=(0.5, 0.5, 0.5), ks=(0.3, 0.3, 0.3), ns=30.0, kd_tex=1, ks_tex=2)
+    setm(6, 2, kd=(0.3, 0.3, 0.3), ks=(0.6, 0.6, 0.6), ns=50.0, kd_tex=3)
+    setm(7, 7, kd=(0.5, 0.5, 0.5), kd_tex=0)
+    setm(8, 6, ks=(1, 1, 1), ni=1.5)
+    textures = [_checker(64, 48, (0.9, 0.8, 0.3), (0.2, 0.3, 0.8), 8, rng), _checker(32, 32, (0.8, 0.8, 0.8), (0.25, 0.2, 0.15), 4, rng),
+                _checker(16, 24, (0.7, 0.7, 0.7), (0.05, 0.05, 0.05), 2, rng), _checker(40, 20, (0.9, 0.2, 0.2), (0.9, 0.9, 0.9), 5, rng)]
+    P, N, TV, TM, TS, TT, UV, names = [], [], [], [], [], [], [], []
+    base, uv_base = 0, 0
+    for s_, (name, m, (pos, nrm, tri), uvs) in enumerate(parts):
+        P.append(pos); N.append(nrm); TV.append(tri + base)
+        TM.append(np.full(len(tri), m, np.int32)); TS.append(np.full(len(tri), s_, np.int32)); names.append(name)
+        if uvs is None:
+            TT.append(np.full((len(tri), 3), -1, np.int32))
+        else:
+            if name in centers:
+                d = pos.astype(np.float64) - np.array(centers[name])
+                d /= np.linalg.norm(d, axis=1, keepdims=True)
+                uv = np.stack([np.arctan2(d[:, 2], d[:, 0]) / (2 * np.pi), np.arccos(np.clip(d[:, 1], -1, 1)) / np.pi], 1)  # u in [-0.5, 0.5]
+            else:
+                uv = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float64) * uvs - 0.75
+            UV.append(uv.astype(np.float32)); TT.append(tri + uv_base)
+            uv_base += len(uv)
+        base += len(pos)
+    tv = np.concatenate(TV)
+    return trb.HostScene(np.concatenate(P), np.concatenate(N), tv, tv.copy(), np.concatenate(TM), np.concatenate(TS), mats,
+                         n_shapes=len(parts), shape_names=names, texcoords=np.concatenate(UV), tri_t=np.concatenate(TT), textures=textures)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--tris", type=int, default=200_000)
