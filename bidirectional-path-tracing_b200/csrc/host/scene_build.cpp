@@ -30,7 +30,8 @@ inline float lum(float r, float g, float b) { return (r * 0.212671f + g * 0.7151
 size_t FlatScene::bytes() const {
     return nodes.size() * sizeof(DevNode) + tris.size() * sizeof(DevTri) + shade.size() * sizeof(DevShade) +
            materials.size() * sizeof(DevMaterial) + emitters.size() * sizeof(DevEmitter) +
-           emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float);
+           emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float) +
+           tex_info.size() * sizeof(DevTexInfo) + tri_uv.size() * sizeof(DevTriUV) + texels.size() * sizeof(float);
 }
 
 void texture_max_average(const trb_texture& t, float mx[3], float avg[3]) {
@@ -60,6 +61,8 @@ bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, st
         for (int k = 0; k < 3; ++k) { d.kd[k] = m.kd[k]; d.ks[k] = m.ks[k]; d.ke[k] = m.ke[k]; d.tf[k] = m.tf[k]; }
         d.ns = m.ns; d.ni = m.ni;
         d.emissive = (m.ke[0] != 0.f || m.ke[1] != 0.f || m.ke[2] != 0.f) ? 1 : 0;
+        // which bitmaps the BSDF class reads: Diffuse map_Kd (diffuse.h:23-26), Phong / Mixture both (phong.h:28-36), mirror and glass none
+        d.tex = m.illum == 7 ? (m.tex & 0xffff) : (m.illum == 3 || m.illum == 6) ? 0 : m.tex;
         d.scale = 1.f; d.spec_weight = 0.f;
         const uint32_t EDiffuseReflection = 0x2, EGlossyReflection = 0x8, EDeltaReflection = 0x20, EDeltaTransmission = 0x40;
         switch (m.illum) {
@@ -340,8 +343,25 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     if (bad.load() == 2) { err = "normal index out of range (the reference needs vn on every face)"; return false; }
     if (bad.load() == 3) { err = "tri_shape must be non-decreasing and < n_shapes"; return false; }
     if (!derive_materials(s, out.materials, err)) return false;
-    for (size_t i = 0; i < s.n_materials; ++i)
-        if (s.materials[i].tex) { err = "bitmap textures are not on the device path yet (not supported)"; return false; }  // TEXGUARD
+    // bitmap textures: table, texels, per-triangle coordinates (filled with the triangles below)
+    out.tex_info.clear(); out.texels.clear(); out.tri_uv.clear();
+    bool textured = false;
+    for (const DevMaterial& m : out.materials) textured = textured || m.tex != 0;
+    if (textured) {
+        for (size_t t = 0; t < s.n_textures; ++t) {
+            const trb_texture& x = s.textures[t];
+            if (!x.rgb || x.width <= 0 || x.height <= 0) { err = "empty texture"; return false; }
+            if (out.texels.size() / 3 + size_t(x.width) * x.height > 0xffffffffu) { err = "textures too large"; return false; }
+            out.tex_info.push_back(DevTexInfo{uint32_t(out.texels.size() / 3), x.width, x.height, 0});
+            out.texels.insert(out.texels.end(), x.rgb, x.rgb + size_t(x.width) * x.height * 3);
+        }
+        if (!s.tri_t || !s.texcoords) { err = "textured material without texture coordinates"; return false; }
+        for (size_t t = 0; t < s.n_tris; ++t) {
+            if (!out.materials[s.tri_mat[t]].tex) continue;
+            for (int k = 0; k < 3; ++k)  // the reference indexes attrib.texcoords with -1 here (core.h:572-577): undefined
+                if (s.tri_t[3 * t + k] < 0 || size_t(s.tri_t[3 * t + k]) >= s.n_texcoords) { err = "face of a textured material without vt: undefined in the reference"; return false; }
+        }
+    }
     std::vector<int32_t> shape_to_emitter;
     if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
     {
@@ -362,6 +382,7 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
 
     out.tris.resize(n);
     out.shade.resize(n);
+    if (textured) out.tri_uv.assign(n, DevTriUV{{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}});
     parallel_for(n, 1 << 16, [&](size_t p0, size_t p1) {
     for (size_t p = p0; p < p1; ++p) {
         const int32_t t = tree.order[p];
@@ -386,6 +407,13 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         ds.n2[0] = n2.x; ds.n2[1] = n2.y; ds.n2[2] = n2.z;
         ds.shape = s.tri_shape[t]; ds.prim = t - shape_first[s.tri_shape[t]]; ds.mat = mat;
         ds.emitter = shape_to_emitter[s.tri_shape[t]]; ds.tri = t; ds.pad = 0;
+        if (textured && out.materials[mat].tex) {
+            DevTriUV& uv = out.tri_uv[p];
+            for (int k = 0; k < 2; ++k) {
+                uv.st0[k] = s.texcoords[2 * s.tri_t[3 * t] + k]; uv.st1[k] = s.texcoords[2 * s.tri_t[3 * t + 1] + k];
+                uv.st2[k] = s.texcoords[2 * s.tri_t[3 * t + 2] + k];
+            }
+        }
     }
     });
 

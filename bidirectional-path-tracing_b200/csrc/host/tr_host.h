@@ -82,7 +82,7 @@ struct alignas(16) DevMaterial {
     float scale;                      // phong.h:41-43
     float spec_weight;                // specularSamplingWeight, phong.h:45-47
     int32_t emissive;                 // any(ke != 0)
-    int32_t pad;
+    int32_t tex;                      // (1 + map_Kd texture) | (1 + map_Ks texture) << 16 as the BSDF class reads them; 0 = constants
 };
 static_assert(sizeof(DevMaterial) == 80, "material record must be 80 B");
 
@@ -101,6 +101,11 @@ struct alignas(16) DevEmitterTri {
 static_assert(sizeof(DevEmitterTri) == 80, "emitter triangle must be 80 B");
 
 #define TRB_TOP_NODES_MAX 1024
+// bitmap textures (BitmapTexture3f, core.h:525-585): table entry + per-triangle texture coordinates (build order, like DevTri)
+struct alignas(16) DevTexInfo { uint32_t first_texel; int32_t w, h, pad; };
+struct alignas(16) DevTriUV { float st0[2], st1[2], st2[2], pad[2]; };
+static_assert(sizeof(DevTexInfo) == 16 && sizeof(DevTriUV) == 32, "texture records");
+
 struct FlatScene {
     std::vector<DevNode> nodes;
     std::vector<DevTri> tris;
@@ -109,6 +114,9 @@ struct FlatScene {
     std::vector<DevEmitter> emitters;
     std::vector<DevEmitterTri> emitter_tris;
     std::vector<float> emitter_cdf;
+    std::vector<DevTexInfo> tex_info;   // empty for an untextured scene (then tri_uv and texels are empty too)
+    std::vector<DevTriUV> tri_uv;
+    std::vector<float> texels;          // RGB, all textures back to back
     std::vector<float> emitter_sphere;  // per emitter: Scene::getShapeCenter xyz, getShapeRadius (renderer.cpp:349-358) - DirectIntegrator's sphere lights
     std::vector<int32_t> order;  // order[pos] = global tri id
     int32_t top_nodes = 0;       // nodes [0, top_nodes) are the top of the tree in breadth-first order (<= TRB_TOP_NODES_MAX)

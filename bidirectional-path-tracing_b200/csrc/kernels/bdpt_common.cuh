@@ -15,6 +15,10 @@ struct SceneDev {
     const trb::DevEmitter* emitters;
     const trb::DevEmitterTri* etris;
     const float* cdf;
+    const float4* tri_uv;   // 2 per triangle (DevTriUV), build order; textured scenes only
+    const int4* tex_info;   // DevTexInfo per texture
+    const float* texels;    // RGB
+    int32_t has_tex;        // 0: every reflectance is a constant (no shipped scene has map_Kd / map_Ks)
     const float4* esphere;  // per emitter: shape centre xyz, radius (renderer.cpp:349-358; DirectIntegrator only)
     int32_t root_ref;
     int32_t n_emitters;
@@ -82,6 +86,8 @@ struct WaveParams {
     int32_t* q_in;        // P   live slots entering this bounce
     int32_t* q_out;       // P   live slots leaving it
     EyeVertex* ev;        // P   eye vertex of the current bounce (connecting slots only)
+    float4* lv_tex;       // K * P, textured scenes only: (triangle position bits, u, v, -) of the stored vertex, for BitmapTexture3f::eval
+    float4* ev_tex;       // P
     int32_t* q_conn;      // P*K (slot << 6 | light vertex) pairs to connect this bounce, dense (path tracer: a P-slot queue)
     uint32_t* counters;   // [0]=q_out count, [1]=shadow count, [2]=closest rays traced, [3]=any rays traced
     RayT* sray;           // shadow capacity
@@ -165,6 +171,34 @@ __device__ __forceinline__ Surf make_surf(const SceneDev& sc, const HitT& h, con
     o.shape = __float_as_int(a.w); o.mat = __float_as_int(c.w); o.emitter = __float_as_int(d.w);
     return o;
 }
+
+// ---- bitmap textures (BitmapTexture3f::eval, core.h:569-585): nearest texel at the wrapped interpolated coordinate -------
+__device__ __forceinline__ V3 tex_eval(const SceneDev& sc, int tex, int pos, float u, float v) {
+    const float4 a = __ldg(sc.tri_uv + 2 * size_t(pos)), b = __ldg(sc.tri_uv + 2 * size_t(pos) + 1);
+    const int4 ti = __ldg(sc.tex_info + tex);
+    const float k = 1 - u - v;
+    float sx = ((a.x * k + a.z * u) + b.x * v) + 1.0f, sy = ((a.y * k + a.w * u) + b.y * v) + 1.0f;
+    sx = sx - floorf(sx); sy = sy - floorf(sy);
+    const int px = min(max(int(sx * float(ti.y)), 0), ti.y - 1), py = min(max(int(sy * float(ti.z)), 0), ti.z - 1);
+    const float* t = sc.texels + 3 * (size_t(uint32_t(ti.x)) + size_t(ti.y) * py + px);
+    return mk(__ldg(t), __ldg(t + 1), __ldg(t + 2));
+}
+// the material as the BSDF sees it at a hit: Kd / Ks replaced by their bitmaps where the material has them
+__device__ __forceinline__ void apply_tex(const SceneDev& sc, Mat& m, int pos, float u, float v) {
+    if (m.tex & 0xffff) m.kd = tex_eval(sc, (m.tex & 0xffff) - 1, pos, u, v);
+    if (m.tex >> 16) m.ks = tex_eval(sc, (m.tex >> 16) - 1, pos, u, v);
+}
+__device__ __forceinline__ Mat load_mat_at(const SceneDev& sc, int id, const HitT& h) {
+    Mat m = load_mat(sc.mats, id);
+    if (sc.has_tex && m.tex) apply_tex(sc, m, h.pos, h.u, h.v);
+    return m;
+}
+__device__ __forceinline__ Mat load_mat_stored(const SceneDev& sc, int id, const float4* rec) {  // rec: the vertex's entry in lv_tex / ev_tex
+    Mat m = load_mat(sc.mats, id);
+    if (sc.has_tex && m.tex) { const float4 t = *rec; apply_tex(sc, m, __float_as_int(t.x), t.y, t.z); }
+    return m;
+}
+__device__ __forceinline__ float4 tex_record(const HitT& h) { return make_float4(__int_as_float(h.pos), h.u, h.v, 0.f); }
 
 // ---- emitter services (integrator.cpp:46-100, math.h:99-111,229-234) -----------------------------------
 struct EmitterSample {

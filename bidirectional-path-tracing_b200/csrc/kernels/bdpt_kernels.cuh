@@ -243,7 +243,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_light_bounce(const __grid_co
         if (hit_valid(h, r)) {
             alive = true;
             s = make_surf(p.sc, h, r);
-            m = load_mat(p.sc.mats, s.mat);
+            m = load_mat_at(p.sc, s.mat, h);
             float4 st = p.st_t[slot];
             T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
             const float distSquared = s.t * s.t;
@@ -269,6 +269,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_light_bounce(const __grid_co
                 lv.wox = s.wo.x; lv.woy = s.wo.y; lv.woz = s.wo.z; lv.mat = s.mat;
                 lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.rr = rr;
                 p.lv[size_t(j) * p.P + slot] = lv;
+                if (p.sc.has_tex) p.lv_tex[size_t(j) * p.P + slot] = tex_record(p.hit[slot]);
                 p.nlv[slot] = j + 1;
             }
             if (rr_continue(p, depth + 1, rr, rng)) {
@@ -343,7 +344,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
         if (hit_valid(h, r)) {
             alive = true;
             s = make_surf(p.sc, h, r);
-            m = load_mat(p.sc.mats, s.mat);
+            m = load_mat_at(p.sc, s.mat, h);
             float4 st = p.st_t[slot];
             T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
             const float distSquared = s.t * s.t;
@@ -431,6 +432,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
             e.wox = s.wo.x; e.woy = s.wo.y; e.woz = s.wo.z; e.mat = s.mat | (rr < 1.f ? EV_RR_HALF : 0);
             e.tx = T.x; e.ty = T.y; e.tz = T.z; e.target = li_target;
             p.ev[slot] = e;
+            if (p.sc.has_tex) p.ev_tex[slot] = tex_record(p.hit[slot]);
         }
     }
     if (in) {
@@ -455,6 +457,8 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
 
 // ---- connectVertices (bdpt.h:434-483): one thread per (eye vertex, stored light vertex) pair of the dense list k_eye_bounce wrote.
 // Replaces the per-thread loop over the sample's light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). ----
+// TEX: the scene has bitmap textures (their lookup is compiled out of the untextured instance, which every shipped scene runs)
+template <bool TEX>
 __global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_pairs_ptr) {
     const unsigned long long total = *n_pairs_ptr;
     const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballot of push_shadow
@@ -485,9 +489,11 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_con
                 float cosL = l_wi.z, cosE = e_wi.z;
                 if (!(cosL <= 0.f || cosE <= 0.f)) {
                     Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
+                    if (TEX && lm.tex) { const float4 t = p.lv_tex[size_t(j) * p.P + slot]; apply_tex(p.sc, lm, __float_as_int(t.x), t.y, t.z); }
                     const int emat = __float_as_int(ec.w);
                     const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
                     Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
+                    if (TEX && m.tex) { const float4 t = p.ev_tex[slot]; apply_tex(p.sc, m, __float_as_int(t.x), t.y, t.z); }
                     Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
                     Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
                     float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * lrr;

@@ -40,6 +40,7 @@ struct Mat {
     int cls;
     uint32_t type;
     bool emissive;
+    int tex;   // DevMaterial::tex
 };
 
 __device__ __forceinline__ Mat load_mat(const trb::DevMaterial* mats, int id) {
@@ -50,7 +51,7 @@ __device__ __forceinline__ Mat load_mat(const trb::DevMaterial* mats, int id) {
     m.ks = mk(b.x, b.y, b.z); m.type = __float_as_uint(b.w);
     m.ke = mk(c.x, c.y, c.z); m.ns = c.w;
     m.tf = mk(d.x, d.y, d.z); m.ni = d.w;
-    m.scale = e.x; m.sw = e.y; m.emissive = __float_as_int(e.z) != 0;
+    m.scale = e.x; m.sw = e.y; m.emissive = __float_as_int(e.z) != 0; m.tex = __float_as_int(e.w);
     return m;
 }
 

@@ -86,6 +86,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_di_init(const __grid_constant__ W
             v.wox = s.wo.x; v.woy = s.wo.y; v.woz = s.wo.z; v.mat = s.mat;
             v.tx = 0.f; v.ty = 0.f; v.tz = 0.f; v.rr = 0.f;
             p.lv[i] = v;
+            if (p.sc.has_tex) p.lv_tex[i] = tex_record(h);
             float4* st = reinterpret_cast<float4*>(p.ev + i);
             st[2] = make_float4(0.f, 0.f, 0.f, 0.f); st[3] = make_float4(0.f, 0.f, 0.f, 0.f);
             n = 1;
@@ -110,7 +111,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_di_gen(const __grid_constant__ Wa
         float4* st = reinterpret_cast<float4*>(p.ev + slot);
         const float inf = __int_as_float(0x7f800000);
         if (phase == 1) {  // direct.h:251-256, :409-414: the ray is traced whatever the sample's value
-            Mat m = load_mat(p.sc.mats, v.mat);
+            Mat m = load_mat_stored(p.sc, v.mat, p.lv_tex + slot);
             float ux = rng.next(), uy = rng.next();
             V3 wi; float pdf;
             V3 fcos = bsdf_sample(m, v.wo, ux, uy, &wi, &pdf);
@@ -192,7 +193,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_di_resolve(const __grid_constant_
     float4* st = reinterpret_cast<float4*>(p.ev + slot);
     const float4 a = st[0], b = st[1];
     PtVertex v = pt_load_vertex(p, 0, slot, nullptr, nullptr, nullptr, nullptr);
-    Mat m = load_mat(p.sc.mats, v.mat);
+    Mat m = load_mat_stored(p.sc, v.mat, p.lv_tex + slot);
     V3 c = mk(0.f);
     int which = 2;
     if (phase == 1) {

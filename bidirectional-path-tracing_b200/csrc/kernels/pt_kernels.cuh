@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_implicit(const __grid_constant
         }
         if (shade && depth < pt.max_depth) {
             Surf s = make_surf(p.sc, h, r);
-            Mat m = load_mat(p.sc.mats, s.mat);
+            Mat m = load_mat_at(p.sc, s.mat, h);
             uint32_t pixel, sample;
             slot_ids(p, slot, &pixel, &sample);
             float4 sv = p.st_v[slot];
@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_begin(const __grid_constant__ 
         const float rrSample = rng.next();
         if (depth < pt.max_depth || (pt.max_depth == -1 && (depth < pt.rr_depth || rrSample < pt.rr_prob))) {
             Surf s = make_surf(p.sc, h, r);
-            Mat m = load_mat(p.sc.mats, s.mat);
+            Mat m = load_mat_at(p.sc, s.mat, h);
             float ux = rng.next(), uy = rng.next();
             V3 wi; float pdf;
             V3 fcos = bsdf_sample(m, s.wo, ux, uy, &wi, &pdf);
@@ -152,6 +152,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_begin(const __grid_constant__ 
             v.wox = s.wo.x; v.woy = s.wo.y; v.woz = s.wo.z; v.mat = s.mat | (scaled ? PT_RR_SCALED : 0);
             v.tx = fcos.x; v.ty = fcos.y; v.tz = fcos.z; v.rr = 0.f;
             p.lv[size_t(depth) * p.P + slot] = v;
+            if (p.sc.has_tex) p.lv_tex[size_t(depth) * p.P + slot] = tex_record(h);
             p.nlv[slot] = depth + 1;
             p.ray[slot] = pt_ray(s.p, to_world(s.f, wi));
             go = true;
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_check(const __grid_constant__ 
             Rng rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
             float pdf0; uint32_t ns;
             PtVertex v = pt_load_vertex(p, depth, slot, nullptr, nullptr, &pdf0, &ns);
-            Mat m = load_mat(p.sc.mats, v.mat);
+            Mat m = load_mat_stored(p.sc, v.mat, p.lv_tex + size_t(depth) * p.P + slot);
             const BvhView bvh = bvh_of(p.sc);
             uint32_t tries = 0, traced = 0;
             while (!is_zero(ke) && rng.next() < 0.95f && tries < TRB_PT_MAX_RETRIES) {
@@ -272,7 +273,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_emitter_resolve(const __grid_c
     float4 a = st[0], b = st[1];
     if (vem != __float_as_int(b.z)) return;  // visibilityInteraction.shapeID == emitter.shapeID
     PtVertex v = pt_load_vertex(p, depth, slot, nullptr, nullptr, nullptr, nullptr);
-    Mat m = load_mat(p.sc.mats, v.mat);
+    Mat m = load_mat_stored(p.sc, v.mat, p.lv_tex + size_t(depth) * p.P + slot);
     V3 Li = pt_vis_emission(p, true, vmat);
     V3 wiL = mk(a.x, a.y, a.z);
     float a2s = a.w, emitterPdf = b.x, emitterAreaPdf = b.y;
@@ -291,7 +292,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_bsdf_gen(const __grid_constant
     bool go = false;
     if (slot < p.P && p.nlv[slot] > depth) {
         PtVertex v = pt_load_vertex(p, depth, slot, nullptr, nullptr, nullptr, nullptr);
-        Mat m = load_mat(p.sc.mats, v.mat);
+        Mat m = load_mat_stored(p.sc, v.mat, p.lv_tex + size_t(depth) * p.P + slot);
         uint32_t pixel, sample;
         slot_ids(p, slot, &pixel, &sample);
         float4 sv = p.st_v[slot];

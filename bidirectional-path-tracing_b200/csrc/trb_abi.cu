@@ -43,6 +43,7 @@ struct DevBuf {
     size_t bytes() const { return n * sizeof(T); }
 };
 
+#define TRB_SCENE_ARRAYS 11
 enum LaunchKind { LK_CLOSEST = 0, LK_ANY = 1, LK_LOGIC = 2, LK_N = 3 };
 
 }  // namespace
@@ -64,6 +65,9 @@ struct trb_context {
     DevBuf<trb::DevEmitterTri> d_etris;
     DevBuf<float> d_cdf;
     DevBuf<float4> d_esphere;
+    DevBuf<trb::DevTexInfo> d_tex_info;   // bitmap textures: empty for an untextured scene
+    DevBuf<trb::DevTriUV> d_tri_uv;
+    DevBuf<float> d_texels;
     SceneDev sc{};
     uint8_t* pinned = nullptr;  // flattened scene staged in pinned host memory (trb_scene_refresh)
     size_t pinned_bytes = 0;
@@ -77,6 +81,7 @@ struct trb_context {
     DevBuf<uint32_t> sort_keys[2], sort_hist[2];   // ray-queue sort (trace_sort.cuh): [0] main stream (closest), [1] shadow stream
     DevBuf<int32_t> sort_q[2];
     DevBuf<EyeVertex> ev;
+    DevBuf<float4> lv_tex, ev_tex;       // textured scenes only: (triangle, u, v) of the stored vertices
     DevBuf<Pending> spend, spend2;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
     DevBuf<uint32_t> fetch_ctr;          // queue cursor of the stand-alone trace entry points
@@ -209,6 +214,7 @@ int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P * kk)); TRB_CUDA(c, c->ev.alloc(P));  // q_conn: (slot, light vertex) pairs
     TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
     TRB_CUDA(c, c->sray2.alloc(shadow_cap)); TRB_CUDA(c, c->spend2.alloc(shadow_cap));
+    if (c->sc.has_tex) { TRB_CUDA(c, c->lv_tex.alloc(P * kk)); TRB_CUDA(c, c->ev_tex.alloc(P)); }
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
     TRB_CUDA(c, c->d_stats.alloc(8));
     return TRB_OK;
@@ -267,6 +273,7 @@ void trb_destroy(trb_context* c) {
     cudaStreamSynchronize(c->stream);
     c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
     c->d_etris.release(); c->d_cdf.release(); c->d_esphere.release(); c->pt_ctr.release();
+    c->d_tex_info.release(); c->d_tri_uv.release(); c->d_texels.release(); c->lv_tex.release(); c->ev_tex.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->sray2.release(); c->spend2.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->q_conn.release(); c->ev.release(); c->spend.release();
     c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
@@ -303,13 +310,15 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     TRB_CUDA(c, c->d_shade.alloc(f.shade.size())); TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
     TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
     TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size())); TRB_CUDA(c, c->d_esphere.alloc(f.emitter_sphere.size() / 4));
+    TRB_CUDA(c, c->d_tex_info.alloc(f.tex_info.size())); TRB_CUDA(c, c->d_tri_uv.alloc(f.tri_uv.size())); TRB_CUDA(c, c->d_texels.alloc(f.texels.size()));
     // stage everything in one pinned blob so that (re-)uploads are plain async copies from pinned memory
-    const size_t sizes[8] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+    const size_t sizes[TRB_SCENE_ARRAYS] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
                              f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
                              f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
-                             f.emitter_sphere.size() * sizeof(float)};
-    const void* srcs[8] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data(),
-                           f.emitter_sphere.data()};
+                             f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
+                             f.tri_uv.size() * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
+    const void* srcs[TRB_SCENE_ARRAYS] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(),
+                                          f.emitter_cdf.data(), f.emitter_sphere.data(), f.tex_info.data(), f.tri_uv.data(), f.texels.data()};
     size_t total = 0;
     for (size_t b : sizes) total += (b + 255) & ~size_t(255);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
@@ -318,7 +327,7 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     size_t off = 0;
     {   // the staging copy (1.8 GB for 10 M triangles) on a few host threads
         std::vector<std::thread> th;
-        for (int k = 0; k < 8; ++k) {
+        for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) {
             const size_t piece = size_t(64) << 20;
             for (size_t o = 0; o < sizes[k]; o += piece) {
                 uint8_t* dst = c->pinned + off + o; const char* src = static_cast<const char*>(srcs[k]) + o; const size_t len = std::min(piece, sizes[k] - o);
@@ -332,6 +341,8 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
     c->sc.tris = reinterpret_cast<const F4*>(c->d_tris.p);
     c->sc.shade = c->d_shade.p; c->sc.mats = c->d_mats.p; c->sc.emitters = c->d_emitters.p; c->sc.etris = c->d_etris.p;
+    c->sc.tri_uv = reinterpret_cast<const float4*>(c->d_tri_uv.p); c->sc.tex_info = reinterpret_cast<const int4*>(c->d_tex_info.p);
+    c->sc.texels = c->d_texels.p; c->sc.has_tex = f.tex_info.empty() ? 0 : 1;
     c->sc.cdf = c->d_cdf.p; c->sc.esphere = c->d_esphere.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
     c->has_scene = true;
     return trb_scene_refresh(c);
@@ -341,14 +352,16 @@ int trb_scene_refresh(trb_context* c) {
     if (!c) return TRB_ERR_INVALID;
     if (!c->has_scene || !c->pinned) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     cudaSetDevice(c->device);
-    void* dsts[8] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p};
+    void* dsts[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p,
+                                    c->d_tex_info.p, c->d_tri_uv.p, c->d_texels.p};
     const trb::FlatScene& f = c->flat;
-    const size_t sizes[8] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
+    const size_t sizes[TRB_SCENE_ARRAYS] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
                              f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
                              f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
-                             f.emitter_sphere.size() * sizeof(float)};
+                             f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
+                             f.tri_uv.size() * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
     size_t off = 0;
-    for (int k = 0; k < 8; ++k) {
+    for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) {
         if (sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], c->pinned + off, sizes[k], cudaMemcpyHostToDevice, c->stream));
         off += (sizes[k] + 255) & ~size_t(255);
     }
@@ -386,7 +399,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
     p.accum = w.d_accum; p.splat_pix = w.d_splat_pix;
     p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
-    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p; p.q_conn = c->q_conn.p; p.sray = c->sray.p; p.spend = c->spend.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p; p.lv_tex = c->lv_tex.p; p.ev_tex = c->ev_tex.p; p.q_conn = c->q_conn.p; p.sray = c->sray.p; p.spend = c->spend.p;
     p.shadow_cap = uint32_t(std::min<size_t>(c->sray.n, 0xffffffffu));
     const int n_stage = 2 * kk + 4;
     TRB_CUDA(c, cudaMemsetAsync(c->counters.p, 0, size_t(n_stage) * CTR_N * sizeof(uint32_t), c->stream));
@@ -473,7 +486,9 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         if (depth > 1) closest(p.ray, p.q_in, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
         shadow_buffers();
         k_eye_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in);
-        k_connect_vertices<<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN); c->mark(LK_LOGIC);
+        if (c->sc.has_tex) k_connect_vertices<true><<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN);
+        else k_connect_vertices<false><<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN);
+        c->mark(LK_LOGIC);
         ++c->launches;
         trace_shadow();
     }
@@ -597,7 +612,7 @@ int run_pt_wave(trb_context* c, const WaveRun& w, const PtParams& pt, const trb:
     p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
     p.accum = w.d_accum;
     p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
-    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p; p.lv_tex = c->lv_tex.p; p.ev_tex = c->ev_tex.p;
     const int D = pt.cap, M = pt.emitter_samples, NB = pt.bsdf_samples;
     // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then the other queues, then one fetch cursor per traversal launch
     const size_t n_ray = size_t(D) * size_t(1 + M + NB) + size_t(pt.max_depth >= 0 ? pt.max_depth : 0) + 8;
@@ -714,7 +729,7 @@ int run_di_wave(trb_context* c, const WaveRun& w, const DiParams& dp, const trb:
     p.inject_rays = w.d_inject_rays; p.inject_rng = w.d_inject_rng; p.inject_stride = w.inject_stride; p.parity = w.parity ? 1 : 0;
     p.accum = w.d_accum;
     p.cam_ray = c->cam_ray.p; p.ray = c->ray.p; p.hit = c->hit.p; p.hit0 = c->hit0.p; p.st_t = c->st_t.p; p.st_v = c->st_v.p;
-    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p;
+    p.lv = c->lv.p; p.nlv = c->nlv.p; p.ev = c->ev.p; p.lv_tex = c->lv_tex.p; p.ev_tex = c->ev_tex.p;
     const int M = dp.strategy == DI_BSDF ? 0 : dp.emitter_samples;
     const int NB = (dp.strategy == DI_MIS || dp.strategy == DI_BSDF) ? dp.bsdf_samples : 0;
     // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then one fetch cursor per traversal launch
