@@ -28,10 +28,10 @@ inline float lum(float r, float g, float b) { return (r * 0.212671f + g * 0.7151
 }  // namespace
 
 size_t FlatScene::bytes() const {
-    return nodes.size() * sizeof(DevNode) + tris.size() * sizeof(DevTri) + shade.size() * sizeof(DevShade) +
+    return n_nodes * sizeof(DevNode) + n_tris * sizeof(DevTri) + n_tris * sizeof(DevShade) +
            materials.size() * sizeof(DevMaterial) + emitters.size() * sizeof(DevEmitter) +
            emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float) +
-           tex_info.size() * sizeof(DevTexInfo) + tri_uv.size() * sizeof(DevTriUV) + texels.size() * sizeof(float);
+           tex_info.size() * sizeof(DevTexInfo) + n_tri_uv * sizeof(DevTriUV) + texels.size() * sizeof(float);
 }
 
 void texture_max_average(const trb_texture& t, float mx[3], float avg[3]) {
@@ -326,6 +326,11 @@ bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
 }
 
 bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
+    return flatten_tables(s, out, err) && flatten_geometry(s, out, err);
+}
+
+// Everything but the acceleration structure and the per-triangle records: validation, BSDF parameters, textures, emitters.
+bool flatten_tables(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     if (!s.positions || !s.normals || !s.tri_v || !s.tri_n || !s.tri_mat || !s.tri_shape || !s.materials) {
         err = "null array in scene description"; return false;
     }
@@ -362,8 +367,14 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
                 if (s.tri_t[3 * t + k] < 0 || size_t(s.tri_t[3 * t + k]) >= s.n_texcoords) { err = "face of a textured material without vt: undefined in the reference"; return false; }
         }
     }
-    std::vector<int32_t> shape_to_emitter;
+    std::vector<int32_t>& shape_to_emitter = out.shape_to_emitter;
     if (!derive_emitters(s, out.materials, out.emitters, out.emitter_tris, out.emitter_cdf, shape_to_emitter, err)) return false;
+    out.shape_first.assign(s.n_shapes + 1, 0);
+    for (size_t t = 0; t < s.n_tris; ++t) out.shape_first[s.tri_shape[t] + 1] = int32_t(t + 1);
+    for (size_t k = 1; k <= s.n_shapes; ++k) out.shape_first[k] = std::max(out.shape_first[k], out.shape_first[k - 1]);
+    out.textured = textured;
+    out.nodes.clear(); out.tris.clear(); out.shade.clear(); out.order.clear();
+    out.n_nodes = out.n_tris = out.n_tri_uv = 0;
     {
         std::vector<float> sph;
         shape_spheres(s, sph);
@@ -371,14 +382,19 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         for (const DevEmitter& e : out.emitters) out.emitter_sphere.insert(out.emitter_sphere.end(), sph.begin() + 4 * e.shape, sph.begin() + 4 * e.shape + 4);
     }
 
+    return true;
+}
+
+// The reference-order BVH on the host cores and the per-triangle records in its primitive order (the device build of
+// kernels/bvh_build.cuh produces the same arrays on the GPU).
+bool flatten_geometry(const trb_scene_desc& s, FlatScene& out, std::string& err) {
+    const bool textured = out.textured;
+    const std::vector<int32_t>& shape_to_emitter = out.shape_to_emitter;
+    const std::vector<int32_t>& shape_first = out.shape_first;
     RefTree tree;
     if (!build_ref_tree(s, tree, err)) return false;
     out.order = tree.order;
     const size_t n = s.n_tris;
-
-    std::vector<int32_t> shape_first(s.n_shapes + 1, 0);
-    for (size_t t = 0; t < n; ++t) shape_first[s.tri_shape[t] + 1] = int32_t(t + 1);
-    for (size_t k = 1; k <= s.n_shapes; ++k) shape_first[k] = std::max(shape_first[k], shape_first[k - 1]);
 
     out.tris.resize(n);
     out.shade.resize(n);
@@ -423,7 +439,8 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     // Only the child references depend on the numbering; the set of boxes a ray tests and the hits do not.
     std::vector<int32_t> inner_index(tree.nodes.size(), -1);
     int32_t n_inner = 0;
-    if (!tree.nodes.empty() && tree.nodes[0].left >= 0) {
+    const char* top_env = std::getenv("TRB_TOP_NUMBERING");  // only the -DTRB_TOP experiment builds of the kernel need it
+    if (top_env && std::atoi(top_env) > 0 && !tree.nodes.empty() && tree.nodes[0].left >= 0) {
         std::vector<int32_t> bfs;
         bfs.push_back(0);
         for (size_t k = 0; k < bfs.size() && bfs.size() < size_t(TRB_TOP_NODES_MAX); ++k) {
@@ -466,6 +483,7 @@ bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
         md = std::max(md, depth[i]);
     }
     out.max_depth = md;
+    out.n_nodes = out.nodes.size(); out.n_tris = out.tris.size(); out.n_tri_uv = out.tri_uv.size();
     return true;
 }
 

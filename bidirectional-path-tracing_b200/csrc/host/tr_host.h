@@ -118,7 +118,11 @@ struct FlatScene {
     std::vector<DevTriUV> tri_uv;
     std::vector<float> texels;          // RGB, all textures back to back
     std::vector<float> emitter_sphere;  // per emitter: Scene::getShapeCenter xyz, getShapeRadius (renderer.cpp:349-358) - DirectIntegrator's sphere lights
-    std::vector<int32_t> order;  // order[pos] = global tri id
+    std::vector<int32_t> order;  // order[pos] = global tri id (host build only)
+    // counts of the device arrays (nodes / tris = shade / tri_uv): the vectors above are empty after a device build
+    size_t n_nodes = 0, n_tris = 0, n_tri_uv = 0;
+    bool textured = false;
+    std::vector<int32_t> shape_to_emitter, shape_first;  // per shape: emitter index or -1; first global triangle (n_shapes + 1)
     int32_t top_nodes = 0;       // nodes [0, top_nodes) are the top of the tree in breadth-first order (<= TRB_TOP_NODES_MAX)
     int32_t root_ref = 0;        // root as a child reference (leaf when the scene has <= 4 triangles)
     int32_t max_depth = 0;       // tree depth (traversal stack bound)
@@ -141,7 +145,9 @@ bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& ma
 // Scene::load's tail (renderer.cpp:294-304): per shape the mean of the vertices its indices name (running fp32 sum in index
 // order) and radius = AABB max.x - centre.x; out4 = n_shapes x (cx, cy, cz, r)
 void shape_spheres(const trb_scene_desc& s, std::vector<float>& out4);
-bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err);
+bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err);      // = tables + geometry
+bool flatten_tables(const trb_scene_desc& s, FlatScene& out, std::string& err);
+bool flatten_geometry(const trb_scene_desc& s, FlatScene& out, std::string& err);
 
 // ---- camera (glm-order arithmetic; renderer.cpp:143-153, bdpt.h:49-55,485-496) --------------------
 struct CameraDev {

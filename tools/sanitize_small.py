@@ -34,3 +34,16 @@ for name in ("caustic", "tess"):
                                          pr, gp["rng"][:200])
     print(name, "hits", int(h["hit"].sum()), "occluded", int(o.sum()), "means", [round(float(x.mean()), 4) for x in (a, b, c, d, e, f)],
           "paths ok", bool(np.isfinite(li).all()))
+    for strat in trb.DI_STRATEGIES:
+        di, _ = ctx.render_direct(trb.render_desc(**dict(kw, rr_depth=5)), trb.direct_desc(strat, 2, 2))
+        assert np.isfinite(di).all(), strat
+    ctx.close()
+# bitmap textures: every integrator on the textured scene
+ctx = trb.Context(0)
+ctx.upload(trb.HostScene.load_npz(GOLD / "scene_textured.npz"))
+kw = dict(width=96, height=72, spp=3, rr_depth=6, wave_samples=5000)
+t1, _ = ctx.render_bdpt(trb.render_desc(**kw))
+t2, _ = ctx.render_path(trb.render_desc(**kw), trb.path_desc(True, 3, 0.95, 2, 2))
+t3, _ = ctx.render_direct(trb.render_desc(**kw), trb.direct_desc("mis", 2, 2))
+print("textured means", [round(float(x.mean()), 4) for x in (t1, t2, t3)])
+ctx.close()
