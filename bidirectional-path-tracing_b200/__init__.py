@@ -112,6 +112,13 @@ MATERIAL_DTYPE = np.dtype([("kd", "<f4", 3), ("ks", "<f4", 3), ("ke", "<f4", 3),
                            ("ni", "<f4"), ("illum", "<i4"), ("tex", "<i4")])
 assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 32 and MATERIAL_DTYPE.itemsize == C.sizeof(Material) == 64
 assert BSDF_QUERY_DTYPE.itemsize == 40 and BSDF_OUT_DTYPE.itemsize == 48
+# device scene records (csrc/host/tr_host.h), for Context.download
+DEV_NODE_DTYPE = np.dtype([("c0min", "<f4", 3), ("c0max", "<f4", 3), ("c1min", "<f4", 3), ("c1max", "<f4", 3), ("ref0", "<i4"), ("ref1", "<i4"), ("pad", "<i4", 2)])
+DEV_TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("tri", "<i4"), ("e1", "<f4", 3), ("illk", "<f4"), ("e2", "<f4", 3), ("flags", "<i4")])
+DEV_SHADE_DTYPE = np.dtype([("v0", "<f4", 3), ("shape", "<i4"), ("v1", "<f4", 3), ("prim", "<i4"), ("v2", "<f4", 3), ("mat", "<i4"),
+                            ("n0", "<f4", 3), ("emitter", "<i4"), ("n1", "<f4", 3), ("tri", "<i4"), ("n2", "<f4", 3), ("pad", "<i4")])
+DEV_TRI_UV_DTYPE = np.dtype([("st", "<f4", (3, 2)), ("pad", "<f4", 2)])
+assert DEV_NODE_DTYPE.itemsize == 64 and DEV_TRI_DTYPE.itemsize == 48 and DEV_SHADE_DTYPE.itemsize == 96 and DEV_TRI_UV_DTYPE.itemsize == 32
 
 _lib = None
 
@@ -381,10 +388,23 @@ class Context:
             raise TrbError(rc, self._L.trb_last_error(self._h).decode())
         return rc
 
-    def upload(self, scene: HostScene) -> None:
+    def upload(self, scene: HostScene, build: str = "auto") -> None:
+        """trb_scene_upload_ex: build = "auto" | "host" | "device" - where BVH::build and the triangle gather run (same result)"""
         d = scene.desc()
-        self._chk(self._L.trb_scene_upload(self._h, C.byref(d)))
+        self._chk(self._L.trb_scene_upload_ex(self._h, C.byref(d), C.c_uint32({"auto": 0, "host": 1, "device": 2}[build])))
         self.scene = scene
+
+    def built_on_device(self) -> bool:
+        return bool(self._L.trb_scene_built_on_device(self._h))
+
+    def download(self, which: str) -> np.ndarray:
+        """test hook (trb_scene_download): "nodes" | "tris" | "shade" | "tri_uv" of the device scene as structured arrays"""
+        idx, dt = {"nodes": (0, DEV_NODE_DTYPE), "tris": (1, DEV_TRI_DTYPE), "shade": (2, DEV_SHADE_DTYPE), "tri_uv": (3, DEV_TRI_UV_DTYPE)}[which]
+        n = C.c_size_t(0)
+        self._chk(self._L.trb_scene_download(self._h, idx, None, C.c_size_t(0), C.byref(n)))
+        out = np.zeros(n.value, dt)
+        self._chk(self._L.trb_scene_download(self._h, idx, _ptr(out), C.c_size_t(out.nbytes), C.byref(n)))
+        return out
 
     def refresh_scene(self) -> None:
         """host->device copy of the flattened scene from pinned memory (trb_scene_refresh)"""

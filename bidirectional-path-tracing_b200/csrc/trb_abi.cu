@@ -14,6 +14,7 @@
 #include "kernels/bdpt_kernels.cuh"
 #include "kernels/pt_kernels.cuh"
 #include "kernels/di_kernels.cuh"
+#include "kernels/bvh_build.cuh"
 #include "kernels/trace_warp.cuh"
 #include "kernels/trace_coop.cuh"
 #include "kernels/trace_sort.cuh"
@@ -56,6 +57,7 @@ struct trb_context {
     cudaDeviceProp prop{};
     // scene
     bool has_scene = false;
+    bool built_on_device = false;   // the acceleration structure and the triangle records came from kernels/bvh_build.cuh
     trb::FlatScene flat;
     DevBuf<trb::DevNode> d_nodes;
     DevBuf<trb::DevTri> d_tris;
@@ -298,46 +300,165 @@ const char* trb_build_info(void) {
 #endif
 }
 
-int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
-    if (!c || !s) return TRB_ERR_INVALID;
-    cudaSetDevice(c->device);
-    std::string err;
-    trb::FlatScene& f = c->flat;
-    if (!trb::flatten_scene(*s, f, err)) return c->fail(err.find("illum 5") != std::string::npos ? TRB_ERR_UNSUPPORTED : TRB_ERR_INVALID, err);
-    if (f.emitters.empty()) return c->fail(TRB_ERR_INVALID, "scene has no emitter (the reference divides by emitters.size())");
-    if (f.max_depth + 2 > TRB_STACK) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
-    TRB_CUDA(c, c->d_nodes.alloc(f.nodes.size())); TRB_CUDA(c, c->d_tris.alloc(f.tris.size()));
-    TRB_CUDA(c, c->d_shade.alloc(f.shade.size())); TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
-    TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
-    TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size())); TRB_CUDA(c, c->d_esphere.alloc(f.emitter_sphere.size() / 4));
-    TRB_CUDA(c, c->d_tex_info.alloc(f.tex_info.size())); TRB_CUDA(c, c->d_tri_uv.alloc(f.tri_uv.size())); TRB_CUDA(c, c->d_texels.alloc(f.texels.size()));
-    // stage everything in one pinned blob so that (re-)uploads are plain async copies from pinned memory
-    const size_t sizes[TRB_SCENE_ARRAYS] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
-                             f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
-                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
-                             f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
-                             f.tri_uv.size() * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
+}  // extern "C"
+
+namespace {
+
+void scene_array_sizes(const trb::FlatScene& f, size_t sizes[TRB_SCENE_ARRAYS]) {
+    const size_t v[TRB_SCENE_ARRAYS] = {f.n_nodes * sizeof(trb::DevNode), f.n_tris * sizeof(trb::DevTri), f.n_tris * sizeof(trb::DevShade),
+                                        f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
+                                        f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
+                                        f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
+                                        f.n_tri_uv * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
+    for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) sizes[k] = v[k];
+}
+
+// The flattened scene in ONE pinned blob, so that trb_scene_refresh is plain async copies from pinned memory.  Arrays the host
+// built are copied from their vectors; arrays the device built (kernels/bvh_build.cuh) are read back from the device.
+int stage_scene(trb_context* c) {
+    const trb::FlatScene& f = c->flat;
+    size_t sizes[TRB_SCENE_ARRAYS];
+    scene_array_sizes(f, sizes);
     const void* srcs[TRB_SCENE_ARRAYS] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(),
                                           f.emitter_cdf.data(), f.emitter_sphere.data(), f.tex_info.data(), f.tri_uv.data(), f.texels.data()};
+    const bool on_host[TRB_SCENE_ARRAYS] = {!f.nodes.empty(), !f.tris.empty(), !f.shade.empty(), true, true, true, true, true, true, !f.tri_uv.empty(), true};
+    const void* devs[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, c->d_tri_uv.p, nullptr};
     size_t total = 0;
     for (size_t b : sizes) total += (b + 255) & ~size_t(255);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
     TRB_CUDA(c, cudaMallocHost(reinterpret_cast<void**>(&c->pinned), std::max<size_t>(total, 256)));
     c->pinned_bytes = total;
     size_t off = 0;
-    {   // the staging copy (1.8 GB for 10 M triangles) on a few host threads
-        std::vector<std::thread> th;
-        for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) {
+    std::vector<std::thread> th;   // the staging copy (1.8 GB for 10 M triangles) on a few host threads
+    for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) {
+        if (sizes[k] && !on_host[k]) {
+            TRB_CUDA(c, cudaMemcpyAsync(c->pinned + off, devs[k], sizes[k], cudaMemcpyDeviceToHost, c->stream));
+        } else {
             const size_t piece = size_t(64) << 20;
             for (size_t o = 0; o < sizes[k]; o += piece) {
                 uint8_t* dst = c->pinned + off + o; const char* src = static_cast<const char*>(srcs[k]) + o; const size_t len = std::min(piece, sizes[k] - o);
                 if (sizes[k] <= piece || th.size() >= 8) std::memcpy(dst, src, len);
                 else th.emplace_back([=]() { std::memcpy(dst, src, len); });
             }
-            off += (sizes[k] + 255) & ~size_t(255);
         }
-        for (auto& t : th) t.join();
+        off += (sizes[k] + 255) & ~size_t(255);
     }
+    for (auto& t : th) t.join();
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+// BVH::build + the per-triangle records on the device (kernels/bvh_build.cuh): same arrays as trb::flatten_geometry
+int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
+    trb::FlatScene& f = c->flat;
+    const uint32_t n = uint32_t(s.n_tris);
+    DevBuf<float> d_pos, d_nrm, d_tc;
+    DevBuf<int32_t> d_tv, d_tn, d_tm, d_ts, d_sf, d_se, d_tt, ord_a, ord_b, range_of;
+    DevBuf<float4> tmin, tmax, tcen;
+    DevBuf<uint32_t> is_l, pref, counter;
+    DevBuf<BuildNode> nodes;
+    DevBuf<uint8_t> cub_tmp;
+    auto release = [&]() {
+        d_pos.release(); d_nrm.release(); d_tc.release(); d_tv.release(); d_tn.release(); d_tm.release(); d_ts.release(); d_sf.release(); d_se.release();
+        d_tt.release(); ord_a.release(); ord_b.release(); range_of.release(); tmin.release(); tmax.release(); tcen.release(); is_l.release(); pref.release();
+        counter.release(); nodes.release(); cub_tmp.release();
+    };
+    struct Guard { decltype(release)& r; ~Guard() { r(); } } guard{release};
+    auto up = [&](auto& buf, const auto* src, size_t count) -> cudaError_t {
+        cudaError_t e = buf.alloc(count);
+        if (e == cudaSuccess && count) e = cudaMemcpyAsync(buf.p, src, count * sizeof(*src), cudaMemcpyHostToDevice, c->stream);
+        return e;
+    };
+    TRB_CUDA(c, up(d_pos, s.positions, 3 * s.n_positions)); TRB_CUDA(c, up(d_nrm, s.normals, 3 * s.n_normals));
+    TRB_CUDA(c, up(d_tv, s.tri_v, 3 * size_t(n))); TRB_CUDA(c, up(d_tn, s.tri_n, 3 * size_t(n)));
+    TRB_CUDA(c, up(d_tm, s.tri_mat, size_t(n))); TRB_CUDA(c, up(d_ts, s.tri_shape, size_t(n)));
+    TRB_CUDA(c, up(d_sf, f.shape_first.data(), f.shape_first.size())); TRB_CUDA(c, up(d_se, f.shape_to_emitter.data(), f.shape_to_emitter.size()));
+    if (f.textured) { TRB_CUDA(c, up(d_tc, s.texcoords, 2 * s.n_texcoords)); TRB_CUDA(c, up(d_tt, s.tri_t, 3 * size_t(n))); }
+    TRB_CUDA(c, cudaMemcpyAsync(c->d_mats.p, f.materials.data(), f.materials.size() * sizeof(trb::DevMaterial), cudaMemcpyHostToDevice, c->stream));
+    TRB_CUDA(c, ord_a.alloc(n)); TRB_CUDA(c, ord_b.alloc(n)); TRB_CUDA(c, range_of.alloc(n));
+    TRB_CUDA(c, tmin.alloc(n)); TRB_CUDA(c, tmax.alloc(n)); TRB_CUDA(c, tcen.alloc(n));
+    TRB_CUDA(c, is_l.alloc(size_t(n) + 1)); TRB_CUDA(c, pref.alloc(size_t(n) + 1)); TRB_CUDA(c, counter.alloc(1));
+    const size_t cap = 2 * size_t(n) + 2;   // a leaf holds >= 1 triangle and the tree is binary
+    TRB_CUDA(c, nodes.alloc(cap));
+    size_t tmp_bytes = 0;
+    TRB_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, is_l.p, pref.p, int(n + 1), c->stream));
+    TRB_CUDA(c, cub_tmp.alloc(tmp_bytes));
+    BuildScene bs{d_pos.p, d_nrm.p, d_tv.p, d_tn.p, d_tm.p, d_ts.p, d_sf.p, d_se.p, c->d_mats.p, d_tc.p, d_tt.p, n};
+    const int B = 256, gN = int((size_t(n) + B - 1) / B), gN1 = int((size_t(n) + 1 + B - 1) / B);
+    auto gK = [&](int32_t count) { return std::max(1, (count + B - 1) / B); };
+    k_bb_prep<<<gN, B, 0, c->stream>>>(bs, tmin.p, tmax.p, tcen.p, ord_a.p, range_of.p);
+    k_bb_root<<<1, 1, 0, c->stream>>>(nodes.p, n, counter.p);
+    std::vector<std::pair<int32_t, int32_t>> levels;   // node id ranges in creation order
+    int32_t lb = 0, le = 1;
+    int32_t* ord = ord_a.p; int32_t* ord_next = ord_b.p;
+    while (le > lb) {
+        levels.push_back({lb, le});
+        if (levels.size() > size_t(TRB_STACK)) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
+        k_bb_bounds<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tmin.p, tmax.p, tcen.p, n);
+        k_bb_split<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le);
+        k_bb_flags<<<gN1, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tcen.p, is_l.p, n);
+        TRB_CUDA(c, cub::DeviceScan::ExclusiveSum(cub_tmp.p, tmp_bytes, is_l.p, pref.p, int(n + 1), c->stream));
+        k_bb_children<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le, pref.p, counter.p);
+        k_bb_permute<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, ord_next, range_of.p, is_l.p, pref.p, n);
+        std::swap(ord, ord_next);
+        uint32_t total = 0;
+        TRB_CUDA(c, cudaMemcpyAsync(&total, counter.p, sizeof(total), cudaMemcpyDeviceToHost, c->stream));
+        TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (size_t(total) > cap) return c->fail(TRB_ERR_CUDA, "device BVH build: node capacity exceeded");
+        lb = le; le = int32_t(total);
+    }
+    const int32_t total_nodes = le;
+    for (size_t l = levels.size(); l-- > 0;) k_bb_sizes<<<gK(levels[l].second - levels[l].first), B, 0, c->stream>>>(nodes.p, levels[l].first, levels[l].second);
+    for (size_t l = 0; l < levels.size(); ++l) k_bb_number<<<gK(levels[l].second - levels[l].first), B, 0, c->stream>>>(nodes.p, levels[l].first, levels[l].second);
+    BuildNode root;
+    TRB_CUDA(c, cudaMemcpyAsync(&root, nodes.p, sizeof(root), cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    f.n_nodes = size_t(root.sub_inner); f.n_tris = n; f.n_tri_uv = f.textured ? n : 0;
+    f.root_ref = root.left >= 0 ? 0 : ~int32_t((0u << 3) | n);
+    f.max_depth = int32_t(levels.size()) - 1;
+    f.top_nodes = 0;
+    for (int k = 0; k < 3; ++k) { f.scene_min[k] = root.bmin[k]; f.scene_max[k] = root.bmax[k]; }
+    TRB_CUDA(c, c->d_nodes.alloc(f.n_nodes)); TRB_CUDA(c, c->d_tris.alloc(n)); TRB_CUDA(c, c->d_shade.alloc(n)); TRB_CUDA(c, c->d_tri_uv.alloc(f.n_tri_uv));
+    k_bb_emit_nodes<<<gK(total_nodes), B, 0, c->stream>>>(nodes.p, total_nodes, c->d_nodes.p);
+    k_bb_emit_tris<<<gN, B, 0, c->stream>>>(bs, ord, c->d_tris.p, c->d_shade.p, f.textured ? c->d_tri_uv.p : nullptr);
+    TRB_CUDA(c, cudaGetLastError());
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int trb_scene_upload(trb_context* c, const trb_scene_desc* s) { return trb_scene_upload_ex(c, s, TRB_UPLOAD_AUTO); }
+
+int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags) {
+    if (!c || !s) return TRB_ERR_INVALID;
+    cudaSetDevice(c->device);
+    std::string err;
+    trb::FlatScene& f = c->flat;
+    c->has_scene = false;
+    auto code = [&]() { return err.find("illum 5") != std::string::npos ? TRB_ERR_UNSUPPORTED : TRB_ERR_INVALID; };
+    if (!trb::flatten_tables(*s, f, err)) return c->fail(code(), err);
+    if (f.emitters.empty()) return c->fail(TRB_ERR_INVALID, "scene has no emitter (the reference divides by emitters.size())");
+    if (s->n_tris == 0) return c->fail(TRB_ERR_INVALID, "empty scene");
+    if (s->n_tris >= (size_t(1) << 27)) return c->fail(TRB_ERR_UNSUPPORTED, "more than 2^27 triangles");   // (owner lane << 27 | position) queue words
+    const bool on_device = flags == TRB_UPLOAD_DEVICE_BUILD || (flags == TRB_UPLOAD_AUTO && s->n_tris >= TRB_DEVICE_BUILD_MIN_TRIS);
+    TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
+    TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));
+    TRB_CUDA(c, c->d_cdf.alloc(f.emitter_cdf.size())); TRB_CUDA(c, c->d_esphere.alloc(f.emitter_sphere.size() / 4));
+    TRB_CUDA(c, c->d_tex_info.alloc(f.tex_info.size())); TRB_CUDA(c, c->d_texels.alloc(f.texels.size()));
+    if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
+    if (on_device) {
+        int rc = build_geometry_on_device(c, *s);
+        if (rc) return rc;
+    } else {
+        if (!trb::flatten_geometry(*s, f, err)) return c->fail(code(), err);
+        TRB_CUDA(c, c->d_nodes.alloc(f.n_nodes)); TRB_CUDA(c, c->d_tris.alloc(f.n_tris));
+        TRB_CUDA(c, c->d_shade.alloc(f.n_tris)); TRB_CUDA(c, c->d_tri_uv.alloc(f.n_tri_uv));
+    }
+    if (f.max_depth + 2 > TRB_STACK) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
+    c->built_on_device = on_device;
     c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
     c->sc.tris = reinterpret_cast<const F4*>(c->d_tris.p);
     c->sc.shade = c->d_shade.p; c->sc.mats = c->d_mats.p; c->sc.emitters = c->d_emitters.p; c->sc.etris = c->d_etris.p;
@@ -345,21 +466,32 @@ int trb_scene_upload(trb_context* c, const trb_scene_desc* s) {
     c->sc.texels = c->d_texels.p; c->sc.has_tex = f.tex_info.empty() ? 0 : 1;
     c->sc.cdf = c->d_cdf.p; c->sc.esphere = c->d_esphere.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
     c->has_scene = true;
+    if (on_device) {
+        // the tables go up directly; the pinned staging blob (geometry read back from the device) is made by the first trb_scene_refresh
+        size_t sizes[TRB_SCENE_ARRAYS];
+        scene_array_sizes(f, sizes);
+        void* dsts[TRB_SCENE_ARRAYS] = {nullptr, nullptr, nullptr, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p, c->d_tex_info.p, nullptr, c->d_texels.p};
+        const void* srcs[TRB_SCENE_ARRAYS] = {nullptr, nullptr, nullptr, f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data(),
+                                              f.emitter_sphere.data(), f.tex_info.data(), nullptr, f.texels.data()};
+        for (int k = 0; k < TRB_SCENE_ARRAYS; ++k)
+            if (dsts[k] && sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], srcs[k], sizes[k], cudaMemcpyHostToDevice, c->stream));
+        TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+        return TRB_OK;
+    }
+    int rc = stage_scene(c);
+    if (rc) return rc;
     return trb_scene_refresh(c);
 }
 
 int trb_scene_refresh(trb_context* c) {
     if (!c) return TRB_ERR_INVALID;
-    if (!c->has_scene || !c->pinned) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     cudaSetDevice(c->device);
+    if (!c->pinned) { int rc = stage_scene(c); if (rc) return rc; }
     void* dsts[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p,
                                     c->d_tex_info.p, c->d_tri_uv.p, c->d_texels.p};
-    const trb::FlatScene& f = c->flat;
-    const size_t sizes[TRB_SCENE_ARRAYS] = {f.nodes.size() * sizeof(trb::DevNode), f.tris.size() * sizeof(trb::DevTri), f.shade.size() * sizeof(trb::DevShade),
-                             f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
-                             f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
-                             f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
-                             f.tri_uv.size() * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
+    size_t sizes[TRB_SCENE_ARRAYS];
+    scene_array_sizes(c->flat, sizes);
     size_t off = 0;
     for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) {
         if (sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], c->pinned + off, sizes[k], cudaMemcpyHostToDevice, c->stream));
@@ -368,6 +500,26 @@ int trb_scene_refresh(trb_context* c) {
     TRB_CUDA(c, cudaStreamSynchronize(c->stream));
     return TRB_OK;
 }
+
+/* Test hook: the device scene's geometry arrays read back (nodes, triangles, shading records) so that a device-built scene can be
+ * compared with a host-built one. which: 0 nodes (64 B), 1 triangles (48 B), 2 shading records (96 B), 3 texture coordinates (32 B). */
+int trb_scene_download(trb_context* c, int which, void* out, size_t capacity_bytes, size_t* count_out) {
+    if (!c) return TRB_ERR_INVALID;
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    cudaSetDevice(c->device);
+    const trb::FlatScene& f = c->flat;
+    const void* src[4] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_tri_uv.p};
+    const size_t cnt[4] = {f.n_nodes, f.n_tris, f.n_tris, f.n_tri_uv}, rec[4] = {sizeof(trb::DevNode), sizeof(trb::DevTri), sizeof(trb::DevShade), sizeof(trb::DevTriUV)};
+    if (which < 0 || which > 3) return c->fail(TRB_ERR_INVALID, "trb_scene_download: which must be 0..3");
+    if (count_out) *count_out = cnt[which];
+    if (!out) return TRB_OK;
+    if (capacity_bytes < cnt[which] * rec[which]) return c->fail(TRB_ERR_INVALID, "trb_scene_download: buffer too small");
+    if (cnt[which]) TRB_CUDA(c, cudaMemcpyAsync(out, src[which], cnt[which] * rec[which], cudaMemcpyDeviceToHost, c->stream));
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}
+
+int trb_scene_built_on_device(const trb_context* c) { return (c && c->has_scene && c->built_on_device) ? 1 : 0; }
 
 size_t trb_scene_device_bytes(const trb_context* c) { return (c && c->has_scene) ? c->flat.bytes() : 0; }
 

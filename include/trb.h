@@ -247,7 +247,19 @@ const char* trb_last_error(const trb_context*);
 
 /* Scene::load's tail + AcceleratorBVH::build (renderer.cpp:259-312, accel.h:115-123): derives BSDF
  * parameters, emitters and the BVH on the host and uploads the flattened scene. */
-int trb_scene_upload(trb_context*, const trb_scene_desc*);
+int trb_scene_upload(trb_context*, const trb_scene_desc*);   /* = trb_scene_upload_ex(.., TRB_UPLOAD_AUTO) */
+/* The same with the place of BVH::build chosen.  The device build (csrc/kernels/bvh_build.cuh) produces the
+ * reference's exact tree and primitive order one level at a time, then gathers the triangle records on the device; the host
+ * build does it on the host cores.  Both give the same device scene (tests compare them through trb_scene_download). */
+#define TRB_UPLOAD_AUTO 0u          /* device build from TRB_DEVICE_BUILD_MIN_TRIS triangles on, host build below */
+#define TRB_UPLOAD_HOST_BUILD 1u
+#define TRB_UPLOAD_DEVICE_BUILD 2u
+#define TRB_DEVICE_BUILD_MIN_TRIS 65536u
+int trb_scene_upload_ex(trb_context*, const trb_scene_desc*, uint32_t flags);
+int trb_scene_built_on_device(const trb_context*);
+/* Test hook: geometry arrays of the device scene read back. which: 0 nodes (64 B records), 1 triangles (48 B), 2 shading records
+ * (96 B), 3 texture coordinates (32 B).  out may be NULL to query the count. */
+int trb_scene_download(trb_context*, int which, void* out, size_t capacity_bytes, size_t* count_out);
 /* Copies the already flattened scene (kept in pinned host memory by trb_scene_upload) to the device again:
  * the per-frame host->device transfer of an end-to-end render without redoing the host-side BVH build. */
 int trb_scene_refresh(trb_context*);
