@@ -12,8 +12,11 @@
 //     j = i - f, the sequence of tail insertions is  P[j] = a[f + j]  if a[f + j] goes right,  else  P[h(j)],
 //     h(j) = number of left-hand elements in (f, f + j)  (< j: the queue head at that moment), and the right-hand part is
 //     P[H .. end - f), H = number of left-hand elements after f.  h comes from ONE prefix sum of the left/right flags over the
-//     whole array; a destination resolves its source by following h until it lands on a right-hand element (the index at
-//     least halves per step when half the elements go left).
+//     whole array; a destination resolves its source by following h until it lands on a right-hand element.  One step moves
+//     the position back by r = the number of right-hand elements before it, which is constant inside a RUN of left-hand
+//     elements, so the steps of a run are taken at once (the run's start comes from a running maximum of the right-hand
+//     positions, a second scan): a mesh split across its rows gives runs of a whole row - thousands of single steps, a handful
+//     of run jumps.
 // Per level: bounds of every range (warp-aggregated float atomics; min / max are order-independent), split decision, flags,
 // prefix sum (CUB), children, permutation.  Then subtree sizes bottom-up, pre-order numbers top-down, the 64 B two-child
 // nodes and the per-triangle records gathered in the final order.  All arithmetic as the host build does it (fp32, no FMA).
@@ -47,11 +50,15 @@ struct BuildScene {   // raw scene arrays on the device (what trb_scene_desc poi
     uint32_t n;
 };
 
-// float min / max through integer atomics: exact, order-independent (a -0 / +0 tie may keep either zero; they compare equal)
+// float min / max through integer atomics: exact, order-independent (a -0 / +0 tie may keep either zero; they compare equal).
+// The value is read first (from L2; a stale read only costs a needless atomic, min / max are monotone): after the first few
+// elements of a range almost none moves its bounds, so almost no atomic is issued.
 __device__ __forceinline__ void atomic_min_f(float* a, float v) {
+    if (!(v < __ldcg(a))) return;
     if (v >= 0.f) atomicMin(reinterpret_cast<int*>(a), __float_as_int(v)); else atomicMax(reinterpret_cast<unsigned*>(a), __float_as_uint(v));
 }
 __device__ __forceinline__ void atomic_max_f(float* a, float v) {
+    if (!(v > __ldcg(a))) return;
     if (v >= 0.f) atomicMax(reinterpret_cast<int*>(a), __float_as_int(v)); else atomicMin(reinterpret_cast<unsigned*>(a), __float_as_uint(v));
 }
 
@@ -127,7 +134,7 @@ __global__ void k_bb_split(BuildNode* __restrict__ nodes, int32_t lb, int32_t le
 }
 
 __global__ void k_bb_flags(BuildNode* __restrict__ nodes, int32_t lb, const int32_t* __restrict__ ord, const int32_t* __restrict__ range_of,
-                           const float4* __restrict__ tcen, uint32_t* __restrict__ is_l, uint32_t n) {
+                           const float4* __restrict__ tcen, uint32_t* __restrict__ is_l, uint32_t* __restrict__ r_pos, uint32_t n) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i > n) return;
     uint32_t l = 0;
@@ -139,11 +146,12 @@ __global__ void k_bb_flags(BuildNode* __restrict__ nodes, int32_t lb, const int3
                 const float4 c = tcen[ord[i]];
                 const float x = dim == 0 ? c.x : (dim == 1 ? c.y : c.z);
                 l = x < nodes[node].split ? 1u : 0u;
-                if (!l) atomicMin(&nodes[node].first_r, i);
+                if (!l && i < __ldcg(&nodes[node].first_r)) atomicMin(&nodes[node].first_r, i);
             }
         }
     }
     is_l[i] = l;   // entry n is a zero so that the exclusive sum has n + 1 entries
+    r_pos[i] = l ? 0u : i;   // running maximum = the nearest right-hand (or inactive) position at or before i
 }
 
 // mid (with the median-index fallback of bvh.h:216-218) and the two children (bvh.h:221-227)
@@ -163,7 +171,8 @@ __global__ void k_bb_children(BuildNode* __restrict__ nodes, int32_t lb, int32_t
 
 // the order the reference's swap loop leaves (see the file header), and the range each position belongs to on the next level
 __global__ void k_bb_permute(const BuildNode* __restrict__ nodes, int32_t lb, const int32_t* __restrict__ ord, int32_t* __restrict__ ord_next,
-                             int32_t* __restrict__ range_of, const uint32_t* __restrict__ is_l, const uint32_t* __restrict__ pref, uint32_t n) {
+                             int32_t* __restrict__ range_of, const uint32_t* __restrict__ is_l, const uint32_t* __restrict__ pref,
+                             const uint32_t* __restrict__ last_r, uint32_t n) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int32_t node = range_of[i];
@@ -176,7 +185,11 @@ __global__ void k_bb_permute(const BuildNode* __restrict__ nodes, int32_t lb, co
         const uint32_t f = nd.first_r, pf = pref[f];
         const uint32_t H = pref[nd.end] - pf;
         uint32_t pos = f + H + (i - nd.mid);
-        while (is_l[pos]) pos = f + (pref[pos] - pf);
+        while (is_l[pos]) {
+            const uint32_t r = (pos - f) - (pref[pos] - pf);   // right-hand elements in [f, pos): one step is pos -= r
+            const uint32_t b = last_r[pos] + 1u;               // first position of this run of left-hand elements
+            pos -= ((pos - b) / r + 1u) * r;                   // all the steps that stay inside the run, and the one that leaves it
+        }
         ord_next[i] = ord[pos];
     }
 }

@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <chrono>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -351,16 +353,25 @@ int stage_scene(trb_context* c) {
 // BVH::build + the per-triangle records on the device (kernels/bvh_build.cuh): same arrays as trb::flatten_geometry
 int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     trb::FlatScene& f = c->flat;
+    const bool timing = std::getenv("TRB_BUILD_TIMING") != nullptr;
+    auto t_prev = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        cudaStreamSynchronize(c->stream);
+        auto now = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[trb build] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(now - t_prev).count());
+        t_prev = now;
+    };
     const uint32_t n = uint32_t(s.n_tris);
     DevBuf<float> d_pos, d_nrm, d_tc;
     DevBuf<int32_t> d_tv, d_tn, d_tm, d_ts, d_sf, d_se, d_tt, ord_a, ord_b, range_of;
     DevBuf<float4> tmin, tmax, tcen;
-    DevBuf<uint32_t> is_l, pref, counter;
+    DevBuf<uint32_t> is_l, pref, r_pos, last_r, counter;
     DevBuf<BuildNode> nodes;
     DevBuf<uint8_t> cub_tmp;
     auto release = [&]() {
         d_pos.release(); d_nrm.release(); d_tc.release(); d_tv.release(); d_tn.release(); d_tm.release(); d_ts.release(); d_sf.release(); d_se.release();
-        d_tt.release(); ord_a.release(); ord_b.release(); range_of.release(); tmin.release(); tmax.release(); tcen.release(); is_l.release(); pref.release();
+        d_tt.release(); ord_a.release(); ord_b.release(); range_of.release(); tmin.release(); tmax.release(); tcen.release(); is_l.release(); pref.release(); r_pos.release(); last_r.release();
         counter.release(); nodes.release(); cub_tmp.release();
     };
     struct Guard { decltype(release)& r; ~Guard() { r(); } } guard{release};
@@ -375,14 +386,20 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     TRB_CUDA(c, up(d_sf, f.shape_first.data(), f.shape_first.size())); TRB_CUDA(c, up(d_se, f.shape_to_emitter.data(), f.shape_to_emitter.size()));
     if (f.textured) { TRB_CUDA(c, up(d_tc, s.texcoords, 2 * s.n_texcoords)); TRB_CUDA(c, up(d_tt, s.tri_t, 3 * size_t(n))); }
     TRB_CUDA(c, cudaMemcpyAsync(c->d_mats.p, f.materials.data(), f.materials.size() * sizeof(trb::DevMaterial), cudaMemcpyHostToDevice, c->stream));
+    lap("raw arrays to the device");
     TRB_CUDA(c, ord_a.alloc(n)); TRB_CUDA(c, ord_b.alloc(n)); TRB_CUDA(c, range_of.alloc(n));
     TRB_CUDA(c, tmin.alloc(n)); TRB_CUDA(c, tmax.alloc(n)); TRB_CUDA(c, tcen.alloc(n));
     TRB_CUDA(c, is_l.alloc(size_t(n) + 1)); TRB_CUDA(c, pref.alloc(size_t(n) + 1)); TRB_CUDA(c, counter.alloc(1));
+    TRB_CUDA(c, r_pos.alloc(size_t(n) + 1)); TRB_CUDA(c, last_r.alloc(size_t(n) + 1));
     const size_t cap = 2 * size_t(n) + 2;   // a leaf holds >= 1 triangle and the tree is binary
     TRB_CUDA(c, nodes.alloc(cap));
     size_t tmp_bytes = 0;
+    size_t tmp_bytes2 = 0;
     TRB_CUDA(c, cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, is_l.p, pref.p, int(n + 1), c->stream));
+    TRB_CUDA(c, cub::DeviceScan::InclusiveScan(nullptr, tmp_bytes2, r_pos.p, last_r.p, cub::Max(), int(n + 1), c->stream));
+    tmp_bytes = std::max(tmp_bytes, tmp_bytes2);
     TRB_CUDA(c, cub_tmp.alloc(tmp_bytes));
+    lap("scratch allocation");
     BuildScene bs{d_pos.p, d_nrm.p, d_tv.p, d_tn.p, d_tm.p, d_ts.p, d_sf.p, d_se.p, c->d_mats.p, d_tc.p, d_tt.p, n};
     const int B = 256, gN = int((size_t(n) + B - 1) / B), gN1 = int((size_t(n) + 1 + B - 1) / B);
     auto gK = [&](int32_t count) { return std::max(1, (count + B - 1) / B); };
@@ -391,15 +408,24 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     std::vector<std::pair<int32_t, int32_t>> levels;   // node id ranges in creation order
     int32_t lb = 0, le = 1;
     int32_t* ord = ord_a.p; int32_t* ord_next = ord_b.p;
+    double kind_ms[6] = {0, 0, 0, 0, 0, 0};
+    auto klap = [&](int kind) {   // TRB_BUILD_TIMING only: per-kernel-kind time summed over the levels (serialises the loop)
+        if (!timing) return;
+        cudaStreamSynchronize(c->stream);
+        auto now = std::chrono::steady_clock::now();
+        kind_ms[kind] += std::chrono::duration<double, std::milli>(now - t_prev).count();
+        t_prev = now;
+    };
     while (le > lb) {
         levels.push_back({lb, le});
         if (levels.size() > size_t(TRB_STACK)) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
-        k_bb_bounds<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tmin.p, tmax.p, tcen.p, n);
-        k_bb_split<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le);
-        k_bb_flags<<<gN1, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tcen.p, is_l.p, n);
+        k_bb_bounds<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tmin.p, tmax.p, tcen.p, n); klap(0);
+        k_bb_split<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le); klap(1);
+        k_bb_flags<<<gN1, B, 0, c->stream>>>(nodes.p, lb, ord, range_of.p, tcen.p, is_l.p, r_pos.p, n); klap(2);
         TRB_CUDA(c, cub::DeviceScan::ExclusiveSum(cub_tmp.p, tmp_bytes, is_l.p, pref.p, int(n + 1), c->stream));
-        k_bb_children<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le, pref.p, counter.p);
-        k_bb_permute<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, ord_next, range_of.p, is_l.p, pref.p, n);
+        TRB_CUDA(c, cub::DeviceScan::InclusiveScan(cub_tmp.p, tmp_bytes, r_pos.p, last_r.p, cub::Max(), int(n + 1), c->stream)); klap(3);
+        k_bb_children<<<gK(le - lb), B, 0, c->stream>>>(nodes.p, lb, le, pref.p, counter.p); klap(4);
+        k_bb_permute<<<gN, B, 0, c->stream>>>(nodes.p, lb, ord, ord_next, range_of.p, is_l.p, pref.p, last_r.p, n); klap(5);
         std::swap(ord, ord_next);
         uint32_t total = 0;
         TRB_CUDA(c, cudaMemcpyAsync(&total, counter.p, sizeof(total), cudaMemcpyDeviceToHost, c->stream));
@@ -408,6 +434,9 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
         lb = le; le = int32_t(total);
     }
     const int32_t total_nodes = le;
+    if (timing) std::fprintf(stderr, "[trb build] levels: bounds %.1f split %.1f flags %.1f scan %.1f children %.1f permute %.1f ms\n", kind_ms[0], kind_ms[1],
+                             kind_ms[2], kind_ms[3], kind_ms[4], kind_ms[5]);
+    lap("levels (tail)");
     for (size_t l = levels.size(); l-- > 0;) k_bb_sizes<<<gK(levels[l].second - levels[l].first), B, 0, c->stream>>>(nodes.p, levels[l].first, levels[l].second);
     for (size_t l = 0; l < levels.size(); ++l) k_bb_number<<<gK(levels[l].second - levels[l].first), B, 0, c->stream>>>(nodes.p, levels[l].first, levels[l].second);
     BuildNode root;
@@ -423,6 +452,8 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     k_bb_emit_tris<<<gN, B, 0, c->stream>>>(bs, ord, c->d_tris.p, c->d_shade.p, f.textured ? c->d_tri_uv.p : nullptr);
     TRB_CUDA(c, cudaGetLastError());
     TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    lap("numbering + emit");
+    if (timing) std::fprintf(stderr, "[trb build] %d levels, %d nodes (%zu inner)\n", int(levels.size()), total_nodes, f.n_nodes);
     return TRB_OK;
 }
 
@@ -439,7 +470,9 @@ int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags)
     trb::FlatScene& f = c->flat;
     c->has_scene = false;
     auto code = [&]() { return err.find("illum 5") != std::string::npos ? TRB_ERR_UNSUPPORTED : TRB_ERR_INVALID; };
+    const auto t_up0 = std::chrono::steady_clock::now();
     if (!trb::flatten_tables(*s, f, err)) return c->fail(code(), err);
+    if (std::getenv("TRB_BUILD_TIMING")) std::fprintf(stderr, "[trb build] %-28s %8.2f ms\n", "host tables + validation", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_up0).count());
     if (f.emitters.empty()) return c->fail(TRB_ERR_INVALID, "scene has no emitter (the reference divides by emitters.size())");
     if (s->n_tris == 0) return c->fail(TRB_ERR_INVALID, "empty scene");
     if (s->n_tris >= (size_t(1) << 27)) return c->fail(TRB_ERR_UNSUPPORTED, "more than 2^27 triangles");   // (owner lane << 27 | position) queue words
