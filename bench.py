@@ -268,7 +268,9 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     scene = load_scene(trb, wl)
     ctx = trb.Context(local)
-    ctx.upload(scene)
+    t_up = time.perf_counter()
+    ctx.upload(scene)   # trb_scene_upload: BVH::build on the device from 65536 triangles on, on the host cores below
+    upload_info = {"seconds": round(time.perf_counter() - t_up, 3), "triangles": int(scene.n_tris), "built_on": "device" if ctx.built_on_device() else "host"}
     W, H = wl["width"], wl["height"]
     total_spp = args.spp * world
     s_begin, s_end = par.sample_range(total_spp, rank, world)  # shard by sample index
@@ -349,6 +351,7 @@ def run_ours(args):
                           "partition": f"sample index, {world} rank(s), one NCCL reduce of the {W}x{H}x3 float frame buffer per step",
                           "l2": "384 MB buffer written between timed steps (L2 flush); wave buffers (>1 GB) exceed the 126 MB L2"},
                "clocks": clk, "gpu_launches": int(agg.get("launches", 0)),
+               "scene_upload": upload_info,
                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(ctx.scene_bytes()), "d2h_bytes_per_step": W * H * 3 * 4,
                        "steps": e2e_steps, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (host frame buffer out)"},
                "mrays_per_s": {"closest": agg["rays_closest"] / (tot_ms * 1e-3) / 1e6, "any": agg["rays_any"] / (tot_ms * 1e-3) / 1e6,
