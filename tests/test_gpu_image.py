@@ -139,6 +139,15 @@ def test_in_library_multi_gpu_render(trb, gpu_ctx):
     one, _ = ctxs[0].render_path(trb.render_desc(width=320, height=240, spp=8, rr_depth=5), pd)
     two, _ = trb.render_path_multi(ctxs, trb.render_desc(width=320, height=240, spp=8, rr_depth=5), pd)
     assert np.allclose(one, two, rtol=2e-5, atol=2e-6), float(np.abs(one - two).max())
+    dd = trb.direct_desc("mis", 2, 2)
+    one, _ = ctxs[0].render_direct(trb.render_desc(width=320, height=240, spp=8), dd)
+    two, _ = trb.render_direct_multi(ctxs, trb.render_desc(width=320, height=240, spp=8), dd)
+    assert np.allclose(one, two, rtol=2e-5, atol=2e-6), float(np.abs(one - two).max())
+    # a scene built on the second device by the device BVH build serves the same frame
+    ctxs[1].upload(scene, build="device")
+    two, _ = trb.render_bdpt_multi(ctxs, desc)
+    one, _ = ctxs[0].render_bdpt(desc)
+    assert np.allclose(one, two, rtol=2e-5, atol=2e-6)
     ctxs[1].close()
     # and through the host surface: `gpus = 2` in the TOML
     cv2 = pytest.importorskip("cv2")
