@@ -193,6 +193,23 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
 // left with the hit triangle (DevTri.flags: class | emissive << 3; 15 = no valid hit), so that most warps of the block
 // see ONE class (ncu before: 16 active threads per instruction in k_light_bounce, 3 on the Phong-lobe powf).
 #define TRB_SORT_BLOCK 256
+// Launch bounds of the bounce / connect kernels.  The bounce kernels wait on scattered per-slot state (ncu r1o: long scoreboard,
+// 23-35 % occupancy), so resident warps count for more than a few spilled registers: capping k_eye_bounce for 3 blocks per SM
+// (92 -> 80 registers) and k_light_bounce for 4 (78 -> 64) takes the logic share of a caustic step from 35.2 to 31.6 ms.  Tighter
+// caps (eye 64, light 48, connect 72 / 64) and no cap at all (94 / 86 / 94) are slower (profiles/r1o_ncu_logic_summary.md).
+#ifndef TRB_LB_MINB
+#define TRB_LB_MINB 4
+#endif
+#ifndef TRB_EB_MINB
+#define TRB_EB_MINB 3
+#endif
+#define TRB_LB_BOUNDS __launch_bounds__(TRB_SORT_BLOCK, TRB_LB_MINB)
+#define TRB_EB_BOUNDS __launch_bounds__(TRB_SORT_BLOCK, TRB_EB_MINB)
+#ifdef TRB_CV_MINB
+#define TRB_CV_BOUNDS __launch_bounds__(TRB_BLOCK, TRB_CV_MINB)
+#else
+#define TRB_CV_BOUNDS __launch_bounds__(TRB_BLOCK)
+#endif
 #ifndef TRB_MATSORT
 #define TRB_MATSORT 0
 #endif
@@ -226,7 +243,7 @@ __device__ __forceinline__ int block_sort_slot(const WaveParams& p, uint32_t k, 
 }
 
 // ---- one light bounce (body of the loop at bdpt.h:188-216) -------------------------------------------------
-__global__ void __launch_bounds__(TRB_SORT_BLOCK) k_light_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
+__global__ void TRB_LB_BOUNDS k_light_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
     uint32_t n = *n_in;
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x * blockDim.x >= n) return;  // block-uniform
@@ -322,7 +339,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ 
 }
 
 // ---- one eye bounce (body of the loop at bdpt.h:68-154) --------------------------------------------------------
-__global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
+__global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
     uint32_t n = *n_in;
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x * blockDim.x >= n) return;  // block-uniform
@@ -459,7 +476,7 @@ __global__ void __launch_bounds__(TRB_SORT_BLOCK) k_eye_bounce(const __grid_cons
 // Replaces the per-thread loop over the sample's light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). ----
 // TEX: the scene has bitmap textures (their lookup is compiled out of the untextured instance, which every shipped scene runs)
 template <bool TEX>
-__global__ void __launch_bounds__(TRB_BLOCK) k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_pairs_ptr) {
+__global__ void TRB_CV_BOUNDS k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_pairs_ptr) {
     const unsigned long long total = *n_pairs_ptr;
     const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballot of push_shadow
     const float li_scale = p.parity ? 1.f : (1.f / p.spp);
