@@ -192,7 +192,9 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
 // Before doing so, the TRB_SORT_BLOCK slots of a block are counting-sorted in shared memory by the key the traversal
 // left with the hit triangle (DevTri.flags: class | emissive << 3; 15 = no valid hit), so that most warps of the block
 // see ONE class (ncu before: 16 active threads per instruction in k_light_bounce, 3 on the Phong-lobe powf).
+#ifndef TRB_SORT_BLOCK
 #define TRB_SORT_BLOCK 256
+#endif
 // Launch bounds of the bounce / connect kernels.  The bounce kernels wait on scattered per-slot state (ncu r1o: long scoreboard,
 // 23-35 % occupancy), so resident warps count for more than a few spilled registers: capping k_eye_bounce for 3 blocks per SM
 // (92 -> 80 registers) and k_light_bounce for 4 (78 -> 64) takes the logic share of a caustic step from 35.2 to 31.6 ms.  Tighter
