@@ -259,11 +259,11 @@ __global__ void TRB_LB_BOUNDS k_light_bounce(const __grid_constant__ WaveParams 
         r = p.ray[slot];
         HitT h = p.hit[slot];
         sv = p.st_v[slot];
+        const float4 st = p.st_t[slot];  // read with the other per-slot records, not behind the triangle and material fetches
         if (hit_valid(h, r)) {
             alive = true;
             s = make_surf(p.sc, h, r);
             m = load_mat_at(p.sc, s.mat, h);
-            float4 st = p.st_t[slot];
             T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
             const float distSquared = s.t * s.t;
             const float absCosIn = fabsf(s.wo.z);
@@ -357,6 +357,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
         RayT r = p.ray[slot];
         HitT h = p.hit[slot];
         sv = p.st_v[slot];
+        const float4 st = p.st_t[slot];  // read with the other per-slot records, not behind the triangle and material fetches
         slot_ids(p, slot, &pixel, &sample);
         li_target = p.parity ? uint32_t(slot) * uint32_t(p.K + 1) : pixel;
         rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
@@ -364,7 +365,6 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
             alive = true;
             s = make_surf(p.sc, h, r);
             m = load_mat_at(p.sc, s.mat, h);
-            float4 st = p.st_t[slot];
             T = mk(st.x, st.y, st.z); vcm = st.w; vc = sv.x;
             const float distSquared = s.t * s.t;
             const float absCosIn = fabsf(s.wo.z);
