@@ -146,8 +146,9 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
 #if TRB_COOP
-    static const bool attr = (cudaFuncSetAttribute(k_trace_coop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64), true);
-    (void)attr;
+#if TRB_TOP > 0   // experiment only (compiled out): the attribute is per device, so it is set on every launch's current device
+    cudaFuncSetAttribute(k_trace_coop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64);
+#endif
     k_trace_coop<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, c->stream>>>(a);
 #else
     k_trace_warp<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
@@ -163,8 +164,9 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
 #if TRB_COOP
-    static const bool attr = (cudaFuncSetAttribute(k_trace_coop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64), true);
-    (void)attr;
+#if TRB_TOP > 0   // experiment only (compiled out): the attribute is per device, so it is set on every launch's current device
+    cudaFuncSetAttribute(k_trace_coop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64);
+#endif
     k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, stream>>>(a);
 #else
     k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
