@@ -47,3 +47,31 @@ def gpu_ctx(trb):
             _ctx_cache[name] = ctx
         return _ctx_cache[name]
     return get
+
+
+_parity_counts = {}
+
+
+@pytest.fixture(scope="session")
+def parity_record():
+    """record(config, agree, total, **extra): the measured agreement counts of the parity tests, written at the end of the session to
+    profiles/parity_counts.json (and gpurun_out/, which is what travels back from the GPU box) - the driver runs pytest with -q, so
+    printed counts would be lost."""
+    def record(config, agree, total, **extra):
+        _parity_counts[config] = dict(agree=int(agree), total=int(total), **extra)
+    return record
+
+
+def pytest_sessionfinish(session, exitstatus):
+    if not _parity_counts:
+        return
+    import json
+    for d in (ROOT / "profiles", ROOT / "gpurun_out"):
+        try:
+            d.mkdir(exist_ok=True)
+            f = d / "parity_counts.json"
+            old = json.loads(f.read_text()) if f.exists() else {}
+            old.update(_parity_counts)
+            f.write_text(json.dumps(old, indent=1, sort_keys=True) + "\n")
+        except OSError:
+            pass

@@ -129,7 +129,7 @@ def _paths_agree(g_li, g_pix, g_rgb, li, pix, rgb):
     return ok
 
 
-def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
+def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, parity_record, scene_name):
     g = gold("paths", scene_name)
     desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
     li, pix, rgb, draws = gpu_ctx(scene_name).bdpt_paths(desc, _rays(trb, g["rays"]), g["rng"])
@@ -141,12 +141,13 @@ def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, scene_name):
     frac = ok.mean()
     draws_same = (draws == g["draws"])
     print(f"{scene_name}: paths ok {ok.sum()}/{n}, draws identical {draws_same.sum()}/{n}")
+    parity_record(f"bdpt_paths_golden/{scene_name}/96x72/rrDepth{int(g['rr_depth'])}", (ok & draws_same).sum(), n)
     assert frac >= 0.99, f"only {frac:.4f} of paths within {REL}"
     assert draws_same[ok].all()
 
 
 @pytest.mark.parametrize("rr_depth", [1, 2, 3])
-def test_bdpt_paths_at_the_smallest_depths(trb, gpu_ctx, gold, scene_name, rr_depth):
+def test_bdpt_paths_at_the_smallest_depths(trb, gpu_ctx, gold, parity_record, scene_name, rr_depth):
     """rrDepth 1 (no vertex at all: only the loop tests' draws, Q3), 2 (the shipped cbox_bdpt.toml: one vertex per subpath) and 3,
     against the restatement (pinned bit-exact to the reference) on the golden rays and random streams: Li, splats, draws"""
     oracle_port = pytest.importorskip("oracle_port")
@@ -162,6 +163,7 @@ def test_bdpt_paths_at_the_smallest_depths(trb, gpu_ctx, gold, scene_name, rr_de
     li, pix, rgb, draws = gpu_ctx(scene_name).bdpt_paths(desc, _rays(trb, g["rays"][:n]), g["rng"][:n])
     ok = _paths_agree(c_li, c_pix, c_rgb, li, pix, rgb) & (draws == c_draws)
     print(f"{scene_name} rrDepth {rr_depth}: {ok.sum()}/{n} agree, mean draws {draws.mean():.2f}")
+    parity_record(f"bdpt_paths/{scene_name}/96x72/rrDepth{rr_depth}", ok.sum(), n, checker="restatement")
     assert ok.mean() >= 0.99
     if rr_depth == 1:
         assert not li.any() and (pix < 0).all()      # nothing is ever connected
@@ -191,7 +193,7 @@ def test_edge_configurations_render(trb, gpu_ctx):
         ctx.render_path(d, trb.path_desc(True, 2, 0.95, 17, 0))
 
 
-def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, scene_name):
+def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, parity_record, scene_name):
     """TRB_FLAG_RUSSIAN_ROULETTE against the reference built with its own Russian-roulette code enabled (NO_RR 0,
     tools/gen_golden_rr.py).  The reference's walks are unbounded; the device caps them at max_depth, so the walks
     the cap cuts short are compared with the restatement run with the same cap (pinned bit-exact to the reference
@@ -223,13 +225,15 @@ def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, scene_name):
     ok_cap = _paths_agree(c_li, c_pix, c_rgb, li, pix, rgb) & (draws == c_draws)
     print(f"{scene_name} RR: vs reference {ok_ref[untouched].sum()}/{untouched.sum()} untouched walks, vs capped restatement {ok_cap.sum()}/{n}; "
           f"mean draws {draws.mean():.1f}, splat columns used {int((pix >= 0).sum(1).max())} (reference {kk})")
+    parity_record(f"bdpt_paths_rr/{scene_name}/vs_reference_uncapped_walks", ok_ref[untouched].sum(), untouched.sum())
+    parity_record(f"bdpt_paths_rr/{scene_name}/vs_capped_restatement", ok_cap.sum(), n, checker="restatement")
     assert ok_ref[untouched].mean() >= 0.99
     assert ok_cap.mean() >= 0.99
     assert draws.mean() > 45  # the walks do run past rr_depth
 
 
 @pytest.mark.parametrize("config", ["rr", "mis", "implicit"])
-def test_path_tracer_paths_match_reference(trb, gpu_ctx, gold, scene_name, config):
+def test_path_tracer_paths_match_reference(trb, gpu_ctx, gold, parity_record, scene_name, config):
     """the path tracer on the wavefront (trb_path_paths) against whole samples of the unmodified reference's
     PathTracerIntegrator::render under identical injected random numbers: Li within 1e-5 relative and the same number of draws
     (= the same sequence of decisions, re-sampling loops included) for >= 99 % of the paths.  Walks longer than the device's
@@ -258,6 +262,7 @@ def test_path_tracer_paths_match_reference(trb, gpu_ctx, gold, scene_name, confi
     ok = (np.abs(li - ref_li) <= REL * np.maximum(scale, np.abs(li))).all(1) & (draws == ref_draws)
     print(f"{scene_name}/{config}: {ok.sum()}/{len(ok)} paths agree; mean draws {draws.mean():.1f} (reference {g['draws'].mean():.1f}); "
           f"mean Li {li.mean():.4f} (reference {g['li'].mean():.4f})")
+    parity_record(f"path_tracer/{scene_name}/{config}", ok.sum(), len(ok))
     assert ok.mean() >= 0.99
     assert (li > 0).any()
 
@@ -274,18 +279,115 @@ def ref_harness(trb):
     import scene_to_obj
     cache = {}
 
-    def get(name):
-        if name not in cache:
-            scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{name}.npz")
-            obj = scene_to_obj.export_verified(scene, Path(tempfile.mkdtemp(prefix="trb_t_")) / "scene.obj")
-            cache[name] = (refh.RefHarness.open_scene(obj, width=64, height=64, spp=1, rr_depth=8), scene)
-        return cache[name]
+    objs = {}
+
+    def get(name, width=64, height=64, rr_depth=8, spp=1):
+        key = (name, width, height, rr_depth, spp)
+        if key not in cache:
+            if name not in objs:
+                scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{name}.npz")
+                objs[name] = (scene_to_obj.export_verified(scene, Path(tempfile.mkdtemp(prefix="trb_t_")) / "scene.obj"), scene)
+            obj, scene = objs[name]
+            cache[key] = (refh.RefHarness.open_scene(obj, width=width, height=height, spp=spp, rr_depth=rr_depth), scene)
+        return cache[key]
     yield get
     for rh, _ in cache.values():
         rh.close()
 
 
-def test_trace_million_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
+@pytest.mark.parametrize("name,rr_depth", [("caustic", 8), ("caustic", 16), ("hardlight", 8), ("hardlight", 16)])
+def test_bdpt_paths_golden_at_baseline_film_and_depth(trb, gpu_ctx, gold, parity_record, name, rr_depth):
+    """the committed golden walks on BASELINE.json's films and depths (tools/gen_golden_baseline.py: 1024 x 1024, rrDepth 8 / 16)"""
+    oracle_port = pytest.importorskip("oracle_port")
+    g = gold("paths", f"{name}_1024_rr{rr_depth}")
+    K = rr_depth - 1
+    desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=rr_depth)
+    streams = np.stack([oracle_port.sampler_stream(int(s), 10 + 10 * K) for s in g["seeds"]])
+    li, pix, rgb, draws = gpu_ctx(name).bdpt_paths(desc, _rays(trb, g["rays"]), streams)
+    ok = _paths_agree(g["li"], g["splat_pix"], g["splat_rgb"], li, pix, rgb) & (draws == g["draws"])
+    n = len(ok)
+    parity_record(f"bdpt_paths_golden/{name}/1024x1024/rrDepth{rr_depth}", ok.sum(), n)
+    assert ok.sum() >= n - 4, f"only {ok.sum()} of {n} golden walks within {REL}"
+
+
+@pytest.mark.parametrize("name,rr_depth", [("caustic", 8), ("caustic", 16), ("hardlight", 8), ("hardlight", 16)])
+def test_bdpt_paths_live_at_baseline_film_and_depth(trb, gpu_ctx, ref_harness, parity_record, name, rr_depth):
+    """Level 2 on the configurations BASELINE.json names (configs[1], configs[2]): film 1024 x 1024 (the W*H normaliser of
+    bdpt.h:330 and the pixel truncation of :494-495) at rrDepth 8 and at 16 ("max path length 16": K = 15 vertices per subpath, up
+    to 225 connectVertices calls per sample, bdpt.h:146-148, :434-483).  Whole samples of the UNMODIFIED reference's
+    BDPTIntegrator::render, run live on this box with private Sampler(seed)s, against trb_bdpt_paths on the same camera rays and
+    the same float streams: Li, every splat pixel and value, and the number of draws."""
+    oracle_port = pytest.importorskip("oracle_port")
+    import dev_rays
+    W = H = 1024
+    n = 2400
+    rh, scene = ref_harness(name, width=W, height=H, rr_depth=rr_depth, spp=16)
+    desc = trb.render_desc(width=W, height=H, spp=16, rr_depth=rr_depth)
+    rng = np.random.default_rng(1000 + rr_depth)
+    cam = dev_rays.camera_rays(trb.camera_matrices(desc), (0.0, 0.8, 3.8), 30.0, W, H)
+    prays = cam[rng.choice(len(cam), n, replace=False)]
+    seeds = rng.integers(1, 2**31 - 1, n).astype(np.int32)
+    K = rr_depth - 1
+    g_li, g_pix, g_rgb, g_draws = rh.bdpt_paths(prays, seeds, K)
+    stride = 10 + 10 * K
+    assert g_draws.max() <= stride
+    streams = np.stack([oracle_port.sampler_stream(int(s), stride) for s in seeds])
+    li, pix, rgb, draws = gpu_ctx(name).bdpt_paths(desc, _rays(trb, prays), streams)
+    ok = _paths_agree(g_li, g_pix, g_rgb, li, pix, rgb) & (draws == g_draws)
+    exact = np.all(li.view(np.uint32) == g_li.view(np.uint32), 1) & (draws == g_draws)
+    n_splats = int((g_pix >= 0).sum())
+    parity_record(f"bdpt_paths_live/{name}/1024x1024/rrDepth{rr_depth}", ok.sum(), n, li_bit_exact=int(exact.sum()), reference_splats=n_splats,
+                  mean_draws=float(g_draws.mean()), max_draws=int(g_draws.max()))
+    print(f"{name} 1024^2 rrDepth {rr_depth}: {ok.sum()}/{n} walks agree ({exact.sum()} Li bit for bit), {n_splats} splats, mean draws {g_draws.mean():.1f}")
+    assert n_splats > n // 4 and (g_li > 0).any()
+    assert ok.sum() >= n - 12, f"only {ok.sum()} of {n} walks within {REL}"
+
+
+def test_tessellated_scene_10m_vs_oracle(trb, parity_record):
+    """configs[4] AT SIZE: ~10 M triangles, BVH built on the device (the reference's own tree, 0.8 GB of nodes + triangles in HBM):
+    >= 10^5 seeded rays bit-exact (ids, t, u, v, occlusion flags) and >= 2000 whole BDPT samples within 1e-5 against the oracle
+    restatement, which is pinned bit-exact to the reference on the golden vectors (incl. the 20 k-triangle instance of this scene)."""
+    import dev_rays
+    import gen_tess_scene
+    import oracle_port
+    scene = gen_tess_scene.make_scene(10_000_000, seed=1)
+    assert scene.n_tris > 9_000_000
+    ctx = trb.Context(0)
+    ctx.upload(scene, build="device")
+    assert ctx.built_on_device()
+    orc = oracle_port.Oracle(scene)
+    rng = np.random.default_rng(12)
+    desc = trb.render_desc(width=1024, height=1024, spp=4, rr_depth=8)
+    orc.set_config(desc)
+    cam = dev_rays.camera_rays(trb.camera_matrices(desc), (0.0, 0.8, 3.8), 30.0, 1024, 1024)
+    rays = np.concatenate([cam[rng.choice(len(cam), 40_000, replace=False)], dev_rays.random_dir_rays(scene, 40_000, rng),
+                           dev_rays.segment_rays(scene, 40_000, rng)[0], dev_rays.axis_rays(scene, 4_000, rng)])
+    assert len(rays) >= 100_000
+    ids, tuv = orc.intersect(rays)
+    base = np.concatenate([[0], np.cumsum(np.bincount(scene.tri_shape, minlength=scene.n_shapes))])
+    tri_ref = np.where(ids[:, 0] == 1, base[np.clip(ids[:, 1], 0, None)] + ids[:, 2], -1).astype(np.int32)
+    h = ctx.trace_closest(_rays(trb, rays))
+    m = ids[:, 0] == 1
+    same_id = h["tri"] == tri_ref
+    same_tuv = np.all(np.stack([h["t"], h["u"], h["v"]], 1).view(np.uint32) == tuv.view(np.uint32), 1) | ~m
+    occ_same = ctx.trace_any(_rays(trb, rays)) == orc.occluded(rays)
+    parity_record("trace/tess10M/closest", (same_id & same_tuv).sum(), len(rays), bit_exact=True, hits=int(m.sum()))
+    parity_record("trace/tess10M/any", occ_same.sum(), len(rays), bit_exact=True)
+    assert same_id.all() and same_tuv.all() and occ_same.all()
+    n, stride = 2400, 128
+    prays = cam[rng.choice(len(cam), n, replace=False)]
+    seeds = rng.integers(1, 2**31 - 1, n).astype(np.int32)
+    li_ref, pix_ref, rgb_ref, nd_ref = orc.bdpt_paths(prays, 7, seeds=seeds)
+    streams = np.stack([oracle_port.sampler_stream(int(s), stride) for s in seeds])
+    li, pix, rgb, draws = ctx.bdpt_paths(desc, _rays(trb, prays), streams)
+    ok = _paths_agree(li_ref, pix_ref, rgb_ref, li, pix, rgb) & (draws == nd_ref)
+    parity_record("bdpt_paths/tess10M/1024x1024/rrDepth8", ok.sum(), n, checker="restatement")
+    print(f"tess 10M ({scene.n_tris} triangles): {len(rays)} rays bit-exact, walks ok {ok.sum()}/{n}")
+    assert ok.sum() >= n - 12
+    ctx.close(); orc.close()
+
+
+def test_trace_million_rays_vs_reference(trb, gpu_ctx, ref_harness, parity_record, scene_name):
     """SURVEY 8(c) level 1 at size: >= 10^6 seeded rays per scene (camera, random surface rays, visibility segments,
     axis-parallel rays) through the persistent-warp kernels vs AcceleratorBVH::intersect / BVH::getIntersection of the
     reference itself: ids and (t,u,v) bit-exact, occlusion flags exact."""
@@ -309,6 +411,7 @@ def test_trace_million_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
     for k, f in enumerate(("t", "u", "v")):
         assert np.array_equal(h[f][m].view(np.uint32), tuv[m, k].view(np.uint32)), f
     assert np.array_equal(ctx.trace_any(_rays(trb, rays)), occ_ref)
+    parity_record(f"trace/{scene_name}/closest+any_vs_reference", len(rays), len(rays), bit_exact=True, hits=int(m.sum()), occluded=int(occ_ref.sum()))
 
 
 def test_degenerate_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
@@ -359,7 +462,7 @@ def test_degenerate_rays_vs_reference(trb, gpu_ctx, ref_harness, scene_name):
     print(f"{scene_name}: {len(rays)} degenerate rays, {int(m.sum())} hits, {int(occ_ref.sum())} occluded - identical")
 
 
-def test_tessellated_scene_at_size_vs_oracle(trb):
+def test_tessellated_scene_at_size_vs_oracle(trb, parity_record):
     """configs[4] at 2 M triangles (HBM-resident acceleration structure, mirror / glass / Phong / Mixture materials):
     hits bit-exact and whole BDPT samples within 1e-5 against the oracle restatement (oracle/bdpt_oracle.cpp, itself
     pinned bit-exact to the reference on the golden vectors including the 20 k-triangle instance of this scene)."""
@@ -393,5 +496,6 @@ def test_tessellated_scene_at_size_vs_oracle(trb):
     scale = np.maximum(np.abs(li_ref).max(1, keepdims=True), 1e-6)
     ok = (np.abs(li - li_ref) <= REL * np.maximum(scale, np.abs(li))).all(1) & (draws == nd_ref)
     print(f"tess 2M: paths ok {ok.sum()}/{n}")
+    parity_record("bdpt_paths/tess2M/256x192/rrDepth8", ok.sum(), n, checker="restatement")
     assert ok.mean() >= 0.99
     ctx.close(); orc.close()

@@ -112,6 +112,25 @@ def test_bdpt_paths_bit_exact(trb, orc, gold, scene_name):
     assert np.array_equal(li2.view(np.uint32), g["li"][:500].view(np.uint32)) and np.array_equal(nd2, g["draws"][:500])
 
 
+@pytest.mark.parametrize("name,rr_depth", [("caustic", 8), ("caustic", 16), ("hardlight", 8), ("hardlight", 16)])
+def test_bdpt_paths_bit_exact_at_baseline_film_and_depth(trb, gold, name, rr_depth):
+    """the restatement on BASELINE.json's films and depths (1024 x 1024; rrDepth 8 and 16 = up to 15 vertices per subpath and 225
+    connectVertices calls per sample) against whole samples of the unmodified reference (tools/gen_golden_baseline.py)"""
+    from conftest import GOLD
+    g = gold("paths", f"{name}_1024_rr{rr_depth}")
+    o = oracle_port.Oracle(trb.HostScene.load_npz(GOLD / f"scene_{name}.npz"))
+    try:
+        o.set_config(trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=rr_depth))
+        li, pix, rgb, nd = o.bdpt_paths(g["rays"], rr_depth - 1, seeds=g["seeds"])
+    finally:
+        o.close()
+    assert np.array_equal(nd, g["draws"])
+    assert np.array_equal(li.view(np.uint32), g["li"].view(np.uint32))
+    assert np.array_equal(pix, g["splat_pix"])
+    assert np.array_equal(rgb.view(np.uint32), g["splat_rgb"].view(np.uint32))
+    assert (pix >= 0).sum() > 1000
+
+
 DI_SCENES = ["spherelight", "caustic", "tess"]
 DI_STRATEGIES = ["mis", "area", "solidAngle", "cosineHemisphere", "bsdf"]
 
