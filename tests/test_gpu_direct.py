@@ -26,7 +26,7 @@ def _rays(trb, r8):
 
 @pytest.mark.parametrize("strategy", STRATEGIES)
 @pytest.mark.parametrize("scene", SCENES)
-def test_direct_paths_match_reference(trb, gpu_ctx, gold, scene, strategy):
+def test_direct_paths_match_reference(trb, gpu_ctx, gold, parity_record, scene, strategy):
     """Li within 1e-5 relative and the same number of draws as the unmodified reference for >= 99 % of the samples (a sample whose
     shadow-ray decision sits on a rounding boundary may flip; everything else must agree)"""
     oracle_port = pytest.importorskip("oracle_port")
@@ -41,8 +41,9 @@ def test_direct_paths_match_reference(trb, gpu_ctx, gold, scene, strategy):
     ok = (np.abs(li - ref_li) <= REL * np.maximum(scale, np.abs(li))).all(1) & (draws == ref_draws)
     exact = (li.view(np.uint32) == ref_li.view(np.uint32)).all(1)
     print(f"{scene}/{strategy}: {ok.sum()}/{len(ok)} samples agree ({exact.sum()} bit-exact); mean Li {li.mean():.4f} (reference {ref_li.mean():.4f})")
+    parity_record(f"direct_paths/{scene}/{strategy}", ok.sum(), len(ok), li_bit_exact=int(exact.sum()))
     assert np.array_equal(draws, ref_draws)
-    assert ok.mean() >= 0.99
+    assert ok.sum() >= len(ok) - 3   # measured on B200: 1500/1500 in all 15 configurations
     assert (li > 0).any()
 
 
@@ -168,7 +169,7 @@ def test_cli_and_cpp_api_direct(trb, gpu_ctx, gold, tmp_path):
     ref = g["li"][:n]
     scale = np.maximum(np.abs(ref).max(1, keepdims=True), 1e-6)
     ok = (np.abs(out[:, :3] - ref) <= 1e-5 * np.maximum(scale, np.abs(out[:, :3]))).all(1)
-    assert ok.mean() >= 0.99, ok.mean()
+    assert ok.sum() >= n - 3, ok.sum()
     # the reference's own default strategy name is one its integrator rejects ("Error: wrong strategy", direct.h:460)
     write("emitter")
     bad = subprocess.run(exe, capture_output=True, text=True, timeout=300)

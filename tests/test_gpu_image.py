@@ -256,7 +256,7 @@ def test_cli_and_cpp_api_path_tracer(trb, gpu_ctx, gold, tmp_path):
     ref = g["li"][:n]
     scale = np.maximum(np.abs(ref).max(1, keepdims=True), 1e-6)
     ok = (np.abs(out[:, :3] - ref) <= 1e-5 * np.maximum(scale, np.abs(out[:, :3]))).all(1)
-    assert ok.mean() >= 0.99, ok.mean()
+    assert ok.sum() >= n - 3, ok.sum()
 
 
 def test_cpp_host_api_paths_match_reference(trb, gold, tmp_path):
@@ -279,5 +279,5 @@ def test_cpp_host_api_paths_match_reference(trb, gold, tmp_path):
     ref = g["li"][:n]
     scale = np.maximum(np.abs(ref).max(1, keepdims=True), 1e-6)
     ok = (np.abs(out[:, :3] - ref) <= 1e-5 * np.maximum(scale, np.abs(out[:, :3]))).all(1)
-    assert ok.mean() >= 0.99, ok.mean()
+    assert ok.sum() >= n - 3, ok.sum()
     assert out[:, 3].view(np.int32).sum() > n // 2  # most camera rays hit the box

@@ -142,7 +142,7 @@ def test_bdpt_paths_match_reference(trb, gpu_ctx, gold, parity_record, scene_nam
     draws_same = (draws == g["draws"])
     print(f"{scene_name}: paths ok {ok.sum()}/{n}, draws identical {draws_same.sum()}/{n}")
     parity_record(f"bdpt_paths_golden/{scene_name}/96x72/rrDepth{int(g['rr_depth'])}", (ok & draws_same).sum(), n)
-    assert frac >= 0.99, f"only {frac:.4f} of paths within {REL}"
+    assert (ok & draws_same).sum() >= n - 6, f"only {ok.sum()} of {n} paths within {REL}"   # measured on B200: 3000 / 2998 / 3000 (profiles/parity_counts.json)
     assert draws_same[ok].all()
 
 
@@ -164,7 +164,7 @@ def test_bdpt_paths_at_the_smallest_depths(trb, gpu_ctx, gold, parity_record, sc
     ok = _paths_agree(c_li, c_pix, c_rgb, li, pix, rgb) & (draws == c_draws)
     print(f"{scene_name} rrDepth {rr_depth}: {ok.sum()}/{n} agree, mean draws {draws.mean():.2f}")
     parity_record(f"bdpt_paths/{scene_name}/96x72/rrDepth{rr_depth}", ok.sum(), n, checker="restatement")
-    assert ok.mean() >= 0.99
+    assert ok.sum() >= n - 4   # measured: 1500 everywhere but hardlight rrDepth 3 (1499)
     if rr_depth == 1:
         assert not li.any() and (pix < 0).all()      # nothing is ever connected
 
@@ -227,8 +227,8 @@ def test_bdpt_paths_russian_roulette(trb, gpu_ctx, gold, parity_record, scene_na
           f"mean draws {draws.mean():.1f}, splat columns used {int((pix >= 0).sum(1).max())} (reference {kk})")
     parity_record(f"bdpt_paths_rr/{scene_name}/vs_reference_uncapped_walks", ok_ref[untouched].sum(), untouched.sum())
     parity_record(f"bdpt_paths_rr/{scene_name}/vs_capped_restatement", ok_cap.sum(), n, checker="restatement")
-    assert ok_ref[untouched].mean() >= 0.99
-    assert ok_cap.mean() >= 0.99
+    assert ok_ref[untouched].sum() >= untouched.sum() - 10   # measured: 1500/1500, 1499/1500, 1481/1486
+    assert ok_cap.sum() >= n - 10                            # measured: 1500, 1499, 1495 of 1500
     assert draws.mean() > 45  # the walks do run past rr_depth
 
 
@@ -263,7 +263,7 @@ def test_path_tracer_paths_match_reference(trb, gpu_ctx, gold, parity_record, sc
     print(f"{scene_name}/{config}: {ok.sum()}/{len(ok)} paths agree; mean draws {draws.mean():.1f} (reference {g['draws'].mean():.1f}); "
           f"mean Li {li.mean():.4f} (reference {g['li'].mean():.4f})")
     parity_record(f"path_tracer/{scene_name}/{config}", ok.sum(), len(ok))
-    assert ok.mean() >= 0.99
+    assert ok.sum() >= len(ok) - 4   # measured: 1200/1200 in 8 configurations, 1199/1200 in tess/rr
     assert (li > 0).any()
 
 
@@ -340,7 +340,7 @@ def test_bdpt_paths_live_at_baseline_film_and_depth(trb, gpu_ctx, ref_harness, p
                   mean_draws=float(g_draws.mean()), max_draws=int(g_draws.max()))
     print(f"{name} 1024^2 rrDepth {rr_depth}: {ok.sum()}/{n} walks agree ({exact.sum()} Li bit for bit), {n_splats} splats, mean draws {g_draws.mean():.1f}")
     assert n_splats > n // 4 and (g_li > 0).any()
-    assert ok.sum() >= n - 12, f"only {ok.sum()} of {n} walks within {REL}"
+    assert ok.sum() >= n - 6, f"only {ok.sum()} of {n} walks within {REL}"   # measured: 2399, 2400, 2398, 2398 of 2400
 
 
 def test_tessellated_scene_10m_vs_oracle(trb, parity_record):
@@ -383,7 +383,7 @@ def test_tessellated_scene_10m_vs_oracle(trb, parity_record):
     ok = _paths_agree(li_ref, pix_ref, rgb_ref, li, pix, rgb) & (draws == nd_ref)
     parity_record("bdpt_paths/tess10M/1024x1024/rrDepth8", ok.sum(), n, checker="restatement")
     print(f"tess 10M ({scene.n_tris} triangles): {len(rays)} rays bit-exact, walks ok {ok.sum()}/{n}")
-    assert ok.sum() >= n - 12
+    assert ok.sum() >= n - 6   # measured: 2400/2400
     ctx.close(); orc.close()
 
 
@@ -497,5 +497,5 @@ def test_tessellated_scene_at_size_vs_oracle(trb, parity_record):
     ok = (np.abs(li - li_ref) <= REL * np.maximum(scale, np.abs(li))).all(1) & (draws == nd_ref)
     print(f"tess 2M: paths ok {ok.sum()}/{n}")
     parity_record("bdpt_paths/tess2M/256x192/rrDepth8", ok.sum(), n, checker="restatement")
-    assert ok.mean() >= 0.99
+    assert ok.sum() >= n - 8   # measured: 3997/4000
     ctx.close(); orc.close()

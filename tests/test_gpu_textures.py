@@ -24,14 +24,15 @@ def _agree(li, ref):
     return (np.abs(li - ref) <= REL * np.maximum(scale, np.abs(li))).all(1)
 
 
-def test_textured_bdpt_paths_match_reference(trb, gpu_ctx, gold):
+def test_textured_bdpt_paths_match_reference(trb, gpu_ctx, gold, parity_record):
     g = gold("paths", "textured")
     desc = trb.render_desc(width=int(g["width"]), height=int(g["height"]), spp=int(g["spp"]), rr_depth=int(g["rr_depth"]))
     li, pix, rgb, draws = gpu_ctx("textured").bdpt_paths(desc, _rays(trb, g["rays"]), g["rng"])
     from test_gpu_parity import _paths_agree   # Li + the splat pixel -> rgb map (the reference lists splats by pixel)
     ok = _paths_agree(g["li"], g["splat_pix"], g["splat_rgb"], li, pix, rgb) & (draws == g["draws"])
     print(f"textured BDPT: {ok.sum()}/{len(ok)} paths agree; mean Li {li.mean():.4f} (reference {g['li'].mean():.4f})")
-    assert ok.mean() >= 0.99 and (li > 0).any()
+    parity_record("bdpt_paths_golden/textured", ok.sum(), len(ok))
+    assert ok.sum() >= len(ok) - 4 and (li > 0).any()   # measured: 2000/2000
     # the textures matter: the same paths on the scene with its bitmaps removed differ
     plain = trb.HostScene.load_npz(GOLD / "scene_textured.npz")
     plain.materials["tex"] = 0
@@ -42,7 +43,7 @@ def test_textured_bdpt_paths_match_reference(trb, gpu_ctx, gold):
     assert (~_agree(li0, g["li"])).mean() > 0.3
 
 
-def test_textured_path_and_direct_match_reference(trb, gpu_ctx, gold):
+def test_textured_path_and_direct_match_reference(trb, gpu_ctx, gold, parity_record):
     oracle_port = pytest.importorskip("oracle_port")
     ctx = gpu_ctx("textured")
     g = gold("ptpaths", "textured_mis")
@@ -52,13 +53,15 @@ def test_textured_path_and_direct_match_reference(trb, gpu_ctx, gold):
     li, draws = ctx.path_paths(desc, pd, _rays(trb, g["rays"]), streams)
     ok = _agree(li, g["li"]) & (draws == g["draws"])
     print(f"textured path tracer: {ok.sum()}/{len(ok)} agree")
-    assert ok.mean() >= 0.99
+    parity_record("path_tracer/textured/mis", ok.sum(), len(ok))
+    assert ok.sum() >= len(ok) - 3   # measured: 1200/1200
     g = gold("dipaths", "textured_mis")
     streams = np.stack([oracle_port.sampler_stream(int(s), int(g["draws"].max()) + 4) for s in g["seeds"]])
     li, draws = ctx.direct_paths(desc, trb.direct_desc("mis", int(g["emitter_samples"]), int(g["bsdf_samples"])), _rays(trb, g["rays"]), streams)
     ok = _agree(li, g["li"]) & (draws == g["draws"])
     print(f"textured direct integrator: {ok.sum()}/{len(ok)} agree")
-    assert ok.mean() >= 0.99
+    parity_record("direct_paths/textured/mis", ok.sum(), len(ok))
+    assert ok.sum() >= len(ok) - 3   # measured: 1500/1500
 
 
 def _box(img, k):
