@@ -24,7 +24,7 @@ TRB_FLAG_NO_JITTER = 1
 TRB_FLAG_NO_OVERLAP = 2
 TRB_FLAG_RUSSIAN_ROULETTE = 4  # the reference's NO_RR 0 behaviour (bdpt.h:18,68,129); default off = shipped behaviour
 TRB_RR_DEFAULT_MAX_DEPTH = 32
-TRB_FLAG_SORT_RAYS = 8      # experiment: sort every ray queue by (origin cell, direction) before traversal (off by default)
+TRB_FLAG_SORT_RAYS = 8      # accepted and ignored (round-1 experiment, removed: profiles/r1f_tuning_variants.md)
 
 
 class TrbError(RuntimeError):
@@ -118,6 +118,8 @@ DEV_TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("tri", "<i4"), ("e1", "<f4", 3), ("
 DEV_SHADE_DTYPE = np.dtype([("v0", "<f4", 3), ("shape", "<i4"), ("v1", "<f4", 3), ("prim", "<i4"), ("v2", "<f4", 3), ("mat", "<i4"),
                             ("n0", "<f4", 3), ("emitter", "<i4"), ("n1", "<f4", 3), ("tri", "<i4"), ("n2", "<f4", 3), ("pad", "<i4")])
 DEV_TRI_UV_DTYPE = np.dtype([("st", "<f4", (3, 2)), ("pad", "<f4", 2)])
+DEV_NODE4_DTYPE = np.dtype([("lox", "<f4", 4), ("loy", "<f4", 4), ("loz", "<f4", 4), ("hix", "<f4", 4), ("hiy", "<f4", 4), ("hiz", "<f4", 4), ("ref", "<i4", 4), ("pad", "<i4", 4)])
+assert DEV_NODE4_DTYPE.itemsize == 128
 assert DEV_NODE_DTYPE.itemsize == 64 and DEV_TRI_DTYPE.itemsize == 48 and DEV_SHADE_DTYPE.itemsize == 96 and DEV_TRI_UV_DTYPE.itemsize == 32
 
 _lib = None
@@ -398,8 +400,9 @@ class Context:
         return bool(self._L.trb_scene_built_on_device(self._h))
 
     def download(self, which: str) -> np.ndarray:
-        """test hook (trb_scene_download): "nodes" | "tris" | "shade" | "tri_uv" of the device scene as structured arrays"""
-        idx, dt = {"nodes": (0, DEV_NODE_DTYPE), "tris": (1, DEV_TRI_DTYPE), "shade": (2, DEV_SHADE_DTYPE), "tri_uv": (3, DEV_TRI_UV_DTYPE)}[which]
+        """test hook (trb_scene_download): "nodes" | "tris" | "shade" | "tri_uv" | "wnodes" of the device scene as structured arrays"""
+        idx, dt = {"nodes": (0, DEV_NODE_DTYPE), "tris": (1, DEV_TRI_DTYPE), "shade": (2, DEV_SHADE_DTYPE), "tri_uv": (3, DEV_TRI_UV_DTYPE),
+                   "wnodes": (4, DEV_NODE4_DTYPE)}[which]
         n = C.c_size_t(0)
         self._chk(self._L.trb_scene_download(self._h, idx, None, C.c_size_t(0), C.byref(n)))
         out = np.zeros(n.value, dt)

@@ -28,7 +28,7 @@ inline float lum(float r, float g, float b) { return (r * 0.212671f + g * 0.7151
 }  // namespace
 
 size_t FlatScene::bytes() const {
-    return n_nodes * sizeof(DevNode) + n_tris * sizeof(DevTri) + n_tris * sizeof(DevShade) +
+    return n_nodes * sizeof(DevNode) + n_wnodes * sizeof(DevNode4) + n_tris * sizeof(DevTri) + n_tris * sizeof(DevShade) +
            materials.size() * sizeof(DevMaterial) + emitters.size() * sizeof(DevEmitter) +
            emitter_tris.size() * sizeof(DevEmitterTri) + emitter_cdf.size() * sizeof(float) + emitter_sphere.size() * sizeof(float) +
            tex_info.size() * sizeof(DevTexInfo) + n_tri_uv * sizeof(DevTriUV) + texels.size() * sizeof(float);
@@ -325,6 +325,74 @@ bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err) {
     return true;
 }
 
+// The 4-wide upper tree (tr_host.h: DevNode4), level by level.  A wide node starts from a binary inner node's two children and
+// opens, while it has fewer than four, the inner child of largest surface area (ties: the first); an opened child is replaced
+// in place by its two children, so the children keep the reference's left-to-right order.  Inner children are numbered in
+// (parent order, slot order) on the next level - the same rule the device build follows with a prefix sum.
+void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& depth) {
+    out.clear(); depth = 0;
+    if (tree.nodes.empty() || tree.nodes[0].left < 0) return;   // a single leaf: the root reference is the leaf itself
+    std::vector<int32_t> level{0}, next;
+    while (!level.empty()) {
+        const size_t base = out.size();
+        out.resize(base + level.size());
+        // children of every node of the level (disjoint outputs), then the numbering of the inner ones
+        std::vector<int32_t> slots(4 * level.size(), -1);
+        parallel_for(level.size(), 1 << 14, [&](size_t i0, size_t i1) {
+            for (size_t i = i0; i < i1; ++i) {
+                int32_t* sl = &slots[4 * i];
+                const RefTree::Node& b = tree.nodes[level[i]];
+                sl[0] = b.left; sl[1] = b.right;
+                int n = 2;
+                while (n < 4) {
+                    int best = -1; float best_a = 0.f;
+                    for (int k = 0; k < n; ++k) {
+                        const RefTree::Node& c = tree.nodes[sl[k]];
+                        if (c.left < 0) continue;
+                        const float a = wide_box_area(c.bmin, c.bmax);
+                        if (best < 0 || a > best_a) { best = k; best_a = a; }
+                    }
+                    if (best < 0) break;
+                    const RefTree::Node& c = tree.nodes[sl[best]];
+                    for (int k = n; k > best + 1; --k) sl[k] = sl[k - 1];
+                    sl[best] = c.left; sl[best + 1] = c.right;
+                    ++n;
+                }
+            }
+        });
+        next.clear();
+        std::vector<uint32_t> first_inner(level.size() + 1, 0);
+        for (size_t i = 0; i < level.size(); ++i) {
+            uint32_t c = 0;
+            for (int k = 0; k < 4; ++k) if (slots[4 * i + k] >= 0 && tree.nodes[slots[4 * i + k]].left >= 0) ++c;
+            first_inner[i + 1] = first_inner[i] + c;
+        }
+        next.resize(first_inner[level.size()]);
+        const size_t next_base = base + level.size();
+        parallel_for(level.size(), 1 << 14, [&](size_t i0, size_t i1) {
+            for (size_t i = i0; i < i1; ++i) {
+                DevNode4& w = out[base + i];
+                uint32_t at = first_inner[i];
+                for (int k = 0; k < 4; ++k) {
+                    const int32_t ci = slots[4 * i + k];
+                    if (ci < 0) {
+                        w.lox[k] = w.loy[k] = w.loz[k] = w.hix[k] = w.hiy[k] = w.hiz[k] = 0.f; w.ref[k] = TRB_WIDE_EMPTY;
+                    } else {
+                        const RefTree::Node& c = tree.nodes[ci];
+                        w.lox[k] = c.bmin[0]; w.loy[k] = c.bmin[1]; w.loz[k] = c.bmin[2];
+                        w.hix[k] = c.bmax[0]; w.hiy[k] = c.bmax[1]; w.hiz[k] = c.bmax[2];
+                        if (c.left >= 0) { next[at] = ci; w.ref[k] = int32_t(next_base + at); ++at; }
+                        else w.ref[k] = ~int32_t((c.start << 3) | c.count);
+                    }
+                    w.pad[k] = 0;
+                }
+            }
+        });
+        level.swap(next);
+        ++depth;
+    }
+}
+
 bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     return flatten_tables(s, out, err) && flatten_geometry(s, out, err);
 }
@@ -373,8 +441,8 @@ bool flatten_tables(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     for (size_t t = 0; t < s.n_tris; ++t) out.shape_first[s.tri_shape[t] + 1] = int32_t(t + 1);
     for (size_t k = 1; k <= s.n_shapes; ++k) out.shape_first[k] = std::max(out.shape_first[k], out.shape_first[k - 1]);
     out.textured = textured;
-    out.nodes.clear(); out.tris.clear(); out.shade.clear(); out.order.clear();
-    out.n_nodes = out.n_tris = out.n_tri_uv = 0;
+    out.nodes.clear(); out.wnodes.clear(); out.tris.clear(); out.shade.clear(); out.order.clear();
+    out.n_nodes = out.n_tris = out.n_tri_uv = out.n_wnodes = 0; out.wide_depth = 0;
     {
         std::vector<float> sph;
         shape_spheres(s, sph);
@@ -433,25 +501,10 @@ bool flatten_geometry(const trb_scene_desc& s, FlatScene& out, std::string& err)
     }
     });
 
-    // inner nodes only; leaves become negative child references
-    // Numbering: the first TRB_TOP_NODES_MAX inner nodes in breadth-first order come first (the traversal kernel stages a prefix
-    // of them - the top levels of the tree - in shared memory), the rest follow in the reference's pre-order (left child adjacent).
-    // Only the child references depend on the numbering; the set of boxes a ray tests and the hits do not.
+    // inner nodes only, in the reference's pre-order (left child adjacent); leaves become negative child references
     std::vector<int32_t> inner_index(tree.nodes.size(), -1);
     int32_t n_inner = 0;
-    const char* top_env = std::getenv("TRB_TOP_NUMBERING");  // only the -DTRB_TOP experiment builds of the kernel need it
-    if (top_env && std::atoi(top_env) > 0 && !tree.nodes.empty() && tree.nodes[0].left >= 0) {
-        std::vector<int32_t> bfs;
-        bfs.push_back(0);
-        for (size_t k = 0; k < bfs.size() && bfs.size() < size_t(TRB_TOP_NODES_MAX); ++k) {
-            const RefTree::Node& nd = tree.nodes[bfs[k]];
-            for (int32_t ch : {nd.left, nd.right})
-                if (tree.nodes[ch].left >= 0 && bfs.size() < size_t(TRB_TOP_NODES_MAX)) bfs.push_back(ch);
-        }
-        for (int32_t ni : bfs) inner_index[ni] = n_inner++;
-    }
-    out.top_nodes = n_inner;
-    for (size_t i = 0; i < tree.nodes.size(); ++i) if (tree.nodes[i].left >= 0 && inner_index[i] < 0) inner_index[i] = n_inner++;
+    for (size_t i = 0; i < tree.nodes.size(); ++i) if (tree.nodes[i].left >= 0) inner_index[i] = n_inner++;
     auto make_ref = [&](int32_t ni) -> int32_t {
         const RefTree::Node& nd = tree.nodes[ni];
         if (nd.left >= 0) return inner_index[ni];
@@ -483,7 +536,8 @@ bool flatten_geometry(const trb_scene_desc& s, FlatScene& out, std::string& err)
         md = std::max(md, depth[i]);
     }
     out.max_depth = md;
-    out.n_nodes = out.nodes.size(); out.n_tris = out.tris.size(); out.n_tri_uv = out.tri_uv.size();
+    build_wide_nodes(tree, out.wnodes, out.wide_depth);
+    out.n_nodes = out.nodes.size(); out.n_tris = out.tris.size(); out.n_tri_uv = out.tri_uv.size(); out.n_wnodes = out.wnodes.size();
     return true;
 }
 

@@ -47,6 +47,24 @@ struct alignas(16) DevNode {
 };
 static_assert(sizeof(DevNode) == 64, "node must be 64 B");
 
+// 128-byte 4-wide node of the UPPER tree the traversal kernels walk (kernels/trace_wide.cuh).
+// The reference's answer is "min (t, list position) over the triangles ALL of whose ancestor boxes pass BBox::intersect"
+// (bvh.h:259-352).  Every box of the reference's tree is the exact min/max union of its children's (bvh.h:171-182) and
+// fl((b - o) / d) is monotone in b, so for a ray whose direction has three finite non-zero components a LEAF box that
+// passes implies that all its ancestors pass: the candidate set is decided by the leaf boxes alone, and any tree over the
+// reference's leaves whose inner boxes are unions of leaf boxes finds it.  This one is the reference's own binary tree
+// collapsed to four children per node (the child of largest surface area is opened first): half the dependent fetches per
+// ray.  Leaves, their exact boxes and the primitive order (= the tie-break rank) are the reference's.  Rays with a zero or
+// non-finite direction component (NaN poisoning in the slab test, where the equivalence does not hold) are traced on the
+// binary DevNode tree.  SoA over the four children: 7 x LDG.128.
+#define TRB_WIDE_EMPTY INT32_MIN   // an unused child slot (never a leaf code: first < 2^27)
+struct alignas(16) DevNode4 {
+    float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+    int32_t ref[4];   // >= 0: wide node index; < 0: leaf, ~ref = (first << 3) | count; TRB_WIDE_EMPTY: unused slot
+    int32_t pad[4];
+};
+static_assert(sizeof(DevNode4) == 128, "wide node must be 128 B");
+
 // 48-byte intersection record, stored in the reference's build-reordered primitive order so that the
 // array position IS the tie-break rank (first found wins, bvh.h:305).
 struct alignas(16) DevTri {
@@ -100,7 +118,6 @@ struct alignas(16) DevEmitterTri {
 };
 static_assert(sizeof(DevEmitterTri) == 80, "emitter triangle must be 80 B");
 
-#define TRB_TOP_NODES_MAX 1024
 // bitmap textures (BitmapTexture3f, core.h:525-585): table entry + per-triangle texture coordinates (build order, like DevTri)
 struct alignas(16) DevTexInfo { uint32_t first_texel; int32_t w, h, pad; };
 struct alignas(16) DevTriUV { float st0[2], st1[2], st2[2], pad[2]; };
@@ -108,6 +125,7 @@ static_assert(sizeof(DevTexInfo) == 16 && sizeof(DevTriUV) == 32, "texture recor
 
 struct FlatScene {
     std::vector<DevNode> nodes;
+    std::vector<DevNode4> wnodes;       // the 4-wide upper tree (level order); empty after a device build
     std::vector<DevTri> tris;
     std::vector<DevShade> shade;
     std::vector<DevMaterial> materials;
@@ -120,10 +138,10 @@ struct FlatScene {
     std::vector<float> emitter_sphere;  // per emitter: Scene::getShapeCenter xyz, getShapeRadius (renderer.cpp:349-358) - DirectIntegrator's sphere lights
     std::vector<int32_t> order;  // order[pos] = global tri id (host build only)
     // counts of the device arrays (nodes / tris = shade / tri_uv): the vectors above are empty after a device build
-    size_t n_nodes = 0, n_tris = 0, n_tri_uv = 0;
+    size_t n_nodes = 0, n_tris = 0, n_tri_uv = 0, n_wnodes = 0;
+    int32_t wide_depth = 0;      // levels of the wide tree
     bool textured = false;
     std::vector<int32_t> shape_to_emitter, shape_first;  // per shape: emitter index or -1; first global triangle (n_shapes + 1)
-    int32_t top_nodes = 0;       // nodes [0, top_nodes) are the top of the tree in breadth-first order (<= TRB_TOP_NODES_MAX)
     int32_t root_ref = 0;        // root as a child reference (leaf when the scene has <= 4 triangles)
     int32_t max_depth = 0;       // tree depth (traversal stack bound)
     float scene_min[3], scene_max[3];
@@ -137,6 +155,16 @@ struct RefTree {
     std::vector<int32_t> order;
 };
 bool build_ref_tree(const trb_scene_desc& s, RefTree& out, std::string& err);
+// the reference's tree collapsed to 4-wide nodes in level order (same result as kernels/bvh_build.cuh: k_wide_*)
+void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& depth);
+// surface-area measure that orders the collapse: ((dx*dy) + (dy*dz)) + (dz*dx), fp32, no contraction (host and device alike)
+#if defined(__CUDACC__)
+__host__ __device__
+#endif
+inline float wide_box_area(const float mn[3], const float mx[3]) {
+    const float dx = mx[0] - mn[0], dy = mx[1] - mn[1], dz = mx[2] - mn[2];
+    return (dx * dy + dy * dz) + dz * dx;
+}
 
 bool derive_materials(const trb_scene_desc& s, std::vector<DevMaterial>& out, std::string& err);
 bool derive_emitters(const trb_scene_desc& s, const std::vector<DevMaterial>& mats, std::vector<DevEmitter>& em,

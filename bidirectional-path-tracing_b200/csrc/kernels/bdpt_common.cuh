@@ -95,7 +95,10 @@ struct WaveParams {
     uint32_t shadow_cap;
 };
 
-enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_CONN = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 5, CTR_N = 8 };
+// a traversal launch owns three consecutive words: [0] ray-queue cursor of k_trace_wide, [1] number of rays it deferred to the binary tree,
+// [2] cursor of the k_trace_coop launch that traces those
+enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_CONN = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 8, CTR_N = 12 };
+enum : uint32_t { TRACE_CTR_WORDS = 3 };
 enum : uint32_t { SLOT_PURE_SPECULAR = 1u };
 
 // ---- random numbers ----------------------------------------------------------------------------------

@@ -12,9 +12,9 @@ namespace trbk {
 
 #define TRB_BLOCK 128
 
-__device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref, 0}; }
+__device__ __forceinline__ BvhView bvh_of(const SceneDev& sc) { return BvhView{sc.nodes, sc.tris, sc.root_ref}; }
 
-// (the traversal kernels live in trace_warp.cuh)
+// (the traversal kernels live in trace_wide.cuh / trace_coop.cuh)
 
 // ---- camera rays (renderer.cpp:161-192) ------------------------------------------------------------------
 __global__ void __launch_bounds__(TRB_BLOCK) k_gen_camera(const __grid_constant__ WaveParams p) {

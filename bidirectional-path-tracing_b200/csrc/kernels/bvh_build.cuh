@@ -229,6 +229,57 @@ __global__ void k_bb_emit_nodes(const BuildNode* __restrict__ nodes, int32_t tot
     out[nd.inner_pre] = d;
 }
 
+// ---- the 4-wide upper tree (tr_host.h: DevNode4), level by level: the device twin of trb::build_wide_nodes ----
+// children of every wide node of a level: start from the binary node's two children and open, while fewer than four, the inner
+// child of largest surface area (ties: the first); an opened child is replaced in place by its two children
+__global__ void k_wide_expand(const BuildNode* __restrict__ nodes, const int32_t* __restrict__ level, int32_t n_level, int4* __restrict__ slots,
+                              uint32_t* __restrict__ n_inner) {
+    int32_t i = int32_t(blockIdx.x * blockDim.x + threadIdx.x);
+    if (i > n_level) return;
+    if (i == n_level) { n_inner[i] = 0u; return; }   // the exclusive sum has n_level + 1 entries
+    const BuildNode& b = nodes[level[i]];
+    int32_t sl[4] = {b.left, b.right, -1, -1};
+    int n = 2;
+    while (n < 4) {
+        int best = -1; float best_a = 0.f;
+        for (int k = 0; k < n; ++k) {
+            const BuildNode& c = nodes[sl[k]];
+            if (c.left < 0) continue;
+            const float a = trb::wide_box_area(c.bmin, c.bmax);
+            if (best < 0 || a > best_a) { best = k; best_a = a; }
+        }
+        if (best < 0) break;
+        const BuildNode& c = nodes[sl[best]];
+        for (int k = n; k > best + 1; --k) sl[k] = sl[k - 1];
+        sl[best] = c.left; sl[best + 1] = c.right;
+        ++n;
+    }
+    uint32_t cnt = 0;
+    for (int k = 0; k < 4; ++k) if (sl[k] >= 0 && nodes[sl[k]].left >= 0) ++cnt;
+    slots[i] = make_int4(sl[0], sl[1], sl[2], sl[3]);
+    n_inner[i] = cnt;
+}
+// the node records of the level and the binary nodes of the next one: inner children are numbered in (parent order, slot order)
+__global__ void k_wide_emit(const BuildNode* __restrict__ nodes, int32_t n_level, const int4* __restrict__ slots, const uint32_t* __restrict__ first_inner,
+                            uint32_t base, trb::DevNode4* __restrict__ out, int32_t* __restrict__ next_level) {
+    int32_t i = int32_t(blockIdx.x * blockDim.x + threadIdx.x);
+    if (i >= n_level) return;
+    const int4 s4 = slots[i];
+    const int32_t sl[4] = {s4.x, s4.y, s4.z, s4.w};
+    const uint32_t next_base = base + uint32_t(n_level);
+    uint32_t at = first_inner[i];
+    trb::DevNode4 w;
+    for (int k = 0; k < 4; ++k) {
+        w.pad[k] = 0;
+        if (sl[k] < 0) { w.lox[k] = w.loy[k] = w.loz[k] = w.hix[k] = w.hiy[k] = w.hiz[k] = 0.f; w.ref[k] = TRB_WIDE_EMPTY; continue; }
+        const BuildNode& c = nodes[sl[k]];
+        w.lox[k] = c.bmin[0]; w.loy[k] = c.bmin[1]; w.loz[k] = c.bmin[2]; w.hix[k] = c.bmax[0]; w.hiy[k] = c.bmax[1]; w.hiz[k] = c.bmax[2];
+        if (c.left >= 0) { next_level[at] = sl[k]; w.ref[k] = int32_t(next_base + at); ++at; }
+        else w.ref[k] = ~int32_t((c.start << 3) | (c.end - c.start));
+    }
+    out[base + uint32_t(i)] = w;
+}
+
 // the per-triangle records in the final primitive order (what flatten_geometry gathers on the host)
 __global__ void k_bb_emit_tris(BuildScene s, const int32_t* __restrict__ ord, trb::DevTri* __restrict__ tris, trb::DevShade* __restrict__ shade,
                                trb::DevTriUV* __restrict__ tri_uv) {

@@ -50,7 +50,6 @@ struct BvhView {
     const F4* nodes;  // 4 x F4 per node (DevNode)
     const F4* tris;   // 3 x F4 per triangle (DevTri)
     int32_t root_ref;
-    int32_t n_top;    // nodes [0, n_top) are the top levels in breadth-first order (host numbering): staged in shared memory by k_trace_coop
 };
 
 #ifndef TRB_STACK

@@ -1,21 +1,35 @@
-// trace_coop.cuh -- warp-cooperative traversal: node traversal per lane, triangle tests redistributed over the warp.
+// trace_coop.cuh -- persistent-warp traversal of the reference's BINARY tree (64 B DevNode), warp-cooperative triangle tests.
 //
-// trace_warp.cuh keeps a lane's postponed triangles private to the lane, so its triangle phase runs with ~15 of 32
-// lanes and its node phase with ~18 (lanes draining triangles, lanes whose pending list is full).  Here the two
-// kinds of work are decoupled through a per-warp queue in shared memory:
-//   * node phase: every lane with a current node tests its two child boxes; a reached leaf (or pair of sibling
-//     leaves = one contiguous range) is pushed triangle by triangle into the warp's queue as (owner lane, triangle);
-//   * triangle phase: runs whenever the queue holds >= 32 entries (or nothing else is left to do); lane i tests
-//     entry i for its OWNER's ray - the ray is read from the owner's registers with warp shuffles - and merges the
-//     result into the owner's record in shared memory: atomicMin on the packed (t bits << 32 | list position) for
-//     closest hits, which IS the reference's rule (min t, ties -> first in the build-reordered list, bvh.h:305), an
-//     OR of flags for occlusion / ill-conditioning.  (u, v) of the winner are recomputed once at completion by the
-//     same arithmetic, hence bit-identical.
-// Everything else (persistent warps with lane refill, straight-line slab tests, pruning, the exhaustive re-trace
-// of ill-conditioned rays, the result resolve) is as in trace_warp.cuh.
+// Since round 2 the production rays go through the 4-wide upper tree (trace_wide.cuh: k_trace_wide); this kernel traces what
+// that one sets aside - rays with a zero / non-finite direction component, for which the reference's NaN behaviour in
+// BBox::intersect (bvh.h:33-69) makes "all ancestors pass" differ from "the leaf passes" - on the reference's own topology.
+// It is also the shared machinery of both kernels (TraceArgs, the per-warp triangle queue):
+//   * persistent warps REFILL idle lanes from the ray queue whenever TRB_FETCH_T lanes are idle (warp ballot + popc ranks, one
+//     atomicAdd per refill), so the loop stays populated and the tail is balanced;
+//   * node phase: every lane with a current node tests its two child boxes; a reached leaf (or pair of sibling leaves = one
+//     contiguous range) is pushed triangle by triangle into the warp's queue in shared memory as (owner lane, triangle);
+//   * triangle phase: runs whenever the queue holds >= 32 entries (or nothing else is left to do); lane i tests entry i for
+//     its OWNER's ray - read from the owner's registers with warp shuffles - and merges the result into the owner's record in
+//     shared memory: atomicMin on the packed (t bits << 32 | list position) for closest hits, which IS the reference's rule
+//     (min t, ties -> first in the build-reordered list, bvh.h:305), an OR of flags for occlusion / ill-conditioning.  (u, v)
+//     of the winner are recomputed once at completion by the same arithmetic, hence bit-identical;
+//   * the exhaustive re-trace of an ill-conditioned ray is a per-lane flag (prune off) on the same code path.
+// Results: closest -> HitT per ray; any -> occlusion byte, or the pending contribution resolved into the frame buffer with
+// atomics (replaces g_FrameBufferLocks, bdpt.h:360-370).
+// Measured and removed in round 2 (notes kept under profiles/): per-lane postponed leaves (r1d), top levels of the tree
+// staged in shared memory (r1n_top_levels_shared.md: 3-7 % slower), sorting the ray queue (r1f_tuning_variants.md).
 #pragma once
-#include "trace_warp.cuh"
+#include "bdpt_common.cuh"
 
+#ifndef TRB_FETCH_T
+#define TRB_FETCH_T 8        // refill when this many lanes are idle
+#endif
+#ifndef TRB_TRACE_BLOCK
+#define TRB_TRACE_BLOCK 128
+#endif
+#ifndef TRB_TRACE_MINBLOCKS
+#define TRB_TRACE_MINBLOCKS 8  // resident blocks per SM the register budget is capped for (8 x 128 threads x 64 registers)
+#endif
 #ifndef TRB_COOP_DRAIN
 #define TRB_COOP_DRAIN 32u    // run a triangle phase when this many tests are queued
 #endif
@@ -23,11 +37,27 @@
 #define TRB_COOP_Q 512u       // queue entries per warp (power of two); a node phase adds at most 8 x 32
 #endif
 
-#ifndef TRB_TOP
-#define TRB_TOP 0             // inner nodes (64 B each) of the top of the tree staged in shared memory per block; 0 = none
-#endif
-
 namespace trbk {
+
+struct TraceArgs {
+    BvhView bvh;             // the reference's binary tree (k_trace_coop)
+    const F4* wnodes;        // the 4-wide upper tree (k_trace_wide); wroot = 0 or a leaf code
+    int32_t wroot;
+    const RayT* rays;
+    const int32_t* q;        // optional indirection (ray / result slot of queue entry k)
+    const uint32_t* n_ptr;   // device-side count (queue length) or nullptr
+    uint32_t n_fixed;
+    uint32_t cap;            // clamp of *n_ptr (queue capacity)
+    HitT* hits;              // closest
+    uint8_t* occ_out;        // any (ABI)
+    const Pending* pend;     // any (wavefront): contribution per shadow ray
+    float* accum;
+    uint32_t* fetch;         // queue cursor of THIS launch (zeroed by the host before the launch)
+    int32_t* defer_q;        // k_trace_wide: slots of the rays it leaves to k_trace_coop, and their count
+    uint32_t* defer_n;
+    unsigned long long* visit;      // TRB_COUNTERS builds: [0] nodes visited, [1] triangles tested
+    unsigned long long* visit_exh;  // TRB_COUNTERS builds: exhaustive re-traces
+};
 
 struct CoopWarp {
     unsigned long long best[32];   // closest: (float bits of t << 32) | list position; init (bits(max_t) << 32)
@@ -42,19 +72,11 @@ template <bool ANY>
 __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_coop(const TraceArgs a) {
     __shared__ CoopWarp sh_all[TRB_TRACE_BLOCK / 32];
     CoopWarp& sh = sh_all[threadIdx.x >> 5];
-#if TRB_TOP > 0
-    // The top levels of the tree (host numbering: breadth-first prefix) in shared memory: a warp whose lanes sit in unrelated
-    // nodes pays one L1 wavefront per lane and load for global memory, four per load for conflict-free 16 B shared reads.
-    extern __shared__ float4 top[];   // TRB_TOP x 64 B, dynamic (may exceed the 48 KB static limit)
-    const int32_t n_top = min(a.bvh.n_top, int32_t(TRB_TOP));
-    for (int i = threadIdx.x; i < n_top * 4; i += TRB_TRACE_BLOCK) { const F4 v = ld4(a.bvh.nodes + i); top[i] = make_float4(v.x, v.y, v.z, v.w); }
-    __syncthreads();
-#endif
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt = (1u << lane) - 1u;
     uint32_t n = a.n_ptr ? *a.n_ptr : a.n_fixed;
-    if (ANY && a.n_ptr) n = min(n, a.cap);
+    if (a.n_ptr) n = min(n, a.cap);
     bool more = true;       // warp-uniform: the ray queue may still hold rays
     uint32_t head = 0;      // warp-uniform read cursor of the triangle queue
 
@@ -157,18 +179,8 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         }
         // ---- node phase ----
         if (cur >= 0) {
-            F4 na, nb, nc, nd;
-#if TRB_TOP > 0
-            if (cur < n_top) {
-                const float4* tp4 = top + 4 * cur;
-                const float4 t0 = tp4[0], t1 = tp4[1], t2 = tp4[2], t3 = tp4[3];
-                na = F4{t0.x, t0.y, t0.z, t0.w}; nb = F4{t1.x, t1.y, t1.z, t1.w}; nc = F4{t2.x, t2.y, t2.z, t2.w}; nd = F4{t3.x, t3.y, t3.z, t3.w};
-            } else
-#endif
-            {
-                const F4* np = a.bvh.nodes + 4 * size_t(cur);
-                na = ld4(np); nb = ld4(np + 1); nc = ld4(np + 2); nd = ld4(np + 3);
-            }
+            const F4* np = a.bvh.nodes + 4 * size_t(cur);
+            const F4 na = ld4(np), nb = ld4(np + 1), nc = ld4(np + 2), nd = ld4(np + 3);
 #ifdef TRB_COUNTERS
             ++c_nodes;
 #endif

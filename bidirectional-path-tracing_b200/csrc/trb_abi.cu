@@ -17,13 +17,8 @@
 #include "kernels/pt_kernels.cuh"
 #include "kernels/di_kernels.cuh"
 #include "kernels/bvh_build.cuh"
-#include "kernels/trace_warp.cuh"
 #include "kernels/trace_coop.cuh"
-#include "kernels/trace_sort.cuh"
-
-#ifndef TRB_COOP
-#define TRB_COOP 1  // 1: warp-cooperative triangle queue (trace_coop.cuh); 0: per-lane postponed leaves (trace_warp.cuh)
-#endif
+#include "kernels/trace_wide.cuh"
 
 using namespace trbk;
 
@@ -46,7 +41,7 @@ struct DevBuf {
     size_t bytes() const { return n * sizeof(T); }
 };
 
-#define TRB_SCENE_ARRAYS 11
+#define TRB_SCENE_ARRAYS 12
 enum LaunchKind { LK_CLOSEST = 0, LK_ANY = 1, LK_LOGIC = 2, LK_N = 3 };
 
 }  // namespace
@@ -60,8 +55,10 @@ struct trb_context {
     // scene
     bool has_scene = false;
     bool built_on_device = false;   // the acceleration structure and the triangle records came from kernels/bvh_build.cuh
+    bool force_binary = false;      // TRB_TRAVERSAL=binary at trb_create: every ray on the reference's binary tree (A/B measurements, tests of k_trace_coop)
     trb::FlatScene flat;
-    DevBuf<trb::DevNode> d_nodes;
+    DevBuf<trb::DevNode> d_nodes;      // the reference's binary tree (degenerate rays, k_pt_check)
+    DevBuf<trb::DevNode4> d_wnodes;   // the 4-wide upper tree (every other ray)
     DevBuf<trb::DevTri> d_tris;
     DevBuf<trb::DevShade> d_shade;
     DevBuf<trb::DevMaterial> d_mats;
@@ -82,8 +79,7 @@ struct trb_context {
     DevBuf<LightVertex> lv;
     DevBuf<int32_t> nlv, q_a, q_b, q_conn;
     DevBuf<uint32_t> pt_ctr;             // path tracer: one counter per queue / traversal launch
-    DevBuf<uint32_t> sort_keys[2], sort_hist[2];   // ray-queue sort (trace_sort.cuh): [0] main stream (closest), [1] shadow stream
-    DevBuf<int32_t> sort_q[2];
+    DevBuf<int32_t> defer_q[2];          // slots of the rays k_trace_wide leaves to the binary tree: [0] main stream (closest hits), [1] shadow stream
     DevBuf<EyeVertex> ev;
     DevBuf<float4> lv_tex, ev_tex;       // textured scenes only: (triangle, u, v) of the stored vertices
     DevBuf<Pending> spend, spend2;
@@ -138,68 +134,41 @@ inline int grid_exact(size_t n) { return int(std::max<size_t>(1, (n + TRB_BLOCK 
 // persistent traversal grid: one wave of resident warps per SM (64 registers/thread -> 8 blocks of 128 per SM)
 inline int trace_grid(int sm_count) { return sm_count * TRB_TRACE_MINBLOCKS; }
 
-// `fetch` is the launch's own queue cursor; the caller has zeroed it on the stream
+// `ctr`: the launch's own TRACE_CTR_WORDS counters (ray-queue cursor, deferred count, cursor of the deferred launch), zeroed by the
+// caller on the stream.  k_trace_wide traces every ray but those with a zero / non-finite direction component, which it appends to
+// defer_q; k_trace_coop then traces those on the reference's binary tree (a grid of warps that find an empty queue and leave).
+int ensure_defer(trb_context* c, int which, size_t n) { TRB_CUDA(c, c->defer_q[which].alloc(n)); return TRB_OK; }
+
 void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, HitT* hits,
-                    uint32_t* fetch, unsigned long long* visit) {
+                    uint32_t* ctr, unsigned long long* visit) {
     TraceArgs a{};
-    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref, c->flat.top_nodes};
-    a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = fetch;
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = ctr;
+    a.defer_q = c->defer_q[0].p; a.defer_n = ctr + 1;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
-#if TRB_COOP
-#if TRB_TOP > 0   // experiment only (compiled out): the attribute is per device, so it is set on every launch's current device
-    cudaFuncSetAttribute(k_trace_coop<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64);
-#endif
-    k_trace_coop<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, c->stream>>>(a);
-#else
-    k_trace_warp<false><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, c->stream>>>(a);
-#endif
+    const int grid = trace_grid(c->prop.multiProcessorCount);
+    if (c->force_binary) { k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a); return; }
+    k_trace_wide<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    a.q = c->defer_q[0].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu)); a.fetch = ctr + 2;
+    k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
 }
 
 void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t cap, uint8_t* occ_out,
-                const Pending* pend, float* accum, uint32_t* fetch, unsigned long long* visit, cudaStream_t stream = nullptr,
-                const int32_t* q = nullptr) {
+                const Pending* pend, float* accum, uint32_t* ctr, unsigned long long* visit, cudaStream_t stream = nullptr) {
+    const int which = (stream && stream != c->stream) ? 1 : 0;
     if (!stream) stream = c->stream;
     TraceArgs a{};
-    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref, c->flat.top_nodes};
-    a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = fetch;
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.rays = rays; a.q = nullptr; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = ctr;
+    a.defer_q = c->defer_q[which].p; a.defer_n = ctr + 1;
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
-#if TRB_COOP
-#if TRB_TOP > 0   // experiment only (compiled out): the attribute is per device, so it is set on every launch's current device
-    cudaFuncSetAttribute(k_trace_coop<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TRB_TOP * 64);
-#endif
-    k_trace_coop<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, TRB_TOP * 64, stream>>>(a);
-#else
-    k_trace_warp<true><<<trace_grid(c->prop.multiProcessorCount), TRB_TRACE_BLOCK, 0, stream>>>(a);
-#endif
-}
-
-// Re-order a ray queue for coherence before it is traversed (kernels/trace_sort.cuh). `which`: 0 = main stream, 1 = shadow stream.
-// Returns the queue to hand to the traversal launch.
-inline bool sort_enabled(const trb_context* c, const trb_render_desc& d) {
-    (void)c;
-    return (d.flags & TRB_FLAG_SORT_RAYS) != 0;  // off by default: measured, the sort costs more than the traversal gains (profiles/r1f_tuning_variants.md)
-}
-const int32_t* sort_queue(trb_context* c, int which, cudaStream_t st, const RayT* rays, const int32_t* q, const uint32_t* n_ptr,
-                          uint32_t n_fixed, uint32_t cap) {
-    SortArgs a{};
-    a.rays = rays; a.q_in = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap;
-    const trb::FlatScene& f = c->flat;
-    a.mnx = f.scene_min[0]; a.mny = f.scene_min[1]; a.mnz = f.scene_min[2];
-    a.sx = 16.f / std::max(f.scene_max[0] - f.scene_min[0], 1e-20f);
-    a.sy = 16.f / std::max(f.scene_max[1] - f.scene_min[1], 1e-20f);
-    a.sz = 16.f / std::max(f.scene_max[2] - f.scene_min[2], 1e-20f);
-    a.keys = c->sort_keys[which].p; a.hist = c->sort_hist[which].p; a.q_out = c->sort_q[which].p;
-    cudaMemsetAsync(a.hist, 0, size_t(TRB_SORT_BINS) * sizeof(uint32_t), st);
-    const int g = c->prop.multiProcessorCount * 8;
-    k_sort_count<<<g, 256, 0, st>>>(a);
-    k_sort_scan<<<1, 1024, 0, st>>>(a.hist);
-    k_sort_scatter<<<g, 256, 0, st>>>(a);
-    return a.q_out;
-}
-int ensure_sort(trb_context* c, size_t n_main, size_t n_shadow) {
-    TRB_CUDA(c, c->sort_keys[0].alloc(n_main)); TRB_CUDA(c, c->sort_q[0].alloc(n_main)); TRB_CUDA(c, c->sort_hist[0].alloc(TRB_SORT_BINS));
-    TRB_CUDA(c, c->sort_keys[1].alloc(n_shadow)); TRB_CUDA(c, c->sort_q[1].alloc(n_shadow)); TRB_CUDA(c, c->sort_hist[1].alloc(TRB_SORT_BINS));
-    return TRB_OK;
+    const int grid = trace_grid(c->prop.multiProcessorCount);
+    if (c->force_binary) { k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a); return; }
+    k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a);
+    a.q = c->defer_q[which].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu)); a.fetch = ctr + 2;
+    k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a);
 }
 
 // depth cap and vertices per subpath of a render description (bdpt.h:68,188: `depth < rrDepth`, depth starts at 1)
@@ -222,6 +191,7 @@ int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     TRB_CUDA(c, c->sray2.alloc(shadow_cap)); TRB_CUDA(c, c->spend2.alloc(shadow_cap));
     if (c->sc.has_tex) { TRB_CUDA(c, c->lv_tex.alloc(P * kk)); TRB_CUDA(c, c->ev_tex.alloc(P)); }
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
+    TRB_CUDA(c, c->defer_q[0].alloc(P)); TRB_CUDA(c, c->defer_q[1].alloc(shadow_cap));
     TRB_CUDA(c, c->d_stats.alloc(8));
     return TRB_OK;
 }
@@ -266,9 +236,11 @@ int trb_create(int device, trb_context** out) {
     if (c->prop.major < 10) {
         g_create_err = "device is not sm_100 class (library is built for sm_100a only)";
         cudaStreamDestroy(c->stream);
+        cudaStreamDestroy(c->stream2);
         delete c;
         return TRB_ERR_NO_DEVICE;
     }
+    if (const char* e = std::getenv("TRB_TRAVERSAL")) c->force_binary = std::string(e) == "binary";
     *out = c;
     return TRB_OK;
 }
@@ -277,7 +249,7 @@ void trb_destroy(trb_context* c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    c->d_nodes.release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
+    c->d_nodes.release(); c->d_wnodes.release(); c->defer_q[0].release(); c->defer_q[1].release(); c->d_tris.release(); c->d_shade.release(); c->d_mats.release(); c->d_emitters.release();
     c->d_etris.release(); c->d_cdf.release(); c->d_esphere.release(); c->pt_ctr.release();
     c->d_tex_info.release(); c->d_tri_uv.release(); c->d_texels.release(); c->lv_tex.release(); c->ev_tex.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->sray2.release(); c->spend2.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
@@ -313,7 +285,7 @@ void scene_array_sizes(const trb::FlatScene& f, size_t sizes[TRB_SCENE_ARRAYS]) 
                                         f.materials.size() * sizeof(trb::DevMaterial), f.emitters.size() * sizeof(trb::DevEmitter),
                                         f.emitter_tris.size() * sizeof(trb::DevEmitterTri), f.emitter_cdf.size() * sizeof(float),
                                         f.emitter_sphere.size() * sizeof(float), f.tex_info.size() * sizeof(trb::DevTexInfo),
-                                        f.n_tri_uv * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float)};
+                                        f.n_tri_uv * sizeof(trb::DevTriUV), f.texels.size() * sizeof(float), f.n_wnodes * sizeof(trb::DevNode4)};
     for (int k = 0; k < TRB_SCENE_ARRAYS; ++k) sizes[k] = v[k];
 }
 
@@ -324,9 +296,9 @@ int stage_scene(trb_context* c) {
     size_t sizes[TRB_SCENE_ARRAYS];
     scene_array_sizes(f, sizes);
     const void* srcs[TRB_SCENE_ARRAYS] = {f.nodes.data(), f.tris.data(), f.shade.data(), f.materials.data(), f.emitters.data(), f.emitter_tris.data(),
-                                          f.emitter_cdf.data(), f.emitter_sphere.data(), f.tex_info.data(), f.tri_uv.data(), f.texels.data()};
-    const bool on_host[TRB_SCENE_ARRAYS] = {!f.nodes.empty(), !f.tris.empty(), !f.shade.empty(), true, true, true, true, true, true, !f.tri_uv.empty(), true};
-    const void* devs[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, c->d_tri_uv.p, nullptr};
+                                          f.emitter_cdf.data(), f.emitter_sphere.data(), f.tex_info.data(), f.tri_uv.data(), f.texels.data(), f.wnodes.data()};
+    const bool on_host[TRB_SCENE_ARRAYS] = {!f.nodes.empty(), !f.tris.empty(), !f.shade.empty(), true, true, true, true, true, true, !f.tri_uv.empty(), true, !f.wnodes.empty()};
+    const void* devs[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, c->d_tri_uv.p, nullptr, c->d_wnodes.p};
     size_t total = 0;
     for (size_t b : sizes) total += (b + 255) & ~size_t(255);
     if (c->pinned) { cudaFreeHost(c->pinned); c->pinned = nullptr; }
@@ -447,7 +419,6 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     f.n_nodes = size_t(root.sub_inner); f.n_tris = n; f.n_tri_uv = f.textured ? n : 0;
     f.root_ref = root.left >= 0 ? 0 : ~int32_t((0u << 3) | n);
     f.max_depth = int32_t(levels.size()) - 1;
-    f.top_nodes = 0;
     for (int k = 0; k < 3; ++k) { f.scene_min[k] = root.bmin[k]; f.scene_max[k] = root.bmax[k]; }
     TRB_CUDA(c, c->d_nodes.alloc(f.n_nodes)); TRB_CUDA(c, c->d_tris.alloc(n)); TRB_CUDA(c, c->d_shade.alloc(n)); TRB_CUDA(c, c->d_tri_uv.alloc(f.n_tri_uv));
     k_bb_emit_nodes<<<gK(total_nodes), B, 0, c->stream>>>(nodes.p, total_nodes, c->d_nodes.p);
@@ -455,6 +426,33 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     TRB_CUDA(c, cudaGetLastError());
     TRB_CUDA(c, cudaStreamSynchronize(c->stream));
     lap("numbering + emit");
+    // the 4-wide upper tree (k_wide_*: the device twin of trb::build_wide_nodes), one level per pass; scratch of the build is re-used
+    f.n_wnodes = 0; f.wide_depth = 0;
+    if (root.left >= 0) {
+        DevBuf<trb::DevNode4> wtmp;
+        struct WGuard { DevBuf<trb::DevNode4>& b; ~WGuard() { b.release(); } } wguard{wtmp};
+        TRB_CUDA(c, wtmp.alloc(f.n_nodes));   // upper bound: every wide node takes at least one binary inner node
+        int32_t* lvl = range_of.p; int32_t* lvl_next = ord_next;
+        int4* slots = reinterpret_cast<int4*>(tmin.p);
+        TRB_CUDA(c, cudaMemsetAsync(lvl, 0, sizeof(int32_t), c->stream));   // the root is node 0 in creation order
+        uint32_t base = 0; int32_t n_level = 1;
+        while (n_level > 0) {
+            if (size_t(base) + size_t(n_level) > f.n_nodes) return c->fail(TRB_ERR_CUDA, "device BVH build: wide node capacity exceeded");
+            k_wide_expand<<<gK(n_level + 1), B, 0, c->stream>>>(nodes.p, lvl, n_level, slots, is_l.p);
+            TRB_CUDA(c, cub::DeviceScan::ExclusiveSum(cub_tmp.p, tmp_bytes, is_l.p, pref.p, n_level + 1, c->stream));
+            k_wide_emit<<<gK(n_level), B, 0, c->stream>>>(nodes.p, n_level, slots, pref.p, base, wtmp.p, lvl_next);
+            uint32_t next_n = 0;
+            TRB_CUDA(c, cudaMemcpyAsync(&next_n, pref.p + n_level, sizeof(next_n), cudaMemcpyDeviceToHost, c->stream));
+            TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+            base += uint32_t(n_level); std::swap(lvl, lvl_next); n_level = int32_t(next_n); ++f.wide_depth;
+        }
+        f.n_wnodes = base;
+        TRB_CUDA(c, c->d_wnodes.alloc(base));
+        TRB_CUDA(c, cudaMemcpyAsync(c->d_wnodes.p, wtmp.p, size_t(base) * sizeof(trb::DevNode4), cudaMemcpyDeviceToDevice, c->stream));
+        TRB_CUDA(c, cudaGetLastError());
+        TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    lap("wide tree");
     if (timing) std::fprintf(stderr, "[trb build] %d levels, %d nodes (%zu inner)\n", int(levels.size()), total_nodes, f.n_nodes);
     return TRB_OK;
 }
@@ -490,8 +488,9 @@ int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags)
     } else {
         if (!trb::flatten_geometry(*s, f, err)) return c->fail(code(), err);
         TRB_CUDA(c, c->d_nodes.alloc(f.n_nodes)); TRB_CUDA(c, c->d_tris.alloc(f.n_tris));
-        TRB_CUDA(c, c->d_shade.alloc(f.n_tris)); TRB_CUDA(c, c->d_tri_uv.alloc(f.n_tri_uv));
+        TRB_CUDA(c, c->d_shade.alloc(f.n_tris)); TRB_CUDA(c, c->d_tri_uv.alloc(f.n_tri_uv)); TRB_CUDA(c, c->d_wnodes.alloc(f.n_wnodes));
     }
+    if (3 * f.wide_depth + 4 > 3 * TRB_STACK) return c->fail(TRB_ERR_UNSUPPORTED, "wide BVH deeper than the traversal stack");
     if (f.max_depth + 2 > TRB_STACK) return c->fail(TRB_ERR_UNSUPPORTED, "BVH deeper than the traversal stack");
     c->built_on_device = on_device;
     c->sc.nodes = reinterpret_cast<const F4*>(c->d_nodes.p);
@@ -505,9 +504,9 @@ int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags)
         // the tables go up directly; the pinned staging blob (geometry read back from the device) is made by the first trb_scene_refresh
         size_t sizes[TRB_SCENE_ARRAYS];
         scene_array_sizes(f, sizes);
-        void* dsts[TRB_SCENE_ARRAYS] = {nullptr, nullptr, nullptr, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p, c->d_tex_info.p, nullptr, c->d_texels.p};
+        void* dsts[TRB_SCENE_ARRAYS] = {nullptr, nullptr, nullptr, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p, c->d_tex_info.p, nullptr, c->d_texels.p, nullptr};
         const void* srcs[TRB_SCENE_ARRAYS] = {nullptr, nullptr, nullptr, f.materials.data(), f.emitters.data(), f.emitter_tris.data(), f.emitter_cdf.data(),
-                                              f.emitter_sphere.data(), f.tex_info.data(), nullptr, f.texels.data()};
+                                              f.emitter_sphere.data(), f.tex_info.data(), nullptr, f.texels.data(), nullptr};
         for (int k = 0; k < TRB_SCENE_ARRAYS; ++k)
             if (dsts[k] && sizes[k]) TRB_CUDA(c, cudaMemcpyAsync(dsts[k], srcs[k], sizes[k], cudaMemcpyHostToDevice, c->stream));
         TRB_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -524,7 +523,7 @@ int trb_scene_refresh(trb_context* c) {
     cudaSetDevice(c->device);
     if (!c->pinned) { int rc = stage_scene(c); if (rc) return rc; }
     void* dsts[TRB_SCENE_ARRAYS] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_mats.p, c->d_emitters.p, c->d_etris.p, c->d_cdf.p, c->d_esphere.p,
-                                    c->d_tex_info.p, c->d_tri_uv.p, c->d_texels.p};
+                                    c->d_tex_info.p, c->d_tri_uv.p, c->d_texels.p, c->d_wnodes.p};
     size_t sizes[TRB_SCENE_ARRAYS];
     scene_array_sizes(c->flat, sizes);
     size_t off = 0;
@@ -537,15 +536,16 @@ int trb_scene_refresh(trb_context* c) {
 }
 
 /* Test hook: the device scene's geometry arrays read back (nodes, triangles, shading records) so that a device-built scene can be
- * compared with a host-built one. which: 0 nodes (64 B), 1 triangles (48 B), 2 shading records (96 B), 3 texture coordinates (32 B). */
+ * compared with a host-built one. which: 0 binary nodes (64 B), 1 triangles (48 B), 2 shading records (96 B), 3 texture coordinates (32 B), 4 wide nodes (128 B). */
 int trb_scene_download(trb_context* c, int which, void* out, size_t capacity_bytes, size_t* count_out) {
     if (!c) return TRB_ERR_INVALID;
     if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     cudaSetDevice(c->device);
     const trb::FlatScene& f = c->flat;
-    const void* src[4] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_tri_uv.p};
-    const size_t cnt[4] = {f.n_nodes, f.n_tris, f.n_tris, f.n_tri_uv}, rec[4] = {sizeof(trb::DevNode), sizeof(trb::DevTri), sizeof(trb::DevShade), sizeof(trb::DevTriUV)};
-    if (which < 0 || which > 3) return c->fail(TRB_ERR_INVALID, "trb_scene_download: which must be 0..3");
+    const void* src[5] = {c->d_nodes.p, c->d_tris.p, c->d_shade.p, c->d_tri_uv.p, c->d_wnodes.p};
+    const size_t cnt[5] = {f.n_nodes, f.n_tris, f.n_tris, f.n_tri_uv, f.n_wnodes};
+    const size_t rec[5] = {sizeof(trb::DevNode), sizeof(trb::DevTri), sizeof(trb::DevShade), sizeof(trb::DevTriUV), sizeof(trb::DevNode4)};
+    if (which < 0 || which > 4) return c->fail(TRB_ERR_INVALID, "trb_scene_download: which must be 0..4");
     if (count_out) *count_out = cnt[which];
     if (!out) return TRB_OK;
     if (capacity_bytes < cnt[which] * rec[which]) return c->fail(TRB_ERR_INVALID, "trb_scene_download: buffer too small");
@@ -613,18 +613,14 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         if (last_any_of_buf[b] >= 0) cudaStreamWaitEvent(c->stream, c->dep_b[last_any_of_buf[b]], 0);
     };
     const bool overlap = (d.flags & TRB_FLAG_NO_OVERLAP) == 0;
-    const bool sort = sort_enabled(c, d);
     auto closest = [&](const RayT* rays, const int32_t* q, const uint32_t* n_ptr, uint32_t n_fixed, uint32_t* fetch) {
-        if (sort) { q = sort_queue(c, 0, c->stream, rays, q, n_ptr, n_fixed, 0xffffffffu); c->mark(LK_LOGIC); }
         launch_closest(c, rays, q, n_ptr, n_fixed, p.hit, fetch, visit); c->mark(LK_CLOSEST);
     };
     auto trace_shadow = [&]() {          // after the bounce kernel(s) of a stage
         const int b = n_any & 1;
         if (!overlap) {
-            const int32_t* sq = sort ? sort_queue(c, 1, c->stream, p.sray, nullptr, p.counters + CTR_SHADOW, 0u, p.shadow_cap) : nullptr;
-            if (sort) c->mark(LK_LOGIC);
             launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
-                       visit ? visit + 2 : nullptr, c->stream, sq);
+                       visit ? visit + 2 : nullptr, c->stream);
             c->mark(LK_ANY);
             ++n_any;
             return;
@@ -632,10 +628,8 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
         cudaEventRecord(c->dep_a[n_any], c->stream);
         cudaStreamWaitEvent(c->stream2, c->dep_a[n_any], 0);
         c->mark(-1, true);
-        const int32_t* sq = sort ? sort_queue(c, 1, c->stream2, p.sray, nullptr, p.counters + CTR_SHADOW, 0u, p.shadow_cap) : nullptr;
-        if (sort) c->mark(LK_LOGIC, true);
         launch_any(c, p.sray, p.counters + CTR_SHADOW, 0u, p.shadow_cap, nullptr, p.spend, p.accum, p.counters + CTR_FETCH_ANY,
-                   visit ? visit + 2 : nullptr, c->stream2, sq);
+                   visit ? visit + 2 : nullptr, c->stream2);
         c->mark(LK_ANY, true);
         cudaEventRecord(c->dep_b[n_any], c->stream2);
         last_any_of_buf[b] = n_any;
@@ -736,7 +730,6 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");  // (slot << 6 | vertex) pair words
     rc = ensure_wave(c, size_t(P), K);
     if (rc) return rc;
-    if (sort_enabled(c, *d)) { rc = ensure_sort(c, size_t(P), c->sray.n); if (rc) return rc; }
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -803,13 +796,13 @@ int run_pt_wave(trb_context* c, const WaveRun& w, const PtParams& pt, const trb:
     const int D = pt.cap, M = pt.emitter_samples, NB = pt.bsdf_samples;
     // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then the other queues, then one fetch cursor per traversal launch
     const size_t n_ray = size_t(D) * size_t(1 + M + NB) + size_t(pt.max_depth >= 0 ? pt.max_depth : 0) + 8;
-    const size_t n_other = size_t(D) + 8, n_fetch = n_ray + 8;
+    const size_t n_other = size_t(D) + 8, n_fetch = TRACE_CTR_WORDS * (n_ray + 8);
     TRB_CUDA(c, c->pt_ctr.alloc(n_ray + n_other + n_fetch));
     TRB_CUDA(c, cudaMemsetAsync(c->pt_ctr.p, 0, (n_ray + n_other + n_fetch) * sizeof(uint32_t), c->stream));
     size_t i_ray = 0, i_other = n_ray, i_fetch = n_ray + n_other;
     auto ray_ctr = [&]() { return c->pt_ctr.p + i_ray++; };
     auto other_ctr = [&]() { return c->pt_ctr.p + i_other++; };
-    auto fetch_ctr = [&]() { return c->pt_ctr.p + i_fetch++; };
+    auto fetch_ctr = [&]() { uint32_t* f = c->pt_ctr.p + i_fetch; i_fetch += TRACE_CTR_WORDS; return f; };
     unsigned long long* visit = nullptr;
 #ifdef TRB_COUNTERS
     visit = c->d_stats.p + 2;
@@ -920,7 +913,7 @@ int run_di_wave(trb_context* c, const WaveRun& w, const DiParams& dp, const trb:
     const int M = dp.strategy == DI_BSDF ? 0 : dp.emitter_samples;
     const int NB = (dp.strategy == DI_MIS || dp.strategy == DI_BSDF) ? dp.bsdf_samples : 0;
     // counters: [0, n_ray) sizes of the traced queues (their sum + P = rays traced), then one fetch cursor per traversal launch
-    const size_t n_ray = size_t(M + NB) + 8, n_fetch = n_ray + 8;
+    const size_t n_ray = size_t(M + NB) + 8, n_fetch = TRACE_CTR_WORDS * (n_ray + 8);
     TRB_CUDA(c, c->pt_ctr.alloc(n_ray + n_fetch));
     TRB_CUDA(c, cudaMemsetAsync(c->pt_ctr.p, 0, (n_ray + n_fetch) * sizeof(uint32_t), c->stream));
     size_t i_ray = 0, i_fetch = n_ray;
@@ -930,13 +923,14 @@ int run_di_wave(trb_context* c, const WaveRun& w, const DiParams& dp, const trb:
 #endif
     const int gP = grid_exact(size_t(P));
     k_gen_camera<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
-    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, c->pt_ctr.p + i_fetch++, visit); c->mark(LK_CLOSEST);
+    auto fetch_ctr = [&]() { uint32_t* f = c->pt_ctr.p + i_fetch; i_fetch += TRACE_CTR_WORDS; return f; };
+    launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
     k_di_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
     for (int phase = 0; phase < 2; ++phase)
         for (int i = 0; i < (phase == 0 ? M : NB); ++i) {
             uint32_t* n_try = c->pt_ctr.p + i_ray++;
             k_di_gen<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp, phase, c->q_conn.p, n_try); c->mark(LK_LOGIC);
-            launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, c->pt_ctr.p + i_fetch++, visit); c->mark(LK_CLOSEST);
+            launch_closest(c, p.ray, c->q_conn.p, n_try, 0u, p.hit, fetch_ctr(), visit); c->mark(LK_CLOSEST);
             k_di_resolve<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp, phase, c->q_conn.p, n_try); c->mark(LK_LOGIC);
         }
     k_di_combine<<<gP, TRB_BLOCK, 0, c->stream>>>(p, dp); c->mark(LK_LOGIC);
@@ -1312,8 +1306,9 @@ int trace_device(trb_context* c, bool any, const RayT* d_rays, size_t n, HitT* d
     visit = c->d_stats.p + 2;
 #endif
     if (n) {
-        TRB_CUDA(c, c->fetch_ctr.alloc(1));
-        TRB_CUDA(c, cudaMemsetAsync(c->fetch_ctr.p, 0, sizeof(uint32_t), c->stream));
+        TRB_CUDA(c, c->fetch_ctr.alloc(TRACE_CTR_WORDS));
+        TRB_CUDA(c, cudaMemsetAsync(c->fetch_ctr.p, 0, TRACE_CTR_WORDS * sizeof(uint32_t), c->stream));
+        TRB_CUDA(c, c->defer_q[0].alloc(n));
         if (any) launch_any(c, d_rays, nullptr, uint32_t(n), uint32_t(n), d_occ, nullptr, nullptr, c->fetch_ctr.p, visit ? visit + 2 : nullptr);
         else launch_closest(c, d_rays, nullptr, nullptr, uint32_t(n), d_hits, c->fetch_ctr.p, visit);
     }
@@ -1409,7 +1404,6 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
     if (stride < size_t(10 + 10 * K)) return c->fail(TRB_ERR_INVALID, "trb_bdpt_paths: rng stride must be >= 10 + 10*K, K = max vertices per subpath");
     rc = ensure_wave(c, n, K);
     if (rc) return rc;
-    if (sort_enabled(c, *d)) { rc = ensure_sort(c, n, c->sray.n); if (rc) return rc; }
     DevBuf<RayT> d_rays; DevBuf<float> d_rng, d_acc; DevBuf<int32_t> d_pix, d_draws;
     TRB_CUDA(c, d_rays.alloc(n)); TRB_CUDA(c, d_rng.alloc(n * stride)); TRB_CUDA(c, d_acc.alloc(n * size_t(K + 1) * 3));
     TRB_CUDA(c, d_pix.alloc(n * size_t(K))); TRB_CUDA(c, d_draws.alloc(n));

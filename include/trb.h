@@ -125,8 +125,8 @@ typedef struct trb_render_desc {
  * behaviour: rr_depth is a hard cap.  renderer.rrProb is read but never used by the reference (bdpt.h:40). */
 #define TRB_FLAG_RUSSIAN_ROULETTE 4u
 #define TRB_RR_DEFAULT_MAX_DEPTH 32
-/* Experiment switch: counting sort of each ray queue by (origin cell, direction) before it is traversed.  Same results;
- * traversal gets 10-15 % faster, the sort costs more than that (profiles/r1f_tuning_variants.md), so it is off by default. */
+/* Accepted and ignored.  (Round 1 had an experiment behind it: a counting sort of each ray queue before traversal; the traversal got
+ * 10-15 % faster and the sort cost more than that - profiles/r1f_tuning_variants.md - so the code was removed in round 2.) */
 #define TRB_FLAG_SORT_RAYS 8u
 
 /* PathTracerIntegrator settings (Config::integratorSettings.pt, core.h:229-236; TOML defaults main.cpp:94-102).

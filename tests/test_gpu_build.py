@@ -24,7 +24,7 @@ def _compare(trb, scene, label):
         host.upload(scene, build="host")
         dev.upload(scene, build="device")
         assert dev.built_on_device() and not host.built_on_device()
-        for which in ("nodes", "tris", "shade", "tri_uv"):
+        for which in ("nodes", "wnodes", "tris", "shade", "tri_uv"):
             a, b = host.download(which), dev.download(which)
             assert _same(a, b), f"{label}: {which} differ ({len(a)} vs {len(b)} records)"
         assert host.scene_bytes() == dev.scene_bytes()

@@ -38,3 +38,89 @@ extern "C" int hc_trace(const trb_scene_desc* s, const float* rays8, long n, int
     counters[0] = nn; counters[1] = nt; counters[2] = nill;
     return 0;
 }
+
+#include "../bidirectional-path-tracing_b200/csrc/kernels/trace_wide.cuh"
+
+// the 4-wide upper tree (trace_wide.cuh) on the same rays; counters: nodes, boxes, tris, max stack, degenerate rays
+extern "C" int hc_trace_wide(const trb_scene_desc* s, const float* rays8, long n, int any, float* tuv, int* tri_out,
+                             unsigned char* occ, unsigned long long* counters) {
+    static trb::FlatScene fs;            // cached across calls on the same scene pointer (development aid)
+    static const void* cached = nullptr;
+    std::string err;
+    if (cached != s->positions) {
+        if (!trb::flatten_scene(*s, fs, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        cached = s->positions;
+    }
+    trbk::BvhView bv{reinterpret_cast<const trbk::F4*>(fs.nodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.root_ref};
+    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(fs.wnodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.wnodes.empty() ? fs.root_ref : 0};
+    trbk::WideCounters c{0, 0, 0, 0};
+    unsigned long long nn = 0, nb = 0, nt = 0, ndeg = 0;
+    for (long i = 0; i < n; ++i) {
+        trbk::RayT r; memcpy(&r, rays8 + 8 * i, 32);
+        trbk::HitT h; bool oc = false;
+        if (trbk::ray_pre(r).degenerate) ++ndeg;
+        c.nodes = c.boxes = c.tris = 0;
+        if (any) trbk::trace_ray_wide<true>(wv, bv, r, &h, &oc, &c); else trbk::trace_ray_wide<false>(wv, bv, r, &h, &oc, &c);
+        nn += c.nodes; nb += c.boxes; nt += c.tris;
+        if (any) occ[i] = oc;
+        else {
+            tuv[3 * i] = h.t; tuv[3 * i + 1] = h.u; tuv[3 * i + 2] = h.v;
+            tri_out[i] = h.pos >= 0 ? fs.tris[h.pos].tri : -1;
+        }
+    }
+    counters[0] = nn; counters[1] = nb; counters[2] = nt; counters[3] = c.max_sp; counters[4] = ndeg;
+    counters[5] = fs.wnodes.size(); counters[6] = fs.nodes.size(); counters[7] = (unsigned long long)fs.wide_depth;
+    return 0;
+}
+
+// The claim the wide tree rests on (tr_host.h: DevNode4), checked by brute force against the reference's own box test restated
+// in trace.cuh (box_exact = bvh.h:33-69): over EVERY leaf of the reference's tree, "the leaf box passes" must imply "every ancestor
+// box passes" for a ray whose direction has three finite non-zero components.  out[0] non-degenerate rays, out[1] (ray, leaf)
+// pairs whose leaf box passes, out[2] of those with a failing ancestor (must be 0), out[3] degenerate rays (excluded),
+// out[4] the same violation count among the degenerate rays (informational: why they keep the binary tree).
+#include <thread>
+extern "C" int hc_leaf_implies_ancestors(const trb_scene_desc* s, const float* rays8, long n, unsigned long long* out) {
+    trb::RefTree tree; std::string err;
+    if (!trb::build_ref_tree(*s, tree, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+    const size_t nn = tree.nodes.size();
+    std::vector<int32_t> parent(nn, -1);
+    for (size_t i = 0; i < nn; ++i) if (tree.nodes[i].left >= 0) { parent[tree.nodes[i].left] = int32_t(i); parent[tree.nodes[i].right] = int32_t(i); }
+    const unsigned T = std::max(1u, std::min(std::thread::hardware_concurrency(), 16u));
+    std::vector<std::vector<unsigned long long>> part(T, std::vector<unsigned long long>(5, 0));
+    auto work = [&](unsigned tid) {
+        std::vector<unsigned char> pass(nn);
+        auto& c = part[tid];
+        for (long i = tid; i < n; i += T) {
+            trbk::RayT r; memcpy(&r, rays8 + 8 * i, 32);
+            const bool deg = trbk::ray_pre(r).degenerate;
+            ++c[deg ? 3 : 0];
+            for (size_t k = 1; k < nn; ++k) {   // the root's own box is never tested (bvh.h:276)
+                const auto& b = tree.nodes[k];
+                pass[k] = trbk::box_exact(b.bmin[0], b.bmin[1], b.bmin[2], b.bmax[0], b.bmax[1], b.bmax[2], r.ox, r.oy, r.oz, r.dx, r.dy, r.dz).hit;
+            }
+            pass[0] = 1;
+            for (size_t k = 1; k < nn; ++k) {
+                if (tree.nodes[k].left >= 0 || !pass[k]) continue;
+                if (!deg) ++c[1];
+                bool anc = true;
+                for (int32_t a = parent[k]; a > 0; a = parent[a]) anc = anc && pass[a];
+                if (!anc) ++c[deg ? 4 : 2];
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (unsigned t = 1; t < T; ++t) th.emplace_back(work, t);
+    work(0);
+    for (auto& t : th) t.join();
+    for (int k = 0; k < 5; ++k) { out[k] = 0; for (unsigned t = 0; t < T; ++t) out[k] += part[t][k]; }
+    return 0;
+}
+
+// the host-built wide nodes (structure tests)
+extern "C" int hc_wide_nodes(const trb_scene_desc* s, void* out, size_t* n) {
+    trb::FlatScene fs; std::string err;
+    if (!trb::flatten_scene(*s, fs, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+    if (out) memcpy(out, fs.wnodes.data(), std::min(*n, fs.wnodes.size()) * sizeof(trb::DevNode4));
+    *n = fs.wnodes.size();
+    return 0;
+}

@@ -22,7 +22,7 @@ for name in ("caustic", "tess"):
     kw = dict(width=96, height=72, spp=3, rr_depth=8, wave_samples=5000)
     a, st = ctx.render_bdpt(trb.render_desc(**kw))
     b, _ = ctx.render_bdpt(trb.render_desc(flags=trb.TRB_FLAG_RUSSIAN_ROULETTE, **dict(kw, rr_depth=4)))
-    c, _ = ctx.render_bdpt(trb.render_desc(flags=trb.TRB_FLAG_NO_OVERLAP | trb.TRB_FLAG_SORT_RAYS, **kw))
+    c, _ = ctx.render_bdpt(trb.render_desc(flags=trb.TRB_FLAG_NO_OVERLAP, **kw))
     d, _ = ctx.render_path(trb.render_desc(**dict(kw, rr_depth=5)), trb.path_desc())
     e, _ = ctx.render_path(trb.render_desc(**dict(kw, rr_depth=5)), trb.path_desc(True, 3, 0.95, 2, 2))
     f, _ = ctx.render_path(trb.render_desc(**dict(kw, rr_depth=5)), trb.path_desc(False, 4))
