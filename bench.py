@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--spp", type=int, default=16, help="samples per pixel per GPU per step")
     ap.add_argument("--wave", type=int, default=0, help="samples per wavefront (0 = library default)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-visits", action="store_true", help="skip the counters-build pass (A/B runs: no roofline figure)")
     ap.add_argument("--_visits", action="store_true", help=argparse.SUPPRESS)  # internal: counters build, prints visit stats
     return ap.parse_args()
 
@@ -370,7 +371,7 @@ def run_ours(args):
         out["stage_ms_serial"] = {k: ser[k] for k in ("ms_total", "ms_trace_closest", "ms_trace_any", "ms_logic")}
         agg_s = {k: ser[k] * args.steps for k in ser}  # same units as agg (sums over args.steps steps)
         peak, how = measured_peak()
-        vis = visits_subprocess(args) if world == 1 else None
+        vis = visits_subprocess(args) if (world == 1 and not args.no_visits) else None
         any_dom = agg_s["ms_trace_any"] >= agg_s["ms_trace_closest"]
         dom = "k_trace_coop<1>" if any_dom else "k_trace_coop<0>"   # <1>: occlusion + resolve, <0>: closest hit
         K = wl["rr_depth"] - 1

@@ -19,7 +19,7 @@ import numpy as np
 PKG_DIR = Path(__file__).resolve().parent
 LIB_PATH = PKG_DIR / "libtrb.so"
 
-TRB_OK = 0
+TRB_OK, TRB_ERR_INVALID, TRB_ERR_NO_DEVICE, TRB_ERR_CUDA, TRB_ERR_NO_SCENE, TRB_ERR_IO, TRB_ERR_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6
 TRB_FLAG_NO_JITTER = 1
 TRB_FLAG_NO_OVERLAP = 2
 TRB_FLAG_RUSSIAN_ROULETTE = 4  # the reference's NO_RR 0 behaviour (bdpt.h:18,68,129); default off = shipped behaviour
@@ -96,7 +96,8 @@ class Stats(C.Structure):
                 ("ms_logic", C.c_double), ("samples", C.c_uint64), ("rays_closest", C.c_uint64),
                 ("rays_any", C.c_uint64), ("launches", C.c_uint64), ("node_visits", C.c_uint64),
                 ("tri_tests", C.c_uint64), ("node_visits_any", C.c_uint64), ("tri_tests_any", C.c_uint64),
-                ("retraces", C.c_uint64), ("retraces_any", C.c_uint64)]
+                ("retraces", C.c_uint64), ("retraces_any", C.c_uint64), ("rays_deferred", C.c_uint64), ("rays_deferred_any", C.c_uint64),
+                ("node_visits_bin", C.c_uint64), ("tri_tests_bin", C.c_uint64), ("node_visits_bin_any", C.c_uint64), ("tri_tests_bin_any", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -114,12 +115,12 @@ assert RAY_DTYPE.itemsize == 32 and HIT_DTYPE.itemsize == 32 and MATERIAL_DTYPE.
 assert BSDF_QUERY_DTYPE.itemsize == 40 and BSDF_OUT_DTYPE.itemsize == 48
 # device scene records (csrc/host/tr_host.h), for Context.download
 DEV_NODE_DTYPE = np.dtype([("c0min", "<f4", 3), ("c0max", "<f4", 3), ("c1min", "<f4", 3), ("c1max", "<f4", 3), ("ref0", "<i4"), ("ref1", "<i4"), ("pad", "<i4", 2)])
+DEV_NODE4_DTYPE = np.dtype([("half", DEV_NODE_DTYPE, 2)])   # two DevNode-shaped halves: children 0,1 and 2,3
+assert DEV_NODE4_DTYPE.itemsize == 128
 DEV_TRI_DTYPE = np.dtype([("v0", "<f4", 3), ("tri", "<i4"), ("e1", "<f4", 3), ("illk", "<f4"), ("e2", "<f4", 3), ("flags", "<i4")])
 DEV_SHADE_DTYPE = np.dtype([("v0", "<f4", 3), ("shape", "<i4"), ("v1", "<f4", 3), ("prim", "<i4"), ("v2", "<f4", 3), ("mat", "<i4"),
                             ("n0", "<f4", 3), ("emitter", "<i4"), ("n1", "<f4", 3), ("tri", "<i4"), ("n2", "<f4", 3), ("pad", "<i4")])
 DEV_TRI_UV_DTYPE = np.dtype([("st", "<f4", (3, 2)), ("pad", "<f4", 2)])
-DEV_NODE4_DTYPE = np.dtype([("lox", "<f4", 4), ("loy", "<f4", 4), ("loz", "<f4", 4), ("hix", "<f4", 4), ("hiy", "<f4", 4), ("hiz", "<f4", 4), ("ref", "<i4", 4), ("pad", "<i4", 4)])
-assert DEV_NODE4_DTYPE.itemsize == 128
 assert DEV_NODE_DTYPE.itemsize == 64 and DEV_TRI_DTYPE.itemsize == 48 and DEV_SHADE_DTYPE.itemsize == 96 and DEV_TRI_UV_DTYPE.itemsize == 32
 
 _lib = None

@@ -90,6 +90,35 @@ int trb_host_load_checkpoint(const char* path, trb_checkpoint_info* info_out, fl
     return TRB_OK;
 }
 
+uint64_t trb_host_scene_hash(const trb_scene_desc* s) {
+    if (!s) return 1;
+    uint64_t h = 1469598103934665603ull;
+    auto mix = [&](const void* p, size_t bytes) {
+        const unsigned char* b = static_cast<const unsigned char*>(p);
+        // 8 bytes per step (FNV-1a over 64-bit words, tail by bytes): the geometry of a 10 M-triangle scene is ~0.5 GB
+        size_t i = 0;
+        for (; i + 8 <= bytes; i += 8) { uint64_t w; std::memcpy(&w, b + i, 8); h = (h ^ w) * 1099511628211ull; }
+        for (; i < bytes; ++i) h = (h ^ b[i]) * 1099511628211ull;
+    };
+    const uint64_t counts[8] = {s->n_positions, s->n_normals, s->n_tris, s->n_materials, s->n_shapes, s->n_texcoords, s->n_textures, 0};
+    mix(counts, sizeof(counts));
+    if (s->positions) mix(s->positions, s->n_positions * 3 * sizeof(float));
+    if (s->normals) mix(s->normals, s->n_normals * 3 * sizeof(float));
+    if (s->tri_v) mix(s->tri_v, s->n_tris * 3 * sizeof(int32_t));
+    if (s->tri_n) mix(s->tri_n, s->n_tris * 3 * sizeof(int32_t));
+    if (s->tri_mat) mix(s->tri_mat, s->n_tris * sizeof(int32_t));
+    if (s->tri_shape) mix(s->tri_shape, s->n_tris * sizeof(int32_t));
+    if (s->materials) mix(s->materials, s->n_materials * sizeof(trb_material));
+    if (s->texcoords) mix(s->texcoords, s->n_texcoords * 2 * sizeof(float));
+    if (s->tri_t) mix(s->tri_t, s->n_tris * 3 * sizeof(int32_t));
+    for (size_t t = 0; s->textures && t < s->n_textures; ++t) {
+        const int32_t wh[2] = {s->textures[t].width, s->textures[t].height};
+        mix(wh, sizeof(wh));
+        if (s->textures[t].rgb && wh[0] > 0 && wh[1] > 0) mix(s->textures[t].rgb, size_t(wh[0]) * wh[1] * 3 * sizeof(float));
+    }
+    return h ? h : 1;
+}
+
 int trb_host_checkpoint_matches(const trb_checkpoint_info* a, const trb_checkpoint_info* b) {
     return (a && b && trb::checkpoint_matches(*a, *b)) ? 1 : 0;
 }

@@ -10,7 +10,8 @@
 //     non-degenerate corner (tiny_obj_loader.h:1043-1239) - not fanned;
 //   * `o` and `g` start a new shape, `usemtl` only switches the material of following faces
 //     (tiny_obj_loader.h:1861-1990); shapes without faces are dropped.
-// tests/test_loader.py pins this file against the reference's tinyobj output for every shipped scene.
+// tests/test_host.py (test_reference_loader_parity_if_available, test_obj_loader_semantics) and tools/gen_golden.py pin this file
+// against the reference's tinyobj output for every shipped scene.
 #include <cmath>
 #include <cstdio>
 #include <cstring>

@@ -374,17 +374,16 @@ void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& 
                 DevNode4& w = out[base + i];
                 uint32_t at = first_inner[i];
                 for (int k = 0; k < 4; ++k) {
+                    DevNode4::Half& hf = w.half[k >> 1];
+                    float* mn = (k & 1) ? hf.c1min : hf.c0min; float* mx = (k & 1) ? hf.c1max : hf.c0max;
+                    int32_t& ref = (k & 1) ? hf.ref1 : hf.ref0;
+                    hf.pad0 = hf.pad1 = 0;
                     const int32_t ci = slots[4 * i + k];
-                    if (ci < 0) {
-                        w.lox[k] = w.loy[k] = w.loz[k] = w.hix[k] = w.hiy[k] = w.hiz[k] = 0.f; w.ref[k] = TRB_WIDE_EMPTY;
-                    } else {
-                        const RefTree::Node& c = tree.nodes[ci];
-                        w.lox[k] = c.bmin[0]; w.loy[k] = c.bmin[1]; w.loz[k] = c.bmin[2];
-                        w.hix[k] = c.bmax[0]; w.hiy[k] = c.bmax[1]; w.hiz[k] = c.bmax[2];
-                        if (c.left >= 0) { next[at] = ci; w.ref[k] = int32_t(next_base + at); ++at; }
-                        else w.ref[k] = ~int32_t((c.start << 3) | c.count);
-                    }
-                    w.pad[k] = 0;
+                    if (ci < 0) { for (int a = 0; a < 3; ++a) mn[a] = mx[a] = 0.f; ref = TRB_WIDE_EMPTY; continue; }
+                    const RefTree::Node& c = tree.nodes[ci];
+                    for (int a = 0; a < 3; ++a) { mn[a] = c.bmin[a]; mx[a] = c.bmax[a]; }
+                    if (c.left >= 0) { next[at] = ci; ref = int32_t(next_base + at); ++at; }
+                    else ref = ~int32_t((c.start << 3) | c.count);
                 }
             }
         });

@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstring>
 #include <iostream>
+#include <mutex>
 #include <thread>
 
 #include "tr_host.h"
@@ -265,7 +266,9 @@ v3f BDPTIntegrator::render(const Ray& ray, Sampler& sampler) const {
     if (trb_bdpt_paths(c, &d, &r, rng.data(), 1, stride, li, pix.data(), srgb.data(), &draws) != TRB_OK)
         throw std::runtime_error(std::string("BDPTIntegrator::render: ") + trb_last_error(c));
     for (int k = 0; k < draws; ++k) sampler.next();
-    if (rgb) {  // light-tracing splats land in the frame buffer as a side effect (bdpt.h:360-370)
+    if (rgb) {  // light-tracing splats land in the frame buffer as a side effect (bdpt.h:360-370); the reference takes a per-pixel lock there
+        static std::mutex splat_lock;   // one lock for the few splats of a sample: render() may be called from several host threads
+        std::lock_guard<std::mutex> guard(splat_lock);
         for (int k = 0; k < K; ++k)
             if (pix[k] >= 0 && pix[k] < rgb->width * rgb->height) rgb->data[pix[k]] += v3f(srgb[3 * k], srgb[3 * k + 1], srgb[3 * k + 2]);
     }
@@ -493,7 +496,8 @@ void Renderer::render() {
     trb_checkpoint_info me;
     integrator->describe(me);
     const trb_scene_desc* sd = scene.desc();
-    me.scene_hash = sd ? (uint64_t(sd->n_tris) * 1000003ull) ^ (uint64_t(sd->n_positions) << 20) ^ uint64_t(sd->n_materials) : 0;
+    me.scene_hash = trb_host_scene_hash(sd);   // content of every scene array: an edited OBJ / MTL / texture starts a new render
+    if (cfg.gpus > 1) std::printf("Checkpointed renders run on one device (gpus = %d ignored): each slice is rendered by context 0\n", cfg.gpus);
     float* out = reinterpret_cast<float*>(integrator->rgb->data.get());
     const size_t nf = size_t(cfg.width) * cfg.height * 3;
     int done = 0;

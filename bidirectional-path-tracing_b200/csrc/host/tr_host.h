@@ -56,12 +56,16 @@ static_assert(sizeof(DevNode) == 64, "node must be 64 B");
 // collapsed to four children per node (the child of largest surface area is opened first): half the dependent fetches per
 // ray.  Leaves, their exact boxes and the primitive order (= the tie-break rank) are the reference's.  Rays with a zero or
 // non-finite direction component (NaN poisoning in the slab test, where the equivalence does not hold) are traced on the
-// binary DevNode tree.  SoA over the four children: 7 x LDG.128.
+// binary DevNode tree.  Laid out as two 64-byte halves of two children each (the DevNode layout twice), 32-byte aligned
+// pieces: 4 x LDG.256 per node (sm_100 has 256-bit global loads), and a half is consumed as soon as its two loads land.
 #define TRB_WIDE_EMPTY INT32_MIN   // an unused child slot (never a leaf code: first < 2^27)
-struct alignas(16) DevNode4 {
-    float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
-    int32_t ref[4];   // >= 0: wide node index; < 0: leaf, ~ref = (first << 3) | count; TRB_WIDE_EMPTY: unused slot
-    int32_t pad[4];
+struct alignas(32) DevNode4 {
+    struct Half {
+        float c0min[3], c0max[3];
+        float c1min[3], c1max[3];
+        int32_t ref0, ref1;   // >= 0: wide node index; < 0: leaf, ~ref = (first << 3) | count; TRB_WIDE_EMPTY: unused slot
+        int32_t pad0, pad1;
+    } half[2];                // children 0,1 and 2,3 in the reference's left-to-right order
 };
 static_assert(sizeof(DevNode4) == 128, "wide node must be 128 B");
 

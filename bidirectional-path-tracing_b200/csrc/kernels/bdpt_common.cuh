@@ -102,8 +102,10 @@ enum : uint32_t { TRACE_CTR_WORDS = 3 };
 enum : uint32_t { SLOT_PURE_SPECULAR = 1u };
 
 // ---- random numbers ----------------------------------------------------------------------------------
-// Production: counter-based, keyed by (seed, pixel, sample index, dimension) - independent of wave size and
-// GPU count, disjoint across samples.  Parity: the caller's floats, consumed in the reference's order (Q17).
+// Production: counter-based, keyed by (seed, pixel, sample index, dimension) - independent of wave size and GPU count.  The key
+// is 64 bits (two independent 32-bit hashes of the triple): configs[3] renders 3840 x 2160 x 4096 = 3.4e10 samples, eight times
+// the 2^32 streams a 32-bit key can name, and a shared stream would repeat jitter, light and eye subpaths at two pixels.
+// Parity: the caller's floats, consumed in the reference's order (Q17).
 __device__ __forceinline__ uint32_t mix32(uint32_t x) {
     x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
     return x;
@@ -111,12 +113,13 @@ __device__ __forceinline__ uint32_t mix32(uint32_t x) {
 struct Rng {
     const float* inj;  // parity mode pointer to this path's row, or nullptr
     uint32_t key;      // hash of (seed, pixel, sample)
+    uint32_t key2;     // a second, independent hash of the same triple
     uint32_t ctr;
     uint32_t lim;      // parity mode: floats in the row; past its end every draw reads 0.99 (ends any roulette)
     __device__ __forceinline__ float next() {
         uint32_t c = ctr++;
         if (inj) return c < lim ? inj[c] : 0.99f;
-        uint32_t h = mix32(key ^ mix32(c * 0x9e3779b9u + 0x85ebca6bu));
+        uint32_t h = mix32(key2 ^ mix32(key ^ mix32(c * 0x9e3779b9u + 0x85ebca6bu)));
         return float(h >> 8) * (1.0f / 16777216.0f);
     }
 };
@@ -124,6 +127,7 @@ __device__ __forceinline__ Rng make_rng(const WaveParams& p, int slot, uint32_t 
     Rng r;
     r.inj = p.inject_rng ? p.inject_rng + size_t(slot) * p.inject_stride : nullptr;
     r.key = mix32(p.seed ^ mix32(pixel * 0x9e3779b9u + 0x7f4a7c15u) ^ mix32(sample * 0x85ebca6bu + 0xc2b2ae35u));
+    r.key2 = mix32(mix32(p.seed + 0x632be5abu) + pixel * 0xcc9e2d51u) ^ mix32(sample * 0x1b873593u + 0x68e31da4u);
     r.ctr = ctr;
     r.lim = uint32_t(p.inject_stride);
     return r;

@@ -352,7 +352,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
     float4 sv = make_float4(0.f, 0.f, 0.f, 0.f);
     uint32_t pixel = 0, sample = 0, li_target = 0;
     const float li_scale = p.parity ? 1.f : (1.f / p.spp);  // renderer.cpp:201: averageRadiance * (1.f / spp)
-    Rng rng; rng.inj = nullptr; rng.key = 0; rng.ctr = 0; rng.lim = 0;
+    Rng rng; rng.inj = nullptr; rng.key = 0; rng.key2 = 0; rng.ctr = 0; rng.lim = 0;
     if (in) {
         RayT r = p.ray[slot];
         HitT h = p.hit[slot];

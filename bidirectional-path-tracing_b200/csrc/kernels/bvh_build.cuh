@@ -270,12 +270,15 @@ __global__ void k_wide_emit(const BuildNode* __restrict__ nodes, int32_t n_level
     uint32_t at = first_inner[i];
     trb::DevNode4 w;
     for (int k = 0; k < 4; ++k) {
-        w.pad[k] = 0;
-        if (sl[k] < 0) { w.lox[k] = w.loy[k] = w.loz[k] = w.hix[k] = w.hiy[k] = w.hiz[k] = 0.f; w.ref[k] = TRB_WIDE_EMPTY; continue; }
+        trb::DevNode4::Half& hf = w.half[k >> 1];
+        float* mn = (k & 1) ? hf.c1min : hf.c0min; float* mx = (k & 1) ? hf.c1max : hf.c0max;
+        int32_t& ref = (k & 1) ? hf.ref1 : hf.ref0;
+        hf.pad0 = 0; hf.pad1 = 0;
+        if (sl[k] < 0) { for (int a = 0; a < 3; ++a) { mn[a] = 0.f; mx[a] = 0.f; } ref = TRB_WIDE_EMPTY; continue; }
         const BuildNode& c = nodes[sl[k]];
-        w.lox[k] = c.bmin[0]; w.loy[k] = c.bmin[1]; w.loz[k] = c.bmin[2]; w.hix[k] = c.bmax[0]; w.hiy[k] = c.bmax[1]; w.hiz[k] = c.bmax[2];
-        if (c.left >= 0) { next_level[at] = sl[k]; w.ref[k] = int32_t(next_base + at); ++at; }
-        else w.ref[k] = ~int32_t((c.start << 3) | (c.end - c.start));
+        for (int a = 0; a < 3; ++a) { mn[a] = c.bmin[a]; mx[a] = c.bmax[a]; }
+        if (c.left >= 0) { next_level[at] = sl[k]; ref = int32_t(next_base + at); ++at; }
+        else ref = ~int32_t((c.start << 3) | (c.end - c.start));
     }
     out[base + uint32_t(i)] = w;
 }

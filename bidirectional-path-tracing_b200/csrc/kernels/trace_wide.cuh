@@ -28,7 +28,7 @@ namespace trbk {
 #endif
 
 struct WideView {
-    const F4* wnodes;   // 8 x F4 per node (DevNode4)
+    const F4* wnodes;   // 8 x F4 per node (DevNode4: two 64-byte halves)
     const F4* tris;     // 3 x F4 per triangle (DevTri)
     int32_t root_ref;   // 0 (wide node 0) or a leaf code when the scene is a single leaf
 };
@@ -60,12 +60,15 @@ TRB_HD bool traverse_wide(const WideView& bvh, const RayT& r, const RayPre& pre,
     const int32_t NONE = 0x7fffffff;
     while (cur != NONE) {
         if (cur >= 0) {
-            const F4* n = bvh.wnodes + 8 * size_t(cur);
-            const F4 lx = ld4(n), ly = ld4(n + 1), lz = ld4(n + 2), hx = ld4(n + 3), hy = ld4(n + 4), hz = ld4(n + 5), rf = ld4(n + 6);
+            const F4* n = bvh.wnodes + 8 * size_t(cur);   // two 64-byte halves: {c0min c0max c1min c1max ref0 ref1 pad pad}
             if (cnt) { ++cnt->nodes; }
-            const float L[4][6] = {{lx.x, ly.x, lz.x, hx.x, hy.x, hz.x}, {lx.y, ly.y, lz.y, hx.y, hy.y, hz.y},
-                                   {lx.z, ly.z, lz.z, hx.z, hy.z, hz.z}, {lx.w, ly.w, lz.w, hx.w, hy.w, hz.w}};
-            const int32_t ref[4] = {f2i(rf.x), f2i(rf.y), f2i(rf.z), f2i(rf.w)};
+            float L[4][6]; int32_t ref[4];
+            for (int hf = 0; hf < 2; ++hf) {
+                const F4 a = ld4(n + 4 * hf), b = ld4(n + 4 * hf + 1), c = ld4(n + 4 * hf + 2), d = ld4(n + 4 * hf + 3);
+                const float c0[6] = {a.x, a.y, a.z, a.w, b.x, b.y}, c1[6] = {b.z, b.w, c.x, c.y, c.z, c.w};
+                for (int k = 0; k < 6; ++k) { L[2 * hf][k] = c0[k]; L[2 * hf + 1][k] = c1[k]; }
+                ref[2 * hf] = f2i(d.x); ref[2 * hf + 1] = f2i(d.y);
+            }
             float en[4]; bool ok[4];
             const float lim = best + 1e-3f * (1.f + fabsf(best));
             for (int k = 0; k < 4; ++k) {
@@ -127,14 +130,31 @@ TRB_HD void trace_ray_wide(const WideView& wide, const BvhView& bin, const RayT&
 #include "trace_coop.cuh"
 
 #ifndef TRB_SSTACK
-#define TRB_SSTACK 8          // stack entries per lane kept in shared memory ([entry][thread]: conflict-free); deeper entries spill to local memory
+#define TRB_SSTACK 12         // stack entries per lane kept in shared memory ([entry][thread]: conflict-free); deeper entries spill to local memory
 #endif
 #define TRB_LSTACK (3 * TRB_STACK - TRB_SSTACK)   // a visit pushes at most 3; the upload checks 3 * wide_depth + 4 <= 3 * TRB_STACK
 
 namespace trbk {
 
+struct F8 { float a, b, c, d, e, f, g, h; };
+// 256-bit read-only global load (sm_100: LDG.E.256): half the L1 wavefronts of two LDG.128 when every lane reads its own line
+__device__ __forceinline__ F8 ld8(const float* p) {
+    F8 v;
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v.a), "=f"(v.b), "=f"(v.c), "=f"(v.d), "=f"(v.e), "=f"(v.f), "=f"(v.g), "=f"(v.h) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ F8 ld8_2x4(const float* p) {
+    const float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    return F8{a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+}
+#ifndef TRB_WIDE_LD256
+#define TRB_WIDE_LD256 1
+#endif
+
 // The production traversal kernel: persistent warps, lane refill, per-warp triangle queue (trace_coop.cuh) over the 4-wide tree.
-// Per node visit a lane loads 7 x 16 B, tests four boxes in straight-line code and
+// Per node visit a lane loads 4 x 32 B, tests four boxes in straight-line code and
 //   * queues the triangles of up to two hit leaves (one range push, <= 8 entries: the queue invariant of trace_coop.cuh) and parks
 //     further hit leaves on its stack as leaf references;
 //   * continues with the nearest hit inner child (first in slot order for occlusion / exhaustive rays) and stacks the others.
@@ -246,7 +266,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                 const uint32_t idx = base + uint32_t(__popc(wm & lt));
                 if (want && idx < n) {
                     slot = a.q ? a.q[idx] : int32_t(idx);
-                    const float4* rp = reinterpret_cast<const float4*>(a.rays + slot);
+                    const float4* rp = reinterpret_cast<const float4*>(a.rays + slot);   // (plain loads: the rays were written by the previous kernel)
                     float4 r0 = rp[0], r1 = rp[1];
                     r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.dx = r0.w; r.dy = r1.x; r.dz = r1.y; r.min_t = r1.z; r.max_t = r1.w;
                     pre = ray_pre(r);
@@ -260,56 +280,55 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         }
         // ---- node phase ----
         if (cur != NONE) {
+            const bool stop = ANY && (sh.flags[lane] & 2u) != 0;   // already occluded: nothing left to find
             if (cur < 0) {          // a leaf parked on the stack (its box passed when its parent was visited)
-                if (ANY && (sh.flags[lane] & 2u) != 0) sp = 0;   // already occluded
-                else push_leaves(uint32_t(~cur), 0u);
+                if (stop) sp = 0; else push_leaves(uint32_t(~cur), 0u);
                 cur = pop();
             } else {
-                const F4* np = a.wnodes + 8 * size_t(cur);
-                const F4 lx = ld4(np), ly = ld4(np + 1), lz = ld4(np + 2), hx = ld4(np + 3), hy = ld4(np + 4), hz = ld4(np + 5), rf = ld4(np + 6);
+                const float* np = reinterpret_cast<const float*>(a.wnodes + 8 * size_t(cur));
+#if TRB_WIDE_LD256
+                const F8 h0a = ld8(np), h0b = ld8(np + 8), h1a = ld8(np + 16), h1b = ld8(np + 24);   // 4 x LDG.256
+#else
+                const F8 h0a = ld8_2x4(np), h0b = ld8_2x4(np + 8), h1a = ld8_2x4(np + 16), h1b = ld8_2x4(np + 24);   // 8 x LDG.128
+#endif
 #ifdef TRB_COUNTERS
                 ++c_nodes;
 #endif
-                const int32_t ref[4] = {f2i(rf.x), f2i(rf.y), f2i(rf.z), f2i(rf.w)};
-                float en[4], ex[4]; bool hit[4];
-                // inner child: entered unless the straight-line test rejects it; leaf child: the reference's decision - the slow tiers run
-                // right here, child by child (flat boxes - every wall of a Cornell box - take them on every visit)
-#define TRB_WCHILD(k, c) { BoxF f = box_fast(lx.c, ly.c, lz.c, hx.c, hy.c, hz.c, r, pre); hit[k] = f.pass || f.undecided; \
-                           if (f.undecided && ref[k] < 0) hit[k] = box_slow(lx.c, ly.c, lz.c, hx.c, hy.c, hz.c, r, pre, f); \
-                           en[k] = f.en; ex[k] = f.ex; }
-                TRB_WCHILD(0, x) TRB_WCHILD(1, y) TRB_WCHILD(2, z) TRB_WCHILD(3, w)
-#undef TRB_WCHILD
-                const bool stop = ANY && (sh.flags[lane] & 2u) != 0;   // already occluded: nothing left to find
+                float lim = 0.f;
                 if (!exh) {
                     const float best = ANY ? r.max_t : __uint_as_float(uint32_t(sh.best[lane] >> 32));
-                    const float lim = best + 1e-3f * (1.f + fabsf(best));
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) hit[k] = hit[k] && !(en[k] > lim) && !(ex[k] < -0.0010011f);   // beyond the best hit / wholly behind the origin
+                    lim = best + 1e-3f * (1.f + fabsf(best));
                 }
-#pragma unroll
-                for (int k = 0; k < 4; ++k) hit[k] = hit[k] && ref[k] != TRB_WIDE_EMPTY && !stop;
-                // leaves: the two lowest hit slots are queued now (adjacent in list order when adjacent slots), further ones wait on the stack
-                uint32_t ca = 0u, cb = 0u; int nl = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    if (hit[k] && ref[k] < 0) {
-                        if (nl == 0) ca = uint32_t(~ref[k]); else if (nl == 1) cb = uint32_t(~ref[k]); else push(ref[k]);
-                        ++nl;
-                    }
-                }
+                // One child: an inner child is entered unless the straight-line test rejects it; a leaf child gets the reference's
+                // decision - its slow tiers run right here (flat boxes - every wall of a Cornell box - take them on every visit).
+                // Then the distance cull (beyond the best hit / wholly behind the origin), unless the ray is in exhaustive mode.
+                uint32_t ca = 0u, cb = 0u; int nl = 0;        // leaf codes queued by this visit
+                int32_t nref = -1; float nen = 0.f;           // the inner child to continue with
+                int32_t o0 = -1, o1 = -1, o2 = -1;            // the other hit inner children, slot order
+#define TRB_WCHILD(mnx, mny, mnz, mxx, mxy, mxz, rf) { \
+                    const int32_t ref = (rf); \
+                    BoxF f = box_fast(mnx, mny, mnz, mxx, mxy, mxz, r, pre); \
+                    bool hit = f.pass || f.undecided; \
+                    if (f.undecided && ref < 0) hit = box_slow(mnx, mny, mnz, mxx, mxy, mxz, r, pre, f); \
+                    hit = hit && ref != TRB_WIDE_EMPTY && !stop && (exh || (!(f.en > lim) && !(f.ex < -0.0010011f))); \
+                    if (hit && ref < 0) { if (nl == 0) ca = uint32_t(~ref); else if (nl == 1) cb = uint32_t(~ref); else push(ref); ++nl; } \
+                    if (hit && ref >= 0) { \
+                        const bool take = nref < 0 || (!ANY && !exh && f.en < nen); \
+                        const int32_t other = take ? nref : ref; \
+                        if (take) { nref = ref; nen = f.en; } \
+                        if (other >= 0) { if (o0 < 0) o0 = other; else if (o1 < 0) o1 = other; else o2 = other; } \
+                    } }
+                TRB_WCHILD(h0a.a, h0a.b, h0a.c, h0a.d, h0a.e, h0a.f, f2i(h0b.e))
+                TRB_WCHILD(h0a.g, h0a.h, h0b.a, h0b.b, h0b.c, h0b.d, f2i(h0b.f))
+                TRB_WCHILD(h1a.a, h1a.b, h1a.c, h1a.d, h1a.e, h1a.f, f2i(h1b.e))
+                TRB_WCHILD(h1a.g, h1a.h, h1b.a, h1b.b, h1b.c, h1b.d, f2i(h1b.f))
+#undef TRB_WCHILD
                 if (nl > 0) push_leaves(ca, cb);
-                // inner children: nearest first (pruning closest-hit rays), the others in slot order with slot 0 on top
-                int nb = -1;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const bool in = hit[k] && ref[k] >= 0;
-                    if (in && (nb < 0 || (!ANY && !exh && en[k] < en[nb]))) nb = k;
-                }
-#pragma unroll
-                for (int k = 3; k >= 0; --k)
-                    if (hit[k] && ref[k] >= 0 && k != nb) push(ref[k]);
+                if (o2 >= 0) push(o2);
+                if (o1 >= 0) push(o1);
+                if (o0 >= 0) push(o0);
                 if (stop) sp = 0;
-                cur = nb >= 0 ? ref[nb] : pop();
+                cur = nref >= 0 ? nref : pop();
             }
         }
         __syncwarp();
@@ -326,26 +345,35 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             o.ox = __shfl_sync(FULL, r.ox, owner); o.oy = __shfl_sync(FULL, r.oy, owner); o.oz = __shfl_sync(FULL, r.oz, owner);
             o.dx = __shfl_sync(FULL, r.dx, owner); o.dy = __shfl_sync(FULL, r.dy, owner); o.dz = __shfl_sync(FULL, r.dz, owner);
             o.max_t = __shfl_sync(FULL, r.max_t, owner); o.min_t = 0.f;
+            float t = 0.f, u, v;
+            bool ill = false, thit = false;
             if (act) {
                 const F4* tp = a.bvh.tris + 3 * size_t(pos);
                 F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
 #ifdef TRB_COUNTERS
                 ++c_tris;
 #endif
-                float t, u, v;
-                bool ill = false;
-                const bool thit = tri_test(q0, q1, q2, o, &t, &u, &v, &ill);
-                if (thit) {
-                    if (ANY) {
-                        // bvh.h:299-307 + :351: occluded iff some accepted t <= max_t (min_t <= max_t holds for a traced ray)
-                        if (t <= o.max_t) { atomicOr(&sh.flags[owner], 2u); ill = false; }
-                    } else {
-                        // (t, list position) lexicographic minimum == strict '<' in list order for any visiting order
-                        atomicMin(&sh.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | pos);
-                    }
+                thit = tri_test(q0, q1, q2, o, &t, &u, &v, &ill);
+            }
+            if (thit) {
+                if (ANY) {
+                    // bvh.h:299-307 + :351: occluded iff some accepted t <= max_t (min_t <= max_t holds for a traced ray)
+                    if (t <= o.max_t) { atomicOr(&sh.flags[owner], 2u); ill = false; }
+                } else {
+                    // (t, list position) lexicographic minimum == strict '<' in list order for any visiting order
+                    atomicMin(&sh.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | pos);
                 }
-                if (ill) atomicOr(&sh.flags[owner], 1u);
-                atomicSub(&sh.outst[owner], 1);
+            }
+            if (ill) atomicOr(&sh.flags[owner], 1u);
+            // outstanding-test counts: one subtraction per RUN of entries of the same owner (a leaf's triangles are adjacent in the
+            // queue), not one per lane - every lane hitting the same word serialises in the shared-memory atomic unit
+            const int prev_owner = __shfl_up_sync(FULL, owner, 1);
+            const bool run_head = act && (lane == 0 || prev_owner != owner);
+            const unsigned heads = __ballot_sync(FULL, run_head);
+            if (run_head) {
+                const unsigned rest = lane == 31 ? 0u : (heads >> (lane + 1));
+                const int len = rest ? __ffs(int(rest)) : int(nb_) - lane;
+                atomicSub(&sh.outst[owner], len);
             }
             head += nb_; count -= nb_;
             __syncwarp();

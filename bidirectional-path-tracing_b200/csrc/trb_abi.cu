@@ -43,6 +43,7 @@ struct DevBuf {
 
 #define TRB_SCENE_ARRAYS 12
 enum LaunchKind { LK_CLOSEST = 0, LK_ANY = 1, LK_LOGIC = 2, LK_N = 3 };
+#define TRB_NSTATS 16
 
 }  // namespace
 
@@ -85,7 +86,8 @@ struct trb_context {
     DevBuf<Pending> spend, spend2;
     DevBuf<uint32_t> counters;           // per stage CTR_N counters
     DevBuf<uint32_t> fetch_ctr;          // queue cursor of the stand-alone trace entry points
-    DevBuf<unsigned long long> d_stats;  // [0] closest rays, [1] any rays, [2] node visits, [3] tri tests
+    DevBuf<unsigned long long> d_stats;  // TRB_NSTATS words: [0] closest rays, [1] any rays, [2..5] wide node visits / tri tests (closest, any), [6,7] re-traces,
+                                         // [8..11] binary-tree node visits / tri tests of the deferred rays (closest, any), [12,13] deferred rays
     DevBuf<float> fb;                    // frame buffer W*H*3
     // scratch for the parity entry points
     DevBuf<RayT> io_rays;
@@ -151,6 +153,7 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     if (c->force_binary) { k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a); return; }
     k_trace_wide<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
     a.q = c->defer_q[0].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu)); a.fetch = ctr + 2;
+    if (visit) a.visit = c->d_stats.p + 8;
     k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
 }
 
@@ -168,6 +171,7 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     if (c->force_binary) { k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a); return; }
     k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a);
     a.q = c->defer_q[which].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu)); a.fetch = ctr + 2;
+    if (visit) a.visit = c->d_stats.p + 10;
     k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a);
 }
 
@@ -192,7 +196,7 @@ int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     if (c->sc.has_tex) { TRB_CUDA(c, c->lv_tex.alloc(P * kk)); TRB_CUDA(c, c->ev_tex.alloc(P)); }
     TRB_CUDA(c, c->counters.alloc(size_t(2 * kk + 8) * CTR_N));
     TRB_CUDA(c, c->defer_q[0].alloc(P)); TRB_CUDA(c, c->defer_q[1].alloc(shadow_cap));
-    TRB_CUDA(c, c->d_stats.alloc(8));
+    TRB_CUDA(c, c->d_stats.alloc(TRB_NSTATS));
     return TRB_OK;
 }
 
@@ -207,7 +211,9 @@ __global__ void k_fold_stats(const uint32_t* __restrict__ counters, int n_stage,
         bool is_eye_init = (s == K + 1);
         if (!is_eye_init) closest += qo;  // every queued slot is traced once more; eye depth 1 reuses the primary hit
     }
-    stats[0] += closest; stats[1] += any;
+    unsigned long long dc = 0, da = 0;   // rays k_trace_wide left to the binary tree (word [1] of every launch's counters)
+    for (int s = 0; s < n_stage; ++s) { dc += counters[s * CTR_N + CTR_FETCH_CLOSEST + 1]; da += counters[s * CTR_N + CTR_FETCH_ANY + 1]; }
+    stats[0] += closest; stats[1] += any; stats[12] += dc; stats[13] += da;
 }
 
 }  // namespace
@@ -692,10 +698,11 @@ int check_desc(trb_context* c, const trb_render_desc* d) {
 void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
     if (!st) return;
     std::memset(st, 0, sizeof(*st));
-    unsigned long long h[8] = {0};
+    unsigned long long h[TRB_NSTATS] = {0};
     cudaMemcpyAsync(h, c->d_stats.p, sizeof(h), cudaMemcpyDeviceToHost, c->stream);
     cudaStreamSynchronize(c->stream);
     st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5]; st->retraces = h[6]; st->retraces_any = h[7];
+    st->node_visits_bin = h[8]; st->tri_tests_bin = h[9]; st->node_visits_bin_any = h[10]; st->tri_tests_bin_any = h[11]; st->rays_deferred = h[12]; st->rays_deferred_any = h[13];
     st->launches = c->launches;
     double ms[LK_N] = {0, 0, 0};
     // kernel time summed per kind on each stream; the two streams overlap, so the kinds can add up to more than ms_total
@@ -733,7 +740,7 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     c->mark(LK_LOGIC);
     if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
     WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
@@ -870,7 +877,7 @@ int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_de
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     c->mark(LK_LOGIC);
     if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
     WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
@@ -958,7 +965,7 @@ int render_direct_impl(trb_context* c, const trb_render_desc* d, const trb_direc
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     c->mark(LK_LOGIC);
     if (!accumulate) TRB_CUDA(c, cudaMemsetAsync(d_rgb, 0, size_t(npix) * 3 * sizeof(float), c->stream));
     WaveRun w{d, d_rgb, nullptr, nullptr, nullptr, 0, false};
@@ -1028,7 +1035,7 @@ int trb_direct_paths(trb_context* c, const trb_render_desc* d, const trb_direct_
     TRB_CUDA(c, cudaMemcpyAsync(d_rays.p, cam_rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -1089,7 +1096,7 @@ int trb_path_paths(trb_context* c, const trb_render_desc* d, const trb_path_desc
     TRB_CUDA(c, cudaMemcpyAsync(d_rays.p, cam_rays, n * sizeof(RayT), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -1157,16 +1164,22 @@ struct Nccl {
     std::string err;
     bool load() {
         if (lib) return true;
-        const char* names[] = {std::getenv("TRB_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
-        for (const char* nm : names) { if (nm && *nm && (lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL))) break; }
-        if (!lib) { err = std::string("cannot load libnccl.so.2: ") + (dlerror() ? dlerror() : "?"); return false; }
+        // TRB_NCCL_LIB, when set, is the only library tried (an explicit override; a bad path fails instead of silently taking another copy)
+        const char* over = std::getenv("TRB_NCCL_LIB");
+        const char* names[] = {over && *over ? over : "libnccl.so.2", over && *over ? nullptr : "libnccl.so"};
+        for (const char* nm : names) { if (nm && (lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL))) break; }
+        if (!lib) {
+            const char* e = dlerror();   // ONE call: dlerror() clears the message it returns
+            err = std::string("cannot load ") + (over && *over ? over : "libnccl.so.2") + ": " + (e ? e : "?");
+            return false;
+        }
         CommInitAll = reinterpret_cast<decltype(CommInitAll)>(dlsym(lib, "ncclCommInitAll"));
         CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
         Reduce = reinterpret_cast<decltype(Reduce)>(dlsym(lib, "ncclReduce"));
         GroupStart = reinterpret_cast<decltype(GroupStart)>(dlsym(lib, "ncclGroupStart"));
         GroupEnd = reinterpret_cast<decltype(GroupEnd)>(dlsym(lib, "ncclGroupEnd"));
         GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
-        if (!CommInitAll || !CommDestroy || !Reduce || !GroupStart || !GroupEnd) { err = "libnccl.so.2 lacks a required symbol"; lib = nullptr; return false; }
+        if (!CommInitAll || !CommDestroy || !Reduce || !GroupStart || !GroupEnd) { err = "libnccl.so.2 lacks a required symbol"; dlclose(lib); lib = nullptr; return false; }
         return true;
     }
     std::vector<int> devs;      // communicators are kept for the device list they were made for
@@ -1190,6 +1203,9 @@ template <class RenderOne>
 int render_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, float* rgb_out, trb_stats* stats, RenderOne fn) {
     trb_context* c0 = ctxs[0];
     if (d->width <= 0 || d->height <= 0 || d->spp < n) return c0->fail(TRB_ERR_INVALID, "trb_render_bdpt_multi: needs spp >= number of devices");
+    const int s0 = d->spp_begin, s1 = d->spp_end > 0 ? d->spp_end : d->spp;
+    // every device gets a non-empty slice of [s0, s1): an empty one would reach render_impl as spp_end == 0, which means "up to spp"
+    if (s0 < 0 || s1 > d->spp || s1 - s0 < n) return c0->fail(TRB_ERR_INVALID, "trb_render_*_multi: the sample range must hold at least one sample per device");
     std::lock_guard<std::mutex> lock(g_nccl_mutex);
     if (!g_nccl.load()) return c0->fail(TRB_ERR_UNSUPPORTED, g_nccl.err);
     std::vector<int> devs;
@@ -1197,7 +1213,6 @@ int render_multi(trb_context* const* ctxs, int n, const trb_render_desc* d, floa
     for (int g = 0; g < n; ++g) for (int h = g + 1; h < n; ++h) if (devs[g] == devs[h]) return c0->fail(TRB_ERR_INVALID, "trb_render_bdpt_multi: one context per device");
     if (!g_nccl.comms_for(devs)) return c0->fail(TRB_ERR_CUDA, g_nccl.err);
     const size_t nf = size_t(d->width) * d->height * 3;
-    const int s0 = d->spp_begin, s1 = d->spp_end > 0 ? d->spp_end : d->spp;
     std::vector<int> rc(size_t(n), TRB_OK);
     std::vector<std::thread> th;
     for (int g = 0; g < n; ++g) {
@@ -1302,7 +1317,7 @@ int trace_device(trb_context* c, bool any, const RayT* d_rays, size_t n, HitT* d
     if (ms_out) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, c->stream); }
     unsigned long long* visit = nullptr;
 #ifdef TRB_COUNTERS
-    TRB_CUDA(c, c->d_stats.alloc(8));
+    TRB_CUDA(c, c->d_stats.alloc(TRB_NSTATS));
     visit = c->d_stats.p + 2;
 #endif
     if (n) {
@@ -1411,7 +1426,7 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
     TRB_CUDA(c, cudaMemcpyAsync(d_rng.p, rng, n * stride * sizeof(float), cudaMemcpyHostToDevice, c->stream));
     TRB_CUDA(c, cudaMemsetAsync(d_acc.p, 0, d_acc.bytes(), c->stream));
     TRB_CUDA(c, cudaMemsetAsync(d_pix.p, 0xff, d_pix.bytes(), c->stream));
-    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, 8 * sizeof(unsigned long long), c->stream));
+    TRB_CUDA(c, cudaMemsetAsync(c->d_stats.p, 0, TRB_NSTATS * sizeof(unsigned long long), c->stream));
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = false; c->n_events = 0; c->n_events2 = 0; c->launches = 0;

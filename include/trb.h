@@ -171,6 +171,14 @@ typedef struct trb_stats {
     uint64_t tri_tests_any;
     uint64_t retraces;        /* closest-hit rays re-traced without distance pruning (ill-conditioned candidate met); TRB_COUNTERS only */
     uint64_t retraces_any;    /* same for occlusion rays */
+    /* node_visits / node_visits_any count 128-byte nodes of the 4-wide upper tree (k_trace_wide).  Rays with a zero / non-finite
+     * direction component are traced on the reference's binary tree instead (k_trace_coop, 64-byte nodes): */
+    uint64_t rays_deferred;      /* closest-hit rays traced on the binary tree (always counted)               */
+    uint64_t rays_deferred_any;  /* occlusion rays traced on the binary tree (always counted)                 */
+    uint64_t node_visits_bin;    /* their 64-byte node visits and triangle tests; TRB_COUNTERS builds only     */
+    uint64_t tri_tests_bin;
+    uint64_t node_visits_bin_any;
+    uint64_t tri_tests_bin_any;
 } trb_stats;
 
 /* BSDF query in the local shading frame (SurfaceInteraction::{wo,wi}, core.h:173-180) */
@@ -220,6 +228,10 @@ int trb_host_save_checkpoint(const char* path, const trb_checkpoint_info* info, 
 /* rgb_out may be null to read the header only */
 int trb_host_load_checkpoint(const char* path, trb_checkpoint_info* info_out, float* rgb_out, size_t capacity_floats);
 int trb_host_checkpoint_matches(const trb_checkpoint_info* a, const trb_checkpoint_info* b);
+/* Fingerprint of a scene for trb_checkpoint_info::scene_hash: FNV-1a over the CONTENT of every array of the description (positions,
+ * normals, indices, material and shape ids, material records, texture coordinates and texels) - an edited vertex, Kd / Ke / illum
+ * or texture changes it, so a checkpoint of the old scene is not continued on the new one.  Never 0. */
+uint64_t trb_host_scene_hash(const trb_scene_desc* scene);
 /* quick-look image: 8-bit sRGB PNG of exposure * rgb (row 0 = top) */
 int trb_host_save_png(const char* path, const float* rgb, int width, int height, float exposure);
 /* saveEXR (src/core/utils.h:95-156): channels B,G,R stored as half, row 0 = top. */

@@ -114,7 +114,15 @@ def test_direct_strategies_agree_on_sphere_lights(trb, gpu_ctx):
     on 150 k samples of this scene: 0.617 / 0.619 / 0.617 / 0.621 / 0.618)"""
     ctx = gpu_ctx("spherelight")
     desc = trb.render_desc(width=160, height=120, spp=256)
-    means = {s: float(ctx.render_direct(desc, trb.direct_desc(s, 2, 2))[0].mean()) for s in ("mis", "solidAngle", "bsdf", "cosineHemisphere", "area")}
+    means = {}
+    for s in ("mis", "solidAngle", "bsdf", "cosineHemisphere", "area"):
+        img = ctx.render_direct(desc, trb.direct_desc(s, 2, 2))[0]
+        # a direction drawn ON the rim of the disc (a sample number that is exactly 0: probability 2^-24 per draw, ~1 event per image
+        # here) has z = 0 and pdf = 0, and the reference multiplies eval = 0 by 1 / pdf = inf (direct.h:227, :260): those samples are NaN in the
+        # reference too.  They are counted, not hidden.
+        bad = ~np.isfinite(img).all(2)
+        assert bad.sum() <= 8, (s, int(bad.sum()))
+        means[s] = float(img[~bad].mean())
     print(means)
     for s in ("solidAngle", "bsdf", "cosineHemisphere", "area"):
         assert abs(means[s] / means["mis"] - 1) < 0.03, means

@@ -281,3 +281,35 @@ def test_cpp_host_api_paths_match_reference(trb, gold, tmp_path):
     ok = (np.abs(out[:, :3] - ref) <= 1e-5 * np.maximum(scale, np.abs(out[:, :3]))).all(1)
     assert ok.sum() >= n - 3, ok.sum()
     assert out[:, 3].view(np.int32).sum() > n // 2  # most camera rays hit the box
+
+
+def test_multi_gpu_entry_points_fail_cleanly(trb, gpu_ctx, tmp_path):
+    """(1) a sample range that cannot give every device a sample is refused (an empty slice would reach the renderer as
+    spp_end == 0 = "up to spp" and be over-counted); (2) with NCCL unloadable (TRB_NCCL_LIB names a file that is not there - the override
+    is the only library tried) trb_render_bdpt_multi answers TRB_ERR_UNSUPPORTED with the loader's message instead of crashing in
+    std::string(nullptr) - the status the host API turns into a host-side sum."""
+    a, b = gpu_ctx("caustic"), trb.Context(0)
+    try:
+        b.upload(a.scene)
+        with pytest.raises(trb.TrbError) as e:
+            trb.render_bdpt_multi([a, b], trb.render_desc(width=32, height=32, spp=100, rr_depth=4, spp_begin=0, spp_end=1))
+        assert e.value.code == trb.TRB_ERR_INVALID and "at least one sample per device" in str(e.value)
+    finally:
+        b.close()
+    prog = tmp_path / "nccl_missing.py"
+    prog.write_text(
+        "import importlib, sys\n"
+        f"sys.path.insert(0, {str(ROOT)!r})\n"
+        "trb = importlib.import_module('bidirectional-path-tracing_b200')\n"
+        f"sc = trb.HostScene.load_npz({str(GOLD / 'scene_caustic.npz')!r})\n"
+        "a, b = trb.Context(0), trb.Context(0)\n"
+        "a.upload(sc); b.upload(sc)\n"
+        "try:\n"
+        "    trb.render_bdpt_multi([a, b], trb.render_desc(width=32, height=32, spp=4, rr_depth=4))\n"
+        "    print('NO ERROR')\n"
+        "except trb.TrbError as e:\n"
+        "    print('CODE', e.code, str(e))\n")
+    env = dict(os.environ, TRB_NCCL_LIB=str(tmp_path / "no_such_libnccl.so"))
+    r = subprocess.run([sys.executable, str(prog)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert f"CODE {trb.TRB_ERR_UNSUPPORTED}" in r.stdout and "no_such_libnccl.so" in r.stdout, r.stdout

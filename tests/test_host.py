@@ -293,3 +293,36 @@ def test_textured_obj_loader(trb, tmp_path):
     pink = trb.HostScene.load_obj(obj)
     i = [k for k, t in enumerate(pink.textures) if t.shape == (1, 1, 3)]
     assert len(i) == 1 and np.array_equal(pink.textures[i[0]].ravel(), [1.0, 0.0, 1.0])
+
+
+def test_scene_hash_follows_content(trb):
+    """trb_host_scene_hash (the checkpoint's scene fingerprint) covers the CONTENT of the scene arrays: a moved vertex, a changed Kd /
+    Ke / illum or a swapped face changes it even though every count stays the same (the old fingerprint held three counts)"""
+    L = trb.lib()
+    L.trb_host_scene_hash.restype = ctypes.c_uint64
+    sc = trb.HostScene.load_npz(GOLD / "scene_caustic.npz")
+
+    def h(scene):
+        d = scene.desc()
+        return int(L.trb_host_scene_hash(ctypes.byref(d)))
+    base = h(sc)
+    assert base != 0 and h(trb.HostScene.load_npz(GOLD / "scene_caustic.npz")) == base
+    seen = {base}
+    for edit in ("vertex", "kd", "ke", "illum", "face", "normal"):
+        e = trb.HostScene.load_npz(GOLD / "scene_caustic.npz")
+        if edit == "vertex":
+            e.positions[17, 1] += np.float32(1e-3)
+        elif edit == "kd":
+            e.materials["kd"][0, 0] = np.float32(e.materials["kd"][0, 0] * 0.5 + 0.1)
+        elif edit == "ke":
+            k = int(np.flatnonzero(e.materials["ke"].sum(1) > 0)[0]); e.materials["ke"][k] *= np.float32(2)
+        elif edit == "illum":
+            e.materials["illum"][0] = 3 if e.materials["illum"][0] != 3 else 7
+        elif edit == "face":
+            e.tri_v[[5, 6]] = e.tri_v[[6, 5]]
+        else:
+            e.normals[3] = -e.normals[3]
+        v = h(e)
+        assert v not in seen, edit
+        seen.add(v)
+    assert h(trb.HostScene.load_npz(GOLD / "scene_hardlight.npz")) not in seen

@@ -50,7 +50,10 @@ def test_wide_tree_structure(trb, scene_name):
     assert L.hc_wide_nodes(C.byref(d), None, C.byref(n)) == 0
     w = np.zeros(n.value, trb.DEV_NODE4_DTYPE)
     assert L.hc_wide_nodes(C.byref(d), w.ctypes.data_as(C.c_void_p), C.byref(n)) == 0
-    ref = w["ref"]
+    hf = w["half"]                                                          # (n, 2) DevNode-shaped halves: children 0,1 and 2,3
+    ref = np.stack([hf["ref0"][:, 0], hf["ref1"][:, 0], hf["ref0"][:, 1], hf["ref1"][:, 1]], 1)
+    lo = np.stack([hf["c0min"][:, 0], hf["c1min"][:, 0], hf["c0min"][:, 1], hf["c1min"][:, 1]], 1)
+    hi = np.stack([hf["c0max"][:, 0], hf["c1max"][:, 0], hf["c0max"][:, 1], hf["c1max"][:, 1]], 1)
     empty = np.int32(-2**31)
     inner = ref[(ref >= 0)]
     assert np.array_equal(np.sort(inner), np.arange(1, len(w)))            # every node but the root has exactly one parent
@@ -61,7 +64,6 @@ def test_wide_tree_structure(trb, scene_name):
     assert first[o][0] == 0 and np.array_equal(first[o][1:], (first[o] + count[o])[:-1]) and (first[o] + count[o])[-1] == scene.n_tris
     assert (count >= 1).all() and (count <= 4).all()
     # a child node's slot boxes lie inside the box its parent holds for it
-    lo = np.stack([w["lox"], w["loy"], w["loz"]], -1); hi = np.stack([w["hix"], w["hiy"], w["hiz"]], -1)
     pi, ps = np.nonzero(ref >= 0)
     for p_, s_ in list(zip(pi, ps))[:: max(1, len(pi) // 2000)]:
         c = ref[p_, s_]
