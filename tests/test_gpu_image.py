@@ -74,10 +74,13 @@ def test_path_tracer_image(trb, gpu_ctx):
     (2) against BDPT on the same scene, the cross-check the reference's author made.  The two are NOT estimators of the same
     integral: recursiveExplicit drops every indirect direction that lands on the emitter (path.h:108-117), so light reaching a
     surface through a specular bounce is missing; the reference's own shipped pair differs by the same amount
-    (cbox_bdpt_path.exr mean 0.1162 vs cbox_bdpt_final.exr 0.1255, ratio 0.926)."""
+    (cbox_bdpt_path.exr mean 0.1162 vs cbox_bdpt_final.exr 0.1255, ratio 0.926).
+    The shipped image is itself a 512 spp render, so the statistic is (its noise) + (ours).  At 512 spp on both sides it sat AT the
+    bound and moved with the random streams (1.98e-2 with the 32-bit stream keys of round 1, 2.12e-2 with the 64-bit keys); the
+    device side is rendered at 2048 spp so that the bound tests the estimator, not one noise realisation."""
     ctx = gpu_ctx("hardlight")
     g = np.load(GOLD / "image_hardlight_path.npz")
-    desc = trb.render_desc(width=800, height=600, spp=512, rr_depth=int(g["rr_depth"]))
+    desc = trb.render_desc(width=800, height=600, spp=2048, rr_depth=int(g["rr_depth"]))
     pt, st = ctx.render_path(desc, trb.path_desc())
     a, b = _box(pt, int(g["box"])), g["image"].astype(np.float64)
     rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
