@@ -72,6 +72,7 @@ def path_desc(is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, b
 
 
 TRB_PT_DEFAULT_DEPTH_CAP = 64
+TRB_NOALLOC_MAX_RAYS = 1 << 20  # include/trb.h
 
 
 class DirectDesc(C.Structure):
@@ -509,6 +510,10 @@ class Context:
         ms = C.c_float(0)
         self._chk(self._L.trb_trace_closest_device(self._h, C.c_void_p(d_rays_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr), C.byref(ms)))
         return ms.value
+
+    def trace_any_device_noalloc(self, d_rays_ptr: int, n: int, d_out_ptr: int) -> None:
+        """trb_trace_any_device_noalloc: the occlusion query on device pointers with the library's fixed scratch array (no cudaMalloc)"""
+        self._chk(self._L.trb_trace_any_device_noalloc(self._h, C.c_void_p(d_rays_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr)))
 
     def trace_any_device(self, d_rays_ptr: int, n: int, d_out_ptr: int) -> float:
         ms = C.c_float(0)

@@ -1460,3 +1460,65 @@ int trb_bdpt_paths(trb_context* c, const trb_render_desc* d, const trb_ray* cam_
 }
 
 }  // extern "C"
+
+// ---- an entry point that allocates nothing (no counterpart in the reference) --------
+// Some callers cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it.  This is
+// trb_trace_any_device with the scratch the traversal needs - the launch's three queue counters (bdpt_common.cuh: TRACE_CTR_WORDS) and
+// the queue of ray slots k_trace_wide hands to k_trace_coop (rays with a zero / non-finite direction component, at most one entry per
+// ray) - in a file-scope device array instead of cudaMalloc'ed buffers of the context.  Every GPU that loads the library holds the
+// array (256 B + 4 B x TRB_NOALLOC_MAX_RAYS = 4 MiB + 256 B) until exit.  All calls on a device share it and it keeps the last call's
+// contents: the counters are cleared on the stream before every launch (the queue needs no clearing: only entries below the freshly
+// counted length are read); two calls that overlap on one GPU (two contexts of one device from two threads) race on it.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + sizeof(int32_t) * size_t(TRB_NOALLOC_MAX_RAYS)];
+
+namespace {
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+std::mutex g_noalloc_mutex;
+void* g_noalloc_ptr[64] = {nullptr};
+int noalloc_scratch(trb_context* c, unsigned char** out) {
+    if (c->device < 0 || c->device >= 64) return c->fail(TRB_ERR_UNSUPPORTED, "trb_trace_any_device_noalloc: device index beyond 63");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[c->device]) {
+        void* p = nullptr;
+        TRB_CUDA(c, cudaSetDevice(c->device));
+        TRB_CUDA(c, cudaGetSymbolAddress(&p, g_noalloc_scratch));
+        if (!p) return c->fail(TRB_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the scratch array");
+        g_noalloc_ptr[c->device] = p;
+    }
+    *out = static_cast<unsigned char*>(g_noalloc_ptr[c->device]);
+    return TRB_OK;
+}
+}  // namespace
+
+extern "C" int trb_trace_any_device_noalloc(trb_context* c, const trb_ray* d_rays, size_t n, uint8_t* d_out) {
+    if (!c) return TRB_ERR_INVALID;
+    if (n && (!d_rays || !d_out)) return c->fail(TRB_ERR_INVALID, "trb_trace_any_device_noalloc: null ray or output pointer");
+    if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
+    if (n > size_t(TRB_NOALLOC_MAX_RAYS))
+        return c->fail(TRB_ERR_INVALID, "trb_trace_any_device_noalloc: " + std::to_string(n) + " rays exceed the fixed scratch of TRB_NOALLOC_MAX_RAYS = " +
+                                            std::to_string(size_t(TRB_NOALLOC_MAX_RAYS)) + " rays per call; split the batch or use trb_trace_any_device");
+    if (n == 0) return TRB_OK;
+    unsigned char* scratch = nullptr;
+    int rc = noalloc_scratch(c, &scratch);
+    if (rc) return rc;
+    TRB_CUDA(c, cudaSetDevice(c->device));
+    uint32_t* ctr = reinterpret_cast<uint32_t*>(scratch);               // [0] ray cursor, [1] deferred count, [2] cursor of the deferred launch
+    int32_t* defer_q = reinterpret_cast<int32_t*>(scratch + 256);
+    TRB_CUDA(c, cudaMemsetAsync(ctr, 0, TRACE_CTR_WORDS * sizeof(uint32_t), c->stream));
+    TraceArgs a{};
+    a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
+    a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.rays = reinterpret_cast<const RayT*>(d_rays); a.q = nullptr; a.n_ptr = nullptr; a.n_fixed = uint32_t(n); a.cap = uint32_t(n);
+    a.occ_out = d_out; a.pend = nullptr; a.accum = nullptr; a.fetch = ctr;
+    a.defer_q = defer_q; a.defer_n = ctr + 1;
+    a.visit = nullptr; a.visit_exh = nullptr;
+    const int grid = trace_grid(c->prop.multiProcessorCount);
+    k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    a.q = defer_q; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(TRB_NOALLOC_MAX_RAYS); a.fetch = ctr + 2;
+    k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
+    c->launches += 2;
+    TRB_CUDA(c, cudaGetLastError());
+    TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    return TRB_OK;
+}

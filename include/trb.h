@@ -334,6 +334,15 @@ int trb_bdpt_paths(trb_context*, const trb_render_desc*, const trb_ray* cam_rays
 int trb_trace_closest_device(trb_context*, const trb_ray* d_rays, size_t n, trb_hit* d_out, float* ms_out);
 int trb_trace_any_device(trb_context*, const trb_ray* d_rays, size_t n, uint8_t* d_out, float* ms_out);
 
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  Same query and results as trb_trace_any_device (d_rays and
+ * d_out are DEVICE pointers the caller owns; d_out[i] = 1 when ray i is occluded), but the call allocates NOTHING: the traversal's
+ * scratch (queue counters + the queue of rays handed to the binary tree) lives in a fixed device array inside the library, which
+ * every GPU that loads the library holds until exit (4 MiB + 256 B).  n > TRB_NOALLOC_MAX_RAYS is refused with TRB_ERR_INVALID.
+ * All calls on a device share that array: calls that overlap on one GPU race; calls on one context (one stream) do not. */
+#define TRB_NOALLOC_MAX_RAYS (1u << 20)
+int trb_trace_any_device_noalloc(trb_context*, const trb_ray* d_rays, size_t n, uint8_t* d_out);
+
 /* library build info: "sm_100a;fmad=off;..." */
 const char* trb_build_info(void);
 
