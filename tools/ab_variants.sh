@@ -7,7 +7,7 @@ for v in "$@"; do
     lib=bidirectional-path-tracing_b200/libtrb_$v.so; mode=wide
     [ $v = default ] && lib=bidirectional-path-tracing_b200/libtrb.so
     [ $v = binary ] && lib=bidirectional-path-tracing_b200/libtrb.so && mode=binary
-    TRB_LIB=$GRAFT_REPO_ROOT/$lib TRB_TRAVERSAL=$mode python bench.py --workload $w --spp $spp --steps 3 --warmup 3 --no-cpu-baseline --no-visits 2> gpurun_out/${TAG}_ab_${v}_$w.err | tail -1 > gpurun_out/${TAG}_ab_${v}_$w.json
+    TRB_LIB=$GRAFT_REPO_ROOT/$lib TRB_TRAVERSAL=$mode python bench.py --workload $w --spp $spp --steps 3 --warmup 3 --no-cpu-baseline --no-visits --no-extras 2> gpurun_out/${TAG}_ab_${v}_$w.err | tail -1 > gpurun_out/${TAG}_ab_${v}_$w.json
     python - <<PY
 import json
 try:
