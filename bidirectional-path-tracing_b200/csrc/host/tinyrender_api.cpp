@@ -3,6 +3,7 @@
 #include "../../../include/tinyrender/tinyrender.h"
 
 #include <cmath>
+#include <algorithm>
 #include <cstdio>
 #include <cstring>
 #include <iostream>
@@ -133,6 +134,14 @@ bool Scene::load(bool isRealTime) {
     for (int k = 0; k < 3; ++k) { aabb.min[k] = 3.4e38f; aabb.max[k] = -3.4e38f; }
     for (size_t v = 0; v < sdesc.n_positions; ++v)
         for (int k = 0; k < 3; ++k) { aabb.min[k] = std::fmin(aabb.min[k], sdesc.positions[3 * v + k]); aabb.max[k] = std::fmax(aabb.max[k], sdesc.positions[3 * v + k]); }
+    {   // the WorldData view: per-shape centre and radius as Scene::load derives them (renderer.cpp:294-304)
+        std::vector<float> sph(4 * sdesc.n_shapes);
+        if (trb_host_shape_spheres(&sdesc, sph.data(), sdesc.n_shapes) != TRB_OK) { err = trb_host_last_error(); std::printf("%s\n", err.c_str()); return false; }
+        worldData.owner = this; worldData.flat = &sdesc;
+        worldData.shapesCenter.clear(); worldData.shapesRadius.clear();
+        for (size_t k = 0; k < sdesc.n_shapes; ++k) { worldData.shapesCenter.push_back(v3f(sph[4 * k], sph[4 * k + 1], sph[4 * k + 2])); worldData.shapesRadius.push_back(sph[4 * k + 3]); }
+        for (auto& b : bsdfs) b->emission = v3f(sdesc.materials[b->matID].ke[0], sdesc.materials[b->matID].ke[1], sdesc.materials[b->matID].ke[2]);
+    }
     std::printf("Found %zu shapes, %zu triangles, %zu emitters\n", nShapes, nTriangles, emitters.size());
     // AcceleratorBVH::build (accel.h:115-123) + device upload: fails loudly without a GPU
     if (!context(0)) { std::printf("%s\n", err.c_str()); return false; }
@@ -195,6 +204,58 @@ bool AcceleratorBVH::intersect(const Ray& ray, SurfaceInteraction& info, bool) c
 }
 
 // ---- BSDF (core.h:256-318) ------------------------------------------------------------------------------------
+// the reference's constructor (core.h:299-305): emission = materials[matID].emission
+BSDF::BSDF(const WorldData& d, const Config& c, size_t id) : worldData(d), config(c), scene(*d.owner), matID(id) {
+    if (!d.owner || !d.flat) throw std::runtime_error("BSDF: the WorldData view is not bound to a loaded Scene");
+    if (id >= d.flat->n_materials) throw std::out_of_range("BSDF: material index out of range");
+    const trb_material& m = d.flat->materials[id];
+    emission = v3f(m.ke[0], m.ke[1], m.ke[2]);
+    emissive = m.ke[0] != 0.f || m.ke[1] != 0.f || m.ke[2] != 0.f;
+}
+BSDF::BSDF(const Scene& s, size_t id) : worldData(s.worldData), config(s.config), scene(s), matID(id) {}
+
+float Scene::getShapeRadius(size_t shapeID) const { return worldData.shapesRadius.at(shapeID); }
+v3f Scene::getShapeCenter(size_t shapeID) const { return worldData.shapesCenter.at(shapeID); }
+float Scene::getShapeArea(size_t shapeID) const {   // the running fp32 sum Distribution1D::add keeps (math.h:88-91), face order
+    if (shapeID >= sdesc.n_shapes) throw std::out_of_range("Scene::getShapeArea: shape index out of range");
+    float sum = 0.f;
+    for (size_t t = 0; t < sdesc.n_tris; ++t) {
+        if (size_t(sdesc.tri_shape[t]) != shapeID) continue;
+        const float* a = sdesc.positions + 3 * size_t(sdesc.tri_v[3 * t]);
+        const float* b = sdesc.positions + 3 * size_t(sdesc.tri_v[3 * t + 1]);
+        const float* c = sdesc.positions + 3 * size_t(sdesc.tri_v[3 * t + 2]);
+        const float e1[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, e2[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+        const float cx = e1[1] * e2[2] - e2[1] * e1[2], cy = e1[2] * e2[0] - e2[2] * e1[0], cz = e1[0] * e2[1] - e2[0] * e1[1];   // glm::cross order
+        sum += 0.5f * std::sqrt(cx * cx + cy * cy + cz * cz);
+    }
+    return sum;
+}
+
+size_t Integrator::getEmitterIDByShapeID(size_t shapeID) const {
+    for (size_t e = 0; e < scene.emitters.size(); ++e) if (scene.emitters[e].shapeID == shapeID) return e;
+    throw std::out_of_range("Integrator::getEmitterIDByShapeID: the shape is not an emitter");
+}
+const BSDF* Integrator::getBSDF(const SurfaceInteraction& hit) const {   // material of face primID of shape shapeID
+    const trb_scene_desc* d = scene.desc();
+    size_t first = 0;
+    while (first < d->n_tris && size_t(d->tri_shape[first]) < hit.shapeID) ++first;   // triangles are shape-major
+    const size_t t = first + hit.primID;
+    if (t >= d->n_tris || size_t(d->tri_shape[t]) != hit.shapeID) throw std::out_of_range("Integrator::getBSDF: no such face");
+    return scene.bsdfs.at(size_t(d->tri_mat[t])).get();
+}
+v3f Integrator::getEmission(const SurfaceInteraction& hit) const {
+    const trb_scene_desc* d = scene.desc();
+    if (hit.matID < 0 || size_t(hit.matID) >= d->n_materials) throw std::out_of_range("Integrator::getEmission: material index out of range");
+    const trb_material& m = d->materials[hit.matID];
+    return v3f(m.ke[0], m.ke[1], m.ke[2]);
+}
+size_t Integrator::selectEmitter(float sample, float& pdf) const {
+    size_t id = size_t(sample * scene.emitters.size());
+    id = std::min(id, scene.emitters.size() - 1);
+    pdf = 1.f / scene.emitters.size();
+    return id;
+}
+
 bool BSDF::evalBatch(const trb_bsdf_query* q, size_t n, trb_bsdf_out* out) const {
     trb_context* c = scene.context(0);
     return c && trb_bsdf_batch(c, q, n, out) == TRB_OK;

@@ -114,15 +114,32 @@ struct Sampler {  // math.h:63-76
 
 struct Scene;
 
+// WorldData (core.h:151-160 holds tinyobj's attrib / shapes / materials): here a thin VIEW over the flat arrays of the loaded
+// scene (what tinyobj::LoadObj yields, shape-major; trb_scene_desc), plus the per-shape centres and radii Scene::load derives
+// (renderer.cpp:294-304).  It exists so that code written against the reference's signatures - BSDF(const WorldData&, const
+// Config&, size_t), scene.worldData - compiles; the arrays are owned by the Scene.
+struct WorldData {
+    const Scene* owner = nullptr;
+    const trb_scene_desc* flat = nullptr;        // attrib.vertices / normals / texcoords, indices, material ids, materials
+    std::vector<v3f> shapesCenter;               // renderer.cpp:294-301
+    std::vector<float> shapesRadius;             // shapesAABOX[s].max.x - shapesCenter[s].x (renderer.cpp:349-353)
+    size_t nShapes() const { return flat ? flat->n_shapes : 0; }
+    size_t nMaterials() const { return flat ? flat->n_materials : 0; }
+};
+
 // BSDF (core.h:256-318). eval/sample return f * cos(theta_i); directions are in the local shading frame.
 struct BSDF {
     enum EBSDFType { EUnknown = 0x0, EDiffuseReflection = 0x2, EGlossyReflection = 0x8, EDeltaReflection = 0x20, EDeltaTransmission = 0x40,
                      EDelta = 0x1 | EDeltaReflection | EDeltaTransmission };
+    const WorldData& worldData;   // core.h:296-298
+    const Config& config;
+    v3f emission;                 // core.h:299, :303: materials[matID].emission
     const Scene& scene;
     size_t matID;
     unsigned combinedType = EUnknown;
     bool emissive = false;
-    BSDF(const Scene& s, size_t id) : scene(s), matID(id) {}
+    BSDF(const WorldData& d, const Config& c, size_t matID);   // the reference's constructor (core.h:299-305)
+    BSDF(const Scene& s, size_t id);
     virtual ~BSDF() = default;
     virtual v3f eval(const SurfaceInteraction& i) const;
     virtual float pdf(const SurfaceInteraction& i) const;
@@ -163,8 +180,13 @@ struct Scene {  // core.h:352-374
     std::vector<std::unique_ptr<BSDF>> bsdfs;
     std::vector<Emitter> emitters;
     std::unique_ptr<AcceleratorBVH> bvh;
+    WorldData worldData;          // core.h:355 (a view, see WorldData)
     struct { float min[3], max[3]; } aabb{};
     size_t nShapes = 0, nTriangles = 0;
+    float getShapeArea(size_t shapeID) const;     // renderer.cpp:317-339: sum of the shape's face areas (fp32, face order)
+    float getShapeRadius(size_t shapeID) const;   // renderer.cpp:349-353
+    v3f getShapeCenter(size_t shapeID) const;     // renderer.cpp:355-358
+    size_t getFirstLight() const { return emitters.empty() ? 0 : emitters[0].shapeID; }   // renderer.cpp:360-362
 
     explicit Scene(const Config& config);
     ~Scene();
@@ -194,6 +216,13 @@ struct Integrator {  // integrator.h:23-70
     virtual void describe(trb_checkpoint_info& info) const { std::memset(&info, 0, sizeof(info)); }
     virtual void cleanUp() { save(); }                          // integrator.cpp:22-24
     bool save();                                                // writes <toml stem>.exr (integrator.cpp:26-30, utils.h:95-156)
+    // emitter / BSDF getters (integrator.h:37-60, integrator.cpp:32-63): host evaluators over the tables the device uses
+    const Emitter& getEmitterByID(int emitterID) const { return scene.emitters[size_t(emitterID)]; }
+    size_t getEmitterIDByShapeID(size_t shapeID) const;         // throws std::out_of_range where the reference asserts
+    float getEmitterPdf(const Emitter&) const { return 1.f / scene.emitters.size(); }   // integrator.cpp:60-62: the selection probability, as written
+    const BSDF* getBSDF(const SurfaceInteraction& hit) const;   // by (shapeID, primID), integrator.cpp:35-39
+    v3f getEmission(const SurfaceInteraction& hit) const;       // materials[hit.matID].emission, integrator.cpp:41-44
+    size_t selectEmitter(float sample, float& pdf) const;       // integrator.cpp:46-51
 };
 
 struct BDPTIntegrator : Integrator {  // bdpt.h:37-518

@@ -18,6 +18,29 @@ int main(int argc, char** argv) {
     bool rt = loadTOML(config, argv[1]);
     Renderer renderer(config);
     if (!renderer.init(rt, true)) return 3;
+    {   // the reference's own signatures (core.h:299-305, 352-374; integrator.h:37-60) on the loaded scene
+        const Scene& sc = renderer.scene;
+        struct MyDiffuse : BSDF {   // a BSDF subclass written against the reference's constructor
+            MyDiffuse(const WorldData& d, const Config& c, size_t matID) : BSDF(d, c, matID) { combinedType = EDiffuseReflection; }
+            std::string toString() const override { return "MyDiffuse"; }
+        };
+        MyDiffuse mine(sc.worldData, sc.config, 0);
+        const Integrator& in = *renderer.integrator;
+        if (&mine.worldData != &sc.worldData || &mine.config != &config || !(mine.emission == sc.bsdfs[0]->emission)) return 6;
+        if (sc.emitters.empty()) return 6;
+        const Emitter& em = in.getEmitterByID(0);
+        if (in.getEmitterIDByShapeID(em.shapeID) != 0 || in.getEmitterPdf(em) != 1.f / sc.emitters.size()) return 6;
+        float pdf = 0.f;
+        if (in.selectEmitter(0.999999f, pdf) != sc.emitters.size() - 1 || pdf != 1.f / sc.emitters.size()) return 6;
+        if (sc.getShapeArea(em.shapeID) != em.area || !(sc.getShapeRadius(em.shapeID) > 0.f) || sc.getFirstLight() != em.shapeID) return 6;
+        SurfaceInteraction lightFace; lightFace.shapeID = em.shapeID; lightFace.primID = 0;
+        const BSDF* lb = in.getBSDF(lightFace);
+        lightFace.matID = int(lb->matID);
+        if (!lb->isEmissive() || !(in.getEmission(lightFace) == em.radiance)) return 6;
+        v3f c = sc.getShapeCenter(em.shapeID);
+        std::printf("api_check: emitter shape %zu area %g centre (%g %g %g) radius %g\n", em.shapeID, double(em.area), double(c.x), double(c.y), double(c.z),
+                    double(sc.getShapeRadius(em.shapeID)));
+    }
     FILE* f = std::fopen(argv[2], "rb");
     if (!f) return 4;
     int32_t n = 0;

@@ -316,3 +316,33 @@ def test_multi_gpu_entry_points_fail_cleanly(trb, gpu_ctx, tmp_path):
     r = subprocess.run([sys.executable, str(prog)], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
     assert f"CODE {trb.TRB_ERR_UNSUPPORTED}" in r.stdout and "no_such_libnccl.so" in r.stdout, r.stdout
+
+
+def test_patched_reference_renders_on_the_device(trb, gpu_ctx, tmp_path):
+    """INTEGRATION.md section B, compiled and run (`make -C oracle ref_b200` -> oracle/_ref/tinyrender_ref_b200): the reference's OWN
+    main(), loadTOML, tinyobj loader, Scene::load and saveEXR, with BDPTIntegrator::renderFrame bound to libtrb.so by the three edits
+    the document lists.  The frame must come from the device ("B200 path:" line, no CPU pixel loop), equal the library's own render of
+    the same description (same seed => same sample streams; half-float storage), and match the reference's shipped converged image."""
+    cv2 = pytest.importorskip("cv2")
+    exe = ROOT / "oracle" / "_ref" / "tinyrender_ref_b200"
+    if not exe.exists():
+        pytest.skip("oracle/_ref/tinyrender_ref_b200 not built (make -C oracle ref_b200, where /root/reference exists)")
+    g = np.load(GOLD / "image_caustic_rr8.npz")
+    W, H, rr = int(g["width"]), int(g["height"]), int(g["rr_depth"])
+    _, toml = _export(trb, "caustic", tmp_path, width=W, height=H, rr_depth=rr, spp=128)
+    r = subprocess.run([str(exe), str(toml), "nogui"], capture_output=True, text=True, timeout=900, env=dict(os.environ, TRB_SEED="4242"))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "B200 path:" in r.stdout and "Saved EXR" in r.stdout, r.stdout + r.stderr
+    assert "falling back" not in r.stdout + r.stderr
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    bgr = cv2.imread(str(tmp_path / "scene.exr"), cv2.IMREAD_UNCHANGED)
+    assert bgr is not None and bgr.shape == (H, W, 3)
+    ref_img = bgr[:, :, ::-1].astype(np.float32)
+    mine, _ = gpu_ctx("caustic").render_bdpt(trb.render_desc(width=W, height=H, spp=128, rr_depth=rr, seed=4242))
+    # same description and seed: the same sample streams (float atomics may reorder sums; the EXR stores halves)
+    assert np.allclose(ref_img, mine, rtol=4e-3, atol=2e-4), float(np.abs(ref_img - mine).max())
+    a, b = _box(ref_img, int(g["box"])), g["image"].astype(np.float64)
+    rel_mse = float(np.mean((a - b) ** 2 / (b ** 2 + 1e-3)))
+    ratio = float(ref_img.mean() / float(g["mean"]))
+    print(f"patched reference on the device vs cbox_bdpt_glass_8depth.exr: relMSE {rel_mse:.2e}, mean ratio {ratio:.4f}")
+    assert rel_mse <= 2e-3 and abs(ratio - 1) <= 0.01

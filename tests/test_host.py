@@ -238,6 +238,11 @@ def test_cpp_host_api_compiles_and_fails_loudly_without_gpu(trb, tmp_path):
     toml.write_text(body % "nonsense")
     r = subprocess.run([str(exe), str(toml)], capture_output=True, text=True)
     assert r.returncode == 7 and "Invalid integrator type" in r.stdout  # main.cpp:109
+    # the program that drives the API like the reference's own code - including a BSDF subclass built with the reference's constructor
+    # signature BSDF(const WorldData&, const Config&, size_t) and the Scene / Integrator getters - compiles warning-free (it RUNS in
+    # tests/test_gpu_image.py: Scene::load needs a device)
+    subprocess.run(["g++", "-std=c++17", "-Wall", "-Werror", "-I", str(root / "include"), str(root / "tests/cpp/api_check.cpp"), "-o", str(tmp_path / "api_check"),
+                    "-L", str(pkg), "-l:libtrb.so", f"-Wl,-rpath,{pkg}", *trb_build._stdcxx_link_args(), "-lm"], check=True)
     cli = pkg / "tinyrender_b200"
     assert cli.exists()
     r = subprocess.run([str(cli)], capture_output=True, text=True)
