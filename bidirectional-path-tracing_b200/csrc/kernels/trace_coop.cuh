@@ -37,6 +37,16 @@
 #define TRB_COOP_Q 512u       // queue entries per warp (power of two); a node phase adds at most 8 x 32
 #endif
 
+// -DTRB_CHECKS (build.py --variant checks): a device assert on every index the traversal kernels form - node, triangle, stack, per-warp
+// queue occupancy, deferred-ray queue, outstanding-test counts.  compute-sanitizer is closed on this pool, so this variant run over
+// tools/sanitize_small.py (tests/test_gpu_build.py::test_checked_build_runs_clean) is the memory-safety evidence of the traversal.
+#ifdef TRB_CHECKS
+#include <cassert>
+#define TRB_CHECK(x) assert(x)
+#else
+#define TRB_CHECK(x) ((void)0)
+#endif
+
 namespace trbk {
 
 struct TraceArgs {
@@ -55,6 +65,7 @@ struct TraceArgs {
     uint32_t* fetch;         // queue cursor of THIS launch (zeroed by the host before the launch)
     int32_t* defer_q;        // k_trace_wide: slots of the rays it leaves to k_trace_coop, and their count
     uint32_t* defer_n;
+    uint32_t n_nodes, n_wnodes, n_tris, defer_cap;   // array lengths (TRB_CHECKS builds assert against them)
     unsigned long long* visit;      // TRB_COUNTERS builds: [0] nodes visited, [1] triangles tested
     unsigned long long* visit_exh;  // TRB_COUNTERS builds: exhaustive re-traces
 };
@@ -96,6 +107,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
     __syncwarp();
 
     auto push_range = [&](uint32_t first, uint32_t cnt) {   // this lane's ray must test triangles [first, first+cnt)
+        TRB_CHECK(cnt >= 1u && cnt <= 8u && first + cnt <= a.n_tris);
         const uint32_t base = atomicAdd(&sh.tail, cnt);
         const uint32_t e0 = (uint32_t(lane) << 27) | first;
 #pragma unroll
@@ -179,6 +191,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         }
         // ---- node phase ----
         if (cur >= 0) {
+            TRB_CHECK(uint32_t(cur) < a.n_nodes);
             const F4* np = a.bvh.nodes + 4 * size_t(cur);
             const F4 na = ld4(np), nb = ld4(np + 1), nc = ld4(np + 2), nd = ld4(np + 3);
 #ifdef TRB_COUNTERS
@@ -210,6 +223,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             if (stop) { cur = -1; sp = 0; }
             else if (i0 && i1) {
                 const bool swap = !exh && (e1 < e0);  // nearer child first when pruning
+                TRB_CHECK(sp < TRB_STACK);
                 stack[sp++] = swap ? r0 : r1;
                 cur = swap ? r1 : r0;
             } else if (i0) cur = r0;
@@ -219,6 +233,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         __syncwarp();
         // ---- triangle phases: full warps of queued tests; drain when no lane is traversing or the queue is filling up ----
         uint32_t count = sh.tail - head;
+        TRB_CHECK(count <= TRB_COOP_Q);   // the per-warp queue never wraps onto unread entries
         const bool trav = __ballot_sync(FULL, cur >= 0) != 0;
         while (count >= TRB_COOP_DRAIN || (count > 0u && (!trav || count > TRB_COOP_Q - 256u))) {
             const uint32_t nb_ = min(count, 32u);
@@ -231,6 +246,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             o.dx = __shfl_sync(FULL, r.dx, owner); o.dy = __shfl_sync(FULL, r.dy, owner); o.dz = __shfl_sync(FULL, r.dz, owner);
             o.max_t = __shfl_sync(FULL, r.max_t, owner); o.min_t = 0.f;
             if (act) {
+                TRB_CHECK(pos < a.n_tris);
                 const F4* tp = a.bvh.tris + 3 * size_t(pos);
                 F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
 #ifdef TRB_COUNTERS
@@ -249,7 +265,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                     }
                 }
                 if (ill) atomicOr(&sh.flags[owner], 1u);
-                atomicSub(&sh.outst[owner], 1);
+                { const int before = atomicSub(&sh.outst[owner], 1); TRB_CHECK(before >= 1); (void)before; }
             }
             head += nb_; count -= nb_;
             __syncwarp();

@@ -189,6 +189,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
     __syncwarp();
 
     auto push = [&](int32_t x) {
+        TRB_CHECK(sp < TRB_SSTACK + TRB_LSTACK);
         if (sp < TRB_SSTACK) sstack[sp][threadIdx.x] = x; else lstack[sp - TRB_SSTACK] = x;
         ++sp;
     };
@@ -200,6 +201,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
     // this lane's ray must test the triangles of leaf code ca, then of cb (cb = 0: none); <= 8 entries in all
     auto push_leaves = [&](uint32_t ca, uint32_t cb) {
         const uint32_t na = ca & 7u, cnt = na + (cb & 7u);
+        TRB_CHECK(na >= 1u && na <= 4u && (cb & 7u) <= 4u && (ca >> 3) + na <= a.n_tris && (cb >> 3) + (cb & 7u) <= a.n_tris);
         const uint32_t base = atomicAdd(&sh.tail, cnt);
         const uint32_t ea = (uint32_t(lane) << 27) | (ca >> 3), eb = ((uint32_t(lane) << 27) | (cb >> 3)) - na;
 #pragma unroll
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                     float4 r0 = rp[0], r1 = rp[1];
                     r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.dx = r0.w; r.dy = r1.x; r.dz = r1.y; r.min_t = r1.z; r.max_t = r1.w;
                     pre = ray_pre(r);
-                    if (pre.degenerate) a.defer_q[atomicAdd(a.defer_n, 1u)] = slot;   // for the reference's own tree (k_trace_coop)
+                    if (pre.degenerate) { const uint32_t at = atomicAdd(a.defer_n, 1u); TRB_CHECK(at < a.defer_cap); a.defer_q[at] = slot; }   // for the reference's own tree (k_trace_coop)
                     else { have = true; exh = false; start_ray(); }
                 }
                 more = cnt == 0 || (base + cnt < n);
@@ -285,6 +287,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                 if (stop) sp = 0; else push_leaves(uint32_t(~cur), 0u);
                 cur = pop();
             } else {
+                TRB_CHECK(uint32_t(cur) < a.n_wnodes);
                 const float* np = reinterpret_cast<const float*>(a.wnodes + 8 * size_t(cur));
 #if TRB_WIDE_LD256
                 const F8 h0a = ld8(np), h0b = ld8(np + 8), h1a = ld8(np + 16), h1b = ld8(np + 24);   // 4 x LDG.256
@@ -334,6 +337,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         __syncwarp();
         // ---- triangle phases: full warps of queued tests; drain when no lane is traversing or the queue is filling up ----
         uint32_t count = sh.tail - head;
+        TRB_CHECK(count <= TRB_COOP_Q);   // the per-warp queue never wraps onto unread entries
         const bool trav = __ballot_sync(FULL, cur != NONE) != 0;
         while (count >= TRB_COOP_DRAIN || (count > 0u && (!trav || count > TRB_COOP_Q - 256u))) {
             const uint32_t nb_ = min(count, 32u);
@@ -348,6 +352,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             float t = 0.f, u, v;
             bool ill = false, thit = false;
             if (act) {
+                TRB_CHECK(pos < a.n_tris);
                 const F4* tp = a.bvh.tris + 3 * size_t(pos);
                 F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
 #ifdef TRB_COUNTERS
@@ -373,7 +378,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             if (run_head) {
                 const unsigned rest = lane == 31 ? 0u : (heads >> (lane + 1));
                 const int len = rest ? __ffs(int(rest)) : int(nb_) - lane;
-                atomicSub(&sh.outst[owner], len);
+                { const int before = atomicSub(&sh.outst[owner], len); TRB_CHECK(len >= 1 && before >= len); (void)before; }
             }
             head += nb_; count -= nb_;
             __syncwarp();

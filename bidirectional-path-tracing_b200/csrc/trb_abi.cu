@@ -146,8 +146,9 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     TraceArgs a{};
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.n_nodes = uint32_t(c->flat.n_nodes); a.n_wnodes = uint32_t(c->flat.n_wnodes); a.n_tris = uint32_t(c->flat.n_tris);
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = ctr;
-    a.defer_q = c->defer_q[0].p; a.defer_n = ctr + 1;
+    a.defer_q = c->defer_q[0].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
     const int grid = trace_grid(c->prop.multiProcessorCount);
     if (c->force_binary) { k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a); return; }
@@ -164,8 +165,9 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     TraceArgs a{};
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.n_nodes = uint32_t(c->flat.n_nodes); a.n_wnodes = uint32_t(c->flat.n_wnodes); a.n_tris = uint32_t(c->flat.n_tris);
     a.rays = rays; a.q = nullptr; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = ctr;
-    a.defer_q = c->defer_q[which].p; a.defer_n = ctr + 1;
+    a.defer_q = c->defer_q[which].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
     const int grid = trace_grid(c->prop.multiProcessorCount);
     if (c->force_binary) { k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a); return; }
@@ -1509,9 +1511,10 @@ extern "C" int trb_trace_any_device_noalloc(trb_context* c, const trb_ray* d_ray
     TraceArgs a{};
     a.bvh = BvhView{c->sc.nodes, c->sc.tris, c->sc.root_ref};
     a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
+    a.n_nodes = uint32_t(c->flat.n_nodes); a.n_wnodes = uint32_t(c->flat.n_wnodes); a.n_tris = uint32_t(c->flat.n_tris);
     a.rays = reinterpret_cast<const RayT*>(d_rays); a.q = nullptr; a.n_ptr = nullptr; a.n_fixed = uint32_t(n); a.cap = uint32_t(n);
     a.occ_out = d_out; a.pend = nullptr; a.accum = nullptr; a.fetch = ctr;
-    a.defer_q = defer_q; a.defer_n = ctr + 1;
+    a.defer_q = defer_q; a.defer_n = ctr + 1; a.defer_cap = uint32_t(TRB_NOALLOC_MAX_RAYS);
     a.visit = nullptr; a.visit_exh = nullptr;
     const int grid = trace_grid(c->prop.multiProcessorCount);
     k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);

@@ -70,3 +70,21 @@ def test_device_build_at_size_and_edge_cases(trb, gold):
     assert np.array_equal(h["tri"], g["tri"]) and np.array_equal(h["t"][g["hit"] == 1].view(np.uint32), g["tuv"][g["hit"] == 1, 0].view(np.uint32))
     assert np.array_equal(ctx.trace_any(rays), g["occluded"])
     ctx.close()
+
+
+def test_checked_build_runs_clean(trb):
+    """compute-sanitizer is closed on this pool, so memory safety of the traversal is checked by the kernels themselves: libtrb_checks.so
+    (-DTRB_CHECKS: a device assert on every node / triangle / stack / per-warp-queue / deferred-queue index and on the outstanding-test
+    counts, csrc/kernels/trace_coop.cuh) runs tools/sanitize_small.py - every entry point and integrator on the Cornell, tessellated
+    (device-built BVH) and textured scenes, tiny waves so that queues refill many times.  A failed assert is a CUDA error and a
+    non-zero exit."""
+    import os
+    import subprocess
+    import sys
+    root = Path(__file__).resolve().parent.parent
+    lib = root / "bidirectional-path-tracing_b200" / "libtrb_checks.so"
+    if not lib.exists():
+        pytest.skip("libtrb_checks.so not built (python bidirectional-path-tracing_b200/build.py --variant checks -DTRB_CHECKS=1)")
+    r = subprocess.run([sys.executable, str(root / "tools" / "sanitize_small.py")], env=dict(os.environ, TRB_LIB=str(lib)), capture_output=True, text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert "Assertion" not in r.stderr and "textured means" in r.stdout
