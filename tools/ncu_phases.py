@@ -33,7 +33,14 @@ def main():
     merge = line_of(w, "if (thit) {", tri)
     end = line_of(w, "#ifdef TRB_COUNTERS", merge)
     pl1 = line_of(w, "auto start_ray", k0)
-    qa = line_of(w, "// ---- queue append", k0)
+    try:
+        pl0 = line_of(w, "auto push_leaves", k0)      # shipped kernel: the queue append is a lambda before start_ray
+    except KeyError:
+        pl0 = pl1
+    try:
+        qa = line_of(w, "// ---- queue append", k0)   # convergent variants: a block between the node phase and the triangle phases
+    except KeyError:
+        qa = None
     ps0 = line_of(w, "auto push = ", k0)
     box0, box1 = line_of(t, "struct BoxF"), line_of(t, "// rayTriangleIntersect")
     tt0 = line_of(t, "TRB_HD bool tri_test")
@@ -43,11 +50,12 @@ def main():
 
     def bucket(f, ln):
         if f == "trace_wide.cuh":
-            if ps0 <= ln < pl1: return "stack push/pop"
+            if ps0 <= ln < pl0: return "stack push/pop"
+            if pl0 <= ln < pl1: return "queue append (push_leaves)"
             if pl1 <= ln < loop: return "start_ray / setup"
             if loop <= ln < node: return "refill + finish (idle lanes)"
-            if node <= ln < qa: return "node phase (own lines)"
-            if qa <= ln < tri: return "queue append (prefix sum + stores)"
+            if node <= ln < (qa or tri): return "node phase (own lines)"
+            if qa and qa <= ln < tri: return "queue append (prefix sum + stores)"
             if tri <= ln < merge: return "triangle phase: fetch entries, shuffles"
             if merge <= ln < end: return "triangle phase: merge + outst"
             return "kernel other"
