@@ -24,6 +24,8 @@ TRB_FLAG_NO_JITTER = 1
 TRB_FLAG_NO_OVERLAP = 2
 TRB_FLAG_RUSSIAN_ROULETTE = 4  # the reference's NO_RR 0 behaviour (bdpt.h:18,68,129); default off = shipped behaviour
 TRB_RR_DEFAULT_MAX_DEPTH = 32
+TRB_FLAG_LIGHT_TRACING = 16  # the reference's estimator A/B switches (bdpt.h:16-17): only the light walk / only the eye walk, no MIS weights
+TRB_FLAG_PATH_TRACING = 32
 TRB_FLAG_SORT_RAYS = 8      # accepted and ignored (round-1 experiment, removed: profiles/r1f_tuning_variants.md)
 
 

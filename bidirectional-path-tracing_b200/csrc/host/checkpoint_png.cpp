@@ -117,7 +117,7 @@ bool save_png_srgb(const std::string& path, const float* rgb, int w, int h, floa
 // Same render?  Everything that shapes the image must agree; the sample range, wave size and stream flags may differ.
 bool checkpoint_matches(const trb_checkpoint_info& a, const trb_checkpoint_info& b) {
     const trb_render_desc &x = a.desc, &y = b.desc;
-    const uint32_t image_flags = TRB_FLAG_NO_JITTER | TRB_FLAG_RUSSIAN_ROULETTE;
+    const uint32_t image_flags = TRB_FLAG_NO_JITTER | TRB_FLAG_RUSSIAN_ROULETTE | TRB_FLAG_LIGHT_TRACING | TRB_FLAG_PATH_TRACING;
     bool same = std::memcmp(x.eye, y.eye, sizeof(x.eye)) == 0 && std::memcmp(x.at, y.at, sizeof(x.at)) == 0 && std::memcmp(x.up, y.up, sizeof(x.up)) == 0 &&
                 x.fov_deg == y.fov_deg && x.width == y.width && x.height == y.height && x.spp == y.spp && x.rr_depth == y.rr_depth && x.seed == y.seed &&
                 (x.flags & image_flags) == (y.flags & image_flags) && x.max_depth == y.max_depth && a.integrator == b.integrator && a.scene_hash == b.scene_hash;

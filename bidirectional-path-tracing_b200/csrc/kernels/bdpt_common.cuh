@@ -100,6 +100,7 @@ struct WaveParams {
 enum : uint32_t { CTR_QOUT = 0, CTR_SHADOW = 1, CTR_CONN = 2, CTR_SPARE = 3, CTR_FETCH_CLOSEST = 4, CTR_FETCH_ANY = 8, CTR_N = 12 };
 enum : uint32_t { TRACE_CTR_WORDS = 3 };
 enum : uint32_t { SLOT_PURE_SPECULAR = 1u };
+#define TRB_EST_MASK (TRB_FLAG_LIGHT_TRACING | TRB_FLAG_PATH_TRACING)   // the reference's estimator A/B switches (bdpt.h:16-17)
 
 // ---- random numbers ----------------------------------------------------------------------------------
 // Production: counter-based, keyed by (seed, pixel, sample index, dimension) - independent of wave size and GPU count.  The key

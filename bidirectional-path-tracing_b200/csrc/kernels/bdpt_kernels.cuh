@@ -99,7 +99,7 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
                 float prevRev = bsdf_pdf(m, wi, s.wo) * rr;  // wi/wo swapped (bdpt.h:342)
                 float lightWeight = (revPdfA / nlight) * (vcm + prevRev * vc);
                 float mis = 1.f / (lightWeight + 1.f + 0.f);
-                radiance = radiance * mis;
+                if (!(p.flags & TRB_EST_MASK)) radiance = radiance * mis;   // bdpt.h:355-357: unweighted under LIGHT_TRACING / PATH_TRACING
                 int pixel = yp * p.cam.width + xp;
                 if (p.parity) {
                     target = uint32_t(slot) * uint32_t(p.K + 1) + uint32_t(depth);
@@ -152,8 +152,8 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
         float4 sv = p.st_v[i];
         uint32_t ctr = __float_as_uint(sv.z);
         uint32_t flags = 0;
-        if (hit_valid(h, cr)) {  // bdpt.h:225: no subpaths at all when the primary ray misses
-            flags |= 2u;
+        if (hit_valid(h, cr)) flags |= 2u;   // bdpt.h:225: no subpaths at all when the primary ray misses
+        if ((flags & 2u) && !(p.flags & TRB_FLAG_PATH_TRACING)) {   // (PATH_TRACING, bdpt.h:232-233: no light walk, no draws)
             uint32_t pixel, sample;
             slot_ids(p, i, &pixel, &sample);
             Rng rng = make_rng(p, i, pixel, sample, ctr);
@@ -320,7 +320,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ 
             float imgToSolid = ipd * ipd / cosCamera;
             float t1Pdf = 1.f * imgToSolid;
             float vcm = float(p.cam.width * p.cam.height) * (1.f / t1Pdf);
-            bool cont = 1 < p.rr_depth;
+            bool cont = 1 < p.rr_depth || (p.flags & TRB_FLAG_LIGHT_TRACING);
             if (!cont) {  // the loop test of bdpt.h:68 draws (Q3); with rr == 1 the draw always passes
                 sv.z = __uint_as_float(__float_as_uint(sv.z) + 1u);
                 cont = p.rr_on && 1 < p.max_depth;
@@ -382,7 +382,8 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
                     float dirPdfW = TRB_INV_TWOPI;
                     float cameraWeight = posPdfA * vcm + (posPdfA * dirPdfW) * vc;
                     float mis = 1.f / (1.f + cameraWeight);
-                    if (!pure) c = c * mis;
+                    if (!pure && !(p.flags & TRB_EST_MASK)) c = c * mis;                 // bdpt.h:95-100
+                    if ((p.flags & TRB_FLAG_PATH_TRACING) && !pure) c = mk(0.f, 0.f, 0.f);   // bdpt.h:110-113: NEE already counted this light path
                 } else {
                     c = m.ke;
                 }
@@ -393,6 +394,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
             } else {
                 connect = !is_delta(m);
             }
+            if (p.flags & TRB_FLAG_LIGHT_TRACING) { alive = false; connect = false; }   // bdpt.h:229-231: Li = getEmission(hit), no eye walk
         }
     }
     const float rr = rr_prob(p, depth, T);
@@ -420,7 +422,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
                     float eyeCurRevA = cosAtEye * (1.f / d2) * dirPdfW;
                     float eyeWeight = eyeCurRevA * (vcm + eyePrevRevW * vc);
                     float mis = 1.f / (lightWeight + 1.f + eyeWeight);
-                    Li = Li * mis;
+                    if (!(p.flags & TRB_EST_MASK)) Li = Li * mis;   // bdpt.h:426-428
                     Li = Li * li_scale;
                     want = true;
                 }
@@ -432,7 +434,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
     // A slot has 0..K stored light vertices (3-4 on average): one thread per (slot, j < K) left most lanes of the pair kernel
     // without work.  Each connecting lane reserves nlv entries (warp scan + one atomic per warp) and writes them in order.
     {
-        const int nl = connect ? p.nlv[slot] : 0;
+        const int nl = (connect && !(p.flags & TRB_EST_MASK)) ? p.nlv[slot] : 0;   // bdpt.h:145-149
         int inc = nl;
         const int lane = threadIdx.x & 31;
 #pragma unroll

@@ -650,7 +650,8 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     int stage = 0;
     p.counters = stage_ctr(stage); p.q_out = qa;
     k_light_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
-    for (int depth = 1; depth <= K; ++depth) {
+    const bool light_only = (d.flags & TRB_FLAG_LIGHT_TRACING) != 0, eye_only = (d.flags & TRB_FLAG_PATH_TRACING) != 0;   // bdpt.h:16-17, 229-237
+    for (int depth = 1; depth <= (eye_only ? 0 : K); ++depth) {
         const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
         p.q_in = (stage % 2 == 0) ? qa : qb;
         p.q_out = (stage % 2 == 0) ? qb : qa;
@@ -665,7 +666,7 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     stage = kk + 1;
     p.counters = stage_ctr(stage); p.q_out = qa;
     k_eye_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
-    for (int depth = 1; depth <= K; ++depth) {
+    for (int depth = 1; depth <= (light_only ? 1 : K); ++depth) {   // (LIGHT_TRACING: one pass that adds the primary hit's emission)
         const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
         const bool even = ((stage - (kk + 1)) % 2 == 0);
         p.q_in = even ? qa : qb;
@@ -692,6 +693,8 @@ int check_desc(trb_context* c, const trb_render_desc* d) {
     if (!c->has_scene) return c->fail(TRB_ERR_NO_SCENE, "no scene uploaded");
     if (!d || d->width <= 0 || d->height <= 0 || d->spp <= 0 || d->rr_depth < 1) return c->fail(TRB_ERR_INVALID, "bad render description");
     if (d->rr_depth > 64) return c->fail(TRB_ERR_INVALID, "rr_depth > 64 is not supported");
+    if ((d->flags & TRB_FLAG_LIGHT_TRACING) && (d->flags & TRB_FLAG_PATH_TRACING))
+        return c->fail(TRB_ERR_INVALID, "TRB_FLAG_LIGHT_TRACING and TRB_FLAG_PATH_TRACING exclude each other");
     if (rr_enabled(*d) && (max_depth_of(*d) < d->rr_depth || max_depth_of(*d) > 64))
         return c->fail(TRB_ERR_INVALID, "Russian roulette: max_depth must lie in [rr_depth, 64]");
     return TRB_OK;

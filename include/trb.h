@@ -125,6 +125,13 @@ typedef struct trb_render_desc {
  * behaviour: rr_depth is a hard cap.  renderer.rrProb is read but never used by the reference (bdpt.h:40). */
 #define TRB_FLAG_RUSSIAN_ROULETTE 4u
 #define TRB_RR_DEFAULT_MAX_DEPTH 32
+/* The reference's estimator A/B switches (`#define LIGHT_TRACING 0`, `#define PATH_TRACING 0`, bdpt.h:16-17), which its author flips to
+ * check the bidirectional estimator against its two halves.  LIGHT_TRACING: only the light walk runs; splats carry no MIS weight and Li is
+ * the emission of the primary hit (bdpt.h:229-231, 355-357).  PATH_TRACING: only the eye walk runs; no vertex connections, next-event
+ * estimation and emitter hits carry no MIS weight, and an emitter hit counts only on a purely specular path (bdpt.h:95-118, 145-149,
+ * 232-233, 426-428).  Setting both is refused (the reference's #if / #elif would take LIGHT_TRACING with PATH_TRACING's weights). */
+#define TRB_FLAG_LIGHT_TRACING 16u
+#define TRB_FLAG_PATH_TRACING 32u
 /* Accepted and ignored.  (Round 1 had an experiment behind it: a counting sort of each ray queue before traversal; the traversal got
  * 10-15 % faster and the sort cost more than that - profiles/r1f_tuning_variants.md - so the code was removed in round 2.) */
 #define TRB_FLAG_SORT_RAYS 8u

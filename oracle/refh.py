@@ -20,8 +20,13 @@ REF_BIN = HERE / "_ref" / "tinyrender_ref"
 REF_RR_LIB = HERE / "_ref" / "libtr_ref_rr.so"
 
 
-def available(rr: bool = False) -> bool:
-    return (REF_RR_LIB if rr else REF_LIB).exists()
+# ... and with one of its estimator A/B switches flipped (`make -C oracle ref_lt ref_pt`: LIGHT_TRACING 1 / PATH_TRACING 1, bdpt.h:16-17)
+VARIANT_LIBS = {False: REF_LIB, True: REF_RR_LIB, "lt": HERE / "_ref" / "libtr_ref_lt.so", "pt": HERE / "_ref" / "libtr_ref_pt.so"}
+
+
+def available(rr=False) -> bool:
+    """rr: False = the reference as shipped, True = NO_RR 0, "lt" / "pt" = LIGHT_TRACING 1 / PATH_TRACING 1"""
+    return VARIANT_LIBS[rr].exists()
 
 
 def write_toml(path, objfile, width=800, height=600, spp=1, rr_depth=5, eye=(0.0, 0.8, 3.8), at=(0.0, 0.8, 0.0),
@@ -39,11 +44,11 @@ def write_toml(path, objfile, width=800, height=600, spp=1, rr_depth=5, eye=(0.0
 _libs = {}
 
 
-def _L(rr: bool = False):
+def _L(rr=False):
     if rr not in _libs:
-        path = REF_RR_LIB if rr else REF_LIB
+        path = VARIANT_LIBS[rr]
         if not path.exists():
-            raise FileNotFoundError(f"{path} missing: run `make -C oracle {'ref_rr' if rr else 'ref'}` where /root/reference exists")
+            raise FileNotFoundError(f"{path} missing: run `make -C oracle ref ref_rr ref_lt ref_pt` where /root/reference exists")
         L = C.CDLL(str(path))
         L.refh_open.restype = C.c_void_p
         L.refh_open.argtypes = [C.c_char_p]
@@ -60,7 +65,7 @@ def _p(a):
 class RefHarness:
     """The reference renderer opened on a TOML scene file (stdout chatter of the reference is kept)."""
 
-    def __init__(self, toml_path, rr: bool = False):
+    def __init__(self, toml_path, rr=False):
         self.L = _L(rr)
         self.h = C.c_void_p(self.L.refh_open(str(toml_path).encode()))
         if not self.h:
@@ -71,7 +76,7 @@ class RefHarness:
          self.height, self.spp, self.rr_depth) = [int(x) for x in c]
 
     @classmethod
-    def open_scene(cls, objfile, rr: bool = False, **kw):
+    def open_scene(cls, objfile, rr=False, **kw):
         d = tempfile.mkdtemp(prefix="refh_")
         return cls(write_toml(os.path.join(d, "scene.toml"), objfile, **kw), rr=rr)
 

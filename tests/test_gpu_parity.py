@@ -281,14 +281,17 @@ def ref_harness(trb):
 
     objs = {}
 
-    def get(name, width=64, height=64, rr_depth=8, spp=1):
-        key = (name, width, height, rr_depth, spp)
+    def get(name, width=64, height=64, rr_depth=8, spp=1, variant=False):
+        """variant: False = the reference as shipped, "lt" / "pt" = built with LIGHT_TRACING 1 / PATH_TRACING 1 (oracle/Makefile)"""
+        if not refh.available(variant):
+            pytest.skip(f"oracle/_ref variant {variant!r} not built")
+        key = (name, width, height, rr_depth, spp, variant)
         if key not in cache:
             if name not in objs:
                 scene = trb.HostScene.load_npz(Path(__file__).parent / "golden" / f"scene_{name}.npz")
                 objs[name] = (scene_to_obj.export_verified(scene, Path(tempfile.mkdtemp(prefix="trb_t_")) / "scene.obj"), scene)
             obj, scene = objs[name]
-            cache[key] = (refh.RefHarness.open_scene(obj, width=width, height=height, spp=spp, rr_depth=rr_depth), scene)
+            cache[key] = (refh.RefHarness.open_scene(obj, rr=variant, width=width, height=height, spp=spp, rr_depth=rr_depth), scene)
         return cache[key]
     yield get
     for rh, _ in cache.values():
@@ -341,6 +344,38 @@ def test_bdpt_paths_live_at_baseline_film_and_depth(trb, gpu_ctx, ref_harness, p
     print(f"{name} 1024^2 rrDepth {rr_depth}: {ok.sum()}/{n} walks agree ({exact.sum()} Li bit for bit), {n_splats} splats, mean draws {g_draws.mean():.1f}")
     assert n_splats > n // 4 and (g_li > 0).any()
     assert ok.sum() >= n - 6, f"only {ok.sum()} of {n} walks within {REL}"   # measured: 2399, 2400, 2398, 2398 of 2400
+
+
+@pytest.mark.parametrize("variant,flag", [("lt", "TRB_FLAG_LIGHT_TRACING"), ("pt", "TRB_FLAG_PATH_TRACING")])
+@pytest.mark.parametrize("name", ["caustic", "hardlight"])
+def test_estimator_switches_match_reference(trb, gpu_ctx, ref_harness, parity_record, name, variant, flag):
+    """The reference's estimator A/B switches (`#define LIGHT_TRACING` / `PATH_TRACING`, bdpt.h:16-17, the author's consistency check of
+    the bidirectional estimator against its two halves) as TRB_FLAG_LIGHT_TRACING / TRB_FLAG_PATH_TRACING, against the reference COMPILED
+    with that switch flipped (`make -C oracle ref_lt ref_pt`), live on this box: whole samples with private Sampler(seed)s - Li, every
+    splat pixel and value, the number of draws."""
+    oracle_port = pytest.importorskip("oracle_port")
+    import dev_rays
+    W, H, rr_depth, n = 96, 72, 8, 1500
+    rh, scene = ref_harness(name, width=W, height=H, rr_depth=rr_depth, spp=4, variant=variant)
+    desc = trb.render_desc(width=W, height=H, spp=4, rr_depth=rr_depth, flags=getattr(trb, flag))
+    rng = np.random.default_rng(77)
+    cam = dev_rays.camera_rays(trb.camera_matrices(desc), (0.0, 0.8, 3.8), 30.0, W, H)
+    prays = cam[rng.choice(len(cam), n, replace=False)]
+    seeds = rng.integers(1, 2**31 - 1, n).astype(np.int32)
+    K = rr_depth - 1
+    g_li, g_pix, g_rgb, g_draws = rh.bdpt_paths(prays, seeds, K)
+    streams = np.stack([oracle_port.sampler_stream(int(s), 10 + 10 * K) for s in seeds])
+    li, pix, rgb, draws = gpu_ctx(name).bdpt_paths(desc, _rays(trb, prays), streams)
+    ok = _paths_agree(g_li, g_pix, g_rgb, li, pix, rgb) & (draws == g_draws)
+    parity_record(f"bdpt_paths_live/{name}/{flag}", ok.sum(), n, reference_splats=int((g_pix >= 0).sum()), mean_draws=float(g_draws.mean()))
+    print(f"{name} {flag}: {ok.sum()}/{n} walks agree, {int((g_pix >= 0).sum())} splats, mean draws {g_draws.mean():.1f}, mean Li {g_li.mean():.4f}")
+    if variant == "lt":
+        assert (g_pix >= 0).sum() > n // 4      # the light walk splats ...
+    else:
+        assert (g_pix < 0).all() and (g_li > 0).any()   # ... the eye walk never does
+    assert ok.sum() >= n - 4, f"only {ok.sum()} of {n} walks within {REL}"
+    with pytest.raises(trb.TrbError):
+        gpu_ctx(name).render_bdpt(trb.render_desc(width=16, height=16, spp=1, rr_depth=4, flags=trb.TRB_FLAG_LIGHT_TRACING | trb.TRB_FLAG_PATH_TRACING))
 
 
 def test_tessellated_scene_10m_vs_oracle(trb, parity_record):
