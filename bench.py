@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="skip the short configs[2] / configs[4] passes of the default line")
     ap.add_argument("--no-visits", action="store_true", help="skip the counters-build pass (A/B runs: no roofline figure)")
+    ap.add_argument("--_inproc", type=int, default=0, help=argparse.SUPPRESS)   # internal: N contexts in THIS process, trb_render_bdpt_multi
     ap.add_argument("--_visits", action="store_true", help=argparse.SUPPRESS)  # internal: counters build, prints visit stats
     return ap.parse_args()
 
@@ -389,6 +390,41 @@ def extra_block(trb, torch, name, spp, fb, flush, args):
         ctx.close()
 
 
+def run_inproc_child(args):
+    """one process, N contexts (one per device), trb_render_bdpt_multi: sample-index shards + ONE ncclReduce inside the library - the path
+    the C++ host API and the CLI use for `gpus = N`.  Wall clock around the call, frame buffer download included."""
+    trb = importlib.import_module(PKG)
+    n = args._inproc
+    wl = WORKLOADS[args.workload]
+    scene = load_scene(trb, wl)
+    ctxs = [trb.Context(g) for g in range(n)]
+    for c in ctxs:
+        c.upload(scene)
+    W, H = wl["width"], wl["height"]
+    desc = trb.render_desc(width=W, height=H, spp=args.spp * n, rr_depth=wl["rr_depth"], wave_samples=args.wave)
+    for _ in range(max(args.warmup, 1)):
+        trb.render_bdpt_multi(ctxs, desc)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        img, _ = trb.render_bdpt_multi(ctxs, desc)
+    sec = time.perf_counter() - t0
+    print(json.dumps({"value": W * H * args.spp * n * args.steps / sec / 1e6, "unit": UNIT, "n_gpus": n, "steps": args.steps, "ms_per_step": 1e3 * sec / args.steps,
+                      "image_mean": float(img.mean()), "d2h_bytes_per_step": W * H * 3 * 4,
+                      "timing": "host wall clock around trb_render_bdpt_multi (one process, one context per device, one ncclReduce, host frame buffer out)"}))
+
+
+def inproc_subprocess(args, n) -> dict:
+    """the in-library multi-GPU path, measured by rank 0 in a subprocess of its own with a hard timeout (the other ranks wait at a barrier)"""
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "LOCAL_RANK", "WORLD_SIZE", "MASTER_ADDR", "MASTER_PORT", "TORCHELASTIC_RUN_ID",
+                                                            "GROUP_RANK", "ROLE_RANK", "LOCAL_WORLD_SIZE", "GROUP_WORLD_SIZE", "ROLE_WORLD_SIZE")}
+    try:
+        r = subprocess.run([sys.executable, str(ROOT / "bench.py"), "--_inproc", str(n), "--workload", args.workload, "--spp", str(args.spp), "--wave", str(args.wave),
+                            "--steps", str(min(args.steps, 3)), "--warmup", "2"], env=env, capture_output=True, text=True, timeout=240)
+        return json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as e:  # noqa: BLE001
+        return {"error": str(e)[:300]}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -398,8 +434,11 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     wl = WORKLOADS[args.workload]
     torch.cuda.set_device(local)
+    cpu_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        if not args.no_extras:
+            cpu_group = dist.new_group(backend="gloo")
     scene = load_scene(trb, wl)
     ctx = trb.Context(local)
     t_up = time.perf_counter()
@@ -525,14 +564,29 @@ def run_ours(args):
                     out["cpu_ceiling"] = cpu_port_all_cores(trb, wl, fw, fh)
             except Exception as e:  # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "unavailable", "sample": str(e)}
+        if world > 1 and not args.no_extras:
+            # the same frame through ONE process (trb_render_bdpt_multi: what the C++ API / CLI use for gpus = N), next to the torchrun value
+            out["inproc_multi"] = inproc_subprocess(args, world)
         print(json.dumps(out))
     if world > 1:
+        if cpu_group is not None:
+            dist.barrier(group=cpu_group)   # the other ranks wait on the CPU: an NCCL barrier is a spinning kernel on their GPUs, which the
+                                            # in-process run of rank 0's child would time-slice against
         dist.destroy_process_group()
 
 
 if __name__ == "__main__":
     a = parse_args()
-    if a.impl == "reference":
+    if a._inproc > 0:
+        with quiet_stdout():
+            import io
+            buf = io.StringIO(); real = sys.stdout; sys.stdout = buf
+            try:
+                run_inproc_child(a)
+            finally:
+                sys.stdout = real
+        sys.stdout.write(buf.getvalue()); sys.stdout.flush()
+    elif a.impl == "reference":
         with quiet_stdout():
             import io
             buf = io.StringIO()
