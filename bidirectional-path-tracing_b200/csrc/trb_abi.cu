@@ -56,6 +56,7 @@ struct trb_context {
     // scene
     bool has_scene = false;
     bool built_on_device = false;   // the acceleration structure and the triangle records came from kernels/bvh_build.cuh
+    int trace_blocks_per_sm = TRB_TRACE_MINBLOCKS;   // persistent traversal grid = SMs x this ($TRB_TRACE_GRID_BLOCKS at trb_create: experiments with room left for other kernels)
     bool force_binary = false;      // TRB_TRAVERSAL=binary at trb_create: every ray on the reference's binary tree (A/B measurements, tests of k_trace_coop)
     trb::FlatScene flat;
     DevBuf<trb::DevNode> d_nodes;      // the reference's binary tree (degenerate rays, k_pt_check)
@@ -133,8 +134,6 @@ inline int grid_for(size_t n, int sm_count) {
 }
 inline int grid_exact(size_t n) { return int(std::max<size_t>(1, (n + TRB_BLOCK - 1) / TRB_BLOCK)); }
 
-// persistent traversal grid: one wave of resident warps per SM (64 registers/thread -> 8 blocks of 128 per SM)
-inline int trace_grid(int sm_count) { return sm_count * TRB_TRACE_MINBLOCKS; }
 
 // `ctr`: the launch's own TRACE_CTR_WORDS counters (ray-queue cursor, deferred count, cursor of the deferred launch), zeroed by the
 // caller on the stream.  k_trace_wide traces every ray but those with a zero / non-finite direction component, which it appends to
@@ -150,7 +149,7 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = ctr;
     a.defer_q = c->defer_q[0].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
-    const int grid = trace_grid(c->prop.multiProcessorCount);
+    const int grid = c->prop.multiProcessorCount * c->trace_blocks_per_sm;
     if (c->force_binary) { k_trace_coop<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a); return; }
     k_trace_wide<false><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
     a.q = c->defer_q[0].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu)); a.fetch = ctr + 2;
@@ -169,7 +168,7 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     a.rays = rays; a.q = nullptr; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = ctr;
     a.defer_q = c->defer_q[which].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
-    const int grid = trace_grid(c->prop.multiProcessorCount);
+    const int grid = c->prop.multiProcessorCount * c->trace_blocks_per_sm;
     if (c->force_binary) { k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a); return; }
     k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, stream>>>(a);
     a.q = c->defer_q[which].p; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu)); a.fetch = ctr + 2;
@@ -249,6 +248,7 @@ int trb_create(int device, trb_context** out) {
         return TRB_ERR_NO_DEVICE;
     }
     if (const char* e = std::getenv("TRB_TRAVERSAL")) c->force_binary = std::string(e) == "binary";
+    if (const char* e = std::getenv("TRB_TRACE_GRID_BLOCKS")) { const int v = std::atoi(e); if (v >= 1 && v <= TRB_TRACE_MINBLOCKS) c->trace_blocks_per_sm = v; }
     *out = c;
     return TRB_OK;
 }
@@ -1519,7 +1519,7 @@ extern "C" int trb_trace_any_device_noalloc(trb_context* c, const trb_ray* d_ray
     a.occ_out = d_out; a.pend = nullptr; a.accum = nullptr; a.fetch = ctr;
     a.defer_q = defer_q; a.defer_n = ctr + 1; a.defer_cap = uint32_t(TRB_NOALLOC_MAX_RAYS);
     a.visit = nullptr; a.visit_exh = nullptr;
-    const int grid = trace_grid(c->prop.multiProcessorCount);
+    const int grid = c->prop.multiProcessorCount * c->trace_blocks_per_sm;
     k_trace_wide<true><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
     a.q = defer_q; a.n_ptr = ctr + 1; a.n_fixed = 0u; a.cap = uint32_t(TRB_NOALLOC_MAX_RAYS); a.fetch = ctr + 2;
     k_trace_coop<true><<<grid, TRB_TRACE_BLOCK, 0, c->stream>>>(a);
