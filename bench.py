@@ -518,6 +518,28 @@ def run_ours(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = samples_step * e2e_steps / float(te.item()) / 1e6
 
+    # ---- configs[3] in the multi-GPU line: the 4K film (3840 x 2160, 99.5 MB frame buffer) partitioned by sample index over the ranks, one NCCL
+    # reduce per step; a short pass (8 spp per GPU per step; the full 4096 spp are `--workload cbox4k --spp 512` on 8 GPUs) ----
+    c4 = None
+    if world > 1 and args.workload == "caustic" and not args.no_extras:
+        w4 = WORKLOADS["cbox4k"]
+        W4, H4, spp4 = w4["width"], w4["height"], 8
+        b4, e4 = par.sample_range(spp4 * world, rank, world)
+        d4 = trb.render_desc(width=W4, height=H4, spp=spp4 * world, rr_depth=w4["rr_depth"], spp_begin=b4, spp_end=e4, wave_samples=args.wave)
+        fb4 = torch.zeros(H4, W4, 3, device="cuda", dtype=torch.float32)
+        tot4 = 0.0
+        for it in range(3):   # one warm-up, two timed
+            flush.zero_(); barrier()
+            st4 = ctx.render_bdpt_device(d4, fb4.data_ptr())
+            ev0.record(); par.reduce_framebuffer(fb4, dst=0); ev1.record(); torch.cuda.synchronize()
+            if it:
+                tot4 += st4["ms_total"] + ev0.elapsed_time(ev1)
+        t4 = torch.tensor([tot4], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t4, op=dist.ReduceOp.MAX)
+        c4 = {"workload": w4["desc"], "value": W4 * H4 * spp4 * world * 2 / (float(t4.item()) * 1e-3) / 1e6, "unit": UNIT, "spp_per_gpu_per_step": spp4, "steps": 2, "warmup": 1,
+              "ms_per_step": float(t4.item()) / 2, "reduce_bytes": W4 * H4 * 3 * 4, "image_mean": float(fb4.mean().item()) if rank == 0 else None,
+              "timing": "device time of the render (CUDA events) + the NCCL reduce of the frame buffer, max over ranks"}
+        del fb4
     if rank == 0:
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                "ms_per_step": tot_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -564,6 +586,8 @@ def run_ours(args):
                     out["cpu_ceiling"] = cpu_port_all_cores(trb, wl, fw, fh)
             except Exception as e:  # noqa: BLE001
                 out["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "unavailable", "sample": str(e)}
+        if c4 is not None:
+            out["c4"] = c4
         if world > 1 and not args.no_extras:
             # the same frame through ONE process (trb_render_bdpt_multi: what the C++ API / CLI use for gpus = N), next to the torchrun value
             out["inproc_multi"] = inproc_subprocess(args, world)

@@ -152,6 +152,9 @@ __device__ __forceinline__ F8 ld8_2x4(const float* p) {
 #ifndef TRB_WIDE_LD256
 #define TRB_WIDE_LD256 1
 #endif
+#ifndef TRB_WIDE_PREFETCH
+#define TRB_WIDE_PREFETCH 0      // 1: prefetch the next node of the lane at the end of the node phase (measured: see profiles/r2_node_phase_experiments.md)
+#endif
 
 // The production traversal kernel: persistent warps, lane refill, per-warp triangle queue (trace_coop.cuh) over the 4-wide tree.
 // Per node visit a lane loads 4 x 32 B, tests four boxes in straight-line code and
@@ -333,6 +336,10 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                 if (stop) sp = 0;
                 cur = nref >= 0 ? nref : pop();
             }
+#if TRB_WIDE_PREFETCH
+            // the node this lane visits next is known now, a triangle phase and perhaps a refill away: one line, certain to be used
+            if (cur >= 0 && cur != NONE) asm volatile("prefetch.global.L1 [%0];" :: "l"(a.wnodes + 8 * size_t(cur)));
+#endif
         }
         __syncwarp();
         // ---- triangle phases: full warps of queued tests; drain when no lane is traversing or the queue is filling up ----
