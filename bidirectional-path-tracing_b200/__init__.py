@@ -100,7 +100,7 @@ class Stats(C.Structure):
                 ("rays_any", C.c_uint64), ("launches", C.c_uint64), ("node_visits", C.c_uint64),
                 ("tri_tests", C.c_uint64), ("node_visits_any", C.c_uint64), ("tri_tests_any", C.c_uint64),
                 ("retraces", C.c_uint64), ("retraces_any", C.c_uint64), ("rays_deferred", C.c_uint64), ("rays_deferred_any", C.c_uint64),
-                ("node_visits_bin", C.c_uint64), ("tri_tests_bin", C.c_uint64), ("node_visits_bin_any", C.c_uint64), ("tri_tests_bin_any", C.c_uint64)]
+                ("node_visits_bin", C.c_uint64), ("tri_tests_bin", C.c_uint64), ("node_visits_bin_any", C.c_uint64), ("tri_tests_bin_any", C.c_uint64), ("wave_samples", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {k: getattr(self, k) for k, _ in self._fields_}

@@ -101,6 +101,7 @@ struct trb_context {
     std::vector<cudaEvent_t> dep_a, dep_b;       // untimed dependency events between the two streams
     bool timing = false;
     uint64_t launches = 0;
+    uint64_t wave_used = 0;      // samples per wavefront of the last render call
 
     int fail(int code, const std::string& m) { err = m; return code; }
     int cuda_fail(cudaError_t e, const char* what) {
@@ -183,6 +184,23 @@ inline int max_depth_of(const trb_render_desc& d) {
     return d.max_depth > 0 ? d.max_depth : std::max(TRB_RR_DEFAULT_MAX_DEPTH, d.rr_depth);
 }
 inline int max_vertices_of(const trb_render_desc& d) { return std::max(max_depth_of(d) - 1, 0); }
+
+// Samples per wavefront when the caller leaves it to the library (trb_render_desc.wave_samples == 0).  Bigger waves amortise the tails of
+// the persistent kernels and - on scenes larger than the L2 - put more rays in flight per node (measured, B200, profiles/r2u_wave.log:
+// 10 M triangles 75.2 / 79.3 / 81.5 Msamples/s at 2^22 / 2^23 / 2^24; caustic 117.0 / 117.8 / 118.2).  Memory is what a 180 GB part has:
+// the largest power of two <= 2^24 whose wave buffers (bytes per slot below: what ensure_wave allocates) fit in a quarter of the
+// device memory that is free now (buffers the context already holds count as free), never below 2^20.
+int64_t default_wave_samples(trb_context* c, int K) {
+    const size_t kk = size_t(std::max(K, 1));
+    const size_t per_slot = 228 + 68 * kk + 100 * (kk + 1) + (c->sc.has_tex ? 16 * kk + 16 : 0);
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return int64_t(1) << 22;
+    const size_t held = (c->lv.bytes() + c->sray.bytes() + c->sray2.bytes() + c->spend.bytes() + c->spend2.bytes() + c->ray.bytes() + c->cam_ray.bytes());
+    const size_t budget = (free_b + held) / 4;
+    int shift = 24;
+    while (shift > 20 && (per_slot << shift) > budget) --shift;
+    return int64_t(1) << shift;
+}
 
 int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     size_t kk = size_t(std::max(K, 1));
@@ -708,7 +726,7 @@ void collect_stats(trb_context* c, trb_stats* st, uint64_t samples) {
     cudaStreamSynchronize(c->stream);
     st->samples = samples; st->rays_closest = h[0]; st->rays_any = h[1]; st->node_visits = h[2]; st->tri_tests = h[3]; st->node_visits_any = h[4]; st->tri_tests_any = h[5]; st->retraces = h[6]; st->retraces_any = h[7];
     st->node_visits_bin = h[8]; st->tri_tests_bin = h[9]; st->node_visits_bin_any = h[10]; st->tri_tests_bin_any = h[11]; st->rays_deferred = h[12]; st->rays_deferred_any = h[13];
-    st->launches = c->launches;
+    st->launches = c->launches; st->wave_samples = c->wave_used;
     double ms[LK_N] = {0, 0, 0};
     // kernel time summed per kind on each stream; the two streams overlap, so the kinds can add up to more than ms_total
     for (size_t i = 1; i < c->n_events; ++i) {
@@ -736,12 +754,13 @@ int render_impl(trb_context* c, const trb_render_desc* d, int accumulate, float*
     if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
     const int spp_count = spp_end - spp_begin;
     const int K = std::max(max_vertices_of(*d), 1);
-    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << (rr_enabled(*d) ? 21 : 22));
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : default_wave_samples(c, K);
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");  // (slot << 6 | vertex) pair words
     rc = ensure_wave(c, size_t(P), K);
     if (rc) return rc;
+    c->wave_used = uint64_t(P);
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -879,6 +898,7 @@ int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_de
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     rc = ensure_wave(c, size_t(P), pt.is_explicit ? pt.cap : 1, /*shadow=*/false);
     if (rc) return rc;
+    c->wave_used = uint64_t(P);
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;
@@ -967,6 +987,7 @@ int render_direct_impl(trb_context* c, const trb_render_desc* d, const trb_direc
     if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");
     rc = ensure_wave(c, size_t(P), 1, /*shadow=*/false);
     if (rc) return rc;
+    c->wave_used = uint64_t(P);
     trb::CameraDev cam;
     trb::make_camera(*d, cam);
     c->timing = stats != nullptr; c->n_events = 0; c->n_events2 = 0; c->launches = 0;

@@ -110,7 +110,7 @@ typedef struct trb_render_desc {
     int32_t spp_end;   /* one past the last; 0 means spp                                                */
     uint32_t seed;     /* key of the counter-based RNG; streams are keyed by (seed, pixel, sample, dim) */
     uint32_t flags;    /* TRB_FLAG_*                                                                    */
-    int64_t wave_samples; /* samples per wavefront launch; 0 = library default                          */
+    int64_t wave_samples; /* samples per wavefront launch; 0 = library default: up to 2^24, sized to a quarter of the free device memory */
     int32_t max_depth; /* TRB_FLAG_RUSSIAN_ROULETTE only: hard cap on the walk depth (the reference has none,
                           bdpt.h:66-67); 0 = TRB_RR_DEFAULT_MAX_DEPTH; rr_depth <= max_depth <= 64            */
     int32_t reserved;
@@ -186,6 +186,7 @@ typedef struct trb_stats {
     uint64_t tri_tests_bin;
     uint64_t node_visits_bin_any;
     uint64_t tri_tests_bin_any;
+    uint64_t wave_samples;       /* samples per wavefront this call used (trb_render_desc.wave_samples, or the library's choice) */
 } trb_stats;
 
 /* BSDF query in the local shading frame (SurfaceInteraction::{wo,wi}, core.h:173-180) */
