@@ -81,12 +81,14 @@ struct WaveParams {
     HitT* hit0;           // P   primary hit (eye walk depth 1 reuses it: bdpt.h:70 re-traces the same ray)
     float4* st_t;         // P   throughput.xyz, vcm
     float4* st_v;         // P   vc, flags(bits), rng_ctr(bits), unused
-    LightVertex* lv;      // K * P, vertex j of slot i at [j*P + i]
+    LightVertex* lv;      // K * P.  BDPT: vertex j of slot i at [i*K + j] (slot-major: the <= K pairs that connect one eye vertex read one
+                          // contiguous <= 64 K-byte run; depth-major put them P * 64 B = 1 GB apart at 2^24-sample waves).  The path tracer keeps its
+                          // vertex stack depth-major ([d*P + i]: one kernel works on one depth of every slot)
     int32_t* nlv;         // P
     int32_t* q_in;        // P   live slots entering this bounce
     int32_t* q_out;       // P   live slots leaving it
     EyeVertex* ev;        // P   eye vertex of the current bounce (connecting slots only)
-    float4* lv_tex;       // K * P, textured scenes only: (triangle position bits, u, v, -) of the stored vertex, for BitmapTexture3f::eval
+    float4* lv_tex;       // K * P (indexed like lv), textured scenes only: (triangle position bits, u, v, -) of the stored vertex, for BitmapTexture3f::eval
     float4* ev_tex;       // P
     int32_t* q_conn;      // P*K (slot << 6 | light vertex) pairs to connect this bounce, dense (path tracer: a P-slot queue)
     uint32_t* counters;   // [0]=q_out count, [1]=shadow count, [2]=closest rays traced, [3]=any rays traced

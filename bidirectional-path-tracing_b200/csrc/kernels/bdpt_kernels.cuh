@@ -287,8 +287,8 @@ __global__ void TRB_LB_BOUNDS k_light_bounce(const __grid_constant__ WaveParams 
                 lv.nx = s.n.x; lv.ny = s.n.y; lv.nz = s.n.z; lv.vc = vc;
                 lv.wox = s.wo.x; lv.woy = s.wo.y; lv.woz = s.wo.z; lv.mat = s.mat;
                 lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.rr = rr;
-                p.lv[size_t(j) * p.P + slot] = lv;
-                if (p.sc.has_tex) p.lv_tex[size_t(j) * p.P + slot] = tex_record(p.hit[slot]);
+                p.lv[size_t(slot) * p.K + j] = lv;   // slot-major: the pairs of one eye vertex read one contiguous run (bdpt_common.cuh)
+                if (p.sc.has_tex) p.lv_tex[size_t(slot) * p.K + j] = tex_record(p.hit[slot]);
                 p.nlv[slot] = j + 1;
             }
             if (rr_continue(p, depth + 1, rr, rng)) {
@@ -495,7 +495,7 @@ __global__ void TRB_CV_BOUNDS k_connect_vertices(const __grid_constant__ WavePar
 
                 const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
                 float4 ea = ep[0], eb = ep[1], ec = ep[2], ed = ep[3];
-                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(j) * p.P + slot);
+                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(slot) * p.K + j);
                 float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
                 target = __float_as_uint(ed.w);
                 V3 epnt = mk(ea.x, ea.y, ea.z), lpnt = mk(a.x, a.y, a.z);
@@ -510,7 +510,7 @@ __global__ void TRB_CV_BOUNDS k_connect_vertices(const __grid_constant__ WavePar
                 float cosL = l_wi.z, cosE = e_wi.z;
                 if (!(cosL <= 0.f || cosE <= 0.f)) {
                     Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
-                    if (TEX && lm.tex) { const float4 t = p.lv_tex[size_t(j) * p.P + slot]; apply_tex(p.sc, lm, __float_as_int(t.x), t.y, t.z); }
+                    if (TEX && lm.tex) { const float4 t = p.lv_tex[size_t(slot) * p.K + j]; apply_tex(p.sc, lm, __float_as_int(t.x), t.y, t.z); }
                     const int emat = __float_as_int(ec.w);
                     const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
                     Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
