@@ -75,6 +75,7 @@ def path_desc(is_explicit=True, max_depth=-1, rr_prob=0.95, emitter_samples=1, b
 
 TRB_PT_DEFAULT_DEPTH_CAP = 64
 TRB_NOALLOC_MAX_RAYS = 1 << 20  # include/trb.h
+TRB_UPLOAD_WIDE_COLLAPSE = 0x100
 
 
 class DirectDesc(C.Structure):
@@ -394,10 +395,12 @@ class Context:
             raise TrbError(rc, self._L.trb_last_error(self._h).decode())
         return rc
 
-    def upload(self, scene: HostScene, build: str = "auto") -> None:
-        """trb_scene_upload_ex: build = "auto" | "host" | "device" - where BVH::build and the triangle gather run (same result)"""
+    def upload(self, scene: HostScene, build: str = "auto", wide: str = "sah") -> None:
+        """trb_scene_upload_ex: build = "auto" | "host" | "device" - where BVH::build and the triangle gather run (same result);
+        wide = "sah" (the SAH upper tree over the reference's leaves, the default) | "collapse" (TRB_UPLOAD_WIDE_COLLAPSE)"""
         d = scene.desc()
-        self._chk(self._L.trb_scene_upload_ex(self._h, C.byref(d), C.c_uint32({"auto": 0, "host": 1, "device": 2}[build])))
+        flags = {"auto": 0, "host": 1, "device": 2}[build] | {"sah": 0, "collapse": TRB_UPLOAD_WIDE_COLLAPSE}[wide]
+        self._chk(self._L.trb_scene_upload_ex(self._h, C.byref(d), C.c_uint32(flags)))
         self.scene = scene
 
     def built_on_device(self) -> bool:

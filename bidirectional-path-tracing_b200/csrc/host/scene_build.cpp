@@ -8,7 +8,10 @@
 // partition; what changes is the node layout (children boxes in the parent, 64 B, float4 loads) and the
 // traversal (ordered, pruned, stack in registers/shared memory).
 #include <algorithm>
+#include <array>
 #include <atomic>
+#include <chrono>
+#include <cstdio>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -392,6 +395,139 @@ void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& 
     }
 }
 
+// ---- the SAH upper tree over the reference's leaves (tr_host.h: build_sah_wide) ------------------------------------------------------
+namespace {
+struct SahBin { float mn[3], mx[3]; uint32_t n; };
+inline void bin_clear(SahBin& b) { b.n = 0; for (int k = 0; k < 3; ++k) { b.mn[k] = 3.4e38f; b.mx[k] = -3.4e38f; } }
+inline void bin_add(SahBin& b, const LeafBox& l) { ++b.n; for (int k = 0; k < 3; ++k) { b.mn[k] = std::min(b.mn[k], l.bmin[k]); b.mx[k] = std::max(b.mx[k], l.bmax[k]); } }
+inline void bin_merge(SahBin& b, const SahBin& o) { b.n += o.n; for (int k = 0; k < 3; ++k) { b.mn[k] = std::min(b.mn[k], o.mn[k]); b.mx[k] = std::max(b.mx[k], o.mx[k]); } }
+constexpr int SAH_BINS = 16;
+inline int sah_bin_of(const LeafBox& l, int ax, float cmn, float ext) {
+    const float c = 0.5f * (l.bmin[ax] + l.bmax[ax]);
+    return std::min(SAH_BINS - 1, int((c - cmn) / ext * float(SAH_BINS)));
+}
+}  // namespace
+
+void build_sah_wide(const LeafBox* L, size_t n, std::vector<DevNode4>& out, int32_t& depth) {
+    out.clear(); depth = 0;
+    const auto t_begin = std::chrono::steady_clock::now();
+    if (n < 2) return;   // a single leaf: the root reference is the leaf itself
+    std::vector<uint32_t> idx(n);
+    for (size_t i = 0; i < n; ++i) idx[i] = uint32_t(i);
+    const unsigned T = build_threads();
+    struct Todo { uint32_t lo, hi; int32_t parent; bool is_right; };
+    // bins of one range over one slice of it, all three axes at once
+    auto bin_slice = [&](uint32_t lo, uint32_t hi, const float cmn[3], const float ext[3], SahBin (*bins)[SAH_BINS]) {
+        for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < SAH_BINS; ++b) bin_clear(bins[ax][b]);
+        for (uint32_t i = lo; i < hi; ++i) {
+            const LeafBox& l = L[idx[i]];
+            for (int ax = 0; ax < 3; ++ax) if (ext[ax] > 0.f) bin_add(bins[ax][sah_bin_of(l, ax, cmn[ax], ext[ax])], l);
+        }
+    };
+    // one node: bounds, best split (ties: first axis, first bin), stable partition; `wide` = work on the range with all threads
+    auto step = [&](const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack, bool wide) {
+        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
+        RefTree::Node node;
+        node.left = -1; node.right = -1; node.start = L[idx[lo]].start; node.count = L[idx[lo]].count;
+        float cmn[3], cmx[3];
+        for (int k = 0; k < 3; ++k) { node.bmin[k] = 3.4e38f; node.bmax[k] = -3.4e38f; cmn[k] = 3.4e38f; cmx[k] = -3.4e38f; }
+        for (uint32_t i = lo; i < hi; ++i) {
+            const LeafBox& l = L[idx[i]];
+            for (int k = 0; k < 3; ++k) {
+                node.bmin[k] = std::min(node.bmin[k], l.bmin[k]); node.bmax[k] = std::max(node.bmax[k], l.bmax[k]);
+                const float c = 0.5f * (l.bmin[k] + l.bmax[k]);
+                cmn[k] = std::min(cmn[k], c); cmx[k] = std::max(cmx[k], c);
+            }
+        }
+        const int32_t me = int32_t(nodes.size());
+        nodes.push_back(node);
+        if (td.parent >= 0) { if (td.is_right) nodes[td.parent].right = me; else nodes[td.parent].left = me; }
+        if (cnt == 1) return;
+        const float ext[3] = {cmx[0] - cmn[0], cmx[1] - cmn[1], cmx[2] - cmn[2]};
+        SahBin bins[3][SAH_BINS];
+        if (wide && T > 1 && cnt >= (1u << 16)) {   // min / max / count: the merge does not depend on the slicing
+            std::vector<std::array<std::array<SahBin, SAH_BINS>, 3>> part(T);
+            std::vector<std::thread> th;
+            for (unsigned t = 0; t < T; ++t)
+                th.emplace_back([&, t]() { bin_slice(lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), cmn, ext, reinterpret_cast<SahBin(*)[SAH_BINS]>(part[t].data())); });
+            for (auto& x : th) x.join();
+            for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < SAH_BINS; ++b) { bin_clear(bins[ax][b]); for (unsigned t = 0; t < T; ++t) bin_merge(bins[ax][b], part[t][ax][b]); }
+        } else {
+            bin_slice(lo, hi, cmn, ext, bins);
+        }
+        float best = 3.4e38f; int baxis = -1, bsplit = -1;
+        for (int ax = 0; ax < 3; ++ax) {
+            if (!(ext[ax] > 0.f)) continue;
+            float ra[SAH_BINS]; uint32_t rn[SAH_BINS];
+            SahBin acc; bin_clear(acc);
+            for (int b = SAH_BINS - 1; b >= 0; --b) { bin_merge(acc, bins[ax][b]); rn[b] = acc.n; ra[b] = acc.n ? wide_box_area(acc.mn, acc.mx) : 0.f; }
+            bin_clear(acc);
+            for (int b = 0; b + 1 < SAH_BINS; ++b) {
+                bin_merge(acc, bins[ax][b]);
+                if (!acc.n || !rn[b + 1]) continue;
+                const float cost = wide_box_area(acc.mn, acc.mx) * float(acc.n) + ra[b + 1] * float(rn[b + 1]);
+                if (cost < best) { best = cost; baxis = ax; bsplit = b; }
+            }
+        }
+        uint32_t mid = lo + cnt / 2;   // coincident centroids: split the list in the middle, order untouched
+        if (baxis >= 0) {
+            const float c0 = cmn[baxis], e0 = ext[baxis];
+            auto it = std::stable_partition(idx.begin() + lo, idx.begin() + hi, [&](uint32_t i) { return sah_bin_of(L[i], baxis, c0, e0) <= bsplit; });
+            const uint32_t m = uint32_t(it - idx.begin());
+            if (m > lo && m < hi) mid = m;
+        }
+        stack.push_back({mid, hi, me, true});
+        stack.push_back({lo, mid, me, false});
+    };
+    // top of the tree on the calling thread (wide steps), ranges below `defer_below` leaves as subtree tasks on all threads
+    const uint32_t defer_below = (T > 1 && n >= (size_t(1) << 15)) ? uint32_t(n / (size_t(T) * 8)) : 0u;
+    struct Task { Todo td; int32_t parent; bool is_right; std::vector<RefTree::Node> nodes; };
+    RefTree sah;
+    std::vector<Task> tasks;
+    {
+        std::vector<Todo> stack;
+        stack.push_back({0u, uint32_t(n), -1, false});
+        while (!stack.empty()) {
+            Todo td = stack.back(); stack.pop_back();
+            if (defer_below && td.hi - td.lo < defer_below && td.parent >= 0) {
+                Task t; t.td = {td.lo, td.hi, -1, false}; t.parent = td.parent; t.is_right = td.is_right;
+                tasks.push_back(std::move(t));
+                continue;
+            }
+            step(td, sah.nodes, stack, true);
+        }
+    }
+    if (!tasks.empty()) {   // disjoint ranges of idx: no two tasks touch the same entries
+        std::atomic<size_t> next{0};
+        auto worker = [&]() {
+            std::vector<Todo> stack;
+            for (size_t i = next.fetch_add(1); i < tasks.size(); i = next.fetch_add(1)) {
+                Task& t = tasks[i];
+                t.nodes.reserve(2 * size_t(t.td.hi - t.td.lo));
+                stack.clear(); stack.push_back(t.td);
+                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(td, t.nodes, stack, false); }
+            }
+        };
+        std::vector<std::thread> th;
+        for (unsigned k = 1; k < T; ++k) th.emplace_back(worker);
+        worker();
+        for (auto& x : th) x.join();
+        for (Task& t : tasks) {   // stitch in task order (the order the top pass met them: deterministic)
+            const int32_t base = int32_t(sah.nodes.size());
+            for (RefTree::Node nd : t.nodes) { if (nd.left >= 0) { nd.left += base; nd.right += base; } sah.nodes.push_back(nd); }
+            RefTree::Node& par = sah.nodes[t.parent];
+            if (t.is_right) par.right = base; else par.left = base;
+            std::vector<RefTree::Node>().swap(t.nodes);
+        }
+    }
+    const auto t_tree = std::chrono::steady_clock::now();
+    build_wide_nodes(sah, out, depth);
+    if (std::getenv("TRB_BUILD_TIMING"))
+        std::fprintf(stderr, "[trb build] SAH upper tree: %zu leaves, %zu binary nodes in %.1f ms (%u threads, %zu subtree tasks), collapse to %zu wide nodes in %.1f ms\n", n,
+                     sah.nodes.size(), std::chrono::duration<double, std::milli>(t_tree - t_begin).count(), T, tasks.size(), out.size(),
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_tree).count());
+}
+
 bool flatten_scene(const trb_scene_desc& s, FlatScene& out, std::string& err) {
     return flatten_tables(s, out, err) && flatten_geometry(s, out, err);
 }
@@ -535,7 +671,13 @@ bool flatten_geometry(const trb_scene_desc& s, FlatScene& out, std::string& err)
         md = std::max(md, depth[i]);
     }
     out.max_depth = md;
-    build_wide_nodes(tree, out.wnodes, out.wide_depth);
+    {   // the upper tree the traversal walks: SAH over the reference's leaves (primitive order = the reference's pre-order)
+        std::vector<LeafBox> leaves;
+        for (const RefTree::Node& nd : tree.nodes)
+            if (nd.left < 0) { LeafBox l; for (int k = 0; k < 3; ++k) { l.bmin[k] = nd.bmin[k]; l.bmax[k] = nd.bmax[k]; } l.start = nd.start; l.count = nd.count; leaves.push_back(l); }
+        if (out.wide_collapse) build_wide_nodes(tree, out.wnodes, out.wide_depth);
+        else build_sah_wide(leaves.data(), leaves.size(), out.wnodes, out.wide_depth);
+    }
     out.n_nodes = out.nodes.size(); out.n_tris = out.tris.size(); out.n_tri_uv = out.tri_uv.size(); out.n_wnodes = out.wnodes.size();
     return true;
 }

@@ -229,6 +229,19 @@ __global__ void k_bb_emit_nodes(const BuildNode* __restrict__ nodes, int32_t tot
     out[nd.inner_pre] = d;
 }
 
+// the leaves of the finished tree in primitive order (a leaf's ordinal = its pre-order number minus the inner nodes before it): the
+// input of the SAH upper tree, which is built on the host cores (trb::build_sah_wide)
+__global__ void k_bb_emit_leaves(const BuildNode* __restrict__ nodes, int32_t total, trb::LeafBox* __restrict__ out) {
+    int32_t k = int32_t(blockIdx.x * blockDim.x + threadIdx.x);
+    if (k >= total) return;
+    const BuildNode& nd = nodes[k];
+    if (nd.left >= 0) return;
+    trb::LeafBox l;
+    for (int c = 0; c < 3; ++c) { l.bmin[c] = nd.bmin[c]; l.bmax[c] = nd.bmax[c]; }
+    l.start = nd.start; l.count = nd.end - nd.start;
+    out[nd.pre - nd.inner_pre] = l;
+}
+
 // ---- the 4-wide upper tree (tr_host.h: DevNode4), level by level: the device twin of trb::build_wide_nodes ----
 // children of every wide node of a level: start from the binary node's two children and open, while fewer than four, the inner
 // child of largest surface area (ties: the first); an opened child is replaced in place by its two children

@@ -452,9 +452,28 @@ int build_geometry_on_device(trb_context* c, const trb_scene_desc& s) {
     TRB_CUDA(c, cudaGetLastError());
     TRB_CUDA(c, cudaStreamSynchronize(c->stream));
     lap("numbering + emit");
-    // the 4-wide upper tree (k_wide_*: the device twin of trb::build_wide_nodes), one level per pass; scratch of the build is re-used
-    f.n_wnodes = 0; f.wide_depth = 0;
-    if (root.left >= 0) {
+    f.n_wnodes = 0; f.wide_depth = 0; f.wnodes.clear();
+    if (root.left >= 0 && !f.wide_collapse) {
+        // the SAH upper tree: the leaf list comes down (32 B per leaf), the tree is built on the host cores (trb::build_sah_wide - the same
+        // call the host build makes on the same list), the 128 B nodes go up.  f.wnodes stays on the host (staging for trb_scene_refresh).
+        const size_t n_leaves = size_t(root.sub_nodes - root.sub_inner);
+        DevBuf<trb::LeafBox> d_leaves;
+        struct LGuard { DevBuf<trb::LeafBox>& b; ~LGuard() { b.release(); } } lguard{d_leaves};
+        TRB_CUDA(c, d_leaves.alloc(n_leaves));
+        k_bb_emit_leaves<<<gK(total_nodes), B, 0, c->stream>>>(nodes.p, total_nodes, d_leaves.p);
+        std::vector<trb::LeafBox> leaves(n_leaves);
+        TRB_CUDA(c, cudaMemcpyAsync(leaves.data(), d_leaves.p, n_leaves * sizeof(trb::LeafBox), cudaMemcpyDeviceToHost, c->stream));
+        TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+        lap("leaf list to the host");
+        trb::build_sah_wide(leaves.data(), n_leaves, f.wnodes, f.wide_depth);
+        lap("SAH upper tree (host cores)");
+        f.n_wnodes = f.wnodes.size();
+        TRB_CUDA(c, c->d_wnodes.alloc(f.n_wnodes));
+        TRB_CUDA(c, cudaMemcpyAsync(c->d_wnodes.p, f.wnodes.data(), f.n_wnodes * sizeof(trb::DevNode4), cudaMemcpyHostToDevice, c->stream));
+        TRB_CUDA(c, cudaStreamSynchronize(c->stream));
+    } else if (root.left >= 0) {
+        // TRB_UPLOAD_WIDE_COLLAPSE: the collapse of the reference's own tree (k_wide_*: the device twin of trb::build_wide_nodes), one level
+        // per pass; scratch of the build is re-used
         DevBuf<trb::DevNode4> wtmp;
         struct WGuard { DevBuf<trb::DevNode4>& b; ~WGuard() { b.release(); } } wguard{wtmp};
         TRB_CUDA(c, wtmp.alloc(f.n_nodes));   // upper bound: every wide node takes at least one binary inner node
@@ -502,6 +521,9 @@ int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags)
     if (f.emitters.empty()) return c->fail(TRB_ERR_INVALID, "scene has no emitter (the reference divides by emitters.size())");
     if (s->n_tris == 0) return c->fail(TRB_ERR_INVALID, "empty scene");
     if (s->n_tris >= (size_t(1) << 27)) return c->fail(TRB_ERR_UNSUPPORTED, "more than 2^27 triangles");   // (owner lane << 27 | position) queue words
+    f.wide_collapse = (flags & TRB_UPLOAD_WIDE_COLLAPSE) != 0;
+    flags &= ~uint32_t(TRB_UPLOAD_WIDE_COLLAPSE);
+    if (flags > TRB_UPLOAD_DEVICE_BUILD) return c->fail(TRB_ERR_INVALID, "trb_scene_upload_ex: unknown flags");
     const bool on_device = flags == TRB_UPLOAD_DEVICE_BUILD || (flags == TRB_UPLOAD_AUTO && s->n_tris >= TRB_DEVICE_BUILD_MIN_TRIS);
     TRB_CUDA(c, c->d_mats.alloc(f.materials.size()));
     TRB_CUDA(c, c->d_emitters.alloc(f.emitters.size())); TRB_CUDA(c, c->d_etris.alloc(f.emitter_tris.size()));

@@ -18,11 +18,11 @@ def _same(a, b):
     return all(np.array_equal(a[k], b[k]) for k in a.dtype.names)
 
 
-def _compare(trb, scene, label):
+def _compare(trb, scene, label, wide="sah"):
     host, dev = trb.Context(0), trb.Context(0)
     try:
-        host.upload(scene, build="host")
-        dev.upload(scene, build="device")
+        host.upload(scene, build="host", wide=wide)
+        dev.upload(scene, build="device", wide=wide)
         assert dev.built_on_device() and not host.built_on_device()
         for which in ("nodes", "wnodes", "tris", "shade", "tri_uv"):
             a, b = host.download(which), dev.download(which)
@@ -48,6 +48,8 @@ def test_device_build_equals_host_build(trb, name):
 
 def test_device_build_at_size_and_edge_cases(trb, gold):
     import gen_tess_scene
+    # TRB_UPLOAD_WIDE_COLLAPSE: the upper tree as the collapse of the reference's tree, made on the device by k_wide_* / on the host by build_wide_nodes
+    _compare(trb, trb.HostScene.load_npz(GOLD / "scene_caustic.npz"), "caustic, collapsed upper tree", wide="collapse")
     _compare(trb, gen_tess_scene.make_scene(600_000, seed=3), "tess 600k")   # auto mode takes the device build from 65536 triangles on
     ctx = trb.Context(0)
     ctx.upload(gen_tess_scene.make_scene(100_000, seed=2))

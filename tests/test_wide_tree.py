@@ -70,3 +70,24 @@ def test_wide_tree_structure(trb, scene_name):
         used = ref[c] != empty
         assert (lo[c][used] >= lo[p_, s_]).all() and (hi[c][used] <= hi[p_, s_]).all()
     assert (ref[:, :2] != empty).all()                                       # at least two children per node
+
+
+def test_sah_upper_tree_is_deterministic_across_thread_counts(trb, monkeypatch):
+    """build_sah_wide (csrc/host/scene_build.cpp) on one host thread and on all of them gives the same nodes byte for byte (min / max /
+    count reductions and a stable partition: nothing depends on the slicing) - what lets a host-built and a device-built scene agree
+    record for record (tests/test_gpu_build.py) on boxes with different core counts."""
+    import ctypes as C
+    import check_leaf_claim
+    import gen_tess_scene
+    L = check_leaf_claim.lib()
+    scene = gen_tess_scene.make_scene(300_000, seed=4)     # large enough for the parallel top of the tree and the subtree tasks
+    d = scene.desc()
+    got = []
+    for threads in ("1", "3", "16"):
+        monkeypatch.setenv("TRB_BUILD_THREADS", threads)
+        n = C.c_size_t(0)
+        assert L.hc_wide_nodes(C.byref(d), None, C.byref(n)) == 0
+        w = np.zeros(n.value, trb.DEV_NODE4_DTYPE)
+        assert L.hc_wide_nodes(C.byref(d), w.ctypes.data_as(C.c_void_p), C.byref(n)) == 0
+        got.append(w.tobytes())
+    assert got[0] == got[1] == got[2] and len(got[0]) > 128 * 1000

@@ -124,3 +124,97 @@ extern "C" int hc_wide_nodes(const trb_scene_desc* s, void* out, size_t* n) {
     *n = fs.wnodes.size();
     return 0;
 }
+
+// ---- experiment: a binned-SAH upper tree over the reference's LEAVES (instead of the collapse of its midpoint tree) ----------------
+// Same leaves, same leaf boxes, same primitive order; only the inner nodes differ.  Returns the same outputs as hc_trace_wide so that the
+// hits can be compared and the node visits counted.  (tools/exp_sah_upper.py)
+#include <algorithm>
+#include <numeric>
+namespace {
+struct LeafRef { float bmin[3], bmax[3], cen[3]; uint32_t start, count; };
+float area3(const float* mn, const float* mx) { return trb::wide_box_area(mn, mx); }
+int32_t sah_build(std::vector<LeafRef>& L, size_t lo, size_t hi, trb::RefTree& out) {
+    trb::RefTree::Node nd;
+    for (int k = 0; k < 3; ++k) { nd.bmin[k] = 3.4e38f; nd.bmax[k] = -3.4e38f; }
+    float cmn[3] = {3.4e38f, 3.4e38f, 3.4e38f}, cmx[3] = {-3.4e38f, -3.4e38f, -3.4e38f};
+    for (size_t i = lo; i < hi; ++i)
+        for (int k = 0; k < 3; ++k) {
+            nd.bmin[k] = std::min(nd.bmin[k], L[i].bmin[k]); nd.bmax[k] = std::max(nd.bmax[k], L[i].bmax[k]);
+            cmn[k] = std::min(cmn[k], L[i].cen[k]); cmx[k] = std::max(cmx[k], L[i].cen[k]);
+        }
+    nd.left = nd.right = -1; nd.start = L[lo].start; nd.count = L[lo].count;
+    const int32_t me = int32_t(out.nodes.size());
+    out.nodes.push_back(nd);
+    if (hi - lo == 1) return me;
+    // binned SAH, 16 bins per axis
+    const int NB = 16;
+    float best = 3.4e38f; int baxis = -1, bsplit = -1;
+    for (int ax = 0; ax < 3; ++ax) {
+        const float ext = cmx[ax] - cmn[ax];
+        if (!(ext > 0.f)) continue;
+        struct Bin { float mn[3], mx[3]; int n; } bins[NB];
+        for (auto& b : bins) { b.n = 0; for (int k = 0; k < 3; ++k) { b.mn[k] = 3.4e38f; b.mx[k] = -3.4e38f; } }
+        for (size_t i = lo; i < hi; ++i) {
+            int b = std::min(NB - 1, int((L[i].cen[ax] - cmn[ax]) / ext * NB));
+            bins[b].n++;
+            for (int k = 0; k < 3; ++k) { bins[b].mn[k] = std::min(bins[b].mn[k], L[i].bmin[k]); bins[b].mx[k] = std::max(bins[b].mx[k], L[i].bmax[k]); }
+        }
+        float la[NB], ra[NB]; int ln[NB], rn[NB];
+        float mn[3] = {3.4e38f, 3.4e38f, 3.4e38f}, mx[3] = {-3.4e38f, -3.4e38f, -3.4e38f}; int n = 0;
+        for (int b = 0; b < NB; ++b) { n += bins[b].n; for (int k = 0; k < 3; ++k) { mn[k] = std::min(mn[k], bins[b].mn[k]); mx[k] = std::max(mx[k], bins[b].mx[k]); } la[b] = n ? area3(mn, mx) : 0.f; ln[b] = n; }
+        for (int k = 0; k < 3; ++k) { mn[k] = 3.4e38f; mx[k] = -3.4e38f; } n = 0;
+        for (int b = NB - 1; b >= 0; --b) { n += bins[b].n; for (int k = 0; k < 3; ++k) { mn[k] = std::min(mn[k], bins[b].mn[k]); mx[k] = std::max(mx[k], bins[b].mx[k]); } ra[b] = n ? area3(mn, mx) : 0.f; rn[b] = n; }
+        for (int b = 0; b + 1 < NB; ++b) {
+            if (!ln[b] || !rn[b + 1]) continue;
+            const float cost = la[b] * ln[b] + ra[b + 1] * rn[b + 1];
+            if (cost < best) { best = cost; baxis = ax; bsplit = b; }
+        }
+    }
+    size_t mid;
+    if (baxis < 0) mid = lo + (hi - lo) / 2;
+    else {
+        const float ext = cmx[baxis] - cmn[baxis];
+        auto it = std::partition(L.begin() + lo, L.begin() + hi, [&](const LeafRef& l) { return std::min(NB - 1, int((l.cen[baxis] - cmn[baxis]) / ext * NB)) <= bsplit; });
+        mid = size_t(it - L.begin());
+        if (mid == lo || mid == hi) mid = lo + (hi - lo) / 2;
+    }
+    const int32_t l = sah_build(L, lo, mid, out);
+    const int32_t r = sah_build(L, mid, hi, out);
+    out.nodes[me].left = l; out.nodes[me].right = r;
+    return me;
+}
+}  // namespace
+
+extern "C" int hc_trace_wide_sah(const trb_scene_desc* s, const float* rays8, long n, int any, float* tuv, int* tri_out, unsigned char* occ,
+                                 unsigned long long* counters) {
+    static trb::FlatScene fs; static std::vector<trb::DevNode4> wn; static const void* cached = nullptr;
+    std::string err;
+    if (cached != s->positions) {
+        if (!trb::flatten_scene(*s, fs, err)) { fprintf(stderr, "%s\n", err.c_str()); return -1; }
+        trb::RefTree ref;
+        if (!trb::build_ref_tree(*s, ref, err)) return -1;
+        std::vector<LeafRef> L;
+        for (const auto& nd : ref.nodes)
+            if (nd.left < 0) { LeafRef l; for (int k = 0; k < 3; ++k) { l.bmin[k] = nd.bmin[k]; l.bmax[k] = nd.bmax[k]; l.cen[k] = 0.5f * (nd.bmin[k] + nd.bmax[k]); } l.start = nd.start; l.count = nd.count; L.push_back(l); }
+        trb::RefTree sah;
+        sah_build(L, 0, L.size(), sah);
+        int32_t depth = 0;
+        trb::build_wide_nodes(sah, wn, depth);
+        counters[7] = (unsigned long long)depth;
+        cached = s->positions;
+    }
+    trbk::BvhView bv{reinterpret_cast<const trbk::F4*>(fs.nodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.root_ref};
+    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(wn.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), wn.empty() ? fs.root_ref : 0};
+    trbk::WideCounters c{0, 0, 0, 0};
+    unsigned long long nn = 0, nb = 0, nt = 0;
+    for (long i = 0; i < n; ++i) {
+        trbk::RayT r; memcpy(&r, rays8 + 8 * i, 32);
+        trbk::HitT h; bool oc = false;
+        c.nodes = c.boxes = c.tris = 0;
+        if (any) trbk::trace_ray_wide<true>(wv, bv, r, &h, &oc, &c); else trbk::trace_ray_wide<false>(wv, bv, r, &h, &oc, &c);
+        nn += c.nodes; nb += c.boxes; nt += c.tris;
+        if (any) occ[i] = oc; else { tuv[3 * i] = h.t; tuv[3 * i + 1] = h.u; tuv[3 * i + 2] = h.v; tri_out[i] = h.pos >= 0 ? fs.tris[h.pos].tri : -1; }
+    }
+    counters[0] = nn; counters[1] = nb; counters[2] = nt; counters[3] = c.max_sp; counters[5] = wn.size();
+    return 0;
+}
