@@ -341,6 +341,7 @@ void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& 
         out.resize(base + level.size());
         // children of every node of the level (disjoint outputs), then the numbering of the inner ones
         std::vector<int32_t> slots(4 * level.size(), -1);
+        std::vector<uint8_t> n_inner_of(level.size(), 0);
         parallel_for(level.size(), 1 << 14, [&](size_t i0, size_t i1) {
             for (size_t i = i0; i < i1; ++i) {
                 int32_t* sl = &slots[4 * i];
@@ -361,15 +362,14 @@ void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& 
                     sl[best] = c.left; sl[best + 1] = c.right;
                     ++n;
                 }
+                uint8_t ci = 0;
+                for (int k = 0; k < n; ++k) if (tree.nodes[sl[k]].left >= 0) ++ci;
+                n_inner_of[i] = ci;
             }
         });
         next.clear();
         std::vector<uint32_t> first_inner(level.size() + 1, 0);
-        for (size_t i = 0; i < level.size(); ++i) {
-            uint32_t c = 0;
-            for (int k = 0; k < 4; ++k) if (slots[4 * i + k] >= 0 && tree.nodes[slots[4 * i + k]].left >= 0) ++c;
-            first_inner[i + 1] = first_inner[i] + c;
-        }
+        for (size_t i = 0; i < level.size(); ++i) first_inner[i + 1] = first_inner[i] + n_inner_of[i];
         next.resize(first_inner[level.size()]);
         const size_t next_base = base + level.size();
         parallel_for(level.size(), 1 << 14, [&](size_t i0, size_t i1) {
@@ -402,67 +402,88 @@ inline void bin_clear(SahBin& b) { b.n = 0; for (int k = 0; k < 3; ++k) { b.mn[k
 inline void bin_add(SahBin& b, const LeafBox& l) { ++b.n; for (int k = 0; k < 3; ++k) { b.mn[k] = std::min(b.mn[k], l.bmin[k]); b.mx[k] = std::max(b.mx[k], l.bmax[k]); } }
 inline void bin_merge(SahBin& b, const SahBin& o) { b.n += o.n; for (int k = 0; k < 3; ++k) { b.mn[k] = std::min(b.mn[k], o.mn[k]); b.mx[k] = std::max(b.mx[k], o.mx[k]); } }
 constexpr int SAH_BINS = 16;
-inline int sah_bin_of(const LeafBox& l, int ax, float cmn, float ext) {
+// nb = bins of this node: min(16, leaves in the range) - most nodes of the tree hold 2-4 leaves, and clearing and sweeping 48 bins for
+// each of them was most of the build time
+inline int sah_bin_of(const LeafBox& l, int ax, float cmn, float ext, int nb) {
     const float c = 0.5f * (l.bmin[ax] + l.bmax[ax]);
-    return std::min(SAH_BINS - 1, int((c - cmn) / ext * float(SAH_BINS)));
+    return std::min(nb - 1, int((c - cmn) / ext * float(nb)));
 }
 }  // namespace
 
-void build_sah_wide(const LeafBox* L, size_t n, std::vector<DevNode4>& out, int32_t& depth) {
+void build_sah_wide(const LeafBox* L_in, size_t n, std::vector<DevNode4>& out, int32_t& depth) {
     out.clear(); depth = 0;
     const auto t_begin = std::chrono::steady_clock::now();
     if (n < 2) return;   // a single leaf: the root reference is the leaf itself
-    std::vector<uint32_t> idx(n);
-    for (size_t i = 0; i < n; ++i) idx[i] = uint32_t(i);
+    // The leaf records themselves are partitioned (32 B moves), not an index: every range is contiguous memory, and a subtree task
+    // works on a private copy that fits the caches.
+    std::vector<LeafBox> all(L_in, L_in + n);
+    std::vector<LeafBox> scratch;   // the parallel partition of the top-level ranges
     const unsigned T = build_threads();
     struct Todo { uint32_t lo, hi; int32_t parent; bool is_right; };
-    // bins of one range over one slice of it, all three axes at once
-    auto bin_slice = [&](uint32_t lo, uint32_t hi, const float cmn[3], const float ext[3], SahBin (*bins)[SAH_BINS]) {
-        for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < SAH_BINS; ++b) bin_clear(bins[ax][b]);
-        for (uint32_t i = lo; i < hi; ++i) {
-            const LeafBox& l = L[idx[i]];
-            for (int ax = 0; ax < 3; ++ax) if (ext[ax] > 0.f) bin_add(bins[ax][sah_bin_of(l, ax, cmn[ax], ext[ax])], l);
-        }
-    };
-    // one node: bounds, best split (ties: first axis, first bin), stable partition; `wide` = work on the range with all threads
-    auto step = [&](const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack, bool wide) {
-        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
-        RefTree::Node node;
-        node.left = -1; node.right = -1; node.start = L[idx[lo]].start; node.count = L[idx[lo]].count;
-        float cmn[3], cmx[3];
-        for (int k = 0; k < 3; ++k) { node.bmin[k] = 3.4e38f; node.bmax[k] = -3.4e38f; cmn[k] = 3.4e38f; cmx[k] = -3.4e38f; }
-        for (uint32_t i = lo; i < hi; ++i) {
-            const LeafBox& l = L[idx[i]];
+    struct Bounds { float bmin[3], bmax[3], cmn[3], cmx[3]; };
+    auto bounds_clear = [](Bounds& b) { for (int k = 0; k < 3; ++k) { b.bmin[k] = 3.4e38f; b.bmax[k] = -3.4e38f; b.cmn[k] = 3.4e38f; b.cmx[k] = -3.4e38f; } };
+    auto bounds_slice = [](const LeafBox* L, uint32_t lo, uint32_t hi, Bounds& b) {
+        for (uint32_t i = lo; i < hi; ++i)
             for (int k = 0; k < 3; ++k) {
-                node.bmin[k] = std::min(node.bmin[k], l.bmin[k]); node.bmax[k] = std::max(node.bmax[k], l.bmax[k]);
-                const float c = 0.5f * (l.bmin[k] + l.bmax[k]);
-                cmn[k] = std::min(cmn[k], c); cmx[k] = std::max(cmx[k], c);
+                b.bmin[k] = std::min(b.bmin[k], L[i].bmin[k]); b.bmax[k] = std::max(b.bmax[k], L[i].bmax[k]);
+                const float c = 0.5f * (L[i].bmin[k] + L[i].bmax[k]);
+                b.cmn[k] = std::min(b.cmn[k], c); b.cmx[k] = std::max(b.cmx[k], c);
             }
+    };
+    auto bin_slice = [](const LeafBox* L, uint32_t lo, uint32_t hi, const float cmn[3], const float ext[3], int nbins, SahBin (*bins)[SAH_BINS]) {
+        for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < nbins; ++b) bin_clear(bins[ax][b]);
+        for (uint32_t i = lo; i < hi; ++i)
+            for (int ax = 0; ax < 3; ++ax) if (ext[ax] > 0.f) bin_add(bins[ax][sah_bin_of(L[i], ax, cmn[ax], ext[ax], nbins)], L[i]);
+    };
+    // one node over L[lo, hi): bounds, best split (ties: first axis, first bin), stable partition; `wide` = all threads on this range
+    // (min / max / count reductions: the result does not depend on the slicing)
+    auto step = [&](LeafBox* L, const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack, bool wide) {
+        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
+        const bool par = wide && T > 1 && cnt >= (1u << 16);
+        Bounds nb; bounds_clear(nb);
+        if (par) {
+            std::vector<Bounds> part(T);
+            std::vector<std::thread> th;
+            for (unsigned t = 0; t < T; ++t)
+                th.emplace_back([&, t]() { bounds_clear(part[t]); bounds_slice(L, lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), part[t]); });
+            for (auto& x : th) x.join();
+            for (unsigned t = 0; t < T; ++t)
+                for (int k = 0; k < 3; ++k) {
+                    nb.bmin[k] = std::min(nb.bmin[k], part[t].bmin[k]); nb.bmax[k] = std::max(nb.bmax[k], part[t].bmax[k]);
+                    nb.cmn[k] = std::min(nb.cmn[k], part[t].cmn[k]); nb.cmx[k] = std::max(nb.cmx[k], part[t].cmx[k]);
+                }
+        } else {
+            bounds_slice(L, lo, hi, nb);
         }
+        RefTree::Node node;
+        node.left = -1; node.right = -1; node.start = L[lo].start; node.count = L[lo].count;
+        for (int k = 0; k < 3; ++k) { node.bmin[k] = nb.bmin[k]; node.bmax[k] = nb.bmax[k]; }
         const int32_t me = int32_t(nodes.size());
         nodes.push_back(node);
         if (td.parent >= 0) { if (td.is_right) nodes[td.parent].right = me; else nodes[td.parent].left = me; }
         if (cnt == 1) return;
-        const float ext[3] = {cmx[0] - cmn[0], cmx[1] - cmn[1], cmx[2] - cmn[2]};
+        const float* cmn = nb.cmn;
+        const float ext[3] = {nb.cmx[0] - nb.cmn[0], nb.cmx[1] - nb.cmn[1], nb.cmx[2] - nb.cmn[2]};
         SahBin bins[3][SAH_BINS];
-        if (wide && T > 1 && cnt >= (1u << 16)) {   // min / max / count: the merge does not depend on the slicing
+        const int nbins = int(std::min<uint32_t>(SAH_BINS, cnt));
+        if (par) {
             std::vector<std::array<std::array<SahBin, SAH_BINS>, 3>> part(T);
             std::vector<std::thread> th;
             for (unsigned t = 0; t < T; ++t)
-                th.emplace_back([&, t]() { bin_slice(lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), cmn, ext, reinterpret_cast<SahBin(*)[SAH_BINS]>(part[t].data())); });
+                th.emplace_back([&, t]() { bin_slice(L, lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), cmn, ext, nbins, reinterpret_cast<SahBin(*)[SAH_BINS]>(part[t].data())); });
             for (auto& x : th) x.join();
-            for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < SAH_BINS; ++b) { bin_clear(bins[ax][b]); for (unsigned t = 0; t < T; ++t) bin_merge(bins[ax][b], part[t][ax][b]); }
+            for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < nbins; ++b) { bin_clear(bins[ax][b]); for (unsigned t = 0; t < T; ++t) bin_merge(bins[ax][b], part[t][ax][b]); }
         } else {
-            bin_slice(lo, hi, cmn, ext, bins);
+            bin_slice(L, lo, hi, cmn, ext, nbins, bins);
         }
         float best = 3.4e38f; int baxis = -1, bsplit = -1;
         for (int ax = 0; ax < 3; ++ax) {
             if (!(ext[ax] > 0.f)) continue;
             float ra[SAH_BINS]; uint32_t rn[SAH_BINS];
             SahBin acc; bin_clear(acc);
-            for (int b = SAH_BINS - 1; b >= 0; --b) { bin_merge(acc, bins[ax][b]); rn[b] = acc.n; ra[b] = acc.n ? wide_box_area(acc.mn, acc.mx) : 0.f; }
+            for (int b = nbins - 1; b >= 0; --b) { bin_merge(acc, bins[ax][b]); rn[b] = acc.n; ra[b] = acc.n ? wide_box_area(acc.mn, acc.mx) : 0.f; }
             bin_clear(acc);
-            for (int b = 0; b + 1 < SAH_BINS; ++b) {
+            for (int b = 0; b + 1 < nbins; ++b) {
                 bin_merge(acc, bins[ax][b]);
                 if (!acc.n || !rn[b + 1]) continue;
                 const float cost = wide_box_area(acc.mn, acc.mx) * float(acc.n) + ra[b + 1] * float(rn[b + 1]);
@@ -472,8 +493,45 @@ void build_sah_wide(const LeafBox* L, size_t n, std::vector<DevNode4>& out, int3
         uint32_t mid = lo + cnt / 2;   // coincident centroids: split the list in the middle, order untouched
         if (baxis >= 0) {
             const float c0 = cmn[baxis], e0 = ext[baxis];
-            auto it = std::stable_partition(idx.begin() + lo, idx.begin() + hi, [&](uint32_t i) { return sah_bin_of(L[i], baxis, c0, e0) <= bsplit; });
-            const uint32_t m = uint32_t(it - idx.begin());
+            auto goes_left = [&](const LeafBox& l) { return sah_bin_of(l, baxis, c0, e0, nbins) <= bsplit; };
+            uint32_t m;
+            if (cnt <= 64) {   // small range: stable partition through a stack buffer (std::stable_partition allocates one per call)
+                LeafBox right[64]; uint32_t nr = 0, w = lo;
+                for (uint32_t i = lo; i < hi; ++i) { if (goes_left(L[i])) L[w++] = L[i]; else right[nr++] = L[i]; }
+                for (uint32_t i = 0; i < nr; ++i) L[w + i] = right[i];
+                m = w;
+            } else if (par) {   // stable, on all threads: count per slice, prefix, scatter into a scratch array, copy back
+                std::vector<uint32_t> nl(T + 1, 0);
+                auto slice = [&](unsigned t, uint32_t* a, uint32_t* b) { *a = lo + uint32_t(uint64_t(cnt) * t / T); *b = lo + uint32_t(uint64_t(cnt) * (t + 1) / T); };
+                {
+                    std::vector<std::thread> th;
+                    for (unsigned t = 0; t < T; ++t)
+                        th.emplace_back([&, t]() { uint32_t a, b, c = 0; slice(t, &a, &b); for (uint32_t i = a; i < b; ++i) c += goes_left(L[i]) ? 1u : 0u; nl[t + 1] = c; });
+                    for (auto& x : th) x.join();
+                }
+                for (unsigned t = 0; t < T; ++t) nl[t + 1] += nl[t];
+                const uint32_t n_left = nl[T];
+                scratch.resize(cnt);
+                {
+                    std::vector<std::thread> th;
+                    for (unsigned t = 0; t < T; ++t)
+                        th.emplace_back([&, t]() {
+                            uint32_t a, b; slice(t, &a, &b);
+                            uint32_t wl = nl[t], wr = n_left + ((a - lo) - nl[t]);
+                            for (uint32_t i = a; i < b; ++i) { if (goes_left(L[i])) scratch[wl++] = L[i]; else scratch[wr++] = L[i]; }
+                        });
+                    for (auto& x : th) x.join();
+                }
+                {
+                    std::vector<std::thread> th;
+                    for (unsigned t = 0; t < T; ++t)
+                        th.emplace_back([&, t]() { uint32_t a, b; slice(t, &a, &b); std::memcpy(L + a, scratch.data() + (a - lo), size_t(b - a) * sizeof(LeafBox)); });
+                    for (auto& x : th) x.join();
+                }
+                m = lo + n_left;
+            } else {
+                m = uint32_t(std::stable_partition(L + lo, L + hi, goes_left) - L);
+            }
             if (m > lo && m < hi) mid = m;
         }
         stack.push_back({mid, hi, me, true});
@@ -494,37 +552,57 @@ void build_sah_wide(const LeafBox* L, size_t n, std::vector<DevNode4>& out, int3
                 tasks.push_back(std::move(t));
                 continue;
             }
-            step(td, sah.nodes, stack, true);
+            step(all.data(), td, sah.nodes, stack, true);
         }
     }
-    if (!tasks.empty()) {   // disjoint ranges of idx: no two tasks touch the same entries
+    const auto t_top = std::chrono::steady_clock::now();
+    auto t_tasks = t_top;
+    if (!tasks.empty()) {   // disjoint ranges: every task copies its leaves and builds its subtree from the copy
         std::atomic<size_t> next{0};
         auto worker = [&]() {
             std::vector<Todo> stack;
+            std::vector<LeafBox> local;
             for (size_t i = next.fetch_add(1); i < tasks.size(); i = next.fetch_add(1)) {
                 Task& t = tasks[i];
-                t.nodes.reserve(2 * size_t(t.td.hi - t.td.lo));
-                stack.clear(); stack.push_back(t.td);
-                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(td, t.nodes, stack, false); }
+                local.assign(all.begin() + t.td.lo, all.begin() + t.td.hi);
+                t.nodes.reserve(2 * local.size());
+                stack.clear(); stack.push_back({0u, uint32_t(local.size()), -1, false});
+                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(local.data(), td, t.nodes, stack, false); }
             }
         };
         std::vector<std::thread> th;
         for (unsigned k = 1; k < T; ++k) th.emplace_back(worker);
         worker();
         for (auto& x : th) x.join();
-        for (Task& t : tasks) {   // stitch in task order (the order the top pass met them: deterministic)
-            const int32_t base = int32_t(sah.nodes.size());
-            for (RefTree::Node nd : t.nodes) { if (nd.left >= 0) { nd.left += base; nd.right += base; } sah.nodes.push_back(nd); }
-            RefTree::Node& par = sah.nodes[t.parent];
-            if (t.is_right) par.right = base; else par.left = base;
-            std::vector<RefTree::Node>().swap(t.nodes);
+        t_tasks = std::chrono::steady_clock::now();
+        // stitch in task order (the order the top pass met them: deterministic): bases by a prefix sum, copies on all threads
+        std::vector<size_t> base(tasks.size() + 1, sah.nodes.size());
+        for (size_t k = 0; k < tasks.size(); ++k) base[k + 1] = base[k] + tasks[k].nodes.size();
+        sah.nodes.resize(base[tasks.size()]);
+        std::atomic<size_t> nxt{0};
+        auto copier = [&]() {
+            for (size_t k = nxt.fetch_add(1); k < tasks.size(); k = nxt.fetch_add(1)) {
+                const int32_t b = int32_t(base[k]);
+                RefTree::Node* dst = sah.nodes.data() + base[k];
+                for (RefTree::Node nd : tasks[k].nodes) { if (nd.left >= 0) { nd.left += b; nd.right += b; } *dst++ = nd; }
+                std::vector<RefTree::Node>().swap(tasks[k].nodes);
+            }
+        };
+        std::vector<std::thread> th2;
+        for (unsigned k = 1; k < T; ++k) th2.emplace_back(copier);
+        copier();
+        for (auto& x : th2) x.join();
+        for (size_t k = 0; k < tasks.size(); ++k) {
+            RefTree::Node& par = sah.nodes[tasks[k].parent];
+            if (tasks[k].is_right) par.right = int32_t(base[k]); else par.left = int32_t(base[k]);
         }
     }
     const auto t_tree = std::chrono::steady_clock::now();
     build_wide_nodes(sah, out, depth);
     if (std::getenv("TRB_BUILD_TIMING"))
-        std::fprintf(stderr, "[trb build] SAH upper tree: %zu leaves, %zu binary nodes in %.1f ms (%u threads, %zu subtree tasks), collapse to %zu wide nodes in %.1f ms\n", n,
-                     sah.nodes.size(), std::chrono::duration<double, std::milli>(t_tree - t_begin).count(), T, tasks.size(), out.size(),
+        std::fprintf(stderr, "[trb build] SAH upper tree: %zu leaves, %zu binary nodes in %.1f ms (top %.1f, %zu subtree tasks on %u threads %.1f, stitch %.1f), collapse to %zu wide nodes in %.1f ms\n", n,
+                     sah.nodes.size(), std::chrono::duration<double, std::milli>(t_tree - t_begin).count(), std::chrono::duration<double, std::milli>(t_top - t_begin).count(), tasks.size(), T,
+                     std::chrono::duration<double, std::milli>(t_tasks - t_top).count(), std::chrono::duration<double, std::milli>(t_tree - t_tasks).count(), out.size(),
                      std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_tree).count());
 }
 
