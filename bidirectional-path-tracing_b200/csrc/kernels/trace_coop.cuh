@@ -22,7 +22,7 @@
 #include "bdpt_common.cuh"
 
 #ifndef TRB_FETCH_T
-#define TRB_FETCH_T 8        // refill when this many lanes are idle
+#define TRB_FETCH_T 16       // refill when this many lanes are idle (B200, SAH upper tree: 4 / 8 / 12 / 16 / 20 / 24 / 28 -> caustic 129.9 / 135.9 / 139.5 / 141.8 / 140.9 / 137.9 / 122.1 Msamples/s, profiles/r2_node_phase_experiments.md)
 #endif
 #ifndef TRB_TRACE_BLOCK
 #define TRB_TRACE_BLOCK 128
@@ -76,6 +76,7 @@ struct CoopWarp {
     uint32_t flags[32];            // bit 0: ill-conditioned candidate met, bit 1: occluded
     uint32_t tail;                 // queue write cursor (monotone; entries live at index & (Q-1))
     uint32_t pad[3];
+    float2 uv[32];                 // k_trace_wide, closest: (u, v) of the current winner, written by the lane whose test won
     uint32_t queue[TRB_COOP_Q];    // (owner lane << 27) | triangle position
 };
 

@@ -152,6 +152,9 @@ __device__ __forceinline__ F8 ld8_2x4(const float* p) {
 #ifndef TRB_WIDE_LD256
 #define TRB_WIDE_LD256 1
 #endif
+#ifndef TRB_WIDE_UV
+#define TRB_WIDE_UV 1            // 1: the winning test leaves (u, v) in shared memory; 0: the winner is re-tested when the ray completes
+#endif
 #ifndef TRB_WIDE_PREFETCH
 #define TRB_WIDE_PREFETCH 0      // 1: prefetch the next node of the lane at the end of the node phase (measured: see profiles/r2_node_phase_experiments.md)
 #endif
@@ -251,12 +254,18 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                         const unsigned long long b = sh.best[lane];
                         HitT h; h.t = r.max_t; h.u = 0.f; h.v = 0.f; h.pos = -1;
                         if (uint32_t(b >> 32) != __float_as_uint(r.max_t)) {
+#if TRB_WIDE_UV
+                            // the winner's (u, v) were left in shared memory by the lane whose test won (triangle phase)
+                            const float2 uv = sh.uv[lane];
+                            h.t = __uint_as_float(uint32_t(b >> 32)); h.u = uv.x; h.v = uv.y; h.pos = int32_t(uint32_t(b));
+#else
                             // the winner's (t, u, v): the same arithmetic on the same inputs as when it won
                             const uint32_t pos = uint32_t(b);
                             const F4* tp = a.bvh.tris + 3 * size_t(pos);
                             F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
                             bool ill2 = false; float t, u, v;
                             if (tri_test(q0, q1, q2, r, &t, &u, &v, &ill2)) { h.t = t; h.u = u; h.v = v; h.pos = int32_t(pos); }
+#endif
                         }
                         a.hits[slot] = h;
                     }
@@ -356,8 +365,9 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             o.ox = __shfl_sync(FULL, r.ox, owner); o.oy = __shfl_sync(FULL, r.oy, owner); o.oz = __shfl_sync(FULL, r.oz, owner);
             o.dx = __shfl_sync(FULL, r.dx, owner); o.dy = __shfl_sync(FULL, r.dy, owner); o.dz = __shfl_sync(FULL, r.dz, owner);
             o.max_t = __shfl_sync(FULL, r.max_t, owner); o.min_t = 0.f;
-            float t = 0.f, u, v;
+            float t = 0.f, u = 0.f, v = 0.f;
             bool ill = false, thit = false;
+            unsigned long long mine = 0ull;
             if (act) {
                 TRB_CHECK(pos < a.n_tris);
                 const F4* tp = a.bvh.tris + 3 * size_t(pos);
@@ -373,7 +383,8 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                     if (t <= o.max_t) { atomicOr(&sh.flags[owner], 2u); ill = false; }
                 } else {
                     // (t, list position) lexicographic minimum == strict '<' in list order for any visiting order
-                    atomicMin(&sh.best[owner], ((unsigned long long)__float_as_uint(t) << 32) | pos);
+                    mine = ((unsigned long long)__float_as_uint(t) << 32) | pos;
+                    atomicMin(&sh.best[owner], mine);
                 }
             }
             if (ill) atomicOr(&sh.flags[owner], 1u);
@@ -389,7 +400,15 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             }
             head += nb_; count -= nb_;
             __syncwarp();
+#if TRB_WIDE_UV
+            // every merge of this phase is in: the one lane whose packed value is the owner's minimum now leaves its (u, v) there
+            // (list positions are unique, so at most one lane matches; a later phase can only replace it after its own __syncwarp)
+            if (!ANY && thit && sh.best[owner] == mine) sh.uv[owner] = make_float2(u, v);
+#endif
         }
+#if TRB_WIDE_UV
+        if (!ANY) __syncwarp();   // the (u, v) of the last phase are in place before a completed ray reads its own
+#endif
     }
 #ifdef TRB_COUNTERS
     if (a.visit) {

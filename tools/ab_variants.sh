@@ -2,8 +2,8 @@
 TAG=$1; shift
 cd $GRAFT_REPO_ROOT
 for v in "$@"; do
-  for w in caustic tess; do
-    spp=16; [ $w = tess ] && spp=4
+  for w in ${WORKLOADS:-caustic tess}; do
+    spp=16; [ $w = tess ] && spp=4; [ $w = hardlight ] && spp=8
     lib=bidirectional-path-tracing_b200/libtrb_$v.so; mode=wide
     [ $v = default ] && lib=bidirectional-path-tracing_b200/libtrb.so
     [ $v = binary ] && lib=bidirectional-path-tracing_b200/libtrb.so && mode=binary
