@@ -152,9 +152,6 @@ __device__ __forceinline__ F8 ld8_2x4(const float* p) {
 #ifndef TRB_WIDE_LD256
 #define TRB_WIDE_LD256 1
 #endif
-#ifndef TRB_WIDE_UV
-#define TRB_WIDE_UV 1            // 1: the winning test leaves (u, v) in shared memory; 0: the winner is re-tested when the ray completes
-#endif
 #ifndef TRB_WIDE_PREFETCH
 #define TRB_WIDE_PREFETCH 0      // 1: prefetch the next node of the lane at the end of the node phase (measured: see profiles/r2_node_phase_experiments.md)
 #endif
@@ -230,10 +227,10 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
         const bool idle = cur == NONE && (!have || sh.outst[lane] == 0);
         const unsigned idle_mask = __ballot_sync(FULL, idle);
         if (idle_mask == FULL || (__popc(idle_mask) >= TRB_FETCH_T && more)) {
-            bool want = idle;
+            bool want = idle, fin = false, occ = false;
             if (idle && have) {
                 const uint32_t fl = sh.flags[lane];
-                const bool occ = (fl & 2u) != 0;
+                occ = (fl & 2u) != 0;
                 if ((fl & 1u) && !exh && !(ANY && occ)) {
                     exh = true;   // ill-conditioned candidate met: visit every leaf the reference reaches (no distance pruning)
                     start_ray();
@@ -243,39 +240,40 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
 #endif
                 } else {
                     have = false;
-                    if (ANY) {
-                        if (a.occ_out) a.occ_out[slot] = occ ? 1 : 0;
-                        if (a.pend && !occ) {
-                            Pending pd = a.pend[slot];
-                            float* dst = a.accum + size_t(pd.target) * 3;
-                            atomicAdd(dst, pd.r); atomicAdd(dst + 1, pd.g); atomicAdd(dst + 2, pd.b);
-                        }
-                    } else {
-                        const unsigned long long b = sh.best[lane];
-                        HitT h; h.t = r.max_t; h.u = 0.f; h.v = 0.f; h.pos = -1;
-                        if (uint32_t(b >> 32) != __float_as_uint(r.max_t)) {
-#if TRB_WIDE_UV
-                            // the winner's (u, v) were left in shared memory by the lane whose test won (triangle phase)
-                            const float2 uv = sh.uv[lane];
-                            h.t = __uint_as_float(uint32_t(b >> 32)); h.u = uv.x; h.v = uv.y; h.pos = int32_t(uint32_t(b));
-#else
-                            // the winner's (t, u, v): the same arithmetic on the same inputs as when it won
-                            const uint32_t pos = uint32_t(b);
-                            const F4* tp = a.bvh.tris + 3 * size_t(pos);
-                            F4 q0 = ld4(tp), q1 = ld4(tp + 1), q2 = ld4(tp + 2);
-                            bool ill2 = false; float t, u, v;
-                            if (tri_test(q0, q1, q2, r, &t, &u, &v, &ill2)) { h.t = t; h.u = u; h.v = v; h.pos = int32_t(pos); }
-#endif
-                        }
-                        a.hits[slot] = h;
+                    fin = true;
+                }
+            }
+            // A refill's round trips - the finished shadow ray's pending contribution, the queue cursor - are started before anything
+            // waits on either (the compiler keeps a load behind an atomic it cannot prove unrelated); the next ray's load follows.
+            Pending pd; pd.r = pd.g = pd.b = 0.f; pd.target = 0u;
+            const bool resolve = ANY && fin && !occ && a.pend != nullptr;
+            if (resolve) pd = a.pend[slot];
+            unsigned wm = 0u; uint32_t cnt = 0u, base = 0u;
+            if (more) {
+                wm = __ballot_sync(FULL, want);
+                cnt = uint32_t(__popc(wm));
+                if (lane == 0 && cnt) base = atomicAdd(a.fetch, cnt);
+            }
+            if (fin) {
+                if (ANY) {
+                    if (a.occ_out) a.occ_out[slot] = occ ? 1 : 0;
+                    if (resolve) {
+                        float* dst = a.accum + size_t(pd.target) * 3;
+                        atomicAdd(dst, pd.r); atomicAdd(dst + 1, pd.g); atomicAdd(dst + 2, pd.b);
                     }
+                } else {
+                    const unsigned long long b = sh.best[lane];
+                    HitT h; h.t = r.max_t; h.u = 0.f; h.v = 0.f; h.pos = -1;
+                    if (uint32_t(b >> 32) != __float_as_uint(r.max_t)) {
+                        // the winner's (u, v) were left in shared memory by the lane whose test won (triangle phase): the values of
+                        // the very test that won, so bit-identical to the reference's
+                        const float2 uv = sh.uv[lane];
+                        h.t = __uint_as_float(uint32_t(b >> 32)); h.u = uv.x; h.v = uv.y; h.pos = int32_t(uint32_t(b));
+                    }
+                    a.hits[slot] = h;
                 }
             }
             if (more) {
-                const unsigned wm = __ballot_sync(FULL, want);
-                const uint32_t cnt = uint32_t(__popc(wm));
-                uint32_t base = 0;
-                if (lane == 0 && cnt) base = atomicAdd(a.fetch, cnt);
                 base = __shfl_sync(FULL, base, 0);
                 const uint32_t idx = base + uint32_t(__popc(wm & lt));
                 if (want && idx < n) {
@@ -400,15 +398,11 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
             }
             head += nb_; count -= nb_;
             __syncwarp();
-#if TRB_WIDE_UV
             // every merge of this phase is in: the one lane whose packed value is the owner's minimum now leaves its (u, v) there
             // (list positions are unique, so at most one lane matches; a later phase can only replace it after its own __syncwarp)
             if (!ANY && thit && sh.best[owner] == mine) sh.uv[owner] = make_float2(u, v);
-#endif
         }
-#if TRB_WIDE_UV
         if (!ANY) __syncwarp();   // the (u, v) of the last phase are in place before a completed ray reads its own
-#endif
     }
 #ifdef TRB_COUNTERS
     if (a.visit) {
