@@ -76,11 +76,19 @@ struct WaveParams {
     int32_t* splat_pix;   // parity mode: pixel index per (path, light depth-1)
     // wave buffers
     RayT* cam_ray;        // P
-    RayT* ray;            // P   current walk ray
-    HitT* hit;            // P   current walk hit
+    RayT* ray;            // P   current walk ray (path tracer / direct integrator: per slot)
+    HitT* hit;            // P   current walk hit (BDPT: entry k belongs to queue entry k, see below; the others: per slot)
     HitT* hit0;           // P   primary hit (eye walk depth 1 reuses it: bdpt.h:70 re-traces the same ray)
-    float4* st_t;         // P   throughput.xyz, vcm
-    float4* st_v;         // P   vc, flags(bits), rng_ctr(bits), unused
+    float4* st_t;         // P   throughput.xyz, vcm (path tracer / direct integrator: per slot)
+    float4* st_v;         // P   vc, flags(bits), rng_ctr(bits), unused - per slot; BDPT: the value a walk ENDED with (the eye walk
+                          //     and the draw counts of the parity entry point pick it up there)
+    // BDPT: the state of a live walk travels in QUEUE ORDER - entry k of (ray_in, hit, stt_in, sv_in) belongs to slot q_in[k], and a
+    // bounce writes the walks it continues to entry idx of the *_out arrays, idx being their place in q_out.  Every read and write
+    // of a bounce kernel is then coalesced whatever slots are still alive, and the closest-hit traversal reads its rays and writes
+    // its hits by queue position, with no index list in between.
+    const RayT* ray_in;  RayT* ray_out;      // P each
+    const float4* stt_in; float4* stt_out;   // P each: throughput.xyz, vcm
+    const float4* sv_in;  float4* sv_out;    // P each: vc, flags, rng_ctr, unused
     LightVertex* lv;      // K * P.  BDPT: vertex j of slot i at [i*K + j] (slot-major: the <= K pairs that connect one eye vertex read one
                           // contiguous <= 64 K-byte run; depth-major put them P * 64 B = 1 GB apart at 2^24-sample waves).  The path tracer keeps its
                           // vertex stack depth-major ([d*P + i]: one kernel works on one depth of every slot)

@@ -144,12 +144,14 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool in = i < p.P;
     bool go = false;
+    RayT lr_out; float4 st_out = make_float4(0.f, 0.f, 0.f, 0.f), sv = st_out;
+    lr_out.ox = lr_out.oy = lr_out.oz = lr_out.dx = lr_out.dy = lr_out.dz = lr_out.min_t = lr_out.max_t = 0.f;
     if (in) {
         RayT cr = p.cam_ray[i];
         HitT h = p.hit[i];
         p.hit0[i] = h;
         p.nlv[i] = 0;
-        float4 sv = p.st_v[i];
+        sv = p.st_v[i];
         uint32_t ctr = __float_as_uint(sv.z);
         uint32_t flags = 0;
         if (hit_valid(h, cr)) flags |= 2u;   // bdpt.h:225: no subpaths at all when the primary ray misses
@@ -173,8 +175,8 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
                     go = true;
                     RayT lr; lr.ox = es.pos.x; lr.oy = es.pos.y; lr.oz = es.pos.z; lr.dx = wd.x; lr.dy = wd.y; lr.dz = wd.z;
                     lr.min_t = 1e-8f; lr.max_t = FLT_MAX;
-                    p.ray[i] = lr;
-                    p.st_t[i] = make_float4(T.x, T.y, T.z, vcm);
+                    lr_out = lr;
+                    st_out = make_float4(T.x, T.y, T.z, vcm);
                     sv.x = vc;
                 }
             }
@@ -184,18 +186,14 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
         p.st_v[i] = sv;
     }
     uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
-    if (go) p.q_out[idx] = i;
+    if (go) { p.q_out[idx] = i; p.ray_out[idx] = lr_out; p.stt_out[idx] = st_out; p.sv_out[idx] = sv; }
 }
 
-// ---- material sorting inside a block --------------------------------------------------------------------------
-// The reference dispatches BSDFs through virtual calls; here the bounce kernels switch on the material class per lane.
-// Before doing so, the TRB_SORT_BLOCK slots of a block are counting-sorted in shared memory by the key the traversal
-// left with the hit triangle (DevTri.flags: class | emissive << 3; 15 = no valid hit), so that most warps of the block
-// see ONE class (ncu before: 16 active threads per instruction in k_light_bounce, 3 on the Phong-lobe powf).
+// ---- launch shapes of the bounce kernels ---------------------------------------------------------------------
 #ifndef TRB_SORT_BLOCK
 #define TRB_SORT_BLOCK 256
 #endif
-// Launch bounds of the bounce / connect kernels.  The bounce kernels wait on scattered per-slot state (ncu r1o: long scoreboard,
+// Launch bounds of the bounce / connect kernels.  The bounce kernels wait on the triangle and material their hit names (ncu r1o: long scoreboard,
 // 23-35 % occupancy), so resident warps count for more than a few spilled registers: capping k_eye_bounce for 3 blocks per SM
 // (92 -> 80 registers) and k_light_bounce for 4 (78 -> 64) takes the logic share of a caustic step from 35.2 to 31.6 ms.  Tighter
 // caps (eye 64, light 48, connect 72 / 64) and no cap at all (94 / 86 / 94) are slower (profiles/r1o_ncu_logic_summary.md).
@@ -212,54 +210,23 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
 #else
 #define TRB_CV_BOUNDS __launch_bounds__(TRB_BLOCK)
 #endif
-#ifndef TRB_MATSORT
-#define TRB_MATSORT 0
-#endif
-__device__ __forceinline__ int block_sort_slot(const WaveParams& p, uint32_t k, uint32_t n, bool* in_out) {
-#if !TRB_MATSORT
-    *in_out = k < n;
-    return k < n ? p.q_in[k] : 0;
-#endif
-    __shared__ int s_cnt[16];
-    __shared__ int s_base[16];
-    __shared__ int s_slot[TRB_SORT_BLOCK];
-    const int tid = threadIdx.x;
-    if (tid < 16) s_cnt[tid] = 0;
-    __syncthreads();
-    const bool in = k < n;
-    int slot = 0, key = 15, rank = 0;
-    if (in) {
-        slot = p.q_in[k];
-        const int32_t pos = p.hit[slot].pos;
-        if (pos >= 0) key = __ldg(reinterpret_cast<const int32_t*>(p.sc.tris + 3 * size_t(pos)) + 11) & 15;  // DevTri.flags
-        rank = atomicAdd(&s_cnt[key], 1);
-    }
-    __syncthreads();
-    if (tid == 0) { int acc = 0; for (int c = 0; c < 16; ++c) { s_base[c] = acc; acc += s_cnt[c]; } }
-    __syncthreads();
-    if (in) s_slot[s_base[key] + rank] = slot;
-    __syncthreads();
-    const int total = s_base[15] + s_cnt[15];
-    *in_out = tid < total;
-    return tid < total ? s_slot[tid] : 0;
-}
-
 // ---- one light bounce (body of the loop at bdpt.h:188-216) -------------------------------------------------
 __global__ void TRB_LB_BOUNDS k_light_bounce(const __grid_constant__ WaveParams p, int depth, const uint32_t* __restrict__ n_in) {
     uint32_t n = *n_in;
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x * blockDim.x >= n) return;  // block-uniform
-    bool in;
-    int slot = block_sort_slot(p, k, n, &in);
+    const bool in = k < n;
+    int slot = 0;
     bool alive = false, connect = false, go = false;
     Surf s; Mat m; V3 T = mk(0.f); float vcm = 0.f, vc = 0.f;
     float4 sv = make_float4(0.f, 0.f, 0.f, 0.f);
     RayT r;
     if (in) {
-        r = p.ray[slot];
-        HitT h = p.hit[slot];
-        sv = p.st_v[slot];
-        const float4 st = p.st_t[slot];  // read with the other per-slot records, not behind the triangle and material fetches
+        slot = p.q_in[k];        // the walk's records are read by queue position: four coalesced streams
+        r = p.ray_in[k];
+        HitT h = p.hit[k];
+        sv = p.sv_in[k];
+        const float4 st = p.stt_in[k];
         if (hit_valid(h, r)) {
             alive = true;
             s = make_surf(p.sc, h, r);
@@ -288,29 +255,31 @@ __global__ void TRB_LB_BOUNDS k_light_bounce(const __grid_constant__ WaveParams 
                 lv.wox = s.wo.x; lv.woy = s.wo.y; lv.woz = s.wo.z; lv.mat = s.mat;
                 lv.tx = T.x; lv.ty = T.y; lv.tz = T.z; lv.rr = rr;
                 p.lv[size_t(slot) * p.K + j] = lv;   // slot-major: the pairs of one eye vertex read one contiguous run (bdpt_common.cuh)
-                if (p.sc.has_tex) p.lv_tex[size_t(slot) * p.K + j] = tex_record(p.hit[slot]);
+                if (p.sc.has_tex) p.lv_tex[size_t(slot) * p.K + j] = tex_record(p.hit[k]);
                 p.nlv[slot] = j + 1;
             }
             if (rr_continue(p, depth + 1, rr, rng)) {
                 go = true;
-                p.ray[slot] = nr;
-                p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
+                r = nr;
+                T = Tn; vcm = vcmn;
                 sv.x = vcn;
             }
         }
         sv.z = __uint_as_float(rng.ctr);
-        p.st_v[slot] = sv;
     }
     uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
-    if (go) p.q_out[idx] = slot;
+    if (go) { p.q_out[idx] = slot; p.ray_out[idx] = r; p.stt_out[idx] = make_float4(T.x, T.y, T.z, vcm); p.sv_out[idx] = sv; }
+    else if (in) p.st_v[slot] = sv;   // the walk ends here: what the eye walk (flags, draw count) finds under the slot
 }
 
 // ---- eye subpath start (bdpt.h:46-66) ------------------------------------------------------------------------
 __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ WaveParams p) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     bool go = false;
+    RayT r_out; float4 st_out = make_float4(0.f, 0.f, 0.f, 0.f), sv = st_out;
+    r_out.ox = r_out.oy = r_out.oz = r_out.dx = r_out.dy = r_out.dz = r_out.min_t = r_out.max_t = 0.f;
     if (i < p.P) {
-        float4 sv = p.st_v[i];
+        sv = p.st_v[i];
         uint32_t flags = __float_as_uint(sv.y);
         if (flags & 2u) {
             RayT cr = p.cam_ray[i];
@@ -327,9 +296,8 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ 
             }
             if (cont) {
                 go = true;
-                p.ray[i] = cr;
-                p.hit[i] = p.hit0[i];
-                p.st_t[i] = make_float4(1.f, 1.f, 1.f, vcm);
+                r_out = cr;
+                st_out = make_float4(1.f, 1.f, 1.f, vcm);
                 sv.x = 0.f;
                 sv.y = __uint_as_float(flags | SLOT_PURE_SPECULAR);
             }
@@ -337,7 +305,7 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_eye_init(const __grid_constant__ 
         }
     }
     uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
-    if (go) p.q_out[idx] = i;
+    if (go) { p.q_out[idx] = i; p.ray_out[idx] = r_out; p.hit[idx] = p.hit0[i]; p.stt_out[idx] = st_out; p.sv_out[idx] = sv; }
 }
 
 // ---- one eye bounce (body of the loop at bdpt.h:68-154) --------------------------------------------------------
@@ -345,19 +313,22 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
     uint32_t n = *n_in;
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (blockIdx.x * blockDim.x >= n) return;  // block-uniform
-    bool in;
-    int slot = block_sort_slot(p, k, n, &in);
+    const bool in = k < n;
+    int slot = 0;
     bool alive = false, connect = false, go = false;
     Surf s; Mat m; V3 T = mk(0.f); float vcm = 0.f, vc = 0.f;
     float4 sv = make_float4(0.f, 0.f, 0.f, 0.f);
+    RayT nr_out;
+    nr_out.ox = nr_out.oy = nr_out.oz = nr_out.dx = nr_out.dy = nr_out.dz = nr_out.min_t = nr_out.max_t = 0.f;
     uint32_t pixel = 0, sample = 0, li_target = 0;
     const float li_scale = p.parity ? 1.f : (1.f / p.spp);  // renderer.cpp:201: averageRadiance * (1.f / spp)
     Rng rng; rng.inj = nullptr; rng.key = 0; rng.key2 = 0; rng.ctr = 0; rng.lim = 0;
     if (in) {
-        RayT r = p.ray[slot];
-        HitT h = p.hit[slot];
-        sv = p.st_v[slot];
-        const float4 st = p.st_t[slot];  // read with the other per-slot records, not behind the triangle and material fetches
+        slot = p.q_in[k];        // the walk's records are read by queue position: four coalesced streams
+        RayT r = p.ray_in[k];
+        HitT h = p.hit[k];
+        sv = p.sv_in[k];
+        const float4 st = p.stt_in[k];
         slot_ids(p, slot, &pixel, &sample);
         li_target = p.parity ? uint32_t(slot) * uint32_t(p.K + 1) : pixel;
         rng = make_rng(p, slot, pixel, sample, __float_as_uint(sv.z));
@@ -453,7 +424,7 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
             e.wox = s.wo.x; e.woy = s.wo.y; e.woz = s.wo.z; e.mat = s.mat | (rr < 1.f ? EV_RR_HALF : 0);
             e.tx = T.x; e.ty = T.y; e.tz = T.z; e.target = li_target;
             p.ev[slot] = e;
-            if (p.sc.has_tex) p.ev_tex[slot] = tex_record(p.hit[slot]);
+            if (p.sc.has_tex) p.ev_tex[slot] = tex_record(p.hit[k]);
         }
     }
     if (in) {
@@ -463,17 +434,17 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
             if (continue_walk(s, m, rng, rr, &Tn, &vcn, &vcmn, &nr, &wi)) {
                 if (rr_continue(p, depth + 1, rr, rng)) {
                     go = true;
-                    p.ray[slot] = nr;
-                    p.st_t[slot] = make_float4(Tn.x, Tn.y, Tn.z, vcmn);
+                    nr_out = nr;
+                    T = Tn; vcm = vcmn;
                     sv.x = vcn;
                 }
             }
         }
         sv.z = __uint_as_float(rng.ctr);
-        p.st_v[slot] = sv;
     }
     uint32_t idx = queue_push(p.counters + CTR_QOUT, go);
-    if (go) p.q_out[idx] = slot;
+    if (go) { p.q_out[idx] = slot; p.ray_out[idx] = nr_out; p.stt_out[idx] = make_float4(T.x, T.y, T.z, vcm); p.sv_out[idx] = sv; }
+    else if (in) p.st_v[slot] = sv;   // the walk ends here: the draw count the parity entry point reads
 }
 
 // ---- connectVertices (bdpt.h:434-483): one thread per (eye vertex, stored light vertex) pair of the dense list k_eye_bounce wrote.

@@ -78,6 +78,8 @@ struct trb_context {
     DevBuf<RayT> cam_ray, ray, sray, sray2;   // two shadow queues: one is traced while the next is being filled
     DevBuf<HitT> hit, hit0;
     DevBuf<float4> st_t, st_v;
+    DevBuf<RayT> ray_b;               // BDPT: second set of the queue-ordered walk records (WaveParams: ray_in / ray_out ...)
+    DevBuf<float4> st_t_b, sv_a, sv_b;
     DevBuf<LightVertex> lv;
     DevBuf<int32_t> nlv, q_a, q_b, q_conn;
     DevBuf<uint32_t> pt_ctr;             // path tracer: one counter per queue / traversal launch
@@ -192,7 +194,7 @@ inline int max_vertices_of(const trb_render_desc& d) { return std::max(max_depth
 // device memory that is free now (buffers the context already holds count as free), never below 2^20.
 int64_t default_wave_samples(trb_context* c, int K) {
     const size_t kk = size_t(std::max(K, 1));
-    const size_t per_slot = 228 + 68 * kk + 100 * (kk + 1) + (c->sc.has_tex ? 16 * kk + 16 : 0);
+    const size_t per_slot = 308 + 68 * kk + 100 * (kk + 1) + (c->sc.has_tex ? 16 * kk + 16 : 0);
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return int64_t(1) << 22;
     const size_t held = (c->lv.bytes() + c->sray.bytes() + c->sray2.bytes() + c->spend.bytes() + c->spend2.bytes() + c->ray.bytes() + c->cam_ray.bytes());
@@ -208,6 +210,7 @@ int ensure_wave(trb_context* c, size_t P, int K, bool shadow = true) {
     TRB_CUDA(c, c->cam_ray.alloc(P)); TRB_CUDA(c, c->ray.alloc(P));
     TRB_CUDA(c, c->hit.alloc(P)); TRB_CUDA(c, c->hit0.alloc(P));
     TRB_CUDA(c, c->st_t.alloc(P)); TRB_CUDA(c, c->st_v.alloc(P));
+    if (shadow) { TRB_CUDA(c, c->ray_b.alloc(P)); TRB_CUDA(c, c->st_t_b.alloc(P)); TRB_CUDA(c, c->sv_a.alloc(P)); TRB_CUDA(c, c->sv_b.alloc(P)); }   // (BDPT only)
     TRB_CUDA(c, c->lv.alloc(P * kk)); TRB_CUDA(c, c->nlv.alloc(P));
     TRB_CUDA(c, c->q_a.alloc(P)); TRB_CUDA(c, c->q_b.alloc(P)); TRB_CUDA(c, c->q_conn.alloc(P * kk)); TRB_CUDA(c, c->ev.alloc(P));  // q_conn: (slot, light vertex) pairs
     TRB_CUDA(c, c->sray.alloc(shadow_cap)); TRB_CUDA(c, c->spend.alloc(shadow_cap));
@@ -279,6 +282,7 @@ void trb_destroy(trb_context* c) {
     c->d_etris.release(); c->d_cdf.release(); c->d_esphere.release(); c->pt_ctr.release();
     c->d_tex_info.release(); c->d_tri_uv.release(); c->d_texels.release(); c->lv_tex.release(); c->ev_tex.release();
     c->cam_ray.release(); c->ray.release(); c->sray.release(); c->sray2.release(); c->spend2.release(); c->hit.release(); c->hit0.release(); c->st_t.release();
+    c->ray_b.release(); c->st_t_b.release(); c->sv_a.release(); c->sv_b.release();
     c->st_v.release(); c->lv.release(); c->nlv.release(); c->q_a.release(); c->q_b.release(); c->q_conn.release(); c->ev.release(); c->spend.release();
     c->counters.release(); c->fetch_ctr.release(); c->d_stats.release(); c->fb.release(); c->io_rays.release(); c->io_hits.release(); c->io_occ.release();
     if (c->pinned) cudaFreeHost(c->pinned);
@@ -643,6 +647,13 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     visit = c->d_stats.p + 2;
 #endif
     int32_t* qa = c->q_a.p; int32_t* qb = c->q_b.p;
+    // the two sets of queue-ordered walk records: a stage reads the set its predecessor wrote
+    auto use_sets = [&](bool in_a) {
+        p.q_in = in_a ? qa : qb;                       p.q_out = in_a ? qb : qa;
+        p.ray_in = in_a ? c->ray.p : c->ray_b.p;       p.ray_out = in_a ? c->ray_b.p : c->ray.p;
+        p.stt_in = in_a ? c->st_t.p : c->st_t_b.p;     p.stt_out = in_a ? c->st_t_b.p : c->st_t.p;
+        p.sv_in = in_a ? c->sv_a.p : c->sv_b.p;        p.sv_out = in_a ? c->sv_b.p : c->sv_a.p;
+    };
     auto stage_ctr = [&](int s) { return c->counters.p + size_t(s) * CTR_N; };
     const int gP = grid_exact(size_t(P));
     const int gB = int((size_t(P) + TRB_SORT_BLOCK - 1) / TRB_SORT_BLOCK);
@@ -688,32 +699,30 @@ int run_wave(trb_context* c, const WaveRun& w, const trb::CameraDev& cam, int64_
     launch_closest(c, p.cam_ray, nullptr, nullptr, uint32_t(P), p.hit, stage_ctr(2 * kk + 2) + CTR_FETCH_CLOSEST, visit); c->mark(LK_CLOSEST);  // (camera rays are coherent as generated)
     // light subpath
     int stage = 0;
-    p.counters = stage_ctr(stage); p.q_out = qa;
+    p.counters = stage_ctr(stage); use_sets(false);   // writes set A
     k_light_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
     const bool light_only = (d.flags & TRB_FLAG_LIGHT_TRACING) != 0, eye_only = (d.flags & TRB_FLAG_PATH_TRACING) != 0;   // bdpt.h:16-17, 229-237
     for (int depth = 1; depth <= (eye_only ? 0 : K); ++depth) {
         const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
-        p.q_in = (stage % 2 == 0) ? qa : qb;
-        p.q_out = (stage % 2 == 0) ? qb : qa;
+        use_sets(stage % 2 == 0);
         ++stage;
         p.counters = stage_ctr(stage);
-        closest(p.ray, p.q_in, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
+        closest(p.ray_in, nullptr, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);   // rays and hits by queue position
         shadow_buffers();
         k_light_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in); c->mark(LK_LOGIC);
         trace_shadow();
     }
     // eye subpath
     stage = kk + 1;
-    p.counters = stage_ctr(stage); p.q_out = qa;
+    p.counters = stage_ctr(stage); use_sets(false);
     k_eye_init<<<gP, TRB_BLOCK, 0, c->stream>>>(p); c->mark(LK_LOGIC);
     for (int depth = 1; depth <= (light_only ? 1 : K); ++depth) {   // (LIGHT_TRACING: one pass that adds the primary hit's emission)
         const uint32_t* n_in = stage_ctr(stage) + CTR_QOUT;
         const bool even = ((stage - (kk + 1)) % 2 == 0);
-        p.q_in = even ? qa : qb;
-        p.q_out = even ? qb : qa;
+        use_sets(even);
         ++stage;
         p.counters = stage_ctr(stage);
-        if (depth > 1) closest(p.ray, p.q_in, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
+        if (depth > 1) closest(p.ray_in, nullptr, n_in, 0u, p.counters + CTR_FETCH_CLOSEST);
         shadow_buffers();
         k_eye_bounce<<<gB, TRB_SORT_BLOCK, 0, c->stream>>>(p, depth, n_in);
         if (c->sc.has_tex) k_connect_vertices<true><<<grid_for(size_t(P) * size_t(kk), sm), TRB_BLOCK, 0, c->stream>>>(p, p.counters + CTR_CONN);
