@@ -10,6 +10,9 @@
 #include <algorithm>
 #include <array>
 #include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <chrono>
 #include <cstdio>
 #include <cmath>
@@ -336,6 +339,7 @@ void build_wide_nodes(const RefTree& tree, std::vector<DevNode4>& out, int32_t& 
     out.clear(); depth = 0;
     if (tree.nodes.empty() || tree.nodes[0].left < 0) return;   // a single leaf: the root reference is the leaf itself
     std::vector<int32_t> level{0}, next;
+    out.reserve(tree.nodes.size() / 3 + 16);   // (a wide node stands for about two inner binary nodes: no re-allocation on the way in the common case)
     while (!level.empty()) {
         const size_t base = out.size();
         out.resize(base + level.size());
@@ -410,73 +414,74 @@ inline int sah_bin_of(const LeafBox& l, int ax, float cmn, float ext, int nb) {
 }
 }  // namespace
 
+// a fixed set of threads that runs f(0) .. f(T-1) once per run(): the top of the SAH tree makes hundreds of short passes over one range
+namespace {
+struct BuildPool {
+    unsigned T;
+    std::vector<std::thread> th;
+    std::mutex m;
+    std::condition_variable cv, done_cv;
+    std::function<void(unsigned)> job;
+    uint64_t gen = 0;
+    unsigned pending = 0;
+    bool stop = false;
+    explicit BuildPool(unsigned t) : T(t) { for (unsigned k = 1; k < T; ++k) th.emplace_back([this, k]() { loop(k); }); }
+    void loop(unsigned k) {
+        uint64_t seen = 0;
+        for (;;) {
+            std::function<void(unsigned)> j;
+            { std::unique_lock<std::mutex> l(m); cv.wait(l, [&]() { return stop || gen != seen; }); if (stop) return; seen = gen; j = job; }
+            j(k);
+            { std::lock_guard<std::mutex> l(m); if (--pending == 0) done_cv.notify_one(); }
+        }
+    }
+    void run(const std::function<void(unsigned)>& f) {
+        if (T == 1) { f(0); return; }
+        { std::lock_guard<std::mutex> l(m); job = f; pending = T - 1; ++gen; }
+        cv.notify_all();
+        f(0);
+        std::unique_lock<std::mutex> l(m);
+        done_cv.wait(l, [&]() { return pending == 0; });
+    }
+    ~BuildPool() { { std::lock_guard<std::mutex> l(m); stop = true; } cv.notify_all(); for (auto& x : th) x.join(); }
+};
+}  // namespace
+
 void build_sah_wide(const LeafBox* L_in, size_t n, std::vector<DevNode4>& out, int32_t& depth) {
     out.clear(); depth = 0;
     const auto t_begin = std::chrono::steady_clock::now();
     if (n < 2) return;   // a single leaf: the root reference is the leaf itself
     // The leaf records themselves are partitioned (32 B moves), not an index: every range is contiguous memory, and a subtree task
-    // works on a private copy that fits the caches.
+    // works on a private copy that fits the caches.  The top of the tree partitions a range from one array into the other (`in_scr`
+    // says where a range lives), all threads on one range; two passes per node: bins, then scatter + the children's bounds.
     std::vector<LeafBox> all(L_in, L_in + n);
-    std::vector<LeafBox> scratch;   // the parallel partition of the top-level ranges
+    std::vector<LeafBox> scratch;
     const unsigned T = build_threads();
-    struct Todo { uint32_t lo, hi; int32_t parent; bool is_right; };
+    BuildPool pool(T);
     struct Bounds { float bmin[3], bmax[3], cmn[3], cmx[3]; };
+    struct Todo { uint32_t lo, hi; int32_t parent; bool is_right; bool in_scr; bool has_b; Bounds b; };
     auto bounds_clear = [](Bounds& b) { for (int k = 0; k < 3; ++k) { b.bmin[k] = 3.4e38f; b.bmax[k] = -3.4e38f; b.cmn[k] = 3.4e38f; b.cmx[k] = -3.4e38f; } };
-    auto bounds_slice = [](const LeafBox* L, uint32_t lo, uint32_t hi, Bounds& b) {
-        for (uint32_t i = lo; i < hi; ++i)
-            for (int k = 0; k < 3; ++k) {
-                b.bmin[k] = std::min(b.bmin[k], L[i].bmin[k]); b.bmax[k] = std::max(b.bmax[k], L[i].bmax[k]);
-                const float c = 0.5f * (L[i].bmin[k] + L[i].bmax[k]);
-                b.cmn[k] = std::min(b.cmn[k], c); b.cmx[k] = std::max(b.cmx[k], c);
-            }
+    auto bounds_add = [](Bounds& b, const LeafBox& l) {
+        for (int k = 0; k < 3; ++k) {
+            b.bmin[k] = std::min(b.bmin[k], l.bmin[k]); b.bmax[k] = std::max(b.bmax[k], l.bmax[k]);
+            const float c = 0.5f * (l.bmin[k] + l.bmax[k]);
+            b.cmn[k] = std::min(b.cmn[k], c); b.cmx[k] = std::max(b.cmx[k], c);
+        }
+    };
+    auto bounds_merge = [](Bounds& b, const Bounds& o) {
+        for (int k = 0; k < 3; ++k) {
+            b.bmin[k] = std::min(b.bmin[k], o.bmin[k]); b.bmax[k] = std::max(b.bmax[k], o.bmax[k]);
+            b.cmn[k] = std::min(b.cmn[k], o.cmn[k]); b.cmx[k] = std::max(b.cmx[k], o.cmx[k]);
+        }
     };
     auto bin_slice = [](const LeafBox* L, uint32_t lo, uint32_t hi, const float cmn[3], const float ext[3], int nbins, SahBin (*bins)[SAH_BINS]) {
         for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < nbins; ++b) bin_clear(bins[ax][b]);
         for (uint32_t i = lo; i < hi; ++i)
             for (int ax = 0; ax < 3; ++ax) if (ext[ax] > 0.f) bin_add(bins[ax][sah_bin_of(L[i], ax, cmn[ax], ext[ax], nbins)], L[i]);
     };
-    // one node over L[lo, hi): bounds, best split (ties: first axis, first bin), stable partition; `wide` = all threads on this range
-    // (min / max / count reductions: the result does not depend on the slicing)
-    auto step = [&](LeafBox* L, const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack, bool wide) {
-        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
-        const bool par = wide && T > 1 && cnt >= (1u << 16);
-        Bounds nb; bounds_clear(nb);
-        if (par) {
-            std::vector<Bounds> part(T);
-            std::vector<std::thread> th;
-            for (unsigned t = 0; t < T; ++t)
-                th.emplace_back([&, t]() { bounds_clear(part[t]); bounds_slice(L, lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), part[t]); });
-            for (auto& x : th) x.join();
-            for (unsigned t = 0; t < T; ++t)
-                for (int k = 0; k < 3; ++k) {
-                    nb.bmin[k] = std::min(nb.bmin[k], part[t].bmin[k]); nb.bmax[k] = std::max(nb.bmax[k], part[t].bmax[k]);
-                    nb.cmn[k] = std::min(nb.cmn[k], part[t].cmn[k]); nb.cmx[k] = std::max(nb.cmx[k], part[t].cmx[k]);
-                }
-        } else {
-            bounds_slice(L, lo, hi, nb);
-        }
-        RefTree::Node node;
-        node.left = -1; node.right = -1; node.start = L[lo].start; node.count = L[lo].count;
-        for (int k = 0; k < 3; ++k) { node.bmin[k] = nb.bmin[k]; node.bmax[k] = nb.bmax[k]; }
-        const int32_t me = int32_t(nodes.size());
-        nodes.push_back(node);
-        if (td.parent >= 0) { if (td.is_right) nodes[td.parent].right = me; else nodes[td.parent].left = me; }
-        if (cnt == 1) return;
-        const float* cmn = nb.cmn;
-        const float ext[3] = {nb.cmx[0] - nb.cmn[0], nb.cmx[1] - nb.cmn[1], nb.cmx[2] - nb.cmn[2]};
-        SahBin bins[3][SAH_BINS];
-        const int nbins = int(std::min<uint32_t>(SAH_BINS, cnt));
-        if (par) {
-            std::vector<std::array<std::array<SahBin, SAH_BINS>, 3>> part(T);
-            std::vector<std::thread> th;
-            for (unsigned t = 0; t < T; ++t)
-                th.emplace_back([&, t]() { bin_slice(L, lo + uint32_t(uint64_t(cnt) * t / T), lo + uint32_t(uint64_t(cnt) * (t + 1) / T), cmn, ext, nbins, reinterpret_cast<SahBin(*)[SAH_BINS]>(part[t].data())); });
-            for (auto& x : th) x.join();
-            for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < nbins; ++b) { bin_clear(bins[ax][b]); for (unsigned t = 0; t < T; ++t) bin_merge(bins[ax][b], part[t][ax][b]); }
-        } else {
-            bin_slice(L, lo, hi, cmn, ext, nbins, bins);
-        }
-        float best = 3.4e38f; int baxis = -1, bsplit = -1;
+    // best split of a binned range (ties: first axis, first bin); false when every centroid coincides
+    auto choose_split = [](SahBin (*bins)[SAH_BINS], int nbins, const float ext[3], int* baxis, int* bsplit) {
+        float best = 3.4e38f; *baxis = -1; *bsplit = -1;
         for (int ax = 0; ax < 3; ++ax) {
             if (!(ext[ax] > 0.f)) continue;
             float ra[SAH_BINS]; uint32_t rn[SAH_BINS];
@@ -487,11 +492,35 @@ void build_sah_wide(const LeafBox* L_in, size_t n, std::vector<DevNode4>& out, i
                 bin_merge(acc, bins[ax][b]);
                 if (!acc.n || !rn[b + 1]) continue;
                 const float cost = wide_box_area(acc.mn, acc.mx) * float(acc.n) + ra[b + 1] * float(rn[b + 1]);
-                if (cost < best) { best = cost; baxis = ax; bsplit = b; }
+                if (cost < best) { best = cost; *baxis = ax; *bsplit = b; }
             }
         }
+        return *baxis >= 0;
+    };
+    auto new_node = [](std::vector<RefTree::Node>& nodes, const Todo& td, const Bounds& nb, const LeafBox& first) {
+        RefTree::Node node;
+        node.left = -1; node.right = -1; node.start = first.start; node.count = first.count;
+        for (int k = 0; k < 3; ++k) { node.bmin[k] = nb.bmin[k]; node.bmax[k] = nb.bmax[k]; }
+        const int32_t me = int32_t(nodes.size());
+        nodes.push_back(node);
+        if (td.parent >= 0) { if (td.is_right) nodes[td.parent].right = me; else nodes[td.parent].left = me; }
+        return me;
+    };
+    // one node over L[lo, hi) on the calling thread: bounds, best split, stable partition in place
+    auto step = [&](LeafBox* L, const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack) {
+        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
+        Bounds nb;
+        if (td.has_b) nb = td.b; else { bounds_clear(nb); for (uint32_t i = lo; i < hi; ++i) bounds_add(nb, L[i]); }
+        const int32_t me = new_node(nodes, td, nb, L[lo]);
+        if (cnt == 1) return;
+        const float* cmn = nb.cmn;
+        const float ext[3] = {nb.cmx[0] - nb.cmn[0], nb.cmx[1] - nb.cmn[1], nb.cmx[2] - nb.cmn[2]};
+        SahBin bins[3][SAH_BINS];
+        const int nbins = int(std::min<uint32_t>(SAH_BINS, cnt));
+        bin_slice(L, lo, hi, cmn, ext, nbins, bins);
+        int baxis, bsplit;
         uint32_t mid = lo + cnt / 2;   // coincident centroids: split the list in the middle, order untouched
-        if (baxis >= 0) {
+        if (choose_split(bins, nbins, ext, &baxis, &bsplit)) {
             const float c0 = cmn[baxis], e0 = ext[baxis];
             auto goes_left = [&](const LeafBox& l) { return sah_bin_of(l, baxis, c0, e0, nbins) <= bsplit; };
             uint32_t m;
@@ -500,98 +529,117 @@ void build_sah_wide(const LeafBox* L_in, size_t n, std::vector<DevNode4>& out, i
                 for (uint32_t i = lo; i < hi; ++i) { if (goes_left(L[i])) L[w++] = L[i]; else right[nr++] = L[i]; }
                 for (uint32_t i = 0; i < nr; ++i) L[w + i] = right[i];
                 m = w;
-            } else if (par) {   // stable, on all threads: count per slice, prefix, scatter into a scratch array, copy back
-                std::vector<uint32_t> nl(T + 1, 0);
-                auto slice = [&](unsigned t, uint32_t* a, uint32_t* b) { *a = lo + uint32_t(uint64_t(cnt) * t / T); *b = lo + uint32_t(uint64_t(cnt) * (t + 1) / T); };
-                {
-                    std::vector<std::thread> th;
-                    for (unsigned t = 0; t < T; ++t)
-                        th.emplace_back([&, t]() { uint32_t a, b, c = 0; slice(t, &a, &b); for (uint32_t i = a; i < b; ++i) c += goes_left(L[i]) ? 1u : 0u; nl[t + 1] = c; });
-                    for (auto& x : th) x.join();
-                }
-                for (unsigned t = 0; t < T; ++t) nl[t + 1] += nl[t];
-                const uint32_t n_left = nl[T];
-                scratch.resize(cnt);
-                {
-                    std::vector<std::thread> th;
-                    for (unsigned t = 0; t < T; ++t)
-                        th.emplace_back([&, t]() {
-                            uint32_t a, b; slice(t, &a, &b);
-                            uint32_t wl = nl[t], wr = n_left + ((a - lo) - nl[t]);
-                            for (uint32_t i = a; i < b; ++i) { if (goes_left(L[i])) scratch[wl++] = L[i]; else scratch[wr++] = L[i]; }
-                        });
-                    for (auto& x : th) x.join();
-                }
-                {
-                    std::vector<std::thread> th;
-                    for (unsigned t = 0; t < T; ++t)
-                        th.emplace_back([&, t]() { uint32_t a, b; slice(t, &a, &b); std::memcpy(L + a, scratch.data() + (a - lo), size_t(b - a) * sizeof(LeafBox)); });
-                    for (auto& x : th) x.join();
-                }
-                m = lo + n_left;
             } else {
                 m = uint32_t(std::stable_partition(L + lo, L + hi, goes_left) - L);
             }
             if (m > lo && m < hi) mid = m;
         }
-        stack.push_back({mid, hi, me, true});
-        stack.push_back({lo, mid, me, false});
+        Todo r{mid, hi, me, true, td.in_scr, false, Bounds()}, l{lo, mid, me, false, td.in_scr, false, Bounds()};
+        stack.push_back(r);
+        stack.push_back(l);
     };
-    // top of the tree on the calling thread (wide steps), ranges below `defer_below` leaves as subtree tasks on all threads
+    // the same node with all threads on the range: per-slice bins (their counts give every slice's share of the left side, so the
+    // partition needs no counting pass), then one pass that scatters the range into the OTHER array, stable, and gathers the bounds of
+    // both children on the way.  min / max / count reductions and slice-ordered offsets: the result does not depend on T.
+    auto step_wide = [&](const Todo& td, std::vector<RefTree::Node>& nodes, std::vector<Todo>& stack) {
+        const uint32_t lo = td.lo, hi = td.hi, cnt = hi - lo;
+        const LeafBox* src = td.in_scr ? scratch.data() : all.data();
+        LeafBox* dst = td.in_scr ? all.data() : scratch.data();
+        auto slice = [&](unsigned t, uint32_t* a, uint32_t* b) { *a = lo + uint32_t(uint64_t(cnt) * t / T); *b = lo + uint32_t(uint64_t(cnt) * (t + 1) / T); };
+        Bounds nb;
+        if (td.has_b) nb = td.b;
+        else {
+            std::vector<Bounds> part(T);
+            pool.run([&](unsigned t) { uint32_t a, b; slice(t, &a, &b); bounds_clear(part[t]); for (uint32_t i = a; i < b; ++i) bounds_add(part[t], src[i]); });
+            bounds_clear(nb);
+            for (unsigned t = 0; t < T; ++t) bounds_merge(nb, part[t]);
+        }
+        const int32_t me = new_node(nodes, td, nb, src[lo]);
+        const float* cmn = nb.cmn;
+        const float ext[3] = {nb.cmx[0] - nb.cmn[0], nb.cmx[1] - nb.cmn[1], nb.cmx[2] - nb.cmn[2]};
+        const int nbins = SAH_BINS;
+        std::vector<std::array<std::array<SahBin, SAH_BINS>, 3>> part(T);
+        pool.run([&](unsigned t) { uint32_t a, b; slice(t, &a, &b); bin_slice(src, a, b, cmn, ext, nbins, reinterpret_cast<SahBin(*)[SAH_BINS]>(part[t].data())); });
+        SahBin bins[3][SAH_BINS];
+        for (int ax = 0; ax < 3; ++ax) for (int b = 0; b < nbins; ++b) { bin_clear(bins[ax][b]); for (unsigned t = 0; t < T; ++t) bin_merge(bins[ax][b], part[t][ax][b]); }
+        int baxis, bsplit;
+        if (!choose_split(bins, nbins, ext, &baxis, &bsplit)) {   // coincident centroids: the middle of the list, nothing moves
+            const uint32_t mid = lo + cnt / 2;
+            Todo r{mid, hi, me, true, td.in_scr, false, Bounds()}, l{lo, mid, me, false, td.in_scr, false, Bounds()};
+            stack.push_back(r); stack.push_back(l);
+            return;
+        }
+        std::vector<uint32_t> nl(T + 1, 0);
+        for (unsigned t = 0; t < T; ++t) { uint32_t c = 0; for (int b = 0; b <= bsplit; ++b) c += part[t][baxis][b].n; nl[t + 1] = nl[t] + c; }
+        const uint32_t n_left = nl[T];   // (0 < n_left < cnt: choose_split only takes splits with leaves on both sides)
+        const float c0 = cmn[baxis], e0 = ext[baxis];
+        std::vector<Bounds> bl(T), br(T);
+        pool.run([&](unsigned t) {
+            uint32_t a, b; slice(t, &a, &b);
+            uint32_t wl = lo + nl[t], wr = lo + n_left + ((a - lo) - nl[t]);
+            bounds_clear(bl[t]); bounds_clear(br[t]);
+            for (uint32_t i = a; i < b; ++i) {
+                if (sah_bin_of(src[i], baxis, c0, e0, nbins) <= bsplit) { dst[wl++] = src[i]; bounds_add(bl[t], src[i]); }
+                else { dst[wr++] = src[i]; bounds_add(br[t], src[i]); }
+            }
+        });
+        Todo r{lo + n_left, hi, me, true, !td.in_scr, true, Bounds()}, l{lo, lo + n_left, me, false, !td.in_scr, true, Bounds()};
+        bounds_clear(r.b); bounds_clear(l.b);
+        for (unsigned t = 0; t < T; ++t) { bounds_merge(l.b, bl[t]); bounds_merge(r.b, br[t]); }
+        stack.push_back(r); stack.push_back(l);
+    };
+    // top of the tree with all threads on one range, ranges below `defer_below` leaves as subtree tasks
     const uint32_t defer_below = (T > 1 && n >= (size_t(1) << 15)) ? uint32_t(n / (size_t(T) * 8)) : 0u;
     struct Task { Todo td; int32_t parent; bool is_right; std::vector<RefTree::Node> nodes; };
     RefTree sah;
     std::vector<Task> tasks;
     {
+        if (defer_below) scratch.resize(n);
         std::vector<Todo> stack;
-        stack.push_back({0u, uint32_t(n), -1, false});
+        stack.push_back(Todo{0u, uint32_t(n), -1, false, false, false, Bounds()});
         while (!stack.empty()) {
             Todo td = stack.back(); stack.pop_back();
             if (defer_below && td.hi - td.lo < defer_below && td.parent >= 0) {
-                Task t; t.td = {td.lo, td.hi, -1, false}; t.parent = td.parent; t.is_right = td.is_right;
+                Task t; t.td = td; t.parent = td.parent; t.is_right = td.is_right;
                 tasks.push_back(std::move(t));
                 continue;
             }
-            step(all.data(), td, sah.nodes, stack, true);
+            if (defer_below && td.hi - td.lo >= 4096u) step_wide(td, sah.nodes, stack);
+            else step(td.in_scr ? scratch.data() : all.data(), td, sah.nodes, stack);
         }
     }
     const auto t_top = std::chrono::steady_clock::now();
     auto t_tasks = t_top;
     if (!tasks.empty()) {   // disjoint ranges: every task copies its leaves and builds its subtree from the copy
         std::atomic<size_t> next{0};
-        auto worker = [&]() {
+        pool.run([&](unsigned) {
             std::vector<Todo> stack;
             std::vector<LeafBox> local;
             for (size_t i = next.fetch_add(1); i < tasks.size(); i = next.fetch_add(1)) {
                 Task& t = tasks[i];
-                local.assign(all.begin() + t.td.lo, all.begin() + t.td.hi);
+                const LeafBox* from = t.td.in_scr ? scratch.data() : all.data();
+                local.assign(from + t.td.lo, from + t.td.hi);
                 t.nodes.reserve(2 * local.size());
-                stack.clear(); stack.push_back({0u, uint32_t(local.size()), -1, false});
-                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(local.data(), td, t.nodes, stack, false); }
+                stack.clear();
+                Todo root{0u, uint32_t(local.size()), -1, false, false, t.td.has_b, t.td.b};
+                stack.push_back(root);
+                while (!stack.empty()) { Todo td = stack.back(); stack.pop_back(); step(local.data(), td, t.nodes, stack); }
             }
-        };
-        std::vector<std::thread> th;
-        for (unsigned k = 1; k < T; ++k) th.emplace_back(worker);
-        worker();
-        for (auto& x : th) x.join();
+        });
         t_tasks = std::chrono::steady_clock::now();
         // stitch in task order (the order the top pass met them: deterministic): bases by a prefix sum, copies on all threads
         std::vector<size_t> base(tasks.size() + 1, sah.nodes.size());
         for (size_t k = 0; k < tasks.size(); ++k) base[k + 1] = base[k] + tasks[k].nodes.size();
         sah.nodes.resize(base[tasks.size()]);
         std::atomic<size_t> nxt{0};
-        auto copier = [&]() {
+        pool.run([&](unsigned) {
             for (size_t k = nxt.fetch_add(1); k < tasks.size(); k = nxt.fetch_add(1)) {
                 const int32_t b = int32_t(base[k]);
                 RefTree::Node* dst = sah.nodes.data() + base[k];
                 for (RefTree::Node nd : tasks[k].nodes) { if (nd.left >= 0) { nd.left += b; nd.right += b; } *dst++ = nd; }
                 std::vector<RefTree::Node>().swap(tasks[k].nodes);
             }
-        };
-        std::vector<std::thread> th2;
-        for (unsigned k = 1; k < T; ++k) th2.emplace_back(copier);
-        copier();
-        for (auto& x : th2) x.join();
+        });
         for (size_t k = 0; k < tasks.size(); ++k) {
             RefTree::Node& par = sah.nodes[tasks[k].parent];
             if (tasks[k].is_right) par.right = int32_t(base[k]); else par.left = int32_t(base[k]);

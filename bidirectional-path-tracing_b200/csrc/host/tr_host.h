@@ -155,7 +155,7 @@ struct FlatScene {
 
 // Reference-order BVH build (externals/bvh.h:147-247).  order[pos] = global triangle id.
 struct RefTree {
-    struct Node { float bmin[3], bmax[3]; uint32_t start, count; int32_t left, right; };  // left<0: leaf
+    struct Node { float bmin[3], bmax[3]; uint32_t start, count; int32_t left, right; Node() {} };  // left<0: leaf.  (The empty constructor keeps vector::resize from zero-filling millions of nodes on one thread before the build threads write them.)
     std::vector<Node> nodes;  // pre-order, node 0 = root
     std::vector<int32_t> order;
 };
