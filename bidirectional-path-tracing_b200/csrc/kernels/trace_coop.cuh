@@ -66,6 +66,7 @@ struct TraceArgs {
     int32_t* defer_q;        // k_trace_wide: slots of the rays it leaves to k_trace_coop, and their count
     uint32_t* defer_n;
     uint32_t n_nodes, n_wnodes, n_tris, defer_cap;   // array lengths (TRB_CHECKS builds assert against them)
+    float inv_max;           // near_cull (trace.cuh): 400 / the scene's largest |coordinate|
     unsigned long long* visit;      // TRB_COUNTERS builds: [0] nodes visited, [1] triangles tested
     unsigned long long* visit_exh;  // TRB_COUNTERS builds: exhaustive re-traces
 };

@@ -31,6 +31,7 @@ struct WideView {
     const F4* wnodes;   // 8 x F4 per node (DevNode4: two 64-byte halves)
     const F4* tris;     // 3 x F4 per triangle (DevTri)
     int32_t root_ref;   // 0 (wide node 0) or a leaf code when the scene is a single leaf
+    float inv_max;      // near_cull (trace.cuh): 400 / the scene's largest |coordinate|; 0 = the old rule for every ray
 };
 
 struct WideCounters { uint32_t nodes, boxes, tris, max_sp; };
@@ -58,6 +59,7 @@ TRB_HD bool traverse_wide(const WideView& bvh, const RayT& r, const RayPre& pre,
     *occluded = false;
     if (r.min_t > r.max_t) { *hit = h; return false; }   // bvh.h:287
     const int32_t NONE = 0x7fffffff;
+    const float ncull = near_cull(pre, bvh.inv_max);
     while (cur != NONE) {
         if (cur >= 0) {
             const F4* n = bvh.wnodes + 8 * size_t(cur);   // two 64-byte halves: {c0min c0max c1min c1max ref0 ref1 pad pad}
@@ -75,7 +77,7 @@ TRB_HD bool traverse_wide(const WideView& bvh, const RayT& r, const RayPre& pre,
                 float ex;
                 if (cnt && ref[k] != TRB_WIDE_EMPTY) ++cnt->boxes;
                 ok[k] = wide_child(L[k][0], L[k][1], L[k][2], L[k][3], L[k][4], L[k][5], ref[k], r, pre, &en[k], &ex);
-                if (PRUNE) ok[k] = ok[k] && !(en[k] > lim) && !(ex < -0.0010011f);
+                if (PRUNE) ok[k] = ok[k] && !(en[k] > lim) && !(ex < ncull);
             }
             // onto the stack in slot order, slot 0 on top; when pruning a closest-hit ray the nearest child goes on top of that
             // (what k_trace_wide does: a full sort by entry distance saves 3 % of the triangle tests and costs more in instructions)
@@ -180,6 +182,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
     int sp = 0;
     bool have = false, exh = false;
     RayT r; RayPre pre;
+    float ncull = -0.0010011f;   // near_cull(pre) of the lane's ray
     int32_t slot = 0;
     r.ox = r.oy = r.oz = r.dx = r.dy = r.dz = r.min_t = r.max_t = 0.f;
     pre.ix = pre.iy = pre.iz = 0.f; pre.degenerate = false;
@@ -282,6 +285,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                     float4 r0 = rp[0], r1 = rp[1];
                     r.ox = r0.x; r.oy = r0.y; r.oz = r0.z; r.dx = r0.w; r.dy = r1.x; r.dz = r1.y; r.min_t = r1.z; r.max_t = r1.w;
                     pre = ray_pre(r);
+                    ncull = near_cull(pre, a.inv_max);
                     if (pre.degenerate) { const uint32_t at = atomicAdd(a.defer_n, 1u); TRB_CHECK(at < a.defer_cap); a.defer_q[at] = slot; }   // for the reference's own tree (k_trace_coop)
                     else { have = true; exh = false; start_ray(); }
                 }
@@ -323,7 +327,7 @@ __global__ void __launch_bounds__(TRB_TRACE_BLOCK, TRB_TRACE_MINBLOCKS) k_trace_
                     BoxF f = box_fast(mnx, mny, mnz, mxx, mxy, mxz, r, pre); \
                     bool hit = f.pass || f.undecided; \
                     if (f.undecided && ref < 0) hit = box_slow(mnx, mny, mnz, mxx, mxy, mxz, r, pre, f); \
-                    hit = hit && ref != TRB_WIDE_EMPTY && !stop && (exh || (!(f.en > lim) && !(f.ex < -0.0010011f))); \
+                    hit = hit && ref != TRB_WIDE_EMPTY && !stop && (exh || (!(f.en > lim) && !(f.ex < ncull))); \
                     if (hit && ref < 0) { if (nl == 0) ca = uint32_t(~ref); else if (nl == 1) cb = uint32_t(~ref); else push(ref); ++nl; } \
                     if (hit && ref >= 0) { \
                         const bool take = nref < 0 || (!ANY && !exh && f.en < nen); \

@@ -57,6 +57,7 @@ struct trb_context {
     bool has_scene = false;
     bool built_on_device = false;   // the acceleration structure and the triangle records came from kernels/bvh_build.cuh
     int trace_blocks_per_sm = TRB_TRACE_MINBLOCKS;   // persistent traversal grid = SMs x this ($TRB_TRACE_GRID_BLOCKS at trb_create: experiments with room left for other kernels)
+    float near_inv_max = 0.f;       // TraceArgs::inv_max of the uploaded scene (kernels/trace.cuh: near_cull)
     bool force_binary = false;      // TRB_TRAVERSAL=binary at trb_create: every ray on the reference's binary tree (A/B measurements, tests of k_trace_coop)
     trb::FlatScene flat;
     DevBuf<trb::DevNode> d_nodes;      // the reference's binary tree (degenerate rays, k_pt_check)
@@ -150,6 +151,7 @@ void launch_closest(trb_context* c, const RayT* rays, const int32_t* q, const ui
     a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
     a.n_nodes = uint32_t(c->flat.n_nodes); a.n_wnodes = uint32_t(c->flat.n_wnodes); a.n_tris = uint32_t(c->flat.n_tris);
     a.rays = rays; a.q = q; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = 0xffffffffu; a.hits = hits; a.fetch = ctr;
+    a.inv_max = c->near_inv_max;
     a.defer_q = c->defer_q[0].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[0].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 6 : nullptr;
     const int grid = c->prop.multiProcessorCount * c->trace_blocks_per_sm;
@@ -169,6 +171,7 @@ void launch_any(trb_context* c, const RayT* rays, const uint32_t* n_ptr, uint32_
     a.wnodes = reinterpret_cast<const F4*>(c->d_wnodes.p); a.wroot = c->flat.n_wnodes ? 0 : c->sc.root_ref;
     a.n_nodes = uint32_t(c->flat.n_nodes); a.n_wnodes = uint32_t(c->flat.n_wnodes); a.n_tris = uint32_t(c->flat.n_tris);
     a.rays = rays; a.q = nullptr; a.n_ptr = n_ptr; a.n_fixed = n_fixed; a.cap = cap; a.occ_out = occ_out; a.pend = pend; a.accum = accum; a.fetch = ctr;
+    a.inv_max = c->near_inv_max;
     a.defer_q = c->defer_q[which].p; a.defer_n = ctr + 1; a.defer_cap = uint32_t(std::min<size_t>(c->defer_q[which].n, 0xffffffffu));
     a.visit = visit; a.visit_exh = visit ? c->d_stats.p + 7 : nullptr;
     const int grid = c->prop.multiProcessorCount * c->trace_blocks_per_sm;
@@ -551,6 +554,12 @@ int trb_scene_upload_ex(trb_context* c, const trb_scene_desc* s, uint32_t flags)
     c->sc.tri_uv = reinterpret_cast<const float4*>(c->d_tri_uv.p); c->sc.tex_info = reinterpret_cast<const int4*>(c->d_tex_info.p);
     c->sc.texels = c->d_texels.p; c->sc.has_tex = f.tex_info.empty() ? 0 : 1;
     c->sc.cdf = c->d_cdf.p; c->sc.esphere = c->d_esphere.p; c->sc.root_ref = f.root_ref; c->sc.n_emitters = int32_t(f.emitters.size());
+    {   // near_cull (kernels/trace.cuh) is tied to the size of the scene's coordinates; TRB_NEAR_CULL=0 at upload keeps the old rule (A/B runs)
+        float amax = 0.f;
+        for (int k = 0; k < 3; ++k) amax = std::max(amax, std::max(std::fabs(f.scene_min[k]), std::fabs(f.scene_max[k])));
+        const char* e = std::getenv("TRB_NEAR_CULL");
+        c->near_inv_max = (e && std::string(e) == "0") ? 0.f : (amax > 0.f && std::isfinite(amax) ? 400.f / amax : 0.f);
+    }
     c->has_scene = true;
     if (on_device) {
         // the tables go up directly; the pinned staging blob (geometry read back from the device) is made by the first trb_scene_refresh

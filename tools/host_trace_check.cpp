@@ -8,6 +8,14 @@
 #include "../bidirectional-path-tracing_b200/csrc/host/tr_host.h"
 #include "../bidirectional-path-tracing_b200/csrc/kernels/trace.cuh"
 
+// TraceArgs::inv_max as trb_scene_upload sets it (kernels/trace.cuh: near_cull); HC_NEAR_CULL=0 = the old rule
+static float hc_inv_max(const trb::FlatScene& fs) {
+    if (const char* e = std::getenv("HC_NEAR_CULL")) if (e[0] == '0') return 0.f;
+    float amax = 0.f;
+    for (int k = 0; k < 3; ++k) amax = std::max(amax, std::max(std::fabs(fs.scene_min[k]), std::fabs(fs.scene_max[k])));
+    return amax > 0.f ? 400.f / amax : 0.f;
+}
+
 extern "C" int hc_trace(const trb_scene_desc* s, const float* rays8, long n, int any, float* tuv, int* tri_out,
                         unsigned char* occ, unsigned long long* counters, int force_exhaustive) {
     trb::FlatScene fs;
@@ -52,7 +60,7 @@ extern "C" int hc_trace_wide(const trb_scene_desc* s, const float* rays8, long n
         cached = s->positions;
     }
     trbk::BvhView bv{reinterpret_cast<const trbk::F4*>(fs.nodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.root_ref};
-    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(fs.wnodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.wnodes.empty() ? fs.root_ref : 0};
+    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(fs.wnodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.wnodes.empty() ? fs.root_ref : 0, hc_inv_max(fs)};
     trbk::WideCounters c{0, 0, 0, 0};
     unsigned long long nn = 0, nb = 0, nt = 0, ndeg = 0;
     for (long i = 0; i < n; ++i) {
@@ -204,7 +212,7 @@ extern "C" int hc_trace_wide_sah(const trb_scene_desc* s, const float* rays8, lo
         cached = s->positions;
     }
     trbk::BvhView bv{reinterpret_cast<const trbk::F4*>(fs.nodes.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), fs.root_ref};
-    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(wn.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), wn.empty() ? fs.root_ref : 0};
+    trbk::WideView wv{reinterpret_cast<const trbk::F4*>(wn.data()), reinterpret_cast<const trbk::F4*>(fs.tris.data()), wn.empty() ? fs.root_ref : 0, hc_inv_max(fs)};
     trbk::WideCounters c{0, 0, 0, 0};
     unsigned long long nn = 0, nb = 0, nt = 0;
     for (long i = 0; i < n; ++i) {
