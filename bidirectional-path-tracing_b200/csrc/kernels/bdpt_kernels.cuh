@@ -205,6 +205,9 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_light_init(const __grid_constant_
 #endif
 #define TRB_LB_BOUNDS __launch_bounds__(TRB_SORT_BLOCK, TRB_LB_MINB)
 #define TRB_EB_BOUNDS __launch_bounds__(TRB_SORT_BLOCK, TRB_EB_MINB)
+#ifndef TRB_CV_COMPACT
+#define TRB_CV_COMPACT 1
+#endif
 #ifdef TRB_CV_MINB
 #define TRB_CV_BOUNDS __launch_bounds__(TRB_BLOCK, TRB_CV_MINB)
 #else
@@ -450,61 +453,108 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
 // ---- connectVertices (bdpt.h:434-483): one thread per (eye vertex, stored light vertex) pair of the dense list k_eye_bounce wrote.
 // Replaces the per-thread loop over the sample's light vertices (profiles/r1e: 7 active threads per instruction in k_eye_bounce). ----
 // TEX: the scene has bitmap textures (their lookup is compiled out of the untextured instance, which every shipped scene runs)
+// the two cosines of a connection, exactly as cv_evaluate forms them: they decide whether the pair is evaluated at all (bdpt.h:447-449)
+__device__ __forceinline__ bool cv_cosines_pass(const WaveParams& p, int pair) {
+    const int slot = pair >> 6;
+    const uint32_t j = uint32_t(pair & 63);
+    const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
+    const float4 ea = ep[0], eb = ep[1];
+    const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(slot) * p.K + j);
+    const float4 a = lp[0], b = lp[1];
+    V3 l2e = mk(ea.x, ea.y, ea.z) - mk(a.x, a.y, a.z);
+    const float invD2 = 1.f / length2(l2e);
+    l2e = l2e * sqrtf(invD2);
+    const float cosL = to_local(make_frame(mk(b.x, b.y, b.z)), l2e).z, cosE = to_local(make_frame(mk(eb.x, eb.y, eb.z)), -l2e).z;
+    return !(cosL <= 0.f || cosE <= 0.f);
+}
+// one (eye vertex, light vertex) pair: the contribution and its shadow ray; false when there is nothing to trace
+template <bool TEX>
+__device__ __forceinline__ bool cv_evaluate(const WaveParams& p, int pair, float li_scale, RayT* sr, V3* Li_out, uint32_t* target) {
+    const int slot = pair >> 6;
+    const uint32_t j = uint32_t(pair & 63);
+    const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
+    float4 ea = ep[0], eb = ep[1], ec = ep[2], ed = ep[3];
+    const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(slot) * p.K + j);
+    float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
+    *target = __float_as_uint(ed.w);
+    V3 epnt = mk(ea.x, ea.y, ea.z), lpnt = mk(a.x, a.y, a.z);
+    V3 l2e = epnt - lpnt;
+    float invD2 = 1.f / length2(l2e);
+    l2e = l2e * sqrtf(invD2);
+    Frame lf = make_frame(mk(b.x, b.y, b.z));
+    Frame ef = make_frame(mk(eb.x, eb.y, eb.z));
+    V3 l_wo = mk(c.x, c.y, c.z), e_wo = mk(ec.x, ec.y, ec.z);
+    V3 l_wi = to_local(lf, l2e);
+    V3 e_wi = to_local(ef, -l2e);
+    float cosL = l_wi.z, cosE = e_wi.z;
+    if (cosL <= 0.f || cosE <= 0.f) return false;
+    Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
+    if (TEX && lm.tex) { const float4 t = p.lv_tex[size_t(slot) * p.K + j]; apply_tex(p.sc, lm, __float_as_int(t.x), t.y, t.z); }
+    const int emat = __float_as_int(ec.w);
+    const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
+    Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
+    if (TEX && m.tex) { const float4 t = p.ev_tex[slot]; apply_tex(p.sc, m, __float_as_int(t.x), t.y, t.z); }
+    V3 Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
+    Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
+    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * lrr;
+    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * lrr;
+    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * err;
+    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * err;
+    float lightRevA = lightRevW * (cosL) * invD2;
+    float eyeRevA = eyeRevW * (cosE) * invD2;
+    float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);
+    float eyeWeight = eyeRevA * (ea.w + eyePrevRevW * eb.w);
+    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
+    Li = Li * mis;
+    Li = Li * li_scale;
+    *Li_out = Li;
+    if (is_zero(Li)) return false;
+    *sr = visibility_ray(epnt, lpnt);
+    return true;
+}
+
 template <bool TEX>
 __global__ void TRB_CV_BOUNDS k_connect_vertices(const __grid_constant__ WaveParams p, const uint32_t* __restrict__ n_pairs_ptr) {
     const unsigned long long total = *n_pairs_ptr;
-    const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballot of push_shadow
+    const unsigned long long total_w = (total + 31ull) & ~31ull;  // whole warps take part in the ballots
     const float li_scale = p.parity ? 1.f : (1.f / p.spp);
-    for (unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; t < total_w; t += (unsigned long long)gridDim.x * blockDim.x) {
-        bool want = false; RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
-        if (t < total) {
-            // the pairs of one eye vertex are neighbours: its lanes read the same EyeVertex words (one broadcast transaction)
-            const int pair = p.q_conn[t];
-            const int slot = pair >> 6;
-            const uint32_t j = uint32_t(pair & 63);
-            {
-
-                const float4* ep = reinterpret_cast<const float4*>(p.ev + slot);
-                float4 ea = ep[0], eb = ep[1], ec = ep[2], ed = ep[3];
-                const float4* lp = reinterpret_cast<const float4*>(p.lv + size_t(slot) * p.K + j);
-                float4 a = lp[0], b = lp[1], c = lp[2], d = lp[3];
-                target = __float_as_uint(ed.w);
-                V3 epnt = mk(ea.x, ea.y, ea.z), lpnt = mk(a.x, a.y, a.z);
-                V3 l2e = epnt - lpnt;
-                float invD2 = 1.f / length2(l2e);
-                l2e = l2e * sqrtf(invD2);
-                Frame lf = make_frame(mk(b.x, b.y, b.z));
-                Frame ef = make_frame(mk(eb.x, eb.y, eb.z));
-                V3 l_wo = mk(c.x, c.y, c.z), e_wo = mk(ec.x, ec.y, ec.z);
-                V3 l_wi = to_local(lf, l2e);
-                V3 e_wi = to_local(ef, -l2e);
-                float cosL = l_wi.z, cosE = e_wi.z;
-                if (!(cosL <= 0.f || cosE <= 0.f)) {
-                    Mat lm = load_mat(p.sc.mats, __float_as_int(c.w));
-                    if (TEX && lm.tex) { const float4 t = p.lv_tex[size_t(slot) * p.K + j]; apply_tex(p.sc, lm, __float_as_int(t.x), t.y, t.z); }
-                    const int emat = __float_as_int(ec.w);
-                    const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
-                    Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
-                    if (TEX && m.tex) { const float4 t = p.ev_tex[slot]; apply_tex(p.sc, m, __float_as_int(t.x), t.y, t.z); }
-                    Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
-                    Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
-                    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * lrr;
-                    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * lrr;
-                    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * err;
-                    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * err;
-                    float lightRevA = lightRevW * (cosL) * invD2;
-                    float eyeRevA = eyeRevW * (cosE) * invD2;
-                    float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);
-                    float eyeWeight = eyeRevA * (ea.w + eyePrevRevW * eb.w);
-                    float mis = 1.f / (lightWeight + 1.f + eyeWeight);
-                    Li = Li * mis;
-                    Li = Li * li_scale;
-                    if (!is_zero(Li)) { sr = visibility_ray(epnt, lpnt); want = true; }
-                }
-            }
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    unsigned long long t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+#if TRB_CV_COMPACT
+    // Half the pairs leave at the cosine test and the rest cost ten times as much: a warp tests 32 pairs, keeps the survivors in a
+    // shared-memory list and evaluates them 32 at a time with every lane busy (ncu before: 14 active threads per instruction).
+    __shared__ int s_list[TRB_BLOCK / 32][64];
+    int* list = s_list[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    int cnt = 0;   // warp-uniform
+    for (; t < total_w; t += stride) {
+        int pair = 0; bool pass = false;
+        if (t < total) { pair = p.q_conn[t]; pass = cv_cosines_pass(p, pair); }   // (the pairs of one eye vertex are neighbours: one broadcast read of its record)
+        const unsigned m = __ballot_sync(0xffffffffu, pass);
+        if (pass) list[cnt + __popc(m & lt)] = pair;
+        cnt += __popc(m);
+        __syncwarp();
+        if (cnt >= 32) {
+            cnt -= 32;
+            RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
+            const bool want = cv_evaluate<TEX>(p, list[cnt + lane], li_scale, &sr, &Li, &target);
+            push_shadow(p, want, sr, Li, target);
+            __syncwarp();
         }
+    }
+    {
+        RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
+        const bool want = lane < cnt && cv_evaluate<TEX>(p, list[lane], li_scale, &sr, &Li, &target);
         push_shadow(p, want, sr, Li, target);
     }
+#else
+    for (; t < total_w; t += stride) {
+        bool want = false; RayT sr; V3 Li = mk(0.f); uint32_t target = 0;
+        if (t < total) want = cv_evaluate<TEX>(p, p.q_conn[t], li_scale, &sr, &Li, &target);
+        push_shadow(p, want, sr, Li, target);
+    }
+#endif
 }
 
 }  // namespace trbk
