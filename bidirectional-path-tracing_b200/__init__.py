@@ -499,10 +499,16 @@ class Context:
                                            _ptr(li), _ptr(draws)))
         return li, draws
 
-    def render_bdpt(self, desc: RenderDesc, accumulate: bool = False, download: bool = True):
-        """Renderer::render (offline branch) with the BDPT integrator. Returns (H x W x 3 float32 | None, stats)."""
+    def render_bdpt(self, desc: RenderDesc, accumulate: bool = False, download: bool = True, out=None):
+        """Renderer::render (offline branch) with the BDPT integrator. Returns (H x W x 3 float32 | None, stats).
+        `out`: the caller's own frame buffer (C-contiguous float32, H x W x 3) - e.g. one in pinned memory, which the library's
+        device-to-host copy then reaches at the full speed of the bus; the reference's RenderBuffer is such a caller-owned array."""
         st = Stats()
-        img = np.zeros((desc.height, desc.width, 3), np.float32) if download else None
+        if out is not None:
+            if out.dtype != np.float32 or not out.flags["C_CONTIGUOUS"] or out.shape != (desc.height, desc.width, 3):
+                raise ValueError("out must be a C-contiguous float32 array of shape (height, width, 3)")
+            download = True
+        img = out if out is not None else (np.zeros((desc.height, desc.width, 3), np.float32) if download else None)
         self._chk(self._L.trb_render_bdpt(self._h, C.byref(desc), int(accumulate), _ptr(img) if download else None, C.byref(st)))
         return img, st.as_dict()
 

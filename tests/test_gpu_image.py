@@ -107,6 +107,24 @@ def test_sample_range_additivity(trb, gpu_ctx, scene_name):
     assert full.mean() > 0.01
 
 
+def test_render_into_the_callers_frame_buffer(trb, gpu_ctx):
+    """trb_render_bdpt writes the frame into the caller's own array (the reference's RenderBuffer is caller-owned): a pinned one here,
+    as bench.py's end-to-end loop uses; a wrong shape or dtype is refused before anything is launched"""
+    import torch
+    ctx = gpu_ctx("caustic")
+    kw = dict(width=200, height=150, spp=4, rr_depth=8)
+    ref, _ = ctx.render_bdpt(trb.render_desc(**kw))
+    frame = torch.empty((150, 200, 3), dtype=torch.float32, pin_memory=True).numpy()
+    frame[:] = -1.0
+    got, st = ctx.render_bdpt(trb.render_desc(**kw), out=frame)
+    assert got is frame and st["samples"] == 200 * 150 * 4
+    assert np.allclose(frame, ref, rtol=2e-5, atol=2e-6) and frame.min() >= 0.0
+    with pytest.raises(ValueError):
+        ctx.render_bdpt(trb.render_desc(**kw), out=np.zeros((150, 200, 4), np.float32))
+    with pytest.raises(ValueError):
+        ctx.render_bdpt(trb.render_desc(**kw), out=np.zeros((150, 200, 3), np.float64))
+
+
 def test_4k_film_sharded_by_sample_index(trb, gpu_ctx):
     """configs[3] at its film size (3840x2160, 99.5 MB frame buffer): two sample shards accumulated == one render, and the
     downsampled image agrees with an 800x600 render of the same camera (same estimator, same aspect handling)"""
