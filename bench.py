@@ -375,6 +375,7 @@ def extra_block(trb, torch, name, spp, fb, flush, args):
                "scene_upload": {"seconds": round(up, 3), "triangles": int(scene.n_tris), "built_on": "device" if ctx.built_on_device() else "host"}}
         # end to end: the scene goes up ONCE (what a caller does), then render + frame buffer D2H per step
         frame = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True).numpy()   # the caller's frame buffer, pinned
+        ctx.render_bdpt(desc, out=frame)   # untimed: first use of the buffer
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         for _ in range(steps):
@@ -504,6 +505,7 @@ def run_ours(args):
     e2e_steps = max(3, args.steps)
     ctx.refresh_scene()   # untimed: a device-built scene makes its pinned staging copy (the host side of the transfer) on the first refresh
     frame = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True).numpy()   # the caller's frame buffer, pinned: the D2H copy lands in it
+    ctx.render_bdpt(desc, out=frame)   # untimed: first use of the buffer
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
