@@ -195,9 +195,10 @@ inline int max_vertices_of(const trb_render_desc& d) { return std::max(max_depth
 // 10 M triangles 75.2 / 79.3 / 81.5 Msamples/s at 2^22 / 2^23 / 2^24; caustic 117.0 / 117.8 / 118.2).  Memory is what a 180 GB part has:
 // the largest power of two <= 2^24 whose wave buffers (bytes per slot below: what ensure_wave allocates) fit in a quarter of the
 // device memory that is free now (buffers the context already holds count as free), never below 2^20.
-int64_t default_wave_samples(trb_context* c, int K) {
+// `shadow`: BDPT (two shadow-ray queues of K + 1 entries per slot, the second set of walk records); false = path tracer / direct integrator.
+int64_t default_wave_samples(trb_context* c, int K, bool shadow = true) {
     const size_t kk = size_t(std::max(K, 1));
-    const size_t per_slot = 308 + 68 * kk + 100 * (kk + 1) + (c->sc.has_tex ? 16 * kk + 16 : 0);
+    const size_t per_slot = (shadow ? 308 + 100 * (kk + 1) : 228) + 68 * kk + (c->sc.has_tex ? 16 * kk + 16 : 0);
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return int64_t(1) << 22;
     const size_t held = (c->lv.bytes() + c->sray.bytes() + c->sray2.bytes() + c->spend.bytes() + c->spend2.bytes() + c->ray.bytes() + c->cam_ray.bytes());
@@ -933,7 +934,9 @@ int render_path_impl(trb_context* c, const trb_render_desc* d, const trb_path_de
     const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
     if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
     const int spp_count = spp_end - spp_begin;
-    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 21);
+    // (B200, profiles/r2_node_phase_experiments.md r7: 2^21 / 2^22 / 2^23 samples per wave -> 64.8 / 89.1 / 111.6 Msamples/s on the caustic scene: a path's
+    // 64 depth levels are 64 launches per stage whatever the wave holds, and deep levels hold few rays)
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : default_wave_samples(c, pt.is_explicit ? pt.cap : 1, /*shadow=*/false);
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     rc = ensure_wave(c, size_t(P), pt.is_explicit ? pt.cap : 1, /*shadow=*/false);
@@ -1021,7 +1024,7 @@ int render_direct_impl(trb_context* c, const trb_render_desc* d, const trb_direc
     const int spp_end = d->spp_end > 0 ? d->spp_end : d->spp;
     if (spp_begin < 0 || spp_end > d->spp || spp_begin > spp_end) return c->fail(TRB_ERR_INVALID, "bad sample range");
     const int spp_count = spp_end - spp_begin;
-    int64_t P = d->wave_samples > 0 ? d->wave_samples : (int64_t(1) << 22);
+    int64_t P = d->wave_samples > 0 ? d->wave_samples : default_wave_samples(c, 1, /*shadow=*/false);
     const int64_t total = npix * spp_count;
     P = std::max<int64_t>(1, std::min(P, std::max<int64_t>(total, 1)));
     if (P > (int64_t(1) << 25)) return c->fail(TRB_ERR_INVALID, "wave_samples must not exceed 2^25");
