@@ -85,7 +85,8 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
         ok = ok && !(cosCamera <= 0.f);
         if (ok) {
             V3 wi = to_local(s.f, -e2l);
-            V3 fcos = bsdf_eval(m, s.wo, wi);
+            const Lobe lobe = glossy_lobe(m, s.wo, wi);   // one powf for the value and the reverse pdf (bsdf.cuh)
+            V3 fcos = bsdf_eval(m, s.wo, wi, lobe);
             if (!(is_zero(fcos) || wi.z <= 0.f)) {
                 sr = visibility_ray(eye, s.p);
                 float ipd = p.cam.vnear_dist / cosCamera;
@@ -96,7 +97,7 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
                 int nlight = p.cam.width * p.cam.height;
                 radiance = T * (fcos * (1.f / wi.z)) * (1.f / surfToImg) * (1.f / nlight) * (1.f / p.spp);
                 float revPdfA = 1.f * imgToSurf;
-                float prevRev = bsdf_pdf(m, wi, s.wo) * rr;  // wi/wo swapped (bdpt.h:342)
+                float prevRev = bsdf_pdf(m, wi, s.wo, lobe) * rr;  // wi/wo swapped (bdpt.h:342)
                 float lightWeight = (revPdfA / nlight) * (vcm + prevRev * vc);
                 float mis = 1.f / (lightWeight + 1.f + 0.f);
                 if (!(p.flags & TRB_EST_MASK)) radiance = radiance * mis;   // bdpt.h:355-357: unweighted under LIGHT_TRACING / PATH_TRACING
@@ -118,14 +119,15 @@ __device__ __forceinline__ void connect_to_camera(const WaveParams& p, bool acti
 __device__ __forceinline__ bool continue_walk(const Surf& s, const Mat& m, Rng& rng, float rr, V3* T, float* vc, float* vcm, RayT* next, V3* wi_out) {
     float ux = rng.next(), uy = rng.next();
     V3 wi; float pdf;
-    V3 fcos = bsdf_sample(m, s.wo, ux, uy, &wi, &pdf);
+    Lobe lobe;
+    V3 fcos = bsdf_sample(m, s.wo, ux, uy, &wi, &pdf, &lobe);
     pdf *= rr;
     *wi_out = wi;
     float absCosOut = fabsf(wi.z);
     if (is_zero(fcos)) return false;
     *T = *T * (fcos * (1.f / pdf));
     bool delta = is_delta(m);
-    float prevRev = delta ? pdf : bsdf_pdf(m, wi, s.wo) * rr;
+    float prevRev = delta ? pdf : bsdf_pdf(m, wi, s.wo, lobe) * rr;
     if (delta) {
         *vc = (absCosOut / pdf) * (prevRev * *vc);
         *vcm = 0.f;
@@ -387,12 +389,13 @@ __global__ void TRB_EB_BOUNDS k_eye_bounce(const __grid_constant__ WaveParams p,
                 float connA = es.sel_pdf * es.area_pdf;
                 float connW = connA * d2 / cosAtLight;
                 float dirPdfW = TRB_INV_TWOPI;
-                Li = bsdf_eval(m, s.wo, wi) * (1.f / connW) * T * es.radiance;
+                const Lobe lobe = glossy_lobe(m, s.wo, wi);
+                Li = bsdf_eval(m, s.wo, wi, lobe) * (1.f / connW) * T * es.radiance;
                 if (!is_zero(Li)) {
                     sr = visibility_ray(s.p, es.pos);
-                    float lightRevW = bsdf_pdf(m, s.wo, wi) * rr;
+                    float lightRevW = bsdf_pdf(m, s.wo, wi, lobe) * rr;
                     float lightWeight = lightRevW / connW;
-                    float eyePrevRevW = bsdf_pdf(m, wi, s.wo) * rr;
+                    float eyePrevRevW = bsdf_pdf(m, wi, s.wo, lobe) * rr;
                     float eyeCurRevA = cosAtEye * (1.f / d2) * dirPdfW;
                     float eyeWeight = eyeCurRevA * (vcm + eyePrevRevW * vc);
                     float mis = 1.f / (lightWeight + 1.f + eyeWeight);
@@ -494,12 +497,13 @@ __device__ __forceinline__ bool cv_evaluate(const WaveParams& p, int pair, float
     const float lrr = d.w, err = (emat & EV_RR_HALF) ? 0.5f : 1.f;  // PathVertex::rr of the two vertices
     Mat m = load_mat(p.sc.mats, emat & ~EV_RR_HALF);
     if (TEX && m.tex) { const float4 t = p.ev_tex[slot]; apply_tex(p.sc, m, __float_as_int(t.x), t.y, t.z); }
-    V3 Li = bsdf_eval(lm, l_wo, l_wi) * bsdf_eval(m, e_wo, e_wi);
+    const Lobe ll = glossy_lobe(lm, l_wo, l_wi), le = glossy_lobe(m, e_wo, e_wi);   // two powf instead of six
+    V3 Li = bsdf_eval(lm, l_wo, l_wi, ll) * bsdf_eval(m, e_wo, e_wi, le);
     Li = Li * (mk(d.x, d.y, d.z) * mk(ed.x, ed.y, ed.z) * invD2);
-    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi) * lrr;
-    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo) * lrr;
-    float lightRevW = bsdf_pdf(m, e_wo, e_wi) * err;
-    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo) * err;
+    float eyeRevW = bsdf_pdf(lm, l_wo, l_wi, ll) * lrr;
+    float lightPrevRevW = bsdf_pdf(lm, l_wi, l_wo, ll) * lrr;
+    float lightRevW = bsdf_pdf(m, e_wo, e_wi, le) * err;
+    float eyePrevRevW = bsdf_pdf(m, e_wi, e_wo, le) * err;
     float lightRevA = lightRevW * (cosL) * invD2;
     float eyeRevA = eyeRevW * (cosE) * invD2;
     float lightWeight = lightRevA * (a.w + lightPrevRevW * b.w);

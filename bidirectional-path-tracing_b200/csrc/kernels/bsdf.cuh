@@ -99,48 +99,69 @@ __device__ __forceinline__ float phong_lobe_pdf(V3 v, float exponent) {  // math
 }
 
 // ---- eval / pdf / sample ---------------------------------------------------------------------------
-__device__ __forceinline__ V3 glossy_eval(const Mat& m, V3 wo, V3 wi) {  // phong.h:61-74 == mixture.h:60-73
+// The Phong lobe of a glossy material sees (wo, wi) only through c = dot(wi, reflect_z(wo)).  Reflecting wi instead gives the same float:
+// the products commute and are summed in the same order, and nothing is contracted (-fmad=false).  So the eval of phong.h:61-74, the pdf of
+// phong.h:76-87 for (wo, wi) and that pdf for (wi, wo) - what every connection of bdpt.h asks of a vertex - share ONE powf(c, ns); its
+// value is bit for bit what each of them computed on its own (ncu, round 2: the three inlined powf were 40 % of k_connect_vertices'
+// warp instructions at 6 active lanes).
+struct Lobe { float c, pw; };   // c = dot(wi, reflect_z(wo)); pw = powf(c, ns) when c >= 0
+__device__ __forceinline__ Lobe glossy_lobe(const Mat& m, V3 wo, V3 wi) {
+    Lobe l; l.c = 0.f; l.pw = 0.f;
+    if (m.cls == trb::MAT_PHONG || m.cls == trb::MAT_MIXTURE) {
+        l.c = dot(wi, reflect_z(wo));
+        l.pw = l.c >= 0.f ? v_powf(l.c, m.ns) : 0.f;
+    }
+    return l;
+}
+// powf(min(max(c, 0), 1), e) from the lobe's powf(c, e): the clamp only matters outside [0, 1] (and for a NaN, which fmaxf drops)
+__device__ __forceinline__ float lobe_pow_clamped(const Lobe& l, float e) {
+    if (l.c >= 0.f && l.c <= 1.f) return l.pw;
+    if (l.c > 1.f) return 1.f;                                      // powf(1, e)
+    return e > 0.f ? 0.f : (e == 0.f ? 1.f : v_powf(0.f, e));      // powf(0, e)
+}
+
+__device__ __forceinline__ V3 glossy_eval(const Mat& m, V3 wo, V3 wi, const Lobe& l) {  // phong.h:61-74 == mixture.h:60-73
     V3 val = mk(0.f);
     if (wi.z >= 0.f && wo.z >= 0.f) {
         val = val + m.kd * TRB_INV_PI;
         float e = m.ns;
-        float cosTheta = fminf(fmaxf(dot(wi, reflect_z(wo)), 0.f), 1.f);
-        val = val + m.ks * (e + 2) * TRB_INV_TWOPI * v_powf(cosTheta, e);
+        val = val + m.ks * (e + 2) * TRB_INV_TWOPI * lobe_pow_clamped(l, e);
         val = val * m.scale;
         val = val * wi.z;
     }
     return val;
 }
 
-__device__ __forceinline__ V3 bsdf_eval(const Mat& m, V3 wo, V3 wi) {
+__device__ __forceinline__ V3 bsdf_eval(const Mat& m, V3 wo, V3 wi, const Lobe& l) {
     switch (m.cls) {
         case trb::MAT_DIFFUSE:
             if (wi.z >= 0.f && wo.z >= 0.f) return m.kd * TRB_INV_PI * wi.z;  // diffuse.h:35-43
             return mk(0.f);
         case trb::MAT_PHONG:
-        case trb::MAT_MIXTURE: return glossy_eval(m, wo, wi);
+        case trb::MAT_MIXTURE: return glossy_eval(m, wo, wi, l);
         default: return mk(0.f);  // delta lobes: perfectmirror.h:33-38, glass.h:55-58
     }
 }
 
-__device__ __forceinline__ float phong_pdf(const Mat& m, V3 wo, V3 wi) {  // phong.h:76-87
-    Frame rf = make_frame(reflect_z(wo));
-    V3 s = to_local(rf, wi);
-    return phong_lobe_pdf(s, m.ns);
-}
+// phong.h:76-87: Frame(reflect(wo)).toLocal(wi).z is the lobe's c
+__device__ __forceinline__ float phong_pdf(const Mat& m, const Lobe& l) { return l.c >= 0.f ? (m.ns + 2) * TRB_INV_TWOPI * l.pw : 0.f; }
 
-__device__ __forceinline__ float bsdf_pdf(const Mat& m, V3 wo, V3 wi) {
+// `l`: the lobe of (wo, wi) or of (wi, wo) - the same
+__device__ __forceinline__ float bsdf_pdf(const Mat& m, V3 wo, V3 wi, const Lobe& l) {
     switch (m.cls) {
         case trb::MAT_DIFFUSE: return cosine_hemisphere_pdf(wi);  // diffuse.h:45-50
-        case trb::MAT_PHONG: return phong_pdf(m, wo, wi);
+        case trb::MAT_PHONG: return phong_pdf(m, l);
         case trb::MAT_MIXTURE: {  // mixture.h:75-93
-            float pp = phong_pdf(m, wo, wi);
+            float pp = phong_pdf(m, l);
             float pd = cosine_hemisphere_pdf(wi);
             return (pp * m.sw) + (pd * (1.f - m.sw));
         }
         default: return 0.f;
     }
 }
+// one-off queries
+__device__ __forceinline__ V3 bsdf_eval(const Mat& m, V3 wo, V3 wi) { return bsdf_eval(m, wo, wi, glossy_lobe(m, wo, wi)); }
+__device__ __forceinline__ float bsdf_pdf(const Mat& m, V3 wo, V3 wi) { return bsdf_pdf(m, wo, wi, glossy_lobe(m, wo, wi)); }
 
 __device__ __forceinline__ float fresnel_dielectric(float eta_i, float eta_t, float cos_i, float cos_t) {  // glass.h:40-53
     float eta = eta_i / eta_t;
@@ -151,20 +172,25 @@ __device__ __forceinline__ float fresnel_dielectric(float eta_i, float eta_t, fl
     return (rPar * rPar + rPer * rPer) * 0.5f;
 }
 
-// BSDF::sample: writes wi and pdf, returns f*cos
-__device__ __forceinline__ V3 bsdf_sample(const Mat& m, V3 wo, float ux, float uy, V3* wi, float* pdf) {
+// BSDF::sample: writes wi and pdf, returns f*cos; `lobe_out`: the lobe of (wo, wi), for the caller's reverse pdf
+__device__ __forceinline__ V3 bsdf_sample(const Mat& m, V3 wo, float ux, float uy, V3* wi, float* pdf, Lobe* lobe_out = nullptr) {
+    Lobe lobe; lobe.c = 0.f; lobe.pw = 0.f;
+    V3 ret;
     switch (m.cls) {
         case trb::MAT_DIFFUSE: {  // diffuse.h:52-61
             *wi = sq_to_cosine_hemisphere(ux, uy);
             *pdf = cosine_hemisphere_pdf(*wi);
-            return bsdf_eval(m, wo, *wi);
+            ret = bsdf_eval(m, wo, *wi, lobe);
+            break;
         }
         case trb::MAT_PHONG: {  // phong.h:89-105
             Frame rf = make_frame(reflect_z(wo));
             V3 s = sq_to_phong_lobe(ux, uy, m.ns);
             *pdf = phong_lobe_pdf(s, m.ns);
             *wi = to_world(rf, s);
-            return glossy_eval(m, wo, *wi);
+            lobe = glossy_lobe(m, wo, *wi);
+            ret = glossy_eval(m, wo, *wi, lobe);
+            break;
         }
         case trb::MAT_MIXTURE: {  // mixture.h:95-151
             if (ux < m.sw) {
@@ -174,14 +200,16 @@ __device__ __forceinline__ V3 bsdf_sample(const Mat& m, V3 wo, float ux, float u
             } else {
                 *wi = sq_to_cosine_hemisphere((ux - m.sw) / (1.f - m.sw), uy);
             }
-            V3 val = glossy_eval(m, wo, *wi);
-            *pdf = bsdf_pdf(m, wo, *wi);
-            return val;
+            lobe = glossy_lobe(m, wo, *wi);
+            ret = glossy_eval(m, wo, *wi, lobe);
+            *pdf = bsdf_pdf(m, wo, *wi, lobe);
+            break;
         }
         case trb::MAT_MIRROR: {  // perfectmirror.h:48-59
             *pdf = 1.f;
             *wi = reflect_z(wo);
-            return mk(1.f);
+            ret = mk(1.f);
+            break;
         }
         default: {  // glass.h:60-108
             *pdf = 1.f;
@@ -194,11 +222,13 @@ __device__ __forceinline__ V3 bsdf_sample(const Mat& m, V3 wo, float ux, float u
             float cos_t = sqrtf(fmaxf(0.f, 1.f - sin2_t));
             cos_t = entering ? -cos_t : cos_t;
             float fr = fresnel_dielectric(eta_i, eta_t, fabsf(wo.z), fabsf(cos_t));
-            if (ux < fr) { *wi = reflect_z(wo); return mk(1.f); }
-            *wi = mk(eta * -wo.x, eta * -wo.y, cos_t);
-            return m.tf;
+            if (ux < fr) { *wi = reflect_z(wo); ret = mk(1.f); }
+            else { *wi = mk(eta * -wo.x, eta * -wo.y, cos_t); ret = m.tf; }
+            break;
         }
     }
+    if (lobe_out) *lobe_out = lobe;
+    return ret;
 }
 
 }  // namespace trbk

@@ -228,9 +228,10 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_di_resolve(const __grid_constant_
         if (!contributes) return;
         V3 wiL = mk(a.x, a.y, a.z);
         if (dp.strategy == DI_MIS) {
-            float bsdfPdf = bsdf_pdf(m, v.wo, wiL);
+            const Lobe lobe = glossy_lobe(m, v.wo, wiL);
+            float bsdfPdf = bsdf_pdf(m, v.wo, wiL, lobe);
             float weight = di_balance(float(dp.emitter_samples), a.w * b.x, float(dp.bsdf_samples), bsdfPdf);
-            c = di_radiance(p.sc, id) * bsdf_eval(m, v.wo, wiL) * weight * (1.f / a.w) * (1.f / b.x);
+            c = di_radiance(p.sc, id) * bsdf_eval(m, v.wo, wiL, lobe) * weight * (1.f / a.w) * (1.f / b.x);
         } else {
             c = di_radiance(p.sc, id) * bsdf_eval(m, v.wo, wiL) * (1.f / a.w) * (1.f / b.x);
         }

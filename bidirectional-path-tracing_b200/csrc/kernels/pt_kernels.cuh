@@ -277,10 +277,11 @@ __global__ void __launch_bounds__(TRB_BLOCK) k_pt_emitter_resolve(const __grid_c
     V3 Li = pt_vis_emission(p, true, vmat);
     V3 wiL = mk(a.x, a.y, a.z);
     float a2s = a.w, emitterPdf = b.x, emitterAreaPdf = b.y;
-    float bsdfPdf = bsdf_pdf(m, v.wo, wiL);
+    const Lobe lobe = glossy_lobe(m, v.wo, wiL);   // one powf for the pdf and the value (bsdf.cuh)
+    float bsdfPdf = bsdf_pdf(m, v.wo, wiL, lobe);
     float f = float(pt.emitter_samples) * (emitterAreaPdf * emitterPdf * (1.f / a2s)), g = float(pt.bsdf_samples) * bsdfPdf;
     float weight = f / (f + g);
-    V3 c = weight * Li * bsdf_eval(m, v.wo, wiL) * (1.f / emitterAreaPdf) * (1.f / emitterPdf) * a2s;
+    V3 c = weight * Li * bsdf_eval(m, v.wo, wiL, lobe) * (1.f / emitterAreaPdf) * (1.f / emitterPdf) * a2s;
     float4 acc = st[2];
     st[2] = make_float4(acc.x + c.x, acc.y + c.y, acc.z + c.z, 0.f);
 }
