@@ -508,13 +508,16 @@ def run_ours(args):
     ctx.render_bdpt(desc, out=frame)   # untimed: first use of the buffer
     barrier()
     t0 = time.perf_counter()
+    e2e_step_ms = []
     for _ in range(e2e_steps):
+        ts = time.perf_counter()
         ctx.refresh_scene()
         img, _ = ctx.render_bdpt(desc, out=frame)
         if world > 1:  # the partial frame buffers meet on rank 0 (host result is rank 0's sum)
             part = torch.from_numpy(img).cuda()
             dist.reduce(part, dst=0, op=dist.ReduceOp.SUM)
             img = part.cpu().numpy()
+        e2e_step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
     barrier()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
@@ -555,7 +558,7 @@ def run_ours(args):
                "clocks": clk, "gpu_launches": int(agg.get("launches", 0)),
                "scene_upload": upload_info,
                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(ctx.scene_bytes()), "d2h_bytes_per_step": W * H * 3 * 4,
-                       "steps": e2e_steps, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (frame buffer out into the caller's pinned host array)",
+                       "steps": e2e_steps, "step_ms": e2e_step_ms, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (frame buffer out into the caller's pinned host array)",
                        "note": "the scene is re-sent from pinned memory EVERY step (the contract's letter: a step's inputs cross the bus inside the timed "
                                "region); a caller uploads a scene once and renders many frames - c3.e2e / c5.e2e are measured that way"},
                "mrays_per_s": {"closest": agg["rays_closest"] / (tot_ms * 1e-3) / 1e6, "any": agg["rays_any"] / (tot_ms * 1e-3) / 1e6,
