@@ -331,3 +331,22 @@ def test_scene_hash_follows_content(trb):
         assert v not in seen, edit
         seen.add(v)
     assert h(trb.HostScene.load_npz(GOLD / "scene_hardlight.npz")) not in seen
+
+
+def test_phong_lobe_cosine_is_symmetric_bit_for_bit():
+    """bsdf.cuh: glossy_lobe - the value, the pdf and the reverse pdf of a glossy connection share one powf because
+    dot(wi, reflect_z(wo)) and dot(wo, reflect_z(wi)) are the same float: the products commute, negation is exact, and the sums are
+    taken in the same order (device code is built -fmad=false, so nothing is contracted).  Checked here in float32 on 10^6 random pairs,
+    including denormals and huge values."""
+    rng = np.random.default_rng(11)
+    n = 1_000_000
+    scale = np.float32(10.0) ** rng.integers(-30, 30, (n, 1)).astype(np.float32)
+    wo = (rng.standard_normal((n, 3)).astype(np.float32) * scale).astype(np.float32)
+    wi = (rng.standard_normal((n, 3)).astype(np.float32) * scale[::-1]).astype(np.float32)
+
+    def dot_reflected(a, b):   # dot(a, reflect_z(b)) = (a.x * -b.x + a.y * -b.y) + a.z * b.z, float32 at every step
+        return (a[:, 0] * (-b[:, 0]) + a[:, 1] * (-b[:, 1])) + a[:, 2] * b[:, 2]
+
+    with np.errstate(over="ignore", invalid="ignore"):
+        c1, c2 = dot_reflected(wi, wo), dot_reflected(wo, wi)
+    assert c1.dtype == np.float32 and np.array_equal(c1.view(np.uint32), c2.view(np.uint32))
