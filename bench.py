@@ -504,23 +504,29 @@ def run_ours(args):
     # ---- end to end through the host-buffer C ABI call: scene H2D (pinned) + render + frame buffer D2H ----
     e2e_steps = max(3, args.steps)
     ctx.refresh_scene()   # untimed: a device-built scene makes its pinned staging copy (the host side of the transfer) on the first refresh
-    frame = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True).numpy()   # the caller's frame buffer, pinned: the D2H copy lands in it
-    ctx.render_bdpt(desc, out=frame)   # untimed: first use of the buffer
-    if world > 1:                      # ... and of the reduce of this shape
-        part = torch.from_numpy(frame).cuda()
+    frame_t = torch.empty((H, W, 3), dtype=torch.float32, pin_memory=True)   # the caller's frame buffer, pinned: the D2H copy lands in it
+    frame = frame_t.numpy()
+    part = torch.zeros(H, W, 3, device="cuda", dtype=torch.float32) if world > 1 else None
+
+    def e2e_step():
+        ctx.refresh_scene()
+        if world == 1:
+            ctx.render_bdpt(desc, out=frame)
+            return
+        # N > 1: each rank renders its samples into a device frame, the partial frames meet on rank 0 over NCCL, rank 0 reads the sum back
+        ctx.render_bdpt_device(desc, part.data_ptr())
         dist.reduce(part, dst=0, op=dist.ReduceOp.SUM)
-        part.cpu()
+        if rank == 0:
+            frame_t.copy_(part)
+        torch.cuda.synchronize()
+
+    e2e_step()   # untimed: first use of the buffers and of the reduce of this shape
     barrier()
     t0 = time.perf_counter()
     e2e_step_ms = []
     for _ in range(e2e_steps):
         ts = time.perf_counter()
-        ctx.refresh_scene()
-        img, _ = ctx.render_bdpt(desc, out=frame)
-        if world > 1:  # the partial frame buffers meet on rank 0 (host result is rank 0's sum)
-            part = torch.from_numpy(img).cuda()
-            dist.reduce(part, dst=0, op=dist.ReduceOp.SUM)
-            img = part.cpu().numpy()
+        e2e_step()
         e2e_step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
     barrier()
     e2e_s = time.perf_counter() - t0
@@ -562,7 +568,7 @@ def run_ours(args):
                "clocks": clk, "gpu_launches": int(agg.get("launches", 0)),
                "scene_upload": upload_info,
                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(ctx.scene_bytes()), "d2h_bytes_per_step": W * H * 3 * 4,
-                       "steps": e2e_steps, "step_ms": e2e_step_ms, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (frame buffer out into the caller's pinned host array)",
+                       "steps": e2e_steps, "step_ms": e2e_step_ms, "timing": "host wall clock around trb_scene_refresh + trb_render_bdpt (frame buffer out into the caller's pinned host array; N > 1: trb_render_bdpt_device, NCCL reduce of the device frames, rank 0 reads the sum into its pinned array)",
                        "note": "the scene is re-sent from pinned memory EVERY step (the contract's letter: a step's inputs cross the bus inside the timed "
                                "region); a caller uploads a scene once and renders many frames - c3.e2e / c5.e2e are measured that way"},
                "mrays_per_s": {"closest": agg["rays_closest"] / (tot_ms * 1e-3) / 1e6, "any": agg["rays_any"] / (tot_ms * 1e-3) / 1e6,
