@@ -378,10 +378,13 @@ def extra_block(trb, torch, name, spp, fb, flush, args):
         ctx.render_bdpt(desc, out=frame)   # untimed: first use of the buffer
         torch.cuda.synchronize()
         t0 = time.perf_counter()
+        step_ms = []
         for _ in range(steps):
+            ts = time.perf_counter()
             ctx.render_bdpt(desc, out=frame)
+            step_ms.append(round((time.perf_counter() - ts) * 1e3, 2))
         e2e_s = time.perf_counter() - t0
-        blk["e2e"] = {"value": samples * steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": W * H * 3 * 4,
+        blk["e2e"] = {"value": samples * steps / e2e_s / 1e6, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": W * H * 3 * 4, "step_ms": step_ms,
                       "timing": "host wall clock around trb_render_bdpt (frame buffer out into the caller's pinned host array); the scene (%.2f GB) was uploaded once before" % (ctx.scene_bytes() / 1e9)}
         ser = serial_pass(trb, torch, ctx, fb, flush, wl, W, H, spp, 0, spp, args.wave)
         blk["stage_ms_serial"] = {k: ser[k] for k in ("ms_total", "ms_trace_closest", "ms_trace_any", "ms_logic")}
